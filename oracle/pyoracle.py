@@ -1,0 +1,306 @@
+"""ctypes bindings for the oracle libraries — TEST INFRASTRUCTURE, not product code.
+
+  RefExtractor   the reference's own ORBextractor.cc compiled unchanged on the minicv shim
+                 (oracle/_ref/liborbref_{strict,native}.so, built by oracle/Makefile)
+  port           oracle/liborb_oracle.so: CPU restatement of the path + minicv primitives
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+_u8p = C.POINTER(C.c_uint8)
+
+
+def _ptr(a, t=_u8p):
+    return a.ctypes.data_as(t)
+
+
+def build(quiet=True):
+    """(Re)build the oracle libraries; the _ref targets only where /root/reference exists."""
+    r = subprocess.run(["make", "-C", HERE, "all"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("oracle build failed:\n" + r.stdout + r.stderr)
+    if not quiet:
+        print(r.stdout)
+
+
+def ref_path(mode="strict"):
+    return os.path.join(HERE, "_ref", f"liborbref_{mode}.so")
+
+
+def have_ref(mode="strict"):
+    return os.path.exists(ref_path(mode))
+
+
+_ref_libs = {}
+
+
+def _ref_lib(mode):
+    if mode not in _ref_libs:
+        lib = C.CDLL(ref_path(mode))
+        lib.orbref_create.restype = C.c_void_p
+        lib.orbref_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        lib.orbref_destroy.argtypes = [C.c_void_p]
+        lib.orbref_extract.restype = C.c_int
+        lib.orbref_extract.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                       _u8p, C.c_int, C.POINTER(C.c_int)]
+        lib.orbref_pyramid.restype = C.c_int
+        lib.orbref_pyramid.argtypes = [C.c_void_p, C.c_int, _u8p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        lib.orbref_tables.restype = C.c_int
+        lib.orbref_tables.argtypes = [C.c_void_p] + [C.POINTER(C.c_float)] * 4 + [C.POINTER(C.c_int)] * 2
+        lib.orbref_scale_factor.restype = C.c_float
+        lib.orbref_scale_factor.argtypes = [C.c_void_p]
+        _ref_libs[mode] = lib
+    return _ref_libs[mode]
+
+
+class RefExtractor:
+    """The reference ORB_SLAM3::ORBextractor (ORBextractor.h:43-109) behind ref_wrap.cpp."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, mode="strict"):
+        self.lib = _ref_lib(mode)
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self.h = self.lib.orbref_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.orbref_destroy(self.h)
+            self.h = None
+
+    def extract(self, img, lap=(0, 1000)):
+        """-> (mono_index, keypoints[KP_DTYPE], descriptors[n,32])"""
+        cap = self.nfeatures + 4 * self.nlevels + 64
+        kps = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        n = C.c_int(0)
+        if img is None or img.size == 0:
+            mono = self.lib.orbref_extract(self.h, None, 0, 0, 0, lap[0], lap[1], None, None, 0, C.byref(n))
+            return mono, kps[:0], desc[:0]
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        h, w = img.shape
+        mono = self.lib.orbref_extract(self.h, _ptr(img), w, h, w, lap[0], lap[1], kps.ctypes.data_as(C.c_void_p),
+                                       _ptr(desc), cap, C.byref(n))
+        assert n.value <= cap
+        return mono, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def pyramid(self, level):
+        """Padded plane (h+38, w+38) of the last extract() call."""
+        w, h = C.c_int(0), C.c_int(0)
+        if self.lib.orbref_pyramid(self.h, level, None, C.byref(w), C.byref(h)) != 0:
+            return None
+        out = np.zeros((h.value + 38, w.value + 38), dtype=np.uint8)
+        self.lib.orbref_pyramid(self.h, level, _ptr(out), None, None)
+        return out
+
+    def tables(self):
+        nl = self.nlevels
+        f = [np.zeros(nl, dtype=np.float32) for _ in range(4)]
+        nf = np.zeros(nl, dtype=np.int32)
+        um = np.zeros(16, dtype=np.int32)
+        self.lib.orbref_tables(self.h, *[_ptr(a, C.POINTER(C.c_float)) for a in f], _ptr(nf, C.POINTER(C.c_int)),
+                               _ptr(um, C.POINTER(C.c_int)))
+        return dict(scale=f[0], inv_scale=f[1], sigma2=f[2], inv_sigma2=f[3], nfeatures=nf, umax=um,
+                    scale_factor=self.lib.orbref_scale_factor(self.h))
+
+
+# --------------------------------------------------------------------------------------------
+# the port oracle (oracle/liborb_oracle.so)
+# --------------------------------------------------------------------------------------------
+_i32p = C.POINTER(C.c_int32)
+_f32p = C.POINTER(C.c_float)
+_port = None
+
+
+def port_path():
+    return os.path.join(HERE, "liborb_oracle.so")
+
+
+def port_lib():
+    global _port
+    if _port is None:
+        if not os.path.exists(port_path()):
+            build()
+        lib = C.CDLL(port_path())
+        lib.orbo_create.restype = C.c_void_p
+        lib.orbo_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int]
+        lib.orbo_destroy.argtypes = [C.c_void_p]
+        lib.orbo_extract.restype = C.c_int
+        lib.orbo_extract.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, _u8p,
+                                     C.c_int, C.POINTER(C.c_int)]
+        lib.orbo_pyramid.restype = C.c_int
+        lib.orbo_pyramid.argtypes = [C.c_void_p, C.c_int, _u8p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        lib.orbo_tables.restype = C.c_int
+        lib.orbo_tables.argtypes = [C.c_void_p] + [_f32p] * 4 + [C.POINTER(C.c_int)] * 2
+        lib.orbo_candidates.restype = C.c_int
+        lib.orbo_candidates.argtypes = [C.c_void_p, C.c_int, _i32p, C.c_int]
+        lib.orbo_level_keypoints.restype = C.c_int
+        lib.orbo_level_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        lib.orbo_quadtree.restype = C.c_int
+        lib.orbo_quadtree.argtypes = [_i32p, C.c_int, C.c_int, C.c_int, C.c_int, _i32p, C.c_int]
+        lib.orbo_sort_check.argtypes = [C.POINTER(C.c_int64), C.c_int, _i32p, _i32p]
+        lib.orbo_rbrief.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, _u8p]
+        lib.orbo_sincosf.argtypes = [_f32p, _f32p, _f32p, C.c_int]
+        lib.orbo_hamming.restype = C.c_int
+        lib.orbo_hamming.argtypes = [_u8p, _u8p]
+        lib.orbo_match_top2.argtypes = [_u8p, C.c_int, _u8p, C.c_long, _i32p, _i32p, _i32p, _i32p, C.c_int]
+        lib.orbo_match_stereo_banded.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_void_p, _u8p, C.c_int, _f32p, C.c_int,
+                                                 C.c_float, _i32p, _i32p]
+        lib.orbo_extract_many.restype = C.c_long
+        lib.orbo_extract_many.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, _u8p, C.c_int,
+                                          C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        lib.minicv_resize_linear.argtypes = [_u8p, C.c_int, C.c_int, _u8p, C.c_int, C.c_int]
+        lib.minicv_border101.argtypes = [_u8p, C.c_int, C.c_int, _u8p, C.c_int]
+        lib.minicv_fast.restype = C.c_int
+        lib.minicv_fast.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i32p, C.c_int]
+        lib.minicv_gauss7.argtypes = [_u8p, C.c_int, C.c_int, _u8p]
+        lib.minicv_fast_atan2.argtypes = [_f32p, _f32p, _f32p, C.c_int]
+        _port = lib
+    return _port
+
+
+class PortExtractor:
+    """The restated extractor (orb_oracle.cpp), same call shape as RefExtractor."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, mode="strict"):
+        self.lib = port_lib()
+        self.nlevels, self.nfeatures = nlevels, nfeatures
+        self.h = self.lib.orbo_create(nfeatures, scale_factor, nlevels, ini_th, min_th, 0 if mode == "strict" else 1)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.orbo_destroy(self.h)
+            self.h = None
+
+    def extract(self, img, lap=(0, 1000)):
+        cap = self.nfeatures + 8 * self.nlevels + 64
+        kps = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        n = C.c_int(0)
+        if img is None or img.size == 0:
+            return self.lib.orbo_extract(self.h, None, 0, 0, 0, lap[0], lap[1], None, None, 0, C.byref(n)), kps[:0], desc[:0]
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        h, w = img.shape
+        mono = self.lib.orbo_extract(self.h, _ptr(img), w, h, w, lap[0], lap[1], kps.ctypes.data_as(C.c_void_p),
+                                     _ptr(desc), cap, C.byref(n))
+        assert mono >= -1, "oracle keypoint buffer too small"
+        return mono, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def pyramid(self, level):
+        w, h = C.c_int(0), C.c_int(0)
+        if self.lib.orbo_pyramid(self.h, level, None, C.byref(w), C.byref(h)) != 0:
+            return None
+        out = np.zeros((h.value + 38, w.value + 38), dtype=np.uint8)
+        self.lib.orbo_pyramid(self.h, level, _ptr(out), None, None)
+        return out
+
+    def candidates(self, level):
+        n = self.lib.orbo_candidates(self.h, level, None, 0)
+        out = np.zeros((max(n, 1), 3), dtype=np.int32)
+        self.lib.orbo_candidates(self.h, level, _ptr(out, _i32p), n)
+        return out[:n]
+
+    def level_keypoints(self, level):
+        n = self.lib.orbo_level_keypoints(self.h, level, None, 0)
+        out = np.zeros(max(n, 1), dtype=KP_DTYPE)
+        self.lib.orbo_level_keypoints(self.h, level, out.ctypes.data_as(C.c_void_p), n)
+        return out[:n]
+
+    def tables(self):
+        nl = self.nlevels
+        f = [np.zeros(nl, dtype=np.float32) for _ in range(4)]
+        nf = np.zeros(nl, dtype=np.int32)
+        um = np.zeros(16, dtype=np.int32)
+        self.lib.orbo_tables(self.h, *[_ptr(a, _f32p) for a in f], _ptr(nf, C.POINTER(C.c_int)), _ptr(um, C.POINTER(C.c_int)))
+        return dict(scale=f[0], inv_scale=f[1], sigma2=f[2], inv_sigma2=f[3], nfeatures=nf, umax=um)
+
+
+def quadtree(cand, width, height, N):
+    cand = np.ascontiguousarray(cand, dtype=np.int32).reshape(-1, 3)
+    keep = np.zeros(N + 8, dtype=np.int32)
+    n = port_lib().orbo_quadtree(_ptr(cand, _i32p), len(cand), width, height, N, _ptr(keep, _i32p), len(keep))
+    assert n <= len(keep)
+    return keep[:n].copy()
+
+
+def sort_check(keys):
+    keys = np.ascontiguousarray(keys, dtype=np.int64)
+    a = np.zeros(len(keys), dtype=np.int32)
+    b = np.zeros(len(keys), dtype=np.int32)
+    port_lib().orbo_sort_check(keys.ctypes.data_as(C.POINTER(C.c_int64)), len(keys), _ptr(a, _i32p), _ptr(b, _i32p))
+    return a, b
+
+
+def hamming(a, b):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = np.ascontiguousarray(b, dtype=np.uint8)
+    return port_lib().orbo_hamming(_ptr(a), _ptr(b))
+
+
+def match_top2(q, db, threads=1):
+    q = np.ascontiguousarray(q, dtype=np.uint8).reshape(-1, 32)
+    db = np.ascontiguousarray(db, dtype=np.uint8).reshape(-1, 32)
+    out = [np.zeros(len(q), dtype=np.int32) for _ in range(4)]
+    port_lib().orbo_match_top2(_ptr(q), len(q), _ptr(db), len(db), *[_ptr(o, _i32p) for o in out], threads)
+    return out  # idx1, d1, idx2, d2
+
+
+def match_stereo_banded(kl, dl, kr, dr, scale_factors, n_rows, max_d):
+    kl = np.ascontiguousarray(kl); kr = np.ascontiguousarray(kr)
+    dl = np.ascontiguousarray(dl, dtype=np.uint8); dr = np.ascontiguousarray(dr, dtype=np.uint8)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    bi = np.zeros(len(kl), dtype=np.int32); bd = np.zeros(len(kl), dtype=np.int32)
+    port_lib().orbo_match_stereo_banded(kl.ctypes.data_as(C.c_void_p), _ptr(dl), len(kl), kr.ctypes.data_as(C.c_void_p),
+                                        _ptr(dr), len(kr), _ptr(sf, _f32p), n_rows, max_d, _ptr(bi, _i32p), _ptr(bd, _i32p))
+    return bi, bd
+
+
+def extract_many(imgs, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, lap=(0, 1000), threads=0,
+                 mode="strict"):
+    imgs = np.ascontiguousarray(imgs, dtype=np.uint8)
+    n, h, w = imgs.shape
+    return port_lib().orbo_extract_many(nfeatures, scale_factor, nlevels, ini_th, min_th, 0 if mode == "strict" else 1,
+                                        _ptr(imgs), n, w, h, lap[0], lap[1], threads)
+
+
+def resize_linear(src, dw, dh):
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    dst = np.zeros((dh, dw), dtype=np.uint8)
+    port_lib().minicv_resize_linear(_ptr(src), src.shape[1], src.shape[0], _ptr(dst), dw, dh)
+    return dst
+
+
+def border101(src, b=19):
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    dst = np.zeros((src.shape[0] + 2 * b, src.shape[1] + 2 * b), dtype=np.uint8)
+    port_lib().minicv_border101(_ptr(src), src.shape[1], src.shape[0], _ptr(dst), b)
+    return dst
+
+
+def fast(src, threshold, nms=True):
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    cap = src.size // 2 + 16
+    out = np.zeros((cap, 3), dtype=np.int32)
+    n = port_lib().minicv_fast(_ptr(src), src.shape[1], src.shape[0], src.shape[1], threshold, int(nms), _ptr(out, _i32p), cap)
+    return out[:n].copy()
+
+
+def gauss7(src):
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    dst = np.zeros_like(src)
+    port_lib().minicv_gauss7(_ptr(src), src.shape[1], src.shape[0], _ptr(dst))
+    return dst
+
+
+def fast_atan2(y, x):
+    y = np.ascontiguousarray(y, dtype=np.float32); x = np.ascontiguousarray(x, dtype=np.float32)
+    out = np.zeros_like(y)
+    port_lib().minicv_fast_atan2(_ptr(y, _f32p), _ptr(x, _f32p), _ptr(out, _f32p), len(y))
+    return out

@@ -1,0 +1,109 @@
+"""Deterministic synthetic inputs, integer-only so that numpy, the C oracle
+and the CUDA generator (csrc/synth.cu) agree bit-for-bit.
+
+There is no dataset offline (EuRoC/KITTI/RealSense streams are unavailable), so BASELINE.json's
+configs are measured on these procedurally textured frames and descriptor sets.
+"""
+import numpy as np
+
+K1 = np.uint64(0x9E3779B97F4A7C15)
+K2 = np.uint64(0xC2B2AE3D27D4EB4F)
+K3 = np.uint64(0x165667B19E3779F9)
+OCTAVES = ((4, 10), (8, 25), (16, 40), (32, 50), (64, 60))  # (lattice cell, amplitude)
+ORIGIN = 1024
+
+
+def _mix(z):
+    z = z.astype(np.uint64)
+    with np.errstate(over="ignore"):
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return z ^ (z >> np.uint64(31))
+
+
+def hash3(seed, a, b, c):
+    """splitmix64 finaliser of seed ^ a*K1 ^ b*K2 ^ c*K3 (uint64 wrap-around)."""
+    with np.errstate(over="ignore"):
+        a = np.asarray(a).astype(np.uint64) * K1
+        b = np.asarray(b).astype(np.uint64) * K2
+        c = np.asarray(c).astype(np.uint64) * K3
+    return _mix(np.uint64(seed) ^ a ^ b ^ c)
+
+
+def _tdiv(n, d):
+    """C-style integer division (truncation toward zero)."""
+    q = np.abs(n) // d
+    return np.where(n < 0, -q, q)
+
+
+def canvas(X, Y, seed):
+    """I(X, Y; seed) for integer canvas coordinates X, Y >= 64 (arrays broadcast)."""
+    X = np.asarray(X, dtype=np.int64)
+    Y = np.asarray(Y, dtype=np.int64)
+    X, Y = np.broadcast_arrays(X, Y)
+    val = np.full(X.shape, 128, dtype=np.int64)
+    for o, (c, amp) in enumerate(OCTAVES):
+        i, fx = X // c, X % c
+        j, fy = Y // c, Y % c
+
+        def g(ii, jj):
+            return (hash3(seed, o, ii, jj) & np.uint64(2047)).astype(np.int64) - 1024
+
+        num = (g(i, j) * (c - fx) * (c - fy) + g(i + 1, j) * fx * (c - fy)
+               + g(i, j + 1) * (c - fx) * fy + g(i + 1, j + 1) * fx * fy)
+        val += _tdiv(amp * num, 1024 * c * c)
+    ti, tj = X // 64, Y // 64
+    for dti in (-1, 0):
+        for dtj in (-1, 0):
+            for r in range(3):
+                hv = hash3(seed, 100 + r, ti + dti, tj + dtj)
+                ox = (hv & np.uint64(63)).astype(np.int64)
+                oy = ((hv >> np.uint64(6)) & np.uint64(63)).astype(np.int64)
+                w = 4 + ((hv >> np.uint64(12)) % np.uint64(36)).astype(np.int64)
+                h = 4 + ((hv >> np.uint64(20)) % np.uint64(36)).astype(np.int64)
+                delta = ((hv >> np.uint64(28)) % np.uint64(160)).astype(np.int64) - 80
+                filled = ((hv >> np.uint64(40)) % np.uint64(10)) < np.uint64(7)
+                x0 = (ti + dti) * 64 + ox
+                y0 = (tj + dtj) * 64 + oy
+                inside = (X >= x0) & (X < x0 + w) & (Y >= y0) & (Y < y0 + h)
+                edge = (X == x0) | (X == x0 + w - 1) | (Y == y0) | (Y == y0 + h - 1)
+                val += np.where(inside & (filled | edge), delta, 0)
+    return np.clip(val, 0, 255).astype(np.uint8)
+
+
+def frame(k, width, height, seed=42, right=False):
+    """Frame k of the synthetic stream: crop of the canvas at offset (3k, k); the stereo right
+    image is the same crop shifted by +16 px in X (so uR = uL - 16)."""
+    x = np.arange(width, dtype=np.int64)[None, :] + ORIGIN + 3 * k + (16 if right else 0)
+    y = np.arange(height, dtype=np.int64)[:, None] + ORIGIN + k
+    return np.ascontiguousarray(canvas(x, y, seed))
+
+
+def frames(k0, n, width, height, seed=42, right=False):
+    return np.stack([frame(k0 + i, width, height, seed, right) for i in range(n)])
+
+
+def descriptor_db(n, seed=7, start=0):
+    """n x 32 bytes: row r, 64-bit word j (little endian) = splitmix64 finaliser of hash3(seed, r, j, 0)."""
+    r = np.arange(start, start + n, dtype=np.uint64)[:, None]
+    j = np.arange(4, dtype=np.uint64)[None, :]
+    words = hash3(seed, r, j, 0)
+    return np.ascontiguousarray(words).view(np.uint8).reshape(n, 32)
+
+
+def queries_from_db(nq, n_db, db_seed=7, q_seed=11, flips=20):
+    """Query i = DB row (i*4999+17) mod n_db with `flips` distinct pseudo-random bit flips,
+    so the true nearest neighbour and its distance (= flips) are known."""
+    rows = (np.arange(nq, dtype=np.int64) * 4999 + 17) % n_db
+    q = np.empty((nq, 32), dtype=np.uint8)
+    for i, r in enumerate(rows):
+        d = descriptor_db(1, db_seed, int(r))[0].copy()
+        bits = set()
+        t = 0
+        while len(bits) < flips:
+            bits.add(int(hash3(q_seed, i, t, 1)) & 255)
+            t += 1
+        for b in bits:
+            d[b >> 3] ^= np.uint8(1 << (b & 7))
+        q[i] = d
+    return q, rows

@@ -1,0 +1,99 @@
+"""The port oracle (oracle/orb_oracle.cpp) against fixtures produced by the reference's own
+ORBextractor.cc (compiled unchanged on the minicv shim) and, where oracle/_ref is present,
+against that reference binary directly on fresh inputs."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from orb_slam3_ros2_b200 import synth
+
+E2E = ["euroc752", "d435i640", "kittiL", "kittiR", "hd1080", "milkv360", "init5x", "small320"]
+
+
+@pytest.mark.parametrize("name", E2E)
+def test_port_reproduces_reference_fixture(oracle, name):
+    g = load_golden(f"e2e_{name}.npz")
+    w, h, k, nf = int(g["w"]), int(g["h"]), int(g["k"]), int(g["nfeatures"])
+    lap = tuple(int(v) for v in g["lap"])
+    im = synth.frame(k, w, h, 42, bool(g["right"]))
+    assert hashlib.sha1(im.tobytes()).hexdigest() == str(g["img_sha1"])
+    for mode in ("strict", "native"):
+        e = oracle.PortExtractor(nfeatures=nf, mode=mode)
+        mono, kp, desc = e.extract(im, lap)
+        same = "native_same" in g.files and bool(g["native_same"])
+        src = "strict" if (mode == "strict" or same) else "native"
+        assert mono == int(g[f"{mode}_mono"])
+        assert np.array_equal(kp, g[f"{src}_kp"]), (name, mode)
+        assert np.array_equal(desc, g[f"{src}_desc"]), (name, mode)
+        if mode == "strict":
+            for l in range(8):
+                p = e.pyramid(l)
+                assert p.shape == tuple(g["pyr_shape"][l])
+                assert hashlib.sha1(p.tobytes()).hexdigest() == str(g["pyr_sha1"][l])
+
+
+def test_scale_tables_match_reference_constants(oracle):
+    t = oracle.PortExtractor(nfeatures=1000).tables()
+    assert list(t["nfeatures"]) == [217, 181, 151, 126, 105, 87, 73, 60]
+    assert list(t["umax"]) == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    assert np.allclose(t["scale"][1], 1.2000000477) and np.allclose(t["scale"][7], 3.5831816196)
+    assert list(oracle.PortExtractor(nfeatures=2000).tables()["nfeatures"]) == [434, 362, 302, 251, 209, 175, 145, 122]
+    assert list(oracle.PortExtractor(nfeatures=4000).tables()["nfeatures"]) == [869, 724, 603, 503, 419, 349, 291, 242]
+
+
+def test_empty_image_returns_minus_one(oracle):
+    mono, kp, desc = oracle.PortExtractor().extract(None)
+    assert mono == -1 and len(kp) == 0
+
+
+def test_introsort_port_equals_libstdcxx(oracle):
+    rng = np.random.default_rng(5)
+    for n in [0, 1, 2, 15, 16, 17, 18, 33, 64, 100, 128, 257, 512, 1000, 3000]:
+        for hi in (2, 5, 50, 1 << 40):
+            keys = rng.integers(0, hi, n)
+            a, b = oracle.sort_check(keys)
+            assert np.array_equal(a, b), (n, hi)
+    # adversarial shapes: sorted, reversed, organ pipe, all equal, median-of-3 killer (drives the heap-sort branch)
+    for n in (17, 200, 1024, 4096):
+        shapes = [np.arange(n), np.arange(n)[::-1], np.minimum(np.arange(n), n - np.arange(n)), np.zeros(n, dtype=np.int64)]
+        k = n // 2
+        killer = np.zeros(n, dtype=np.int64)
+        for i in range(k):
+            killer[i] = i + 1 if i % 2 == 0 else k + i + (k % 2 == 0)
+            killer[k + i] = 2 * (i + 1)
+        shapes.append(killer)
+        for s in shapes:
+            a, b = oracle.sort_check(np.ascontiguousarray(s))
+            assert np.array_equal(a, b), n
+
+
+def _compare_with_ref(oracle, im, nf, lap, mode="strict"):
+    r = oracle.RefExtractor(nfeatures=nf, mode=mode)
+    p = oracle.PortExtractor(nfeatures=nf, mode=mode)
+    mr, kr, dr = r.extract(im, lap)
+    mp, kp, dp = p.extract(im, lap)
+    assert mr == mp and np.array_equal(kr, kp) and np.array_equal(dr, dp)
+    for l in range(8):
+        assert np.array_equal(r.pyramid(l), p.pyramid(l))
+    return len(kr)
+
+
+def test_port_equals_reference_binary_on_fresh_inputs(oracle):
+    if not oracle.have_ref("strict"):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rng = np.random.default_rng(9)
+    import numpy as _np
+    total = 0
+    # white noise: thousands of candidates per level, many (count, UL.x) ties in the quadtree sort
+    total += _compare_with_ref(oracle, rng.integers(0, 256, (240, 320), dtype=np.uint8), 500, (0, 1000))
+    total += _compare_with_ref(oracle, rng.integers(0, 256, (376, 1241), dtype=np.uint8), 2000, (0, 0))
+    # low-contrast: forces the minThFAST fallback in most cells and levels with fewer candidates than N
+    low = (synth.frame(3, 400, 300).astype(np.int32) - 128) // 6 + 128
+    total += _compare_with_ref(oracle, low.astype(np.uint8), 1000, (100, 200))
+    # flat image: no keypoints at all
+    assert _compare_with_ref(oracle, np.full((240, 320), 77, dtype=np.uint8), 500, (0, 1000)) == 0
+    for k, (w, h, nf) in enumerate([(752, 480, 1000), (640, 480, 300), (500, 500, 1500), (900, 300, 800)]):
+        total += _compare_with_ref(oracle, synth.frame(20 + k, w, h), nf, (0, 1000), "native" if k % 2 else "strict")
+    assert total > 5000
