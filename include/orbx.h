@@ -1,0 +1,166 @@
+/* orbx.h — C ABI of the B200-native ORB frontend (sm_100a CUDA kernels behind plain pointers).
+ *
+ * This is the drop-in boundary for the ONE hot path of ORB-SLAM3 that the ROS 2 wrapper drives:
+ * ORB_SLAM3::ORBextractor::operator() and brute-force / banded top-2 Hamming matching with
+ * ORBmatcher::DescriptorDistance semantics.  Citations are file:line under the reference tree
+ * (ORB_SLAM3/...).  The C++ adapter `compat/ORBextractor.h` forwards the reference's class surface
+ * (ORB_SLAM3/include/ORBextractor.h:43-109) to these entry points; INTEGRATION.md shows the
+ * reference-side binding.
+ *
+ * Conventions: every function returns ORBX_OK (0) or a negative orbx_status; no exceptions cross
+ * the boundary; orbx_last_error() returns a thread-local message for the last failure.  There is
+ * NO CPU fallback: without a CUDA device every compute entry point fails with ORBX_ERR_CUDA.
+ * Pointers named d_* are device pointers, all others are host pointers.
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum orbx_status {
+    ORBX_OK = 0,
+    ORBX_ERR_ARG = -1,      /* bad argument (null pointer, non-positive size, image too small/large) */
+    ORBX_ERR_CUDA = -2,     /* CUDA runtime/driver failure, or no device */
+    ORBX_ERR_CAPACITY = -3, /* caller's output buffer too small; *n_out holds the needed count */
+    ORBX_ERR_NCCL = -4,     /* NCCL failure */
+    ORBX_ERR_STATE = -5     /* call order violated (e.g. results requested before an extract) */
+} orbx_status;
+
+/* Same 28-byte layout as cv::KeyPoint (pt.x, pt.y, size, angle, response, octave, class_id), so a
+ * std::vector<cv::KeyPoint>::data() can be passed directly (ORBextractor.cc:1112). */
+typedef struct orbx_keypoint {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbx_keypoint;
+
+/* The five constructor arguments of ORB_SLAM3::ORBextractor (ORBextractor.cc:409-411, fed from
+ * YAML by Settings.cc:443-450 / Tracking.cc:1223-1289) plus device-side knobs that never reach the
+ * reference class surface. */
+typedef struct orbx_params {
+    int nfeatures;
+    float scale_factor;
+    int nlevels;
+    int ini_th_fast;
+    int min_th_fast;
+    int device;  /* CUDA device ordinal; -1 = current device */
+    int fp_mode; /* 0 = STRICT (no FMA contraction in computeOrbDescriptor's rotation, -ffp-contract=off build
+                    of the reference); 1 = NATIVE (the reference's -O3 -march=native build: fmaf(x,b,y*a)) */
+} orbx_params;
+
+typedef struct orbx_extractor* orbx_handle;
+
+const char* orbx_last_error(void);
+int orbx_version(void);
+/* number of kernel launches issued by this library in the calling process so far (bench bookkeeping) */
+unsigned long long orbx_launch_count(void);
+
+/* ---- extractor life cycle: ORBextractor::ORBextractor (ORBextractor.cc:409-469) -------------------- */
+int orbx_create(const orbx_params* params, orbx_handle* out);
+void orbx_destroy(orbx_handle h);
+
+/* Per-level tables the reference exposes through GetScaleFactors(), GetInverseScaleFactors(),
+ * GetScaleSigmaSquares(), GetInverseScaleSigmaSquares() (ORBextractor.h:61-83) and mnFeaturesPerLevel
+ * (ORBextractor.cc:434-445).  Each output may be NULL; arrays hold nlevels entries. */
+int orbx_get_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                    int* features_per_level);
+
+/* ---- single frame: ORBextractor::operator() (ORBextractor.cc:1086-1168) ---------------------------
+ * img: host, 8-bit single channel, `stride` bytes per row.  lap0/lap1 = vLappingArea[0..1].
+ * kps/desc: host outputs with room for `cap` keypoints (desc is cap x 32 bytes).  *n_out = number of
+ * keypoints, *mono_index = the value operator() returns.  An empty image (img NULL or w/h <= 0) is not
+ * an error: *mono_index = -1, *n_out = 0 (ORBextractor.cc:1090-1091). */
+int orbx_extract(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int lap0, int lap1,
+                 orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index);
+
+/* mvImagePyramid[level] of the last orbx_extract / batch frame `frame` (ORBextractor.cc:1170-1195): the
+ * level is a ROI at (19,19) of a padded (w+38) x (h+38) plane.  `out` (host, may be NULL to query the
+ * size) receives the padded plane compactly, (h+38) rows of (w+38) bytes. */
+int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* out, int* w, int* hgt);
+
+/* ---- batch of equally sized frames (the throughput path; frames are independent) ------------------
+ * orbx_extract_batch: host frames (frame f at imgs + f*frame_stride, rows `stride` bytes apart) are
+ * copied to the device, extracted, and the results copied back: kps (nframes x cap_per_frame),
+ * desc (nframes x cap_per_frame x 32), n_out[nframes], mono_index[nframes].  Any of the four outputs may
+ * be NULL to leave that result on the device only.
+ * orbx_extract_batch_device: same with frames already resident on the device; results stay there and
+ * are read with orbx_batch_results / orbx_batch_download. */
+int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, int hgt, int stride,
+                       size_t frame_stride, int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc,
+                       int cap_per_frame, int* n_out, int* mono_index);
+int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, int nframes, int w, int hgt, int stride,
+                              size_t frame_stride, int lap0, int lap1);
+/* Device-resident results of the last batch: keypoints/descriptors of frame f start at
+ * d_kps + f*cap, d_desc + f*cap*32; d_n[f] keypoints are valid. */
+int orbx_batch_results(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc, const int** d_n,
+                       const int** d_mono, int* cap_per_frame);
+int orbx_batch_download(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
+                        int* mono_index);
+/* Blocks until the handle's stream is idle (batch_device is asynchronous). */
+int orbx_sync(orbx_handle h);
+/* Elapsed device time in milliseconds of the last batch (CUDA events on the handle's stream); the
+ * per-stage array (pyramid, fast, quadtree, blur, describe) may be NULL. */
+int orbx_last_timing(orbx_handle h, float* total_ms, float stage_ms[5]);
+/* Debug/parity taps of the last extraction: FAST candidates of (frame, level) in the reference's
+ * order (cell row-major, then FAST's row-major inside the cell; ORBextractor.cc:863-868) as
+ * (x, y, response) int32 triplets in cell-offset coordinates; returns the count through *n_out. */
+int orbx_get_candidates(orbx_handle h, int frame, int level, int32_t* out, int cap, int* n_out);
+/* Blurred level (GaussianBlur 7x7 sigma 2 of the un-padded level, ORBextractor.cc:1132-1133), w x h compact. */
+int orbx_get_blurred(orbx_handle h, int frame, int level, uint8_t* out, int* w, int* hgt);
+
+/* Fills d_out (device, nframes x hgt x w, compact) with frames k0..k0+nframes-1 of the deterministic
+ * synthetic stream (bit-identical to orb_slam3_ros2_b200/synth.py). */
+int orbx_synth_frames_device(uint8_t* d_out, int k0, int nframes, int w, int hgt, uint64_t seed, int right,
+                             int device);
+
+/* ---- Hamming matching ----------------------------------------------------------------------------
+ * ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074): 256-bit Hamming distance (host helper). */
+int orbx_hamming(const uint8_t* a, const uint8_t* b);
+
+/* Brute-force k=2: for every query the two database rows with the smallest distance, ordered by
+ * (distance asc, index asc) == cv::BFMatcher(NORM_HAMMING).knnMatch(q, db, m, 2) (Frame.cc:1144) and the
+ * reference's strict-< best/second loops visiting candidates in ascending index (ORBmatcher.cc:83-120).
+ * Missing entries (nd < 2) get idx = -1, dist = 256.  idx outputs are int64 row numbers. */
+int orbx_match_top2(const uint8_t* q, int nq, const uint8_t* db, int64_t nd, int64_t* idx1, int32_t* d1,
+                    int64_t* idx2, int32_t* d2, int device);
+int orbx_match_top2_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t nd, int64_t db_index_base,
+                           int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream);
+
+/* Frame-to-frame top-2 over the last batch held by `h` (config 2): frame f's descriptors against frame
+ * f+1's, f = 0..nframes-2.  Outputs (device or host, selected by `to_host`) are (nframes-1) x cap entries. */
+int orbx_match_batch_consecutive(orbx_handle h, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
+                                 int to_host);
+
+/* Frame::ComputeStereoMatches' Hamming stage (Frame.cc:811-894): for each left keypoint the best right
+ * keypoint among those whose row band [floor(vR - 2*sf[octR]), ceil(vR + 2*sf[octR])] contains (int)vL, with
+ * octave within +-1 and uR in [uL - max_d, uL] (minD = 0, Frame.cc:841); initial best = TH_HIGH (100), strict <,
+ * right keypoints in ascending index.  best_idx = 0 / best_dist = 100 when nothing beats TH_HIGH (:867-868). */
+int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, int nl, const orbx_keypoint* kps_r,
+                             const uint8_t* desc_r, int nr, const float* scale_factors, int nlevels, int n_rows,
+                             float max_d, int32_t* best_idx, int32_t* best_dist, int device);
+
+/* ---- descriptor database sharded over ranks (config 5): one process per GPU ----------------------
+ * Rank 0 calls orbx_comm_unique_id and distributes the 128 bytes out of band (the host launcher's
+ * rendezvous); every rank then calls orbx_comm_init.  orbx_match_top2_sharded computes the local top-2 of
+ * the replicated queries against this rank's shard (rows [db_index_base, db_index_base + nd_local) of the
+ * global database), ncclAllGather's the per-rank candidates and merges them on every rank by
+ * (distance asc, global index asc). */
+typedef struct orbx_comm_s* orbx_comm;
+int orbx_comm_unique_id(uint8_t id[128]);
+int orbx_comm_init(int rank, int nranks, const uint8_t id[128], int device, orbx_comm* out);
+void orbx_comm_destroy(orbx_comm c);
+int orbx_match_top2_sharded(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local,
+                            int64_t db_index_base, int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2);
+/* The merge alone, on already gathered candidates laid out [rank][query] (used by the CPU-side tests of
+ * the exchange step and by the single-process emulation of G shards on one GPU). */
+int orbx_merge_top2_device(const uint64_t* d_keys1, const uint64_t* d_keys2, int nranks, int nq, int64_t* d_idx1,
+                           int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

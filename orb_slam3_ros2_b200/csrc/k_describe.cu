@@ -1,0 +1,243 @@
+// k_describe.cu — K-d IC_Angle, K-f rBRIEF-256 and K-h the ordered output placement of operator().
+//
+// Replaces, in ORB_SLAM3/src/ORBextractor.cc:
+//   IC_Angle :76-103 / computeOrientation :471-478     intensity centroid on the UN-blurred level, cv::fastAtan2
+//   computeOrbDescriptor :107-146 / computeDescriptors :1077-1084   rotated 256-pair test on the blurred level
+//   operator() tail :1103-1167    pt *= scale for level > 0, lapping-area front/back placement, monoIndex
+//
+// Float determinism: fastAtan2 is evaluated with explicitly rounded single
+// operations (no FMA); cos/sin are glibc's sincosf algorithm (double range reduction + polynomials, each
+// operation rounded once); the sample rotation is two rounded products and one rounded sum in STRICT mode, or
+// fmaf(x, b, y*a) in NATIVE mode (what gcc -O3 -march=native emits for the reference).  cvRound = rint.
+#include "orbx_internal.cuh"
+
+namespace orbx {
+namespace {
+
+#include "orb_pattern.inc"  // host table kOrbPattern[256][4]
+
+__device__ char4 gPattern[256];
+
+// umax[v] of the radius-15 disc (ORBextractor.cc:453-468)
+__constant__ int cUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+// cv::fastAtan2 (OpenCV core/mathfuncs_core, scalar path), degrees in [0,360)
+__device__ __forceinline__ float fastAtan2Deg(float y, float x) {
+    const float s = (float)(180.0 / 3.1415926535897932384626433832795);
+    const float p1 = __fmul_rn(0.9997878412794807f, s), p3 = __fmul_rn(-0.3258083974640975f, s);
+    const float p5 = __fmul_rn(0.1555786518463281f, s), p7 = __fmul_rn(-0.04432655554792128f, s);
+    const float eps = 2.2204460492503131e-16f;  // (float)DBL_EPSILON
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// glibc 2.28+ sincosf (sysdeps/ieee754/flt-32/s_sincosf.[ch]), the |y| < 120 paths (y in [0, 2*pi) here)
+__device__ __forceinline__ void glibcSincosf(float y, float* sinp, float* cosp) {
+    const double HPI_INV = 0x1.45f306dc9c883p+23, HPI = 0x1.921fb54442d18p+0;
+    const double C0 = 1.0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10,
+                 C4 = 0x1.99343027bf8c3p-16;
+    const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+    const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ff;
+    double x = (double)y;
+    int n = 0;
+    double s = 1.0, k = 1.0;
+    if (top < ((__float_as_uint(0x1.921FB6p-1f) >> 20) & 0x7ff)) {
+        if (top < ((__float_as_uint(0x1p-12f) >> 20) & 0x7ff)) {
+            *sinp = y;
+            *cosp = 1.0f;
+            return;
+        }
+    } else {
+        const double r = __dmul_rn(x, HPI_INV);
+        n = ((int)r + 0x800000) >> 24;
+        x = __dsub_rn(x, __dmul_rn((double)n, HPI));
+        s = (n & 3) == 1 || (n & 3) == 2 ? -1.0 : 1.0;
+        k = (n & 2) ? -1.0 : 1.0;
+    }
+    const double xs = __dmul_rn(x, s), x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, xs), x4 = __dmul_rn(x2, x2);
+    const double x5 = __dmul_rn(x3, x2), x6 = __dmul_rn(x4, x2);
+    const double c2 = __dadd_rn(k * C3, __dmul_rn(x2, k * C4));
+    const double s1 = __dadd_rn(S2, __dmul_rn(x2, S3));
+    const double c1 = __dadd_rn(k * C0, __dmul_rn(x2, k * C1));
+    const double sn = __dadd_rn(xs, __dmul_rn(x3, S1));
+    const double c = __dadd_rn(c1, __dmul_rn(x4, k * C2));
+    const float Sf = (float)__dadd_rn(sn, __dmul_rn(x5, s1));
+    const float Cf = (float)__dadd_rn(c, __dmul_rn(x6, c2));
+    if (n & 1) { *sinp = Cf; *cosp = Sf; } else { *sinp = Sf; *cosp = Cf; }
+}
+
+// ---- K-h part 1: output slot of every level keypoint (operator() :1120-1166) ---------------------------------
+// The reference walks levels 0..n-1 and, inside a level, the quadtree's list order; a keypoint whose SCALED x lies
+// in [lap0, lap1] is written from the back (stereoIndex--), the others from the front (monoIndex++).
+__global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FramePlan P, const LevelKp* __restrict__ lkp,
+                                                  const int* __restrict__ lkpCnt, int* __restrict__ slot,
+                                                  int* __restrict__ outN, int* __restrict__ outMono, int lap0, int lap1,
+                                                  int* __restrict__ errFlag) {
+    __shared__ int sBase[kMaxLevels + 1];
+    __shared__ int sWarp[8];
+    __shared__ int sCarry;
+    const int f = blockIdx.x, tid = threadIdx.x;
+    if (tid == 0) {
+        int acc = 0;
+        for (int l = 0; l < P.nlevels; ++l) { sBase[l] = acc; acc += lkpCnt[(size_t)f * P.nlevels + l]; }
+        sBase[P.nlevels] = acc;
+        sCarry = 0;
+    }
+    __syncthreads();
+    const int total = sBase[P.nlevels];
+    const LevelKp* kp = lkp + (size_t)f * P.lkpTotal;
+    int* sl = slot + (size_t)f * P.lkpTotal;
+    for (int start = 0; start < total; start += 256) {
+        const int j = start + tid;
+        int inside = 0, l = 0, idx = 0;
+        if (j < total) {
+            while (j >= sBase[l + 1]) ++l;
+            idx = P.lv[l].lkpBase + (j - sBase[l]);
+            float x = (float)kp[idx].x;
+            if (l != 0) x = __fmul_rn(x, P.lv[l].scale);  // :1149-1151
+            inside = (x >= (float)lap0 && x <= (float)lap1) ? 1 : 0;  // :1153
+        }
+        int incl = inside;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((tid & 31) >= o) incl += v;
+        }
+        if ((tid & 31) == 31) sWarp[tid >> 5] = incl;
+        __syncthreads();
+        int base = sCarry;
+        for (int w = 0; w < (tid >> 5); ++w) base += sWarp[w];
+        const int insideBefore = base + incl - inside;
+        if (j < total) sl[idx] = inside ? (total - 1 - insideBefore) : (j - insideBefore);
+        __syncthreads();
+        if (tid == 255) sCarry = base + incl;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        outN[f] = min(total, P.outCap);
+        outMono[f] = total - sCarry;
+        if (total > P.outCap) atomicOr(errFlag, 8);
+    }
+}
+
+// ---- K-d + K-f + K-h part 2: one warp per keypoint -----------------------------------------------------------
+__global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
+                                                      const uint8_t* __restrict__ blur, const LevelKp* __restrict__ lkp,
+                                                      const int* __restrict__ lkpCnt, const int* __restrict__ slot,
+                                                      float* __restrict__ outKps, uint8_t* __restrict__ outDesc) {
+    const int f = blockIdx.y;
+    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (j >= P.lkpTotal) return;
+    int l = 0;
+    while (l + 1 < P.nlevels && j >= P.lv[l + 1].lkpBase) ++l;
+    const LevelPlan& L = P.lv[l];
+    if (j - L.lkpBase >= lkpCnt[(size_t)f * P.nlevels + l]) return;
+    const LevelKp kp = lkp[(size_t)f * P.lkpTotal + j];
+    const int s = slot[(size_t)f * P.lkpTotal + j];
+    if (s >= P.outCap) return;
+
+    // IC_Angle: lane v+15 owns row v of the disc
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int v = lane - 15;
+        const int d = cUmax[v < 0 ? -v : v];
+        const uint8_t* row = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kp.y + kEdge + v) * L.pitch + kp.x + kEdge;
+        int sum = 0;
+        for (int u = -d; u <= d; ++u) {
+            const int val = row[u];
+            m10 += u * val;
+            sum += val;
+        }
+        m01 = v * sum;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fastAtan2Deg((float)m01, (float)m10);
+
+    // rBRIEF: lane i computes byte i (pairs 8i .. 8i+7, LSB first)
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+    float a, b;
+    glibcSincosf(__fmul_rn(angle, factorPI), &b, &a);
+    const uint8_t* center = blur + (size_t)f * P.blurBytes + L.blurOff + (size_t)kp.y * L.bpitch + kp.x;
+    const int step = L.bpitch;
+    uint32_t byte = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const char4 pt = gPattern[lane * 8 + k];
+        int t[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float fx = (float)(h ? pt.z : pt.x), fy = (float)(h ? pt.w : pt.y);
+            int r, c;
+            if (P.fpMode == 0) {
+                r = __float2int_rn(__fadd_rn(__fmul_rn(fx, b), __fmul_rn(fy, a)));
+                c = __float2int_rn(__fsub_rn(__fmul_rn(fx, a), __fmul_rn(fy, b)));
+            } else {
+                r = __float2int_rn(__fmaf_rn(fx, b, __fmul_rn(fy, a)));
+                c = __float2int_rn(__fmaf_rn(fx, a, -__fmul_rn(fy, b)));
+            }
+            t[h] = center[r * step + c];
+        }
+        byte |= (uint32_t)(t[0] < t[1]) << k;
+    }
+    uint32_t word = byte << (8 * (lane & 3));
+    word |= __shfl_xor_sync(0xffffffffu, word, 1);
+    word |= __shfl_xor_sync(0xffffffffu, word, 2);
+    const int half = lane & 16;
+    uint4 q;
+    q.x = __shfl_sync(0xffffffffu, word, half + 0);
+    q.y = __shfl_sync(0xffffffffu, word, half + 4);
+    q.z = __shfl_sync(0xffffffffu, word, half + 8);
+    q.w = __shfl_sync(0xffffffffu, word, half + 12);
+    uint8_t* d = outDesc + ((size_t)f * P.outCap + s) * 32;
+    if ((lane & 15) == 0) *reinterpret_cast<uint4*>(d + (lane >> 4) * 16) = q;
+
+    // cv::KeyPoint record (:880-890, :1149-1151)
+    if (lane < 7) {
+        float x = (float)kp.x, y = (float)kp.y;
+        if (l != 0) { x = __fmul_rn(x, L.scale); y = __fmul_rn(y, L.scale); }
+        float v;
+        switch (lane) {
+            case 0: v = x; break;
+            case 1: v = y; break;
+            case 2: v = L.patchSize; break;
+            case 3: v = angle; break;
+            case 4: v = (float)kp.resp; break;
+            case 5: v = __int_as_float(l); break;
+            default: v = __int_as_float(-1); break;
+        }
+        outKps[((size_t)f * P.outCap + s) * 7 + lane] = v;
+    }
+}
+
+}  // namespace
+
+// per device, once per extractor (orbx_create)
+void uploadDescribeTables() { cudaMemcpyToSymbol(gPattern, kOrbPattern, sizeof(kOrbPattern)); }
+
+void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s) {
+    slotKernel<<<F, 256, 0, s>>>(P, B.lkp, B.lkpCnt, B.slot, B.outN, B.outMono, lap0, lap1, B.errFlag);
+    countLaunch();
+    const int warpsPerBlock = 8;
+    describeKernel<<<dim3((P.lkpTotal + warpsPerBlock - 1) / warpsPerBlock, F), 256, 0, s>>>(
+        P, B.pyr, B.blur, B.lkp, B.lkpCnt, B.slot, reinterpret_cast<float*>(B.outKps), B.outDesc);
+    countLaunch();
+}
+
+}  // namespace orbx

@@ -1,0 +1,269 @@
+// k_match.cu — K-g: brute-force top-2 Hamming matching of 256-bit ORB descriptors.
+//
+// Replaces the inner loop of every reference matcher — ORBmatcher::DescriptorDistance
+// (ORB_SLAM3/src/ORBmatcher.cc:2058-2074) inside the strict-< best/second bookkeeping (:83-120, :273-294) — and
+// cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) (src/Frame.cc:1144).  Result order is (distance asc, index asc),
+// which both the reference loops (candidates visited in ascending index) and knnMatch produce.
+//
+// Bound: the POPC pipe (8 x 32-bit POPC per pair), not HBM — the database is streamed once per query tile.
+// Layout: a CTA stages a block of database rows in shared memory with 128-bit loads; every thread keeps R query
+// descriptors in registers, reads the staged rows as warp-wide broadcasts and maintains two packed keys per
+// query, key = distance << 23 | row-in-chunk, so that `min` reproduces the tie order:
+//     k2 = min(k2, max(k1, key));  k1 = min(k1, key)
+// Chunks of the database (< 2^23 rows) go to different CTAs; their per-chunk top-2 are written as 64-bit keys
+// (distance << 40 | global row) and reduced by mergeKernel — the same kernel that merges the per-rank candidates
+// after the NCCL all-gather of the sharded path.
+#include "orbx_internal.cuh"
+
+namespace orbx {
+namespace {
+
+constexpr int kMT = 256;        // threads per CTA
+constexpr int kStage = 256;     // database rows staged per iteration (8 KB)
+constexpr uint32_t kNoKey32 = 0xffffffffu;
+constexpr unsigned long long kNoKey64 = ~0ull;
+
+__device__ __forceinline__ unsigned long long widenKey(uint32_t k, long long base) {
+    if (k == kNoKey32) return kNoKey64;
+    return ((unsigned long long)(k >> 23) << 40) | (unsigned long long)(base + (long long)(k & 0x7fffffu));
+}
+
+struct MatchProblem {
+    const uint8_t* q;    // nq x 32
+    const uint8_t* db;   // nd x 32
+    int nq;
+    long long nd;
+};
+
+// Problem z: either the single (q, db) pair, or — consecutive mode — frame z against frame z+1 of a batch.
+template <int R>
+__global__ void __launch_bounds__(kMT) matchKernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ db,
+                                                   long long nd, long long indexBase, long long chunkRows,
+                                                   unsigned long long* __restrict__ part1,
+                                                   unsigned long long* __restrict__ part2, const int* __restrict__ counts,
+                                                   int cap) {
+    __shared__ __align__(16) uint4 sDb[kStage * 2];
+    const int tid = threadIdx.x;
+    const int z = blockIdx.z;
+    if (counts) {  // consecutive frames of a batch: q = frame z, db = frame z+1
+        q += (size_t)z * cap * 32;
+        db = q + (size_t)cap * 32;
+        nq = counts[z];
+        nd = counts[z + 1];
+    }
+    const int q0 = blockIdx.y * kMT * R;
+    if (q0 >= nq) return;
+    const long long c0 = (long long)blockIdx.x * chunkRows;
+    const long long c1 = c0 + chunkRows < nd ? c0 + chunkRows : nd;
+
+    uint32_t qw[R][8];
+    uint32_t k1[R], k2[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int qi = q0 + r * kMT + tid;
+        const uint4* p = reinterpret_cast<const uint4*>(q + (size_t)(qi < nq ? qi : 0) * 32);
+        const uint4 a = qi < nq ? __ldg(p) : make_uint4(0, 0, 0, 0), b = qi < nq ? __ldg(p + 1) : make_uint4(0, 0, 0, 0);
+        qw[r][0] = a.x; qw[r][1] = a.y; qw[r][2] = a.z; qw[r][3] = a.w;
+        qw[r][4] = b.x; qw[r][5] = b.y; qw[r][6] = b.z; qw[r][7] = b.w;
+        k1[r] = k2[r] = kNoKey32;
+    }
+
+    for (long long s0 = c0; s0 < c1; s0 += kStage) {
+        const int rows = (int)(c1 - s0 < kStage ? c1 - s0 : kStage);
+        __syncthreads();
+        const uint4* src = reinterpret_cast<const uint4*>(db + (size_t)s0 * 32);
+        for (int i = tid; i < rows * 2; i += kMT) sDb[i] = __ldg(src + i);
+        __syncthreads();
+        const uint32_t idx0 = (uint32_t)(s0 - c0);
+#pragma unroll 2
+        for (int j = 0; j < rows; ++j) {
+            const uint4 a = sDb[2 * j], b = sDb[2 * j + 1];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int d = __popc(qw[r][0] ^ a.x) + __popc(qw[r][1] ^ a.y) + __popc(qw[r][2] ^ a.z) +
+                              __popc(qw[r][3] ^ a.w) + __popc(qw[r][4] ^ b.x) + __popc(qw[r][5] ^ b.y) +
+                              __popc(qw[r][6] ^ b.z) + __popc(qw[r][7] ^ b.w);
+                const uint32_t key = ((uint32_t)d << 23) | (idx0 + (uint32_t)j);
+                k2[r] = min(k2[r], max(k1[r], key));
+                k1[r] = min(k1[r], key);
+            }
+        }
+    }
+    const size_t nqPad = counts ? (size_t)cap : (size_t)nq;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int qi = q0 + r * kMT + tid;
+        if (qi < nq) {
+            const size_t o = ((size_t)z * gridDim.x + blockIdx.x) * nqPad + qi;
+            part1[o] = widenKey(k1[r], indexBase + c0);
+            part2[o] = widenKey(k2[r], indexBase + c0);
+        }
+    }
+}
+
+// Global top-2 over `nsets` candidate sets laid out [set][query]; keys are distance << 40 | global row, so the
+// merged order is (distance asc, global row asc) — knnMatch's tie rule across shard boundaries.
+__global__ void mergeKernel(const unsigned long long* __restrict__ k1, const unsigned long long* __restrict__ k2,
+                            int nsets, int nq, size_t setStride, long long* __restrict__ idx1, int* __restrict__ d1,
+                            long long* __restrict__ idx2, int* __restrict__ d2, unsigned long long* __restrict__ outK1,
+                            unsigned long long* __restrict__ outK2) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    unsigned long long b1 = kNoKey64, b2 = kNoKey64;
+    for (int s = 0; s < nsets; ++s) {
+        const unsigned long long a1 = k1[(size_t)s * setStride + i], a2 = k2[(size_t)s * setStride + i];
+        const unsigned long long lo = b1 < a1 ? b1 : a1, hi = b1 < a1 ? a1 : b1;
+        const unsigned long long m2 = b2 < a2 ? b2 : a2;
+        b1 = lo;
+        b2 = hi < m2 ? hi : m2;
+    }
+    if (outK1) {
+        outK1[i] = b1;
+        outK2[i] = b2;
+        return;
+    }
+    const unsigned long long mask = (1ull << 40) - 1;
+    idx1[i] = b1 == kNoKey64 ? -1 : (long long)(b1 & mask);
+    d1[i] = b1 == kNoKey64 ? 256 : (int)(b1 >> 40);
+    idx2[i] = b2 == kNoKey64 ? -1 : (long long)(b2 & mask);
+    d2[i] = b2 == kNoKey64 ? 256 : (int)(b2 >> 40);
+}
+
+// consecutive mode epilogue: keys [pair][cap] -> int32 outputs [pair][cap]
+__global__ void unpackPairsKernel(const unsigned long long* __restrict__ k1, const unsigned long long* __restrict__ k2,
+                                  const int* __restrict__ counts, int cap, int* __restrict__ idx1, int* __restrict__ d1,
+                                  int* __restrict__ idx2, int* __restrict__ d2) {
+    const int z = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cap) return;
+    const size_t o = (size_t)z * cap + i;
+    const bool valid = i < counts[z];
+    const unsigned long long a = valid ? k1[o] : kNoKey64, b = valid ? k2[o] : kNoKey64;
+    const unsigned long long mask = (1ull << 40) - 1;
+    idx1[o] = a == kNoKey64 ? -1 : (int)(a & mask);
+    d1[o] = a == kNoKey64 ? 256 : (int)(a >> 40);
+    idx2[o] = b == kNoKey64 ? -1 : (int)(b & mask);
+    d2[o] = b == kNoKey64 ? 256 : (int)(b >> 40);
+}
+
+// Frame::ComputeStereoMatches' Hamming stage (src/Frame.cc:825-894): one thread per left keypoint, right keypoints
+// visited in ascending iR (the order the row buckets are filled in, :828-838).
+__global__ void stereoBandedKernel(const float* __restrict__ kl, const uint4* __restrict__ dl, int nl,
+                                   const float* __restrict__ kr, const uint4* __restrict__ dr, int nr,
+                                   const float* __restrict__ sf, int nRows, float maxD, int* __restrict__ bestIdx,
+                                   int* __restrict__ bestDist) {
+    const int iL = blockIdx.x * blockDim.x + threadIdx.x;
+    if (iL >= nl) return;
+    int bd = 100, bi = 0;  // ORBmatcher::TH_HIGH, bestIdxR = 0 (:867-868)
+    const float uL = kl[iL * 7], vL = kl[iL * 7 + 1];
+    const int levelL = __float_as_int(kl[iL * 7 + 5]);
+    const int row = (int)vL;  // vRowIndices[vL] (:858)
+    const float minU = __fsub_rn(uL, maxD), maxU = uL;
+    if (row >= 0 && row < nRows && !(maxU < 0)) {
+        const uint4 a0 = dl[2 * iL], a1 = dl[2 * iL + 1];
+        for (int iR = 0; iR < nr; ++iR) {
+            const float uR = kr[iR * 7], vR = kr[iR * 7 + 1];
+            const int octR = __float_as_int(kr[iR * 7 + 5]);
+            const float r = __fmul_rn(2.0f, sf[octR]);
+            const int maxr = (int)ceilf(__fadd_rn(vR, r)), minr = (int)floorf(__fsub_rn(vR, r));  // :833-834
+            if (row < minr || row > maxr) continue;
+            if (octR < levelL - 1 || octR > levelL + 1) continue;
+            if (!(uR >= minU && uR <= maxU)) continue;
+            const uint4 b0 = dr[2 * iR], b1 = dr[2 * iR + 1];
+            const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                          __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+            if (d < bd) { bd = d; bi = iR; }
+        }
+    }
+    bestIdx[iL] = bi;
+    bestDist[iL] = bd;
+}
+
+}  // namespace
+
+// How the database is cut into chunks: enough CTAs to fill the GPU a few times over, chunk < 2^23 rows.
+static long long chooseChunk(long long nd, int queryTiles, int sms) {
+    long long want = ((long long)sms * 4 + queryTiles - 1) / queryTiles;  // CTAs along the db axis
+    if (want < 1) want = 1;
+    long long rows = (nd + want - 1) / want;
+    rows = ((rows + kStage - 1) / kStage) * kStage;
+    if (rows < kStage) rows = kStage;
+    if (rows > (1 << 23) - kStage) rows = (1 << 23) - kStage;
+    return rows;
+}
+
+int matchNumChunks(int nq, int64_t nd, int sms) {
+    const int tiles = (nq + kMT * 4 - 1) / (kMT * 4);
+    const long long rows = chooseChunk(nd, tiles, sms);
+    return (int)((nd + rows - 1) / rows);
+}
+
+// Per-chunk top-2 keys of (q x db) into dKeys1/2 laid out [chunk][nq]; returns the number of chunks via the layout
+// computed by matchNumChunks (the caller sized the buffers with it).
+void launchMatchTop2(const uint8_t* dq, int nq, const uint8_t* ddb, int64_t nd, int64_t base, uint64_t* dKeys1,
+                     uint64_t* dKeys2, cudaStream_t s) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int tiles = (nq + kMT * 4 - 1) / (kMT * 4);
+    const long long rows = chooseChunk(nd, tiles, sms);
+    const int chunks = (int)((nd + rows - 1) / rows);
+    if (chunks <= 0 || nq <= 0) return;
+    matchKernel<4><<<dim3(chunks, tiles, 1), kMT, 0, s>>>(dq, nq, ddb, nd, base, rows,
+                                                          reinterpret_cast<unsigned long long*>(dKeys1),
+                                                          reinterpret_cast<unsigned long long*>(dKeys2), nullptr, 0);
+    countLaunch();
+}
+
+void launchUnpackTop2Strided(const uint64_t* k1, const uint64_t* k2, int nsets, int nq, size_t setStride, int64_t* idx1,
+                             int32_t* d1, int64_t* idx2, int32_t* d2, cudaStream_t s) {
+    if (nq <= 0) return;
+    mergeKernel<<<(nq + 127) / 128, 128, 0, s>>>(reinterpret_cast<const unsigned long long*>(k1),
+                                                 reinterpret_cast<const unsigned long long*>(k2), nsets, nq, setStride,
+                                                 reinterpret_cast<long long*>(idx1), d1,
+                                                 reinterpret_cast<long long*>(idx2), d2, nullptr, nullptr);
+    countLaunch();
+}
+
+void launchUnpackTop2(const uint64_t* k1, const uint64_t* k2, int nsets, int nq, int64_t* idx1, int32_t* d1,
+                      int64_t* idx2, int32_t* d2, cudaStream_t s) {
+    launchUnpackTop2Strided(k1, k2, nsets, nq, (size_t)nq, idx1, d1, idx2, d2, s);
+}
+
+// [set][nq] keys -> one candidate set (still keys): the per-rank payload of the all-gather
+void launchReduceKeys(const uint64_t* k1, const uint64_t* k2, int nsets, int nq, uint64_t* outK1, uint64_t* outK2,
+                      cudaStream_t s) {
+    if (nq <= 0) return;
+    mergeKernel<<<(nq + 127) / 128, 128, 0, s>>>(reinterpret_cast<const unsigned long long*>(k1),
+                                                 reinterpret_cast<const unsigned long long*>(k2), nsets, nq, (size_t)nq,
+                                                 nullptr, nullptr, nullptr, nullptr,
+                                                 reinterpret_cast<unsigned long long*>(outK1),
+                                                 reinterpret_cast<unsigned long long*>(outK2));
+    countLaunch();
+}
+
+// frame f vs frame f+1 for f = 0..F-2; descriptors [F][cap][32], counts [F]; keys scratch [F-1][cap] x 2
+void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap, uint64_t* keys1, uint64_t* keys2,
+                            int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, cudaStream_t s) {
+    if (F < 2) return;
+    const int tiles = (cap + kMT - 1) / kMT;
+    matchKernel<1><<<dim3(1, tiles, F - 1), kMT, 0, s>>>(dDesc, 0, nullptr, 0, 0, (long long)cap,
+                                                         reinterpret_cast<unsigned long long*>(keys1),
+                                                         reinterpret_cast<unsigned long long*>(keys2), dN, cap);
+    countLaunch();
+    unpackPairsKernel<<<dim3((cap + 127) / 128, F - 1), 128, 0, s>>>(reinterpret_cast<const unsigned long long*>(keys1),
+                                                                    reinterpret_cast<const unsigned long long*>(keys2),
+                                                                    dN, cap, idx1, d1, idx2, d2);
+    countLaunch();
+}
+
+void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
+                        const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s) {
+    if (nl <= 0) return;
+    stereoBandedKernel<<<(nl + 127) / 128, 128, 0, s>>>(static_cast<const float*>(kl), reinterpret_cast<const uint4*>(dl),
+                                                        nl, static_cast<const float*>(kr),
+                                                        reinterpret_cast<const uint4*>(dr), nr, sf, nRows, maxD, bi, bd);
+    countLaunch();
+}
+
+}  // namespace orbx

@@ -1,0 +1,832 @@
+// orbx_api.cu — host side of the C ABI (include/orbx.h): extractor handle, per-resolution plan, device buffers,
+// stage orchestration on one CUDA stream, and the matching entry points.  No CPU fallback anywhere: every compute
+// entry point needs a CUDA device and fails with ORBX_ERR_CUDA otherwise.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/orbx.h"
+#include "orbx_internal.cuh"
+
+namespace orbx {
+
+static std::atomic<unsigned long long> gLaunches{0};
+void countLaunch(int n) { gLaunches += (unsigned long long)n; }
+
+static thread_local std::string tlsError;
+static int fail(int code, const std::string& msg) {
+    tlsError = msg;
+    return code;
+}
+#define ORBX_CUDA(expr)                                                                                   \
+    do {                                                                                                  \
+        cudaError_t e_ = (expr);                                                                          \
+        if (e_ != cudaSuccess) {                                                                          \
+            cudaGetLastError();                                                                           \
+            return fail(ORBX_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));               \
+        }                                                                                                 \
+    } while (0)
+
+static inline int cvRoundF(float v) { return (int)lrintf(v); }  // cvRound: round half to even
+static inline unsigned alignUp(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
+
+struct DevMem {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t need) {
+        if (need <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, need);
+        if (e == cudaSuccess) bytes = need;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+};
+
+}  // namespace orbx
+
+using namespace orbx;
+
+struct orbx_extractor {
+    orbx_params prm;
+    double scaleFactorD;  // the reference stores scaleFactor as a double member (ORBextractor.h:96)
+    int device = 0;
+    std::vector<float> sf, isf, sig2, isig2;
+    std::vector<int> nPerLevel;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[7] = {};
+    // plan + buffers of the current (W, H, capacity F)
+    FramePlan plan{};
+    bool havePlan = false;
+    int capFrames = 0;
+    int lastFrames = 0;
+    size_t tabEntries = 0;
+    Buffers buf{};
+    DevMem mImg, mPyr, mBlur, mCand, mCellCnt, mGath, mNid, mLkp, mLkpCnt, mSlot, mOutK, mOutD, mOutN, mOutM, mTab, mErr;
+    DevMem mKeys1, mKeys2, mMatch;
+    std::vector<uint8_t> hStage;  // pinned staging would be the caller's; this is only for get_* taps
+};
+
+namespace orbx {
+
+// ORBextractor::ORBextractor (ORB_SLAM3/src/ORBextractor.cc:409-445)
+static void initTables(orbx_extractor* h) {
+    const int nl = h->prm.nlevels;
+    h->sf.assign(nl, 1.f); h->sig2.assign(nl, 1.f); h->isf.assign(nl, 1.f); h->isig2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        h->sf[i] = (float)(h->sf[i - 1] * h->scaleFactorD);  // :420
+        h->sig2[i] = h->sf[i] * h->sf[i];
+    }
+    for (int i = 0; i < nl; ++i) { h->isf[i] = 1.0f / h->sf[i]; h->isig2[i] = 1.0f / h->sig2[i]; }
+    h->nPerLevel.assign(nl, 0);
+    const float factor = (float)(1.0f / h->scaleFactorD);  // :435
+    float want = (float)(h->prm.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl)));  // :436
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        h->nPerLevel[l] = cvRoundF(want);
+        sum += h->nPerLevel[l];
+        want *= factor;
+    }
+    h->nPerLevel[nl - 1] = std::max(h->prm.nfeatures - sum, 0);  // :445
+}
+
+// cv::resize INTER_LINEAR coefficient generation (OpenCV imgproc/resize.cpp)
+static void resizeTable(int srcN, int dstN, bool xAxis, std::vector<int16_t>& out) {
+    const double scale = 1.0 / ((double)dstN / srcN);
+    for (int d = 0; d < dstN; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        // the x axis clamps the offset and resets the fraction; the y axis keeps its fraction and the kernel clips
+        // the two row indices instead (OpenCV resize.cpp does exactly this; the roundings differ)
+        if (xAxis) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= srcN - 1) { f = 0; s = srcN - 1; }
+        }
+        auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
+        out.push_back((int16_t)s);
+        out.push_back(sat(cvRoundF((1.f - f) * 2048.f)));
+        out.push_back(sat(cvRoundF(f * 2048.f)));
+        out.push_back(0);
+    }
+}
+
+static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab) {
+    FramePlan& P = h->plan;
+    std::memset(&P, 0, sizeof(P));
+    const int nl = h->prm.nlevels;
+    P.nlevels = nl; P.W = W; P.H = H;
+    P.iniTh = std::min(std::max(h->prm.ini_th_fast, 0), 255);
+    P.minTh = std::min(std::max(h->prm.min_th_fast, 0), 255);
+    P.fpMode = h->prm.fp_mode;
+    unsigned pyrOff = 0, blurOff = 0, candOff = 0, gathOff = 0;
+    int cellBase = 0, lkpBase = 0;
+    for (int l = 0; l < nl; ++l) {
+        LevelPlan& L = P.lv[l];
+        L.w = cvRoundF((float)W * h->isf[l]);  // ORBextractor.cc:1175 (from the ORIGINAL size)
+        L.h = cvRoundF((float)H * h->isf[l]);
+        if (L.w < 1 || L.h < 1) return fail(ORBX_ERR_ARG, "image too small for the number of pyramid levels");
+        L.pitch = (int)alignUp(L.w + 2 * kEdge, 128);
+        L.bpitch = (int)alignUp(L.w, 128);
+        L.planeOff = pyrOff; pyrOff += (unsigned)L.pitch * (L.h + 2 * kEdge);
+        L.blurOff = blurOff; blurOff += (unsigned)L.bpitch * L.h;
+        // FAST grid (ORBextractor.cc:789-803)
+        const float width = (float)(L.w - 2 * kMinBorder), height = (float)(L.h - 2 * kMinBorder);
+        L.nCols = width > 0 ? (int)(width / kCellW) : 0;
+        L.nRows = height > 0 ? (int)(height / kCellW) : 0;
+        if (L.nCols <= 0 || L.nRows <= 0) { L.nCols = L.nRows = 0; L.wCell = L.hCell = 0; }
+        else { L.wCell = (int)std::ceil(width / L.nCols); L.hCell = (int)std::ceil(height / L.nRows); }
+        L.cellCap = ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
+        L.cellBase = cellBase; cellBase += L.nCols * L.nRows;
+        L.candOff = candOff; L.maxCand = L.nCols * L.nRows * L.cellCap; candOff += (unsigned)L.maxCand;
+        L.gathOff = gathOff; gathOff += (unsigned)L.maxCand;
+        if (L.maxCand >= (1 << 24)) return fail(ORBX_ERR_ARG, "level too large (candidate index exceeds 24 bits)");
+        L.nFeat = h->nPerLevel[l];
+        L.lkpBase = lkpBase; L.lkpCap = L.nFeat + 4; lkpBase += L.lkpCap;
+        L.scale = h->sf[l];
+        L.patchSize = (float)(int)(kPatch * h->sf[l]);  // :879
+        if (l > 0) {
+            L.tabX = (int)(tab.size() / 4); resizeTable(P.lv[l - 1].w, L.w, true, tab);
+            L.tabY = (int)(tab.size() / 4); resizeTable(P.lv[l - 1].h, L.h, false, tab);
+        }
+    }
+    if (W > 4000 || H > 4000) return fail(ORBX_ERR_ARG, "images larger than 4000 px are not supported (12-bit packed coordinates)");
+    P.frameBytes = alignUp(pyrOff + 256, 256);
+    P.blurBytes = alignUp(blurOff + 256, 256);
+    P.candWords = candOff; P.gathWords = alignUp(gathOff, 8);
+    P.nCellsTotal = cellBase;
+    P.lkpTotal = lkpBase;
+    P.outCap = lkpBase;
+    if (quadtreeSmemBytes(P) > 220 * 1024) return fail(ORBX_ERR_ARG, "nfeatures too large for the quadtree kernel's shared memory");
+    return ORBX_OK;
+}
+
+static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
+    if (W < 1 || H < 1 || F < 1) return fail(ORBX_ERR_ARG, "bad frame size / count");
+    if (!h->havePlan || h->plan.W != W || h->plan.H != H) {
+        std::vector<int16_t> tab;
+        const int rc = buildPlan(h, W, H, tab);
+        if (rc != ORBX_OK) return rc;
+        ORBX_CUDA(h->mTab.reserve(std::max<size_t>(tab.size() * sizeof(int16_t), 16)));
+        ORBX_CUDA(cudaMemcpyAsync(h->mTab.p, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
+        ORBX_CUDA(cudaStreamSynchronize(h->stream));
+        h->havePlan = true;
+        h->capFrames = 0;
+    }
+    const FramePlan& P = h->plan;
+    if (F > h->capFrames) {
+        const size_t f = (size_t)F;
+        ORBX_CUDA(h->mPyr.reserve(f * P.frameBytes + 4096));
+        ORBX_CUDA(h->mBlur.reserve(f * P.blurBytes + 4096));
+        ORBX_CUDA(h->mCand.reserve(std::max<size_t>(f * P.candWords * 4, 16)));
+        ORBX_CUDA(h->mCellCnt.reserve(std::max<size_t>(f * P.nCellsTotal * 4, 16)));
+        ORBX_CUDA(h->mGath.reserve(std::max<size_t>(f * P.gathWords * 4, 16)));
+        ORBX_CUDA(h->mNid.reserve(std::max<size_t>(f * P.gathWords * 2, 16)));
+        ORBX_CUDA(h->mLkp.reserve(f * P.lkpTotal * sizeof(LevelKp)));
+        ORBX_CUDA(h->mLkpCnt.reserve(f * P.nlevels * 4));
+        ORBX_CUDA(h->mSlot.reserve(f * P.lkpTotal * 4));
+        ORBX_CUDA(h->mOutK.reserve(f * P.outCap * 28));
+        ORBX_CUDA(h->mOutD.reserve(f * P.outCap * 32));
+        ORBX_CUDA(h->mOutN.reserve(f * 4));
+        ORBX_CUDA(h->mOutM.reserve(f * 4));
+        ORBX_CUDA(h->mErr.reserve(16));
+        ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 16, h->stream));
+        h->capFrames = F;
+    }
+    Buffers& B = h->buf;
+    B.img = (uint8_t*)h->mImg.p; B.pyr = (uint8_t*)h->mPyr.p; B.blur = (uint8_t*)h->mBlur.p;
+    B.cand = (uint32_t*)h->mCand.p; B.cellCnt = (int*)h->mCellCnt.p; B.gath = (uint32_t*)h->mGath.p;
+    B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.slot = (int*)h->mSlot.p;
+    B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
+    B.tab = (int16_t*)h->mTab.p; B.errFlag = (int*)h->mErr.p;
+    return ORBX_OK;
+}
+
+// the whole operator() pipeline for F device-resident frames, asynchronous on the handle's stream
+static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size_t frameStride, int F, int lap0, int lap1) {
+    const FramePlan& P = h->plan;
+    const Buffers& B = h->buf;
+    cudaStream_t s = h->stream;
+    cudaEventRecord(h->ev[0], s);
+    launchPyramid(P, B, dImgs, stride, frameStride, F, s);
+    cudaEventRecord(h->ev[1], s);
+    launchFast(P, B, F, s);
+    cudaEventRecord(h->ev[2], s);
+    launchQuadtree(P, B, F, s);
+    cudaEventRecord(h->ev[3], s);
+    launchBlur(P, B, F, s);
+    cudaEventRecord(h->ev[4], s);
+    launchDescribe(P, B, F, lap0, lap1, s);
+    cudaEventRecord(h->ev[5], s);
+    h->lastFrames = F;
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+static int checkDeviceFlags(orbx_extractor* h) {
+    int flag = 0;
+    ORBX_CUDA(cudaMemcpyAsync(&flag, h->mErr.p, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    if (flag) {
+        cudaMemsetAsync(h->mErr.p, 0, 16, h->stream);
+        char msg[96];
+        snprintf(msg, sizeof msg, "device-side capacity invariant violated (flags 0x%x)", flag);
+        return fail(ORBX_ERR_CAPACITY, msg);
+    }
+    return ORBX_OK;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (dev >= 0 && dev != prev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace orbx
+extern "C" {
+
+const char* orbx_last_error(void) { return tlsError.c_str(); }
+int orbx_version(void) { return 100; }
+unsigned long long orbx_launch_count(void) { return gLaunches.load(); }
+
+int orbx_create(const orbx_params* params, orbx_handle* out) {
+    if (!params || !out) return fail(ORBX_ERR_ARG, "null argument");
+    if (params->nlevels < 1 || params->nlevels > kMaxLevels) return fail(ORBX_ERR_ARG, "nlevels must be in [1,16]");
+    if (params->nfeatures < 1 || !(params->scale_factor > 1.0f)) return fail(ORBX_ERR_ARG, "bad nfeatures / scale_factor");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(ORBX_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    int dev = params->device;
+    if (dev < 0) ORBX_CUDA(cudaGetDevice(&dev));
+    if (dev >= ndev) return fail(ORBX_ERR_ARG, "device ordinal out of range");
+    DeviceGuard guard(dev);
+    orbx_extractor* h = new orbx_extractor();
+    h->prm = *params;
+    h->device = dev;
+    h->scaleFactorD = (double)params->scale_factor;
+    initTables(h);
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 7 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    if (e != cudaSuccess) {
+        delete h;
+        return fail(ORBX_ERR_CUDA, std::string("stream/event creation: ") + cudaGetErrorString(e));
+    }
+    uploadDescribeTables();
+    *out = h;
+    return ORBX_OK;
+}
+
+void orbx_destroy(orbx_handle h) {
+    if (!h) return;
+    DeviceGuard guard(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
+                     &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
+                     &h->mMatch};
+    for (DevMem* m : all) m->release();
+    for (int i = 0; i < 7; ++i)
+        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int orbx_get_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* nfeat) {
+    if (!h) return fail(ORBX_ERR_ARG, "null handle");
+    for (int i = 0; i < h->prm.nlevels; ++i) {
+        if (scale) scale[i] = h->sf[i];
+        if (inv_scale) inv_scale[i] = h->isf[i];
+        if (sigma2) sigma2[i] = h->sig2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->isig2[i];
+        if (nfeat) nfeat[i] = h->nPerLevel[i];
+    }
+    return ORBX_OK;
+}
+
+int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, int nframes, int w, int hgt, int stride,
+                              size_t frame_stride, int lap0, int lap1) {
+    if (!h || !d_imgs) return fail(ORBX_ERR_ARG, "null argument");
+    if (stride < w) return fail(ORBX_ERR_ARG, "stride < width");
+    DeviceGuard guard(h->device);
+    int rc = ensureCapacity(h, w, hgt, nframes);
+    if (rc != ORBX_OK) return rc;
+    return runPipeline(h, d_imgs, stride, frame_stride, nframes, lap0, lap1);
+}
+
+int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, int hgt, int stride, size_t frame_stride,
+                       int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* n_out,
+                       int* mono_index) {
+    if (!h || !imgs) return fail(ORBX_ERR_ARG, "null argument");
+    if (stride < w) return fail(ORBX_ERR_ARG, "stride < width");
+    DeviceGuard guard(h->device);
+    int rc = ensureCapacity(h, w, hgt, nframes);
+    if (rc != ORBX_OK) return rc;
+    const size_t frameBytes = (size_t)w * hgt;
+    ORBX_CUDA(h->mImg.reserve((size_t)nframes * frameBytes + 64));
+    h->buf.img = (uint8_t*)h->mImg.p;
+    if (stride == w && frame_stride == frameBytes) {
+        ORBX_CUDA(cudaMemcpyAsync(h->mImg.p, imgs, (size_t)nframes * frameBytes, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        for (int f = 0; f < nframes; ++f)
+            ORBX_CUDA(cudaMemcpy2DAsync((uint8_t*)h->mImg.p + (size_t)f * frameBytes, w, imgs + (size_t)f * frame_stride,
+                                        stride, w, hgt, cudaMemcpyHostToDevice, h->stream));
+    }
+    rc = runPipeline(h, (const uint8_t*)h->mImg.p, w, frameBytes, nframes, lap0, lap1);
+    if (rc != ORBX_OK) return rc;
+    const FramePlan& P = h->plan;
+    if ((kps || desc) && cap_per_frame < P.outCap) {
+        // the compact copy below needs the per-frame counts first
+        std::vector<int> n(nframes);
+        ORBX_CUDA(cudaMemcpyAsync(n.data(), h->buf.outN, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
+        ORBX_CUDA(cudaStreamSynchronize(h->stream));
+        for (int f = 0; f < nframes; ++f)
+            if (n[f] > cap_per_frame) {
+                if (n_out) std::memcpy(n_out, n.data(), (size_t)nframes * 4);
+                return fail(ORBX_ERR_CAPACITY, "cap_per_frame smaller than a frame's keypoint count");
+            }
+        if (kps)
+            ORBX_CUDA(cudaMemcpy2DAsync(kps, (size_t)cap_per_frame * 28, h->buf.outKps, (size_t)P.outCap * 28,
+                                        (size_t)cap_per_frame * 28, nframes, cudaMemcpyDeviceToHost, h->stream));
+        if (desc)
+            ORBX_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap_per_frame * 32, h->buf.outDesc, (size_t)P.outCap * 32,
+                                        (size_t)cap_per_frame * 32, nframes, cudaMemcpyDeviceToHost, h->stream));
+    } else {
+        if (kps)
+            ORBX_CUDA(cudaMemcpy2DAsync(kps, (size_t)cap_per_frame * 28, h->buf.outKps, (size_t)P.outCap * 28,
+                                        (size_t)P.outCap * 28, nframes, cudaMemcpyDeviceToHost, h->stream));
+        if (desc)
+            ORBX_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap_per_frame * 32, h->buf.outDesc, (size_t)P.outCap * 32,
+                                        (size_t)P.outCap * 32, nframes, cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (n_out) ORBX_CUDA(cudaMemcpyAsync(n_out, h->buf.outN, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (mono_index)
+        ORBX_CUDA(cudaMemcpyAsync(mono_index, h->buf.outMono, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
+    return checkDeviceFlags(h);
+}
+
+int orbx_extract(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int lap0, int lap1, orbx_keypoint* kps,
+                 uint8_t* desc, int cap, int* n_out, int* mono_index) {
+    if (!h) return fail(ORBX_ERR_ARG, "null handle");
+    if (n_out) *n_out = 0;
+    if (!img || w <= 0 || hgt <= 0) {  // ORBextractor.cc:1090-1091
+        if (mono_index) *mono_index = -1;
+        return ORBX_OK;
+    }
+    DeviceGuard guard(h->device);
+    int n = 0, mono = 0;
+    int rc = orbx_extract_batch(h, img, 1, w, hgt, stride, (size_t)stride * hgt, lap0, lap1, nullptr, nullptr, 0, &n, &mono);
+    if (rc != ORBX_OK) return rc;
+    if (n_out) *n_out = n;
+    if (mono_index) *mono_index = mono;
+    if (n > cap) return fail(ORBX_ERR_CAPACITY, "keypoint buffer too small");
+    if (kps && n) ORBX_CUDA(cudaMemcpyAsync(kps, h->buf.outKps, (size_t)n * 28, cudaMemcpyDeviceToHost, h->stream));
+    if (desc && n) ORBX_CUDA(cudaMemcpyAsync(desc, h->buf.outDesc, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_sync(orbx_handle h) {
+    if (!h) return fail(ORBX_ERR_ARG, "null handle");
+    DeviceGuard guard(h->device);
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_last_timing(orbx_handle h, float* total_ms, float stage_ms[5]) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    DeviceGuard guard(h->device);
+    ORBX_CUDA(cudaEventSynchronize(h->ev[5]));
+    if (total_ms) ORBX_CUDA(cudaEventElapsedTime(total_ms, h->ev[0], h->ev[5]));
+    if (stage_ms)
+        for (int i = 0; i < 5; ++i) ORBX_CUDA(cudaEventElapsedTime(&stage_ms[i], h->ev[i], h->ev[i + 1]));
+    return ORBX_OK;
+}
+
+int orbx_batch_results(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc, const int** d_n,
+                       const int** d_mono, int* cap_per_frame) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (d_kps) *d_kps = (const orbx_keypoint*)h->buf.outKps;
+    if (d_desc) *d_desc = h->buf.outDesc;
+    if (d_n) *d_n = h->buf.outN;
+    if (d_mono) *d_mono = h->buf.outMono;
+    if (cap_per_frame) *cap_per_frame = h->plan.outCap;
+    return ORBX_OK;
+}
+
+int orbx_batch_download(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (frame < 0 || frame >= h->lastFrames) return fail(ORBX_ERR_ARG, "frame out of range");
+    DeviceGuard guard(h->device);
+    int nm[2] = {0, 0};
+    ORBX_CUDA(cudaMemcpyAsync(&nm[0], h->buf.outN + frame, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaMemcpyAsync(&nm[1], h->buf.outMono + frame, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    if (n_out) *n_out = nm[0];
+    if (mono_index) *mono_index = nm[1];
+    if (nm[0] > cap) return fail(ORBX_ERR_CAPACITY, "keypoint buffer too small");
+    const size_t o = (size_t)frame * h->plan.outCap;
+    if (kps && nm[0]) ORBX_CUDA(cudaMemcpyAsync(kps, (uint8_t*)h->buf.outKps + o * 28, (size_t)nm[0] * 28, cudaMemcpyDeviceToHost, h->stream));
+    if (desc && nm[0]) ORBX_CUDA(cudaMemcpyAsync(desc, h->buf.outDesc + o * 32, (size_t)nm[0] * 32, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return checkDeviceFlags(h);
+}
+
+int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* out, int* w, int* hgt) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (frame < 0 || frame >= h->lastFrames || level < 0 || level >= h->plan.nlevels) return fail(ORBX_ERR_ARG, "frame/level out of range");
+    const LevelPlan& L = h->plan.lv[level];
+    if (w) *w = L.w;
+    if (hgt) *hgt = L.h;
+    if (!out) return ORBX_OK;
+    DeviceGuard guard(h->device);
+    const int pw = L.w + 2 * kEdge, ph = L.h + 2 * kEdge;
+    ORBX_CUDA(cudaMemcpy2DAsync(out, pw, h->buf.pyr + (size_t)frame * h->plan.frameBytes + L.planeOff, L.pitch, pw, ph,
+                                cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_get_blurred(orbx_handle h, int frame, int level, uint8_t* out, int* w, int* hgt) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (frame < 0 || frame >= h->lastFrames || level < 0 || level >= h->plan.nlevels) return fail(ORBX_ERR_ARG, "frame/level out of range");
+    const LevelPlan& L = h->plan.lv[level];
+    if (w) *w = L.w;
+    if (hgt) *hgt = L.h;
+    if (!out) return ORBX_OK;
+    DeviceGuard guard(h->device);
+    ORBX_CUDA(cudaMemcpy2DAsync(out, L.w, h->buf.blur + (size_t)frame * h->plan.blurBytes + L.blurOff, L.bpitch, L.w, L.h,
+                                cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_get_candidates(orbx_handle h, int frame, int level, int32_t* out, int cap, int* n_out) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (frame < 0 || frame >= h->lastFrames || level < 0 || level >= h->plan.nlevels) return fail(ORBX_ERR_ARG, "frame/level out of range");
+    DeviceGuard guard(h->device);
+    const FramePlan& P = h->plan;
+    const LevelPlan& L = P.lv[level];
+    const int nCells = L.nCols * L.nRows;
+    std::vector<int> cnt(std::max(nCells, 1));
+    if (nCells) ORBX_CUDA(cudaMemcpyAsync(cnt.data(), h->buf.cellCnt + (size_t)frame * P.nCellsTotal + L.cellBase, (size_t)nCells * 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    int n = 0;
+    for (int c = 0; c < nCells; ++c) n += cnt[c];
+    if (n_out) *n_out = n;
+    if (!out) return ORBX_OK;
+    if (n > cap) return fail(ORBX_ERR_CAPACITY, "candidate buffer too small");
+    std::vector<uint32_t> slots((size_t)std::max(L.maxCand, 1));
+    if (L.maxCand) ORBX_CUDA(cudaMemcpyAsync(slots.data(), h->buf.cand + (size_t)frame * P.candWords + L.candOff, (size_t)L.maxCand * 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    int o = 0;
+    for (int c = 0; c < nCells; ++c)
+        for (int k = 0; k < cnt[c]; ++k) {
+            const uint32_t p = slots[(size_t)c * L.cellCap + k];
+            out[3 * o] = p & 0xfff; out[3 * o + 1] = (p >> 12) & 0xfff; out[3 * o + 2] = p >> 24;
+            ++o;
+        }
+    return ORBX_OK;
+}
+
+int orbx_synth_frames_device(uint8_t* d_out, int k0, int nframes, int w, int hgt, uint64_t seed, int right, int device) {
+    if (!d_out || nframes < 1 || w < 1 || hgt < 1) return fail(ORBX_ERR_ARG, "bad argument");
+    DeviceGuard guard(device);
+    launchSynth(d_out, k0, nframes, w, hgt, seed, right, nullptr);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaDeviceSynchronize());
+    return ORBX_OK;
+}
+
+}  // extern "C"
+// ======================================================================================================
+// Matching
+// ======================================================================================================
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace orbx {
+
+// scratch for the non-handle matching entry points (per thread, per device)
+struct MatchScratch {
+    int device = -1;
+    DevMem q, db, k1, k2, i1, i2, d1, d2, misc;
+    cudaStream_t stream = nullptr;
+};
+static thread_local MatchScratch tlsMatch;
+
+static int matchScratch(int device, MatchScratch** out) {
+    MatchScratch& S = tlsMatch;
+    if (S.device != device) {
+        if (S.device >= 0) {
+            DeviceGuard g(S.device);
+            DevMem* all[] = {&S.q, &S.db, &S.k1, &S.k2, &S.i1, &S.i2, &S.d1, &S.d2, &S.misc};
+            for (DevMem* m : all) m->release();
+            if (S.stream) cudaStreamDestroy(S.stream);
+            S.stream = nullptr;
+        }
+        S.device = device;
+    }
+    if (!S.stream) ORBX_CUDA(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
+    *out = &S;
+    return ORBX_OK;
+}
+
+static int smCount() {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+}
+
+// local top-2 keys (one candidate set: all chunks already merged) of q x db on the current device
+static int localTop2Keys(const uint8_t* dq, int nq, const uint8_t* ddb, int64_t nd, int64_t base, DevMem& k1, DevMem& k2,
+                         int* nsets, cudaStream_t s) {
+    const int chunks = nd > 0 ? matchNumChunks(nq, nd, smCount()) : 0;
+    ORBX_CUDA(k1.reserve(std::max<size_t>((size_t)std::max(chunks, 1) * nq * 8, 16)));
+    ORBX_CUDA(k2.reserve(std::max<size_t>((size_t)std::max(chunks, 1) * nq * 8, 16)));
+    if (chunks == 0) {
+        ORBX_CUDA(cudaMemsetAsync(k1.p, 0xff, (size_t)nq * 8, s));
+        ORBX_CUDA(cudaMemsetAsync(k2.p, 0xff, (size_t)nq * 8, s));
+        *nsets = 1;
+        return ORBX_OK;
+    }
+    launchMatchTop2(dq, nq, ddb, nd, base, (uint64_t*)k1.p, (uint64_t*)k2.p, s);
+    *nsets = chunks;
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// ---- NCCL through dlopen: the extractor half of the library must load on hosts without NCCL -------------------
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi gNccl;
+static std::mutex gNcclMutex;
+
+static int loadNccl() {
+    std::lock_guard<std::mutex> lock(gNcclMutex);
+    if (gNccl.lib) return ORBX_OK;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return fail(ORBX_ERR_NCCL, std::string("cannot load libnccl.so.2: ") + dlerror());
+    gNccl.GetUniqueId = (decltype(gNccl.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    gNccl.CommInitRank = (decltype(gNccl.CommInitRank))dlsym(lib, "ncclCommInitRank");
+    gNccl.CommDestroy = (decltype(gNccl.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    gNccl.AllGather = (decltype(gNccl.AllGather))dlsym(lib, "ncclAllGather");
+    gNccl.GetErrorString = (decltype(gNccl.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    if (!gNccl.GetUniqueId || !gNccl.CommInitRank || !gNccl.CommDestroy || !gNccl.AllGather || !gNccl.GetErrorString)
+        return fail(ORBX_ERR_NCCL, "libnccl lacks a required symbol");
+    gNccl.lib = lib;
+    return ORBX_OK;
+}
+#define ORBX_NCCL(expr)                                                                               \
+    do {                                                                                              \
+        ncclResult_t r_ = (expr);                                                                     \
+        if (r_ != ncclSuccess) return fail(ORBX_ERR_NCCL, std::string(#expr) + ": " + gNccl.GetErrorString(r_)); \
+    } while (0)
+
+}  // namespace orbx
+
+struct orbx_comm_s {
+    ncclComm_t comm = nullptr;
+    int rank = 0, nranks = 1, device = 0;
+    cudaStream_t stream = nullptr;
+    DevMem k1, k2, loc, gathered;
+};
+
+extern "C" {
+
+// ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074): sum of popcounts of eight 32-bit XOR words
+int orbx_hamming(const uint8_t* a, const uint8_t* b) {
+    uint32_t pa[8], pb[8];
+    std::memcpy(pa, a, 32);
+    std::memcpy(pb, b, 32);
+    int dist = 0;
+    for (int i = 0; i < 8; ++i) dist += __builtin_popcount(pa[i] ^ pb[i]);
+    return dist;
+}
+
+int orbx_match_top2_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t nd, int64_t db_index_base,
+                           int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream) {
+    if (nq < 0 || nd < 0 || (nq > 0 && !d_q) || (nd > 0 && !d_db)) return fail(ORBX_ERR_ARG, "bad argument");
+    if (nq == 0) return ORBX_OK;
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    int rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    int nsets = 1;
+    rc = localTop2Keys(d_q, nq, d_db, nd, db_index_base, S->k1, S->k2, &nsets, s);
+    if (rc != ORBX_OK) return rc;
+    launchUnpackTop2((const uint64_t*)S->k1.p, (const uint64_t*)S->k2.p, nsets, nq, d_idx1, d_d1, d_idx2, d_d2, s);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int orbx_match_top2(const uint8_t* q, int nq, const uint8_t* db, int64_t nd, int64_t* idx1, int32_t* d1, int64_t* idx2,
+                    int32_t* d2, int device) {
+    if (nq < 0 || nd < 0 || (nq > 0 && !q) || (nd > 0 && !db) || !idx1 || !d1 || !idx2 || !d2) return fail(ORBX_ERR_ARG, "bad argument");
+    if (nq == 0) return ORBX_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(ORBX_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    int rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA(S->q.reserve((size_t)nq * 32));
+    ORBX_CUDA(S->db.reserve(std::max<size_t>((size_t)nd * 32, 16)));
+    ORBX_CUDA(S->i1.reserve((size_t)nq * 8));
+    ORBX_CUDA(S->i2.reserve((size_t)nq * 8));
+    ORBX_CUDA(S->d1.reserve((size_t)nq * 4));
+    ORBX_CUDA(S->d2.reserve((size_t)nq * 4));
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaMemcpyAsync(S->q.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    if (nd) ORBX_CUDA(cudaMemcpyAsync(S->db.p, db, (size_t)nd * 32, cudaMemcpyHostToDevice, s));
+    rc = orbx_match_top2_device((const uint8_t*)S->q.p, nq, (const uint8_t*)S->db.p, nd, 0, (int64_t*)S->i1.p,
+                                (int32_t*)S->d1.p, (int64_t*)S->i2.p, (int32_t*)S->d2.p, s);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA(cudaMemcpyAsync(idx1, S->i1.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(idx2, S->i2.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(d1, S->d1.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(d2, S->d2.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_merge_top2_device(const uint64_t* d_keys1, const uint64_t* d_keys2, int nranks, int nq, int64_t* d_idx1,
+                           int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream) {
+    if (!d_keys1 || !d_keys2 || nranks < 1 || nq < 0) return fail(ORBX_ERR_ARG, "bad argument");
+    launchUnpackTop2(d_keys1, d_keys2, nranks, nq, d_idx1, d_d1, d_idx2, d_d2, (cudaStream_t)stream);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int orbx_match_batch_consecutive(orbx_handle h, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, int to_host) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (!idx1 || !d1 || !idx2 || !d2) return fail(ORBX_ERR_ARG, "null output");
+    const int F = h->lastFrames, cap = h->plan.outCap;
+    if (F < 2) return ORBX_OK;
+    DeviceGuard guard(h->device);
+    const size_t n = (size_t)(F - 1) * cap;
+    ORBX_CUDA(h->mKeys1.reserve(n * 8));
+    ORBX_CUDA(h->mKeys2.reserve(n * 8));
+    int32_t *o1 = idx1, *o2 = d1, *o3 = idx2, *o4 = d2;
+    if (to_host) {
+        ORBX_CUDA(h->mMatch.reserve(n * 16));
+        o1 = (int32_t*)h->mMatch.p; o2 = o1 + n; o3 = o2 + n; o4 = o3 + n;
+    }
+    launchMatchConsecutive(h->buf.outDesc, h->buf.outN, F, cap, (uint64_t*)h->mKeys1.p, (uint64_t*)h->mKeys2.p, o1, o2, o3,
+                           o4, h->stream);
+    ORBX_CUDA(cudaGetLastError());
+    if (to_host) {
+        ORBX_CUDA(cudaMemcpyAsync(idx1, o1, n * 4, cudaMemcpyDeviceToHost, h->stream));
+        ORBX_CUDA(cudaMemcpyAsync(d1, o2, n * 4, cudaMemcpyDeviceToHost, h->stream));
+        ORBX_CUDA(cudaMemcpyAsync(idx2, o3, n * 4, cudaMemcpyDeviceToHost, h->stream));
+        ORBX_CUDA(cudaMemcpyAsync(d2, o4, n * 4, cudaMemcpyDeviceToHost, h->stream));
+        ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    return ORBX_OK;
+}
+
+int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, int nl, const orbx_keypoint* kps_r,
+                             const uint8_t* desc_r, int nr, const float* scale_factors, int nlevels, int n_rows,
+                             float max_d, int32_t* best_idx, int32_t* best_dist, int device) {
+    if (nl < 0 || nr < 0 || !scale_factors || nlevels < 1 || !best_idx || !best_dist) return fail(ORBX_ERR_ARG, "bad argument");
+    if (nl == 0) return ORBX_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(ORBX_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    int rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    const size_t bl = (size_t)nl * 60, br = (size_t)std::max(nr, 1) * 60;
+    ORBX_CUDA(S->q.reserve(bl + 64));
+    ORBX_CUDA(S->db.reserve(br + 64));
+    ORBX_CUDA(S->misc.reserve((size_t)nlevels * 4 + (size_t)nl * 8 + 64));
+    cudaStream_t s = S->stream;
+    // layout: descriptors first (16-B aligned), keypoints after
+    uint8_t* dl = (uint8_t*)S->q.p; uint8_t* kl = dl + (size_t)nl * 32;
+    uint8_t* dr = (uint8_t*)S->db.p; uint8_t* kr = dr + (size_t)std::max(nr, 1) * 32;
+    float* sf = (float*)S->misc.p;
+    int32_t* bi = (int32_t*)((uint8_t*)S->misc.p + (((size_t)nlevels * 4 + 15) & ~(size_t)15));
+    int32_t* bd = bi + nl;
+    ORBX_CUDA(cudaMemcpyAsync(dl, desc_l, (size_t)nl * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(kl, kps_l, (size_t)nl * 28, cudaMemcpyHostToDevice, s));
+    if (nr) {
+        ORBX_CUDA(cudaMemcpyAsync(dr, desc_r, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
+        ORBX_CUDA(cudaMemcpyAsync(kr, kps_r, (size_t)nr * 28, cudaMemcpyHostToDevice, s));
+    }
+    ORBX_CUDA(cudaMemcpyAsync(sf, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, s));
+    launchStereoBanded(kl, dl, nl, kr, dr, nr, sf, n_rows, max_d, bi, bd, s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(best_idx, bi, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(best_dist, bd, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+// ---- sharded database ------------------------------------------------------------------------------------
+int orbx_comm_unique_id(uint8_t id[128]) {
+    int rc = loadNccl();
+    if (rc != ORBX_OK) return rc;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    ncclUniqueId u;
+    ORBX_NCCL(gNccl.GetUniqueId(&u));
+    std::memcpy(id, &u, 128);
+    return ORBX_OK;
+}
+
+int orbx_comm_init(int rank, int nranks, const uint8_t id[128], int device, orbx_comm* out) {
+    if (!out || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(ORBX_ERR_ARG, "bad argument");
+    int rc = loadNccl();
+    if (rc != ORBX_OK) return rc;
+    if (device >= 0) ORBX_CUDA(cudaSetDevice(device));
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    orbx_comm_s* c = new orbx_comm_s();
+    c->rank = rank; c->nranks = nranks; c->device = dev;
+    ncclUniqueId u;
+    std::memcpy(&u, id, 128);
+    ncclResult_t r = gNccl.CommInitRank(&c->comm, nranks, u, rank);
+    if (r != ncclSuccess) {
+        delete c;
+        return fail(ORBX_ERR_NCCL, std::string("ncclCommInitRank: ") + gNccl.GetErrorString(r));
+    }
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        gNccl.CommDestroy(c->comm);
+        delete c;
+        return fail(ORBX_ERR_CUDA, cudaGetErrorString(e));
+    }
+    *out = c;
+    return ORBX_OK;
+}
+
+void orbx_comm_destroy(orbx_comm c) {
+    if (!c) return;
+    DeviceGuard guard(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm) gNccl.CommDestroy(c->comm);
+    c->k1.release(); c->k2.release(); c->loc.release(); c->gathered.release();
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+// local top-2 on this rank's shard -> pack (k1[nq] | k2[nq]) -> ncclAllGather over NVLink -> merge on every rank.
+// Synchronous with respect to the host on return.
+int orbx_match_top2_sharded(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local,
+                            int64_t db_index_base, int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2) {
+    if (!c || nq < 1 || !d_q || nd_local < 0) return fail(ORBX_ERR_ARG, "bad argument");
+    DeviceGuard guard(c->device);
+    cudaStream_t s = c->stream;
+    int nsets = 1;
+    int rc = localTop2Keys(d_q, nq, d_db_local, nd_local, db_index_base, c->k1, c->k2, &nsets, s);
+    if (rc != ORBX_OK) return rc;
+    // reduce this rank's chunks to one candidate set, written as keys into loc = [k1 | k2]
+    ORBX_CUDA(c->loc.reserve((size_t)nq * 16));
+    ORBX_CUDA(c->gathered.reserve((size_t)c->nranks * nq * 16));
+    orbx::launchReduceKeys((const uint64_t*)c->k1.p, (const uint64_t*)c->k2.p, nsets, nq, (uint64_t*)c->loc.p,
+                           (uint64_t*)c->loc.p + nq, s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_NCCL(gNccl.AllGather(c->loc.p, c->gathered.p, (size_t)nq * 2, ncclUint64, c->comm, s));
+    // gathered layout: [rank][k1[nq] | k2[nq]]  -> strided candidate sets
+    orbx::launchUnpackTop2Strided((const uint64_t*)c->gathered.p, (const uint64_t*)c->gathered.p + nq, c->nranks, nq,
+                                  (size_t)nq * 2, d_idx1, d_d1, d_idx2, d_d2, s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,112 @@
+// orbx_internal.cuh — shared declarations of the sm_100a ORB frontend (not part of the C ABI).
+//
+// Data layout in HBM (one "batch" = F equally sized frames, everything indexed [frame][level]):
+//   pyr    F x frameBytes     padded pyramid planes, plane l = (h_l+38) rows of pitch_l bytes (pitch multiple
+//                             of 128 B so TMA boxes and 16-B vector rows are legal); the level itself is the
+//                             ROI at (19,19)  — this IS mvImagePyramid (ORBextractor.cc:1176-1178)
+//   blur   F x blurBytes      GaussianBlur'ed levels (no border), pitch multiple of 128 B
+//   cand   F x candWords      per FAST cell a fixed slot of cellCap_l packed candidates
+//                             (resp<<24 | y<<12 | x, cell-offset coordinates) + cellCnt F x nCells
+//   lkp    F x lkpCap         keypoints surviving the quadtree, per level slot of (N_l+4), list order
+//   out    F x cap            final cv::KeyPoint records + F x cap x 32 descriptor bytes, in operator()'s order
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace orbx {
+
+constexpr int kMaxLevels = 16;
+constexpr int kEdge = 19;       // EDGE_THRESHOLD  (ORBextractor.cc:73)
+constexpr int kHalfPatch = 15;  // HALF_PATCH_SIZE (ORBextractor.cc:72)
+constexpr int kPatch = 31;      // PATCH_SIZE      (ORBextractor.cc:71)
+constexpr int kMinBorder = kEdge - 3;  // 16 (ORBextractor.cc:789)
+constexpr float kCellW = 35.f;         // ORBextractor.cc:785
+
+struct LevelPlan {
+    int w, h;            // level size
+    int pitch;           // padded plane pitch (bytes)
+    int bpitch;          // blurred plane pitch
+    unsigned planeOff;   // byte offset of the padded plane inside a frame's pyramid block
+    unsigned blurOff;    // byte offset of the blurred plane inside a frame's blur block
+    int nCols, nRows, wCell, hCell;  // FAST grid (ORBextractor.cc:797-803)
+    int cellCap;         // upper bound of NMS survivors per cell = ceil(wCell/2)*ceil(hCell/2)
+    int cellBase;        // first cell of this level in the frame's cell arrays
+    unsigned candOff;    // word offset of this level's candidate slots inside a frame's cand block
+    int maxCand;         // nCols*nRows*cellCap (capacity of the contiguous candidate list)
+    unsigned gathOff;    // word offset of the level's gathered candidate list in a frame's gather block
+    int nFeat;           // mnFeaturesPerLevel[l]
+    int lkpBase;         // first slot of this level in the frame's level-keypoint array
+    int lkpCap;          // nFeat + 4 (F5: the quadtree returns N..N+3)
+    int tabX, tabY;      // offsets into the resize coefficient table (int16 triplets ofs,a0,a1)
+    float scale;         // mvScaleFactor[l]
+    float patchSize;     // (float)(int)(31*scale) (ORBextractor.cc:879)
+};
+
+struct FramePlan {
+    int nlevels;
+    int W, H;
+    int nCellsTotal;
+    int lkpTotal;       // sum of lkpCap
+    int outCap;         // keypoint capacity per frame in the final arrays
+    unsigned frameBytes, blurBytes, candWords, gathWords;
+    int iniTh, minTh;
+    int fpMode;
+    LevelPlan lv[kMaxLevels];
+};
+
+// Keypoint kept by the quadtree, level coordinates (already offset by minBorder).
+struct LevelKp {
+    short x, y;
+    short resp;
+    short level;
+};
+
+struct Buffers {
+    uint8_t* img;        // staged input frames (F x H x W compact) when the caller passes host memory
+    uint8_t* pyr;
+    uint8_t* blur;
+    uint32_t* cand;
+    int* cellCnt;        // F x nCellsTotal
+    uint32_t* gath;      // gathered candidates F x gathWords
+    uint16_t* nid;       // node id per gathered candidate, F x gathWords
+    LevelKp* lkp;        // F x lkpTotal
+    int* lkpCnt;         // F x nlevels
+    int* slot;           // F x lkpTotal : final output slot of each level keypoint
+    void* outKps;        // F x outCap x 28 B
+    uint8_t* outDesc;    // F x outCap x 32 B
+    int* outN;           // F
+    int* outMono;        // F
+    int16_t* tab;        // resize coefficient tables
+    int* errFlag;        // device-side invariant violations (capacity overflow)
+};
+
+// kernel launchers (each in its own .cu); all asynchronous on `s`
+void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
+                   cudaStream_t s);
+void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s);
+size_t quadtreeSmemBytes(const FramePlan& P);
+
+void launchSynth(uint8_t* dOut, int k0, int F, int w, int h, uint64_t seed, int right, cudaStream_t s);
+
+int matchNumChunks(int nq, int64_t nd, int sms);
+void launchMatchTop2(const uint8_t* dq, int nq, const uint8_t* ddb, int64_t nd, int64_t base, uint64_t* dKeys1,
+                     uint64_t* dKeys2, cudaStream_t s);
+void launchUnpackTop2(const uint64_t* k1, const uint64_t* k2, int nsets, int nq, int64_t* idx1, int32_t* d1,
+                      int64_t* idx2, int32_t* d2, cudaStream_t s);
+void launchUnpackTop2Strided(const uint64_t* k1, const uint64_t* k2, int nsets, int nq, size_t setStride, int64_t* idx1,
+                             int32_t* d1, int64_t* idx2, int32_t* d2, cudaStream_t s);
+void launchReduceKeys(const uint64_t* k1, const uint64_t* k2, int nsets, int nq, uint64_t* outK1, uint64_t* outK2,
+                      cudaStream_t s);
+void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap, uint64_t* keys1, uint64_t* keys2,
+                            int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, cudaStream_t s);
+void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
+                        const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s);
+void uploadDescribeTables();
+
+void countLaunch(int n = 1);
+
+}  // namespace orbx
