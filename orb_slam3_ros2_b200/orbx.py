@@ -1,0 +1,343 @@
+"""ctypes binding of the C ABI (include/orbx.h) and a host-side mirror of the reference's class surface.
+
+`ORBextractor` mirrors ORB_SLAM3::ORBextractor (ORB_SLAM3/include/ORBextractor.h:43-109): same constructor
+arguments, `__call__(image, mask, lapping_area)` returning what operator() produces (monoIndex, keypoints,
+descriptors), `mvImagePyramid`, and the Get* accessors.  `DescriptorDistance`, `TH_LOW`, `TH_HIGH` mirror
+ORBmatcher (ORB_SLAM3/src/ORBmatcher.cc:35-37, :2058-2074).
+
+There is no CPU fallback: if liborbx.so is missing this module raises at import, and every compute call
+fails with OrbxError when no CUDA device is present.  Nothing here imports oracle/.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liborbx.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+TH_HIGH = 100          # ORBmatcher.cc:35
+TH_LOW = 50            # ORBmatcher.cc:36
+HISTO_LENGTH = 30      # ORBmatcher.cc:37
+
+ORBX_OK, ORBX_ERR_ARG, ORBX_ERR_CUDA, ORBX_ERR_CAPACITY, ORBX_ERR_NCCL, ORBX_ERR_STATE = 0, -1, -2, -3, -4, -5
+
+
+class OrbxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"orbx error {code}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("scale_factor", C.c_float), ("nlevels", C.c_int), ("ini_th_fast", C.c_int),
+                ("min_th_fast", C.c_int), ("device", C.c_int), ("fp_mode", C.c_int)]
+
+
+_u8p = C.POINTER(C.c_uint8)
+_i32p = C.POINTER(C.c_int32)
+_i64p = C.POINTER(C.c_int64)
+_f32p = C.POINTER(C.c_float)
+_vp = C.c_void_p
+
+# every symbol include/orbx.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "orbx_last_error": (C.c_char_p, []),
+    "orbx_version": (C.c_int, []),
+    "orbx_launch_count": (C.c_ulonglong, []),
+    "orbx_create": (C.c_int, [C.POINTER(Params), C.POINTER(_vp)]),
+    "orbx_destroy": (None, [_vp]),
+    "orbx_get_tables": (C.c_int, [_vp, _f32p, _f32p, _f32p, _f32p, _i32p]),
+    "orbx_extract": (C.c_int, [_vp, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
+    "orbx_get_pyramid": (C.c_int, [_vp, C.c_int, C.c_int, _u8p, _i32p, _i32p]),
+    "orbx_extract_batch": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, _vp, _vp,
+                                     C.c_int, _vp, _vp]),
+    "orbx_extract_batch_device": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int]),
+    "orbx_batch_results": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i32p]),
+    "orbx_batch_download": (C.c_int, [_vp, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
+    "orbx_sync": (C.c_int, [_vp]),
+    "orbx_last_timing": (C.c_int, [_vp, _f32p, _f32p]),
+    "orbx_get_candidates": (C.c_int, [_vp, C.c_int, C.c_int, _i32p, C.c_int, _i32p]),
+    "orbx_get_blurred": (C.c_int, [_vp, C.c_int, C.c_int, _u8p, _i32p, _i32p]),
+    "orbx_synth_frames_device": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int]),
+    "orbx_hamming": (C.c_int, [_u8p, _u8p]),
+    "orbx_match_top2": (C.c_int, [_u8p, C.c_int, _u8p, C.c_int64, _i64p, _i32p, _i64p, _i32p, C.c_int]),
+    "orbx_match_top2_device": (C.c_int, [_vp, C.c_int, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_match_batch_consecutive": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int]),
+    "orbx_match_stereo_banded": (C.c_int, [_vp, _u8p, C.c_int, _vp, _u8p, C.c_int, _f32p, C.c_int, C.c_int, C.c_float,
+                                           _i32p, _i32p, C.c_int]),
+    "orbx_comm_unique_id": (C.c_int, [_u8p]),
+    "orbx_comm_init": (C.c_int, [C.c_int, C.c_int, _u8p, C.c_int, C.POINTER(_vp)]),
+    "orbx_comm_destroy": (None, [_vp]),
+    "orbx_match_top2_sharded": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp]),
+    "orbx_merge_top2_device": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded liborbx.so.  Raises (no fallback) if the CUDA extension has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `make -C orb_slam3_ros2_b200/csrc` "
+                              "(or __graft_entry__.build()); this package has no CPU path")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(l, name)  # AttributeError = header/library mismatch
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def _check(rc):
+    if rc != ORBX_OK:
+        raise OrbxError(rc, lib().orbx_last_error().decode(errors="replace"))
+
+
+def _ptr(a, t=_u8p):
+    return a.ctypes.data_as(t)
+
+
+def launch_count():
+    return int(lib().orbx_launch_count())
+
+
+class ORBextractor:
+    """Mirror of ORB_SLAM3::ORBextractor (ORBextractor.h:43-109) over the C ABI."""
+    HARRIS_SCORE, FAST_SCORE = 0, 1  # ORBextractor.h:47
+
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device=-1, fp_mode="strict"):
+        self._h = _vp()
+        self.nfeatures, self.nlevels = int(nfeatures), int(nlevels)
+        p = Params(int(nfeatures), float(scaleFactor), int(nlevels), int(iniThFAST), int(minThFAST), int(device),
+                   0 if fp_mode == "strict" else 1)
+        _check(lib().orbx_create(C.byref(p), C.byref(self._h)))
+        f = [np.zeros(self.nlevels, dtype=np.float32) for _ in range(4)]
+        self._nfeat = np.zeros(self.nlevels, dtype=np.int32)
+        _check(lib().orbx_get_tables(self._h, *[_ptr(a, _f32p) for a in f], _ptr(self._nfeat, _i32p)))
+        self._sf, self._isf, self._sig2, self._isig2 = f
+        self._scale_factor = np.float32(np.float64(np.float32(scaleFactor)))
+        self.mvImagePyramid = []
+        self._w = self._h_img = 0
+        self._frames = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().orbx_destroy(self._h)
+            self._h = _vp()
+
+    __del__ = close
+
+    # --- accessors (ORBextractor.h:61-83)
+    def GetLevels(self): return self.nlevels
+    def GetScaleFactor(self): return float(self._scale_factor)
+    def GetScaleFactors(self): return self._sf.copy()
+    def GetInverseScaleFactors(self): return self._isf.copy()
+    def GetScaleSigmaSquares(self): return self._sig2.copy()
+    def GetInverseScaleSigmaSquares(self): return self._isig2.copy()
+    def features_per_level(self): return self._nfeat.copy()
+
+    @property
+    def capacity(self):
+        """Upper bound of keypoints per frame (sum over levels of N_l + 4)."""
+        return int(self._nfeat.sum()) + 4 * self.nlevels
+
+    # --- operator() (ORBextractor.cc:1086-1168)
+    def __call__(self, image, mask=None, vLappingArea=(0, 1000), pyramid=True):
+        """-> (monoIndex, keypoints[KP_DTYPE], descriptors[n,32]).  `mask` is ignored, as in the reference."""
+        cap = self.capacity
+        kps = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        n, mono = C.c_int32(0), C.c_int32(0)
+        if image is None or image.size == 0:
+            _check(lib().orbx_extract(self._h, None, 0, 0, 0, vLappingArea[0], vLappingArea[1], None, None, 0,
+                                      C.byref(n), C.byref(mono)))
+            return mono.value, kps[:0], desc[:0]
+        assert image.dtype == np.uint8 and image.ndim == 2  # assert(image.type() == CV_8UC1), ORBextractor.cc:1094
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        h, w = image.shape
+        _check(lib().orbx_extract(self._h, _ptr(image), w, h, image.strides[0], vLappingArea[0], vLappingArea[1],
+                                  kps.ctypes.data_as(_vp), _ptr(desc), cap, C.byref(n), C.byref(mono)))
+        self._frames = 1
+        if pyramid:
+            self.mvImagePyramid = [self.pyramid_level(0, l)[19:-19, 19:-19] for l in range(self.nlevels)]
+        return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def pyramid_level(self, frame, level):
+        """Padded plane (h+38, w+38) of `level`; mvImagePyramid[level] is its [19:-19, 19:-19] view."""
+        w, h = C.c_int32(0), C.c_int32(0)
+        _check(lib().orbx_get_pyramid(self._h, frame, level, None, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value + 38, w.value + 38), dtype=np.uint8)
+        _check(lib().orbx_get_pyramid(self._h, frame, level, _ptr(out), None, None))
+        return out
+
+    def blurred_level(self, frame, level):
+        w, h = C.c_int32(0), C.c_int32(0)
+        _check(lib().orbx_get_blurred(self._h, frame, level, None, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), dtype=np.uint8)
+        _check(lib().orbx_get_blurred(self._h, frame, level, _ptr(out), None, None))
+        return out
+
+    def candidates(self, frame, level):
+        n = C.c_int32(0)
+        _check(lib().orbx_get_candidates(self._h, frame, level, None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), 3), dtype=np.int32)
+        _check(lib().orbx_get_candidates(self._h, frame, level, _ptr(out, _i32p), n.value, C.byref(n)))
+        return out[:n.value]
+
+    # --- batch path (frames are independent: ORBextractor holds only constants + scratch)
+    def extract_batch(self, images, vLappingArea=(0, 1000), download=True):
+        """images: (F, H, W) uint8 host array.  -> (mono[F], n[F], kps[F,cap], desc[F,cap,32])"""
+        images = np.ascontiguousarray(images, dtype=np.uint8)
+        F, h, w = images.shape
+        cap = self.capacity
+        n = np.zeros(F, dtype=np.int32)
+        mono = np.zeros(F, dtype=np.int32)
+        kps = np.zeros((F, cap), dtype=KP_DTYPE) if download else None
+        desc = np.zeros((F, cap, 32), dtype=np.uint8) if download else None
+        _check(lib().orbx_extract_batch(self._h, images.ctypes.data_as(_vp), F, w, h, w, w * h, vLappingArea[0],
+                                        vLappingArea[1], kps.ctypes.data_as(_vp) if download else None,
+                                        desc.ctypes.data_as(_vp) if download else None, cap, n.ctypes.data_as(_vp),
+                                        mono.ctypes.data_as(_vp)))
+        self._frames = F
+        return mono, n, kps, desc
+
+    def extract_batch_ptr(self, host_ptr, F, w, h, vLappingArea, kps_ptr, desc_ptr, cap, n_ptr, mono_ptr):
+        """Raw-pointer form (pinned host buffers owned by the caller; used by bench.py's e2e leg)."""
+        _check(lib().orbx_extract_batch(self._h, host_ptr, F, w, h, w, w * h, vLappingArea[0], vLappingArea[1], kps_ptr,
+                                        desc_ptr, cap, n_ptr, mono_ptr))
+        self._frames = F
+
+    def extract_batch_device(self, dev_ptr, F, w, h, vLappingArea=(0, 1000), stride=None, frame_stride=None):
+        _check(lib().orbx_extract_batch_device(self._h, dev_ptr, F, w, h, stride or w, frame_stride or w * h,
+                                               vLappingArea[0], vLappingArea[1]))
+        self._frames = F
+
+    def sync(self):
+        _check(lib().orbx_sync(self._h))
+
+    def timing(self):
+        """-> (total_ms, [pyramid, fast, quadtree, blur, describe] ms) of the last batch (CUDA events)."""
+        tot = C.c_float(0)
+        st = (C.c_float * 5)()
+        _check(lib().orbx_last_timing(self._h, C.byref(tot), st))
+        return tot.value, [st[i] for i in range(5)]
+
+    def download(self, frame):
+        cap = self.capacity
+        kps = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        n, mono = C.c_int32(0), C.c_int32(0)
+        _check(lib().orbx_batch_download(self._h, frame, kps.ctypes.data_as(_vp), _ptr(desc), cap, C.byref(n),
+                                         C.byref(mono)))
+        return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def results_device(self):
+        """-> (d_kps, d_desc, d_n, d_mono, cap) raw device addresses of the last batch."""
+        p = [_vp() for _ in range(4)]
+        cap = C.c_int32(0)
+        _check(lib().orbx_batch_results(self._h, *[C.byref(x) for x in p], C.byref(cap)))
+        return p[0].value, p[1].value, p[2].value, p[3].value, cap.value
+
+    def match_consecutive(self):
+        """Top-2 of frame f against frame f+1 over the last batch -> idx1, d1, idx2, d2, each (F-1, cap) int32."""
+        F = self._frames
+        cap = self.results_device()[4]
+        out = [np.zeros((max(F - 1, 0), cap), dtype=np.int32) for _ in range(4)]
+        if F >= 2:
+            _check(lib().orbx_match_batch_consecutive(self._h, *[o.ctypes.data_as(_vp) for o in out], 1))
+        return out
+
+    def match_consecutive_device(self, d_idx1, d_d1, d_idx2, d_d2):
+        _check(lib().orbx_match_batch_consecutive(self._h, d_idx1, d_d1, d_idx2, d_d2, 0))
+
+
+def DescriptorDistance(a, b):
+    """ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074)."""
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = np.ascontiguousarray(b, dtype=np.uint8)
+    assert a.size == 32 and b.size == 32
+    return lib().orbx_hamming(_ptr(a), _ptr(b))
+
+
+def match_top2(q, db, device=-1):
+    """Brute-force k=2 (knnMatch order) -> idx1 (int64), d1, idx2, d2."""
+    q = np.ascontiguousarray(q, dtype=np.uint8).reshape(-1, 32)
+    db = np.ascontiguousarray(db, dtype=np.uint8).reshape(-1, 32)
+    nq = len(q)
+    i1, i2 = np.zeros(nq, dtype=np.int64), np.zeros(nq, dtype=np.int64)
+    d1, d2 = np.zeros(nq, dtype=np.int32), np.zeros(nq, dtype=np.int32)
+    _check(lib().orbx_match_top2(_ptr(q), nq, _ptr(db), len(db), _ptr(i1, _i64p), _ptr(d1, _i32p), _ptr(i2, _i64p),
+                                 _ptr(d2, _i32p), device))
+    return i1, d1, i2, d2
+
+
+def match_stereo_banded(kps_l, desc_l, kps_r, desc_r, scale_factors, n_rows, max_d, device=-1):
+    """Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894) -> best_idx, best_dist."""
+    kps_l = np.ascontiguousarray(kps_l, dtype=KP_DTYPE)
+    kps_r = np.ascontiguousarray(kps_r, dtype=KP_DTYPE)
+    desc_l = np.ascontiguousarray(desc_l, dtype=np.uint8)
+    desc_r = np.ascontiguousarray(desc_r, dtype=np.uint8)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    bi = np.zeros(len(kps_l), dtype=np.int32)
+    bd = np.zeros(len(kps_l), dtype=np.int32)
+    _check(lib().orbx_match_stereo_banded(kps_l.ctypes.data_as(_vp), _ptr(desc_l), len(kps_l), kps_r.ctypes.data_as(_vp),
+                                          _ptr(desc_r), len(kps_r), _ptr(sf, _f32p), len(sf), int(n_rows), float(max_d),
+                                          _ptr(bi, _i32p), _ptr(bd, _i32p), device))
+    return bi, bd
+
+
+def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):
+    """The 'BoW KF->F' accept rule (ORBmatcher.cc:327-329): best1 <= TH_LOW and (float)best1 < nnratio*(float)best2."""
+    d1 = np.asarray(d1)
+    d2 = np.asarray(d2)
+    return (d1 <= th) & (d1.astype(np.float32) < np.float32(nnratio) * d2.astype(np.float32))
+
+
+class ShardedMatcher:
+    """One rank of the sharded top-2 matcher (config 5): local top-2 -> ncclAllGather -> merge on every rank."""
+
+    def __init__(self, rank, nranks, unique_id, device):
+        self._c = _vp()
+        uid = np.frombuffer(bytes(unique_id), dtype=np.uint8).copy()
+        assert uid.size == 128
+        _check(lib().orbx_comm_init(rank, nranks, _ptr(uid), device, C.byref(self._c)))
+        self.rank, self.nranks = rank, nranks
+
+    @staticmethod
+    def unique_id():
+        uid = np.zeros(128, dtype=np.uint8)
+        _check(lib().orbx_comm_unique_id(_ptr(uid)))
+        return uid.tobytes()
+
+    def match(self, d_q, nq, d_db_local, nd_local, index_base, d_idx1, d_d1, d_idx2, d_d2):
+        _check(lib().orbx_match_top2_sharded(self._c, d_q, nq, d_db_local, nd_local, index_base, d_idx1, d_d1, d_idx2,
+                                             d_d2))
+
+    def close(self):
+        if getattr(self, "_c", None) is not None and self._c.value:
+            lib().orbx_comm_destroy(self._c)
+            self._c = _vp()
+
+    __del__ = close
+
+
+def shard_range(n, rank, nranks):
+    """Rows [lo, hi) of an n-row database owned by `rank` (rows [r*N/G, (r+1)*N/G))."""
+    return (n * rank) // nranks, (n * (rank + 1)) // nranks
+
+
+def merge_top2_host(keys1, keys2):
+    """Host restatement of the merge rule for CPU-side (gloo) tests of the exchange step: keys are
+    distance << 40 | global row, sets along axis 0; returns merged (k1, k2)."""
+    allk = np.concatenate([np.asarray(keys1, dtype=np.uint64), np.asarray(keys2, dtype=np.uint64)], axis=0)
+    s = np.sort(allk, axis=0)
+    return s[0], s[1]

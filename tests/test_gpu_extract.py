@@ -1,0 +1,150 @@
+"""GPU parity of the extractor (through the C ABI) against the oracle: stage taps (pyramid, blur, FAST candidates),
+end-to-end operator() results against the committed reference fixtures, the port, and — where oracle/_ref
+travelled — the reference binary itself.  Integer/byte/index results must be bit-exact; angles are produced by
+the same non-FMA float sequence as the oracle, so they are compared bit-exactly too (north_star allows 1e-3 deg)."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from orb_slam3_ros2_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+E2E = ["euroc752", "d435i640", "kittiL", "kittiR", "hd1080", "milkv360", "init5x", "small320"]
+
+
+@pytest.fixture(scope="module")
+def orbx():
+    from orb_slam3_ros2_b200 import orbx
+    orbx.lib()
+    return orbx
+
+
+def _same(a, b, what):
+    assert len(a) == len(b), f"{what}: count {len(a)} vs {len(b)}"
+    assert np.array_equal(a, b), f"{what}: first diff at {np.flatnonzero(np.any(a != b, axis=-1) if a.ndim > 1 else a != b)[:5]}"
+
+
+def test_pyramid_blur_candidates_match_oracle(orbx, oracle):
+    im = synth.frame(5, 752, 480)
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    po = oracle.PortExtractor(nfeatures=1000)
+    ex(im, None, (0, 1000))
+    po.extract(im, (0, 1000))
+    for l in range(8):
+        want = po.pyramid(l)
+        got = ex.pyramid_level(0, l)
+        assert got.shape == want.shape
+        assert np.array_equal(got, want), f"pyramid level {l}: {np.count_nonzero(got != want)} bytes differ"
+        assert np.array_equal(ex.mvImagePyramid[l], want[19:-19, 19:-19])
+        blur = oracle.gauss7(np.ascontiguousarray(want[19:-19, 19:-19]))
+        assert np.array_equal(ex.blurred_level(0, l), blur), f"blur level {l}"
+        _same(ex.candidates(0, l), po.candidates(l), f"FAST candidates level {l}")
+
+
+@pytest.mark.parametrize("name", E2E)
+def test_operator_matches_reference_fixture(orbx, name):
+    g = load_golden(f"e2e_{name}.npz")
+    w, h, k, nf = int(g["w"]), int(g["h"]), int(g["k"]), int(g["nfeatures"])
+    lap = tuple(int(v) for v in g["lap"])
+    im = synth.frame(k, w, h, 42, bool(g["right"]))
+    assert hashlib.sha1(im.tobytes()).hexdigest() == str(g["img_sha1"])
+    for mode in ("strict", "native"):
+        ex = orbx.ORBextractor(nf, 1.2, 8, 20, 7, fp_mode=mode)
+        mono, kp, desc = ex(im, None, lap)
+        same = "native_same" in g.files and bool(g["native_same"])
+        src = "strict" if (mode == "strict" or same) else "native"
+        assert mono == int(g[f"{mode}_mono"])
+        _same(kp, g[f"{src}_kp"], f"{name}/{mode} keypoints")
+        _same(desc, g[f"{src}_desc"], f"{name}/{mode} descriptors")
+        if mode == "strict":
+            for l in range(8):
+                p = ex.pyramid_level(0, l)
+                assert p.shape == tuple(g["pyr_shape"][l])
+                assert hashlib.sha1(p.tobytes()).hexdigest() == str(g["pyr_sha1"][l])
+        ex.close()
+
+
+def _vs(orbx, oracle, im, nf, lap, mode="strict", ini=20, mn=7):
+    ex = orbx.ORBextractor(nf, 1.2, 8, ini, mn, fp_mode=mode)
+    mono, kp, desc = ex(im, None, lap)
+    checker = oracle.RefExtractor if oracle.have_ref(mode) else oracle.PortExtractor
+    rm, rk, rd = checker(nfeatures=nf, ini_th=ini, min_th=mn, mode=mode).extract(im, lap)
+    assert mono == rm
+    _same(kp, rk, "keypoints")
+    _same(desc, rd, "descriptors")
+    ex.close()
+    return len(kp)
+
+
+def test_adversarial_inputs_match_reference(orbx, oracle):
+    rng = np.random.default_rng(9)
+    total = 0
+    # white noise: thousands of candidates per level and many (count, UL.x) ties in the quadtree's sort
+    total += _vs(orbx, oracle, rng.integers(0, 256, (240, 320), dtype=np.uint8), 500, (0, 1000))
+    total += _vs(orbx, oracle, rng.integers(0, 256, (376, 1241), dtype=np.uint8), 2000, (0, 0))
+    total += _vs(orbx, oracle, rng.integers(0, 256, (480, 640), dtype=np.uint8), 5000, (0, 1000), "native")
+    # low contrast: minThFAST fallback in most cells, levels with fewer candidates than N
+    low = (synth.frame(3, 400, 300).astype(np.int32) - 128) // 6 + 128
+    total += _vs(orbx, oracle, low.astype(np.uint8), 1000, (100, 200))
+    # flat image: no keypoints at all
+    assert _vs(orbx, oracle, np.full((240, 320), 77, dtype=np.uint8), 500, (0, 1000)) == 0
+    # tall image (nIni = round(w/h) = 0 is not reachable by the reference without crashing; 1 is), odd sizes
+    total += _vs(orbx, oracle, synth.frame(7, 301, 517), 700, (0, 1000))
+    total += _vs(orbx, oracle, synth.frame(8, 1000, 130), 600, (300, 600))
+    # few features: N_l small, the quadtree stops in its first rounds
+    total += _vs(orbx, oracle, synth.frame(9, 640, 480), 40, (0, 1000))
+    assert total > 8000
+
+
+def test_empty_image_returns_minus_one(orbx):
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    mono, kp, desc = ex(None)
+    assert mono == -1 and len(kp) == 0 and len(desc) == 0
+
+
+def test_tables_match_reference_constants(orbx, oracle):
+    for nf in (1000, 1250, 2000, 4000, 5000):
+        ex = orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+        t = oracle.PortExtractor(nfeatures=nf).tables()
+        assert np.array_equal(ex.features_per_level(), t["nfeatures"])
+        assert np.array_equal(ex.GetScaleFactors(), t["scale"])
+        assert np.array_equal(ex.GetInverseScaleFactors(), t["inv_scale"])
+        assert np.array_equal(ex.GetScaleSigmaSquares(), t["sigma2"])
+        assert np.array_equal(ex.GetInverseScaleSigmaSquares(), t["inv_sigma2"])
+        assert ex.GetLevels() == 8
+
+
+def test_batch_equals_single_frame_and_device_synth(orbx, oracle):
+    import torch
+    F, w, h = 6, 640, 480
+    imgs = synth.frames(10, F, w, h)
+    dev = torch.empty((F, h, w), dtype=torch.uint8, device="cuda")
+    orbx._check(orbx.lib().orbx_synth_frames_device(dev.data_ptr(), 10, F, w, h, 42, 0, -1))
+    assert np.array_equal(dev.cpu().numpy(), imgs), "device synthetic generator differs from synth.py"
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    mono, n, kps, desc = ex.extract_batch(imgs, (0, 1000))
+    po = oracle.PortExtractor(nfeatures=1000)
+    for f in range(F):
+        pm, pk, pd = po.extract(imgs[f], (0, 1000))
+        assert mono[f] == pm and n[f] == len(pk)
+        _same(kps[f, :n[f]], pk, f"batch frame {f} keypoints")
+        _same(desc[f, :n[f]], pd, f"batch frame {f} descriptors")
+    # device-resident path gives the same
+    ex.extract_batch_device(dev.data_ptr(), F, w, h, (0, 1000))
+    ex.sync()
+    for f in (0, F - 1):
+        m2, k2, d2 = ex.download(f)
+        assert m2 == mono[f]
+        _same(k2, kps[f, :n[f]], "device batch keypoints")
+        _same(d2, desc[f, :n[f]], "device batch descriptors")
+    # frame-to-frame matching over the batch (config 2)
+    i1, d1, i2, d2m = ex.match_consecutive()
+    for f in range(F - 1):
+        want = oracle.match_top2(desc[f, :n[f]], desc[f + 1, :n[f + 1]])
+        got = (i1[f, :n[f]], d1[f, :n[f]], i2[f, :n[f]], d2m[f, :n[f]])
+        for g_, w_ in zip(got, want):
+            assert np.array_equal(g_, w_)
+    assert orbx.accept_bow(d1[0, :n[0]], d2m[0, :n[0]]).sum() > 100  # the synthetic stream really overlaps
