@@ -102,6 +102,8 @@ int orbx_batch_download(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* d
                         int* mono_index);
 /* Blocks until the handle's stream is idle (batch_device is asynchronous). */
 int orbx_sync(orbx_handle h);
+/* The handle's cudaStream_t (for callers that record their own events around a run of batch calls). */
+void* orbx_get_stream(orbx_handle h);
 /* Elapsed device time in milliseconds of the last batch (CUDA events on the handle's stream); the
  * per-stage array (pyramid, fast, quadtree, blur, describe) may be NULL. */
 int orbx_last_timing(orbx_handle h, float* total_ms, float stage_ms[5]);

@@ -123,13 +123,18 @@ __global__ void __launch_bounds__(kThreads) fastCellsKernel(const __grid_constan
         for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
 #pragma unroll
         for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
-        int best = -255;
+        // strongest "centre brighter" arc = max_k min9(d); strongest "centre darker" arc = -min_k max9(d).
+        // NOTE: written without `max(best, max(mn9, -mx9))` on purpose — ptxas 12.9 (sm_100a) fuses that into a
+        // VIMNMX3 and drops the negation of the third operand (seen in SASS and in results on a B200).
+        int bestMin = -255, bestMax = 255;
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
             const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-            best = max(best, max(mn9, -mx9));
+            bestMin = max(bestMin, mn9);
+            bestMax = min(bestMax, mx9);
         }
+        const int best = (bestMin + bestMax > 0) ? bestMin : 0 - bestMax;  // max(bestMin, -bestMax) as a select
         sArc[(y + 1) * arcPitch + x + 1] = (uint8_t)best;  // > tmin >= 0 here
     }
     __syncthreads();
@@ -207,11 +212,7 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     const int tilePitch = (maxW + 6 + 3) & ~3;
     const int arcBytes = (maxW + 2) * (maxH + 2);
     const size_t smem = (size_t)tilePitch * (maxH + 6) + ((arcBytes + 3) & ~3) + 2 * (size_t)maxW * maxH + 16;
-    static bool attr = false;
-    if (!attr) {
-        cudaFuncSetAttribute(fastCellsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr = true;
-    }
+    if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     fastCellsKernel<<<dim3(P.nCellsTotal, F), kThreads, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, tilePitch, arcBytes);
     countLaunch();
 }

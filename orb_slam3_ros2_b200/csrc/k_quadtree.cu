@@ -471,7 +471,7 @@ size_t quadtreeSmemBytes(const FramePlan& P) { return qtSmem(qtNodeCap(P), qtMax
 void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     const int NC = qtNodeCap(P), maxCells = qtMaxCells(P);
     const size_t smem = qtSmem(NC, maxCells);
-    cudaFuncSetAttribute(quadtreeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(quadtreeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     quadtreeKernel<<<dim3(P.nlevels, F), kQT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag,
                                                          NC, maxCells);
     countLaunch();

@@ -408,6 +408,8 @@ int orbx_sync(orbx_handle h) {
     return ORBX_OK;
 }
 
+void* orbx_get_stream(orbx_handle h) { return h ? (void*)h->stream : nullptr; }
+
 int orbx_last_timing(orbx_handle h, float* total_ms, float stage_ms[5]) {
     if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
     DeviceGuard guard(h->device);

@@ -60,6 +60,7 @@ SYMBOLS = {
     "orbx_batch_results": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i32p]),
     "orbx_batch_download": (C.c_int, [_vp, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
     "orbx_sync": (C.c_int, [_vp]),
+    "orbx_get_stream": (_vp, [_vp]),
     "orbx_last_timing": (C.c_int, [_vp, _f32p, _f32p]),
     "orbx_get_candidates": (C.c_int, [_vp, C.c_int, C.c_int, _i32p, C.c_int, _i32p]),
     "orbx_get_blurred": (C.c_int, [_vp, C.c_int, C.c_int, _u8p, _i32p, _i32p]),
@@ -223,6 +224,9 @@ class ORBextractor:
 
     def sync(self):
         _check(lib().orbx_sync(self._h))
+
+    def stream_ptr(self):
+        return lib().orbx_get_stream(self._h)
 
     def timing(self):
         """-> (total_ms, [pyramid, fast, quadtree, blur, describe] ms) of the last batch (CUDA events)."""
