@@ -145,6 +145,10 @@ int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, 
                              const uint8_t* desc_r, int nr, const float* scale_factors, int nlevels, int n_rows,
                              float max_d, int32_t* best_idx, int32_t* best_dist, int device);
 
+/* Measured sustained 32-bit POPC rate of the device in giga-POPC/s (8 independent XOR+POPC chains per thread):
+ * the denominator of the matcher's roofline, pairs/s = POPC/s / 8. */
+int orbx_bench_popc(int device, double* gpopc_per_s);
+
 /* ---- descriptor database sharded over ranks (config 5): one process per GPU ----------------------
  * Rank 0 calls orbx_comm_unique_id and distributes the 128 bytes out of band (the host launcher's
  * rendezvous); every rank then calls orbx_comm_init.  orbx_match_top2_sharded computes the local top-2 of

@@ -267,3 +267,57 @@ void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* k
 }
 
 }  // namespace orbx
+
+// ---- POPC issue-rate microbenchmark: the denominator of the matcher's roofline -----------------------------------
+// Every thread runs 8 independent XOR+POPC chains (the shape of one descriptor pair) with nothing else in the loop
+// but the accumulation; the result is the chip's sustained 32-bit POPC rate (pairs/s = POPC/s / 8).
+namespace orbx {
+namespace {
+__global__ void __launch_bounds__(256) popcBenchKernel(uint32_t seed, int iters, uint32_t* __restrict__ out) {
+    uint32_t a[8], acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a[i] = seed * (threadIdx.x + 1u + 977u * i) + blockIdx.x; acc[i] = 0; }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            acc[i] += __popc(a[i] ^ (uint32_t)it);
+            a[i] += acc[i];  // keeps the chain data dependent on its own history so nothing is hoisted
+        }
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += acc[i];
+    if (s == 0x12345u) out[0] = s;  // practically never; defeats dead-code elimination
+}
+}  // namespace
+
+// returns giga-POPC per second, or a negative value on failure
+double benchPopcRate(cudaStream_t s) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint32_t* d = nullptr;
+    if (cudaMalloc(&d, 16) != cudaSuccess) return -1.0;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int iters = 1 << 15, blocks = sms * 8;
+    popcBenchKernel<<<blocks, 256, 0, s>>>(12345u, 1 << 10, d);  // warm-up
+    double best = -1.0;
+    for (int rep = 0; rep < 3; ++rep) {
+        cudaEventRecord(e0, s);
+        popcBenchKernel<<<blocks, 256, 0, s>>>(777u + rep, iters, d);
+        cudaEventRecord(e1, s);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double rate = (double)blocks * 256.0 * iters * 8.0 / (ms * 1e-3) / 1e9;
+        if (rate > best) best = rate;
+    }
+    countLaunch(4);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    return cudaGetLastError() == cudaSuccess ? best : -1.0;
+}
+}  // namespace orbx

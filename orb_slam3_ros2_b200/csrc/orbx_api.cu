@@ -759,6 +759,20 @@ int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, 
     return ORBX_OK;
 }
 
+int orbx_bench_popc(int device, double* gpopc_per_s) {
+    if (!gpopc_per_s) return fail(ORBX_ERR_ARG, "null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(ORBX_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    DeviceGuard guard(device);
+    const double r = benchPopcRate(nullptr);
+    if (r < 0) return fail(ORBX_ERR_CUDA, "POPC microbenchmark failed");
+    *gpopc_per_s = r;
+    return ORBX_OK;
+}
+
 // ---- sharded database ------------------------------------------------------------------------------------
 int orbx_comm_unique_id(uint8_t id[128]) {
     int rc = loadNccl();

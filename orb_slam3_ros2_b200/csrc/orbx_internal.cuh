@@ -106,6 +106,7 @@ void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap,
 void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
                         const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s);
 void uploadDescribeTables();
+double benchPopcRate(cudaStream_t s);
 
 void countLaunch(int n = 1);
 

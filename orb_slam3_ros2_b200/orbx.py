@@ -71,6 +71,7 @@ SYMBOLS = {
     "orbx_match_batch_consecutive": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int]),
     "orbx_match_stereo_banded": (C.c_int, [_vp, _u8p, C.c_int, _vp, _u8p, C.c_int, _f32p, C.c_int, C.c_int, C.c_float,
                                            _i32p, _i32p, C.c_int]),
+    "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_comm_unique_id": (C.c_int, [_u8p]),
     "orbx_comm_init": (C.c_int, [C.c_int, C.c_int, _u8p, C.c_int, C.POINTER(_vp)]),
     "orbx_comm_destroy": (None, [_vp]),
@@ -297,6 +298,13 @@ def match_stereo_banded(kps_l, desc_l, kps_r, desc_r, scale_factors, n_rows, max
                                           _ptr(desc_r), len(kps_r), _ptr(sf, _f32p), len(sf), int(n_rows), float(max_d),
                                           _ptr(bi, _i32p), _ptr(bd, _i32p), device))
     return bi, bd
+
+
+def bench_popc(device=-1):
+    """Measured sustained POPC rate (giga-POPC/s) of the device: the matcher's roofline denominator."""
+    r = C.c_double(0)
+    _check(lib().orbx_bench_popc(device, C.byref(r)))
+    return r.value
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):
