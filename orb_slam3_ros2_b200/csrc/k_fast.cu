@@ -2,56 +2,58 @@
 //
 // Replaces the cell loop of ORBextractor::ComputeKeyPointsOctTree (ORB_SLAM3/src/ORBextractor.cc:787-872) and the
 // cv::FAST(cell, kps, th, true) calls inside it (:826, :845).  Semantics reproduced:
-//   * a pixel is a corner at threshold t iff some 9 of the 16 ring pixels are all > I+t or all < I-t;
-//     its score is (max over the sixteen 9-arcs of min|d|) - 1 and does not depend on t;
+//   * a pixel is a corner at threshold t iff some 9 of the 16 ring pixels are all > I+t or all < I-t; with
+//     arc(p) = max over the sixteen 9-arcs of max(min(I-ring), min(ring-I)) that is arc(p) > t, and FAST's
+//     response is arc(p) - 1 — independent of t;
 //   * FAST is called on the CELL SUB-IMAGE: only pixels >= 3 px inside the cell are tested and the 3x3 strict
-//     non-max suppression sees scores outside that rectangle (and of non-corners at t) as 0;
+//     non-max suppression sees everything outside that rectangle as 0;
 //   * a cell that yields nothing at iniThFAST is redone at minThFAST;
 //   * output order inside a cell is row-major; cells are visited row-major (:863-868).
 //
-// One CTA per (cell, frame).  The cell (+3-px ring apron) is staged in shared memory, every lane classifies its
-// pixels branch-free with two 16-bit ring masks (brighter / darker than the centre by more than minThFAST) and a
-// shift-and trick for "9 consecutive bits on a 16-cycle"; pixels that pass are queued so the expensive arc
-// strength is computed by all lanes on a dense work list.  The survivors of the NMS are compacted in row-major
-// order with a block scan and written as packed words (resp<<24 | y<<12 | x) into the cell's slot.
+// Two observations make the kernel branch-free and threshold-free until the very end:
+//   (1) min over an arc of (I - ring) = I - max(ring): the arc strength needs only sliding max/min of the RAW ring
+//       values, 80 three-input min/max per pixel, no subtraction and no corner pre-test;
+//   (2) a corner at t survives NMS iff arc(p) > arc(q) for its 8 neighbours: neighbours that are not corners at t
+//       have arc(q) <= t < arc(p), so thresholding them to 0 (what OpenCV does) changes nothing.  Hence the
+//       local-maximum flag is computed once and both thresholds are just counts over it.
+//
+// sm_100a specifics: pixels are widened to 16 bits and processed two per thread with the native packed
+// VIMNMX3.S16x2 / VIADD.16x2 instructions; the cell is kept in shared memory twice (pairs starting at even and at
+// odd columns; row pitch = 2*words+1 so column 0 has an odd-aligned home) so every ring pair is ONE aligned 32-bit LDS.  One CTA per (cell, frame).
 #include "orbx_internal.cuh"
 
 namespace orbx {
 namespace {
 
-constexpr int kThreads = 128;
+constexpr int kFT = 128;  // threads per CTA
 
 // ring offsets (dx,dy), k = 0..15 (OpenCV features2d/fast.cpp makeOffsets, patternSize 16)
-__constant__ int8_t cRingX[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
-__constant__ int8_t cRingY[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+#define ORBX_RING_DX {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1}
+#define ORBX_RING_DY {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3}
 
-__device__ __forceinline__ bool hasArc9(uint32_t m16) {
-    const uint32_t x = m16 | (m16 << 16);
-    uint32_t r = x & (x >> 1);
-    r &= r >> 2;
-    r &= r >> 4;
-    r &= x >> 8;
-    return (r & 0xffffu) != 0;
-}
+__device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
+__device__ __forceinline__ uint32_t min3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
 
-__global__ void __launch_bounds__(kThreads) fastCellsKernel(const __grid_constant__ FramePlan P,
-                                                            const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
-                                                            int* __restrict__ cellCnt, int tilePitch, int arcPitchMax) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int sQueueN;
-    __shared__ int sWarpSum[kThreads / 32];
+// TW2 = 32-bit words per tile row in each copy (tile columns / 2)
+template <int TW2>
+__global__ void __launch_bounds__(kFT) fastCellsKernel(const __grid_constant__ FramePlan P,
+                                                       const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
+                                                       int* __restrict__ cellCnt, int tileRows, unsigned levelMask) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ int sWarpSum[kFT / 32];
 
     // ---- which cell -------------------------------------------------------------------------------------
     int c = blockIdx.x, l = 0;
-    for (; l < P.nlevels; ++l) {
+    for (; l < P.nlevels; ++l) {  // blockIdx.x enumerates the cells of the levels selected by levelMask
+        if (!((levelMask >> l) & 1u)) continue;
         const int nc = P.lv[l].nCols * P.lv[l].nRows;
         if (c < nc) break;
         c -= nc;
     }
     if (l >= P.nlevels) return;
     const LevelPlan& L = P.lv[l];
-    const int ci = c / L.nCols, cj = c % L.nCols;
-    const int f = blockIdx.y;
+    const int ci = c / L.nCols, cj = c - ci * L.nCols;
+    const int f = blockIdx.y, tid = threadIdx.x;
     int* cntOut = cellCnt + (size_t)f * P.nCellsTotal + L.cellBase + c;
     const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
     const int iniX = kMinBorder + cj * L.wCell, iniY = kMinBorder + ci * L.hCell;
@@ -61,160 +63,183 @@ __global__ void __launch_bounds__(kThreads) fastCellsKernel(const __grid_constan
     const int cw = maxX - iniX, ch = maxY - iniY;
     // ORBextractor.cc:813-816, :820-823 skip rules; cv::FAST returns nothing below 7x7
     if (iniY >= maxBY - 3 || iniX >= maxBX - 6 || cw < 7 || ch < 7) {
-        if (threadIdx.x == 0) *cntOut = 0;
+        if (tid == 0) *cntOut = 0;
         return;
     }
-    const int tw = cw - 6, th = ch - 6;  // tested rectangle
-    const int npx = tw * th;
-    const int arcPitch = tw + 2;  // 1-px zero apron for the NMS
 
-    uint8_t* sTile = smem;                                            // ch x tilePitch
-    uint8_t* sArc = sTile + (size_t)tilePitch * (L.hCell + 6);        // (th+2) x arcPitch
-    uint16_t* sQueue = reinterpret_cast<uint16_t*>(sArc + ((arcPitchMax + 3) & ~3));  // npx entries max
-    const int tid = threadIdx.x;
+    // Tile coordinates: column tc = x_cell + shift so that tile column 0 is a 4-byte aligned address in the plane.
+    const int gx0 = kEdge + iniX;
+    const int shift = gx0 & 3;
+    uint32_t* tileE = smem;                       // [tileRows][TW2]  word i = columns (2i, 2i+1)
+    uint32_t* tileO = tileE + tileRows * TW2;     // [tileRows][TW2]  word i = columns (2i-1, 2i)
+    uint32_t* arcE = tileO + tileRows * TW2;      // same geometry: arc strength clamped to >= 0, 0 outside the tested rect
+    uint32_t* arcO = arcE + tileRows * TW2;
+    uint32_t* flags = tileE;                      // reused after the arc pass: local-maximum arcs per pair
 
-    // ---- stage the cell ----------------------------------------------------------------------------------
-    const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + kEdge + iniX;
-    for (int i = tid; i < cw * ch; i += kThreads) {
-        const int y = i / cw, x = i - y * cw;
-        sTile[y * tilePitch + x] = __ldg(src + (size_t)y * L.pitch + x);
-    }
-    for (int i = tid; i < (th + 2) * arcPitch; i += kThreads) sArc[i] = 0;
-    if (tid == 0) sQueueN = 0;
-    __syncthreads();
-
-    int ofs[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) ofs[k] = cRingY[k] * tilePitch + cRingX[k];
-
-    // ---- pass 1: branch-free corner test at minThFAST, queue the survivors ---------------------------------
-    const int tmin = P.minTh < P.iniTh ? P.minTh : P.iniTh;
-    for (int e = tid; e < npx; e += kThreads) {
-        const int y = e / tw, x = e - y * tw;
-        const uint8_t* p = sTile + (y + 3) * tilePitch + x + 3;
-        const int v = p[0], hi = v + tmin, lo = v - tmin;
-        uint32_t mb = 0, md = 0;
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int q = p[ofs[k]];
-            mb |= (uint32_t)(q > hi) << k;
-            md |= (uint32_t)(q < lo) << k;
-        }
-        if (hasArc9(mb) || hasArc9(md)) {
-            const int pos = atomicAdd(&sQueueN, 1);
-            sQueue[pos] = (uint16_t)e;
+    // ---- stage the cell, widening bytes to 16 bits, in both pair alignments ----------------------------------
+    {
+        const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + (gx0 - shift);
+        const int nW = (shift + cw + 3) >> 2;     // aligned words per row
+        const float invW = 1.0f / (float)nW;
+        for (int i = tid; i < ch * nW; i += kFT) {
+            const int r = (int)(((float)i + 0.5f) * invW), wi = i - r * nW;
+            const uint32_t* g = reinterpret_cast<const uint32_t*>(src + (size_t)r * L.pitch) + wi;
+            const uint32_t w0 = __ldg(g), w1 = __ldg(g + 1);
+            uint2 e, o;
+            e.x = __byte_perm(w0, 0, 0x4140);                        // (p0, p1)
+            e.y = __byte_perm(w0, 0, 0x4342);                        // (p2, p3)
+            o.x = __byte_perm(w0, 0, 0x4241);                        // (p1, p2)
+            o.y = __byte_perm(w0, w1, 0x7473) & 0x00ff00ffu;         // (p3, p4)
+            *reinterpret_cast<uint2*>(tileE + r * TW2 + 2 * wi) = e;
+            tileO[r * TW2 + 2 * wi + 1] = o.x;
+            tileO[r * TW2 + 2 * wi + 2] = o.y;
+            if (wi == 0) tileO[r * TW2] = __byte_perm(w0, 0, 0x4044);  // (-, p0): column 0 lives in the high half
         }
     }
     __syncthreads();
 
-    // ---- pass 2: arc strength of the queued pixels ----------------------------------------------------------
-    const int qn = sQueueN;
-    for (int i = tid; i < qn; i += kThreads) {
-        const int e = sQueue[i];
-        const int y = e / tw, x = e - y * tw;
-        const uint8_t* p = sTile + (y + 3) * tilePitch + x + 3;
-        const int v = p[0];
-        int d[16];
+    // ---- pass 1: arc strength of every tested pixel, two pixels per thread ---------------------------------------
+    // Pair grid over the tested rectangle plus a 1-px apron (which is written as 0 for the NMS).
+    const int ec0 = (2 + shift) & ~1;                               // first pair column (even)
+    const int PW = ((((cw - 3 + shift) & ~1) - ec0) >> 1) + 1;      // pair columns
+    const int PR = ch - 4;                                          // rows ty = 2 .. ch-3
+    const float invPW = 1.0f / (float)PW;
+    {
+        constexpr int dx[16] = ORBX_RING_DX, dy[16] = ORBX_RING_DY;
+        for (int i = tid; i < PR * PW; i += kFT) {
+            const int r = (int)(((float)i + 0.5f) * invPW), pc = i - r * PW;
+            const int ty = r + 2, tc = ec0 + 2 * pc;
+            const int x0 = tc - shift;                               // cell x of lane 0
+            const bool rowOk = ty >= 3 && ty < ch - 3;
+            const bool ok0 = rowOk && x0 >= 3 && x0 < cw - 3, ok1 = rowOk && x0 + 1 >= 3 && x0 + 1 < cw - 3;
+            const int b = ty * TW2 + (tc >> 1);
+            uint32_t arc = 0;
+            if (ok0 || ok1) {
+                uint32_t q[16];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) d[k] = v - (int)p[ofs[k]];
-        // min / max over every cyclic window of 9 by doubling: w2 -> w4 -> w8 -> w9
-        int mn2[16], mx2[16], mn4[16], mx4[16];
+                for (int k = 0; k < 16; ++k)
+                    q[k] = (dx[k] & 1) ? tileO[b + dy[k] * TW2 + ((dx[k] + 1) >> 1)] : tileE[b + dy[k] * TW2 + (dx[k] >> 1)];
+                const uint32_t cen = tileE[b];
+                uint32_t mx3[16], mn3[16];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
-#pragma unroll
-        for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
-        // strongest "centre brighter" arc = max_k min9(d); strongest "centre darker" arc = -min_k max9(d).
-        // NOTE: written without `max(best, max(mn9, -mx9))` on purpose — ptxas 12.9 (sm_100a) fuses that into a
-        // VIMNMX3 and drops the negation of the third operand (seen in SASS and in results on a B200).
-        int bestMin = -255, bestMax = 255;
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-            const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-            bestMin = max(bestMin, mn9);
-            bestMax = min(bestMax, mx9);
-        }
-        const int best = (bestMin + bestMax > 0) ? bestMin : 0 - bestMax;  // max(bestMin, -bestMax) as a select
-        sArc[(y + 1) * arcPitch + x + 1] = (uint8_t)best;  // > tmin >= 0 here
-    }
-    __syncthreads();
-
-    // ---- pass 3: NMS at iniThFAST, then (if the cell is empty) at minThFAST; ordered compaction ---------------
-    const int per = (npx + kThreads - 1) / kThreads;  // <= 64 (cells are < 76 px wide)
-    const int e0 = tid * per, e1 = min(e0 + per, npx);
-    uint32_t* slot = cand + (size_t)f * P.candWords + L.candOff + (size_t)c * L.cellCap;
-    const int xOff = cj * L.wCell, yOff = ci * L.hCell;
-    for (int pass = 0; pass < 2; ++pass) {
-        const int t = pass == 0 ? P.iniTh : P.minTh;
-        unsigned long long keep = 0;
-        for (int e = e0; e < e1; ++e) {
-            const int y = e / tw, x = e - y * tw;
-            const uint8_t* a = sArc + (y + 1) * arcPitch + x + 1;
-            const int ap = a[0];
-            if (ap <= t) continue;
-            const int s = ap - 1;
-            bool k = true;
-#pragma unroll
-            for (int dy = -1; dy <= 1; ++dy)
-#pragma unroll
-                for (int dx = -1; dx <= 1; ++dx) {
-                    if (dx == 0 && dy == 0) continue;
-                    const int aq = a[dy * arcPitch + dx];
-                    const int cq = aq > t ? aq - 1 : 0;
-                    k = k && (s > cq);
+                for (int k = 0; k < 16; ++k) {
+                    mx3[k] = max3(q[k], q[(k + 1) & 15], q[(k + 2) & 15]);
+                    mn3[k] = min3(q[k], q[(k + 1) & 15], q[(k + 2) & 15]);
                 }
-            if (k) keep |= 1ull << (e - e0);
-        }
-        // block exclusive scan of popcounts
-        const int mine = __popcll(keep);
-        int incl = mine;
+                uint32_t mx9[16], mn9[16];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int n = __shfl_up_sync(0xffffffffu, incl, o);
-            if ((tid & 31) >= o) incl += n;
-        }
-        if ((tid & 31) == 31) sWarpSum[tid >> 5] = incl;
-        __syncthreads();
-        int base = 0, total = 0;
+                for (int k = 0; k < 16; ++k) {
+                    mx9[k] = max3(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
+                    mn9[k] = min3(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
+                }
+                // A = min_k max9_k (strongest "centre brighter": I - A), B = max_k min9_k ("centre darker": B - I)
+                uint32_t A = min3(mx9[0], mx9[1], mx9[2]), B = max3(mn9[0], mn9[1], mn9[2]);
 #pragma unroll
-        for (int w = 0; w < kThreads / 32; ++w) {
-            if (w < (tid >> 5)) base += sWarpSum[w];
-            total += sWarpSum[w];
-        }
-        __syncthreads();
-        if (total > 0 || pass == 1) {
-            int o = base + incl - mine;
-            while (keep) {
-                const int b = __ffsll((long long)keep) - 1;
-                keep &= keep - 1;
-                const int e = e0 + b;
-                const int y = e / tw, x = e - y * tw;
-                const int resp = (int)sArc[(y + 1) * arcPitch + x + 1] - 1;
-                if (o < L.cellCap) slot[o] = ((uint32_t)resp << 24) | ((uint32_t)(y + 3 + yOff) << 12) | (uint32_t)(x + 3 + xOff);
-                ++o;
+                for (int k = 3; k < 15; k += 2) {
+                    A = min3(A, mx9[k], mx9[k + 1]);
+                    B = max3(B, mn9[k], mn9[k + 1]);
+                }
+                A = __vmins2(A, mx9[15]);
+                B = __vmaxs2(B, mn9[15]);
+                arc = __vimax3_s16x2_relu(__vsub2(cen, A), __vsub2(B, cen), 0u);
+                arc &= (ok0 ? 0x0000ffffu : 0u) | (ok1 ? 0xffff0000u : 0u);
             }
-            if (tid == 0) *cntOut = total;
-            break;
+            arcE[b] = arc;
+            // odd-aligned copy: column tc is the high half of O word tc/2, column tc+1 the low half of O word tc/2+1
+            reinterpret_cast<uint16_t*>(arcO)[2 * b + 1] = (uint16_t)(arc & 0xffffu);
+            reinterpret_cast<uint16_t*>(arcO)[2 * b + 2] = (uint16_t)(arc >> 16);
         }
     }
+    __syncthreads();
+
+    // ---- pass 2: strict 3x3 local maximum (threshold independent), kept arcs into `flags` ------------------------
+    const int NR = ch - 6;  // tested rows
+    const int nF = NR * PW;
+    for (int i = tid; i < nF; i += kFT) {
+        const int r = (int)(((float)i + 0.5f) * invPW), pc = i - r * PW;
+        const int b = (r + 3) * TW2 + ((ec0 >> 1) + pc);
+        const uint32_t up = max3(arcO[b - TW2], arcE[b - TW2], arcO[b - TW2 + 1]);
+        const uint32_t dn = max3(arcO[b + TW2], arcE[b + TW2], arcO[b + TW2 + 1]);
+        const uint32_t nm = max3(up, dn, __vmaxs2(arcO[b], arcO[b + 1]));
+        const uint32_t cen = arcE[b];
+        flags[i] = cen & __vcmpgts2(cen, nm);  // arcs are >= 0 and invalid lanes are 0, so they never pass
+    }
+    __syncthreads();
+
+    // ---- pass 3: count at both thresholds, ordered compaction (row-major), fallback to minThFAST -----------------
+    const int per = (nF + kFT - 1) / kFT;
+    const int i0 = min(tid * per, nF), i1 = min(i0 + per, nF);
+    // response = arc - 1 must beat the zero score of non-corners: arc >= 2 (only matters for thresholds < 1)
+    const int tIni = max(P.iniTh, 1), tMin = max(P.minTh, 1);
+    int cnt = 0;  // (count at ini) << 16 | (count at min)
+    for (int i = i0; i < i1; ++i) {
+        const uint32_t v = flags[i];
+        const int a0 = v & 0xffff, a1 = v >> 16;
+        cnt += ((a0 > tIni) << 16) + (a0 > tMin) + ((a1 > tIni) << 16) + (a1 > tMin);
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += n;
+    }
+    if ((tid & 31) == 31) sWarpSum[tid >> 5] = incl;
+    __syncthreads();
+    int base = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kFT / 32; ++w) {
+        if (w < (tid >> 5)) base += sWarpSum[w];
+        total += sWarpSum[w];
+    }
+    const bool useIni = (total >> 16) > 0;  // ORBextractor.cc:843-846: redo at minThFAST only if nothing was found
+    const int t = useIni ? tIni : tMin;
+    const int excl = base + incl - cnt;
+    int o = useIni ? (excl >> 16) : (excl & 0xffff);
+    uint32_t* slot = cand + (size_t)f * P.candWords + L.candOff + (size_t)c * L.cellCap;
+    const int xOff = cj * L.wCell - shift + ec0, yOff = ci * L.hCell + 3;
+    for (int i = i0; i < i1; ++i) {
+        const uint32_t v = flags[i];
+        const int a0 = v & 0xffff, a1 = v >> 16;
+        if (a0 > t || a1 > t) {
+            const int r = (int)(((float)i + 0.5f) * invPW), pc = i - r * PW;
+            const uint32_t xy = ((uint32_t)(r + yOff) << 12) | (uint32_t)(xOff + 2 * pc);
+            if (a0 > t) { if (o < L.cellCap) slot[o] = ((uint32_t)(a0 - 1) << 24) | xy; ++o; }
+            if (a1 > t) { if (o < L.cellCap) slot[o] = ((uint32_t)(a1 - 1) << 24) | (xy + 1); ++o; }
+        }
+    }
+    if (tid == 0) *cntOut = useIni ? (total >> 16) : (total & 0xffff);
 }
 
 }  // namespace
 
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
-    int maxW = 0, maxH = 0;
-    for (int l = 0; l < P.nlevels; ++l)
-        if (P.lv[l].nCols > 0 && P.lv[l].nRows > 0) {
-            maxW = P.lv[l].wCell > maxW ? P.lv[l].wCell : maxW;
-            maxH = P.lv[l].hCell > maxH ? P.lv[l].hCell : maxH;
+    // Two launches at most: levels whose cells fit the narrow tile (wCell + 9 <= 48 columns: every level of a large
+    // image) and the few small levels with wider cells (wCell < 70 always, since nCols = floor(width / 35)).
+    for (int wide = 0; wide < 2; ++wide) {
+        unsigned mask = 0;
+        int cells = 0, maxH = 0;
+        for (int l = 0; l < P.nlevels; ++l) {
+            const LevelPlan& L = P.lv[l];
+            if (L.nCols <= 0 || L.nRows <= 0) continue;
+            if ((L.wCell + 9 > 48) != (wide == 1)) continue;
+            mask |= 1u << l;
+            cells += L.nCols * L.nRows;
+            maxH = L.hCell > maxH ? L.hCell : maxH;
         }
-    if (P.nCellsTotal == 0) return;
-    const int tilePitch = (maxW + 6 + 3) & ~3;
-    const int arcBytes = (maxW + 2) * (maxH + 2);
-    const size_t smem = (size_t)tilePitch * (maxH + 6) + ((arcBytes + 3) & ~3) + 2 * (size_t)maxW * maxH + 16;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    fastCellsKernel<<<dim3(P.nCellsTotal, F), kThreads, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, tilePitch, arcBytes);
-    countLaunch();
+        if (!cells) continue;
+        const int tileRows = maxH + 6 + 1;
+        const dim3 grid(cells, F);
+        if (!wide) {
+            const size_t smem = (size_t)4 * tileRows * 26 * 4;
+            if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<26>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            fastCellsKernel<26><<<grid, kFT, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, tileRows, mask);
+        } else {
+            const size_t smem = (size_t)4 * tileRows * 46 * 4;
+            if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<46>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            fastCellsKernel<46><<<grid, kFT, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, tileRows, mask);
+        }
+        countLaunch();
+    }
 }
 
 }  // namespace orbx
