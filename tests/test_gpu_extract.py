@@ -67,11 +67,11 @@ def test_operator_matches_reference_fixture(orbx, name):
         ex.close()
 
 
-def _vs(orbx, oracle, im, nf, lap, mode="strict", ini=20, mn=7):
-    ex = orbx.ORBextractor(nf, 1.2, 8, ini, mn, fp_mode=mode)
+def _vs(orbx, oracle, im, nf, lap, mode="strict", ini=20, mn=7, scale=1.2, levels=8):
+    ex = orbx.ORBextractor(nf, scale, levels, ini, mn, fp_mode=mode)
     mono, kp, desc = ex(im, None, lap)
     checker = oracle.RefExtractor if oracle.have_ref(mode) else oracle.PortExtractor
-    rm, rk, rd = checker(nfeatures=nf, ini_th=ini, min_th=mn, mode=mode).extract(im, lap)
+    rm, rk, rd = checker(nfeatures=nf, scale_factor=scale, nlevels=levels, ini_th=ini, min_th=mn, mode=mode).extract(im, lap)
     assert mono == rm
     _same(kp, rk, "keypoints")
     _same(desc, rd, "descriptors")
@@ -98,6 +98,20 @@ def test_adversarial_inputs_match_reference(orbx, oracle):
     # few features: N_l small, the quadtree stops in its first rounds
     total += _vs(orbx, oracle, synth.frame(9, 640, 480), 40, (0, 1000))
     assert total > 8000
+
+
+def test_other_constructor_settings_match_reference(orbx, oracle):
+    """Scale factors / level counts / thresholds other than the shipped YAMLs (the class accepts any): wider resize
+    strips, 12-level pyramids whose top levels are smaller than one FAST cell, high and inverted thresholds."""
+    total = 0
+    total += _vs(orbx, oracle, synth.frame(11, 752, 480), 1000, (0, 1000), scale=1.5, levels=5)
+    total += _vs(orbx, oracle, synth.frame(12, 640, 480), 800, (0, 1000), scale=1.1, levels=12)
+    total += _vs(orbx, oracle, synth.frame(13, 1241, 376), 1500, (0, 0), scale=1.9, levels=4, mode="native")
+    total += _vs(orbx, oracle, synth.frame(14, 333, 251), 300, (0, 1000), scale=1.3, levels=6)
+    total += _vs(orbx, oracle, synth.frame(15, 640, 480), 1000, (0, 1000), ini=60, mn=30)
+    total += _vs(orbx, oracle, synth.frame(16, 640, 480), 1000, (0, 1000), ini=7, mn=20)
+    total += _vs(orbx, oracle, synth.frame(17, 640, 480), 1000, (0, 1000), ini=140, mn=130)
+    assert total > 3000
 
 
 def test_empty_image_returns_minus_one(orbx):

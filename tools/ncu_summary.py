@@ -1,0 +1,21 @@
+#!/usr/bin/env python
+"""One line per kernel launch of an .ncu-rep: time, DRAM bytes, issue %, occupancy, pipes.  usage: ncu_summary.py rep"""
+import csv, subprocess, sys
+out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(out.splitlines()))
+hdr = rows[0]; idx = {h: i for i, h in enumerate(hdr)}
+cols = [("gpu__time_duration.sum", "us"), ("dram__bytes_read.sum", "rdMB"), ("dram__bytes_write.sum", "wrMB"),
+        ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue%"), ("sm__warps_active.avg.pct_of_peak_sustained_active", "occ%"),
+        ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "alu%"), ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma%"),
+        ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu%"), ("smsp__inst_executed.sum", "winst"),
+        ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "bankconf"), ("launch__registers_per_thread", "regs"),
+        ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram%"), ("lts__t_sector_hit_rate.pct", "l2hit%")]
+print("kernel".ljust(28), " ".join(n.rjust(9) for _, n in cols), " grid")
+for r in rows[2:]:
+    name = r[idx["Kernel Name"]].split("(")[0].split("::")[-1][:28]
+    vals = []
+    for c, _ in cols:
+        v = r[idx[c]] if c in idx else ""
+        try: vals.append(f"{float(v):9.2f}" if float(v) < 1e6 else f"{float(v):9.3g}")
+        except ValueError: vals.append(v.rjust(9))
+    print(name.ljust(28), " ".join(vals), " ", r[idx["Grid Size"]])
