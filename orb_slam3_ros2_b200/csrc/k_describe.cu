@@ -16,10 +16,7 @@ namespace {
 
 #include "orb_pattern.inc"  // host table kOrbPattern[256][4]
 
-__device__ char4 gPattern[256];
 
-// umax[v] of the radius-15 disc (ORBextractor.cc:453-468)
-__constant__ int cUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
 // cv::fastAtan2 (OpenCV core/mathfuncs_core, scalar path), degrees in [0,360)
 __device__ __forceinline__ float fastAtan2Deg(float y, float x) {
@@ -133,35 +130,65 @@ __global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FrameP
 }
 
 // ---- K-d + K-f + K-h part 2: one warp per keypoint -----------------------------------------------------------
+// IC_Angle: the 31 x 31 bounding box of the disc is read as 31 rows x 8 aligned-and-shifted 32-bit words (every row of
+// the 128-B-pitched plane has the same misalignment, so one funnel shift amount serves the whole patch); each word
+// goes through two byte dot products against per-(row, word) coefficient words — u (signed, 0 outside the disc) for
+// m10 and the 0/1 disc mask for the row sum of m01.  248 words / 32 lanes = 8 per lane, all loads independent.
+__device__ uint2 gIcCoef[248];   // x: s8 u-coefficients, y: u8 disc mask, entry = row * 8 + word
+__device__ float4 gPatternF[256];
+
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 __global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
                                                       const uint8_t* __restrict__ blur, const LevelKp* __restrict__ lkp,
                                                       const int* __restrict__ lkpCnt, const int* __restrict__ slot,
                                                       float* __restrict__ outKps, uint8_t* __restrict__ outDesc) {
     const int f = blockIdx.y;
-    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (j >= P.lkpTotal) return;
-    int l = 0;
-    while (l + 1 < P.nlevels && j >= P.lv[l + 1].lkpBase) ++l;
+    // blockIdx.x enumerates 8-keypoint chunks level by level (uniform per block)
+    int chunk = blockIdx.x, l = 0;
+    for (; l < P.nlevels; ++l) {
+        const int nch = (P.lv[l].lkpCap + 7) >> 3;
+        if (chunk < nch) break;
+        chunk -= nch;
+    }
+    if (l >= P.nlevels) return;
     const LevelPlan& L = P.lv[l];
-    if (j - L.lkpBase >= lkpCnt[(size_t)f * P.nlevels + l]) return;
+    const int i = chunk * 8 + (threadIdx.x >> 5);
+    if (i >= lkpCnt[(size_t)f * P.nlevels + l]) return;
+    const int j = L.lkpBase + i;
     const LevelKp kp = lkp[(size_t)f * P.lkpTotal + j];
     const int s = slot[(size_t)f * P.lkpTotal + j];
     if (s >= P.outCap) return;
 
-    // IC_Angle: lane v+15 owns row v of the disc
+    // ---- IC_Angle (ORBextractor.cc:76-103) -----------------------------------------------------------------------
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int v = lane - 15;
-        const int d = cUmax[v < 0 ? -v : v];
-        const uint8_t* row = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kp.y + kEdge + v) * L.pitch + kp.x + kEdge;
-        int sum = 0;
-        for (int u = -d; u <= d; ++u) {
-            const int val = row[u];
-            m10 += u * val;
-            sum += val;
+    {
+        const uint8_t* plane = pyr + (size_t)f * P.frameBytes + L.planeOff;
+        const int px = kp.x + kEdge - kHalfPatch;                 // plane column of u = -15
+        const uint8_t* p0 = plane + (size_t)(kp.y + kEdge - kHalfPatch) * L.pitch + (px & ~3);
+        const int sh = (px & 3) * 8;
+        uint32_t lo[8], hi[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int item = it * 32 + lane;                      // row = item >> 3, word = item & 7
+            const uint32_t* q = reinterpret_cast<const uint32_t*>(p0 + (size_t)((item >> 3) * L.pitch)) + (item & 7);
+            const bool ok = item < 248;
+            lo[it] = ok ? __ldg(q) : 0u;
+            hi[it] = ok ? __ldg(q + 1) : 0u;
         }
-        m01 = v * sum;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int item = it * 32 + lane;
+            const uint2 cf = gIcCoef[item < 248 ? item : 0];
+            const uint32_t w = __funnelshift_r(lo[it], hi[it], sh);
+            m10 = dp4a_us(w, cf.x, m10);
+            m01 += ((item >> 3) - kHalfPatch) * (int)__dp4a(w, cf.y, 0u);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -170,32 +197,35 @@ __global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ Fr
     }
     const float angle = fastAtan2Deg((float)m01, (float)m10);
 
-    // rBRIEF: lane i computes byte i (pairs 8i .. 8i+7, LSB first)
+    // ---- rBRIEF: lane i computes byte i (pairs 8i .. 8i+7, LSB first) ----------------------------------------------------
     const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
     float a, b;
     glibcSincosf(__fmul_rn(angle, factorPI), &b, &a);
     const uint8_t* center = blur + (size_t)f * P.blurBytes + L.blurOff + (size_t)kp.y * L.bpitch + kp.x;
     const int step = L.bpitch;
-    uint32_t byte = 0;
+    const bool strict = P.fpMode == 0;
+    uint32_t t0[8], t1[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const char4 pt = gPattern[lane * 8 + k];
-        int t[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const float fx = (float)(h ? pt.z : pt.x), fy = (float)(h ? pt.w : pt.y);
-            int r, c;
-            if (P.fpMode == 0) {
-                r = __float2int_rn(__fadd_rn(__fmul_rn(fx, b), __fmul_rn(fy, a)));
-                c = __float2int_rn(__fsub_rn(__fmul_rn(fx, a), __fmul_rn(fy, b)));
-            } else {
-                r = __float2int_rn(__fmaf_rn(fx, b, __fmul_rn(fy, a)));
-                c = __float2int_rn(__fmaf_rn(fx, a, -__fmul_rn(fy, b)));
-            }
-            t[h] = center[r * step + c];
+        const float4 pt = gPatternF[lane * 8 + k];
+        int r0, c0, r1, c1;
+        if (strict) {
+            r0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
+            c0 = __float2int_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
+            r1 = __float2int_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
+            c1 = __float2int_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
+        } else {
+            r0 = __float2int_rn(__fmaf_rn(pt.x, b, __fmul_rn(pt.y, a)));
+            c0 = __float2int_rn(__fmaf_rn(pt.x, a, -__fmul_rn(pt.y, b)));
+            r1 = __float2int_rn(__fmaf_rn(pt.z, b, __fmul_rn(pt.w, a)));
+            c1 = __float2int_rn(__fmaf_rn(pt.z, a, -__fmul_rn(pt.w, b)));
         }
-        byte |= (uint32_t)(t[0] < t[1]) << k;
+        t0[k] = center[r0 * step + c0];
+        t1[k] = center[r1 * step + c1];
     }
+    uint32_t byte = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) byte |= (uint32_t)(t0[k] < t1[k]) << k;
     uint32_t word = byte << (8 * (lane & 3));
     word |= __shfl_xor_sync(0xffffffffu, word, 1);
     word |= __shfl_xor_sync(0xffffffffu, word, 2);
@@ -229,14 +259,37 @@ __global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ Fr
 }  // namespace
 
 // per device, once per extractor (orbx_create)
-void uploadDescribeTables() { cudaMemcpyToSymbol(gPattern, kOrbPattern, sizeof(kOrbPattern)); }
+void uploadDescribeTables() {
+    static const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};  // ORBextractor.cc:453-468
+    float4 pat[256];
+    for (int i = 0; i < 256; ++i)
+        pat[i] = make_float4((float)kOrbPattern[i][0], (float)kOrbPattern[i][1], (float)kOrbPattern[i][2], (float)kOrbPattern[i][3]);
+    cudaMemcpyToSymbol(gPatternF, pat, sizeof(pat));
+    uint2 coef[248];
+    for (int r = 0; r < 31; ++r)
+        for (int k = 0; k < 8; ++k) {
+            uint32_t cu = 0, cm = 0;
+            const int v = r - 15;
+            for (int b = 0; b < 4; ++b) {
+                const int u = 4 * k - 15 + b;
+                const int au = u < 0 ? -u : u;
+                if (au <= umax[v < 0 ? -v : v]) {  // u = 16 (last byte of word 7) is never inside
+                    cu |= (uint32_t)(uint8_t)(int8_t)u << (8 * b);
+                    cm |= 1u << (8 * b);
+                }
+            }
+            coef[r * 8 + k] = make_uint2(cu, cm);
+        }
+    cudaMemcpyToSymbol(gIcCoef, coef, sizeof(coef));
+}
 
 void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s) {
     slotKernel<<<F, 256, 0, s>>>(P, B.lkp, B.lkpCnt, B.slot, B.outN, B.outMono, lap0, lap1, B.errFlag);
     countLaunch();
-    const int warpsPerBlock = 8;
-    describeKernel<<<dim3((P.lkpTotal + warpsPerBlock - 1) / warpsPerBlock, F), 256, 0, s>>>(
-        P, B.pyr, B.blur, B.lkp, B.lkpCnt, B.slot, reinterpret_cast<float*>(B.outKps), B.outDesc);
+    int chunks = 0;
+    for (int l = 0; l < P.nlevels; ++l) chunks += (P.lv[l].lkpCap + 7) / 8;
+    describeKernel<<<dim3(chunks, F), 256, 0, s>>>(P, B.pyr, B.blur, B.lkp, B.lkpCnt, B.slot,
+                                                   reinterpret_cast<float*>(B.outKps), B.outDesc);
     countLaunch();
 }
 
