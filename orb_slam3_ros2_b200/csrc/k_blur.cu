@@ -10,17 +10,25 @@
 // aligned and are fetched with 128-bit loads.
 //
 // One launch covers all levels and frames: blockIdx.x enumerates (level, tile), blockIdx.y the frame.
+//
+// Arithmetic layout (v2): both passes are byte / half-word DOT PRODUCTS, which sm_100a executes as single instructions:
+//   horizontal  H[x] = sum_i k[i] * I[x+i-3]  = dp4a(bytes x-3..x, (18,34,48,56)) + dp4a(bytes x+1..x+4, (48,34,18,0));
+//               the two byte windows of each pixel are funnel shifts of three aligned words shared by 4 pixels;
+//   vertical    H rows are stored as VERTICAL pairs (rows 2m, 2m+1 of the staged tile in one 32-bit word), so the 7-tap
+//               column sum is four dp2a (16-bit x 8-bit, 2-way) on consecutive pairs; even and odd output rows differ
+//               only in the coefficient bytes.  The rounding constant rides in the first accumulator.
+// H <= 65280 fits 16 bits and V <= 65280 * 256 + 32768 fits 32 bits, exactly OpenCV's fixed-point path.
 #include "orbx_internal.cuh"
 
 namespace orbx {
 namespace {
 
-constexpr int kTileW = 128, kTileH = 32, kInRows = kTileH + 6, kInPitch = 144;
+constexpr int kTileW = 128, kTileH = 32, kInRows = kTileH + 6, kInPitch = 144, kPairs = kInRows / 2;
 
 __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
                                                   uint8_t* __restrict__ blur) {
     __shared__ __align__(16) uint8_t sIn[kInRows * kInPitch];
-    __shared__ __align__(16) uint16_t sH[kInRows * kTileW];
+    __shared__ __align__(16) uint32_t sHp[kPairs * kTileW];  // (H[2m][x] | H[2m+1][x] << 16)
 
     int t = blockIdx.x, l = 0;
     for (; l < P.nlevels; ++l) {
@@ -36,7 +44,7 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     const int ph = L.h + 2 * kEdge;
     const int tid = threadIdx.x;
 
-    // stage (kTileH+6) rows x 144 bytes, padded coordinates (x0+16, y0+16)
+    // stage (kTileH+6) rows x 144 bytes, padded coordinates (x0+16, y0+16): staged byte 0 of a row = level column x0-3
     for (int i = tid; i < kInRows * (kInPitch / 16); i += 256) {
         const int r = i / (kInPitch / 16), c = i % (kInPitch / 16);
         const int yy = min(y0 + 16 + r, ph - 1);
@@ -47,50 +55,57 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     }
     __syncthreads();
 
-    // horizontal pass: 4 outputs per item from 12 staged bytes
-    for (int i = tid; i < kInRows * (kTileW / 4); i += 256) {
-        const int r = i / (kTileW / 4), g = i % (kTileW / 4);
-        const uint32_t* p = reinterpret_cast<const uint32_t*>(sIn + r * kInPitch + g * 4);
-        const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
-        int b[12];
+    // horizontal pass: item = (row pair m, 4 columns g)
+    constexpr uint32_t K1 = 0x38302212u, K2 = 0x00122230u;  // (18,34,48,56), (48,34,18,0)
+    for (int i = tid; i < kPairs * (kTileW / 4); i += 256) {
+        const int m = i >> 5, g = i & 31;
+        uint32_t h[2][4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            b[k] = (w0 >> (8 * k)) & 255;
-            b[4 + k] = (w1 >> (8 * k)) & 255;
-            b[8 + k] = (w2 >> (8 * k)) & 255;
+        for (int rr = 0; rr < 2; ++rr) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(sIn + (2 * m + rr) * kInPitch) + g;
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t a = j ? __funnelshift_r(w0, w1, 8 * j) : w0;
+                const uint32_t b = j ? __funnelshift_r(w1, w2, 8 * j) : w1;
+                h[rr][j] = __dp4a(a, K1, __dp4a(b, K2, 0u));
+            }
         }
-        uint16_t o[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            o[k] = (uint16_t)(18 * (b[k] + b[k + 6]) + 34 * (b[k + 1] + b[k + 5]) + 48 * (b[k + 2] + b[k + 4]) +
-                              56 * b[k + 3]);
-        uint2 pk;
-        pk.x = o[0] | ((uint32_t)o[1] << 16);
-        pk.y = o[2] | ((uint32_t)o[3] << 16);
-        *reinterpret_cast<uint2*>(sH + r * kTileW + g * 4) = pk;
+        uint4 pk;
+        pk.x = h[0][0] | (h[1][0] << 16);
+        pk.y = h[0][1] | (h[1][1] << 16);
+        pk.z = h[0][2] | (h[1][2] << 16);
+        pk.w = h[0][3] | (h[1][3] << 16);
+        *reinterpret_cast<uint4*>(sHp + m * kTileW + g * 4) = pk;
     }
     __syncthreads();
 
-    // vertical pass: thread = 4 columns x 4 rows, sliding 10-row window
-    const int tx = tid & 31, ty = tid >> 5;
-    uint32_t h[10][4];
+    // vertical pass: thread = 4 columns x 4 rows; output row 4q+i taps staged rows 4q+i .. 4q+i+6 = pairs 2q .. 2q+4
+    const int tx = tid & 31, q = tid >> 5;
+    uint4 pr[5];
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const uint2 v = *reinterpret_cast<const uint2*>(sH + (ty * 4 + r) * kTileW + tx * 4);
-        h[r][0] = v.x & 0xffff; h[r][1] = v.x >> 16; h[r][2] = v.y & 0xffff; h[r][3] = v.y >> 16;
-    }
+    for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * q + k) * kTileW + tx * 4);
     uint8_t* out = blur + (size_t)blockIdx.y * P.blurBytes + L.blurOff;
     const int x = x0 + tx * 4;
+    // coefficient byte pairs (low byte multiplies the even row of a pair)
+    constexpr uint32_t Ea = 0x2212u, Eb = 0x3830u, Ec = 0x2230u, Ed = 0x0012u;   // even start: 18,34 | 48,56 | 48,34 | 18,0
+    constexpr uint32_t Oa = 0x1200u, Ob = 0x3022u, Oc = 0x3038u, Od = 0x1222u;   // odd start:  0,18 | 34,48 | 56,48 | 34,18
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        const int y = y0 + ty * 4 + r;
-        uint32_t word = 0;
+    for (int i = 0; i < 4; ++i) {
+        const int y = y0 + q * 4 + i;
+        const int b = i >> 1;  // first pair
+        const uint32_t ca = (i & 1) ? Oa : Ea, cb = (i & 1) ? Ob : Eb, cc = (i & 1) ? Oc : Ec, cd = (i & 1) ? Od : Ed;
+        uint32_t v[4];
+        const uint32_t* p0 = &pr[b].x; const uint32_t* p1 = &pr[b + 1].x; const uint32_t* p2 = &pr[b + 2].x; const uint32_t* p3 = &pr[b + 3].x;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const uint32_t acc = 18u * (h[r][k] + h[r + 6][k]) + 34u * (h[r + 1][k] + h[r + 5][k]) +
-                                 48u * (h[r + 2][k] + h[r + 4][k]) + 56u * h[r + 3][k];
-            word |= ((acc + 32768u) >> 16) << (8 * k);
+            uint32_t acc = __dp2a_lo(p0[k], ca, 32768u);
+            acc = __dp2a_lo(p1[k], cb, acc);
+            acc = __dp2a_lo(p2[k], cc, acc);
+            acc = __dp2a_lo(p3[k], cd, acc);
+            v[k] = acc >> 16;
         }
+        const uint32_t word = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
         if (y < L.h && x < L.bpitch) *reinterpret_cast<uint32_t*>(out + (size_t)y * L.bpitch + x) = word;
     }
 }
