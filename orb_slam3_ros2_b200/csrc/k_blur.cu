@@ -30,16 +30,12 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     __shared__ __align__(16) uint8_t sIn[kInRows * kInPitch];
     __shared__ __align__(16) uint32_t sHp[kPairs * kTileW];  // (H[2m][x] | H[2m+1][x] << 16)
 
-    int t = blockIdx.x, l = 0;
-    for (; l < P.nlevels; ++l) {
-        const int nt = ((P.lv[l].w + kTileW - 1) / kTileW) * ((P.lv[l].h + kTileH - 1) / kTileH);
-        if (t < nt) break;
-        t -= nt;
-    }
-    if (l >= P.nlevels) return;
+    int l = 0;
+    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].blurTile0) ++l;
     const LevelPlan& L = P.lv[l];
-    const int tilesX = (L.w + kTileW - 1) / kTileW;
-    const int x0 = (t % tilesX) * kTileW, y0 = (t / tilesX) * kTileH;
+    const int t = blockIdx.x - L.blurTile0;
+    const int ty = t / L.blurTilesX;
+    const int x0 = (t - ty * L.blurTilesX) * kTileW, y0 = ty * kTileH;
     const uint8_t* plane = pyr + (size_t)blockIdx.y * P.frameBytes + L.planeOff;
     const int ph = L.h + 2 * kEdge;
     const int tid = threadIdx.x;
@@ -85,8 +81,8 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     uint4 pr[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * q + k) * kTileW + tx * 4);
-    uint8_t* out = blur + (size_t)blockIdx.y * P.blurBytes + L.blurOff;
     const int x = x0 + tx * 4;
+    uint8_t* out = blur + (size_t)blockIdx.y * P.blurBytes + L.blurOff + (size_t)(y0 + q * 4) * L.bpitch + x;
     // coefficient byte pairs (low byte multiplies the even row of a pair)
     constexpr uint32_t Ea = 0x2212u, Eb = 0x3830u, Ec = 0x2230u, Ed = 0x0012u;   // even start: 18,34 | 48,56 | 48,34 | 18,0
     constexpr uint32_t Oa = 0x1200u, Ob = 0x3022u, Oc = 0x3038u, Od = 0x1222u;   // odd start:  0,18 | 34,48 | 56,48 | 34,18
@@ -106,17 +102,15 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
             v[k] = acc >> 16;
         }
         const uint32_t word = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
-        if (y < L.h && x < L.bpitch) *reinterpret_cast<uint32_t*>(out + (size_t)y * L.bpitch + x) = word;
+        if (y < L.h && x < L.bpitch) *reinterpret_cast<uint32_t*>(out + i * L.bpitch) = word;
     }
 }
 
 }  // namespace
 
 void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
-    int tiles = 0;
-    for (int l = 0; l < P.nlevels; ++l)
-        tiles += ((P.lv[l].w + kTileW - 1) / kTileW) * ((P.lv[l].h + kTileH - 1) / kTileH);
-    blurKernel<<<dim3(tiles, F), 256, 0, s>>>(P, B.pyr, B.blur);
+    static_assert(kTileW == 128 && kTileH == 32, "the plan's blurTile0 / blurTilesX assume 128 x 32 tiles");
+    blurKernel<<<dim3(P.blurTiles, F), 256, 0, s>>>(P, B.pyr, B.blur);
     countLaunch();
 }
 

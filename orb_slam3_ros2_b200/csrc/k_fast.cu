@@ -15,22 +15,23 @@
 //
 // Work decomposition (v3): ONE WARP PER CELL, eight cells per CTA, no block-level synchronisation.
 //   1. the cell (plus the bytes left of it down to a 16-B boundary) is staged in shared memory with 128-bit loads;
-//   2. quick reject, 4 pixels per lane with byte SIMD: any 9-arc contains ring[0] or ring[8] and ring[4] or ring[12],
+//   2. quick reject, 16 pixels per lane (128-bit shared loads) with byte SIMD: any 9-arc contains ring[0] or ring[8] and ring[4] or ring[12],
 //      so a corner needs max(|up-c|,|dn-c|) > t and max(|l-c|,|r-c|) > t.  |.| is the native VABSDIFF4; "> t" per
 //      byte is one masked add whose carry lands in bit 7.  ~97 % of the pixels end here at t = 20;
-//   3. the flagged 4-pixel groups are appended, in row-major order, to a list (ballot + popc), expanded to a pixel
-//      list, and the exact arc strength is computed for two pixels per lane with the packed 16-bit VIMNMX3
+//   3. the flagged 16-pixel chunks are appended, in row-major order, to a list (ballot + popc), expanded to a pixel
+//      list (segments of <= 256 pixels), and the exact arc strength is computed for two pixels per lane with the packed 16-bit VIMNMX3
 //      (80 three-input min/max per pair) and written to a byte arc map (0 everywhere else);
 //   4. every listed pixel with arc > t is compared with its 8 neighbours in the arc map; survivors are written
 //      in order (ballot + popc again) as resp<<24 | y<<12 | x.
+#include <algorithm>
+
 #include "orbx_internal.cuh"
 
 namespace orbx {
 namespace {
 
 constexpr int kWarpsPerCta = 8;
-constexpr int kPixCap = 512;      // pixel list capacity per warp (one segment = 128 groups of <= 4 pixels)
-constexpr int kSegGroups = 128;
+constexpr int kPixCap = 256;      // pixel list capacity per warp (one segment of flagged pixels)
 
 __device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
 __device__ __forceinline__ uint32_t min3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
@@ -63,26 +64,34 @@ __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32
 
 // PITCH = bytes per tile row in shared memory (multiple of 16)
 template <int PITCH>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     fastCellsKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
-                    int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes, unsigned levelMask) {
+                    int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes, unsigned levelMask,
+                    int cellsInLaunch, int totalWork, int* __restrict__ workCounter) {
     extern __shared__ __align__(16) uint8_t smem[];
     constexpr int P4 = PITCH / 4, P16 = PITCH / 16;
     const int lane = threadIdx.x & 31, wip = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
 
-    // ---- which cell -------------------------------------------------------------------------------------
-    int c = blockIdx.x * kWarpsPerCta + wip, l = 0;
+    // ---- persistent warps: cells are handed out through a global counter, so a warp that drew an expensive cell (the
+    // minThFAST fallback costs several times the common case) never keeps seven finished warps' shared memory idle ----
+    for (;;) {
+    __syncwarp();
+    int work = 0;
+    if (lane == 0) work = atomicAdd(workCounter, 1);
+    work = __shfl_sync(0xffffffffu, work, 0);
+    if (work >= totalWork) break;
+    const int f = work / cellsInLaunch;
+    int c = work - f * cellsInLaunch, l = 0;
     for (; l < P.nlevels; ++l) {  // cells of the levels selected by levelMask, level-major
         if (!((levelMask >> l) & 1u)) continue;
         const int nc = P.lv[l].nCols * P.lv[l].nRows;
         if (c < nc) break;
         c -= nc;
     }
-    if (l >= P.nlevels) return;
+    if (l >= P.nlevels) continue;
     const LevelPlan& L = P.lv[l];
     const int ci = c / L.nCols, cj = c - ci * L.nCols;
-    const int f = blockIdx.y;
     int* cntOut = cellCnt + (size_t)f * P.nCellsTotal + L.cellBase + c;
     const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
     const int iniX = kMinBorder + cj * L.wCell, iniY = kMinBorder + ci * L.hCell;
@@ -93,35 +102,37 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
     // ORBextractor.cc:813-816, :820-823 skip rules; cv::FAST returns nothing below 7x7
     if (iniY >= maxBY - 3 || iniX >= maxBX - 6 || cw < 7 || ch < 7) {
         if (lane == 0) *cntOut = 0;
-        return;
+        continue;
     }
 
     uint8_t* tile = smem + (size_t)wip * warpBytes;      // [rowsMax][PITCH] pixels; tile x = cell x + shift
-    uint8_t* arc = tile + rowsMax * PITCH;               // same geometry: arc strength, 0 where not computed
-    uint16_t* glist = reinterpret_cast<uint16_t*>(arc + rowsMax * PITCH);  // flagged groups: item << 4 | nibble
-    uint16_t* pbuf = glist + itemsMax;                   // pixel list of the current segment: y << 7 | x (tile coords)
+    uint8_t* arcStore = tile + rowsMax * PITCH;          // [rowsMax-4][PITCH] arc strength of tile rows 2 .. ch-3
+    uint8_t* arc = arcStore - 2 * PITCH;                 // indexed like the tile; 0 where not computed
+    uint32_t* glist = reinterpret_cast<uint32_t*>(arcStore + (rowsMax - 4) * PITCH);  // flagged chunks: item << 16 | mask
+    uint16_t* pbuf = reinterpret_cast<uint16_t*>(glist + itemsMax);  // pixel list of the current segment: y << 7 | x
     const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(tile);
+    const uint4* tile128 = reinterpret_cast<const uint4*>(tile);
 
     // ---- stage the cell with 128-bit loads; clear the arc map --------------------------------------------------
     const int gx0 = kEdge + iniX;
     const int shift = gx0 & 15;
     {
         const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + (gx0 - shift);
-        const int n16 = ch * P16;
+        const int n16 = ch * P16, nArc = (ch - 4) * P16;
         for (int i = lane; i < n16; i += 32) {
             const int r = i / P16, k = i - r * P16;
             const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * L.pitch) + k);
             reinterpret_cast<uint4*>(tile)[i] = v;
-            reinterpret_cast<uint4*>(arc)[i] = make_uint4(0, 0, 0, 0);
+            if (i < nArc) reinterpret_cast<uint4*>(arcStore)[i] = make_uint4(0, 0, 0, 0);
         }
     }
     __syncwarp();
 
-    // tested pixels: tile x in [xs, xe), rows [3, ch-3)
+    // tested pixels: tile x in [xs, xe), rows [3, ch-3); an item of the quick test is one 16-byte chunk of a row
     const int xs = shift + 3, xe = shift + cw - 3;
-    const int w0 = xs >> 2, nW = ((xe - 1) >> 2) - w0 + 1, nR = ch - 6;
-    const int nItems = nR * nW;
-    const unsigned divW = 65536u / (unsigned)nW + 1u;   // (i * divW) >> 16 == i / nW for i < 2048, nW <= 32
+    const int c0 = xs >> 4, nC = ((xe - 1) >> 4) - c0 + 1, nR = ch - 6;
+    const int nItems = nR * nC;
+    const unsigned divC = 65536u / (unsigned)nC + 1u;   // (i * divC) >> 16 == i / nC for i < 2048, nC <= 32
     uint32_t* slot = cand + (size_t)f * P.candWords + L.candOff + (size_t)c * L.cellCap;
     const int xOut = cj * L.wCell - shift, yOut = ci * L.hCell;  // tile coords -> cell-grid coords of :865-866
     // response = arc - 1 must beat the zero score of non-corners: arc >= 2 (only matters for thresholds < 1)
@@ -134,69 +145,88 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
         // per byte: ((d & 0x7f) + K) | d has bit 7 set iff d > tq, tq = min(t, 126) (a NECESSARY condition for t > 126)
         const uint32_t K = (uint32_t)(0x7f - min(t, 126)) * 0x01010101u;
 
-        // ---- quick reject: flagged 4-pixel groups appended in row-major order ----------------------------------
+        // ---- quick reject, 16 pixels per lane: flagged chunks appended in row-major order ------------------------
         int nG = 0;
         for (int i0 = 0; i0 < nItems; i0 += 32) {
             const int i = i0 + lane;
-            uint32_t F = 0;
+            uint32_t m = 0;
             if (i < nItems) {
-                const int r = (int)(((unsigned)i * divW) >> 16);
-                const int idx = (r + 3) * P4 + w0 + (i - r * nW);
-                const uint32_t cc = tile32[idx];
-                const uint32_t up = tile32[idx - 3 * P4], dn = tile32[idx + 3 * P4];
-                const uint32_t lf = __byte_perm(tile32[idx - 1], cc, 0x4321);  // pixels x-3 .. x
-                const uint32_t rt = __byte_perm(cc, tile32[idx + 1], 0x6543);  // pixels x+3 .. x+6
-                const uint32_t d0 = __vabsdiffu4(up, cc), d8 = __vabsdiffu4(dn, cc);
-                const uint32_t d4 = __vabsdiffu4(rt, cc), d12 = __vabsdiffu4(lf, cc);
-                const uint32_t v = (((d0 & 0x7f7f7f7fu) + K) | d0) | (((d8 & 0x7f7f7f7fu) + K) | d8);
-                const uint32_t h = (((d4 & 0x7f7f7f7fu) + K) | d4) | (((d12 & 0x7f7f7f7fu) + K) | d12);
-                F = v & h & 0x80808080u;
+                const int r = (int)(((unsigned)i * divC) >> 16);
+                const int cx = c0 + (i - r * nC);
+                const int idx = (r + 3) * P16 + cx;
+                const uint4 cc = tile128[idx], up = tile128[idx - 3 * P16], dn = tile128[idx + 3 * P16];
+                const uint32_t lw = tile32[4 * idx - 1], rw = tile32[4 * idx + 4];
+                const uint32_t cw4[6] = {lw, cc.x, cc.y, cc.z, cc.w, rw};
+                const uint32_t uw[4] = {up.x, up.y, up.z, up.w}, dw4[4] = {dn.x, dn.y, dn.z, dn.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t ce = cw4[k + 1];
+                    const uint32_t lf = __byte_perm(cw4[k], ce, 0x4321);      // pixels x-3 .. x
+                    const uint32_t rt = __byte_perm(ce, cw4[k + 2], 0x6543);  // pixels x+3 .. x+6
+                    const uint32_t d0 = __vabsdiffu4(uw[k], ce), d8 = __vabsdiffu4(dw4[k], ce);
+                    const uint32_t d4 = __vabsdiffu4(rt, ce), d12 = __vabsdiffu4(lf, ce);
+                    const uint32_t v = (((d0 & 0x7f7f7f7fu) + K) | d0) | (((d8 & 0x7f7f7f7fu) + K) | d8);
+                    const uint32_t h = (((d4 & 0x7f7f7f7fu) + K) | d4) | (((d12 & 0x7f7f7f7fu) + K) | d12);
+                    const uint32_t F = v & h & 0x80808080u;
+                    m |= (((F >> 7) * 0x01020408u) >> 24) << (4 * k);  // bit 4k+j = pixel 4k+j of the chunk
+                }
+                // drop the pixels of edge chunks that lie outside the tested columns
+                const int x0 = cx << 4;
+                const int lo = min(max(xs - x0, 0), 16), hi = min(max(xe - x0, 0), 16);
+                m &= ((1u << hi) - 1u) & ~((1u << lo) - 1u);
             }
-            const unsigned bal = __ballot_sync(0xffffffffu, F != 0);
-            if (F) {
-                const uint32_t nib = (((F >> 7) * 0x01020408u) >> 24) & 0xfu;  // bit j = pixel j of the group
-                glist[nG + __popc(bal & ltMask)] = (uint16_t)((i << 4) | nib);
-            }
+            const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
+            if (m) glist[nG + __popc(bal & ltMask)] = ((uint32_t)i << 16) | m;
             nG += __popc(bal);
         }
         __syncwarp();
 
-        // ---- segments of <= 128 groups: expand -> exact arcs (phase A); then expand -> NMS -> output (phase B) ----
-        const int nSeg = (nG + kSegGroups - 1) / kSegGroups;
+        // ---- segments of <= kPixCap flagged pixels: expand -> exact arcs (phase A); then expand -> NMS -> output (B) ----
+        bool single = false;
         int nPix = 0;
         for (int phase = 0; phase < 2; ++phase) {
-            for (int seg = 0; seg < nSeg; ++seg) {
-                if (!(phase == 1 && nSeg == 1)) {  // with a single segment the pixel list of phase A is still valid
+            int cursor = 0, nSeg = 0;
+            while (cursor < nG) {
+                if (!(phase == 1 && single)) {  // with a single segment the pixel list of phase A is still valid
                     nPix = 0;
-                    const int g1 = min(nG, (seg + 1) * kSegGroups);
-                    for (int g0 = seg * kSegGroups; g0 < g1; g0 += 32) {
-                        const int g = g0 + lane;
-                        int nib = 0, y = 0, x0 = 0;
-                        if (g < g1) {
-                            const int e = glist[g];
-                            const int i = e >> 4;
-                            const int r = (int)(((unsigned)i * divW) >> 16);
+                    while (cursor < nG) {
+                        const int g = cursor + lane;
+                        uint32_t mm = 0;
+                        int y = 0, x0 = 0;
+                        if (g < nG) {
+                            const uint32_t e = glist[g];
+                            const int i = (int)(e >> 16);
+                            const int r = (int)(((unsigned)i * divC) >> 16);
                             y = r + 3;
-                            x0 = (w0 + (i - r * nW)) << 2;
-                            // drop the pixels of edge groups that lie outside the tested columns
-                            const int lo = min(max(xs - x0, 0), 4), hi = min(max(xe - x0, 0), 4);
-                            nib = (e & 0xf) & ((1 << hi) - 1) & ~((1 << lo) - 1);
+                            x0 = (c0 + (i - r * nC)) << 4;
+                            mm = e & 0xffffu;
                         }
-                        const int n = __popc(nib);
+                        const int n = __popc(mm);
                         int incl = n;
 #pragma unroll
                         for (int o = 1; o < 32; o <<= 1) {
                             const int v = __shfl_up_sync(0xffffffffu, incl, o);
                             if (lane >= o) incl += v;
                         }
-                        int pos = nPix + incl - n;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if ((nib >> j) & 1) pbuf[pos++] = (uint16_t)((y << 7) | (x0 + j));
-                        nPix += __shfl_sync(0xffffffffu, incl, 31);
+                        const bool accept = g < nG && nPix + incl <= kPixCap;  // a prefix of the lanes
+                        const int nAcc = __popc(__ballot_sync(0xffffffffu, accept));
+                        if (accept) {
+                            int pos = nPix + incl - n;
+                            while (mm) {
+                                const int j = __ffs(mm) - 1;
+                                mm &= mm - 1;
+                                pbuf[pos++] = (uint16_t)((y << 7) | (x0 + j));
+                            }
+                        }
+                        if (nAcc) nPix += __shfl_sync(0xffffffffu, incl, nAcc - 1);
+                        cursor += nAcc;
+                        if (nAcc < 32) break;  // list exhausted, or the segment is full
                     }
                     __syncwarp();
+                } else {
+                    cursor = nG;
                 }
+                ++nSeg;
                 if (phase == 0) {
                     // exact arc strength, two pixels per lane
                     for (int b = 0; b < nPix; b += 64) {
@@ -242,10 +272,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
                     }
                 }
             }
+            if (phase == 0) single = nSeg == 1;
+            __syncwarp();
         }
-        __syncwarp();
     }
     if (lane == 0) *cntOut = kept;
+    }  // persistent loop
 }
 
 struct FastGeom {
@@ -259,22 +291,30 @@ FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch) {
         const LevelPlan& L = P.lv[l];
         const int ch = L.hCell + 6, cw = L.wCell + 6;
         g.rowsMax = ch > g.rowsMax ? ch : g.rowsMax;
-        const int items = (ch - 6) * ((cw - 6 + 3) / 4 + 2);
+        const int items = (ch - 6) * (pitch / 16);
         g.itemsMax = items > g.itemsMax ? items : g.itemsMax;
     }
-    g.itemsMax = (g.itemsMax + 7) & ~7;
-    g.warpBytes = 2 * g.rowsMax * pitch + 2 * g.itemsMax + 2 * kPixCap;
+    g.itemsMax = (g.itemsMax + 3) & ~3;
+    g.warpBytes = (2 * g.rowsMax - 4) * pitch + 4 * g.itemsMax + 2 * kPixCap;
     g.warpBytes = (g.warpBytes + 15) & ~15;
     return g;
 }
 
 template <int PITCH>
-void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, cudaStream_t s) {
+void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, int* counter, cudaStream_t s) {
     const FastGeom g = geomFor(P, mask, PITCH);
     const size_t smem = (size_t)g.warpBytes * kWarpsPerCta;
     if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<PITCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    const dim3 grid((cells + kWarpsPerCta - 1) / kWarpsPerCta, F);
-    fastCellsKernel<PITCH><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, mask);
+    int dev = 0, sms = 148, perSm = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fastCellsKernel<PITCH>, kWarpsPerCta * 32, smem);
+    const long long total = (long long)cells * F;
+    const long long want = (total + kWarpsPerCta - 1) / kWarpsPerCta;
+    const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
+    cudaMemsetAsync(counter, 0, sizeof(int), s);
+    fastCellsKernel<PITCH><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, mask,
+                                                                 cells, (int)total, counter);
     countLaunch();
 }
 
@@ -295,8 +335,8 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
-        if (!wide) launchClass<64>(P, B, F, mask, cells, s);
-        else launchClass<96>(P, B, F, mask, cells, s);
+        if (!wide) launchClass<64>(P, B, F, mask, cells, B.errFlag + 4, s);
+        else launchClass<96>(P, B, F, mask, cells, B.errFlag + 5, s);
     }
 }
 

@@ -130,7 +130,7 @@ static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab)
     P.minTh = std::min(std::max(h->prm.min_th_fast, 0), 255);
     P.fpMode = h->prm.fp_mode;
     unsigned pyrOff = 0, blurOff = 0, candOff = 0, gathOff = 0;
-    int cellBase = 0, lkpBase = 0;
+    int cellBase = 0, lkpBase = 0, blurTiles = 0;
     for (int l = 0; l < nl; ++l) {
         LevelPlan& L = P.lv[l];
         L.w = cvRoundF((float)W * h->isf[l]);  // ORBextractor.cc:1175 (from the ORIGINAL size)
@@ -140,6 +140,7 @@ static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab)
         L.bpitch = (int)alignUp(L.w, 128);
         L.planeOff = pyrOff; pyrOff += (unsigned)L.pitch * (L.h + 2 * kEdge);
         L.blurOff = blurOff; blurOff += (unsigned)L.bpitch * L.h;
+        L.blurTile0 = blurTiles; L.blurTilesX = (L.w + 127) / 128; blurTiles += L.blurTilesX * ((L.h + 31) / 32);
         // FAST grid (ORBextractor.cc:789-803)
         const float width = (float)(L.w - 2 * kMinBorder), height = (float)(L.h - 2 * kMinBorder);
         L.nCols = width > 0 ? (int)(width / kCellW) : 0;
@@ -165,6 +166,7 @@ static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab)
     P.blurBytes = alignUp(blurOff + 256, 256);
     P.candWords = candOff; P.gathWords = alignUp(gathOff, 8);
     P.nCellsTotal = cellBase;
+    P.blurTiles = blurTiles;
     P.lkpTotal = lkpBase;
     P.outCap = lkpBase;
     if (quadtreeSmemBytes(P) > 220 * 1024) return fail(ORBX_ERR_ARG, "nfeatures too large for the quadtree kernel's shared memory");
@@ -199,8 +201,8 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         ORBX_CUDA(h->mOutD.reserve(f * P.outCap * 32));
         ORBX_CUDA(h->mOutN.reserve(f * 4));
         ORBX_CUDA(h->mOutM.reserve(f * 4));
-        ORBX_CUDA(h->mErr.reserve(16));
-        ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 16, h->stream));
+        ORBX_CUDA(h->mErr.reserve(64));  // [0] error flags, [4..] work counters of persistent kernels
+        ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 64, h->stream));
         h->capFrames = F;
     }
     Buffers& B = h->buf;

@@ -39,6 +39,7 @@ struct LevelPlan {
     int lkpBase;         // first slot of this level in the frame's level-keypoint array
     int lkpCap;          // nFeat + 4 (F5: the quadtree returns N..N+3)
     int tabX, tabY;      // offsets into the resize coefficient table (int16 triplets ofs,a0,a1)
+    int blurTile0, blurTilesX;  // first 128x32 blur tile of the level in the launch's tile list, tiles per row
     float scale;         // mvScaleFactor[l]
     float patchSize;     // (float)(int)(31*scale) (ORBextractor.cc:879)
 };
@@ -52,6 +53,7 @@ struct FramePlan {
     unsigned frameBytes, blurBytes, candWords, gathWords;
     int iniTh, minTh;
     int fpMode;
+    int blurTiles;      // total 128x32 tiles over all levels
     LevelPlan lv[kMaxLevels];
 };
 
