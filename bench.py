@@ -280,41 +280,63 @@ def run_ours(args, rank, world, local_rank):
 
 def run_e2e(ctx, args, world):
     """Same step through the reference-facing C ABI with HOST buffers: pinned frames H2D, keypoints + descriptors +
-    counts + matches D2H, every step, inside the timed region."""
-    torch, dist, orbx, ex = ctx["torch"], ctx["dist"], ctx["orbx"], ctx["ex"]
+    counts + matches D2H, every step, inside the timed region.  Two extractor handles each take half of the step's
+    frames through the enqueue-only entry points (orbx_extract_batch_async / orbx_match_batch_consecutive mode 2), so one
+    handle's PCIe copies overlap the other's kernels — the reference's own two-extractors-on-two-threads pattern
+    (Frame.cc:122-125).  Before a handle is given step i it is checked (orbx_check) for step i-1, i.e. the caller
+    holds complete results of the previous step, as a streaming consumer would."""
+    torch, dist, orbx = ctx["torch"], ctx["dist"], ctx["orbx"]
     F, cap = ctx["F"], ctx["cap"]
     h_img = torch.empty((F, H, W), dtype=torch.uint8).pin_memory()
     h_img.copy_(ctx["imgs"][0].cpu())
-    h_kps = torch.empty((F, cap, 7), dtype=torch.float32).pin_memory()
-    h_desc = torch.empty((F, cap, 32), dtype=torch.uint8).pin_memory()
-    h_n = torch.empty(F, dtype=torch.int32).pin_memory()
-    h_mono = torch.empty(F, dtype=torch.int32).pin_memory()
-    h_m = [torch.empty((max(F - 1, 1), cap), dtype=torch.int32).pin_memory() for _ in range(4)]
+    half = F // 2
+    # handle 0: frames [0, half); handle 1: frames [half-1, F) so that the pair (half-1, half) is matched too
+    parts = [(0, half), (half - 1, F - half + 1)] if F >= 4 else [(0, F)]
+    handles = [ctx["ex"]] + [orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=ctx["dev"].index) for _ in parts[1:]]
+    bufs = []
+    for lo, cnt in parts:
+        bufs.append(dict(kps=torch.empty((cnt, cap, 7), dtype=torch.float32).pin_memory(),
+                         desc=torch.empty((cnt, cap, 32), dtype=torch.uint8).pin_memory(),
+                         n=torch.empty(cnt, dtype=torch.int32).pin_memory(), mono=torch.empty(cnt, dtype=torch.int32).pin_memory(),
+                         m=[torch.empty((max(cnt - 1, 1), cap), dtype=torch.int32).pin_memory() for _ in range(4)]))
 
     def step():
-        ex.extract_batch_ptr(h_img.data_ptr(), F, W, H, LAP, h_kps.data_ptr(), h_desc.data_ptr(), cap, h_n.data_ptr(),
-                             h_mono.data_ptr())
-        if not args.skip_match:
-            orbx._check(orbx.lib().orbx_match_batch_consecutive(ex._h, *[m.data_ptr() for m in h_m], 1))
+        for ex, (lo, cnt), b in zip(handles, parts, bufs):
+            ex.check()  # results of this handle's previous step are complete from here on
+            ex.extract_batch_async_ptr(h_img[lo].data_ptr(), cnt, W, H, LAP, b["kps"].data_ptr(), b["desc"].data_ptr(), cap,
+                                       b["n"].data_ptr(), b["mono"].data_ptr())
+            if not args.skip_match:
+                ex.match_consecutive_async_ptr(*[m.data_ptr() for m in b["m"]])
 
-    for _ in range(2):
+    def drain():
+        for ex in handles:
+            ex.check()
+
+    for _ in range(3):
         step()
+    drain()
     ctx["barrier"]()
     steps = max(3, min(args.steps, 10))
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
-    ex.sync()
+    drain()
     dt = time.perf_counter() - t0
     if world > 1:
         t = torch.tensor([dt], dtype=torch.float64, device=ctx["dev"])
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
-    h2d = F * H * W
-    d2h = F * cap * (28 + 32) + 8 * F + (0 if args.skip_match else 4 * 4 * (F - 1) * cap)
-    assert int(h_n[0]) > 900, "e2e leg produced no keypoints"
+    nfr = sum(c for _, c in parts)
+    h2d = nfr * H * W
+    d2h = nfr * cap * (28 + 32) + 8 * nfr + (0 if args.skip_match else 4 * 4 * sum(c - 1 for _, c in parts) * cap)
+    assert all(int(b["n"][0]) > 900 and int(b["n"][-1]) > 900 for b in bufs), "e2e leg produced no keypoints"
+    if not args.skip_match:
+        assert int((bufs[-1]["m"][1][0, :900] < 64).sum()) > 300, "e2e leg produced no matches"
+    for ex in handles[1:]:
+        ex.close()
     return {"value": world * F * steps / dt, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "steps": steps, "api": "orbx_extract_batch + orbx_match_batch_consecutive (pinned host buffers)"}
+            "steps": steps, "handles": len(handles),
+            "api": "orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check on 2 handles (pinned host buffers)"}
 
 
 def run_match_cfg5(ctx, args, rank, world, local_rank):
@@ -380,6 +402,7 @@ def main():
     ap.add_argument("--db-rows", type=int, default=10_000_000)
     ap.add_argument("--skip-match", action="store_true")
     ap.add_argument("--skip-secondary", action="store_true", help="skip e2e / cfg5 / cpu_baseline legs (profiling runs)")
+    ap.add_argument("--only-match", action="store_true", help="development: run only the cfg5 matching leg and print it")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" and not args.skip_secondary else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -387,6 +410,22 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.only_match:
+        import torch
+        import torch.distributed as dist
+        from orb_slam3_ros2_b200 import orbx, synth
+        torch.cuda.set_device(local_rank)
+        dev = torch.device("cuda", local_rank)
+        if world > 1:
+            dist.init_process_group("nccl", device_id=dev)
+        ctx = dict(torch=torch, dist=dist, orbx=orbx, synth=synth, dev=dev,
+                   barrier=lambda: (dist.barrier() if world > 1 else None, torch.cuda.synchronize()))
+        m = run_match_cfg5(ctx, args, rank, world, local_rank)
+        if rank == 0:
+            print(json.dumps(m), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
         return
     ctx = run_ours(args, rank, world, local_rank)
     peak, peak_src = measured_peaks()

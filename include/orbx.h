@@ -94,6 +94,16 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, i
                        int cap_per_frame, int* n_out, int* mono_index);
 int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, int nframes, int w, int hgt, int stride,
                               size_t frame_stride, int lap0, int lap1);
+/* Asynchronous form of orbx_extract_batch: the H2D copy of the frames, the kernels and the D2H copies of the results
+ * are only ENQUEUED on the handle's stream (host buffers should be page-locked, and must stay untouched until
+ * orbx_sync / orbx_check returns).  cap_per_frame must be at least the extractor's capacity (sum over levels of
+ * N_l + 4).  Two handles driven this way overlap one handle's copies with the other's kernels, the way the reference
+ * runs its left / right extractors on two threads (Frame.cc:122-125).  orbx_check = orbx_sync + the device-side
+ * invariant flags (ORBX_ERR_CAPACITY if one tripped). */
+int orbx_extract_batch_async(orbx_handle h, const uint8_t* imgs, int nframes, int w, int hgt, int stride,
+                             size_t frame_stride, int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc,
+                             int cap_per_frame, int* n_out, int* mono_index);
+int orbx_check(orbx_handle h);
 /* Device-resident results of the last batch: keypoints/descriptors of frame f start at
  * d_kps + f*cap, d_desc + f*cap*32; d_n[f] keypoints are valid. */
 int orbx_batch_results(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc, const int** d_n,
@@ -133,7 +143,8 @@ int orbx_match_top2_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int6
                            int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream);
 
 /* Frame-to-frame top-2 over the last batch held by `h` (config 2): frame f's descriptors against frame
- * f+1's, f = 0..nframes-2.  Outputs (device or host, selected by `to_host`) are (nframes-1) x cap entries. */
+ * f+1's, f = 0..nframes-2.  Outputs are (nframes-1) x cap entries; to_host = 0: device pointers, results left on the
+ * stream; 1: host pointers, synchronous; 2: host pointers, copies only enqueued (see orbx_extract_batch_async). */
 int orbx_match_batch_consecutive(orbx_handle h, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
                                  int to_host);
 

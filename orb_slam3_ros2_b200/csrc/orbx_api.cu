@@ -237,6 +237,10 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
 
 static int checkDeviceFlags(orbx_extractor* h) {
     int flag = 0;
+    if (!h->mErr.p) {  // nothing has run on this handle yet
+        ORBX_CUDA(cudaStreamSynchronize(h->stream));
+        return ORBX_OK;
+    }
     ORBX_CUDA(cudaMemcpyAsync(&flag, h->mErr.p, 4, cudaMemcpyDeviceToHost, h->stream));
     ORBX_CUDA(cudaStreamSynchronize(h->stream));
     if (flag) {
@@ -331,12 +335,9 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, int nframes,
     return runPipeline(h, d_imgs, stride, frame_stride, nframes, lap0, lap1);
 }
 
-int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, int hgt, int stride, size_t frame_stride,
-                       int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* n_out,
-                       int* mono_index) {
-    if (!h || !imgs) return fail(ORBX_ERR_ARG, "null argument");
-    if (stride < w) return fail(ORBX_ERR_ARG, "stride < width");
-    DeviceGuard guard(h->device);
+// H2D of the frames + the pipeline, enqueued on the handle's stream (no host synchronisation)
+static int enqueueHostBatch(orbx_extractor* h, const uint8_t* imgs, int nframes, int w, int hgt, int stride,
+                            size_t frame_stride, int lap0, int lap1) {
     int rc = ensureCapacity(h, w, hgt, nframes);
     if (rc != ORBX_OK) return rc;
     const size_t frameBytes = (size_t)w * hgt;
@@ -349,7 +350,51 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, i
             ORBX_CUDA(cudaMemcpy2DAsync((uint8_t*)h->mImg.p + (size_t)f * frameBytes, w, imgs + (size_t)f * frame_stride,
                                         stride, w, hgt, cudaMemcpyHostToDevice, h->stream));
     }
-    rc = runPipeline(h, (const uint8_t*)h->mImg.p, w, frameBytes, nframes, lap0, lap1);
+    return runPipeline(h, (const uint8_t*)h->mImg.p, w, frameBytes, nframes, lap0, lap1);
+}
+
+// D2H of full per-frame slots (cap_per_frame >= the handle's capacity), enqueued
+static int enqueueResultCopies(orbx_extractor* h, int nframes, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* n_out,
+                               int* mono_index) {
+    const FramePlan& P = h->plan;
+    if (kps)
+        ORBX_CUDA(cudaMemcpy2DAsync(kps, (size_t)cap_per_frame * 28, h->buf.outKps, (size_t)P.outCap * 28,
+                                    (size_t)P.outCap * 28, nframes, cudaMemcpyDeviceToHost, h->stream));
+    if (desc)
+        ORBX_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap_per_frame * 32, h->buf.outDesc, (size_t)P.outCap * 32,
+                                    (size_t)P.outCap * 32, nframes, cudaMemcpyDeviceToHost, h->stream));
+    if (n_out) ORBX_CUDA(cudaMemcpyAsync(n_out, h->buf.outN, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (mono_index)
+        ORBX_CUDA(cudaMemcpyAsync(mono_index, h->buf.outMono, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
+    return ORBX_OK;
+}
+
+int orbx_extract_batch_async(orbx_handle h, const uint8_t* imgs, int nframes, int w, int hgt, int stride, size_t frame_stride,
+                             int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* n_out,
+                             int* mono_index) {
+    if (!h || !imgs) return fail(ORBX_ERR_ARG, "null argument");
+    if (stride < w) return fail(ORBX_ERR_ARG, "stride < width");
+    DeviceGuard guard(h->device);
+    int rc = enqueueHostBatch(h, imgs, nframes, w, hgt, stride, frame_stride, lap0, lap1);
+    if (rc != ORBX_OK) return rc;
+    if ((kps || desc) && cap_per_frame < h->plan.outCap)
+        return fail(ORBX_ERR_CAPACITY, "the asynchronous form needs cap_per_frame >= the extractor's capacity (sum of N_l + 4)");
+    return enqueueResultCopies(h, nframes, kps, desc, cap_per_frame, n_out, mono_index);
+}
+
+int orbx_check(orbx_handle h) {
+    if (!h) return fail(ORBX_ERR_ARG, "null handle");
+    DeviceGuard guard(h->device);
+    return checkDeviceFlags(h);
+}
+
+int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, int hgt, int stride, size_t frame_stride,
+                       int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* n_out,
+                       int* mono_index) {
+    if (!h || !imgs) return fail(ORBX_ERR_ARG, "null argument");
+    if (stride < w) return fail(ORBX_ERR_ARG, "stride < width");
+    DeviceGuard guard(h->device);
+    int rc = enqueueHostBatch(h, imgs, nframes, w, hgt, stride, frame_stride, lap0, lap1);
     if (rc != ORBX_OK) return rc;
     const FramePlan& P = h->plan;
     if ((kps || desc) && cap_per_frame < P.outCap) {
@@ -368,17 +413,11 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* imgs, int nframes, int w, i
         if (desc)
             ORBX_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap_per_frame * 32, h->buf.outDesc, (size_t)P.outCap * 32,
                                         (size_t)cap_per_frame * 32, nframes, cudaMemcpyDeviceToHost, h->stream));
+        rc = enqueueResultCopies(h, nframes, nullptr, nullptr, cap_per_frame, n_out, mono_index);
     } else {
-        if (kps)
-            ORBX_CUDA(cudaMemcpy2DAsync(kps, (size_t)cap_per_frame * 28, h->buf.outKps, (size_t)P.outCap * 28,
-                                        (size_t)P.outCap * 28, nframes, cudaMemcpyDeviceToHost, h->stream));
-        if (desc)
-            ORBX_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap_per_frame * 32, h->buf.outDesc, (size_t)P.outCap * 32,
-                                        (size_t)P.outCap * 32, nframes, cudaMemcpyDeviceToHost, h->stream));
+        rc = enqueueResultCopies(h, nframes, kps, desc, cap_per_frame, n_out, mono_index);
     }
-    if (n_out) ORBX_CUDA(cudaMemcpyAsync(n_out, h->buf.outN, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
-    if (mono_index)
-        ORBX_CUDA(cudaMemcpyAsync(mono_index, h->buf.outMono, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (rc != ORBX_OK) return rc;
     return checkDeviceFlags(h);
 }
 
@@ -714,7 +753,7 @@ int orbx_match_batch_consecutive(orbx_handle h, int32_t* idx1, int32_t* d1, int3
         ORBX_CUDA(cudaMemcpyAsync(d1, o2, n * 4, cudaMemcpyDeviceToHost, h->stream));
         ORBX_CUDA(cudaMemcpyAsync(idx2, o3, n * 4, cudaMemcpyDeviceToHost, h->stream));
         ORBX_CUDA(cudaMemcpyAsync(d2, o4, n * 4, cudaMemcpyDeviceToHost, h->stream));
-        ORBX_CUDA(cudaStreamSynchronize(h->stream));
+        if (to_host != 2) ORBX_CUDA(cudaStreamSynchronize(h->stream));  // 2 = enqueue only (orbx_sync / orbx_check later)
     }
     return ORBX_OK;
 }

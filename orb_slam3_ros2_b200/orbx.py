@@ -56,6 +56,9 @@ SYMBOLS = {
     "orbx_get_pyramid": (C.c_int, [_vp, C.c_int, C.c_int, _u8p, _i32p, _i32p]),
     "orbx_extract_batch": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, _vp, _vp,
                                      C.c_int, _vp, _vp]),
+    "orbx_extract_batch_async": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, _vp, _vp,
+                                           C.c_int, _vp, _vp]),
+    "orbx_check": (C.c_int, [_vp]),
     "orbx_extract_batch_device": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int]),
     "orbx_batch_results": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i32p]),
     "orbx_batch_download": (C.c_int, [_vp, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
@@ -217,6 +220,19 @@ class ORBextractor:
         _check(lib().orbx_extract_batch(self._h, host_ptr, F, w, h, w, w * h, vLappingArea[0], vLappingArea[1], kps_ptr,
                                         desc_ptr, cap, n_ptr, mono_ptr))
         self._frames = F
+
+    def extract_batch_async_ptr(self, host_ptr, F, w, h, vLappingArea, kps_ptr, desc_ptr, cap, n_ptr, mono_ptr):
+        """Enqueue-only form (pinned host buffers): H2D + kernels + D2H on this handle's stream; call check() later."""
+        _check(lib().orbx_extract_batch_async(self._h, host_ptr, F, w, h, w, w * h, vLappingArea[0], vLappingArea[1],
+                                              kps_ptr, desc_ptr, cap, n_ptr, mono_ptr))
+        self._frames = F
+
+    def match_consecutive_async_ptr(self, idx1, d1, idx2, d2):
+        _check(lib().orbx_match_batch_consecutive(self._h, idx1, d1, idx2, d2, 2))
+
+    def check(self):
+        """Wait for the handle's stream and raise if a device-side capacity invariant tripped."""
+        _check(lib().orbx_check(self._h))
 
     def extract_batch_device(self, dev_ptr, F, w, h, vLappingArea=(0, 1000), stride=None, frame_stride=None):
         _check(lib().orbx_extract_batch_device(self._h, dev_ptr, F, w, h, stride or w, frame_stride or w * h,
