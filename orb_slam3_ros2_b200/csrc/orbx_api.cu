@@ -64,7 +64,8 @@ struct orbx_extractor {
     std::vector<float> sf, isf, sig2, isig2;
     std::vector<int> nPerLevel;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[7] = {};
+    cudaStream_t aux = nullptr;  // blur runs here, beside FAST + quadtree on `stream` (both only need the pyramid)
+    cudaEvent_t ev[9] = {};      // 0..5 stage boundaries on `stream`; 6 pyramid done -> aux, 7/8 blur begin/end on aux
     // plan + buffers of the current (W, H, capacity F)
     FramePlan plan{};
     bool havePlan = false;
@@ -219,14 +220,21 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
     const FramePlan& P = h->plan;
     const Buffers& B = h->buf;
     cudaStream_t s = h->stream;
+    cudaStream_t x = h->aux;
     cudaEventRecord(h->ev[0], s);
     launchPyramid(P, B, dImgs, stride, frameStride, F, s);
     cudaEventRecord(h->ev[1], s);
     launchFast(P, B, F, s);
     cudaEventRecord(h->ev[2], s);
+    // fork: the quadtree is latency-bound (one CTA per (frame, level), serial rounds with barriers, ~30 % issue rate), the
+    // blur is issue-bound and independent of it: run them side by side so the blur fills the quadtree's bubbles
+    cudaStreamWaitEvent(x, h->ev[2], 0);
+    cudaEventRecord(h->ev[7], x);
+    launchBlur(P, B, F, x);
+    cudaEventRecord(h->ev[8], x);
     launchQuadtree(P, B, F, s);
     cudaEventRecord(h->ev[3], s);
-    launchBlur(P, B, F, s);
+    cudaStreamWaitEvent(s, h->ev[8], 0);  // join
     cudaEventRecord(h->ev[4], s);
     launchDescribe(P, B, F, lap0, lap1, s);
     cudaEventRecord(h->ev[5], s);
@@ -289,7 +297,8 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     h->scaleFactorD = (double)params->scale_factor;
     initTables(h);
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
-    for (int i = 0; i < 7 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
+    for (int i = 0; i < 9 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e != cudaSuccess) {
         delete h;
         return fail(ORBX_ERR_CUDA, std::string("stream/event creation: ") + cudaGetErrorString(e));
@@ -307,8 +316,9 @@ void orbx_destroy(orbx_handle h) {
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
                      &h->mMatch};
     for (DevMem* m : all) m->release();
-    for (int i = 0; i < 7; ++i)
+    for (int i = 0; i < 9; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->aux) cudaStreamDestroy(h->aux);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -457,7 +467,15 @@ int orbx_last_timing(orbx_handle h, float* total_ms, float stage_ms[5]) {
     ORBX_CUDA(cudaEventSynchronize(h->ev[5]));
     if (total_ms) ORBX_CUDA(cudaEventElapsedTime(total_ms, h->ev[0], h->ev[5]));
     if (stage_ms)
-        for (int i = 0; i < 5; ++i) ORBX_CUDA(cudaEventElapsedTime(&stage_ms[i], h->ev[i], h->ev[i + 1]));
+    {
+        // pyramid, fast, quadtree on the main stream; blur from its own events on the aux stream (it overlaps fast and
+        // quadtree, so the stage times no longer add up to the total); describe after the join
+        ORBX_CUDA(cudaEventElapsedTime(&stage_ms[0], h->ev[0], h->ev[1]));
+        ORBX_CUDA(cudaEventElapsedTime(&stage_ms[1], h->ev[1], h->ev[2]));
+        ORBX_CUDA(cudaEventElapsedTime(&stage_ms[2], h->ev[2], h->ev[3]));
+        ORBX_CUDA(cudaEventElapsedTime(&stage_ms[3], h->ev[7], h->ev[8]));
+        ORBX_CUDA(cudaEventElapsedTime(&stage_ms[4], h->ev[4], h->ev[5]));
+    }
     return ORBX_OK;
 }
 
