@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FrameP
 // the 128-B-pitched plane has the same misalignment, so one funnel shift amount serves the whole patch); each word
 // goes through two byte dot products against per-(row, word) coefficient words — u (signed, 0 outside the disc) for
 // m10 and the 0/1 disc mask for the row sum of m01.  248 words / 32 lanes = 8 per lane, all loads independent.
+constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitch = 64;
 __device__ uint2 gIcCoef[248];   // x: s8 u-coefficients, y: u8 disc mask, entry = row * 8 + word
 __device__ float4 gPatternF[256];
 
@@ -143,7 +144,10 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
     return d;
 }
 
-__global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
+#ifndef ORBX_DESC_MINB
+#define ORBX_DESC_MINB 4
+#endif
+__global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
                                                       const uint8_t* __restrict__ blur, const LevelKp* __restrict__ lkp,
                                                       const int* __restrict__ lkpCnt, const int* __restrict__ slot,
                                                       float* __restrict__ outKps, uint8_t* __restrict__ outDesc) {
@@ -164,6 +168,24 @@ __global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ Fr
     const LevelKp kp = lkp[(size_t)f * P.lkpTotal + j];
     const int s = slot[(size_t)f * P.lkpTotal + j];
     if (s >= P.outCap) return;
+
+    // ---- the blurred 37 x 37 patch the 512 samples can touch (|offset| <= round(13 * sqrt 2) = 18) is fetched now, as
+    // 37 rows x 4 aligned 16-byte chunks, together with the orientation patch: one round trip to memory instead of two,
+    // and the samples then come from shared memory.  (Sampling the plane directly costs one L1 tag lookup per distinct
+    // 128-B line per request — ~25 per 32-lane byte gather — which made the L1 pipeline the kernel's bottleneck.)
+    __shared__ __align__(16) uint8_t sPatch[8][kPatchRows * kPatchPitch];
+    uint8_t* patch = sPatch[threadIdx.x >> 5];
+    const int bx0 = (kp.x - kPatchR) & ~15;   // blurred-plane column of the patch's first byte
+    uint4 pv[5];
+    {
+        const uint8_t* src = blur + (size_t)f * P.blurBytes + L.blurOff + (size_t)(kp.y - kPatchR) * L.bpitch + bx0;
+#pragma unroll
+        for (int it = 0; it < 5; ++it) {
+            const int item = it * 32 + lane;  // row = item >> 2, chunk = item & 3
+            pv[it] = item < kPatchRows * 4 ? __ldg(reinterpret_cast<const uint4*>(src + (size_t)((item >> 2) * L.bpitch)) + (item & 3))
+                                           : make_uint4(0, 0, 0, 0);
+        }
+    }
 
     // ---- IC_Angle (ORBextractor.cc:76-103) -----------------------------------------------------------------------
     int m10 = 0, m01 = 0;
@@ -201,8 +223,14 @@ __global__ void __launch_bounds__(256) describeKernel(const __grid_constant__ Fr
     const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
     float a, b;
     glibcSincosf(__fmul_rn(angle, factorPI), &b, &a);
-    const uint8_t* center = blur + (size_t)f * P.blurBytes + L.blurOff + (size_t)kp.y * L.bpitch + kp.x;
-    const int step = L.bpitch;
+#pragma unroll
+    for (int it = 0; it < 5; ++it) {
+        const int item = it * 32 + lane;
+        if (item < kPatchRows * 4) reinterpret_cast<uint4*>(patch)[item] = pv[it];
+    }
+    __syncwarp();
+    const uint8_t* center = patch + kPatchR * kPatchPitch + (kp.x - bx0);
+    constexpr int step = kPatchPitch;
     const bool strict = P.fpMode == 0;
     uint32_t t0[8], t1[8];
 #pragma unroll
