@@ -9,6 +9,8 @@
 // operations (no FMA); cos/sin are glibc's sincosf algorithm (double range reduction + polynomials, each
 // operation rounded once); the sample rotation is two rounded products and one rounded sum in STRICT mode, or
 // fmaf(x, b, y*a) in NATIVE mode (what gcc -O3 -march=native emits for the reference).  cvRound = rint.
+#include <algorithm>
+
 #include "orbx_internal.cuh"
 
 namespace orbx {
@@ -79,7 +81,7 @@ __device__ __forceinline__ void glibcSincosf(float y, float* sinp, float* cosp) 
 // The reference walks levels 0..n-1 and, inside a level, the quadtree's list order; a keypoint whose SCALED x lies
 // in [lap0, lap1] is written from the back (stereoIndex--), the others from the front (monoIndex++).
 __global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FramePlan P, const LevelKp* __restrict__ lkp,
-                                                  const int* __restrict__ lkpCnt, int* __restrict__ slot,
+                                                  const int* __restrict__ lkpCnt, LevelKp* __restrict__ sorted,
                                                   int* __restrict__ outN, int* __restrict__ outMono, int lap0, int lap1,
                                                   int* __restrict__ errFlag) {
     __shared__ int sBase[kMaxLevels + 1];
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FrameP
     __syncthreads();
     const int total = sBase[P.nlevels];
     const LevelKp* kp = lkp + (size_t)f * P.lkpTotal;
-    int* sl = slot + (size_t)f * P.lkpTotal;
+    LevelKp* sl = sorted + (size_t)f * P.outCap;  // keypoints in operator()'s output order
     for (int start = 0; start < total; start += 256) {
         const int j = start + tid;
         int inside = 0, l = 0, idx = 0;
@@ -117,7 +119,10 @@ __global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FrameP
         int base = sCarry;
         for (int w = 0; w < (tid >> 5); ++w) base += sWarp[w];
         const int insideBefore = base + incl - inside;
-        if (j < total) sl[idx] = inside ? (total - 1 - insideBefore) : (j - insideBefore);
+        if (j < total) {
+            const int dst = inside ? (total - 1 - insideBefore) : (j - insideBefore);
+            if (dst < P.outCap) sl[dst] = kp[idx];
+        }
         __syncthreads();
         if (tid == 255) sCarry = base + incl;
         __syncthreads();
@@ -148,33 +153,45 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
 #define ORBX_DESC_MINB 4
 #endif
 __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
-                                                      const uint8_t* __restrict__ blur, const LevelKp* __restrict__ lkp,
-                                                      const int* __restrict__ lkpCnt, const int* __restrict__ slot,
-                                                      float* __restrict__ outKps, uint8_t* __restrict__ outDesc) {
-    const int f = blockIdx.y;
+                                                      const uint8_t* __restrict__ blur, const LevelKp* __restrict__ sorted,
+                                                      const int* __restrict__ outN, float* __restrict__ outKps,
+                                                      uint8_t* __restrict__ outDesc, int F) {
+    // Persistent CTAs: the pattern and the disc coefficients are copied to shared memory once, then every warp walks
+    // output slots (frame, s) with a grid-wide stride, fetching the NEXT slot's record while it works on the current one.
+    __shared__ float4 sPat[256];
+    __shared__ uint2 sCoef[248];
+    __shared__ __align__(16) uint8_t sPatch[8][kPatchRows * kPatchPitch];
+    sPat[threadIdx.x] = gPatternF[threadIdx.x];
+    if (threadIdx.x < 248) sCoef[threadIdx.x] = gIcCoef[threadIdx.x];
+    __syncthreads();
     const int lane = threadIdx.x & 31;
-    // blockIdx.x enumerates 8-keypoint chunks level by level (uniform per block)
-    int chunk = blockIdx.x, l = 0;
-    for (; l < P.nlevels; ++l) {
-        const int nch = (P.lv[l].lkpCap + 7) >> 3;
-        if (chunk < nch) break;
-        chunk -= nch;
+    uint8_t* patch = sPatch[threadIdx.x >> 5];
+    const int total = F * P.outCap, stride = gridDim.x * 8;
+    int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+    int nNext = 0;
+    LevelKp kpNext = {0, 0, 0, 0};
+    if (w < total) {
+        const int f0 = w / P.outCap;
+        nNext = __ldg(outN + f0);
+        kpNext = sorted[w];
     }
-    if (l >= P.nlevels) return;
+    for (; w < total; w += stride) {
+    const int f = w / P.outCap, s = w - f * P.outCap;
+    const int n = nNext;
+    const LevelKp kp = kpNext;
+    if (w + stride < total) {  // prefetch the next slot's record
+        nNext = __ldg(outN + (w + stride) / P.outCap);
+        kpNext = sorted[w + stride];
+    }
+    if (s >= n) continue;
+    const int l = kp.level;
     const LevelPlan& L = P.lv[l];
-    const int i = chunk * 8 + (threadIdx.x >> 5);
-    if (i >= lkpCnt[(size_t)f * P.nlevels + l]) return;
-    const int j = L.lkpBase + i;
-    const LevelKp kp = lkp[(size_t)f * P.lkpTotal + j];
-    const int s = slot[(size_t)f * P.lkpTotal + j];
-    if (s >= P.outCap) return;
+    __syncwarp();  // the previous iteration's samples are done with `patch`
 
     // ---- the blurred 37 x 37 patch the 512 samples can touch (|offset| <= round(13 * sqrt 2) = 18) is fetched now, as
     // 37 rows x 4 aligned 16-byte chunks, together with the orientation patch: one round trip to memory instead of two,
     // and the samples then come from shared memory.  (Sampling the plane directly costs one L1 tag lookup per distinct
     // 128-B line per request — ~25 per 32-lane byte gather — which made the L1 pipeline the kernel's bottleneck.)
-    __shared__ __align__(16) uint8_t sPatch[8][kPatchRows * kPatchPitch];
-    uint8_t* patch = sPatch[threadIdx.x >> 5];
     const int bx0 = (kp.x - kPatchR) & ~15;   // blurred-plane column of the patch's first byte
     uint4 pv[5];
     {
@@ -206,7 +223,7 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int item = it * 32 + lane;
-            const uint2 cf = gIcCoef[item < 248 ? item : 0];
+            const uint2 cf = sCoef[item < 248 ? item : 0];
             const uint32_t w = __funnelshift_r(lo[it], hi[it], sh);
             m10 = dp4a_us(w, cf.x, m10);
             m01 += ((item >> 3) - kHalfPatch) * (int)__dp4a(w, cf.y, 0u);
@@ -235,7 +252,7 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
     uint32_t t0[8], t1[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const float4 pt = gPatternF[lane * 8 + k];
+        const float4 pt = sPat[lane * 8 + k];
         int r0, c0, r1, c1;
         if (strict) {
             r0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
@@ -282,6 +299,7 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
         }
         outKps[((size_t)f * P.outCap + s) * 7 + lane] = v;
     }
+    }  // persistent loop
 }
 
 }  // namespace
@@ -312,12 +330,15 @@ void uploadDescribeTables() {
 }
 
 void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s) {
-    slotKernel<<<F, 256, 0, s>>>(P, B.lkp, B.lkpCnt, B.slot, B.outN, B.outMono, lap0, lap1, B.errFlag);
+    slotKernel<<<F, 256, 0, s>>>(P, B.lkp, B.lkpCnt, B.sorted, B.outN, B.outMono, lap0, lap1, B.errFlag);
     countLaunch();
-    int chunks = 0;
-    for (int l = 0; l < P.nlevels; ++l) chunks += (P.lv[l].lkpCap + 7) / 8;
-    describeKernel<<<dim3(chunks, F), 256, 0, s>>>(P, B.pyr, B.blur, B.lkp, B.lkpCnt, B.slot,
-                                                   reinterpret_cast<float*>(B.outKps), B.outDesc);
+    int dev = 0, sms = 148, perSm = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, describeKernel, 256, 0);
+    const long long want = ((long long)F * P.outCap + 7) / 8;
+    const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
+    describeKernel<<<grid, 256, 0, s>>>(P, B.pyr, B.blur, B.sorted, B.outN, reinterpret_cast<float*>(B.outKps), B.outDesc, F);
     countLaunch();
 }
 

@@ -197,7 +197,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         ORBX_CUDA(h->mNid.reserve(std::max<size_t>(f * P.gathWords * 2, 16)));
         ORBX_CUDA(h->mLkp.reserve(f * P.lkpTotal * sizeof(LevelKp)));
         ORBX_CUDA(h->mLkpCnt.reserve(f * P.nlevels * 4));
-        ORBX_CUDA(h->mSlot.reserve(f * P.lkpTotal * 4));
+        ORBX_CUDA(h->mSlot.reserve(f * P.outCap * sizeof(LevelKp)));
         ORBX_CUDA(h->mOutK.reserve(f * P.outCap * 28));
         ORBX_CUDA(h->mOutD.reserve(f * P.outCap * 32));
         ORBX_CUDA(h->mOutN.reserve(f * 4));
@@ -209,7 +209,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     Buffers& B = h->buf;
     B.img = (uint8_t*)h->mImg.p; B.pyr = (uint8_t*)h->mPyr.p; B.blur = (uint8_t*)h->mBlur.p;
     B.cand = (uint32_t*)h->mCand.p; B.cellCnt = (int*)h->mCellCnt.p; B.gath = (uint32_t*)h->mGath.p;
-    B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.slot = (int*)h->mSlot.p;
+    B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.sorted = (LevelKp*)h->mSlot.p;
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
     B.tab = (int16_t*)h->mTab.p; B.errFlag = (int*)h->mErr.p;
     return ORBX_OK;

@@ -74,7 +74,7 @@ struct Buffers {
     uint16_t* nid;       // node id per gathered candidate, F x gathWords
     LevelKp* lkp;        // F x lkpTotal
     int* lkpCnt;         // F x nlevels
-    int* slot;           // F x lkpTotal : final output slot of each level keypoint
+    LevelKp* sorted;     // F x outCap : the kept keypoints in operator()'s output order (slotKernel)
     void* outKps;        // F x outCap x 28 B
     uint8_t* outDesc;    // F x outCap x 32 B
     int* outN;           // F
