@@ -77,6 +77,17 @@ int orbx_get_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2
 int orbx_extract(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int lap0, int lap1,
                  orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index);
 
+/* Input staging fused ahead of the pyramid: System::TrackMonocular's cv::resize(im, resized, newImSize) (System.cc:420-425)
+ * followed by Tracking::GrabImageMonocular's cvtColor(... -> GRAY) (Tracking.cc:1569-1582), in the reference's order
+ * (resize on the interleaved colour image, then grey), then operator().  img: host, `channels` (1, 3 or 4) interleaved
+ * bytes per pixel, `stride` bytes per row; rgb = the reference's mbRGB (1: RGB/RGBA order, 0: BGR/BGRA);
+ * new_w/new_h = Settings::newImSize() or 0/0 for no resize.  The other arguments are orbx_extract's. */
+int orbx_extract_color(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int channels, int rgb, int new_w,
+                       int new_h, int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
+                       int* mono_index);
+/* The grey frame the last orbx_extract_color handed to the extractor (w x h compact; `out` may be NULL to query sizes). */
+int orbx_get_staged_gray(orbx_handle h, uint8_t* out, int* w, int* hgt);
+
 /* mvImagePyramid[level] of the last orbx_extract / batch frame `frame` (ORBextractor.cc:1170-1195): the
  * level is a ROI at (19,19) of a padded (w+38) x (h+38) plane.  `out` (host, may be NULL to query the
  * size) receives the padded plane compactly, (h+38) rows of (w+38) bytes. */
@@ -155,6 +166,61 @@ int orbx_match_batch_consecutive(orbx_handle h, int32_t* idx1, int32_t* d1, int3
 int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, int nl, const orbx_keypoint* kps_r,
                              const uint8_t* desc_r, int nr, const float* scale_factors, int nlevels, int n_rows,
                              float max_d, int32_t* best_idx, int32_t* best_dist, int device);
+
+/* ---- accept rules on top-2 results (ORBmatcher constants TH_LOW = 50, TH_HIGH = 100: ORBmatcher.cc:35-36) ------
+ * One flag per query from (d1, d2), the float comparisons written exactly as the reference writes them.  A missing
+ * second candidate is d2 = 256, the reference's initial bestDist2 (ORBmatcher.cc:83, :271, :669). */
+typedef enum orbx_accept_rule {
+    ORBX_ACCEPT_PROJ_MAP = 0,   /* SearchByProjection(F, map points), ORBmatcher.cc:123-128: d1 <= TH_HIGH and
+                                   (level1 != level2 or (float)d1 <= nnratio * d2); levels NULL = always equal */
+    ORBX_ACCEPT_BOW_KF_F = 1,   /* SearchByBoW(KF, F), :327-329: d1 <= TH_LOW and (float)d1 < nnratio * (float)d2 */
+    ORBX_ACCEPT_INIT = 2,       /* SearchForInitialization, :697-699: d1 <= TH_LOW and d1 < (float)d2 * nnratio */
+    ORBX_ACCEPT_BOW_KF_KF = 3,  /* SearchByBoW(KF, KF), :848-850: d1 < TH_LOW (strict) and (float)d1 < nnratio * (float)d2 */
+    ORBX_ACCEPT_BEST_HIGH = 4,  /* SearchByProjection(frame, frame), :1767: d1 <= TH_HIGH, best only */
+    ORBX_ACCEPT_BEST_LOW = 5,   /* Fuse / SearchBySim3 style, :1312, :1437: d1 <= TH_LOW, best only */
+    ORBX_ACCEPT_KNN_RATIO = 6   /* fisheye stereo on knnMatch results, Frame.cc:1149: two results and
+                                   (double)d1 < (double)d2 * 0.7 (the literal is a double; nnratio is ignored) */
+} orbx_accept_rule;
+/* d1, d2: n distances; idx2: second indices (only ORBX_ACCEPT_KNN_RATIO reads it: < 0 = fewer than two results; may be
+ * NULL = always two); level1/level2: octaves of the best / second candidate (PROJ_MAP only, may be NULL).
+ * accept: n bytes, 1 = accepted.  Host pointers; the _device form takes device pointers and a cudaStream_t. */
+int orbx_accept_top2(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2,
+                     const int32_t* level1, const int32_t* level2, int n, uint8_t* accept, int device);
+int orbx_accept_top2_device(int rule, float nnratio, const int32_t* d_d1, const int32_t* d_d2, const int64_t* d_idx2,
+                            const int32_t* d_level1, const int32_t* d_level2, int n, uint8_t* d_accept, void* stream);
+
+/* ---- guided search: Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea + the best/second loop ---------------
+ * The inner loop of ORBmatcher::SearchByProjection (frame to frame, ORBmatcher.cc:1676-1887), SearchForInitialization
+ * (:648-763) and SearchByProjection(F, map points) (:45-138): for every query (u, v, radius, [min_level, max_level],
+ * descriptor) the candidates are the target keypoints GetFeaturesInArea returns (Frame.cc:657-723: grid cells
+ * ix outer / iy inner, insertion order inside a cell, octave filter, |dx| < r and |dy| < r), visited in that order with
+ * strict-< best/second updates.  The grid is the reference's 64 x 48 (Frame.h:44-45) over [min_x, max_x) x
+ * [min_y, max_y) (Frame::ComputeImageBounds), cell of a keypoint = round((x - min) * inv) (Frame::PosInGrid,
+ * Frame.cc:725-736).  Outputs per query: idx1/idx2 = target keypoint indices (-1 = none), d1/d2 (256 = none),
+ * lvl1/lvl2 = octaves of the two (may be NULL).  max_level < 0 = no upper bound, as in the reference.
+ * Two host-state filters of the reference loops are optional inputs: skip_t[i] != 0 drops target i (a map point with
+ * observations is already attached, ORBmatcher.cc:87-89, :1746-1748), and with u_right_t != NULL a target whose
+ * u_right_t[i] > 0 is dropped when fabs(query.ur - u_right_t[i]) > query.r (:91-96, :1750-1756). */
+typedef struct orbx_grid_query {
+    float u, v, r;
+    int32_t min_level, max_level;
+    float ur; /* projected right-image coordinate; only read when u_right_t != NULL */
+} orbx_grid_query;
+int orbx_search_grid_top2(const orbx_keypoint* kps_t, const uint8_t* desc_t, int nt, float min_x, float max_x, float min_y,
+                          float max_y, const uint8_t* skip_t, const float* u_right_t, const orbx_grid_query* queries,
+                          const uint8_t* desc_q, int nq, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
+                          int32_t* lvl1, int32_t* lvl2, int device);
+
+/* ---- Frame::ComputeStereoMatches, whole function (Frame.cc:811-980) -------------------------------------------
+ * After the banded Hamming stage (orbx_match_stereo_banded) the reference refines every match with best < 75
+ * ((TH_HIGH + TH_LOW) / 2) by an 11 x 11 L1 patch correlation over +-5 px on pyramid level kpL.octave of the two
+ * extractors (:896-935), fits a parabola (:937-949), converts to disparity / depth (:951-966) and finally removes
+ * matches whose correlation distance is >= 1.5 * 1.4 * median (:969-980).  `left` / `right` are the two extractor
+ * handles whose LAST single-frame extraction produced kps_l / kps_r (their device-resident pyramids are read in place:
+ * no mvImagePyramid download).  bf = mbf, b = mb.  u_right / depth: nl floats, -1 where unmatched (:813-814). */
+int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, const orbx_keypoint* kps_l,
+                                const uint8_t* desc_l, int nl, const orbx_keypoint* kps_r, const uint8_t* desc_r, int nr,
+                                float bf, float b, float* u_right, float* depth);
 
 /* Measured sustained 32-bit POPC rate of the device in giga-POPC/s (8 independent XOR+POPC chains per thread):
  * the denominator of the matcher's roofline, pairs/s = POPC/s / 8. */

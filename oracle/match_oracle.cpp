@@ -1,0 +1,242 @@
+// match_oracle.cpp — CPU restatement (TEST INFRASTRUCTURE, never on the product path) of the matcher-side rows that
+// sit next to the extractor: the accept rules of ORBmatcher, the guided search built on Frame::GetFeaturesInArea, and
+// the whole of Frame::ComputeStereoMatches.  The reference's ORBmatcher.cc / Frame.cc cannot be compiled here (they
+// pull Eigen, Sophus, DBoW2, g2o, KeyFrame, MapPoint), so these functions follow the cited lines statement by
+// statement.  PARITY UNPINNED for these rows: the reference holds no tests or golden vectors for them.
+// Citations are file:line under /root/reference/ORB_SLAM3/.
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <utility>
+#include <vector>
+
+extern "C" int orbo_hamming(const uint8_t* a, const uint8_t* b);
+
+namespace {
+struct Kp {  // cv::KeyPoint, 28 bytes
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+};
+struct GridQuery {
+    float u, v, r;
+    int32_t minLevel, maxLevel;
+    float ur;
+};
+constexpr int TH_HIGH = 100, TH_LOW = 50;         // src/ORBmatcher.cc:35-36
+constexpr int GRID_ROWS = 48, GRID_COLS = 64;     // include/Frame.h:44-45
+}  // namespace
+
+extern "C" {
+
+// rules: see include/orbx.h (orbx_accept_rule); each line is the reference's own condition
+void orbo_accept_top2(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2,
+                      const int32_t* level1, const int32_t* level2, int n, uint8_t* accept) {
+    for (int i = 0; i < n; ++i) {
+        const int bestDist = d1[i], bestDist2 = d2[i];
+        bool ok = false;
+        switch (rule) {
+            case 0: {  // src/ORBmatcher.cc:123-128
+                const int bestLevel = level1 ? level1[i] : 0, bestLevel2 = level2 ? level2[i] : 0;
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) break;
+                    if (bestLevel != bestLevel2 || bestDist <= nnratio * bestDist2) ok = true;
+                }
+                break;
+            }
+            case 1:  // :327-329
+                if (bestDist <= TH_LOW) ok = static_cast<float>(bestDist) < nnratio * static_cast<float>(bestDist2);
+                break;
+            case 2:  // :697-699
+                if (bestDist <= TH_LOW) ok = bestDist < (float)bestDist2 * nnratio;
+                break;
+            case 3:  // :848-850
+                if (bestDist < TH_LOW) ok = static_cast<float>(bestDist) < nnratio * static_cast<float>(bestDist2);
+                break;
+            case 4: ok = bestDist <= TH_HIGH; break;  // :1767
+            case 5: ok = bestDist <= TH_LOW; break;   // :1312, :1437
+            case 6: {                                 // src/Frame.cc:1149 (DMatch::distance is float, 0.7 a double)
+                const float f1 = (float)bestDist, f2 = (float)bestDist2;
+                ok = (!idx2 || idx2[i] >= 0) && f1 < f2 * 0.7;
+                break;
+            }
+        }
+        accept[i] = ok ? 1 : 0;
+    }
+}
+
+// Frame::AssignFeaturesToGrid (src/Frame.cc:385-416), Frame::PosInGrid (:725-736), Frame::GetFeaturesInArea
+// (:657-723) and the best/second loop of ORBmatcher::SearchByProjection (src/ORBmatcher.cc:75-117; the frame-to-frame
+// and initialization variants :1740-1765, :669-695 visit the same list with the same strict-< updates).
+void orbo_search_grid_top2(const void* kpsT_, const uint8_t* descT, int nt, float mnMinX, float mnMaxX, float mnMinY,
+                           float mnMaxY, const uint8_t* skipT, const float* uRightT, const void* queries_,
+                           const uint8_t* descQ, int nq, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
+                           int32_t* lvl1, int32_t* lvl2) {
+    const Kp* kt = static_cast<const Kp*>(kpsT_);
+    const GridQuery* qs = static_cast<const GridQuery*>(queries_);
+    const float mfGridElementWidthInv = static_cast<float>(GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);  // :251
+    const float mfGridElementHeightInv = static_cast<float>(GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+    std::vector<std::vector<int>> grid((size_t)GRID_COLS * GRID_ROWS);
+    for (int i = 0; i < nt; ++i) {
+        const int posX = (int)std::round((kt[i].x - mnMinX) * mfGridElementWidthInv);
+        const int posY = (int)std::round((kt[i].y - mnMinY) * mfGridElementHeightInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        grid[(size_t)posX * GRID_ROWS + posY].push_back(i);
+    }
+    for (int q = 0; q < nq; ++q) {
+        const float x = qs[q].u, y = qs[q].v, r = qs[q].r;
+        const int minLevel = qs[q].minLevel, maxLevel = qs[q].maxLevel;
+        int bestDist = 256, bestDist2 = 256, bestIdx = -1, bestIdx2 = -1, bestLevel = -1, bestLevel2 = -1;
+        auto done = [&]() {
+            idx1[q] = bestIdx; d1[q] = bestDist; idx2[q] = bestIdx2; d2[q] = bestDist2;
+            if (lvl1) lvl1[q] = bestLevel;
+            if (lvl2) lvl2[q] = bestLevel2;
+        };
+        const float factorX = r, factorY = r;
+        const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * mfGridElementWidthInv));
+        if (nMinCellX >= GRID_COLS) { done(); continue; }
+        const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * mfGridElementWidthInv));
+        if (nMaxCellX < 0) { done(); continue; }
+        const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * mfGridElementHeightInv));
+        if (nMinCellY >= GRID_ROWS) { done(); continue; }
+        const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * mfGridElementHeightInv));
+        if (nMaxCellY < 0) { done(); continue; }
+        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+        for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+            for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+                for (int idx : grid[(size_t)ix * GRID_ROWS + iy]) {
+                    const Kp& kpUn = kt[idx];
+                    if (bCheckLevels) {
+                        if (kpUn.octave < minLevel) continue;
+                        if (maxLevel >= 0)
+                            if (kpUn.octave > maxLevel) continue;
+                    }
+                    const float distx = kpUn.x - x, disty = kpUn.y - y;
+                    if (!(std::fabs(distx) < factorX && std::fabs(disty) < factorY)) continue;
+                    // ---- the matcher's loop body ----
+                    if (skipT && skipT[idx]) continue;  // src/ORBmatcher.cc:87-89
+                    if (uRightT && uRightT[idx] > 0) {  // :91-96
+                        const float er = std::fabs(qs[q].ur - uRightT[idx]);
+                        if (er > r) continue;
+                    }
+                    const int dist = orbo_hamming(descQ + (size_t)q * 32, descT + (size_t)idx * 32);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist; bestIdx2 = bestIdx; bestLevel2 = bestLevel;
+                        bestDist = dist; bestIdx = idx; bestLevel = kpUn.octave;
+                    } else if (dist < bestDist2) {
+                        bestDist2 = dist; bestIdx2 = idx; bestLevel2 = kpUn.octave;
+                    }
+                }
+        done();
+    }
+}
+
+// Frame::ComputeStereoMatches (src/Frame.cc:811-980).  pyrL/pyrR[level] point at pixel (0,0) of mvImagePyramid[level]
+// of the left/right extractor (a ROI at (19,19) of the padded plane), strideL/strideR[level] are their row pitches and
+// cols[level] the level widths.  Compiled with -ffp-contract=off (STRICT).
+void orbo_compute_stereo_matches(const void* kpsL_, const uint8_t* descL, int N, const void* kpsR_, const uint8_t* descR,
+                                 int Nr, const float* mvScaleFactors, const float* mvInvScaleFactors, int nlevels,
+                                 const uint8_t* const* pyrL, const int* strideL, const uint8_t* const* pyrR,
+                                 const int* strideR, const int* cols, int nRows, float mbf, float mb, float* mvuRight,
+                                 float* mvDepth) {
+    (void)nlevels;
+    const Kp* mvKeys = static_cast<const Kp*>(kpsL_);
+    const Kp* mvKeysRight = static_cast<const Kp*>(kpsR_);
+    for (int i = 0; i < N; ++i) { mvuRight[i] = -1.0f; mvDepth[i] = -1.0f; }  // :813-814
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    std::vector<std::vector<size_t>> vRowIndices(nRows, std::vector<size_t>());
+    for (int iR = 0; iR < Nr; iR++) {
+        const Kp& kp = mvKeysRight[iR];
+        const float& kpY = kp.y;
+        const float r = 2.0f * mvScaleFactors[mvKeysRight[iR].octave];
+        const int maxr = ceil(kpY + r);
+        const int minr = floor(kpY - r);
+        for (int yi = minr; yi <= maxr; yi++)
+            if (yi >= 0 && yi < nRows) vRowIndices[yi].push_back(iR);  // (the reference indexes unchecked)
+    }
+    const float minZ = mb;
+    const float minD = 0;
+    const float maxD = mbf / minZ;
+    std::vector<std::pair<int, int>> vDistIdx;
+    for (int iL = 0; iL < N; iL++) {
+        const Kp& kpL = mvKeys[iL];
+        const int& levelL = kpL.octave;
+        const float& vL = kpL.y;
+        const float& uL = kpL.x;
+        if (!(vL >= 0 && vL < nRows)) continue;
+        const std::vector<size_t>& vCandidates = vRowIndices[(size_t)vL];
+        if (vCandidates.empty()) continue;
+        const float minU = uL - maxD;
+        const float maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH;
+        size_t bestIdxR = 0;
+        for (size_t iC = 0; iC < vCandidates.size(); iC++) {
+            const size_t iR = vCandidates[iC];
+            const Kp& kpR = mvKeysRight[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float& uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = orbo_hamming(descL + (size_t)iL * 32, descR + iR * 32);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {  // :896
+            const float uR0 = mvKeysRight[bestIdxR].x;
+            const float scaleFactor = mvInvScaleFactors[kpL.octave];
+            const float scaleduL = std::round(kpL.x * scaleFactor);
+            const float scaledvL = std::round(kpL.y * scaleFactor);
+            const float scaleduR0 = std::round(uR0 * scaleFactor);
+            const int w = 5;
+            const uint8_t* IL = pyrL[kpL.octave] + (ptrdiff_t)(int)(scaledvL - w) * strideL[kpL.octave] + (int)(scaleduL - w);
+            int bestDist = INT_MAX;
+            int bestincR = 0;
+            const int L = 5;
+            std::vector<float> vDists;
+            vDists.resize(2 * L + 1);
+            const float iniu = scaleduR0 + L - w;
+            const float endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= cols[kpL.octave]) continue;
+            for (int incR = -L; incR <= +L; incR++) {
+                const uint8_t* IR = pyrR[kpL.octave] + (ptrdiff_t)(int)(scaledvL - w) * strideR[kpL.octave] +
+                                    (int)(scaleduR0 + incR - w);
+                int l1 = 0;  // cv::norm(IL, IR, cv::NORM_L1) over the 11 x 11 window
+                for (int yy = 0; yy < 2 * w + 1; ++yy)
+                    for (int xx = 0; xx < 2 * w + 1; ++xx)
+                        l1 += std::abs((int)IL[(ptrdiff_t)yy * strideL[kpL.octave] + xx] - (int)IR[(ptrdiff_t)yy * strideR[kpL.octave] + xx]);
+                float dist = (float)l1;
+                if (dist < bestDist) { bestDist = dist; bestincR = incR; }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1];
+            const float dist2 = vDists[L + bestincR];
+            const float dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = mvScaleFactors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) {
+                    disparity = 0.01;
+                    bestuR = uL - 0.01;
+                }
+                mvDepth[iL] = mbf / disparity;
+                mvuRight[iL] = bestuR;
+                vDistIdx.push_back(std::pair<int, int>(bestDist, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return;  // (the reference would index an empty vector here)
+    std::sort(vDistIdx.begin(), vDistIdx.end());
+    const float median = vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+        if (vDistIdx[i].first < thDist) break;
+        mvuRight[vDistIdx[i].second] = -1;
+        mvDepth[vDistIdx[i].second] = -1;
+    }
+}
+
+}  // extern "C"

@@ -153,6 +153,12 @@ def port_lib():
         lib.orbo_match_top2.argtypes = [_u8p, C.c_int, _u8p, C.c_long, _i32p, _i32p, _i32p, _i32p, C.c_int]
         lib.orbo_match_stereo_banded.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_void_p, _u8p, C.c_int, _f32p, C.c_int,
                                                  C.c_float, _i32p, _i32p]
+        lib.orbo_accept_top2.argtypes = [C.c_int, C.c_float, _i32p, _i32p, C.POINTER(C.c_int64), _i32p, _i32p, C.c_int, _u8p]
+        lib.orbo_search_grid_top2.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, _u8p, _f32p,
+                                              C.c_void_p, _u8p, C.c_int] + [_i32p] * 6
+        lib.orbo_compute_stereo_matches.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_void_p, _u8p, C.c_int, _f32p, _f32p, C.c_int,
+                                                    C.POINTER(C.c_void_p), _i32p, C.POINTER(C.c_void_p), _i32p, _i32p, C.c_int,
+                                                    C.c_float, C.c_float, _f32p, _f32p]
         lib.orbo_extract_many.restype = C.c_long
         lib.orbo_extract_many.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, _u8p, C.c_int,
                                           C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -260,6 +266,75 @@ def match_stereo_banded(kl, dl, kr, dr, scale_factors, n_rows, max_d):
     port_lib().orbo_match_stereo_banded(kl.ctypes.data_as(C.c_void_p), _ptr(dl), len(kl), kr.ctypes.data_as(C.c_void_p),
                                         _ptr(dr), len(kr), _ptr(sf, _f32p), n_rows, max_d, _ptr(bi, _i32p), _ptr(bd, _i32p))
     return bi, bd
+
+
+def accept_top2(rule, d1, d2, nnratio=0.7, idx2=None, level1=None, level2=None):
+    """ORBmatcher's accept rules (see include/orbx.h orbx_accept_rule) -> bool array."""
+    d1 = np.ascontiguousarray(d1, dtype=np.int32); d2 = np.ascontiguousarray(d2, dtype=np.int32)
+    keep = []
+
+    def opt(a, dt, t):
+        if a is None:
+            return None
+        a = np.ascontiguousarray(a, dtype=dt)
+        keep.append(a)
+        return _ptr(a, t)
+    acc = np.zeros(max(len(d1), 1), dtype=np.uint8)
+    port_lib().orbo_accept_top2(int(rule), float(nnratio), _ptr(d1, _i32p), _ptr(d2, _i32p), opt(idx2, np.int64, C.POINTER(C.c_int64)),
+                                opt(level1, np.int32, _i32p), opt(level2, np.int32, _i32p), len(d1), _ptr(acc))
+    return acc[:len(d1)].astype(bool)
+
+
+def search_grid_top2(kps_t, desc_t, bounds, queries, desc_q, skip_t=None, u_right_t=None):
+    """Frame::GetFeaturesInArea + best/second loop -> idx1, d1, idx2, d2, lvl1, lvl2."""
+    kps_t = np.ascontiguousarray(kps_t); queries = np.ascontiguousarray(queries)
+    desc_t = np.ascontiguousarray(desc_t, dtype=np.uint8); desc_q = np.ascontiguousarray(desc_q, dtype=np.uint8)
+    assert kps_t.dtype.itemsize == 28 and queries.dtype.itemsize == 24
+    sk = None if skip_t is None else np.ascontiguousarray(skip_t, dtype=np.uint8)
+    ur = None if u_right_t is None else np.ascontiguousarray(u_right_t, dtype=np.float32)
+    nq = len(queries)
+    out = [np.zeros(max(nq, 1), dtype=np.int32) for _ in range(6)]
+    port_lib().orbo_search_grid_top2(kps_t.ctypes.data_as(C.c_void_p), _ptr(desc_t), len(kps_t), *[float(b) for b in bounds],
+                                     None if sk is None else _ptr(sk), None if ur is None else _ptr(ur, _f32p),
+                                     queries.ctypes.data_as(C.c_void_p), _ptr(desc_q), nq, *[_ptr(o, _i32p) for o in out])
+    return [o[:nq] for o in out]
+
+
+def compute_stereo_matches(kl, dl, kr, dr, scale_factors, inv_scale_factors, pyr_l, pyr_r, bf, b):
+    """Frame::ComputeStereoMatches (Frame.cc:811-980).  pyr_l / pyr_r: lists of PADDED planes (h+38, w+38) per level,
+    as PortExtractor.pyramid returns them -> (mvuRight, mvDepth)."""
+    kl = np.ascontiguousarray(kl); kr = np.ascontiguousarray(kr)
+    dl = np.ascontiguousarray(dl, dtype=np.uint8); dr = np.ascontiguousarray(dr, dtype=np.uint8)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32); isf = np.ascontiguousarray(inv_scale_factors, dtype=np.float32)
+    nl = len(sf)
+    pl = [np.ascontiguousarray(p, dtype=np.uint8) for p in pyr_l]
+    pr = [np.ascontiguousarray(p, dtype=np.uint8) for p in pyr_r]
+    ptr_l = (C.c_void_p * nl)(*[p.ctypes.data + 19 * p.shape[1] + 19 for p in pl])
+    ptr_r = (C.c_void_p * nl)(*[p.ctypes.data + 19 * p.shape[1] + 19 for p in pr])
+    st_l = np.array([p.shape[1] for p in pl], dtype=np.int32); st_r = np.array([p.shape[1] for p in pr], dtype=np.int32)
+    cols = np.array([p.shape[1] - 38 for p in pl], dtype=np.int32)
+    n_rows = pl[0].shape[0] - 38
+    n = len(kl)
+    ur = np.zeros(max(n, 1), dtype=np.float32); dp = np.zeros(max(n, 1), dtype=np.float32)
+    port_lib().orbo_compute_stereo_matches(kl.ctypes.data_as(C.c_void_p), _ptr(dl), n, kr.ctypes.data_as(C.c_void_p), _ptr(dr),
+                                           len(kr), _ptr(sf, _f32p), _ptr(isf, _f32p), nl, ptr_l, _ptr(st_l, _i32p), ptr_r,
+                                           _ptr(st_r, _i32p), _ptr(cols, _i32p), n_rows, float(bf), float(b), _ptr(ur, _f32p),
+                                           _ptr(dp, _f32p))
+    return ur[:n], dp[:n]
+
+
+def stage_gray(img, rgb=True, new_size=None):
+    """System.cc:420-425 (cv::resize on the interleaved colour image) then Tracking.cc:1569-1582 (cvtColor -> GRAY);
+    OpenCV 8-bit RGB2Gray = (R*9798 + G*19235 + B*3735 + 2^14) >> 15."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    planes = [img] if img.ndim == 2 else [np.ascontiguousarray(img[..., c]) for c in range(img.shape[2])]
+    if new_size is not None and tuple(new_size) != (img.shape[1], img.shape[0]):
+        planes = [resize_linear(p, new_size[0], new_size[1]) for p in planes]
+    if len(planes) == 1:
+        return planes[0]
+    r, g, b = (planes[0], planes[1], planes[2]) if rgb else (planes[2], planes[1], planes[0])
+    v = r.astype(np.int64) * 9798 + g.astype(np.int64) * 19235 + b.astype(np.int64) * 3735 + (1 << 14)
+    return (v >> 15).astype(np.uint8)
 
 
 def extract_many(imgs, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, lap=(0, 1000), threads=0,

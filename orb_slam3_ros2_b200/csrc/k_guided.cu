@@ -1,0 +1,341 @@
+// k_guided.cu — the matcher-side rows next to the extractor:
+//   * acceptKernel          the accept rules of ORBmatcher on top-2 results (ORBmatcher.cc:123-128, :327-329, :697-699,
+//                           :848-850, :1767, Frame.cc:1149), float comparisons written as the reference writes them;
+//   * gridSortKernel +      Frame::AssignFeaturesToGrid / PosInGrid (Frame.cc:385-416, :725-736) as ONE sort of
+//     gridSearchKernel      (cell << 20 | index) keys: with cells numbered column-major (ix * 48 + iy) the candidates of
+//                           one grid column of a GetFeaturesInArea window (Frame.cc:657-723) are a contiguous key range
+//                           already in the reference's visiting order, so a warp walks a query's window column by
+//                           column, 32 candidates at a time, and keeps (distance, visit position) top-2 keys;
+//   * stereoRefineKernel +  the second half of Frame::ComputeStereoMatches (Frame.cc:896-980): 11 x 11 L1 correlation
+//     stereoCutKernel       over +-5 px read straight from the two extractors' device-resident pyramids, parabola fit,
+//                           disparity / depth, and the 1.5 * 1.4 * median cut through a histogram select.
+#include "orbx_internal.cuh"
+
+namespace orbx {
+namespace {
+
+constexpr int kGridRows = 48, kGridCols = 64, kGridCells = kGridRows * kGridCols;  // Frame.h:44-45
+constexpr unsigned kNoCell = 0xfffu;
+
+__global__ void acceptKernel(int rule, float nnratio, const int* __restrict__ d1, const int* __restrict__ d2,
+                             const long long* __restrict__ idx2, const int* __restrict__ l1, const int* __restrict__ l2, int n,
+                             uint8_t* __restrict__ accept) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b1 = d1[i], b2 = d2[i];
+    const float f1 = (float)b1, f2 = (float)b2;
+    const float lim = __fmul_rn(nnratio, f2);
+    bool ok = false;
+    switch (rule) {
+        case 0: {
+            const bool same = (l1 ? l1[i] : 0) == (l2 ? l2[i] : 0);
+            ok = b1 <= 100 && (!same || f1 <= lim);
+            break;
+        }
+        case 1: ok = b1 <= 50 && f1 < lim; break;
+        case 2: ok = b1 <= 50 && f1 < lim; break;
+        case 3: ok = b1 < 50 && f1 < lim; break;
+        case 4: ok = b1 <= 100; break;
+        case 5: ok = b1 <= 50; break;
+        case 6: ok = (!idx2 || idx2[i] >= 0) && (double)f1 < __dmul_rn((double)f2, 0.7); break;
+    }
+    accept[i] = ok ? 1 : 0;
+}
+
+// ---- grid: keys (cell << 20 | index) sorted by one CTA (bitonic, shared memory), then the cell boundaries -------------
+__global__ void __launch_bounds__(1024) gridSortKernel(const float* __restrict__ kps, int nt, int nPow2, float minX, float minY,
+                                                       float invW, float invH, uint32_t* __restrict__ sortedOut,
+                                                       int* __restrict__ cellStart) {
+    extern __shared__ uint32_t keys[];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < nPow2; i += 1024) {
+        uint32_t key = 0xffffffffu;
+        if (i < nt) {
+            // posX = round((kp.pt.x - mnMinX) * mfGridElementWidthInv)  (Frame.cc:727-728; float round, half away from 0)
+            const int px = (int)roundf(__fmul_rn(__fsub_rn(kps[i * 7], minX), invW));
+            const int py = (int)roundf(__fmul_rn(__fsub_rn(kps[i * 7 + 1], minY), invH));
+            const bool in = px >= 0 && px < kGridCols && py >= 0 && py < kGridRows;
+            key = ((in ? (uint32_t)(px * kGridRows + py) : kNoCell) << 20) | (uint32_t)i;
+        }
+        keys[i] = key;
+    }
+    __syncthreads();
+    for (int k = 2; k <= nPow2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < nPow2; i += 1024) {
+                const int p = i ^ j;
+                if (p > i) {
+                    const uint32_t a = keys[i], b = keys[p];
+                    if (((i & k) == 0) ? (a > b) : (a < b)) { keys[i] = b; keys[p] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    // cellStart[c] = first position whose cell >= c (cells 0..kGridCells)
+    for (int i = tid; i < nt; i += 1024) {
+        sortedOut[i] = keys[i];
+        const int c = (int)(keys[i] >> 20);
+        const int prev = i == 0 ? -1 : (int)(keys[i - 1] >> 20);
+        for (int cc = prev + 1; cc <= min(c, kGridCells); ++cc) cellStart[cc] = i;
+    }
+    {
+        const int last = nt > 0 ? (int)(keys[nt - 1] >> 20) : -1;
+        for (int cc = last + 1 + tid; cc <= kGridCells; cc += 1024) cellStart[cc] = nt;
+    }
+}
+
+struct GridQuery {
+    float u, v, r;
+    int minLevel, maxLevel;
+    float ur;
+};
+
+__device__ __forceinline__ void top2Insert(unsigned long long& k1, unsigned long long& k2, unsigned long long k) {
+    k2 = min(k2, max(k1, k));
+    k1 = min(k1, k);
+}
+
+// one warp per query
+__global__ void __launch_bounds__(256) gridSearchKernel(const float* __restrict__ kps, const uint4* __restrict__ desc,
+                                                        const uint32_t* __restrict__ sorted, const int* __restrict__ cellStart,
+                                                        const uint8_t* __restrict__ skip, const float* __restrict__ uRight,
+                                                        float minX, float minY, float invW, float invH,
+                                                        const GridQuery* __restrict__ qs, const uint4* __restrict__ descQ, int nq,
+                                                        int* __restrict__ idx1, int* __restrict__ d1, int* __restrict__ idx2,
+                                                        int* __restrict__ d2, int* __restrict__ lvl1, int* __restrict__ lvl2) {
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const GridQuery Q = qs[q];
+    const uint4 a0 = descQ[2 * q], a1 = descQ[2 * q + 1];
+    unsigned long long k1 = ~0ull, k2 = ~0ull;  // distance << 48 | visit position << 24 | index
+    // Frame.cc:665-687
+    const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(Q.u, minX), Q.r), invW)));
+    const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(Q.u, minX), Q.r), invW)));
+    const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(Q.v, minY), Q.r), invH)));
+    const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(Q.v, minY), Q.r), invH)));
+    if (!(minCX >= kGridCols || maxCX < 0 || minCY >= kGridRows || maxCY < 0)) {
+        const bool checkLevels = Q.minLevel > 0 || Q.maxLevel >= 0;
+        unsigned visit = 0;
+        for (int ix = minCX; ix <= maxCX; ++ix) {
+            if (minCY > maxCY) break;
+            const int b = cellStart[ix * kGridRows + minCY], e = cellStart[ix * kGridRows + maxCY + 1];
+            for (int p0 = b; p0 < e; p0 += 32) {
+                const int p = p0 + lane;
+                if (p < e) {
+                    const int idx = (int)(sorted[p] & 0xfffffu);
+                    const float x = kps[idx * 7], y = kps[idx * 7 + 1];
+                    const int oct = __float_as_int(kps[idx * 7 + 5]);
+                    bool ok = true;
+                    if (checkLevels) ok = !(oct < Q.minLevel) && !(Q.maxLevel >= 0 && oct > Q.maxLevel);
+                    ok = ok && fabsf(__fsub_rn(x, Q.u)) < Q.r && fabsf(__fsub_rn(y, Q.v)) < Q.r;
+                    if (ok && skip) ok = skip[idx] == 0;
+                    if (ok && uRight) {
+                        const float urt = uRight[idx];
+                        if (urt > 0.f) ok = !(fabsf(__fsub_rn(Q.ur, urt)) > Q.r);
+                    }
+                    if (ok) {
+                        const uint4 b0 = desc[2 * idx], b1 = desc[2 * idx + 1];
+                        const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                                      __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+                        const unsigned long long key = ((unsigned long long)d << 48) |
+                                                       ((unsigned long long)(visit + (unsigned)(p - b)) << 24) | (unsigned)idx;
+                        top2Insert(k1, k2, key);
+                    }
+                }
+            }
+            visit += (unsigned)(e - b);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        top2Insert(k1, k2, o1);
+        top2Insert(k1, k2, o2);
+    }
+    if (lane == 0) {
+        const bool h1 = k1 != ~0ull, h2 = k2 != ~0ull;
+        const int i1 = h1 ? (int)(k1 & 0xffffffu) : -1, i2 = h2 ? (int)(k2 & 0xffffffu) : -1;
+        idx1[q] = i1; d1[q] = h1 ? (int)(k1 >> 48) : 256;
+        idx2[q] = i2; d2[q] = h2 ? (int)(k2 >> 48) : 256;
+        if (lvl1) lvl1[q] = h1 ? __float_as_int(kps[i1 * 7 + 5]) : -1;
+        if (lvl2) lvl2[q] = h2 ? __float_as_int(kps[i2 * 7 + 5]) : -1;
+    }
+}
+
+// ---- ComputeStereoMatches, Frame.cc:896-966: one warp per left keypoint ------------------------------------------------
+struct StereoLevels {
+    unsigned planeOff[kMaxLevels];
+    int pitch[kMaxLevels];
+    int cols[kMaxLevels];
+    float sf[kMaxLevels], isf[kMaxLevels];
+};
+
+__global__ void __launch_bounds__(256) stereoRefineKernel(const __grid_constant__ StereoLevels LV, const uint8_t* __restrict__ pyrL,
+                                                          const uint8_t* __restrict__ pyrR, const float* __restrict__ kl,
+                                                          const float* __restrict__ kr, int nl, const int* __restrict__ bestIdx,
+                                                          const int* __restrict__ bestDist, float mbf, float maxD,
+                                                          float* __restrict__ uRight, float* __restrict__ depth,
+                                                          int* __restrict__ sad) {
+    const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (iL >= nl) return;
+    float outU = -1.0f, outD = -1.0f;
+    int outS = -1;
+    const int bd = bestDist[iL];
+    if (bd < 75) {  // thOrbDist = (TH_HIGH + TH_LOW) / 2
+        const float uL = kl[iL * 7], vL = kl[iL * 7 + 1];
+        const int oct = __float_as_int(kl[iL * 7 + 5]);
+        const float uR0 = kr[bestIdx[iL] * 7];
+        const float scaleFactor = LV.isf[oct];
+        const float scaleduL = roundf(__fmul_rn(uL, scaleFactor));
+        const float scaledvL = roundf(__fmul_rn(vL, scaleFactor));
+        const float scaleduR0 = roundf(__fmul_rn(uR0, scaleFactor));
+        const float iniu = scaleduR0, endu = __fadd_rn(scaleduR0, 11.0f);  // scaleduR0 + L - w, + L + w + 1 (small integers)
+        if (!(iniu < 0 || endu >= (float)LV.cols[oct])) {
+            const int pitch = LV.pitch[oct];
+            // level pixel (x, y) lives at plane + (y + 19) * pitch + x + 19
+            const uint8_t* pl = pyrL + LV.planeOff[oct] + (size_t)((int)scaledvL - 5 + kEdge) * pitch + ((int)scaleduL - 5 + kEdge);
+            const uint8_t* pr = pyrR + LV.planeOff[oct] + (size_t)((int)scaledvL - 5 + kEdge) * pitch + ((int)scaleduR0 - 5 + kEdge);
+            int acc[11];
+#pragma unroll
+            for (int k = 0; k < 11; ++k) acc[k] = 0;
+            // lanes 0..10 own one row of the window: 11 left pixels against 21 right pixels
+            if (lane < 11) {
+                int a[11], b[21];
+#pragma unroll
+                for (int x = 0; x < 11; ++x) a[x] = pl[(size_t)lane * pitch + x];
+#pragma unroll
+                for (int x = 0; x < 21; ++x) b[x] = pr[(size_t)lane * pitch + x - 5];
+#pragma unroll
+                for (int k = 0; k < 11; ++k)
+#pragma unroll
+                    for (int x = 0; x < 11; ++x) acc[k] += abs(a[x] - b[x + k]);
+            }
+#pragma unroll
+            for (int k = 0; k < 11; ++k)
+#pragma unroll
+                for (int o = 8; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+            // (lanes 0..15 now hold the sums of rows 0..15; rows 11..15 contributed 0)
+            int best = 0x7fffffff, bestInc = 0;
+#pragma unroll
+            for (int k = 0; k < 11; ++k)
+                if (acc[k] < best) { best = acc[k]; bestInc = k - 5; }
+            if (!(bestInc == -5 || bestInc == 5)) {
+                float dist1 = 0.f, dist2 = 0.f, dist3 = 0.f;
+#pragma unroll
+                for (int k = 1; k < 10; ++k)
+                    if (k - 5 == bestInc) { dist1 = (float)acc[k - 1]; dist2 = (float)acc[k]; dist3 = (float)acc[k + 1]; }
+                const float den = __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2)));
+                const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3), den);
+                if (!(deltaR < -1.f || deltaR > 1.f)) {
+                    float bestuR = __fmul_rn(LV.sf[oct], __fadd_rn(__fadd_rn(scaleduR0, (float)bestInc), deltaR));
+                    float disparity = __fsub_rn(uL, bestuR);
+                    if (disparity >= 0.f && disparity < maxD) {
+                        if (disparity <= 0.f) {
+                            disparity = 0.01f;                                  // disparity = 0.01 (double -> float)
+                            bestuR = (float)__dsub_rn((double)uL, 0.01);        // bestuR = uL - 0.01
+                        }
+                        outD = __fdiv_rn(mbf, disparity);
+                        outU = bestuR;
+                        outS = best;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) { uRight[iL] = outU; depth[iL] = outD; sad[iL] = outS; }
+}
+
+// Frame.cc:969-980: median of the correlation distances (element size/2 of the sorted list) through a histogram
+// (distances are <= 121 * 255 = 30855), then every match with (float)dist >= 1.5f * 1.4f * median is removed.
+constexpr int kSadBins = 30856;
+__global__ void __launch_bounds__(1024) stereoCutKernel(const int* __restrict__ sad, int nl, float* __restrict__ uRight,
+                                                        float* __restrict__ depth) {
+    extern __shared__ int hist[];
+    __shared__ int sPart[1024];
+    __shared__ int sMedian;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kSadBins; i += 1024) hist[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < nl; i += 1024)
+        if (sad[i] >= 0) atomicAdd(&hist[min(sad[i], kSadBins - 1)], 1);
+    __syncthreads();
+    const int per = (kSadBins + 1023) / 1024;
+    const int b = tid * per, e = min(b + per, kSadBins);
+    int sum = 0;
+    for (int i = b; i < e; ++i) sum += hist[i];
+    sPart[tid] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        int total = 0;
+        for (int i = 0; i < 1024; ++i) total += sPart[i];
+        int median = -1;
+        if (total > 0) {
+            const int rank = total / 2;  // vDistIdx[size / 2]
+            int acc = 0, t = 0;
+            for (; t < 1024; ++t) {
+                if (acc + sPart[t] > rank) break;
+                acc += sPart[t];
+            }
+            for (int i = t * per; i < kSadBins; ++i) {
+                acc += hist[i];
+                if (acc > rank) { median = i; break; }
+            }
+        }
+        sMedian = median;
+    }
+    __syncthreads();
+    if (sMedian < 0) return;
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)sMedian);
+    for (int i = tid; i < nl; i += 1024)
+        if (sad[i] >= 0 && !((float)sad[i] < thDist)) { uRight[i] = -1.0f; depth[i] = -1.0f; }
+}
+
+}  // namespace
+
+void launchAccept(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* l1,
+                  const int32_t* l2, int n, uint8_t* accept, cudaStream_t s) {
+    if (n <= 0) return;
+    acceptKernel<<<(n + 255) / 256, 256, 0, s>>>(rule, nnratio, d1, d2, reinterpret_cast<const long long*>(idx2), l1, l2, n, accept);
+    countLaunch();
+}
+
+int gridSortCapacity() { return 32768; }  // keys of one CTA's shared memory (128 KB)
+
+void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX, float maxX, float minY, float maxY,
+                      const uint8_t* skipT, const float* uRightT, const void* queries, const uint8_t* descQ, int nq,
+                      uint32_t* sortedScratch, int* cellStart, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
+                      int32_t* lvl1, int32_t* lvl2, cudaStream_t s) {
+    const float invW = (float)kGridCols / (maxX - minX), invH = (float)kGridRows / (maxY - minY);  // Frame.cc:251-252
+    int nPow2 = 32;
+    while (nPow2 < nt) nPow2 <<= 1;
+    const size_t smem = (size_t)nPow2 * 4;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    gridSortKernel<<<1, 1024, smem, s>>>(static_cast<const float*>(kpsT), nt, nPow2, minX, minY, invW, invH, sortedScratch, cellStart);
+    countLaunch();
+    if (nq <= 0) return;
+    gridSearchKernel<<<(nq + 7) / 8, 256, 0, s>>>(static_cast<const float*>(kpsT), reinterpret_cast<const uint4*>(descT), sortedScratch,
+                                                  cellStart, skipT, uRightT, minX, minY, invW, invH,
+                                                  static_cast<const GridQuery*>(queries), reinterpret_cast<const uint4*>(descQ), nq, idx1,
+                                                  d1, idx2, d2, lvl1, lvl2);
+    countLaunch();
+}
+
+void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, const uint8_t* pyrL, const uint8_t* pyrR,
+                        const void* kl, const void* kr, int nl, const int* bestIdx, const int* bestDist, float mbf, float maxD,
+                        float* uRight, float* depth, int* sad, cudaStream_t s) {
+    if (nl <= 0) return;
+    StereoLevels LV{};
+    for (int l = 0; l < P.nlevels; ++l) {
+        LV.planeOff[l] = P.lv[l].planeOff; LV.pitch[l] = P.lv[l].pitch; LV.cols[l] = P.lv[l].w;
+        LV.sf[l] = sf[l]; LV.isf[l] = isf[l];
+    }
+    stereoRefineKernel<<<(nl + 7) / 8, 256, 0, s>>>(LV, pyrL, pyrR, static_cast<const float*>(kl), static_cast<const float*>(kr), nl,
+                                                    bestIdx, bestDist, mbf, maxD, uRight, depth, sad);
+    countLaunch();
+    const size_t smem = (size_t)kSadBins * 4;
+    cudaFuncSetAttribute(stereoCutKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    stereoCutKernel<<<1, 1024, smem, s>>>(sad, nl, uRight, depth);
+    countLaunch();
+}
+
+}  // namespace orbx

@@ -75,6 +75,8 @@ struct orbx_extractor {
     Buffers buf{};
     DevMem mImg, mPyr, mBlur, mCand, mCellCnt, mGath, mNid, mLkp, mLkpCnt, mSlot, mOutK, mOutD, mOutN, mOutM, mTab, mErr;
     DevMem mKeys1, mKeys2, mMatch;
+    DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
+    int stagedW = 0, stagedH = 0;
     std::vector<uint8_t> hStage;  // pinned staging would be the caller's; this is only for get_* taps
 };
 
@@ -314,7 +316,7 @@ void orbx_destroy(orbx_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
-                     &h->mMatch};
+                     &h->mMatch, &h->mRaw, &h->mStageTab};
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 9; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -448,6 +450,68 @@ int orbx_extract(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, 
     if (n > cap) return fail(ORBX_ERR_CAPACITY, "keypoint buffer too small");
     if (kps && n) ORBX_CUDA(cudaMemcpyAsync(kps, h->buf.outKps, (size_t)n * 28, cudaMemcpyDeviceToHost, h->stream));
     if (desc && n) ORBX_CUDA(cudaMemcpyAsync(desc, h->buf.outDesc, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_extract_color(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int channels, int rgb, int new_w, int new_h,
+                       int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index) {
+    if (!h) return fail(ORBX_ERR_ARG, "null handle");
+    if (n_out) *n_out = 0;
+    if (!img || w <= 0 || hgt <= 0) {  // ORBextractor.cc:1090-1091
+        if (mono_index) *mono_index = -1;
+        return ORBX_OK;
+    }
+    if (channels != 1 && channels != 3 && channels != 4) return fail(ORBX_ERR_ARG, "channels must be 1, 3 or 4");
+    if (stride < w * channels) return fail(ORBX_ERR_ARG, "stride < width * channels");
+    if ((new_w > 0) != (new_h > 0)) return fail(ORBX_ERR_ARG, "new_w / new_h must both be set or both be 0");
+    const bool resize = new_w > 0 && (new_w != w || new_h != hgt);
+    const int dw = resize ? new_w : w, dh = resize ? new_h : hgt;
+    if (channels == 1 && !resize) return orbx_extract(h, img, w, hgt, stride, lap0, lap1, kps, desc, cap, n_out, mono_index);
+    DeviceGuard guard(h->device);
+    int rc = ensureCapacity(h, dw, dh, 1);
+    if (rc != ORBX_OK) return rc;
+    const size_t rowBytes = (size_t)w * channels;
+    ORBX_CUDA(h->mRaw.reserve(rowBytes * hgt + 64));
+    ORBX_CUDA(h->mImg.reserve((size_t)dw * dh + 64));
+    h->buf.img = (uint8_t*)h->mImg.p;
+    ORBX_CUDA(cudaMemcpy2DAsync(h->mRaw.p, rowBytes, img, stride, rowBytes, hgt, cudaMemcpyHostToDevice, h->stream));
+    const int16_t *tx = nullptr, *ty = nullptr;
+    if (resize) {
+        std::vector<int16_t> tab;
+        resizeTable(w, dw, true, tab);
+        resizeTable(hgt, dh, false, tab);
+        ORBX_CUDA(h->mStageTab.reserve(tab.size() * sizeof(int16_t)));
+        ORBX_CUDA(cudaMemcpyAsync(h->mStageTab.p, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
+        ORBX_CUDA(cudaStreamSynchronize(h->stream));  // `tab` is pageable host memory about to go out of scope
+        tx = (const int16_t*)h->mStageTab.p;
+        ty = tx + (size_t)dw * 4;
+    }
+    launchStage((const uint8_t*)h->mRaw.p, w, hgt, (int)rowBytes, channels, rgb, (uint8_t*)h->mImg.p, dw, dh, tx, ty, h->stream);
+    h->stagedW = dw; h->stagedH = dh;
+    rc = runPipeline(h, (const uint8_t*)h->mImg.p, dw, (size_t)dw * dh, 1, lap0, lap1);
+    if (rc != ORBX_OK) return rc;
+    int nm[2] = {0, 0};
+    ORBX_CUDA(cudaMemcpyAsync(&nm[0], h->buf.outN, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaMemcpyAsync(&nm[1], h->buf.outMono, 4, cudaMemcpyDeviceToHost, h->stream));
+    rc = checkDeviceFlags(h);
+    if (rc != ORBX_OK) return rc;
+    if (n_out) *n_out = nm[0];
+    if (mono_index) *mono_index = nm[1];
+    if (nm[0] > cap) return fail(ORBX_ERR_CAPACITY, "keypoint buffer too small");
+    if (kps && nm[0]) ORBX_CUDA(cudaMemcpyAsync(kps, h->buf.outKps, (size_t)nm[0] * 28, cudaMemcpyDeviceToHost, h->stream));
+    if (desc && nm[0]) ORBX_CUDA(cudaMemcpyAsync(desc, h->buf.outDesc, (size_t)nm[0] * 32, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_get_staged_gray(orbx_handle h, uint8_t* out, int* w, int* hgt) {
+    if (!h || h->stagedW == 0) return fail(ORBX_ERR_STATE, "no orbx_extract_color yet");
+    if (w) *w = h->stagedW;
+    if (hgt) *hgt = h->stagedH;
+    if (!out) return ORBX_OK;
+    DeviceGuard guard(h->device);
+    ORBX_CUDA(cudaMemcpyAsync(out, h->mImg.p, (size_t)h->stagedW * h->stagedH, cudaMemcpyDeviceToHost, h->stream));
     ORBX_CUDA(cudaStreamSynchronize(h->stream));
     return ORBX_OK;
 }
@@ -814,6 +878,154 @@ int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, 
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(best_idx, bi, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(best_dist, bd, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+static int needDevice() {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(ORBX_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    return ORBX_OK;
+}
+
+int orbx_accept_top2_device(int rule, float nnratio, const int32_t* d_d1, const int32_t* d_d2, const int64_t* d_idx2,
+                            const int32_t* d_level1, const int32_t* d_level2, int n, uint8_t* d_accept, void* stream) {
+    if (rule < 0 || rule > ORBX_ACCEPT_KNN_RATIO || n < 0 || (n > 0 && (!d_d1 || !d_d2 || !d_accept))) return fail(ORBX_ERR_ARG, "bad argument");
+    launchAccept(rule, nnratio, d_d1, d_d2, d_idx2, d_level1, d_level2, n, d_accept, (cudaStream_t)stream);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int orbx_accept_top2(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* level1,
+                     const int32_t* level2, int n, uint8_t* accept, int device) {
+    if (rule < 0 || rule > ORBX_ACCEPT_KNN_RATIO || n < 0 || (n > 0 && (!d1 || !d2 || !accept))) return fail(ORBX_ERR_ARG, "bad argument");
+    if (n == 0) return ORBX_OK;
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    const size_t n4 = ((size_t)n * 4 + 15) & ~(size_t)15, n8 = (size_t)n * 8;
+    ORBX_CUDA(S->misc.reserve(4 * n4 + n8 + n + 64));
+    uint8_t* base = (uint8_t*)S->misc.p;
+    int32_t *a = (int32_t*)base, *b = (int32_t*)(base + n4), *l1 = (int32_t*)(base + 2 * n4), *l2 = (int32_t*)(base + 3 * n4);
+    int64_t* i2 = (int64_t*)(base + 4 * n4);
+    uint8_t* acc = base + 4 * n4 + n8;
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaMemcpyAsync(a, d1, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(b, d2, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    if (level1) ORBX_CUDA(cudaMemcpyAsync(l1, level1, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    if (level2) ORBX_CUDA(cudaMemcpyAsync(l2, level2, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    if (idx2) ORBX_CUDA(cudaMemcpyAsync(i2, idx2, n8, cudaMemcpyHostToDevice, s));
+    rc = orbx_accept_top2_device(rule, nnratio, a, b, idx2 ? i2 : nullptr, level1 ? l1 : nullptr, level2 ? l2 : nullptr, n, acc, s);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA(cudaMemcpyAsync(accept, acc, (size_t)n, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_search_grid_top2(const orbx_keypoint* kps_t, const uint8_t* desc_t, int nt, float min_x, float max_x, float min_y,
+                          float max_y, const uint8_t* skip_t, const float* u_right_t, const orbx_grid_query* queries,
+                          const uint8_t* desc_q, int nq, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, int32_t* lvl1,
+                          int32_t* lvl2, int device) {
+    if (nt < 0 || nq < 0 || (nt > 0 && (!kps_t || !desc_t)) || (nq > 0 && (!queries || !desc_q || !idx1 || !d1 || !idx2 || !d2)))
+        return fail(ORBX_ERR_ARG, "bad argument");
+    if (!(max_x > min_x) || !(max_y > min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
+    if (nt > gridSortCapacity()) return fail(ORBX_ERR_ARG, "more than 32768 target keypoints");
+    if (nq == 0) return ORBX_OK;
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    static_assert(sizeof(orbx_grid_query) == 24, "orbx_grid_query layout");
+    const size_t T = (size_t)std::max(nt, 1), Q = (size_t)nq;
+    // db: [desc_t | kps_t | skip | uRight | sorted | cellStart]   q: [desc_q | queries | 6 outputs]
+    const size_t oKt = T * 32, oSk = oKt + ((T * 28 + 15) & ~(size_t)15), oUr = oSk + ((T + 15) & ~(size_t)15),
+                 oSo = oUr + T * 4 + 16, oCs = oSo + T * 4 + 16, dbBytes = oCs + (size_t)(64 * 48 + 1) * 4 + 64;
+    const size_t oQs = Q * 32, oOut = oQs + ((Q * 24 + 15) & ~(size_t)15), qBytes = oOut + 6 * Q * 4 + 64;
+    ORBX_CUDA(S->db.reserve(dbBytes));
+    ORBX_CUDA(S->q.reserve(qBytes));
+    uint8_t* D = (uint8_t*)S->db.p;
+    uint8_t* Qb = (uint8_t*)S->q.p;
+    cudaStream_t s = S->stream;
+    if (nt) {
+        ORBX_CUDA(cudaMemcpyAsync(D, desc_t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+        ORBX_CUDA(cudaMemcpyAsync(D + oKt, kps_t, (size_t)nt * 28, cudaMemcpyHostToDevice, s));
+        if (skip_t) ORBX_CUDA(cudaMemcpyAsync(D + oSk, skip_t, (size_t)nt, cudaMemcpyHostToDevice, s));
+        if (u_right_t) ORBX_CUDA(cudaMemcpyAsync(D + oUr, u_right_t, (size_t)nt * 4, cudaMemcpyHostToDevice, s));
+    }
+    ORBX_CUDA(cudaMemcpyAsync(Qb, desc_q, Q * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Qb + oQs, queries, Q * 24, cudaMemcpyHostToDevice, s));
+    int32_t* out = (int32_t*)(Qb + oOut);
+    launchGridSearch(D + oKt, D, nt, min_x, max_x, min_y, max_y, skip_t ? D + oSk : nullptr, u_right_t ? (const float*)(D + oUr) : nullptr,
+                     Qb + oQs, Qb, nq, (uint32_t*)(D + oSo), (int*)(D + oCs), out, out + Q, out + 2 * Q, out + 3 * Q, out + 4 * Q,
+                     out + 5 * Q, s);
+    ORBX_CUDA(cudaGetLastError());
+    int32_t* host[6] = {idx1, d1, idx2, d2, lvl1, lvl2};
+    for (int k = 0; k < 6; ++k)
+        if (host[k]) ORBX_CUDA(cudaMemcpyAsync(host[k], out + k * Q, Q * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, const orbx_keypoint* kps_l, const uint8_t* desc_l,
+                                int nl, const orbx_keypoint* kps_r, const uint8_t* desc_r, int nr, float bf, float b,
+                                float* u_right, float* depth) {
+    if (!left || !right || nl < 0 || nr < 0 || !u_right || !depth) return fail(ORBX_ERR_ARG, "bad argument");
+    if (left->lastFrames == 0 || right->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (frame < 0 || frame >= left->lastFrames || frame >= right->lastFrames) return fail(ORBX_ERR_ARG, "frame out of range");
+    if (left->device != right->device) return fail(ORBX_ERR_ARG, "the two extractors live on different devices");
+    const FramePlan& P = left->plan;
+    if (P.W != right->plan.W || P.H != right->plan.H || P.nlevels != right->plan.nlevels || left->sf != right->sf)
+        return fail(ORBX_ERR_ARG, "left and right extractors differ in image size or pyramid");
+    if (nl == 0) return ORBX_OK;
+    for (int i = 0; i < nl; ++i)
+        if (kps_l[i].octave < 0 || kps_l[i].octave >= P.nlevels) return fail(ORBX_ERR_ARG, "left keypoint octave out of range");
+    for (int i = 0; i < nr; ++i)
+        if (kps_r[i].octave < 0 || kps_r[i].octave >= P.nlevels) return fail(ORBX_ERR_ARG, "right keypoint octave out of range");
+    DeviceGuard guard(left->device);
+    ORBX_CUDA(cudaStreamSynchronize(left->stream));
+    ORBX_CUDA(cudaStreamSynchronize(right->stream));
+    MatchScratch* S = nullptr;
+    int rc = matchScratch(left->device, &S);
+    if (rc != ORBX_OK) return rc;
+    const size_t L = (size_t)nl, R = (size_t)std::max(nr, 1);
+    ORBX_CUDA(S->q.reserve(L * 60 + 64));
+    ORBX_CUDA(S->db.reserve(R * 60 + 64));
+    ORBX_CUDA(S->misc.reserve((size_t)kMaxLevels * 4 + L * 20 + 128));
+    cudaStream_t s = S->stream;
+    uint8_t* dl = (uint8_t*)S->q.p; uint8_t* kl = dl + L * 32;
+    uint8_t* dr = (uint8_t*)S->db.p; uint8_t* kr = dr + R * 32;
+    float* sf = (float*)S->misc.p;
+    int32_t* bi = (int32_t*)((uint8_t*)S->misc.p + kMaxLevels * 4);
+    int32_t* bd = bi + L;
+    int32_t* sad = bd + L;
+    float* ur = (float*)(sad + L);
+    float* dp = ur + L;
+    ORBX_CUDA(cudaMemcpyAsync(dl, desc_l, L * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(kl, kps_l, L * 28, cudaMemcpyHostToDevice, s));
+    if (nr) {
+        ORBX_CUDA(cudaMemcpyAsync(dr, desc_r, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
+        ORBX_CUDA(cudaMemcpyAsync(kr, kps_r, (size_t)nr * 28, cudaMemcpyHostToDevice, s));
+    }
+    ORBX_CUDA(cudaMemcpyAsync(sf, left->sf.data(), (size_t)P.nlevels * 4, cudaMemcpyHostToDevice, s));
+    const float maxD = bf / b;  // Frame.cc:841
+    launchStereoBanded(kl, dl, nl, kr, dr, nr, sf, P.H, maxD, bi, bd, s);  // nRows = mvImagePyramid[0].rows (:818)
+    launchStereoRefine(P, left->sf.data(), left->isf.data(), left->buf.pyr + (size_t)frame * P.frameBytes,
+                       right->buf.pyr + (size_t)frame * right->plan.frameBytes, kl, kr, nl, bi, bd, bf, maxD, ur, dp, sad, s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(u_right, ur, L * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(depth, dp, L * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
     return ORBX_OK;
 }

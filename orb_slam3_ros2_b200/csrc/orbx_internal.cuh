@@ -107,6 +107,18 @@ void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap,
                             int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, cudaStream_t s);
 void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
                         const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s);
+void launchAccept(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* l1,
+                  const int32_t* l2, int n, uint8_t* accept, cudaStream_t s);
+int gridSortCapacity();
+void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX, float maxX, float minY, float maxY,
+                      const uint8_t* skipT, const float* uRightT, const void* queries, const uint8_t* descQ, int nq,
+                      uint32_t* sortedScratch, int* cellStart, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
+                      int32_t* lvl1, int32_t* lvl2, cudaStream_t s);
+void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, const uint8_t* pyrL, const uint8_t* pyrR,
+                        const void* kl, const void* kr, int nl, const int* bestIdx, const int* bestDist, float mbf, float maxD,
+                        float* uRight, float* depth, int* sad, cudaStream_t s);
+void launchStage(const uint8_t* dSrc, int sw, int sh, int sstride, int ch, int rgb, uint8_t* dDst, int dw, int dh,
+                 const int16_t* tabX, const int16_t* tabY, cudaStream_t s);
 void uploadDescribeTables();
 double benchPopcRate(cudaStream_t s);
 

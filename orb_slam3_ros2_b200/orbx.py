@@ -53,6 +53,9 @@ SYMBOLS = {
     "orbx_destroy": (None, [_vp]),
     "orbx_get_tables": (C.c_int, [_vp, _f32p, _f32p, _f32p, _f32p, _i32p]),
     "orbx_extract": (C.c_int, [_vp, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
+    "orbx_extract_color": (C.c_int, [_vp, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp,
+                                     _u8p, C.c_int, _i32p, _i32p]),
+    "orbx_get_staged_gray": (C.c_int, [_vp, _u8p, _i32p, _i32p]),
     "orbx_get_pyramid": (C.c_int, [_vp, C.c_int, C.c_int, _u8p, _i32p, _i32p]),
     "orbx_extract_batch": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, _vp, _vp,
                                      C.c_int, _vp, _vp]),
@@ -74,6 +77,12 @@ SYMBOLS = {
     "orbx_match_batch_consecutive": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int]),
     "orbx_match_stereo_banded": (C.c_int, [_vp, _u8p, C.c_int, _vp, _u8p, C.c_int, _f32p, C.c_int, C.c_int, C.c_float,
                                            _i32p, _i32p, C.c_int]),
+    "orbx_accept_top2": (C.c_int, [C.c_int, C.c_float, _i32p, _i32p, _i64p, _i32p, _i32p, C.c_int, _u8p, C.c_int]),
+    "orbx_accept_top2_device": (C.c_int, [C.c_int, C.c_float, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp]),
+    "orbx_search_grid_top2": (C.c_int, [_vp, _u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, _u8p, _f32p, _vp, _u8p,
+                                        C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p, _i32p, C.c_int]),
+    "orbx_compute_stereo_matches": (C.c_int, [_vp, _vp, C.c_int, _vp, _u8p, C.c_int, _vp, _u8p, C.c_int, C.c_float, C.c_float,
+                                              _f32p, _f32p]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_comm_unique_id": (C.c_int, [_u8p]),
     "orbx_comm_init": (C.c_int, [C.c_int, C.c_int, _u8p, C.c_int, C.POINTER(_vp)]),
@@ -175,6 +184,31 @@ class ORBextractor:
         if pyramid:
             self.mvImagePyramid = [self.pyramid_level(0, l)[19:-19, 19:-19] for l in range(self.nlevels)]
         return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_color(self, image, rgb=True, new_size=None, vLappingArea=(0, 1000)):
+        """System::Track*'s resize (System.cc:420-425) + Tracking::GrabImage*'s cvtColor (Tracking.cc:1569-1582) fused
+        ahead of operator().  image: (H, W), (H, W, 3) or (H, W, 4) uint8; new_size = (w, h) or None.
+        -> (monoIndex, keypoints, descriptors); the grey frame the extractor saw is `staged_gray()`."""
+        image = np.ascontiguousarray(image, dtype=np.uint8)
+        ch = 1 if image.ndim == 2 else image.shape[2]
+        h, w = image.shape[:2]
+        nw, nh = new_size if new_size else (0, 0)
+        cap = self.capacity
+        kps = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        n, mono = C.c_int32(0), C.c_int32(0)
+        _check(lib().orbx_extract_color(self._h, _ptr(image), w, h, image.strides[0], ch, 1 if rgb else 0, int(nw), int(nh),
+                                        vLappingArea[0], vLappingArea[1], kps.ctypes.data_as(_vp), _ptr(desc), cap, C.byref(n),
+                                        C.byref(mono)))
+        self._frames = 1
+        return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def staged_gray(self):
+        w, h = C.c_int32(0), C.c_int32(0)
+        _check(lib().orbx_get_staged_gray(self._h, None, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), dtype=np.uint8)
+        _check(lib().orbx_get_staged_gray(self._h, _ptr(out), None, None))
+        return out
 
     def pyramid_level(self, frame, level):
         """Padded plane (h+38, w+38) of `level`; mvImagePyramid[level] is its [19:-19, 19:-19] view."""
@@ -321,6 +355,67 @@ def bench_popc(device=-1):
     r = C.c_double(0)
     _check(lib().orbx_bench_popc(device, C.byref(r)))
     return r.value
+
+
+# orbx_accept_rule (include/orbx.h)
+ACCEPT_PROJ_MAP, ACCEPT_BOW_KF_F, ACCEPT_INIT, ACCEPT_BOW_KF_KF, ACCEPT_BEST_HIGH, ACCEPT_BEST_LOW, ACCEPT_KNN_RATIO = range(7)
+
+GRID_QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
+                             ("ur", "<f4")])
+assert GRID_QUERY_DTYPE.itemsize == 24
+
+
+def _opt(a, dtype, t):
+    if a is None:
+        return None, None
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a, _ptr(a, t)
+
+
+def accept_top2(rule, d1, d2, nnratio=0.7, idx2=None, level1=None, level2=None, device=-1):
+    """The reference's accept rules on top-2 results, evaluated on the device (ORBmatcher.cc:123-128, :327-329, :697-699,
+    :848-850, :1767, Frame.cc:1149) -> bool array."""
+    d1 = np.ascontiguousarray(d1, dtype=np.int32)
+    d2 = np.ascontiguousarray(d2, dtype=np.int32)
+    n = len(d1)
+    k2, p2 = _opt(idx2, np.int64, _i64p)
+    l1, pl1 = _opt(level1, np.int32, _i32p)
+    l2, pl2 = _opt(level2, np.int32, _i32p)
+    acc = np.zeros(max(n, 1), dtype=np.uint8)
+    _check(lib().orbx_accept_top2(int(rule), float(nnratio), _ptr(d1, _i32p), _ptr(d2, _i32p), p2, pl1, pl2, n, _ptr(acc), device))
+    return acc[:n].astype(bool)
+
+
+def search_grid_top2(kps_t, desc_t, bounds, queries, desc_q, skip_t=None, u_right_t=None, device=-1):
+    """Guided search: Frame::GetFeaturesInArea windows (Frame.cc:657-723) + the strict-< best/second loop
+    (ORBmatcher.cc:75-117) -> idx1, d1, idx2, d2, lvl1, lvl2 (int32).  bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    kps_t = np.ascontiguousarray(kps_t, dtype=KP_DTYPE)
+    desc_t = np.ascontiguousarray(desc_t, dtype=np.uint8).reshape(-1, 32)
+    queries = np.ascontiguousarray(queries, dtype=GRID_QUERY_DTYPE)
+    desc_q = np.ascontiguousarray(desc_q, dtype=np.uint8).reshape(-1, 32)
+    nq = len(queries)
+    sk, psk = _opt(skip_t, np.uint8, _u8p)
+    ur, pur = _opt(u_right_t, np.float32, _f32p)
+    out = [np.zeros(max(nq, 1), dtype=np.int32) for _ in range(6)]
+    _check(lib().orbx_search_grid_top2(kps_t.ctypes.data_as(_vp), _ptr(desc_t), len(kps_t), *[float(b) for b in bounds], psk, pur,
+                                       queries.ctypes.data_as(_vp), _ptr(desc_q), nq, *[_ptr(o, _i32p) for o in out], device))
+    return [o[:nq] for o in out]
+
+
+def compute_stereo_matches(left, right, kps_l, desc_l, kps_r, desc_r, bf, b, frame=0):
+    """Frame::ComputeStereoMatches (Frame.cc:811-980) on the pyramids held by two ORBextractor objects whose last
+    extraction produced kps_l / kps_r -> (mvuRight, mvDepth)."""
+    kps_l = np.ascontiguousarray(kps_l, dtype=KP_DTYPE)
+    kps_r = np.ascontiguousarray(kps_r, dtype=KP_DTYPE)
+    desc_l = np.ascontiguousarray(desc_l, dtype=np.uint8)
+    desc_r = np.ascontiguousarray(desc_r, dtype=np.uint8)
+    n = len(kps_l)
+    ur = np.zeros(max(n, 1), dtype=np.float32)
+    dp = np.zeros(max(n, 1), dtype=np.float32)
+    _check(lib().orbx_compute_stereo_matches(left._h, right._h, frame, kps_l.ctypes.data_as(_vp), _ptr(desc_l), n,
+                                             kps_r.ctypes.data_as(_vp), _ptr(desc_r), len(kps_r), float(bf), float(b),
+                                             _ptr(ur, _f32p), _ptr(dp, _f32p)))
+    return ur[:n], dp[:n]
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):

@@ -1,0 +1,113 @@
+"""GPU parity (through the C ABI) of the matcher-side rows: accept rules, guided grid search, ComputeStereoMatches."""
+import numpy as np
+import pytest
+
+from orb_slam3_ros2_b200 import synth
+from test_oracle_matcher_rows import make_grid_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def orbx():
+    from orb_slam3_ros2_b200 import orbx as m
+    m.lib()
+    return m
+
+
+def test_accept_rules_match_oracle_exhaustively(orbx, oracle):
+    # every (d1, d2) pair of the ranges that matter, every rule, three ratios
+    d1, d2 = np.meshgrid(np.arange(0, 130, dtype=np.int32), np.arange(0, 257, dtype=np.int32), indexing="ij")
+    d1, d2 = d1.ravel(), d2.ravel()
+    rng = np.random.default_rng(0)
+    l1, l2 = rng.integers(0, 3, d1.size), rng.integers(0, 3, d1.size)
+    idx2 = np.where(d2 == 256, -1, 5).astype(np.int64)
+    for rule in range(7):
+        for nn in (0.6, 0.7, 0.9, 0.75):
+            got = orbx.accept_top2(rule, d1, d2, nn, idx2=idx2, level1=l1, level2=l2)
+            want = oracle.accept_top2(rule, d1, d2, nn, idx2=idx2, level1=l1, level2=l2)
+            assert np.array_equal(got, want), (rule, nn)
+    assert np.array_equal(orbx.accept_top2(1, d1, d2, 0.7), oracle.accept_top2(1, d1, d2, 0.7))
+    assert len(orbx.accept_top2(1, d1[:0], d2[:0])) == 0
+
+
+@pytest.mark.parametrize("seed,nt,nq,filters", [(1, 600, 200, False), (2, 2000, 1500, True), (5, 1, 10, False), (6, 5000, 3000, True)])
+def test_grid_search_matches_oracle(orbx, oracle, seed, nt, nq, filters):
+    kps, desc, bounds, qs, dq, skip, ur = make_grid_case(seed, nt=max(nt, 80), nq=nq)
+    kps, desc, skip, ur = kps[:nt], desc[:nt], skip[:nt], ur[:nt]
+    if not filters:
+        skip = ur = None
+    got = orbx.search_grid_top2(kps, desc, bounds, qs, dq, skip, ur)
+    want = oracle.search_grid_top2(kps, desc, bounds, qs, dq, skip, ur)
+    for g, w, name in zip(got, want, ["idx1", "d1", "idx2", "d2", "lvl1", "lvl2"]):
+        assert np.array_equal(g, w), name
+
+
+def test_grid_search_on_extracted_frames(orbx, oracle):
+    """SearchForInitialization-shaped use: level-0 keypoints of frame 0 searched in frame 1 with windowSize 100."""
+    ex = orbx.ORBextractor(2000, 1.2, 8, 20, 7)
+    _, k0, d0 = ex(synth.frame(0, 752, 480), None, (0, 1000))
+    _, k1, d1 = ex(synth.frame(1, 752, 480), None, (0, 1000))
+    sel = k0["octave"] == 0
+    qs = np.zeros(int(sel.sum()), dtype=orbx.GRID_QUERY_DTYPE)
+    qs["u"], qs["v"], qs["r"] = k0["x"][sel], k0["y"][sel], 100.0
+    qs["min_level"], qs["max_level"] = 0, 0
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    got = orbx.search_grid_top2(k1, d1, bounds, qs, d0[sel])
+    want = oracle.search_grid_top2(k1, d1, bounds, qs, d0[sel])
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    acc = orbx.accept_top2(orbx.ACCEPT_INIT, got[1], got[3], 0.9)
+    assert acc.sum() > 100
+    # frame 1 is frame 0 shifted by (3, 1) px: accepted matches must agree with that motion
+    dx = k0["x"][sel][acc] - k1["x"][got[0][acc]]
+    assert abs(np.median(dx) - 3.0) < 0.5
+
+
+@pytest.mark.parametrize("w,h,nf", [(1241, 376, 2000), (640, 360, 1000)])
+def test_compute_stereo_matches_bit_exact(orbx, oracle, w, h, nf):
+    exl, exr = orbx.ORBextractor(nf, 1.2, 8, 20, 7), orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+    iml, imr = synth.frame(0, w, h), synth.frame(0, w, h, right=True)
+    _, kl, dl = exl(iml, None, (0, 0))
+    _, kr, dr = exr(imr, None, (0, 0))
+    bf, b = 386.1448, 0.53716  # config/Stereo/KITTI00-02.yaml
+    ur, dp = orbx.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, b)
+    ol, orr = oracle.PortExtractor(nfeatures=nf), oracle.PortExtractor(nfeatures=nf)
+    ol.extract(iml, (0, 0)); orr.extract(imr, (0, 0))
+    t = ol.tables()
+    wu, wd = oracle.compute_stereo_matches(kl, dl, kr, dr, t["scale"], t["inv_scale"], [ol.pyramid(l) for l in range(8)],
+                                           [orr.pyramid(l) for l in range(8)], bf, b)
+    assert np.array_equal(ur.view(np.uint32), wu.view(np.uint32))  # bit-exact floats
+    assert np.array_equal(dp.view(np.uint32), wd.view(np.uint32))
+    assert (ur >= 0).sum() > 300
+    # empty right side
+    ur0, dp0 = orbx.compute_stereo_matches(exl, exr, kl, dl, kr[:0], dr[:0], bf, b)
+    assert (ur0 == -1).all() and (dp0 == -1).all()
+
+
+def test_extract_color_staging_matches_cv2_goldens_and_oracle(orbx, oracle):
+    """orbx_extract_color: resize + cvtColor fused ahead of operator() (System.cc:420-425, Tracking.cc:1569-1582)."""
+    from conftest import load_golden
+    g = load_golden("stage.npz")
+    ex = orbx.ORBextractor(300, 1.2, 8, 20, 7)
+    names = sorted(k[:-5] for k in g.files if k.endswith("_meta"))
+    for name in names:
+        ch, rgb, nw, nh = [int(v) for v in g[name + "_meta"]]
+        src = g[name + "_src"]
+        if name == "cube":
+            n = src.shape[1] // 97 * 97
+            src = np.ascontiguousarray(src.reshape(-1, 3)[:n].reshape(-1, 97, 3))  # a 2-D image of the lattice
+            want = oracle.stage_gray(src, True, None)
+            assert np.array_equal(want.ravel(), g["cube_gray"].ravel()[:want.size])
+        else:
+            want = g[name + "_gray"]
+        ex.extract_color(src, bool(rgb), (nw, nh) if nw else None)
+        assert np.array_equal(ex.staged_gray(), want), name
+    # end to end on a real frame: colour frame whose grey conversion is known, resized 2x down
+    base = synth.frame(0, 1504, 960)
+    rgb = np.stack([base, base, base], axis=2)  # R = G = B = v  ->  grey = v exactly (weights sum to 2^15)
+    mono, kp, desc = ex.extract_color(rgb, True, (752, 480))
+    gray = oracle.stage_gray(rgb, True, (752, 480))
+    assert np.array_equal(ex.staged_gray(), gray)
+    wm, wk, wd = oracle.PortExtractor(nfeatures=300).extract(gray, (0, 1000))
+    assert mono == wm and np.array_equal(kp, wk) and np.array_equal(desc, wd)

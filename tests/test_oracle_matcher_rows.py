@@ -1,0 +1,145 @@
+"""CPU tests (no GPU) of the matcher-side oracle rows (oracle/match_oracle.cpp): accept rules, guided grid search and
+Frame::ComputeStereoMatches, each against hand-checked known answers or an independent numpy restatement."""
+import numpy as np
+import pytest
+
+from orb_slam3_ros2_b200 import synth
+
+KP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"),
+               ("class_id", "<i4")])
+GQ = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("ur", "<f4")])
+
+
+def test_accept_rules_known_answers(oracle):
+    # (rule, d1, d2, nnratio, extra) -> expected; boundaries of TH_LOW = 50, TH_HIGH = 100 and of the ratio test
+    A = oracle.accept_top2
+    # BoW KF->F (ORBmatcher.cc:327-329): d1 <= 50 and d1 < 0.7 * d2 (float)
+    assert list(A(1, [50, 51, 35, 34, 0], [100, 100, 50, 50, 256], 0.7)) == [True, False, False, True, True]
+    # BoW KF<->KF (:848-850): strict d1 < 50
+    assert list(A(3, [50, 49], [100, 100], 0.7)) == [False, True]
+    # init (:697-699): same numbers as BoW KF->F
+    assert list(A(2, [50, 51, 35, 34], [100, 100, 50, 50], 0.9)) == [True, False, True, True]
+    # projection to map (:123-128): ratio applies only when both candidates are on the same level
+    assert list(A(0, [100, 101, 90, 90, 90], [100, 200, 100, 100, 256], 0.8, level1=[1, 1, 2, 2, 3], level2=[1, 1, 2, 3, -1])) == \
+        [False, False, False, True, True]
+    assert list(A(4, [100, 101], [0, 0])) == [True, False]
+    assert list(A(5, [50, 51], [0, 0])) == [True, False]
+    # fisheye knn (Frame.cc:1149): needs two results; 7 < 10 * 0.7 is False in double (7.0 < 7.000000000000001 is True!)
+    got = A(6, [7, 69, 70, 10], [10, 100, 100, 256], idx2=[3, 3, 3, -1])
+    assert list(got) == [bool(np.float64(7.0) < np.float64(np.float32(10)) * 0.7), True, bool(70.0 < 100 * 0.7), False]
+
+
+def _grid_search_numpy(kps, desc, bounds, queries, dq, skip=None, ur=None):
+    """Independent restatement (numpy/python) of Frame.cc:657-736 + ORBmatcher.cc:75-117."""
+    f32 = np.float32
+    mnx, mxx, mny, mxy = [f32(b) for b in bounds]
+    iw, ih = f32(64) / f32(mxx - mnx), f32(48) / f32(mxy - mny)
+    grid = {}
+    for i, k in enumerate(kps):
+        vx, vy = f32(f32(k["x"] - mnx) * iw), f32(f32(k["y"] - mny) * ih)
+        px = int(np.sign(vx) * np.floor(abs(vx) + f32(0.5)))  # roundf: half away from zero
+        py = int(np.sign(vy) * np.floor(abs(vy) + f32(0.5)))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    pop = np.unpackbits(np.arange(256, dtype=np.uint8)[:, None], axis=1).sum(1)
+    out = []
+    for qi, q in enumerate(queries):
+        x, y, r = f32(q["u"]), f32(q["v"]), f32(q["r"])
+        best = [256, -1, -1, 256, -1, -1]  # d1 i1 l1 d2 i2 l2
+        x0 = max(0, int(np.floor(f32(f32(f32(x - mnx) - r) * iw))))
+        x1 = min(63, int(np.ceil(f32(f32(f32(x - mnx) + r) * iw))))
+        y0 = max(0, int(np.floor(f32(f32(f32(y - mny) - r) * ih))))
+        y1 = min(47, int(np.ceil(f32(f32(f32(y - mny) + r) * ih))))
+        if not (x0 >= 64 or x1 < 0 or y0 >= 48 or y1 < 0):
+            check = q["min_level"] > 0 or q["max_level"] >= 0
+            for ix in range(x0, x1 + 1):
+                for iy in range(y0, y1 + 1):
+                    for i in grid.get((ix, iy), []):
+                        k = kps[i]
+                        if check and (k["octave"] < q["min_level"] or (q["max_level"] >= 0 and k["octave"] > q["max_level"])):
+                            continue
+                        if not (abs(f32(k["x"] - x)) < r and abs(f32(k["y"] - y)) < r):
+                            continue
+                        if skip is not None and skip[i]:
+                            continue
+                        if ur is not None and ur[i] > 0 and abs(f32(q["ur"] - ur[i])) > r:
+                            continue
+                        d = int(pop[desc[i] ^ dq[qi]].sum())
+                        if d < best[0]:
+                            best = [d, i, int(k["octave"]), best[0], best[1], best[2]]
+                        elif d < best[3]:
+                            best[3:] = [d, i, int(k["octave"])]
+        out.append(best)
+    o = np.array(out, dtype=np.int32)
+    return o[:, 1], o[:, 0], o[:, 4], o[:, 3], o[:, 2], o[:, 5]
+
+
+def make_grid_case(seed, nt=600, nq=200, w=752, h=480):
+    rng = np.random.default_rng(seed)
+    kps = np.zeros(nt, dtype=KP)
+    kps["x"] = rng.uniform(-5, w + 5, nt).astype(np.float32)
+    kps["y"] = rng.uniform(-5, h + 5, nt).astype(np.float32)
+    kps["x"][:40] = np.round(kps["x"][:40])  # integer coordinates sit on rounding boundaries of PosInGrid
+    kps["y"][:40] = np.round(kps["y"][:40])
+    kps["x"][40:80] = kps["x"][0]            # crowded cells: order inside a cell matters for ties
+    kps["y"][40:80] = kps["y"][0]
+    kps["octave"] = rng.integers(0, 8, nt)
+    desc = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    desc[40:80, 4:] = desc[40, 4:]           # near-duplicates -> distance ties
+    qs = np.zeros(nq, dtype=GQ)
+    src = rng.integers(0, nt, nq)
+    qs["u"] = kps["x"][src] + rng.uniform(-3, 3, nq).astype(np.float32)
+    qs["v"] = kps["y"][src] + rng.uniform(-3, 3, nq).astype(np.float32)
+    qs["r"] = rng.choice([7.0, 15.0, 30.0, 100.0], nq).astype(np.float32)
+    lv = kps["octave"][src]
+    mode = rng.integers(0, 3, nq)
+    qs["min_level"] = np.where(mode == 0, 0, np.where(mode == 1, lv - 1, lv))
+    qs["max_level"] = np.where(mode == 0, -1, lv)
+    qs["ur"] = qs["u"] - 10
+    qs["u"][:5] = [-200, 2000, 100, 100, 0]   # windows partly / fully outside the grid
+    qs["v"][:5] = [100, 100, -300, 900, 0]
+    dq = desc[src].copy()
+    flip = rng.integers(0, 256, (nq, 32), dtype=np.uint8) & rng.integers(0, 256, (nq, 32), dtype=np.uint8) & 0x11
+    dq ^= flip.astype(np.uint8)
+    skip = (rng.random(nt) < 0.1).astype(np.uint8)
+    ur = np.where(rng.random(nt) < 0.5, kps["x"] - rng.uniform(0, 40, nt), -1).astype(np.float32)
+    return kps, desc, (0.0, float(w), 0.0, float(h)), qs, dq, skip, ur
+
+
+@pytest.mark.parametrize("filters", [False, True])
+def test_grid_search_oracle_equals_numpy_restatement(oracle, filters):
+    kps, desc, bounds, qs, dq, skip, ur = make_grid_case(3, nt=300, nq=80)
+    if not filters:
+        skip = ur = None
+    got = oracle.search_grid_top2(kps, desc, bounds, qs, dq, skip, ur)
+    want = _grid_search_numpy(kps, desc, bounds, qs, dq, skip, ur)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    assert (got[0] >= 0).sum() > 40
+
+
+def stereo_case(oracle, w=640, h=360, nf=1000):
+    exl, exr = oracle.PortExtractor(nfeatures=nf), oracle.PortExtractor(nfeatures=nf)
+    _, kl, dl = exl.extract(synth.frame(0, w, h), (0, 0))
+    _, kr, dr = exr.extract(synth.frame(0, w, h, right=True), (0, 0))
+    t = exl.tables()
+    pl = [exl.pyramid(l) for l in range(8)]
+    pr = [exr.pyramid(l) for l in range(8)]
+    return kl, dl, kr, dr, t["scale"], t["inv_scale"], pl, pr
+
+
+def test_compute_stereo_matches_known_disparity(oracle):
+    """The synthetic right image is the left one shifted by exactly 16 px, so every refined match must report
+    uRight = uL - 16 up to the parabola's sub-pixel term, and depth = bf / disparity."""
+    kl, dl, kr, dr, sf, isf, pl, pr = stereo_case(oracle)
+    bf, b = 386.1448, 0.53716  # config/Stereo/KITTI00-02.yaml: fx * b, b
+    ur, dp = oracle.compute_stereo_matches(kl, dl, kr, dr, sf, isf, pl, pr, bf, b)
+    ok = ur >= 0
+    assert ok.sum() > 300
+    disp = kl["x"][ok] - ur[ok]
+    assert np.abs(disp - 16.0).max() < 2.5 and abs(np.median(disp) - 16.0) < 0.2
+    assert np.array_equal(dp[ok], (np.float32(bf) / disp.astype(np.float32)).astype(np.float32))
+    assert (dp[~ok] == -1).all() and (ur[~ok] == -1).all()
+    # no right keypoints -> nothing matched, no crash
+    ur0, dp0 = oracle.compute_stereo_matches(kl, dl, kr[:0], dr[:0], sf, isf, pl, pr, bf, b)
+    assert (ur0 == -1).all() and (dp0 == -1).all()

@@ -81,3 +81,14 @@ def test_descriptor_distance_swar(oracle):
     for x, y in zip(a, b):
         assert oracle.hamming(x, y) == int(np.unpackbits(x ^ y).sum())
     assert oracle.hamming(a[0], a[0]) == 0 and oracle.hamming(a[0], ~a[0]) == 256
+
+
+def test_stage_resize_then_gray_matches_cv2(oracle):
+    """Input staging (System.cc:420-425 resize, Tracking.cc:1569-1582 cvtColor) against the cv2 4.13 goldens."""
+    g = load_golden("stage.npz")
+    names = sorted(k[:-5] for k in g.files if k.endswith("_meta"))
+    assert len(names) >= 9
+    for name in names:
+        ch, rgb, nw, nh = [int(v) for v in g[name + "_meta"]]
+        got = oracle.stage_gray(g[name + "_src"], bool(rgb), (nw, nh) if nw else None)
+        assert np.array_equal(got, g[name + "_gray"]), name

@@ -107,6 +107,49 @@ def gen_primitives():
     print("primitives + match goldens written (cv2", cv2.__version__ + ")")
 
 
+STAGE_CASES = [
+    # name, source (w, h), channels, rgb (mbRGB), new size or None
+    ("rgb_same", (97, 61), 3, True, None),
+    ("bgr_same", (97, 61), 3, False, None),
+    ("rgba_same", (64, 48), 4, True, None),
+    ("bgra_half", (128, 96), 4, False, (64, 48)),
+    ("rgb_down", (160, 120), 3, True, (94, 60)),
+    ("bgr_up", (80, 60), 3, False, (101, 77)),
+    ("gray_down", (131, 97), 1, True, (100, 64)),
+    ("rgb_half", (120, 90), 3, True, (60, 45)),
+]
+
+
+def gen_stage():
+    """cv2.resize (on the interleaved colour image) then cv2.cvtColor(-> GRAY): System.cc:420-425 + Tracking.cc:1569-1582."""
+    import cv2
+    assert cv2.__version__.startswith("4.13"), cv2.__version__
+    rng = np.random.default_rng(77)
+    rec = {}
+    codes = {(3, True): cv2.COLOR_RGB2GRAY, (3, False): cv2.COLOR_BGR2GRAY, (4, True): cv2.COLOR_RGBA2GRAY,
+             (4, False): cv2.COLOR_BGRA2GRAY}
+    for name, (w, h), ch, rgb, new in STAGE_CASES:
+        shape = (h, w) if ch == 1 else (h, w, ch)
+        im = rng.integers(0, 256, shape, dtype=np.uint8)
+        if name.endswith("half"):  # smooth content too
+            im = cv2.GaussianBlur(im, (5, 5), 1.5)
+        out = im if new is None else cv2.resize(im, new)
+        if ch != 1:
+            out = cv2.cvtColor(out, codes[(ch, rgb)])
+        rec[name + "_src"] = im
+        rec[name + "_gray"] = out
+        rec[name + "_meta"] = np.array([ch, int(rgb), new[0] if new else 0, new[1] if new else 0])
+    # every (r, g, b) on a lattice that includes the extremes: pins the grey weights and the rounding
+    vals = np.array(sorted(set(list(range(0, 256, 9)) + [1, 127, 128, 254, 255])), dtype=np.uint8)
+    R, G, B = np.meshgrid(vals, vals, vals, indexing="ij")
+    cube = np.stack([R.ravel(), G.ravel(), B.ravel()], 1).reshape(1, -1, 3)
+    rec["cube_src"] = cube
+    rec["cube_gray"] = cv2.cvtColor(cube, cv2.COLOR_RGB2GRAY)
+    rec["cube_meta"] = np.array([3, 1, 0, 0])
+    np.savez_compressed(os.path.join(OUT, "stage.npz"), **rec)
+    print("staging goldens written (cv2", cv2.__version__ + ")")
+
+
 E2E_CASES = [
     # name, w, h, frame k, nfeatures, lapping area, right
     ("euroc752", 752, 480, 0, 1000, (0, 1000), False),
@@ -146,8 +189,10 @@ def gen_e2e():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    what = sys.argv[1:] or ["prim", "e2e"]
+    what = sys.argv[1:] or ["prim", "stage", "e2e"]
     if "prim" in what:
         gen_primitives()
+    if "stage" in what:
+        gen_stage()
     if "e2e" in what:
         gen_e2e()

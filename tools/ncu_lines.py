@@ -5,7 +5,7 @@ import csv, subprocess, sys
 rep, rx = sys.argv[1], sys.argv[2]
 minp = float(sys.argv[3]) if len(sys.argv) > 3 else 0.5
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--kernel-name",
-                      "regex:" + rx, "--launch-skip", "0", "--launch-count", "1"], capture_output=True, text=True).stdout
+                      "regex:" + rx, "--launch-count", "1"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hdr = next(r for r in rows if r and r[0] == "Line No")
 ci, sm = hdr.index("Instructions Executed"), hdr.index("# Samples")
