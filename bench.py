@@ -29,6 +29,7 @@ if ROOT not in sys.path:
 
 W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 LAP = (0, 1000)  # Frame.cc:311 passes {0,1000} for monocular frames
+SUBBATCHES = 1  # default of --subbatches (set from the measured sweep, profiles/)
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
 
 
@@ -220,6 +221,7 @@ def run_ours(args, rank, world, local_rank):
     F = args.frames
     ex = orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local_rank)
     cap = ex.capacity
+    ex.set_subbatches(args.subbatches)
     # two rotating input batches generated on the device (different frames per rank): 2 x 92 MB, and ~0.7 GB of
     # intermediates are rewritten every step, so nothing survives in the 126 MB L2 from one step to the next
     nb = 2
@@ -260,7 +262,12 @@ def run_ours(args, rank, world, local_rank):
     ms = e0.elapsed_time(e1)
     launches = orbx.launch_count() - launches0
     clocks = sampler.stop()
-    total_ms, stage_ms = ex.timing()  # last batch, CUDA events on the handle's stream
+    # per-stage times: one more batch with the stages back to back on one stream (in sub-batch mode the stages of
+    # different parts overlap and have no time of their own), CUDA events on the handle's stream
+    ex.set_subbatches(1)
+    ex.extract_batch_device(imgs[0].data_ptr(), F, W, H, LAP)
+    total_ms, stage_ms = ex.timing()
+    ex.set_subbatches(args.subbatches)
     n_dev = torch.empty(F, dtype=torch.int32, device=dev)
     d_kps, d_desc, d_n, d_mono, _ = ex.results_device()
     mono0, kp0, desc0 = ex.download(0)
@@ -400,6 +407,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=256, help="frames per batch (per GPU)")
     ap.add_argument("--db-rows", type=int, default=10_000_000)
+    ap.add_argument("--subbatches", type=int, default=SUBBATCHES,
+                    help="parts of a batch run concurrently on internal stream pairs (orbx_set_subbatches)")
     ap.add_argument("--skip-match", action="store_true")
     ap.add_argument("--skip-secondary", action="store_true", help="skip e2e / cfg5 / cpu_baseline legs (profiling runs)")
     ap.add_argument("--only-match", action="store_true", help="development: run only the cfg5 matching leg and print it")
@@ -447,7 +456,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": ctx["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": f"euroc752x480_nf1000_batch{F}_extract" + ("" if args.skip_match else "+consecutive_top2"),
-                   "frames_per_gpu_per_step": F, "nfeatures": NFEAT, "levels": NLEVELS, "fast": [INI_TH, MIN_TH],
+                   "frames_per_gpu_per_step": F, "subbatches": args.subbatches, "nfeatures": NFEAT, "levels": NLEVELS, "fast": [INI_TH, MIN_TH],
                    "l2": "inputs rotate over 2 device batches (2x92 MB) and ~0.7 GB of intermediates are rewritten per step (> 126 MB L2)",
                    "keypoints_per_frame": ctx["nkp"], "fast_candidates_frame0": ctx["ncand"]},
         "clocks": ctx["clocks"], "gpu_launches": int(ctx["launches"]),

@@ -121,6 +121,11 @@ int orbx_batch_results(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t
                        const int** d_mono, int* cap_per_frame);
 int orbx_batch_download(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
                         int* mono_index);
+/* Batch scheduling knob (default 1): with n > 1 a batch of at least 8n frames is cut into n contiguous parts that run
+ * the whole pipeline concurrently on n internal stream pairs (frames are independent), forked from and joined back into
+ * the handle's stream, so one part's latency-bound stages (quadtree, describe) share the SMs with another part's
+ * issue-bound ones.  Results are identical; orbx_last_timing then reports only the total. */
+int orbx_set_subbatches(orbx_handle h, int n);
 /* Blocks until the handle's stream is idle (batch_device is asynchronous). */
 int orbx_sync(orbx_handle h);
 /* The handle's cudaStream_t (for callers that record their own events around a run of batch calls). */

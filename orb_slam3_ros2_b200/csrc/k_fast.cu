@@ -335,8 +335,8 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
-        if (!wide) launchClass<64>(P, B, F, mask, cells, B.errFlag + 4, s);
-        else launchClass<96>(P, B, F, mask, cells, B.errFlag + 5, s);
+        if (!wide) launchClass<64>(P, B, F, mask, cells, B.workCtr, s);
+        else launchClass<96>(P, B, F, mask, cells, B.workCtr + 1, s);
     }
 }
 

@@ -66,6 +66,11 @@ struct orbx_extractor {
     cudaStream_t stream = nullptr;
     cudaStream_t aux = nullptr;  // blur runs here, beside FAST + quadtree on `stream` (both only need the pyramid)
     cudaEvent_t ev[9] = {};      // 0..5 stage boundaries on `stream`; 6 pyramid done -> aux, 7/8 blur begin/end on aux
+    // sub-batch mode (orbx_set_subbatches): part p of a batch runs the whole pipeline on subS[p] (+ subX[p] for the blur)
+    int nSub = 1;
+    bool lastSplit = false;
+    cudaStream_t subS[8] = {}, subX[8] = {};
+    cudaEvent_t subFork = nullptr, subBlur0[8] = {}, subBlur1[8] = {}, subDone[8] = {};
     // plan + buffers of the current (W, H, capacity F)
     FramePlan plan{};
     bool havePlan = false;
@@ -204,8 +209,8 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         ORBX_CUDA(h->mOutD.reserve(f * P.outCap * 32));
         ORBX_CUDA(h->mOutN.reserve(f * 4));
         ORBX_CUDA(h->mOutM.reserve(f * 4));
-        ORBX_CUDA(h->mErr.reserve(64));  // [0] error flags, [4..] work counters of persistent kernels
-        ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 64, h->stream));
+        ORBX_CUDA(h->mErr.reserve(256));  // [0] error flags, [4 + 2p ..] work counters of persistent kernels, sub-batch p
+        ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 256, h->stream));
         h->capFrames = F;
     }
     Buffers& B = h->buf;
@@ -213,12 +218,61 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.cand = (uint32_t*)h->mCand.p; B.cellCnt = (int*)h->mCellCnt.p; B.gath = (uint32_t*)h->mGath.p;
     B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.sorted = (LevelKp*)h->mSlot.p;
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
-    B.tab = (int16_t*)h->mTab.p; B.errFlag = (int*)h->mErr.p;
+    B.tab = (int16_t*)h->mTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
+    return ORBX_OK;
+}
+
+// Buffers of frames [f0, ...) of the batch, with the work counters of sub-batch `part`
+static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int part) {
+    Buffers O = B;
+    const size_t f = (size_t)f0;
+    O.pyr += f * P.frameBytes; O.blur += f * P.blurBytes; O.cand += f * P.candWords; O.cellCnt += f * P.nCellsTotal;
+    O.gath += f * P.gathWords; O.nid += f * P.gathWords; O.lkp += f * P.lkpTotal; O.lkpCnt += f * P.nlevels;
+    O.sorted += f * P.outCap; O.outKps = (uint8_t*)O.outKps + f * P.outCap * 28; O.outDesc += f * P.outCap * 32;
+    O.outN += f; O.outMono += f;
+    O.workCtr = B.errFlag + 4 + 2 * part;
+    return O;
+}
+
+// Sub-batch mode: the batch is cut into nSub contiguous parts, each running the whole pipeline on its own stream pair.
+// Frames are independent, so the parts only share the SMs: one part's latency-bound stages (quadtree, describe) run
+// beside another part's issue-bound ones (FAST, blur, resize) instead of each stage owning the whole GPU in turn.
+static int runPipelineSplit(orbx_extractor* h, const uint8_t* dImgs, int stride, size_t frameStride, int F, int lap0, int lap1) {
+    const FramePlan& P = h->plan;
+    cudaStream_t s = h->stream;
+    const int n = h->nSub;
+    cudaEventRecord(h->ev[0], s);
+    cudaEventRecord(h->subFork, s);
+    for (int p = 0; p < n; ++p) {
+        const int f0 = (int)((long long)F * p / n), f1 = (int)((long long)F * (p + 1) / n);
+        if (f1 <= f0) continue;
+        const Buffers B = offsetBuffers(h->buf, P, f0, p);
+        const uint8_t* img = dImgs + (size_t)f0 * frameStride;
+        cudaStream_t a = h->subS[p], x = h->subX[p];
+        cudaStreamWaitEvent(a, h->subFork, 0);
+        launchPyramid(P, B, img, stride, frameStride, f1 - f0, a);
+        launchFast(P, B, f1 - f0, a);
+        cudaEventRecord(h->subBlur0[p], a);
+        cudaStreamWaitEvent(x, h->subBlur0[p], 0);
+        launchBlur(P, B, f1 - f0, x);
+        cudaEventRecord(h->subBlur1[p], x);
+        launchQuadtree(P, B, f1 - f0, a);
+        cudaStreamWaitEvent(a, h->subBlur1[p], 0);
+        launchDescribe(P, B, f1 - f0, lap0, lap1, a);
+        cudaEventRecord(h->subDone[p], a);
+        cudaStreamWaitEvent(s, h->subDone[p], 0);
+    }
+    cudaEventRecord(h->ev[5], s);
+    h->lastFrames = F;
+    h->lastSplit = true;
+    ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
 }
 
 // the whole operator() pipeline for F device-resident frames, asynchronous on the handle's stream
 static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size_t frameStride, int F, int lap0, int lap1) {
+    if (h->nSub > 1 && F >= 8 * h->nSub) return runPipelineSplit(h, dImgs, stride, frameStride, F, lap0, lap1);
+    h->lastSplit = false;
     const FramePlan& P = h->plan;
     const Buffers& B = h->buf;
     cudaStream_t s = h->stream;
@@ -320,6 +374,14 @@ void orbx_destroy(orbx_handle h) {
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 9; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (int p = 0; p < 8; ++p) {
+        if (h->subS[p]) cudaStreamDestroy(h->subS[p]);
+        if (h->subX[p]) cudaStreamDestroy(h->subX[p]);
+        if (h->subBlur0[p]) cudaEventDestroy(h->subBlur0[p]);
+        if (h->subBlur1[p]) cudaEventDestroy(h->subBlur1[p]);
+        if (h->subDone[p]) cudaEventDestroy(h->subDone[p]);
+    }
+    if (h->subFork) cudaEventDestroy(h->subFork);
     if (h->aux) cudaStreamDestroy(h->aux);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -516,6 +578,23 @@ int orbx_get_staged_gray(orbx_handle h, uint8_t* out, int* w, int* hgt) {
     return ORBX_OK;
 }
 
+int orbx_set_subbatches(orbx_handle h, int n) {
+    if (!h || n < 1 || n > 8) return fail(ORBX_ERR_ARG, "sub-batch count must be in [1, 8]");
+    DeviceGuard guard(h->device);
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    if (!h->subFork) ORBX_CUDA(cudaEventCreateWithFlags(&h->subFork, cudaEventDisableTiming));
+    for (int p = 0; p < n; ++p) {
+        if (h->subS[p]) continue;
+        ORBX_CUDA(cudaStreamCreateWithFlags(&h->subS[p], cudaStreamNonBlocking));
+        ORBX_CUDA(cudaStreamCreateWithFlags(&h->subX[p], cudaStreamNonBlocking));
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->subBlur0[p], cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->subBlur1[p], cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->subDone[p], cudaEventDisableTiming));
+    }
+    h->nSub = n;
+    return ORBX_OK;
+}
+
 int orbx_sync(orbx_handle h) {
     if (!h) return fail(ORBX_ERR_ARG, "null handle");
     DeviceGuard guard(h->device);
@@ -530,8 +609,9 @@ int orbx_last_timing(orbx_handle h, float* total_ms, float stage_ms[5]) {
     DeviceGuard guard(h->device);
     ORBX_CUDA(cudaEventSynchronize(h->ev[5]));
     if (total_ms) ORBX_CUDA(cudaEventElapsedTime(total_ms, h->ev[0], h->ev[5]));
-    if (stage_ms)
-    {
+    if (stage_ms && h->lastSplit) {  // the stages of different sub-batches overlap: there is no per-stage time
+        for (int i = 0; i < 5; ++i) stage_ms[i] = 0.f;
+    } else if (stage_ms) {
         // pyramid, fast, quadtree on the main stream; blur from its own events on the aux stream (it overlaps fast and
         // quadtree, so the stage times no longer add up to the total); describe after the join
         ORBX_CUDA(cudaEventElapsedTime(&stage_ms[0], h->ev[0], h->ev[1]));

@@ -81,6 +81,7 @@ struct Buffers {
     int* outMono;        // F
     int16_t* tab;        // resize coefficient tables
     int* errFlag;        // device-side invariant violations (capacity overflow)
+    int* workCtr;        // two work counters of the persistent FAST launches (distinct per concurrently running sub-batch)
 };
 
 // kernel launchers (each in its own .cu); all asynchronous on `s`

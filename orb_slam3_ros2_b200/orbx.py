@@ -66,6 +66,7 @@ SYMBOLS = {
     "orbx_batch_results": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i32p]),
     "orbx_batch_download": (C.c_int, [_vp, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
     "orbx_sync": (C.c_int, [_vp]),
+    "orbx_set_subbatches": (C.c_int, [_vp, C.c_int]),
     "orbx_get_stream": (_vp, [_vp]),
     "orbx_last_timing": (C.c_int, [_vp, _f32p, _f32p]),
     "orbx_get_candidates": (C.c_int, [_vp, C.c_int, C.c_int, _i32p, C.c_int, _i32p]),
@@ -184,6 +185,9 @@ class ORBextractor:
         if pyramid:
             self.mvImagePyramid = [self.pyramid_level(0, l)[19:-19, 19:-19] for l in range(self.nlevels)]
         return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def set_subbatches(self, n):
+        _check(lib().orbx_set_subbatches(self._h, int(n)))
 
     def extract_color(self, image, rgb=True, new_size=None, vLappingArea=(0, 1000)):
         """System::Track*'s resize (System.cc:420-425) + Tracking::GrabImage*'s cvtColor (Tracking.cc:1569-1582) fused

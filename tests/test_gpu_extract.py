@@ -163,3 +163,25 @@ def test_batch_equals_single_frame_and_device_synth(orbx, oracle):
         for g_, w_ in zip(got, want):
             assert np.array_equal(g_, w_)
     assert orbx.accept_bow(d1[0, :n[0]], d2m[0, :n[0]]).sum() > 100  # the synthetic stream really overlaps
+
+
+@pytest.mark.parametrize("nsub", [2, 3])
+def test_subbatch_streams_give_identical_results(orbx, nsub):
+    """orbx_set_subbatches: parts of the batch on concurrent stream pairs; frames are independent, so nothing changes."""
+    F, w, h = 26, 640, 360
+    imgs = synth.frames(3, F, w, h)
+    ex = orbx.ORBextractor(1250, 1.2, 8, 20, 7)
+    want = ex.extract_batch(imgs, (300, 600))
+    wm = ex.match_consecutive()
+    ex.set_subbatches(nsub)
+    for _ in range(2):  # twice: the work counters and scratch of the parts must reset correctly
+        got = ex.extract_batch(imgs, (300, 600))
+        gm = ex.match_consecutive()
+        n = want[1]
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], n)
+        for f in range(F):
+            assert np.array_equal(got[2][f, :n[f]], want[2][f, :n[f]]) and np.array_equal(got[3][f, :n[f]], want[3][f, :n[f]])
+        for a, b in zip(gm, wm):
+            for f in range(F - 1):
+                assert np.array_equal(a[f, :n[f]], b[f, :n[f]])
+    assert ex.timing()[0] > 0
