@@ -29,7 +29,8 @@ if ROOT not in sys.path:
 
 W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 LAP = (0, 1000)  # Frame.cc:311 passes {0,1000} for monocular frames
-SUBBATCHES = 1  # default of --subbatches (set from the measured sweep, profiles/)
+E2E_HANDLES = 4  # measured sweep (profiles/): 2 -> 85.0k, 3 -> 89.5k, 4 -> 90.3k, 6 -> 81.0k frames/s
+SUBBATCHES = 2  # default of --subbatches; measured sweep (profiles/r01_v6_subbatch_sweep_*): 1 -> 108.7k, 2 -> 113.3k, 3 -> 113.2k, 4 -> 113.0k, 6 -> 106.4k
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
 
 
@@ -296,9 +297,10 @@ def run_e2e(ctx, args, world):
     F, cap = ctx["F"], ctx["cap"]
     h_img = torch.empty((F, H, W), dtype=torch.uint8).pin_memory()
     h_img.copy_(ctx["imgs"][0].cpu())
-    half = F // 2
-    # handle 0: frames [0, half); handle 1: frames [half-1, F) so that the pair (half-1, half) is matched too
-    parts = [(0, half), (half - 1, F - half + 1)] if F >= 4 else [(0, F)]
+    # handle i takes frames [b_i - 1, b_{i+1}) (b_i = F*i/K; the one-frame overlap keeps the pair (b_i - 1, b_i) matched)
+    K = max(1, min(args.e2e_handles, F // 4)) if F >= 4 else 1
+    cuts = [F * i // K for i in range(K + 1)]
+    parts = [(max(cuts[i] - 1, 0), cuts[i + 1] - max(cuts[i] - 1, 0)) for i in range(K)]
     handles = [ctx["ex"]] + [orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=ctx["dev"].index) for _ in parts[1:]]
     bufs = []
     for lo, cnt in parts:
@@ -343,7 +345,7 @@ def run_e2e(ctx, args, world):
         ex.close()
     return {"value": world * F * steps / dt, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": steps, "handles": len(handles),
-            "api": "orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check on 2 handles (pinned host buffers)"}
+            "api": f"orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check on {len(handles)} handles (pinned host buffers)"}
 
 
 def run_match_cfg5(ctx, args, rank, world, local_rank):
@@ -409,6 +411,8 @@ def main():
     ap.add_argument("--db-rows", type=int, default=10_000_000)
     ap.add_argument("--subbatches", type=int, default=SUBBATCHES,
                     help="parts of a batch run concurrently on internal stream pairs (orbx_set_subbatches)")
+    ap.add_argument("--e2e-handles", type=int, default=E2E_HANDLES, help="extractor handles the e2e leg pipelines a step over")
+    ap.add_argument("--only-e2e", action="store_true", help="development: resident leg + e2e leg only, print the e2e object")
     ap.add_argument("--skip-match", action="store_true")
     ap.add_argument("--skip-secondary", action="store_true", help="skip e2e / cfg5 / cpu_baseline legs (profiling runs)")
     ap.add_argument("--only-match", action="store_true", help="development: run only the cfg5 matching leg and print it")
@@ -443,8 +447,16 @@ def main():
     launches_in_stage = {"pyramid": NLEVELS, "fast_cells": 1, "quadtree": 1, "blur": 1, "describe": 2}[STAGES[dom]]
     alg = stage_algorithmic_bytes(STAGES[dom], ctx["nkp"], ctx["ncand"]) * F
     achieved = alg / (stage_ms[dom] * 1e-3) / 1e9
+    # DRAM traffic of the stage from the committed ncu --set full capture of this same workload (per launch, like `achieved`)
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "traffic_r01.json")
+    if os.path.exists(tp) and (W, H) == (752, 480):
+        tj = json.load(open(tp))
+        if STAGES[dom] in tj:
+            traffic = tj[STAGES[dom]]["total"] / tj["frames"] * F / launches_in_stage
+            traffic_src = tj["source"]
     roofline = {"kernel": STAGES[dom], "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg / launches_in_stage, "launches": launches_in_stage,
                 "avg_launch_ms": stage_ms[dom] / launches_in_stage,
                 "share_of_extract": stage_ms[dom] / max(ctx["total_ms"], 1e-9)}
@@ -463,6 +475,11 @@ def main():
         "stage_ms_last_batch": dict(zip(STAGES, [round(x, 4) for x in stage_ms])), "extract_ms_last_batch": ctx["total_ms"],
         "roofline": roofline, "pipeline_roofline": pipeline,
     }
+    if args.only_e2e:
+        e = run_e2e(ctx, args, world)
+        if rank == 0:
+            print(json.dumps({"value": ctx["fps"], "e2e": e}), flush=True)
+        return
     if not args.skip_secondary:
         out["e2e"] = run_e2e(ctx, args, world)
         out["match"] = run_match_cfg5(ctx, args, rank, world, local_rank)

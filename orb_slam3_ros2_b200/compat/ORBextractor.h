@@ -53,6 +53,10 @@ public:
     // back from the device.  Default true = reference behaviour.
     bool downloadPyramid = true;
 
+    // The C-ABI handle behind this instance, for callers that move a consumer of the device-resident pyramid onto the
+    // GPU too (orbx_compute_stereo_matches takes the left and right extractors' handles; Frame.cc:811-980).
+    orbx_extractor* handle() const { return mHandle; }
+
 protected:
     int nfeatures;
     double scaleFactor;

@@ -3,6 +3,7 @@
 // entry point needs a CUDA device and fails with ORBX_ERR_CUDA otherwise.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <atomic>
 #include <mutex>
