@@ -139,7 +139,9 @@ __global__ void __launch_bounds__(256) slotKernel(const __grid_constant__ FrameP
 // the 128-B-pitched plane has the same misalignment, so one funnel shift amount serves the whole patch); each word
 // goes through two byte dot products against per-(row, word) coefficient words — u (signed, 0 outside the disc) for
 // m10 and the 0/1 disc mask for the row sum of m01.  248 words / 32 lanes = 8 per lane, all loads independent.
-constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitch = 64;
+constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1;
+// 80-byte rows (5 x 16 B, 4 used): 20 words per row spread the rows over 8 bank phases; a 64-byte pitch has only 2
+constexpr int kPatchPitch = 80;
 __device__ uint2 gIcCoef[248];   // x: s8 u-coefficients, y: u8 disc mask, entry = row * 8 + word
 __device__ float4 gPatternF[256];
 
@@ -161,7 +163,9 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
     __shared__ float4 sPat[256];
     __shared__ uint2 sCoef[248];
     __shared__ __align__(16) uint8_t sPatch[8][kPatchRows * kPatchPitch];
-    sPat[threadIdx.x] = gPatternF[threadIdx.x];
+    // transposed: pair 8*lane + k lives at [k][lane], so the 32 lanes of a warp read 32 consecutive float4 (the
+    // [lane][k] order put every lane on the same banks: an 8-way conflict on each of the 8 loads per keypoint)
+    sPat[(threadIdx.x & 7) * 32 + (threadIdx.x >> 3)] = gPatternF[threadIdx.x];
     if (threadIdx.x < 248) sCoef[threadIdx.x] = gIcCoef[threadIdx.x];
     __syncthreads();
     const int lane = threadIdx.x & 31;
@@ -243,7 +247,7 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
 #pragma unroll
     for (int it = 0; it < 5; ++it) {
         const int item = it * 32 + lane;
-        if (item < kPatchRows * 4) reinterpret_cast<uint4*>(patch)[item] = pv[it];
+        if (item < kPatchRows * 4) reinterpret_cast<uint4*>(patch)[(item >> 2) * (kPatchPitch / 16) + (item & 3)] = pv[it];
     }
     __syncwarp();
     const uint8_t* center = patch + kPatchR * kPatchPitch + (kp.x - bx0);
@@ -252,7 +256,7 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
     uint32_t t0[8], t1[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const float4 pt = sPat[lane * 8 + k];
+        const float4 pt = sPat[k * 32 + lane];
         int r0, c0, r1, c1;
         if (strict) {
             r0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
