@@ -62,8 +62,13 @@ __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32
     return __vimax3_s16x2_relu(__vsub2(cen, A), __vsub2(B, cen), 0u);
 }
 
-// PITCH = bytes per tile row in shared memory (multiple of 16)
-template <int PITCH>
+// PITCH = bytes per tile row in shared memory (multiple of 16).
+// SHIFTED = true : tile x = cell x + (global column & 15): rows are copied chunk for chunk (cells up to 76 px wide).
+// SHIFTED = false: tile x = cell x: the staging realigns the row with funnel shifts, so a cell of <= 48 columns fits a
+//                  48-byte row.  12 words per row spread consecutive rows over 8 bank phases (a 64-byte row has 2: rows y and
+//                  y+2 collide, which cost the ring gathers 2.3 wavefronts per load), the quick test's chunk index becomes
+//                  contiguous, and its left / right neighbour words come from the neighbouring lanes instead of shared memory.
+template <int PITCH, bool SHIFTED>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     fastCellsKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
                     int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes, unsigned levelMask,
@@ -115,13 +120,38 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
 
     // ---- stage the cell with 128-bit loads; clear the arc map --------------------------------------------------
     const int gx0 = kEdge + iniX;
-    const int shift = gx0 & 15;
-    {
+    const int shift = SHIFTED ? (gx0 & 15) : 0;
+    if (SHIFTED) {
         const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + (gx0 - shift);
         const int n16 = ch * P16, nArc = (ch - 4) * P16;
         for (int i = lane; i < n16; i += 32) {
             const int r = i / P16, k = i - r * P16;
             const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * L.pitch) + k);
+            reinterpret_cast<uint4*>(tile)[i] = v;
+            if (i < nArc) reinterpret_cast<uint4*>(arcStore)[i] = make_uint4(0, 0, 0, 0);
+        }
+    } else {
+        // output chunk k of a row = bytes [16k + s, 16k + s + 16) of the 16-B aligned source row, s = gx0 & 15: two aligned
+        // 128-bit loads, a warp-uniform word offset and four funnel shifts
+        const int s16 = gx0 & 15, wsel = s16 >> 2, bsh = (s16 & 3) * 8;
+        const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + (gx0 - s16);
+        const int n16 = ch * P16, nArc = (ch - 4) * P16;
+        const int nIn = (s16 + cw + 15) >> 4;  // aligned source chunks that hold pixels of the cell
+        for (int i = lane; i < n16; i += 32) {
+            const int r = i / P16, k = i - r * P16;
+            const uint4* row = reinterpret_cast<const uint4*>(src + (size_t)r * L.pitch);
+            const uint4 a = k < nIn ? __ldg(row + k) : make_uint4(0, 0, 0, 0);
+            const uint4 b = (s16 != 0 && k + 1 < nIn) ? __ldg(row + k + 1) : make_uint4(0, 0, 0, 0);
+            uint32_t w0, w1, w2, w3, w4;
+            switch (wsel) {
+                case 0: w0 = a.x; w1 = a.y; w2 = a.z; w3 = a.w; w4 = b.x; break;
+                case 1: w0 = a.y; w1 = a.z; w2 = a.w; w3 = b.x; w4 = b.y; break;
+                case 2: w0 = a.z; w1 = a.w; w2 = b.x; w3 = b.y; w4 = b.z; break;
+                default: w0 = a.w; w1 = b.x; w2 = b.y; w3 = b.z; w4 = b.w; break;
+            }
+            uint4 v;
+            v.x = __funnelshift_r(w0, w1, bsh); v.y = __funnelshift_r(w1, w2, bsh);
+            v.z = __funnelshift_r(w2, w3, bsh); v.w = __funnelshift_r(w3, w4, bsh);
             reinterpret_cast<uint4*>(tile)[i] = v;
             if (i < nArc) reinterpret_cast<uint4*>(arcStore)[i] = make_uint4(0, 0, 0, 0);
         }
@@ -147,15 +177,33 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
 
         // ---- quick reject, 16 pixels per lane: flagged chunks appended in row-major order ------------------------
         int nG = 0;
-        for (int i0 = 0; i0 < nItems; i0 += 32) {
+        // SHIFTED: 32 consecutive items per sweep.  Unshifted: whole rows per sweep (lane = row-in-sweep * nC + chunk), so a
+        // chunk's left / right neighbour words are the neighbouring lanes' registers.
+        const int rowsPerSweep = SHIFTED ? 0 : 32 / nC;
+        const int itemsPerSweep = SHIFTED ? 32 : rowsPerSweep * nC;
+        for (int i0 = 0; i0 < nItems; i0 += itemsPerSweep) {
             const int i = i0 + lane;
+            const bool act = i < nItems && lane < itemsPerSweep;
             uint32_t m = 0;
-            if (i < nItems) {
+            int cx = 0, idx = 0;
+            uint4 cc = make_uint4(0, 0, 0, 0), up = cc, dn = cc;
+            if (act) {
                 const int r = (int)(((unsigned)i * divC) >> 16);
-                const int cx = c0 + (i - r * nC);
-                const int idx = (r + 3) * P16 + cx;
-                const uint4 cc = tile128[idx], up = tile128[idx - 3 * P16], dn = tile128[idx + 3 * P16];
-                const uint32_t lw = tile32[4 * idx - 1], rw = tile32[4 * idx + 4];
+                cx = c0 + (i - r * nC);
+                idx = (r + 3) * P16 + cx;
+                cc = tile128[idx]; up = tile128[idx - 3 * P16]; dn = tile128[idx + 3 * P16];
+            }
+            uint32_t lw, rw;
+            if (SHIFTED) {
+                lw = act ? tile32[4 * idx - 1] : 0u;
+                rw = act ? tile32[4 * idx + 4] : 0u;
+            } else {
+                // chunk 0 never needs its left word (pixels 0..2 are not tested); the last chunk of a row reads its right one
+                lw = __shfl_up_sync(0xffffffffu, cc.w, 1);
+                rw = __shfl_down_sync(0xffffffffu, cc.x, 1);
+                if (act && cx == nC - 1) rw = tile32[4 * idx + 4];
+            }
+            if (act) {
                 const uint32_t cw4[6] = {lw, cc.x, cc.y, cc.z, cc.w, rw};
                 const uint32_t uw[4] = {up.x, up.y, up.z, up.w}, dw4[4] = {dn.x, dn.y, dn.z, dn.w};
 #pragma unroll
@@ -300,20 +348,20 @@ FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch) {
     return g;
 }
 
-template <int PITCH>
+template <int PITCH, bool SHIFTED>
 void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, int* counter, cudaStream_t s) {
     const FastGeom g = geomFor(P, mask, PITCH);
     const size_t smem = (size_t)g.warpBytes * kWarpsPerCta;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<PITCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<PITCH, SHIFTED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int dev = 0, sms = 148, perSm = 1;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fastCellsKernel<PITCH>, kWarpsPerCta * 32, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fastCellsKernel<PITCH, SHIFTED>, kWarpsPerCta * 32, smem);
     const long long total = (long long)cells * F;
     const long long want = (total + kWarpsPerCta - 1) / kWarpsPerCta;
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
     cudaMemsetAsync(counter, 0, sizeof(int), s);
-    fastCellsKernel<PITCH><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, mask,
+    fastCellsKernel<PITCH, SHIFTED><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, mask,
                                                                  cells, (int)total, counter);
     countLaunch();
 }
@@ -321,22 +369,22 @@ void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int
 }  // namespace
 
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
-    // Two launches at most: levels whose cells fit the 64-byte tile row (shift <= 15, cell width wCell+6 <= 45, one
-    // spare word to the right) and 50 rows — every level of a large image — and the few small levels with wider or
-    // taller cells (wCell, hCell <= 70 always, since nCols = floor(width / 35); 15 + 76 + 4 <= 96).
+    // Two launches at most: levels whose cells fit a 48-byte unshifted tile row (cell width wCell+6 <= 48) and 50 rows —
+    // every level of a large image — and the few small levels with wider or taller cells, staged chunk for chunk with
+    // the global misalignment kept (wCell, hCell <= 70 always, since nCols = floor(width / 35); 15 + 76 + 4 <= 96).
     for (int wide = 0; wide < 2; ++wide) {
         unsigned mask = 0;
         int cells = 0;
         for (int l = 0; l < P.nlevels; ++l) {
             const LevelPlan& L = P.lv[l];
             if (L.nCols <= 0 || L.nRows <= 0) continue;
-            if ((15 + L.wCell + 6 + 4 > 64 || L.hCell + 6 > 50) != (wide == 1)) continue;
+            if ((L.wCell + 6 > 48 || L.hCell + 6 > 50) != (wide == 1)) continue;
             mask |= 1u << l;
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
-        if (!wide) launchClass<64>(P, B, F, mask, cells, B.workCtr, s);
-        else launchClass<96>(P, B, F, mask, cells, B.workCtr + 1, s);
+        if (!wide) launchClass<48, false>(P, B, F, mask, cells, B.workCtr, s);
+        else launchClass<96, true>(P, B, F, mask, cells, B.workCtr + 1, s);
     }
 }
 
