@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) pyrLevel0AlignedKernel(const uint8_t* __r
 // SPT = bytes per staged source row (compile-time so that the row loops unroll into immediate offsets).
 constexpr int kRowTiles = 4;
 
-template <int SPT>
+template <int SPT, bool WINDOWED>
 __global__ void __launch_bounds__(256)
     pyrResizeKernel(uint8_t* __restrict__ pyr, unsigned frameBytes, unsigned srcOff, int sw, int sh, int spitch,
                     unsigned dstOff, int dw, int dh, int dpitch, const short4* __restrict__ tabX,
@@ -136,6 +136,19 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int j = 0; j < 4; ++j) { o0[j] += kEdge - A0; o1[j] += kEdge - A0; }
     const int X = X0 + 4 * lane;
+    // The 4 columns of a lane read source bytes within a window of <= 8 bytes whenever the scale step is <= 2 (always at
+    // ORB-SLAM3's 1.2): then a source row costs the lane three aligned 32-bit loads and two funnel shifts, and each
+    // (p0, p1) pair is one PRMT away from the two-way dot product with (a0, a1).  Wider windows keep the byte loads.
+    int wLo = min(min(o0[0], o0[1]), min(o0[2], o0[3]));
+    const int wHi = max(max(o1[0], o1[1]), max(o1[2], o1[3]));
+    (void)wHi;  // WINDOWED is chosen on the host: source step < 2 => wHi - wLo <= 7
+    const int wOfs = wLo & ~3, wSh = (wLo & 3) * 8;
+    uint32_t sel[4], cf[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        sel[j] = (uint32_t)((o0[j] - wLo) & 7) | ((uint32_t)((o1[j] - wLo) & 7) << 4);
+        cf[j] = (uint32_t)a0[j] | ((uint32_t)a1[j] << 16);
+    }
 
     for (int rt = 0; rt < kRowTiles; ++rt) {
         const int Y0 = (blockIdx.y * kRowTiles + rt) * kTH;
@@ -168,14 +181,28 @@ __global__ void __launch_bounds__(256)
         __syncthreads();
 
         // ---- horizontal pass: H[s][x] = (p0*a0 + p1*a1) >> 4  (<= 32640) ------------------------------------------
-        for (int s = warp; s < nS; s += 8) {
-            const uint8_t* row = sSrc + s * SPT;
-            uint4 hv;
-            hv.x = (uint32_t)((int)row[o0[0]] * a0[0] + (int)row[o1[0]] * a1[0]) >> 4;
-            hv.y = (uint32_t)((int)row[o0[1]] * a0[1] + (int)row[o1[1]] * a1[1]) >> 4;
-            hv.z = (uint32_t)((int)row[o0[2]] * a0[2] + (int)row[o1[2]] * a1[2]) >> 4;
-            hv.w = (uint32_t)((int)row[o0[3]] * a0[3] + (int)row[o1[3]] * a1[3]) >> 4;
-            *reinterpret_cast<uint4*>(sH + s * kTW + 4 * lane) = hv;
+        if (WINDOWED) {
+            for (int s = warp; s < nS; s += 8) {
+                const uint32_t* row = reinterpret_cast<const uint32_t*>(sSrc + s * SPT + wOfs);
+                const uint32_t w0 = row[0], w1 = row[1], w2 = row[2];
+                const uint32_t lo = __funnelshift_r(w0, w1, wSh), hi = __funnelshift_r(w1, w2, wSh);
+                uint4 hv;
+                hv.x = __dp2a_lo(cf[0], __byte_perm(lo, hi, sel[0]), 0u) >> 4;
+                hv.y = __dp2a_lo(cf[1], __byte_perm(lo, hi, sel[1]), 0u) >> 4;
+                hv.z = __dp2a_lo(cf[2], __byte_perm(lo, hi, sel[2]), 0u) >> 4;
+                hv.w = __dp2a_lo(cf[3], __byte_perm(lo, hi, sel[3]), 0u) >> 4;
+                *reinterpret_cast<uint4*>(sH + s * kTW + 4 * lane) = hv;
+            }
+        } else {
+            for (int s = warp; s < nS; s += 8) {
+                const uint8_t* row = sSrc + s * SPT;
+                uint4 hv;
+                hv.x = (uint32_t)((int)row[o0[0]] * a0[0] + (int)row[o1[0]] * a1[0]) >> 4;
+                hv.y = (uint32_t)((int)row[o0[1]] * a0[1] + (int)row[o1[1]] * a1[1]) >> 4;
+                hv.z = (uint32_t)((int)row[o0[2]] * a0[2] + (int)row[o1[2]] * a1[2]) >> 4;
+                hv.w = (uint32_t)((int)row[o0[3]] * a0[3] + (int)row[o1[3]] * a1[3]) >> 4;
+                *reinterpret_cast<uint4*>(sH + s * kTW + 4 * lane) = hv;
+            }
         }
         __syncthreads();
 
@@ -201,16 +228,16 @@ __global__ void __launch_bounds__(256)
 
 }  // namespace
 
-template <int SPT>
-static void launchResize(const FramePlan& P, const Buffers& B, int l, int F, cudaStream_t s) {
+template <int SPT, bool WINDOWED>
+static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cudaStream_t s) {
     const LevelPlan& S = P.lv[l - 1];
     const LevelPlan& D = P.lv[l];
     const int pw = D.w + 2 * kEdge, ph = D.h + 2 * kEdge;
     const int maxRows = (int)((double)kTH * S.h / D.h) + 4;  // source rows a 32-row tile can need
     const size_t smem = (size_t)maxRows * (SPT + kTW * 4);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(pyrResizeKernel<SPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(pyrResizeKernel<SPT, WINDOWED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((pw + kTW - 1) / kTW, ((ph + kTH - 1) / kTH + kRowTiles - 1) / kRowTiles, F);
-    pyrResizeKernel<SPT><<<grid, 256, smem, s>>>(B.pyr, P.frameBytes, S.planeOff, S.w, S.h, S.pitch, D.planeOff, D.w, D.h,
+    pyrResizeKernel<SPT, WINDOWED><<<grid, 256, smem, s>>>(B.pyr, P.frameBytes, S.planeOff, S.w, S.h, S.pitch, D.planeOff, D.w, D.h,
                                                  D.pitch, reinterpret_cast<const short4*>(B.tab) + D.tabX,
                                                  reinterpret_cast<const short4*>(B.tab) + D.tabY, maxRows);
     countLaunch();
@@ -238,9 +265,12 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
     for (int l = 1; l < P.nlevels; ++l) {
         // bytes of a source row a 128-column strip can need: 128 * scale + 2, + 15 for the 16-B alignment, rounded to chunks
         const double need = 128.0 * P.lv[l - 1].w / P.lv[l].w + 2 + 15 + 16;
-        if (need <= 192) launchResize<192>(P, B, l, F, s);
-        else if (need <= 512) launchResize<512>(P, B, l, F, s);  // scale factors up to ~3.7
-        else launchResize<2048>(P, B, l, F, s);
+        // windowed horizontal pass: 4 neighbouring columns span <= 8 source bytes iff floor(3 * step) + 2 <= 7
+        const bool windowed = (double)P.lv[l - 1].w / P.lv[l].w < 1.95;
+        if (need <= 192 && windowed) launchResizeT<192, true>(P, B, l, F, s);
+        else if (need <= 192) launchResizeT<192, false>(P, B, l, F, s);
+        else if (need <= 512) launchResizeT<512, false>(P, B, l, F, s);  // scale factors up to ~3.7
+        else launchResizeT<2048, false>(P, B, l, F, s);
     }
 }
 
