@@ -24,6 +24,7 @@
 //   4. every listed pixel with arc > t is compared with its 8 neighbours in the arc map; survivors are written
 //      in order (ballot + popc again) as resp<<24 | y<<12 | x.
 #include <algorithm>
+#include <vector>
 
 #include "orbx_internal.cuh"
 
@@ -71,8 +72,8 @@ __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32
 template <int PITCH, bool SHIFTED>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     fastCellsKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
-                    int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes, unsigned levelMask,
-                    int cellsInLaunch, int totalWork, int* __restrict__ workCounter) {
+                    int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes,
+                    const uint32_t* __restrict__ cellTab, int cellsInLaunch, int totalWork, int* __restrict__ workCounter) {
     extern __shared__ __align__(16) uint8_t smem[];
     constexpr int P4 = PITCH / 4, P16 = PITCH / 16;
     const int lane = threadIdx.x & 31, wip = threadIdx.x >> 5;
@@ -87,16 +88,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     work = __shfl_sync(0xffffffffu, work, 0);
     if (work >= totalWork) break;
     const int f = work / cellsInLaunch;
-    int c = work - f * cellsInLaunch, l = 0;
-    for (; l < P.nlevels; ++l) {  // cells of the levels selected by levelMask, level-major
-        if (!((levelMask >> l) & 1u)) continue;
-        const int nc = P.lv[l].nCols * P.lv[l].nRows;
-        if (c < nc) break;
-        c -= nc;
-    }
-    if (l >= P.nlevels) continue;
+    // (level, cell row, cell column) of the launch's k-th cell: a table built with the plan (level-major, row-major)
+    const uint32_t ce = __ldg(cellTab + (work - f * cellsInLaunch));
+    const int l = (int)(ce >> 24), ci = (int)((ce >> 12) & 0xfffu), cj = (int)(ce & 0xfffu);
     const LevelPlan& L = P.lv[l];
-    const int ci = c / L.nCols, cj = c - ci * L.nCols;
+    const int c = ci * L.nCols + cj;
     int* cntOut = cellCnt + (size_t)f * P.nCellsTotal + L.cellBase + c;
     const int maxBX = L.w - kMinBorder, maxBY = L.h - kMinBorder;
     const int iniX = kMinBorder + cj * L.wCell, iniY = kMinBorder + ci * L.hCell;
@@ -121,39 +117,39 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     // ---- stage the cell with 128-bit loads; clear the arc map --------------------------------------------------
     const int gx0 = kEdge + iniX;
     const int shift = SHIFTED ? (gx0 & 15) : 0;
-    if (SHIFTED) {
-        const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + (gx0 - shift);
-        const int n16 = ch * P16, nArc = (ch - 4) * P16;
-        for (int i = lane; i < n16; i += 32) {
-            const int r = i / P16, k = i - r * P16;
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * L.pitch) + k);
-            reinterpret_cast<uint4*>(tile)[i] = v;
-            if (i < nArc) reinterpret_cast<uint4*>(arcStore)[i] = make_uint4(0, 0, 0, 0);
-        }
-    } else {
-        // output chunk k of a row = bytes [16k + s, 16k + s + 16) of the 16-B aligned source row, s = gx0 & 15: two aligned
-        // 128-bit loads, a warp-uniform word offset and four funnel shifts
+    {
+        constexpr int kRowsPerSweep = 32 / P16;           // whole rows per sweep: lane = row-in-sweep * P16 + chunk
+        const int lr = lane / P16, k = lane - lr * P16;
+        const bool laneOn = lr < kRowsPerSweep;
         const int s16 = gx0 & 15, wsel = s16 >> 2, bsh = (s16 & 3) * 8;
         const uint8_t* src = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kEdge + iniY) * L.pitch + (gx0 - s16);
-        const int n16 = ch * P16, nArc = (ch - 4) * P16;
         const int nIn = (s16 + cw + 15) >> 4;  // aligned source chunks that hold pixels of the cell
-        for (int i = lane; i < n16; i += 32) {
-            const int r = i / P16, k = i - r * P16;
-            const uint4* row = reinterpret_cast<const uint4*>(src + (size_t)r * L.pitch);
-            const uint4 a = k < nIn ? __ldg(row + k) : make_uint4(0, 0, 0, 0);
-            const uint4 b = (s16 != 0 && k + 1 < nIn) ? __ldg(row + k + 1) : make_uint4(0, 0, 0, 0);
-            uint32_t w0, w1, w2, w3, w4;
-            switch (wsel) {
-                case 0: w0 = a.x; w1 = a.y; w2 = a.z; w3 = a.w; w4 = b.x; break;
-                case 1: w0 = a.y; w1 = a.z; w2 = a.w; w3 = b.x; w4 = b.y; break;
-                case 2: w0 = a.z; w1 = a.w; w2 = b.x; w3 = b.y; w4 = b.z; break;
-                default: w0 = a.w; w1 = b.x; w2 = b.y; w3 = b.z; w4 = b.w; break;
-            }
+        const uint4* rowp = reinterpret_cast<const uint4*>(src + (size_t)lr * L.pitch) + k;
+        const size_t rowStep = (size_t)kRowsPerSweep * L.pitch / 16;
+        uint4* dst = reinterpret_cast<uint4*>(tile) + lr * P16 + k;
+        uint4* adst = reinterpret_cast<uint4*>(arcStore) + lr * P16 + k;
+        for (int r = lr; r < ch; r += kRowsPerSweep, rowp += rowStep, dst += kRowsPerSweep * P16, adst += kRowsPerSweep * P16) {
+            if (!laneOn) break;
             uint4 v;
-            v.x = __funnelshift_r(w0, w1, bsh); v.y = __funnelshift_r(w1, w2, bsh);
-            v.z = __funnelshift_r(w2, w3, bsh); v.w = __funnelshift_r(w3, w4, bsh);
-            reinterpret_cast<uint4*>(tile)[i] = v;
-            if (i < nArc) reinterpret_cast<uint4*>(arcStore)[i] = make_uint4(0, 0, 0, 0);
+            if (SHIFTED) {
+                v = __ldg(rowp);
+            } else {
+                // output chunk k of a row = bytes [16k + s, 16k + s + 16) of the 16-B aligned source row, s = gx0 & 15: two
+                // aligned 128-bit loads, a warp-uniform word offset and four funnel shifts
+                const uint4 a = k < nIn ? __ldg(rowp) : make_uint4(0, 0, 0, 0);
+                const uint4 b = (s16 != 0 && k + 1 < nIn) ? __ldg(rowp + 1) : make_uint4(0, 0, 0, 0);
+                uint32_t w0, w1, w2, w3, w4;
+                switch (wsel) {
+                    case 0: w0 = a.x; w1 = a.y; w2 = a.z; w3 = a.w; w4 = b.x; break;
+                    case 1: w0 = a.y; w1 = a.z; w2 = a.w; w3 = b.x; w4 = b.y; break;
+                    case 2: w0 = a.z; w1 = a.w; w2 = b.x; w3 = b.y; w4 = b.z; break;
+                    default: w0 = a.w; w1 = b.x; w2 = b.y; w3 = b.z; w4 = b.w; break;
+                }
+                v.x = __funnelshift_r(w0, w1, bsh); v.y = __funnelshift_r(w1, w2, bsh);
+                v.z = __funnelshift_r(w2, w3, bsh); v.w = __funnelshift_r(w3, w4, bsh);
+            }
+            *dst = v;
+            if (r < ch - 4) *adst = make_uint4(0, 0, 0, 0);
         }
     }
     __syncwarp();
@@ -259,11 +255,16 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
                         const bool accept = g < nG && nPix + incl <= kPixCap;  // a prefix of the lanes
                         const int nAcc = __popc(__ballot_sync(0xffffffffu, accept));
                         if (accept) {
-                            int pos = nPix + incl - n;
+                            // two pixels per trip: the lowest set bit goes to the front of the lane's range, the highest to
+                            // its back, so the range stays sorted and the longest lane needs 8 trips instead of 16
+                            int pos = nPix + incl - n, end = nPix + incl - 1;
+                            const uint32_t yb = (uint32_t)(y << 7) | (uint32_t)x0;
                             while (mm) {
-                                const int j = __ffs(mm) - 1;
+                                const int jl = __ffs(mm) - 1, jh = 31 - __clz(mm);
+                                pbuf[pos++] = (uint16_t)(yb + jl);
+                                pbuf[end--] = (uint16_t)(yb + jh);
                                 mm &= mm - 1;
-                                pbuf[pos++] = (uint16_t)((y << 7) | (x0 + j));
+                                mm &= ~(1u << jh);
                             }
                         }
                         if (nAcc) nPix += __shfl_sync(0xffffffffu, incl, nAcc - 1);
@@ -349,7 +350,8 @@ FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch) {
 }
 
 template <int PITCH, bool SHIFTED>
-void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, int* counter, cudaStream_t s) {
+void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, const uint32_t* cellTab, int* counter,
+                 cudaStream_t s) {
     const FastGeom g = geomFor(P, mask, PITCH);
     const size_t smem = (size_t)g.warpBytes * kWarpsPerCta;
     if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<PITCH, SHIFTED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -361,30 +363,47 @@ void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int
     const long long want = (total + kWarpsPerCta - 1) / kWarpsPerCta;
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
     cudaMemsetAsync(counter, 0, sizeof(int), s);
-    fastCellsKernel<PITCH, SHIFTED><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, mask,
+    fastCellsKernel<PITCH, SHIFTED><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, cellTab,
                                                                  cells, (int)total, counter);
     countLaunch();
 }
 
 }  // namespace
 
+static bool wideLevel(const LevelPlan& L) { return L.wCell + 6 > 48 || L.hCell + 6 > 50; }
+
+// (level << 24 | cell row << 12 | cell column) of every FAST cell, the narrow class first, then the wide one; inside a
+// class level-major and row-major, i.e. the reference's visiting order (ORBextractor.cc:805-808)
+void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab) {
+    tab.clear();
+    for (int wide = 0; wide < 2; ++wide)
+        for (int l = 0; l < P.nlevels; ++l) {
+            const LevelPlan& L = P.lv[l];
+            if (L.nCols <= 0 || L.nRows <= 0 || wideLevel(L) != (wide == 1)) continue;
+            for (int i = 0; i < L.nRows; ++i)
+                for (int j = 0; j < L.nCols; ++j) tab.push_back(((uint32_t)l << 24) | ((uint32_t)i << 12) | (uint32_t)j);
+        }
+}
+
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     // Two launches at most: levels whose cells fit a 48-byte unshifted tile row (cell width wCell+6 <= 48) and 50 rows —
     // every level of a large image — and the few small levels with wider or taller cells, staged chunk for chunk with
     // the global misalignment kept (wCell, hCell <= 70 always, since nCols = floor(width / 35); 15 + 76 + 4 <= 96).
+    int first = 0;
     for (int wide = 0; wide < 2; ++wide) {
         unsigned mask = 0;
         int cells = 0;
         for (int l = 0; l < P.nlevels; ++l) {
             const LevelPlan& L = P.lv[l];
             if (L.nCols <= 0 || L.nRows <= 0) continue;
-            if ((L.wCell + 6 > 48 || L.hCell + 6 > 50) != (wide == 1)) continue;
+            if (wideLevel(L) != (wide == 1)) continue;
             mask |= 1u << l;
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
-        if (!wide) launchClass<48, false>(P, B, F, mask, cells, B.workCtr, s);
-        else launchClass<96, true>(P, B, F, mask, cells, B.workCtr + 1, s);
+        if (!wide) launchClass<48, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
+        else launchClass<96, true>(P, B, F, mask, cells, B.fastTab + first, B.workCtr + 1, s);
+        first += cells;
     }
 }
 

@@ -81,6 +81,7 @@ struct orbx_extractor {
     Buffers buf{};
     DevMem mImg, mPyr, mBlur, mCand, mCellCnt, mGath, mNid, mLkp, mLkpCnt, mSlot, mOutK, mOutD, mOutN, mOutM, mTab, mErr;
     DevMem mKeys1, mKeys2, mMatch;
+    DevMem mFastTab;
     DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
     int stagedW = 0, stagedH = 0;
     std::vector<uint8_t> hStage;  // pinned staging would be the caller's; this is only for get_* taps
@@ -190,6 +191,11 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         if (rc != ORBX_OK) return rc;
         ORBX_CUDA(h->mTab.reserve(std::max<size_t>(tab.size() * sizeof(int16_t), 16)));
         ORBX_CUDA(cudaMemcpyAsync(h->mTab.p, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
+        std::vector<uint32_t> cells;
+        buildFastCellTable(h->plan, cells);
+        ORBX_CUDA(h->mFastTab.reserve(std::max<size_t>(cells.size() * 4, 16)));
+        if (!cells.empty())
+            ORBX_CUDA(cudaMemcpyAsync(h->mFastTab.p, cells.data(), cells.size() * 4, cudaMemcpyHostToDevice, h->stream));
         ORBX_CUDA(cudaStreamSynchronize(h->stream));
         h->havePlan = true;
         h->capFrames = 0;
@@ -219,7 +225,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.cand = (uint32_t*)h->mCand.p; B.cellCnt = (int*)h->mCellCnt.p; B.gath = (uint32_t*)h->mGath.p;
     B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.sorted = (LevelKp*)h->mSlot.p;
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
-    B.tab = (int16_t*)h->mTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
+    B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
     return ORBX_OK;
 }
 
@@ -371,7 +377,7 @@ void orbx_destroy(orbx_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
-                     &h->mMatch, &h->mRaw, &h->mStageTab};
+                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab};
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 9; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);

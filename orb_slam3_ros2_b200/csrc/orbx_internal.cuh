@@ -13,6 +13,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <cuda_runtime.h>
+#include <vector>
 
 namespace orbx {
 
@@ -81,6 +82,7 @@ struct Buffers {
     int* outMono;        // F
     int16_t* tab;        // resize coefficient tables
     int* errFlag;        // device-side invariant violations (capacity overflow)
+    uint32_t* fastTab;   // FAST cell table of the plan (buildFastCellTable)
     int* workCtr;        // two work counters of the persistent FAST launches (distinct per concurrently running sub-batch)
 };
 
@@ -88,6 +90,7 @@ struct Buffers {
 void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
                    cudaStream_t s);
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
 void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
 void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
 void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s);
