@@ -29,7 +29,8 @@ if ROOT not in sys.path:
 
 W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 LAP = (0, 1000)  # Frame.cc:311 passes {0,1000} for monocular frames
-E2E_HANDLES = 4  # measured sweep (profiles/): 2 -> 85.0k, 3 -> 89.5k, 4 -> 90.3k, 6 -> 81.0k frames/s
+E2E_DEPTH = 3   # measured sweep (handles x depth -> frames/s): 2x1 90.2k, 4x1 98.6k, 2x2 110.7k, 4x2 100.2k, 2x3 112.7k, 1x3 112.1k, 3x3 104.4k
+E2E_HANDLES = 2
 SUBBATCHES = 2  # default of --subbatches; measured sweep (profiles/r01_v6_subbatch_sweep_*): 1 -> 108.7k, 2 -> 113.3k, 3 -> 113.2k, 4 -> 113.0k, 6 -> 106.4k
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
 
@@ -301,16 +302,28 @@ def run_e2e(ctx, args, world):
     K = max(1, min(args.e2e_handles, F // 4)) if F >= 4 else 1
     cuts = [F * i // K for i in range(K + 1)]
     parts = [(max(cuts[i] - 1, 0), cuts[i + 1] - max(cuts[i] - 1, 0)) for i in range(K)]
-    handles = [ctx["ex"]] + [orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=ctx["dev"].index) for _ in parts[1:]]
-    bufs = []
-    for lo, cnt in parts:
-        bufs.append(dict(kps=torch.empty((cnt, cap, 7), dtype=torch.float32).pin_memory(),
-                         desc=torch.empty((cnt, cap, 32), dtype=torch.uint8).pin_memory(),
-                         n=torch.empty(cnt, dtype=torch.int32).pin_memory(), mono=torch.empty(cnt, dtype=torch.int32).pin_memory(),
-                         m=[torch.empty((max(cnt - 1, 1), cap), dtype=torch.int32).pin_memory() for _ in range(4)]))
+    # `depth` generations of handles + host buffers: step s uses generation s % depth, so the host enqueues step s+1 while
+    # step s is still in flight and only waits (orbx_check) for step s+1-depth, whose host buffers it is about to reuse
+    depth = max(1, args.e2e_depth)
+    gens = []
+    for g in range(depth):
+        hs = [ctx["ex"] if (g == 0 and i == 0) else orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=ctx["dev"].index)
+              for i in range(len(parts))]
+        bs = []
+        for lo, cnt in parts:
+            bs.append(dict(kps=torch.empty((cnt, cap, 7), dtype=torch.float32).pin_memory(),
+                           desc=torch.empty((cnt, cap, 32), dtype=torch.uint8).pin_memory(),
+                           n=torch.empty(cnt, dtype=torch.int32).pin_memory(), mono=torch.empty(cnt, dtype=torch.int32).pin_memory(),
+                           m=[torch.empty((max(cnt - 1, 1), cap), dtype=torch.int32).pin_memory() for _ in range(4)]))
+        gens.append((hs, bs))
+    handles = [h for hs, _ in gens for h in hs]
+    bufs = gens[0][1]
+    counter = [0]
 
     def step():
-        for ex, (lo, cnt), b in zip(handles, parts, bufs):
+        hs, bs = gens[counter[0] % depth]
+        counter[0] += 1
+        for ex, (lo, cnt), b in zip(hs, parts, bs):
             ex.check()  # results of this handle's previous step are complete from here on
             ex.extract_batch_async_ptr(h_img[lo].data_ptr(), cnt, W, H, LAP, b["kps"].data_ptr(), b["desc"].data_ptr(), cap,
                                        b["n"].data_ptr(), b["mono"].data_ptr())
@@ -341,11 +354,12 @@ def run_e2e(ctx, args, world):
     assert all(int(b["n"][0]) > 900 and int(b["n"][-1]) > 900 for b in bufs), "e2e leg produced no keypoints"
     if not args.skip_match:
         assert int((bufs[-1]["m"][1][0, :900] < 64).sum()) > 300, "e2e leg produced no matches"
-    for ex in handles[1:]:
-        ex.close()
+    for ex in handles:
+        if ex is not ctx["ex"]:
+            ex.close()
     return {"value": world * F * steps / dt, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "steps": steps, "handles": len(handles),
-            "api": f"orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check on {len(handles)} handles (pinned host buffers)"}
+            "steps": steps, "handles": len(parts), "depth": depth,
+            "api": f"orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check; a step is split over {len(parts)} handles, {depth} generation(s) of handles and pinned host buffers in flight"}
 
 
 def run_match_cfg5(ctx, args, rank, world, local_rank):
@@ -412,6 +426,7 @@ def main():
     ap.add_argument("--subbatches", type=int, default=SUBBATCHES,
                     help="parts of a batch run concurrently on internal stream pairs (orbx_set_subbatches)")
     ap.add_argument("--e2e-handles", type=int, default=E2E_HANDLES, help="extractor handles the e2e leg pipelines a step over")
+    ap.add_argument("--e2e-depth", type=int, default=E2E_DEPTH, help="generations of handles/host buffers in flight in the e2e leg")
     ap.add_argument("--only-e2e", action="store_true", help="development: resident leg + e2e leg only, print the e2e object")
     ap.add_argument("--skip-match", action="store_true")
     ap.add_argument("--skip-secondary", action="store_true", help="skip e2e / cfg5 / cpu_baseline legs (profiling runs)")
