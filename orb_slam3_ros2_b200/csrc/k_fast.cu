@@ -23,8 +23,21 @@
 //      (80 three-input min/max per pair) and written to a byte arc map (0 everywhere else);
 //   4. every listed pixel with arc > t is compared with its 8 neighbours in the arc map; survivors are written
 //      in order (ballot + popc again) as resp<<24 | y<<12 | x.
+//
+// v7 staging: the narrow class (every level of a normally sized image) stages its tile with TMA — ONE
+// cp.async.bulk.tensor.3d per cell, issued by one lane against a per-level tensor map of the padded pyramid planes
+// (dims pitch x rows x frames, box 64 x (hCell+6) x 1, no swizzle: the box lands as dense 64-byte rows), completion on a
+// per-warp mbarrier; the lanes clear the arc map while the copy is in flight.  The copy engine needs the box to START on a
+// 16-byte boundary of global memory (measured: an unaligned x coordinate raises "illegal instruction",
+// tools/tma_probe.cu), so the box starts at the cell's x rounded down to 16 and the tile keeps that shift
+// (tile x = cell x + (gx0 & 15) <= 15 + 48 - 1 < 64: the SHIFTED layout).  The arc map stays at the unshifted 48-byte pitch
+// (its rows are 8 bank phases apart and the warp's work area still fits 4 CTAs per SM).  Reads past the plane are
+// zero-filled by the copy engine.
 #include <algorithm>
+#include <cstring>
 #include <vector>
+
+#include <cuda.h>
 
 #include "orbx_internal.cuh"
 
@@ -36,6 +49,37 @@ constexpr int kPixCap = 256;      // pixel list capacity per warp (one segment o
 
 __device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
 __device__ __forceinline__ uint32_t min3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
+
+__device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbarInit(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbarExpectTx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smemAddr(bar)), "r"(parity) : "memory");
+}
+// one box of a 3-D u8 tensor (x = byte column, y = row, z = frame) -> dense rows in shared memory
+__device__ __forceinline__ void tmaLoadTile(void* dst, const CUtensorMap* map, int x, int y, int z, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+            smemAddr(dst)),
+        "l"(map), "r"(x), "r"(y), "r"(z), "r"(smemAddr(bar))
+        : "memory");
+}
+
+struct FastMaps {
+    CUtensorMap m[kMaxLevels];
+};
 
 // arc strength of two pixels at once: q[k] = ring pixel k of pixel A in the low half, of pixel B in the high half
 __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32_t cen) {
@@ -69,15 +113,30 @@ __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32
 //                  48-byte row.  12 words per row spread consecutive rows over 8 bank phases (a 64-byte row has 2: rows y and
 //                  y+2 collide, which cost the ring gathers 2.3 wavefronts per load), the quick test's chunk index becomes
 //                  contiguous, and its left / right neighbour words come from the neighbouring lanes instead of shared memory.
-template <int PITCH, bool SHIFTED>
+// TMA = true (needs SHIFTED): the tile is staged by the copy engine from the per-level tensor maps in M; the arc map
+// then has its own pitch APITCH = 48 and is indexed with cell x (tile x - shift).
+template <int PITCH, bool SHIFTED, bool TMA>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
-    fastCellsKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
-                    int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes,
-                    const uint32_t* __restrict__ cellTab, int cellsInLaunch, int totalWork, int* __restrict__ workCounter) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    constexpr int P4 = PITCH / 4, P16 = PITCH / 16;
+    fastCellsKernel(const __grid_constant__ FramePlan P, const __grid_constant__ FastMaps M, const uint8_t* __restrict__ pyr,
+                    uint32_t* __restrict__ cand, int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes,
+                    const uint32_t* __restrict__ cellTab, int cellsInLaunch, int totalWork, int* __restrict__ workCounter,
+                    int frame0) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int P16 = PITCH / 16;
+    constexpr int APITCH = TMA ? 48 : PITCH, A16 = APITCH / 16;
+    static_assert(!TMA || SHIFTED, "the TMA box starts on a 16-byte boundary: the tile keeps the shift");
     const int lane = threadIdx.x & 31, wip = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
+    // per-warp mbarrier of the TMA staging, behind the warps' work areas
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (size_t)kWarpsPerCta * warpBytes) + wip;
+    uint32_t barPhase = 0;
+    if (TMA) {
+        if (lane == 0) {
+            mbarInit(bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
 
     // ---- persistent warps: cells are handed out through a global counter, so a warp that drew an expensive cell (the
     // minThFAST fallback costs several times the common case) never keeps seven finished warps' shared memory idle ----
@@ -107,9 +166,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     }
 
     uint8_t* tile = smem + (size_t)wip * warpBytes;      // [rowsMax][PITCH] pixels; tile x = cell x + shift
-    uint8_t* arcStore = tile + rowsMax * PITCH;          // [rowsMax-4][PITCH] arc strength of tile rows 2 .. ch-3
-    uint8_t* arc = arcStore - 2 * PITCH;                 // indexed like the tile; 0 where not computed
-    uint32_t* glist = reinterpret_cast<uint32_t*>(arcStore + (rowsMax - 4) * PITCH);  // flagged chunks: item << 16 | mask
+    uint8_t* arcStore = tile + rowsMax * PITCH;          // [rowsMax-4][APITCH] arc strength of tile rows 2 .. ch-3
+    uint8_t* arc = arcStore - 2 * APITCH;                // indexed by (tile row, tile x - ashift); 0 where not computed
+    uint32_t* glist = reinterpret_cast<uint32_t*>(arcStore + (rowsMax - 4) * APITCH);  // flagged chunks: item << 16 | mask
     uint16_t* pbuf = reinterpret_cast<uint16_t*>(glist + itemsMax);  // pixel list of the current segment: y << 7 | x
     const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(tile);
     const uint4* tile128 = reinterpret_cast<const uint4*>(tile);
@@ -117,7 +176,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     // ---- stage the cell with 128-bit loads; clear the arc map --------------------------------------------------
     const int gx0 = kEdge + iniX;
     const int shift = SHIFTED ? (gx0 & 15) : 0;
-    {
+    if (TMA) {
+        // the previous cell's reads of this warp's tile are complete (__syncwarp at the loop head): hand the tile to the
+        // copy engine, clear the arc map meanwhile, then wait for the bytes
+        if (lane == 0) {
+            mbarExpectTx(bar, (uint32_t)(PITCH * (L.hCell + 6)));
+            tmaLoadTile(tile, &M.m[l], gx0 - shift, kEdge + iniY, frame0 + f, bar);
+        }
+        uint4* adst = reinterpret_cast<uint4*>(arcStore);
+        const int nA = (ch - 4) * A16;
+        for (int i = lane; i < nA; i += 32) adst[i] = make_uint4(0, 0, 0, 0);
+        mbarWait(bar, barPhase);
+        barPhase ^= 1u;
+    } else {
         constexpr int kRowsPerSweep = 32 / P16;           // whole rows per sweep: lane = row-in-sweep * P16 + chunk
         const int lr = lane / P16, k = lane - lr * P16;
         const bool laneOn = lr < kRowsPerSweep;
@@ -283,6 +354,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
                         const bool v0 = j0 < nPix, v1 = j1 < nPix;
                         const int p0 = pbuf[v0 ? j0 : 0], p1 = pbuf[v1 ? j1 : (v0 ? j0 : 0)];
                         const int o0 = (p0 >> 7) * PITCH + (p0 & 127), o1 = (p1 >> 7) * PITCH + (p1 & 127);
+                        const int a0 = TMA ? (p0 >> 7) * APITCH + (p0 & 127) - shift : o0;
+                        const int a1 = TMA ? (p1 >> 7) * APITCH + (p1 & 127) - shift : o1;
                         constexpr int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
                         constexpr int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
                         uint32_t q[16];
@@ -291,8 +364,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
                             q[k] = (uint32_t)tile[o0 + dy[k] * PITCH + dx[k]] | ((uint32_t)tile[o1 + dy[k] * PITCH + dx[k]] << 16);
                         const uint32_t cen = (uint32_t)tile[o0] | ((uint32_t)tile[o1] << 16);
                         const uint32_t a = arcStrength2(q, cen);
-                        if (v0) arc[o0] = (uint8_t)(a & 0xffu);
-                        if (v1) arc[o1] = (uint8_t)(a >> 16);
+                        if (v0) arc[a0] = (uint8_t)(a & 0xffu);
+                        if (v1) arc[a1] = (uint8_t)(a >> 16);
                     }
                     __syncwarp();
                 } else {
@@ -303,11 +376,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
                         int a = 0, p = 0;
                         if (j < nPix) {
                             p = pbuf[j];
-                            const int o = (p >> 7) * PITCH + (p & 127);
+                            const int o = (p >> 7) * APITCH + (p & 127) - (TMA ? shift : 0);
                             a = arc[o];
                             if (a > t) {
-                                const int m0 = __vimax3_s32(arc[o - PITCH - 1], arc[o - PITCH], arc[o - PITCH + 1]);
-                                const int m1 = __vimax3_s32(arc[o + PITCH - 1], arc[o + PITCH], arc[o + PITCH + 1]);
+                                const int m0 = __vimax3_s32(arc[o - APITCH - 1], arc[o - APITCH], arc[o - APITCH + 1]);
+                                const int m1 = __vimax3_s32(arc[o + APITCH - 1], arc[o + APITCH], arc[o + APITCH + 1]);
                                 keep = a > __vimax3_s32(m0, m1, max((int)arc[o - 1], (int)arc[o + 1]));
                             }
                         }
@@ -333,7 +406,7 @@ struct FastGeom {
     int pitch, rowsMax, itemsMax, warpBytes;
 };
 
-FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch) {
+FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch, int apitch) {
     FastGeom g{pitch, 7, 1, 0};
     for (int l = 0; l < P.nlevels; ++l) {
         if (!((mask >> l) & 1u)) continue;
@@ -344,31 +417,71 @@ FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch) {
         g.itemsMax = items > g.itemsMax ? items : g.itemsMax;
     }
     g.itemsMax = (g.itemsMax + 3) & ~3;
-    g.warpBytes = (2 * g.rowsMax - 4) * pitch + 4 * g.itemsMax + 2 * kPixCap;
-    g.warpBytes = (g.warpBytes + 15) & ~15;
+    g.warpBytes = g.rowsMax * pitch + (g.rowsMax - 4) * apitch + 4 * g.itemsMax + 2 * kPixCap;
+    g.warpBytes = (g.warpBytes + 127) & ~127;  // TMA destinations are 128-B aligned
     return g;
 }
 
-template <int PITCH, bool SHIFTED>
+template <int PITCH, bool SHIFTED, bool TMA>
 void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, const uint32_t* cellTab, int* counter,
                  cudaStream_t s) {
-    const FastGeom g = geomFor(P, mask, PITCH);
-    const size_t smem = (size_t)g.warpBytes * kWarpsPerCta;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(fastCellsKernel<PITCH, SHIFTED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const FastGeom g = geomFor(P, mask, PITCH, TMA ? 48 : PITCH);
+    const size_t smem = (size_t)g.warpBytes * kWarpsPerCta + 8 * kWarpsPerCta;  // + one mbarrier per warp
+    auto kern = fastCellsKernel<PITCH, SHIFTED, TMA>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int dev = 0, sms = 148, perSm = 1;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fastCellsKernel<PITCH, SHIFTED>, kWarpsPerCta * 32, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, kWarpsPerCta * 32, smem);
     const long long total = (long long)cells * F;
     const long long want = (total + kWarpsPerCta - 1) / kWarpsPerCta;
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
     cudaMemsetAsync(counter, 0, sizeof(int), s);
-    fastCellsKernel<PITCH, SHIFTED><<<grid, kWarpsPerCta * 32, smem, s>>>(P, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, cellTab,
-                                                                 cells, (int)total, counter);
+    static const FastMaps kNoMaps{};
+    const FastMaps& maps = TMA ? *reinterpret_cast<const FastMaps*>(B.fastMaps) : kNoMaps;
+    kern<<<grid, kWarpsPerCta * 32, smem, s>>>(P, maps, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, cellTab, cells,
+                                                (int)total, counter, B.frame0);
     countLaunch();
 }
 
 }  // namespace
+
+static bool wideLevel(const LevelPlan& L);
+
+size_t fastMapsBytes() { return sizeof(FastMaps); }
+
+// One 3-D tensor map per narrow-class level over the handle's WHOLE pyramid allocation: x = byte column of the padded
+// plane (extent = pitch), y = plane row, z = frame (stride frameBytes); box = 64 x (hCell+6) x 1.  Sub-batches address
+// their frames through the z coordinate (Buffers::frame0), so the maps only change when the buffer is reallocated.
+int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn ||
+            qres != cudaDriverEntryPointSuccess)
+            return -1;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    FastMaps* M = reinterpret_cast<FastMaps*>(out);
+    std::memset(M, 0, sizeof(FastMaps));
+    for (int l = 0; l < P.nlevels; ++l) {
+        const LevelPlan& L = P.lv[l];
+        if (L.nCols <= 0 || L.nRows <= 0 || wideLevel(L)) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.h + 2 * kEdge), (cuuint64_t)std::max(capFrames, 1)};
+        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.frameBytes};
+        const cuuint32_t box[3] = {64u, (cuuint32_t)(L.hCell + 6), 1u};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        const CUresult r = encode(&M->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(pyrBase) + L.planeOff, dims,
+                                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return -(int)r - 100;
+    }
+    return 0;
+}
 
 static bool wideLevel(const LevelPlan& L) { return L.wCell + 6 > 48 || L.hCell + 6 > 50; }
 
@@ -401,8 +514,12 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
-        if (!wide) launchClass<48, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
-        else launchClass<96, true>(P, B, F, mask, cells, B.fastTab + first, B.workCtr + 1, s);
+        if (!wide) {
+            if (B.fastMaps) launchClass<64, true, true>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
+            else launchClass<48, false, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
+        } else {
+            launchClass<96, true, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr + 1, s);
+        }
         first += cells;
     }
 }

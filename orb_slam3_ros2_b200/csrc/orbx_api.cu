@@ -82,6 +82,9 @@ struct orbx_extractor {
     DevMem mImg, mPyr, mBlur, mCand, mCellCnt, mGath, mNid, mLkp, mLkpCnt, mSlot, mOutK, mOutD, mOutN, mOutM, mTab, mErr;
     DevMem mKeys1, mKeys2, mMatch;
     DevMem mFastTab;
+    // TMA tensor maps of the FAST tile staging (one per level, over the whole mPyr allocation); rebuilt with the buffers
+    alignas(64) unsigned char fastMaps[kMaxLevels * 128];
+    bool useTma = true;
     DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
     int stagedW = 0, stagedH = 0;
     std::vector<uint8_t> hStage;  // pinned staging would be the caller's; this is only for get_* taps
@@ -219,6 +222,11 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         ORBX_CUDA(h->mErr.reserve(256));  // [0] error flags, [4 + 2p ..] work counters of persistent kernels, sub-batch p
         ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 256, h->stream));
         h->capFrames = F;
+        if (h->useTma) {
+            if (fastMapsBytes() > sizeof(h->fastMaps)) return fail(ORBX_ERR_CUDA, "tensor map table larger than expected");
+            const int rc = buildFastMaps(P, (const uint8_t*)h->mPyr.p, F, h->fastMaps);
+            if (rc != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string(rc) + ")");
+        }
     }
     Buffers& B = h->buf;
     B.img = (uint8_t*)h->mImg.p; B.pyr = (uint8_t*)h->mPyr.p; B.blur = (uint8_t*)h->mBlur.p;
@@ -226,6 +234,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.sorted = (LevelKp*)h->mSlot.p;
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
     B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
+    B.fastMaps = h->useTma ? h->fastMaps : nullptr; B.frame0 = 0;
     return ORBX_OK;
 }
 
@@ -238,6 +247,7 @@ static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int p
     O.sorted += f * P.outCap; O.outKps = (uint8_t*)O.outKps + f * P.outCap * 28; O.outDesc += f * P.outCap * 32;
     O.outN += f; O.outMono += f;
     O.workCtr = B.errFlag + 4 + 2 * part;
+    O.frame0 = B.frame0 + f0;
     return O;
 }
 
@@ -359,6 +369,10 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     h->device = dev;
     h->scaleFactorD = (double)params->scale_factor;
     initTables(h);
+    {
+        const char* t = std::getenv("ORBX_FAST_TMA");  // 0 = stage FAST tiles with ordinary loads (A/B measurements only)
+        h->useTma = !(t && t[0] == '0');
+    }
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
     for (int i = 0; i < 9 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);

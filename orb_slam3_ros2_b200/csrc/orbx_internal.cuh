@@ -84,6 +84,9 @@ struct Buffers {
     int* errFlag;        // device-side invariant violations (capacity overflow)
     uint32_t* fastTab;   // FAST cell table of the plan (buildFastCellTable)
     int* workCtr;        // two work counters of the persistent FAST launches (distinct per concurrently running sub-batch)
+    const void* fastMaps;  // host copy of the per-level TMA tensor maps over the whole pyramid allocation (buildFastMaps);
+                           // nullptr = stage FAST tiles with ordinary loads (ORBX_FAST_TMA=0)
+    int frame0;          // first frame of these buffers inside the allocation (z coordinate base of the tensor maps)
 };
 
 // kernel launchers (each in its own .cu); all asynchronous on `s`
@@ -91,6 +94,8 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
                    cudaStream_t s);
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
 void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
+size_t fastMapsBytes();
+int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
 void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
 void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s);
