@@ -58,8 +58,10 @@ def measured_peaks():
 
 def bind_to_gpu_numa_node(index):
     """Pin this rank's host threads to the CPUs next to its GPU (NVML's ideal affinity) BEFORE any pinned host buffer is
-    allocated, so the e2e leg's staging memory is first-touched on the GPU's own NUMA node: with 8 ranks on one box the
-    H2D streams otherwise cross the socket interconnect and collapse (measured 374k instead of ~900k frames/s at N=8)."""
+    allocated, so the e2e leg's staging memory is first-touched on the GPU's own NUMA node.  On this pool's boxes it is a
+    no-op (one virtual socket, one NUMA node, `nvidia-smi topo -m`: every GPU has CPU affinity 0-31): there the 8-GPU e2e
+    number (370 k frames/s = 163 GB/s of host<->device traffic) is bounded by the VM's host memory / PCIe root, not by
+    placement (profiles/r01_v9_bench_n8.json, profiles/r01_v9_topo_8gpu.txt)."""
     try:
         import pynvml
         pynvml.nvmlInit()

@@ -1,0 +1,111 @@
+// bow_oracle.cpp — TEST INFRASTRUCTURE (oracle side), not product code.  Only tests/, __graft_entry__.smoke() and
+// bench.py's cpu_baseline leg may call into this file.
+//
+// CPU restatement of Frame::ComputeBoW (ORB_SLAM3/src/Frame.cc:738-745) =
+// DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1126-1196) for the ORB vocabulary's settings (TF_IDF weighting, L1_NORM
+// scoring: the "10 6 0 0" header of ORBvoc.txt), on a vocabulary given as flat arrays.
+//
+// Pinned by oracle/_ref/libbowref.so — the reference's own DBoW2 sources compiled unchanged — in
+// tests/test_oracle_bow.py (equal on every case, doubles compared bit for bit) and by tests/golden/bow.npz generated from it.
+//
+// Flat vocabulary: node 0 is the root; parent[i] < i for i >= 1 (loadFromTextFile numbers nodes in file order and
+// appends each to its parent's children, TemplatedVocabulary.h:1373-1388, so children are visited in increasing id
+// order); a node without children is a leaf = a word; word ids are assigned to leaves in node order (:1405-1411).
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <vector>
+
+namespace {
+
+// FORB::distance (Thirdparty/DBoW2/DBoW2/FORB.cpp:81-100): the SWAR popcount over 8 x 32-bit words
+int forbDistance(const uint8_t* a, const uint8_t* b) {
+    int32_t pa[8], pb[8];
+    std::memcpy(pa, a, 32);
+    std::memcpy(pb, b, 32);
+    int dist = 0;
+    for (int i = 0; i < 8; ++i) {
+        unsigned int v = pa[i] ^ pb[i];
+        v = v - ((v >> 1) & 0x55555555);
+        v = (v & 0x33333333) + ((v >> 2) & 0x33333333);
+        dist += (((v + (v >> 4)) & 0xF0F0F0F) * 0x1010101) >> 24;
+    }
+    return dist;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Outputs as in oracle/bow_ref_wrap.cpp: BowVector (word_ids, word_vals)[*n_words] ascending; FeatureVector CSR
+// node_ids[*n_nodes], node_begin[*n_nodes + 1], feat_idx[...].  Returns 0, or -1 for a malformed tree.
+int orbo_bow_transform(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L,
+                       const uint8_t* desc, int n, int levelsup, int32_t* word_ids, double* word_vals, int32_t* n_words,
+                       int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx, int32_t* n_nodes_out) {
+    std::vector<std::vector<int>> children(n_nodes);
+    for (int i = 1; i < n_nodes; ++i) {
+        if (parent[i] < 0 || parent[i] >= i) return -1;
+        children[parent[i]].push_back(i);
+    }
+    std::vector<int> wordOf(n_nodes, -1);
+    int nw = 0;
+    for (int i = 1; i < n_nodes; ++i)
+        if (children[i].empty()) wordOf[i] = nw++;
+
+    std::map<unsigned, double> bow;                     // BowVector  (BowVector.h:52-54)
+    std::map<unsigned, std::vector<unsigned>> fvec;     // FeatureVector (FeatureVector.h:24-25)
+    for (int f = 0; f < n; ++f) {
+        // transform(feature, word_id, weight, nid, levelsup)  (TemplatedVocabulary.h:1217-1263)
+        const uint8_t* feat = desc + (size_t)f * 32;
+        const int nidLevel = L - levelsup;
+        unsigned nid = 0;  // "if(nid_level <= 0 && nid != NULL) *nid = 0" — and 0 where the reference leaves it unset
+        int cur = 0, level = 0;
+        if (children[0].empty()) return -1;
+        do {
+            ++level;
+            const std::vector<int>& ch = children[cur];
+            cur = ch[0];
+            double best = forbDistance(feat, node_desc + (size_t)cur * 32);
+            for (size_t j = 1; j < ch.size(); ++j) {
+                const double d = forbDistance(feat, node_desc + (size_t)ch[j] * 32);
+                if (d < best) {
+                    best = d;
+                    cur = ch[j];
+                }
+            }
+            if (level == nidLevel) nid = (unsigned)cur;
+        } while (!children[cur].empty());
+        const double w = weight[cur];
+        if (w > 0) {  // "not stopped" (:1157)
+            bow[(unsigned)wordOf[cur]] += w;  // BowVector::addWeight (BowVector.cpp:31-43): insert or +=
+            fvec[nid].push_back((unsigned)f); // FeatureVector::addFeature (FeatureVector.cpp:33-47)
+        }
+    }
+    // L1 normalisation (L1Scoring::mustNormalize -> BowVector::normalize, BowVector.cpp:62-84)
+    double norm = 0.0;
+    for (auto& kv : bow) norm += std::fabs(kv.second);
+    if (norm > 0.0)
+        for (auto& kv : bow) kv.second /= norm;
+
+    int k = 0;
+    for (auto& kv : bow) {
+        word_ids[k] = (int32_t)kv.first;
+        word_vals[k] = kv.second;
+        ++k;
+    }
+    *n_words = k;
+    int m = 0, pos = 0;
+    for (auto& kv : fvec) {
+        node_ids[m] = (int32_t)kv.first;
+        node_begin[m] = pos;
+        for (unsigned i : kv.second) feat_idx[pos++] = (int32_t)i;
+        ++m;
+    }
+    node_begin[m] = pos;
+    *n_nodes_out = m;
+    return 0;
+}
+
+}  // extern "C"

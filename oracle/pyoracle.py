@@ -379,3 +379,87 @@ def fast_atan2(y, x):
     out = np.zeros_like(y)
     port_lib().minicv_fast_atan2(_ptr(y, _f32p), _ptr(x, _f32p), _ptr(out, _f32p), len(y))
     return out
+
+
+# ---- Frame::ComputeBoW (DBoW2 transform) ------------------------------------------------------------------------------
+
+def bow_ref_path():
+    return os.path.join(HERE, "_ref", "libbowref.so")
+
+
+def have_bow_ref():
+    return os.path.exists(bow_ref_path())
+
+
+def write_voc_text(path, parent, node_desc, weight, k, L):
+    """ORBvoc.txt format read by the reference's loadFromTextFile (TemplatedVocabulary.h:1340-1420): header "k L scoring
+    weighting", then one line per node 1..n-1: parent, isLeaf, 32 descriptor bytes, weight.  NO trailing newline: the
+    reference's `while(!f.eof())` loop would turn an empty last line into an extra child of the root."""
+    parent = np.asarray(parent)
+    n = len(parent)
+    has_child = np.zeros(n, bool)
+    has_child[parent[1:]] = True
+    lines = [f"{k} {L} 0 0"]
+    for i in range(1, n):
+        d = " ".join(str(int(b)) for b in node_desc[i])
+        lines.append(f"{int(parent[i])} {0 if has_child[i] else 1} {d} {float(weight[i])!r}")
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+def _bow_outputs(n):
+    n = max(int(n), 1)
+    return (np.zeros(n, np.int32), np.zeros(n, np.float64), np.zeros(1, np.int32), np.zeros(n, np.int32),
+            np.zeros(n + 1, np.int32), np.zeros(n, np.int32), np.zeros(1, np.int32))
+
+
+def _bow_pack(o):
+    wi, wv, nw, ni, nb, fi, nn = o
+    nw, nn = int(nw[0]), int(nn[0])
+    return dict(word_ids=wi[:nw].copy(), word_vals=wv[:nw].copy(), node_ids=ni[:nn].copy(), node_begin=nb[:nn + 1].copy(),
+                feat_idx=fi[:int(nb[nn])].copy())
+
+
+class RefVocabulary:
+    """The reference's own DBoW2 vocabulary (oracle/_ref/libbowref.so), loaded from a text file."""
+
+    def __init__(self, path):
+        self.lib = C.CDLL(bow_ref_path())
+        self.lib.bowref_load_text.restype = C.c_void_p
+        self.lib.bowref_load_text.argtypes = [C.c_char_p]
+        self.lib.bowref_destroy.argtypes = [C.c_void_p]
+        self.lib.bowref_words.argtypes = [C.c_void_p]
+        self.lib.bowref_transform.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        self.h = self.lib.bowref_load_text(path.encode())
+        if not self.h:
+            raise RuntimeError("reference loadFromTextFile failed")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.bowref_destroy(self.h)
+            self.h = None
+
+    def words(self):
+        return self.lib.bowref_words(self.h)
+
+    def transform(self, desc, levelsup=4):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        o = _bow_outputs(len(desc))
+        self.lib.bowref_transform(self.h, _ptr(desc), len(desc), levelsup, *[a.ctypes.data for a in o])
+        return _bow_pack(o)
+
+
+def bow_transform(parent, node_desc, weight, L, desc, levelsup=4):
+    """CPU restatement (oracle/bow_oracle.cpp) on the flat vocabulary arrays."""
+    lib = port_lib()
+    parent = np.ascontiguousarray(parent, np.int32)
+    node_desc = np.ascontiguousarray(node_desc, np.uint8).reshape(-1, 32)
+    weight = np.ascontiguousarray(weight, np.float64)
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    o = _bow_outputs(len(desc))
+    lib.orbo_bow_transform.argtypes = [C.c_int, C.c_void_p, _u8p, C.c_void_p, C.c_int, _u8p, C.c_int, C.c_int] + [C.c_void_p] * 7
+    rc = lib.orbo_bow_transform(len(parent), parent.ctypes.data, _ptr(node_desc), weight.ctypes.data, L, _ptr(desc), len(desc),
+                                levelsup, *[a.ctypes.data for a in o])
+    if rc != 0:
+        raise ValueError("malformed vocabulary tree")
+    return _bow_pack(o)

@@ -107,3 +107,57 @@ def queries_from_db(nq, n_db, db_seed=7, q_seed=11, flips=20):
             d[b >> 3] ^= np.uint8(1 << (b & 7))
         q[i] = d
     return q, rows
+
+
+def vocabulary(k=10, L=3, seed=5, ragged=False, stop_every=0, flips=24, leaf_level=None):
+    """Synthetic ORB vocabulary tree in the flat form of orbx_voc_create (ORBvoc.txt.tar.gz is a missing blob offline,
+    .MISSING_LARGE_BLOBS): node 0 = root, nodes in breadth-first order so parent[i] < i, every child descriptor = its parent's
+    with `flips` pseudo-random bits flipped (the descent is then meaningful, like a k-means tree), idf-like weights.
+    ragged: inner nodes get between 2 and k children.  stop_every: every n-th word gets weight 0 (a stopped word,
+    TemplatedVocabulary.h:1157).  leaf_level: leaves may already appear at this depth (< L) for ~1/7 of the nodes there.
+    Returns (parent int32[n], node_desc uint8[n,32], weight float64[n])."""
+    rng = np.random.default_rng(seed)
+    parent, desc, depth = [-1], [np.zeros(32, np.uint8)], [0]
+    frontier = [0]
+    for level in range(1, L + 1):
+        nxt = []
+        for p in frontier:
+            if leaf_level is not None and depth[p] >= leaf_level and p % 7 == 3:
+                continue  # an early leaf
+            nc = int(rng.integers(2, k + 1)) if ragged else k
+            for _ in range(nc):
+                d = desc[p].copy() if p else rng.integers(0, 256, 32, dtype=np.uint8)
+                if p:
+                    for b in rng.integers(0, 256, flips):
+                        d[b >> 3] ^= np.uint8(1 << (b & 7))
+                parent.append(p)
+                desc.append(d)
+                depth.append(level)
+                nxt.append(len(parent) - 1)
+        frontier = nxt
+    n = len(parent)
+    parent = np.asarray(parent, np.int32)
+    weight = np.round(rng.uniform(0.5, 9.0, n), 6)  # 6 decimals: survives the text file round trip exactly
+    has_child = np.zeros(n, bool)
+    has_child[parent[1:]] = True
+    if stop_every:
+        leaves = np.flatnonzero(~has_child)
+        weight[leaves[::stop_every]] = 0.0
+    weight[has_child] = 0.0
+    return parent, np.stack(desc), weight
+
+
+def descriptors_near_words(parent, node_desc, n, seed=9, flips=30):
+    """n query descriptors: random leaves of the vocabulary with `flips` bits flipped (plus a few exact copies, so that
+    distance-0 and tie cases occur)."""
+    rng = np.random.default_rng(seed)
+    has_child = np.zeros(len(parent), bool)
+    has_child[np.asarray(parent)[1:]] = True
+    leaves = np.flatnonzero(~has_child)
+    out = node_desc[rng.choice(leaves, n)].copy()
+    for i in range(n):
+        if i % 17 == 0:
+            continue
+        for b in rng.integers(0, 256, flips):
+            out[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    return out
