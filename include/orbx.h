@@ -227,6 +227,38 @@ int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, 
                                 const uint8_t* desc_l, int nl, const orbx_keypoint* kps_r, const uint8_t* desc_r, int nr,
                                 float bf, float b, float* u_right, float* depth);
 
+/* ---- Frame::ComputeBoW (row N4): DBoW2 vocabulary-tree transform --------------------------------------------------
+ * Replaces mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) (ORB_SLAM3/src/Frame.cc:738-745), i.e.
+ * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1126-1196) with the per-feature descent of :1217-1263 and
+ * FORB::distance (FORB.cpp:81-100), for the ORB vocabulary's settings: TF_IDF weighting, L1_NORM scoring.
+ *
+ * The vocabulary is handed over as flat arrays (what loadFromTextFile builds, TemplatedVocabulary.h:1340-1420):
+ * node 0 = root, parent[i] < i for i >= 1, children of a node are visited in increasing node id (the loader appends
+ * them in file order), a node without children is a word and words are numbered in node order, weight[i] = the
+ * node's idf weight (only read for words; <= 0 = stopped word), L = the tree depth of the file header.
+ *
+ * Outputs per frame f (strides: `cap` entries, node_begin cap + 1), in the iteration order of the reference's std::maps:
+ *   BowVector      word_ids[f][0 .. n_words[f])   ascending, word_vals = L1-normalised tf-idf (doubles, bit-exact)
+ *   FeatureVector  node_ids[f][0 .. n_nodes[f])   ascending node ids at level L - levelsup (0 = root if that is <= 0),
+ *                  node_begin[f][j] .. node_begin[f][j+1] = the slice of feat_idx[f] holding node j's feature indices
+ *                  in insertion (= ascending) order.
+ * Where the reference reads an uninitialised NodeId (a leaf above level L - levelsup, :1225-1258) this returns 0. */
+typedef struct orbx_vocabulary* orbx_voc;
+int orbx_voc_create(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L, int device,
+                    orbx_voc* out);
+void orbx_voc_destroy(orbx_voc v);
+int orbx_voc_info(orbx_voc v, int* n_nodes, int* n_words, int* max_children, int* L);
+/* desc: host, [nframes][cap][32]; n_per_frame: host, descriptors used of each frame (<= cap <= 16384). */
+int orbx_bow_transform(orbx_voc v, const uint8_t* desc, const int32_t* n_per_frame, int nframes, int cap, int levelsup,
+                       int32_t* word_ids, double* word_vals, int32_t* n_words, int32_t* node_ids, int32_t* node_begin,
+                       int32_t* feat_idx, int32_t* n_nodes);
+/* The same on the descriptors of the handle's LAST extraction, read in place on the device (no descriptor download);
+ * cap = the cap_per_frame of orbx_batch_results, nframes = the frames of that extraction. */
+int orbx_bow_transform_extracted(orbx_voc v, orbx_handle h, int levelsup, int32_t* word_ids, double* word_vals,
+                                 int32_t* n_words, int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx,
+                                 int32_t* n_nodes);
+
 /* Measured sustained 32-bit POPC rate of the device in giga-POPC/s (8 independent XOR+POPC chains per thread):
  * the denominator of the matcher's roofline, pairs/s = POPC/s / 8. */
 int orbx_bench_popc(int device, double* gpopc_per_s);

@@ -1,0 +1,216 @@
+// k_bow.cu — row N4: Frame::ComputeBoW (ORB_SLAM3/src/Frame.cc:738-745) =
+// DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1126-1196) with the ORB vocabulary's settings (TF_IDF, L1_NORM).
+//
+// Two kernels per batch of frames:
+//   bowDescendKernel   the tree descent of transform(feature, word_id, weight, nid, levelsup) (:1217-1263): sixteen lanes
+//                      per feature, one child per lane (children's descriptors are stored contiguously in visiting order,
+//                      so a node's k x 32 B are one coalesced read), FORB::distance (FORB.cpp:81-100) as 8 XOR + POPC,
+//                      the first-minimum rule (`d < best_d`, children in order) as a min over keys distance << 20 | position;
+//   bowCollectKernel   one CTA per frame: BowVector = std::map<WordId, double> filled by addWeight in feature order
+//                      (BowVector.cpp:31-43) and L1-normalised in ascending word order (:62-84); FeatureVector =
+//                      std::map<NodeId, vector<feature index>> (FeatureVector.cpp:33-47).  Both maps are ONE bitonic sort
+//                      of 64-bit keys (id << 32 | feature index) each: runs of equal ids are the map entries, already in
+//                      the maps' iteration order, their members in insertion order.
+// Doubles are bit-exact: a word's value is its weight added to itself count-1 times in sequence (what addWeight does,
+// every feature of a word adds the same weight), the norm is accumulated sequentially in ascending word order by one
+// thread, and the division is IEEE.
+#include <algorithm>
+
+#include "orbx_internal.cuh"
+
+namespace orbx {
+namespace {
+
+constexpr uint64_t kSentinel = ~0ull;
+
+__global__ void __launch_bounds__(256) bowDescendKernel(const BowVocDev V, const uint8_t* __restrict__ desc,
+                                                        const int* __restrict__ nPerFrame, int cap, int F, int levelsup,
+                                                        int* __restrict__ leafOut, int* __restrict__ nidOut) {
+    const int lane = threadIdx.x & 31, sub = lane & 15;
+    const unsigned gmask = 0xffffu << (lane & 16);
+    const long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+    if (g >= (long long)F * cap) return;  // whole groups leave together
+    const int f = (int)(g / cap), i = (int)(g - (long long)f * cap);
+    if (i >= nPerFrame[f]) return;
+    const uint4* q4 = reinterpret_cast<const uint4*>(desc + (size_t)g * 32);
+    const uint4 qa = __ldg(q4), qb = __ldg(q4 + 1);
+    const int nidLevel = V.L - levelsup;
+    int cur = 0, level = 0, nid = 0;
+    for (;;) {
+        const int cb = __ldg(V.childBegin + cur), ce = __ldg(V.childBegin + cur + 1);
+        if (cb == ce) break;  // a leaf: isLeaf() = children.empty()
+        ++level;
+        unsigned best = 0xffffffffu;
+        for (int p = cb + sub; p < ce; p += 16) {
+            const uint4* c4 = reinterpret_cast<const uint4*>(V.childDesc + (size_t)p * 32);
+            const uint4 a = __ldg(c4), b = __ldg(c4 + 1);
+            const int d = __popc(a.x ^ qa.x) + __popc(a.y ^ qa.y) + __popc(a.z ^ qa.z) + __popc(a.w ^ qa.w) +
+                          __popc(b.x ^ qb.x) + __popc(b.y ^ qb.y) + __popc(b.z ^ qb.z) + __popc(b.w ^ qb.w);
+            best = min(best, ((unsigned)d << 20) | (unsigned)(p - cb));
+        }
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o));
+        cur = __ldg(V.childId + cb + (int)(best & 0xfffffu));
+        if (level == nidLevel) nid = cur;
+    }
+    if (sub == 0) {
+        leafOut[g] = cur;
+        nidOut[g] = nid;
+    }
+}
+
+// ascending bitonic sort of n2 (a power of two) keys in shared memory
+__device__ void bitonicSort(uint64_t* k, int n2) {
+    for (int size = 2; size <= n2; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (n2 >> 1); t += blockDim.x) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const uint64_t a = k[lo], b = k[hi];
+                if ((a > b) == up) {
+                    k[lo] = b;
+                    k[hi] = a;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// Runs of equal high words in the sorted keys -> entry index of every head (exclusive count of heads before it).
+// Each thread owns the contiguous chunk [t * per, (t + 1) * per); returns the total number of heads.
+__device__ int headIndices(const uint64_t* k, int m, int n2, int* sScan, int& myFirst, int& myBegin, int& myEnd) {
+    const int per = (n2 + blockDim.x - 1) / blockDim.x;
+    myBegin = min((int)threadIdx.x * per, m);
+    myEnd = min(myBegin + per, m);
+    int cnt = 0;
+    for (int p = myBegin; p < myEnd; ++p) cnt += (p == 0 || (uint32_t)(k[p] >> 32) != (uint32_t)(k[p - 1] >> 32));
+    // block-wide exclusive scan of cnt
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) sScan[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        int v = lane < nw ? sScan[lane] : 0, s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += u;
+        }
+        if (lane < nw) sScan[lane] = s - v;
+        if (lane == 31) sScan[32] = s;
+    }
+    __syncthreads();
+    myFirst = sScan[w] + incl - cnt;
+    const int total = sScan[32];
+    __syncthreads();
+    return total;
+}
+
+__global__ void __launch_bounds__(512) bowCollectKernel(const BowVocDev V, const int* __restrict__ nPerFrame, int cap, int n2,
+                                                        const int* __restrict__ leaf, const int* __restrict__ nidIn,
+                                                        int32_t* __restrict__ wordIds, double* __restrict__ wordVals,
+                                                        int32_t* __restrict__ nWords, int32_t* __restrict__ nodeIds,
+                                                        int32_t* __restrict__ nodeBegin, int32_t* __restrict__ featIdx,
+                                                        int32_t* __restrict__ nNodes) {
+    extern __shared__ __align__(16) uint64_t keys[];
+    __shared__ int sScan[33];
+    __shared__ int sValid;
+    __shared__ double sNorm;
+    const int f = blockIdx.x, n = min(nPerFrame[f], cap);
+    const size_t base = (size_t)f * cap;
+    if (threadIdx.x == 0) sValid = 0;
+    __syncthreads();
+
+    // ---- BowVector ------------------------------------------------------------------------------------------
+    int local = 0;
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) {
+        uint64_t key = kSentinel;
+        if (i < n) {
+            const int node = leaf[base + i];
+            if (V.weight[node] > 0) {  // "not stopped" (TemplatedVocabulary.h:1157)
+                key = ((uint64_t)(uint32_t)V.wordOf[node] << 32) | (uint32_t)i;
+                ++local;
+            }
+        }
+        keys[i] = key;
+    }
+    if (local) atomicAdd(&sValid, local);
+    bitonicSort(keys, n2);
+    const int m = sValid;
+    int first, b, e;
+    const int nu = headIndices(keys, m, n2, sScan, first, b, e);
+    for (int p = b; p < e; ++p) {
+        const uint32_t word = (uint32_t)(keys[p] >> 32);
+        if (p != 0 && word == (uint32_t)(keys[p - 1] >> 32)) continue;
+        int q = p + 1;
+        while (q < m && (uint32_t)(keys[q] >> 32) == word) ++q;
+        const double w = V.weight[leaf[base + (uint32_t)keys[p]]];
+        double sum = w;  // addWeight: insert w, then += w for every further feature of the word, in feature order
+        for (int c = p + 1; c < q; ++c) sum = __dadd_rn(sum, w);
+        wordIds[base + first] = (int32_t)word;
+        wordVals[base + first] = sum;
+        ++first;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double norm = 0.0;  // BowVector::normalize(L1): ascending word order, one accumulator
+        for (int u = 0; u < nu; ++u) norm = __dadd_rn(norm, fabs(wordVals[base + u]));
+        sNorm = norm;
+        nWords[f] = nu;
+    }
+    __syncthreads();
+    const double norm = sNorm;
+    if (norm > 0.0)
+        for (int u = threadIdx.x; u < nu; u += blockDim.x) wordVals[base + u] = __ddiv_rn(wordVals[base + u], norm);
+    __syncthreads();
+
+    // ---- FeatureVector --------------------------------------------------------------------------------------
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) {
+        uint64_t key = kSentinel;
+        if (i < n && V.weight[leaf[base + i]] > 0) key = ((uint64_t)(uint32_t)nidIn[base + i] << 32) | (uint32_t)i;
+        keys[i] = key;
+    }
+    bitonicSort(keys, n2);
+    const int nn = headIndices(keys, m, n2, sScan, first, b, e);
+    const size_t nbBase = (size_t)f * (cap + 1);
+    for (int p = b; p < e; ++p) {
+        featIdx[base + p] = (int32_t)(uint32_t)keys[p];
+        if (p == 0 || (uint32_t)(keys[p] >> 32) != (uint32_t)(keys[p - 1] >> 32)) {
+            nodeIds[base + first] = (int32_t)(uint32_t)(keys[p] >> 32);
+            nodeBegin[nbBase + first] = p;
+            ++first;
+        }
+    }
+    if (threadIdx.x == 0) {
+        nodeBegin[nbBase + nn] = m;
+        nNodes[f] = nn;
+    }
+}
+
+}  // namespace
+
+int bowSortCapacity() { return 16384; }
+
+void launchBowTransform(const BowVocDev& V, const uint8_t* dDesc, const int* dN, int cap, int F, int levelsup, int* leaf,
+                        int* nid, int32_t* wordIds, double* wordVals, int32_t* nWords, int32_t* nodeIds, int32_t* nodeBegin,
+                        int32_t* featIdx, int32_t* nNodes, cudaStream_t s) {
+    const long long groups = (long long)F * cap;
+    const int grid = (int)((groups * 16 + 255) / 256);
+    bowDescendKernel<<<grid, 256, 0, s>>>(V, dDesc, dN, cap, F, levelsup, leaf, nid);
+    int n2 = 32;
+    while (n2 < cap) n2 <<= 1;
+    const size_t smem = (size_t)n2 * sizeof(uint64_t);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(bowCollectKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    bowCollectKernel<<<F, 512, smem, s>>>(V, dN, cap, n2, leaf, nid, wordIds, wordVals, nWords, nodeIds, nodeBegin, featIdx, nNodes);
+    countLaunch(2);
+}
+
+}  // namespace orbx

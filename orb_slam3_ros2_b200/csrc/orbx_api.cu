@@ -1131,6 +1131,158 @@ int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, 
     return ORBX_OK;
 }
 
+// ---- Frame::ComputeBoW (row N4) ------------------------------------------------------------------------------------
+struct orbx_vocabulary {
+    int device = 0;
+    int nNodes = 0, nWords = 0, maxChildren = 0, L = 0;
+    DevMem mBegin, mId, mDesc, mWeight, mWord;   // the flat tree
+    DevMem mLeaf, mNid, mIn, mN, mOut;           // per-call scratch (grown on demand)
+    cudaStream_t stream = nullptr;
+    BowVocDev dev{};
+};
+
+int orbx_voc_create(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L, int device,
+                    orbx_voc* out) {
+    if (!out || n_nodes < 2 || !parent || !node_desc || !weight || L < 1) return fail(ORBX_ERR_ARG, "bad argument");
+    // children in increasing node id = the order loadFromTextFile appends them (TemplatedVocabulary.h:1373-1388)
+    std::vector<int> begin((size_t)n_nodes + 1, 0), ids((size_t)n_nodes - 1), wordOf((size_t)n_nodes, -1);
+    for (int i = 1; i < n_nodes; ++i) {
+        if (parent[i] < 0 || parent[i] >= i) return fail(ORBX_ERR_ARG, "vocabulary: parent[i] must be in [0, i)");
+        ++begin[(size_t)parent[i] + 1];
+    }
+    int maxC = 0;
+    for (int i = 0; i < n_nodes; ++i) {
+        maxC = std::max(maxC, begin[(size_t)i + 1]);
+        begin[(size_t)i + 1] += begin[i];
+    }
+    if (maxC >= (1 << 20)) return fail(ORBX_ERR_ARG, "vocabulary: more than 2^20 children under one node");
+    std::vector<int> fill(begin.begin(), begin.end() - 1);
+    std::vector<uint8_t> cdesc((size_t)(n_nodes - 1) * 32);
+    for (int i = 1; i < n_nodes; ++i) {
+        const int pos = fill[parent[i]]++;
+        ids[pos] = i;
+        std::memcpy(&cdesc[(size_t)pos * 32], node_desc + (size_t)i * 32, 32);
+    }
+    int nWords = 0;
+    for (int i = 1; i < n_nodes; ++i)
+        if (begin[(size_t)i + 1] == begin[i]) wordOf[i] = nWords++;  // words numbered in node order (:1405-1411)
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    int dev = device;
+    if (dev < 0) ORBX_CUDA(cudaGetDevice(&dev));
+    DeviceGuard guard(dev);
+    orbx_vocabulary* v = new orbx_vocabulary();
+    v->device = dev; v->nNodes = n_nodes; v->nWords = nWords; v->maxChildren = maxC; v->L = L;
+    cudaError_t e = cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = v->mBegin.reserve(begin.size() * 4);
+    if (e == cudaSuccess) e = v->mId.reserve(ids.size() * 4);
+    if (e == cudaSuccess) e = v->mDesc.reserve(cdesc.size());
+    if (e == cudaSuccess) e = v->mWeight.reserve((size_t)n_nodes * 8);
+    if (e == cudaSuccess) e = v->mWord.reserve((size_t)n_nodes * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(v->mBegin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->mId.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->mDesc.p, cdesc.data(), cdesc.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->mWeight.p, weight, (size_t)n_nodes * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->mWord.p, wordOf.data(), (size_t)n_nodes * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        orbx_voc_destroy(v);
+        cudaGetLastError();
+        return fail(ORBX_ERR_CUDA, std::string("vocabulary upload: ") + cudaGetErrorString(e));
+    }
+    v->dev = BowVocDev{n_nodes, L, (const int*)v->mBegin.p, (const int*)v->mId.p, (const uint8_t*)v->mDesc.p,
+                       (const double*)v->mWeight.p, (const int*)v->mWord.p};
+    *out = v;
+    return ORBX_OK;
+}
+
+void orbx_voc_destroy(orbx_voc v) {
+    if (!v) return;
+    DeviceGuard guard(v->device);
+    if (v->stream) cudaStreamSynchronize(v->stream);
+    DevMem* all[] = {&v->mBegin, &v->mId, &v->mDesc, &v->mWeight, &v->mWord, &v->mLeaf, &v->mNid, &v->mIn, &v->mN, &v->mOut};
+    for (DevMem* m : all) m->release();
+    if (v->stream) cudaStreamDestroy(v->stream);
+    delete v;
+}
+
+int orbx_voc_info(orbx_voc v, int* n_nodes, int* n_words, int* max_children, int* L) {
+    if (!v) return fail(ORBX_ERR_ARG, "null vocabulary");
+    if (n_nodes) *n_nodes = v->nNodes;
+    if (n_words) *n_words = v->nWords;
+    if (max_children) *max_children = v->maxChildren;
+    if (L) *L = v->L;
+    return ORBX_OK;
+}
+
+// descriptors [F][cap][32] and counts already on the device (on stream `after`'s work, joined through an event)
+static int bowRun(orbx_vocabulary* v, const uint8_t* dDesc, const int* dN, int F, int cap, int levelsup, int32_t* word_ids,
+                  double* word_vals, int32_t* n_words, int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx,
+                  int32_t* n_nodes) {
+    const size_t T = (size_t)F * cap;
+    ORBX_CUDA(v->mLeaf.reserve(T * 4 + 16));
+    ORBX_CUDA(v->mNid.reserve(T * 4 + 16));
+    // out: [wordVals f64 T | wordIds T | nodeIds T | featIdx T | nodeBegin F*(cap+1) | nWords F | nNodes F]
+    const size_t oIds = T * 8, oNode = oIds + T * 4, oFeat = oNode + T * 4, oBeg = oFeat + T * 4,
+                 oNw = oBeg + (size_t)F * (cap + 1) * 4, oNn = oNw + (size_t)F * 4, bytes = oNn + (size_t)F * 4;
+    ORBX_CUDA(v->mOut.reserve(bytes + 16));
+    uint8_t* O = (uint8_t*)v->mOut.p;
+    cudaStream_t s = v->stream;
+    launchBowTransform(v->dev, dDesc, dN, cap, F, levelsup, (int*)v->mLeaf.p, (int*)v->mNid.p, (int32_t*)(O + oIds), (double*)O,
+                       (int32_t*)(O + oNw), (int32_t*)(O + oNode), (int32_t*)(O + oBeg), (int32_t*)(O + oFeat), (int32_t*)(O + oNn), s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(word_vals, O, T * 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(word_ids, O + oIds, T * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(node_ids, O + oNode, T * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(feat_idx, O + oFeat, T * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(node_begin, O + oBeg, (size_t)F * (cap + 1) * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(n_words, O + oNw, (size_t)F * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(n_nodes, O + oNn, (size_t)F * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+static int bowArgs(orbx_voc v, int levelsup, const void* a, const void* b, const void* c, const void* d, const void* e,
+                   const void* f, const void* g) {
+    if (!v) return fail(ORBX_ERR_ARG, "null vocabulary");
+    if (levelsup < 0) return fail(ORBX_ERR_ARG, "levelsup must be >= 0");
+    if (!a || !b || !c || !d || !e || !f || !g) return fail(ORBX_ERR_ARG, "null output");
+    return ORBX_OK;
+}
+
+int orbx_bow_transform(orbx_voc v, const uint8_t* desc, const int32_t* n_per_frame, int nframes, int cap, int levelsup,
+                       int32_t* word_ids, double* word_vals, int32_t* n_words, int32_t* node_ids, int32_t* node_begin,
+                       int32_t* feat_idx, int32_t* n_nodes) {
+    int rc = bowArgs(v, levelsup, word_ids, word_vals, n_words, node_ids, node_begin, feat_idx, n_nodes);
+    if (rc != ORBX_OK) return rc;
+    if (!desc || !n_per_frame || nframes < 1 || cap < 1) return fail(ORBX_ERR_ARG, "bad argument");
+    if (cap > bowSortCapacity()) return fail(ORBX_ERR_ARG, "more than 16384 descriptors per frame");
+    for (int f = 0; f < nframes; ++f)
+        if (n_per_frame[f] < 0 || n_per_frame[f] > cap) return fail(ORBX_ERR_ARG, "n_per_frame out of range");
+    DeviceGuard guard(v->device);
+    const size_t T = (size_t)nframes * cap;
+    ORBX_CUDA(v->mIn.reserve(T * 32));
+    ORBX_CUDA(v->mN.reserve((size_t)nframes * 4));
+    ORBX_CUDA(cudaMemcpyAsync(v->mIn.p, desc, T * 32, cudaMemcpyHostToDevice, v->stream));
+    ORBX_CUDA(cudaMemcpyAsync(v->mN.p, n_per_frame, (size_t)nframes * 4, cudaMemcpyHostToDevice, v->stream));
+    return bowRun(v, (const uint8_t*)v->mIn.p, (const int*)v->mN.p, nframes, cap, levelsup, word_ids, word_vals, n_words, node_ids,
+                  node_begin, feat_idx, n_nodes);
+}
+
+int orbx_bow_transform_extracted(orbx_voc v, orbx_handle h, int levelsup, int32_t* word_ids, double* word_vals, int32_t* n_words,
+                                 int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx, int32_t* n_nodes) {
+    int rc = bowArgs(v, levelsup, word_ids, word_vals, n_words, node_ids, node_begin, feat_idx, n_nodes);
+    if (rc != ORBX_OK) return rc;
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (h->device != v->device) return fail(ORBX_ERR_ARG, "vocabulary and extractor live on different devices");
+    if (h->plan.outCap > bowSortCapacity()) return fail(ORBX_ERR_ARG, "more than 16384 keypoint slots per frame");
+    DeviceGuard guard(v->device);
+    // the extraction may still be running on the handle's stream: order the vocabulary's stream behind it
+    ORBX_CUDA(cudaEventRecord(h->ev[6], h->stream));
+    ORBX_CUDA(cudaStreamWaitEvent(v->stream, h->ev[6], 0));
+    return bowRun(v, h->buf.outDesc, h->buf.outN, h->lastFrames, h->plan.outCap, levelsup, word_ids, word_vals, n_words, node_ids,
+                  node_begin, feat_idx, n_nodes);
+}
+
 int orbx_bench_popc(int device, double* gpopc_per_s) {
     if (!gpopc_per_s) return fail(ORBX_ERR_ARG, "null argument");
     int ndev = 0;

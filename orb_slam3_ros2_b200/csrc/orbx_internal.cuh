@@ -128,6 +128,20 @@ void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, c
                         float* uRight, float* depth, int* sad, cudaStream_t s);
 void launchStage(const uint8_t* dSrc, int sw, int sh, int sstride, int ch, int rgb, uint8_t* dDst, int dw, int dh,
                  const int16_t* tabX, const int16_t* tabY, cudaStream_t s);
+// flat DBoW2 vocabulary on the device (k_bow.cu): children of node c are CSR entries [childBegin[c], childBegin[c+1]) in the
+// reference's visiting order, their descriptors stored contiguously in that order
+struct BowVocDev {
+    int nNodes, L;
+    const int* childBegin;     // nNodes + 1
+    const int* childId;        // nNodes - 1
+    const uint8_t* childDesc;  // (nNodes - 1) x 32, 16-B aligned
+    const double* weight;      // nNodes
+    const int* wordOf;         // nNodes, -1 for inner nodes
+};
+int bowSortCapacity();
+void launchBowTransform(const BowVocDev& V, const uint8_t* dDesc, const int* dN, int cap, int F, int levelsup, int* leaf,
+                        int* nid, int32_t* wordIds, double* wordVals, int32_t* nWords, int32_t* nodeIds, int32_t* nodeBegin,
+                        int32_t* featIdx, int32_t* nNodes, cudaStream_t s);
 void uploadDescribeTables();
 double benchPopcRate(cudaStream_t s);
 

@@ -85,6 +85,11 @@ SYMBOLS = {
     "orbx_compute_stereo_matches": (C.c_int, [_vp, _vp, C.c_int, _vp, _u8p, C.c_int, _vp, _u8p, C.c_int, C.c_float, C.c_float,
                                               _f32p, _f32p]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
+    "orbx_voc_create": (C.c_int, [C.c_int, _i32p, _u8p, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(_vp)]),
+    "orbx_voc_destroy": (None, [_vp]),
+    "orbx_voc_info": (C.c_int, [_vp, _i32p, _i32p, _i32p, _i32p]),
+    "orbx_bow_transform": (C.c_int, [_vp, _u8p, _i32p, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_bow_transform_extracted": (C.c_int, [_vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "orbx_comm_unique_id": (C.c_int, [_u8p]),
     "orbx_comm_init": (C.c_int, [C.c_int, C.c_int, _u8p, C.c_int, C.POINTER(_vp)]),
     "orbx_comm_destroy": (None, [_vp]),
@@ -427,6 +432,72 @@ def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):
     d1 = np.asarray(d1)
     d2 = np.asarray(d2)
     return (d1 <= th) & (d1.astype(np.float32) < np.float32(nnratio) * d2.astype(np.float32))
+
+
+class ORBVocabulary:
+    """Device-resident DBoW2 vocabulary tree (ORB_SLAM3/include/ORBVocabulary.h:27-28) given as flat arrays; transform() is
+    Frame::ComputeBoW (src/Frame.cc:738-745) = TemplatedVocabulary::transform(features, BowVector, FeatureVector, levelsup)."""
+
+    def __init__(self, parent, node_desc, weight, L, device=-1):
+        parent = np.ascontiguousarray(parent, np.int32)
+        node_desc = np.ascontiguousarray(node_desc, np.uint8).reshape(-1, 32)
+        weight = np.ascontiguousarray(weight, np.float64)
+        if not (len(parent) == len(node_desc) == len(weight)):
+            raise ValueError("parent, node_desc and weight must have one entry per node")
+        self._h = _vp()
+        _check(lib().orbx_voc_create(len(parent), _ptr(parent, _i32p), _ptr(node_desc), weight.ctypes.data_as(C.POINTER(C.c_double)),
+                                     int(L), device, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orbx_voc_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def info(self):
+        v = [np.zeros(1, np.int32) for _ in range(4)]
+        _check(lib().orbx_voc_info(self._h, *[_ptr(a, _i32p) for a in v]))
+        return dict(n_nodes=int(v[0][0]), n_words=int(v[1][0]), max_children=int(v[2][0]), L=int(v[3][0]))
+
+    @staticmethod
+    def _outputs(F, cap):
+        return (np.zeros((F, cap), np.int32), np.zeros((F, cap), np.float64), np.zeros(F, np.int32), np.zeros((F, cap), np.int32),
+                np.zeros((F, cap + 1), np.int32), np.zeros((F, cap), np.int32), np.zeros(F, np.int32))
+
+    @staticmethod
+    def _unpack(o):
+        wi, wv, nw, ni, nb, fi, nn = o
+        out = []
+        for f in range(len(nw)):
+            a, b = int(nw[f]), int(nn[f])
+            out.append(dict(word_ids=wi[f, :a].copy(), word_vals=wv[f, :a].copy(), node_ids=ni[f, :b].copy(),
+                            node_begin=nb[f, :b + 1].copy(), feat_idx=fi[f, :int(nb[f, b])].copy()))
+        return out
+
+    def transform(self, desc, levelsup=4):
+        """desc: (n, 32) descriptors of ONE frame -> dict(word_ids, word_vals, node_ids, node_begin, feat_idx)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        return self.transform_batch([desc], levelsup)[0]
+
+    def transform_batch(self, descs, levelsup=4):
+        F = len(descs)
+        n = np.asarray([len(d) for d in descs], np.int32)
+        cap = max(int(n.max()) if F else 0, 1)
+        buf = np.zeros((F, cap, 32), np.uint8)
+        for f, d in enumerate(descs):
+            buf[f, :len(d)] = np.asarray(d, np.uint8).reshape(-1, 32)
+        o = self._outputs(F, cap)
+        _check(lib().orbx_bow_transform(self._h, _ptr(buf), _ptr(n, _i32p), F, cap, levelsup, *[a.ctypes.data for a in o]))
+        return self._unpack(o)
+
+    def transform_extracted(self, extractor, levelsup=4):
+        """BoW / feature vectors of every frame of `extractor`'s last extraction, descriptors read in place on the device."""
+        _, _, _, _, cap = extractor.results_device()
+        F = extractor._frames
+        o = self._outputs(F, cap)
+        _check(lib().orbx_bow_transform_extracted(self._h, extractor._h, levelsup, *[a.ctypes.data for a in o]))
+        return self._unpack(o)
 
 
 class ShardedMatcher:

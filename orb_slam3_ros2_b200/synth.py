@@ -161,3 +161,25 @@ def descriptors_near_words(parent, node_desc, n, seed=9, flips=30):
         for b in rng.integers(0, 256, flips):
             out[i, b >> 3] ^= np.uint8(1 << (b & 7))
     return out
+
+
+# (name, k, L, ragged, stop_every, leaf_level, levelsup, n descriptors): the Frame::ComputeBoW parity cases shared by
+# tools/gen_golden.py (reference DBoW2 -> tests/golden/bow.npz) and the CPU / GPU tests
+BOW_CASES = [
+    ("k10L3", 10, 3, False, 0, None, 1, 1000),
+    ("k10L3_ragged_stop", 10, 3, True, 5, None, 2, 1000),
+    ("k6L4_ragged_root", 6, 4, True, 3, None, 4, 700),
+    ("k10L4_earlyleaf", 10, 4, False, 7, 3, 1, 1500),
+    ("k3L2_tiny", 3, 2, False, 0, None, 4, 64),
+    ("k10L4_levelsup2", 10, 4, False, 0, None, 2, 2000),
+    ("k10L3_one", 10, 3, False, 0, None, 1, 1),
+]
+
+
+def bow_case(name):
+    """-> (k, L, levelsup, parent, node_desc, weight, descriptors) of a BOW_CASES entry."""
+    for nm, k, L, ragged, stop, leaf_level, levelsup, n in BOW_CASES:
+        if nm == name:
+            parent, node_desc, weight = vocabulary(k, L, seed=5, ragged=ragged, stop_every=stop, leaf_level=leaf_level)
+            return k, L, levelsup, parent, node_desc, weight, descriptors_near_words(parent, node_desc, n)
+    raise KeyError(name)

@@ -5,6 +5,8 @@
                un-vendored primitives on small inputs -> pins oracle/minicv
   match.npz    cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) on descriptor sets with planted ties
                -> pins the matcher oracle's (distance, index) order (reference: ORB_SLAM3/src/Frame.cc:1144)
+  bow.npz      BowVector / FeatureVector from the reference's own DBoW2 (oracle/_ref/libbowref.so) on synthetic
+               vocabulary trees -> pins the Frame::ComputeBoW oracle and is the GPU parity fixture
   e2e_*.npz    keypoints / descriptors / pyramid digests from the reference's own ORBextractor.cc compiled
                unchanged on the minicv shim (oracle/_ref) on synthetic frames -> pins the port oracle and
                is what the GPU parity tests compare against on the GPU box, where /root/reference is absent.
@@ -187,12 +189,45 @@ def gen_e2e():
         print(name, "n =", len(rec["strict_kp"]), "mono =", rec["strict_mono"], "native_same =", rec.get("native_same", False))
 
 
+def gen_bow():
+    """Frame::ComputeBoW: outputs of the reference's own DBoW2 (oracle/_ref/libbowref.so) on synthetic vocabularies."""
+    import tempfile
+    from oracle import pyoracle as po
+    po.build()
+    assert po.have_bow_ref(), "oracle/_ref/libbowref.so missing: run where /root/reference exists"
+    rec = {}
+    for name, *_ in synth.BOW_CASES:
+        k, L, levelsup, parent, node_desc, weight, desc = synth.bow_case(name)
+        with tempfile.TemporaryDirectory() as t:
+            path = os.path.join(t, "voc.txt")
+            po.write_voc_text(path, parent, node_desc, weight, k, L)
+            voc = po.RefVocabulary(path)
+            out = voc.transform(desc, levelsup)
+            rec[f"{name}__words"] = voc.words()
+        rec[f"{name}__voc_sha1"] = hashlib.sha1(parent.tobytes() + node_desc.tobytes() + weight.tobytes() + desc.tobytes()).hexdigest()
+        for key, val in out.items():
+            rec[f"{name}__{key}"] = val
+        print(name, "nodes", len(parent), "words hit", len(out["word_ids"]), "feature-vector nodes", len(out["node_ids"]))
+    # the descriptors of a real extraction (the 752x480 fixture) through a 10^4-word tree, levelsup 2
+    e2e = np.load(os.path.join(OUT, "e2e_euroc752.npz"))
+    k, L, levelsup, parent, node_desc, weight, _ = synth.bow_case("k10L4_levelsup2")
+    with tempfile.TemporaryDirectory() as t:
+        path = os.path.join(t, "voc.txt")
+        po.write_voc_text(path, parent, node_desc, weight, k, L)
+        out = po.RefVocabulary(path).transform(e2e["strict_desc"], levelsup)
+    for key, val in out.items():
+        rec[f"euroc752__{key}"] = val
+    np.savez_compressed(os.path.join(OUT, "bow.npz"), **rec)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    what = sys.argv[1:] or ["prim", "stage", "e2e"]
+    what = sys.argv[1:] or ["prim", "stage", "e2e", "bow"]
     if "prim" in what:
         gen_primitives()
     if "stage" in what:
         gen_stage()
     if "e2e" in what:
         gen_e2e()
+    if "bow" in what:
+        gen_bow()
