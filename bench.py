@@ -437,6 +437,46 @@ def run_match_cfg5(ctx, args, rank, world, local_rank):
                          "peak_source": f"measured POPC rate {gpopc:.0f} Gpopc/s per GPU / 8 POPC per pair"}}
 
 
+def run_bow(ctx, args, rank, world):
+    """Row N4, Frame::ComputeBoW: orbx_bow_transform_extracted on the resident batch's device-resident descriptors against an
+    ORBvoc-shaped synthetic vocabulary (k = 10, L = 6: 1,111,111 nodes, 10^6 words; the real blob is missing offline).  The
+    timed call includes the download of both maps to host arrays.  CPU leg (rank 0, N = 1): the oracle port on a sample."""
+    import numpy as np
+    orbx, synth, ex = ctx["orbx"], ctx["synth"], ctx["ex"]
+    parent, node_desc, weight = synth.vocabulary_full(10, 6)
+    voc = orbx.ORBVocabulary(parent, node_desc, weight, 6, device=ctx["dev"].index)
+    ex.extract_batch_device(ctx["imgs"][0].data_ptr(), ctx["F"], W, H, LAP)
+    ex.sync()
+    l0 = orbx.launch_count()
+    res = voc.transform_extracted(ex, 4)  # warm-up (scratch allocation); also the unpacked result for the checks below
+    per_call = orbx.launch_count() - l0
+    raw = voc.outputs_for(ex)
+    reps = 10
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        voc.transform_extracted(ex, 4, raw=raw)
+    dt = (time.perf_counter() - t0) / reps
+    out = {"workload": f"ComputeBoW of {ctx['F']} frames x ~{int(ctx['nkp'])} descriptors, vocabulary k=10 L=6 (1111111 nodes), levelsup 4",
+           "frames_per_s": ctx["F"] / dt, "ms": dt * 1e3, "launches_per_call": per_call,
+           "words_per_frame": float(np.mean([len(r["word_ids"]) for r in res])),
+           "d2h_bytes_per_call": int(sum(a.nbytes for a in raw)),
+           "timing": "host wall clock around the C-ABI call (orbx_bow_transform_extracted), both maps downloaded to host arrays"}
+    if rank == 0 and world == 1:
+        from oracle import pyoracle
+        sample = min(64, ctx["F"])
+        descs = [ex.download(f)[2] for f in range(sample)]
+        pv = pyoracle.PortVocabulary(parent, node_desc, weight, 6)
+        t0 = time.perf_counter()
+        want = [pv.transform(d, 4) for d in descs]
+        cdt = time.perf_counter() - t0
+        same = all(np.array_equal(res[f][key], want[f][key]) for f in range(sample) for key in want[f])
+        out["cpu_baseline"] = {"value": sample / cdt, "unit": "frames/s", "cores": 1, "kind": "port",
+                               "sample": f"{sample} frames of the batch, oracle/bow_oracle.cpp, vocabulary built once",
+                               "equal_to_gpu": bool(same)}
+    voc.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -520,6 +560,7 @@ def main():
     if not args.skip_secondary:
         out["e2e"] = run_e2e(ctx, args, world)
         out["match"] = run_match_cfg5(ctx, args, rank, world, local_rank)
+        out["bow"] = run_bow(ctx, args, rank, world)
         if rank == 0 and world == 1:
             from orb_slam3_ros2_b200 import synth
             cores = os.cpu_count() or 1

@@ -34,35 +34,47 @@ int forbDistance(const uint8_t* a, const uint8_t* b) {
     }
     return dist;
 }
+struct Voc {
+    int L = 0;
+    std::vector<std::vector<int>> children;
+    std::vector<int> wordOf;
+    std::vector<uint8_t> desc;
+    std::vector<double> weight;
+};
 
-}  // namespace
-
-extern "C" {
-
-// Outputs as in oracle/bow_ref_wrap.cpp: BowVector (word_ids, word_vals)[*n_words] ascending; FeatureVector CSR
-// node_ids[*n_nodes], node_begin[*n_nodes + 1], feat_idx[...].  Returns 0, or -1 for a malformed tree.
-int orbo_bow_transform(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L,
-                       const uint8_t* desc, int n, int levelsup, int32_t* word_ids, double* word_vals, int32_t* n_words,
-                       int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx, int32_t* n_nodes_out) {
-    std::vector<std::vector<int>> children(n_nodes);
+Voc* buildVoc(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L) {
+    Voc* v = new Voc();
+    v->L = L;
+    v->children.resize(n_nodes);
     for (int i = 1; i < n_nodes; ++i) {
-        if (parent[i] < 0 || parent[i] >= i) return -1;
-        children[parent[i]].push_back(i);
+        if (parent[i] < 0 || parent[i] >= i) {
+            delete v;
+            return nullptr;
+        }
+        v->children[parent[i]].push_back(i);
     }
-    std::vector<int> wordOf(n_nodes, -1);
+    v->wordOf.assign(n_nodes, -1);
     int nw = 0;
     for (int i = 1; i < n_nodes; ++i)
-        if (children[i].empty()) wordOf[i] = nw++;
+        if (v->children[i].empty()) v->wordOf[i] = nw++;
+    v->desc.assign(node_desc, node_desc + (size_t)n_nodes * 32);
+    v->weight.assign(weight, weight + n_nodes);
+    return v;
+}
 
+int transformVoc(const Voc& V, const uint8_t* desc, int n, int levelsup, int32_t* word_ids, double* word_vals, int32_t* n_words,
+                 int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx, int32_t* n_nodes_out) {
+    const std::vector<std::vector<int>>& children = V.children;
+    const uint8_t* node_desc = V.desc.data();
     std::map<unsigned, double> bow;                     // BowVector  (BowVector.h:52-54)
     std::map<unsigned, std::vector<unsigned>> fvec;     // FeatureVector (FeatureVector.h:24-25)
+    if (n > 0 && children[0].empty()) return -1;
     for (int f = 0; f < n; ++f) {
         // transform(feature, word_id, weight, nid, levelsup)  (TemplatedVocabulary.h:1217-1263)
         const uint8_t* feat = desc + (size_t)f * 32;
-        const int nidLevel = L - levelsup;
+        const int nidLevel = V.L - levelsup;
         unsigned nid = 0;  // "if(nid_level <= 0 && nid != NULL) *nid = 0" — and 0 where the reference leaves it unset
         int cur = 0, level = 0;
-        if (children[0].empty()) return -1;
         do {
             ++level;
             const std::vector<int>& ch = children[cur];
@@ -77,10 +89,10 @@ int orbo_bow_transform(int n_nodes, const int32_t* parent, const uint8_t* node_d
             }
             if (level == nidLevel) nid = (unsigned)cur;
         } while (!children[cur].empty());
-        const double w = weight[cur];
+        const double w = V.weight[cur];
         if (w > 0) {  // "not stopped" (:1157)
-            bow[(unsigned)wordOf[cur]] += w;  // BowVector::addWeight (BowVector.cpp:31-43): insert or +=
-            fvec[nid].push_back((unsigned)f); // FeatureVector::addFeature (FeatureVector.cpp:33-47)
+            bow[(unsigned)V.wordOf[cur]] += w;  // BowVector::addWeight (BowVector.cpp:31-43): insert or +=
+            fvec[nid].push_back((unsigned)f);   // FeatureVector::addFeature (FeatureVector.cpp:33-47)
         }
     }
     // L1 normalisation (L1Scoring::mustNormalize -> BowVector::normalize, BowVector.cpp:62-84)
@@ -106,6 +118,34 @@ int orbo_bow_transform(int n_nodes, const int32_t* parent, const uint8_t* node_d
     node_begin[m] = pos;
     *n_nodes_out = m;
     return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// A vocabulary kept between calls (bench.py's cpu_baseline leg); NULL for a malformed tree.
+void* orbo_bow_create(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L) {
+    return buildVoc(n_nodes, parent, node_desc, weight, L);
+}
+void orbo_bow_destroy(void* h) { delete static_cast<Voc*>(h); }
+
+// Outputs as in oracle/bow_ref_wrap.cpp: BowVector (word_ids, word_vals)[*n_words] ascending; FeatureVector CSR
+// node_ids[*n_nodes], node_begin[*n_nodes + 1], feat_idx[...].  Returns 0, or -1 for a malformed tree.
+int orbo_bow_transform_h(void* h, const uint8_t* desc, int n, int levelsup, int32_t* word_ids, double* word_vals,
+                         int32_t* n_words, int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx, int32_t* n_nodes_out) {
+    return transformVoc(*static_cast<Voc*>(h), desc, n, levelsup, word_ids, word_vals, n_words, node_ids, node_begin, feat_idx,
+                        n_nodes_out);
+}
+
+int orbo_bow_transform(int n_nodes, const int32_t* parent, const uint8_t* node_desc, const double* weight, int L,
+                       const uint8_t* desc, int n, int levelsup, int32_t* word_ids, double* word_vals, int32_t* n_words,
+                       int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx, int32_t* n_nodes_out) {
+    Voc* v = buildVoc(n_nodes, parent, node_desc, weight, L);
+    if (!v) return -1;
+    const int rc = transformVoc(*v, desc, n, levelsup, word_ids, word_vals, n_words, node_ids, node_begin, feat_idx, n_nodes_out);
+    delete v;
+    return rc;
 }
 
 }  // extern "C"

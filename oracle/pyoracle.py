@@ -463,3 +463,34 @@ def bow_transform(parent, node_desc, weight, L, desc, levelsup=4):
     if rc != 0:
         raise ValueError("malformed vocabulary tree")
     return _bow_pack(o)
+
+
+class PortVocabulary:
+    """oracle/bow_oracle.cpp with the child lists kept between calls (what bench.py's cpu_baseline leg times)."""
+
+    def __init__(self, parent, node_desc, weight, L):
+        lib = port_lib()
+        parent = np.ascontiguousarray(parent, np.int32)
+        node_desc = np.ascontiguousarray(node_desc, np.uint8).reshape(-1, 32)
+        weight = np.ascontiguousarray(weight, np.float64)
+        lib.orbo_bow_create.restype = C.c_void_p
+        lib.orbo_bow_create.argtypes = [C.c_int, C.c_void_p, _u8p, C.c_void_p, C.c_int]
+        lib.orbo_bow_destroy.argtypes = [C.c_void_p]
+        lib.orbo_bow_transform_h.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        self.lib = lib
+        self.h = lib.orbo_bow_create(len(parent), parent.ctypes.data, _ptr(node_desc), weight.ctypes.data, L)
+        if not self.h:
+            raise ValueError("malformed vocabulary tree")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.orbo_bow_destroy(self.h)
+            self.h = None
+
+    def transform(self, desc, levelsup=4):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        o = _bow_outputs(len(desc))
+        rc = self.lib.orbo_bow_transform_h(self.h, _ptr(desc), len(desc), levelsup, *[a.ctypes.data for a in o])
+        if rc != 0:
+            raise ValueError("malformed vocabulary tree")
+        return _bow_pack(o)

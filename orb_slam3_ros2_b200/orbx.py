@@ -491,13 +491,16 @@ class ORBVocabulary:
         _check(lib().orbx_bow_transform(self._h, _ptr(buf), _ptr(n, _i32p), F, cap, levelsup, *[a.ctypes.data for a in o]))
         return self._unpack(o)
 
-    def transform_extracted(self, extractor, levelsup=4):
-        """BoW / feature vectors of every frame of `extractor`'s last extraction, descriptors read in place on the device."""
-        _, _, _, _, cap = extractor.results_device()
-        F = extractor._frames
-        o = self._outputs(F, cap)
+    def transform_extracted(self, extractor, levelsup=4, raw=None):
+        """BoW / feature vectors of every frame of `extractor`'s last extraction, descriptors read in place on the device.
+        raw = the tuple of preallocated output arrays of a previous call's `outputs_for(extractor)`: filled and returned
+        as they are (the C ABI's own layout, no per-frame unpacking)."""
+        o = raw if raw is not None else self.outputs_for(extractor)
         _check(lib().orbx_bow_transform_extracted(self._h, extractor._h, levelsup, *[a.ctypes.data for a in o]))
-        return self._unpack(o)
+        return o if raw is not None else self._unpack(o)
+
+    def outputs_for(self, extractor):
+        return self._outputs(extractor._frames, extractor.results_device()[4])
 
 
 class ShardedMatcher:

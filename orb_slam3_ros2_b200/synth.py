@@ -183,3 +183,29 @@ def bow_case(name):
             parent, node_desc, weight = vocabulary(k, L, seed=5, ragged=ragged, stop_every=stop, leaf_level=leaf_level)
             return k, L, levelsup, parent, node_desc, weight, descriptors_near_words(parent, node_desc, n)
     raise KeyError(name)
+
+
+def vocabulary_full(k=10, L=6, seed=5, flips=24):
+    """A complete k-ary tree of depth L in breadth-first order, vectorised (the ORBvoc.txt shape k = 10, L = 6 has
+    1,111,111 nodes / 10^6 words): same construction as vocabulary(), level by level with numpy."""
+    rng = np.random.default_rng(seed)
+    parents, descs = [np.array([-1], np.int64)], [np.zeros((1, 32), np.uint8)]
+    first, count = 0, 1
+    for level in range(1, L + 1):
+        n = count * k
+        par = first + np.repeat(np.arange(count, dtype=np.int64), k)
+        if level == 1:
+            d = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        else:
+            d = np.repeat(descs[-1], k, axis=0)
+            pos = rng.integers(0, 256, (n, flips))
+            rows = np.repeat(np.arange(n), flips)
+            np.bitwise_xor.at(d, (rows, (pos >> 3).ravel()), (1 << (pos & 7)).astype(np.uint8).ravel())
+        parents.append(par)
+        descs.append(d)
+        first, count = first + count, n
+    parent = np.concatenate(parents).astype(np.int32)
+    node_desc = np.concatenate(descs)
+    weight = np.round(rng.uniform(0.5, 9.0, len(parent)), 6)
+    weight[:first] = 0.0
+    return parent, node_desc, weight
