@@ -121,6 +121,8 @@ int orbx_batch_results(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t
                        const int** d_mono, int* cap_per_frame);
 int orbx_batch_download(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
                         int* mono_index);
+/* Keypoint counts (and monoIndex values) of ALL frames of the last batch in one copy; either pointer may be NULL. */
+int orbx_batch_counts(orbx_handle h, int32_t* n_out, int32_t* mono_out);
 /* Batch scheduling knob (default 1): with n > 1 a batch of at least 8n frames is cut into n contiguous parts that run
  * the whole pipeline concurrently on n internal stream pairs (frames are independent), forked from and joined back into
  * the handle's stream, so one part's latency-bound stages (quadtree, describe) share the SMs with another part's

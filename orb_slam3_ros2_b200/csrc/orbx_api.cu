@@ -655,6 +655,16 @@ int orbx_batch_results(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t
     return ORBX_OK;
 }
 
+int orbx_batch_counts(orbx_handle h, int32_t* n_out, int32_t* mono_out) {
+    if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    DeviceGuard guard(h->device);
+    const size_t bytes = (size_t)h->lastFrames * 4;
+    if (n_out) ORBX_CUDA(cudaMemcpyAsync(n_out, h->buf.outN, bytes, cudaMemcpyDeviceToHost, h->stream));
+    if (mono_out) ORBX_CUDA(cudaMemcpyAsync(mono_out, h->buf.outMono, bytes, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return checkDeviceFlags(h);
+}
+
 int orbx_batch_download(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index) {
     if (!h || h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
     if (frame < 0 || frame >= h->lastFrames) return fail(ORBX_ERR_ARG, "frame out of range");

@@ -65,6 +65,7 @@ SYMBOLS = {
     "orbx_extract_batch_device": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int]),
     "orbx_batch_results": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _i32p]),
     "orbx_batch_download": (C.c_int, [_vp, C.c_int, _vp, _u8p, C.c_int, _i32p, _i32p]),
+    "orbx_batch_counts": (C.c_int, [_vp, _i32p, _i32p]),
     "orbx_sync": (C.c_int, [_vp]),
     "orbx_set_subbatches": (C.c_int, [_vp, C.c_int]),
     "orbx_get_stream": (_vp, [_vp]),
@@ -303,6 +304,12 @@ class ORBextractor:
         _check(lib().orbx_batch_download(self._h, frame, kps.ctypes.data_as(_vp), _ptr(desc), cap, C.byref(n),
                                          C.byref(mono)))
         return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def counts(self):
+        """-> (n, mono) int32 arrays over all frames of the last batch."""
+        n, mono = np.zeros(self._frames, np.int32), np.zeros(self._frames, np.int32)
+        _check(lib().orbx_batch_counts(self._h, _ptr(n, _i32p), _ptr(mono, _i32p)))
+        return n, mono
 
     def results_device(self):
         """-> (d_kps, d_desc, d_n, d_mono, cap) raw device addresses of the last batch."""

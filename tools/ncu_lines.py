@@ -11,8 +11,9 @@ hdr = next(r for r in rows if r and r[0] == "Line No")
 ci, sm = hdr.index("Instructions Executed"), hdr.index("# Samples")
 lines = [r for r in rows if r and r[0].isdigit() and len(r) > ci and r[ci].isdigit()]
 tot = sum(int(r[ci]) for r in lines) or 1
-tots = sum(int(r[sm]) for r in lines) or 1
+num = lambda v: int(v) if v.isdigit() else 0
+tots = sum(num(r[sm]) for r in lines) or 1
 print(f"total warp instructions {tot}, samples {tots}")
 for r in lines:
-    if int(r[ci]) > tot * minp / 100 or int(r[sm]) > tots * minp / 100:
-        print(f"{r[0]:>5} inst {100*int(r[ci])/tot:6.2f}%  stall-smp {100*int(r[sm])/tots:6.2f}% | {r[1].strip()[:110]}")
+    if int(r[ci]) > tot * minp / 100 or num(r[sm]) > tots * minp / 100:
+        print(f"{r[0]:>5} inst {100*int(r[ci])/tot:6.2f}%  stall-smp {100*num(r[sm])/tots:6.2f}% | {r[1].strip()[:110]}")
