@@ -228,6 +228,10 @@ int orbx_search_grid_top2(const orbx_keypoint* kps_t, const uint8_t* desc_t, int
 int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, const orbx_keypoint* kps_l,
                                 const uint8_t* desc_l, int nl, const orbx_keypoint* kps_r, const uint8_t* desc_r, int nr,
                                 float bf, float b, float* u_right, float* depth);
+/* The same for EVERY pair of the two handles' last batches (pair f = frame f of `left` with frame f of `right`), keypoints,
+ * descriptors and pyramids all read in place on the device: config 3 of BASELINE.json.  u_right / depth: host,
+ * [nframes][cap] floats with cap = cap_per_frame of orbx_batch_results; entries past a frame's keypoint count are unspecified. */
+int orbx_compute_stereo_matches_batch(orbx_handle left, orbx_handle right, float bf, float b, float* u_right, float* depth);
 
 /* ---- Frame::ComputeBoW (row N4): DBoW2 vocabulary-tree transform --------------------------------------------------
  * Replaces mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) (ORB_SLAM3/src/Frame.cc:738-745), i.e.

@@ -175,7 +175,13 @@ __global__ void __launch_bounds__(256) stereoRefineKernel(const __grid_constant_
                                                           const float* __restrict__ kr, int nl, const int* __restrict__ bestIdx,
                                                           const int* __restrict__ bestDist, float mbf, float maxD,
                                                           float* __restrict__ uRight, float* __restrict__ depth,
-                                                          int* __restrict__ sad) {
+                                                          int* __restrict__ sad, const StereoBatch SB) {
+    if (SB.nl) {  // pair blockIdx.y of a batch
+        const size_t o = (size_t)blockIdx.y * SB.cap;
+        nl = min(SB.nl[blockIdx.y], SB.cap);
+        kl += o * 7; kr += o * 7; bestIdx += o; bestDist += o; uRight += o; depth += o; sad += o;
+        pyrL += (size_t)blockIdx.y * SB.pyrStrideL; pyrR += (size_t)blockIdx.y * SB.pyrStrideR;
+    }
     const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (iL >= nl) return;
     float outU = -1.0f, outD = -1.0f;
@@ -249,7 +255,12 @@ __global__ void __launch_bounds__(256) stereoRefineKernel(const __grid_constant_
 // (distances are <= 121 * 255 = 30855), then every match with (float)dist >= 1.5f * 1.4f * median is removed.
 constexpr int kSadBins = 30856;
 __global__ void __launch_bounds__(1024) stereoCutKernel(const int* __restrict__ sad, int nl, float* __restrict__ uRight,
-                                                        float* __restrict__ depth) {
+                                                        float* __restrict__ depth, const StereoBatch SB) {
+    if (SB.nl) {  // pair blockIdx.x of a batch
+        const size_t o = (size_t)blockIdx.x * SB.cap;
+        nl = min(SB.nl[blockIdx.x], SB.cap);
+        sad += o; uRight += o; depth += o;
+    }
     extern __shared__ int hist[];
     __shared__ int sPart[1024];
     __shared__ int sMedian;
@@ -322,19 +333,23 @@ void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX
 
 void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, const uint8_t* pyrL, const uint8_t* pyrR,
                         const void* kl, const void* kr, int nl, const int* bestIdx, const int* bestDist, float mbf, float maxD,
-                        float* uRight, float* depth, int* sad, cudaStream_t s) {
+                        float* uRight, float* depth, int* sad, cudaStream_t s, const StereoBatch* batch) {
+    const StereoBatch SB = batch ? *batch : StereoBatch{};
+    const int frames = batch ? batch->frames : 1;
+    if (batch) nl = batch->cap;
     if (nl <= 0) return;
     StereoLevels LV{};
     for (int l = 0; l < P.nlevels; ++l) {
         LV.planeOff[l] = P.lv[l].planeOff; LV.pitch[l] = P.lv[l].pitch; LV.cols[l] = P.lv[l].w;
         LV.sf[l] = sf[l]; LV.isf[l] = isf[l];
     }
-    stereoRefineKernel<<<(nl + 7) / 8, 256, 0, s>>>(LV, pyrL, pyrR, static_cast<const float*>(kl), static_cast<const float*>(kr), nl,
-                                                    bestIdx, bestDist, mbf, maxD, uRight, depth, sad);
+    stereoRefineKernel<<<dim3((nl + 7) / 8, frames), 256, 0, s>>>(LV, pyrL, pyrR, static_cast<const float*>(kl),
+                                                                  static_cast<const float*>(kr), nl, bestIdx, bestDist, mbf, maxD,
+                                                                  uRight, depth, sad, SB);
     countLaunch();
     const size_t smem = (size_t)kSadBins * 4;
     cudaFuncSetAttribute(stereoCutKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    stereoCutKernel<<<1, 1024, smem, s>>>(sad, nl, uRight, depth);
+    stereoCutKernel<<<frames, 1024, smem, s>>>(sad, nl, uRight, depth, SB);
     countLaunch();
 }
 

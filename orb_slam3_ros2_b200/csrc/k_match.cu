@@ -163,7 +163,12 @@ __global__ void unpackPairsKernel(const unsigned long long* __restrict__ k1, con
 __global__ void stereoBandedKernel(const float* __restrict__ kl, const uint4* __restrict__ dl, int nl,
                                    const float* __restrict__ kr, const uint4* __restrict__ dr, int nr,
                                    const float* __restrict__ sf, int nRows, float maxD, int* __restrict__ bestIdx,
-                                   int* __restrict__ bestDist) {
+                                   int* __restrict__ bestDist, const StereoBatch SB) {
+    if (SB.nl) {  // pair blockIdx.y of a batch
+        const size_t o = (size_t)blockIdx.y * SB.cap;
+        nl = min(SB.nl[blockIdx.y], SB.cap); nr = min(SB.nr[blockIdx.y], SB.cap);
+        kl += o * 7; kr += o * 7; dl += o * 2; dr += o * 2; bestIdx += o; bestDist += o;
+    }
     const int iL = blockIdx.x * blockDim.x + threadIdx.x;
     if (iL >= nl) return;
     int bd = 100, bi = 0;  // ORBmatcher::TH_HIGH, bestIdxR = 0 (:867-868)
@@ -270,11 +275,14 @@ void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap,
 }
 
 void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
-                        const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s) {
+                        const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s,
+                        const StereoBatch* batch) {
+    const StereoBatch SB = batch ? *batch : StereoBatch{};
+    if (batch) nl = batch->cap;
     if (nl <= 0) return;
-    stereoBandedKernel<<<(nl + 127) / 128, 128, 0, s>>>(static_cast<const float*>(kl), reinterpret_cast<const uint4*>(dl),
-                                                        nl, static_cast<const float*>(kr),
-                                                        reinterpret_cast<const uint4*>(dr), nr, sf, nRows, maxD, bi, bd);
+    stereoBandedKernel<<<dim3((nl + 127) / 128, batch ? batch->frames : 1), 128, 0, s>>>(
+        static_cast<const float*>(kl), reinterpret_cast<const uint4*>(dl), nl, static_cast<const float*>(kr),
+        reinterpret_cast<const uint4*>(dr), nr, sf, nRows, maxD, bi, bd, SB);
     countLaunch();
 }
 

@@ -1141,6 +1141,48 @@ int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, 
     return ORBX_OK;
 }
 
+// All pairs of the two handles' last batches at once, everything read in place on the device (config 3 of BASELINE.json).
+int orbx_compute_stereo_matches_batch(orbx_handle left, orbx_handle right, float bf, float b, float* u_right, float* depth) {
+    if (!left || !right || !u_right || !depth) return fail(ORBX_ERR_ARG, "bad argument");
+    if (left->lastFrames == 0 || right->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (left->lastFrames != right->lastFrames) return fail(ORBX_ERR_ARG, "left and right batches differ in length");
+    if (left->device != right->device) return fail(ORBX_ERR_ARG, "the two extractors live on different devices");
+    const FramePlan& P = left->plan;
+    if (P.W != right->plan.W || P.H != right->plan.H || P.nlevels != right->plan.nlevels || left->sf != right->sf ||
+        P.outCap != right->plan.outCap)
+        return fail(ORBX_ERR_ARG, "left and right extractors differ in image size, pyramid or capacity");
+    DeviceGuard guard(left->device);
+    MatchScratch* S = nullptr;
+    int rc = matchScratch(left->device, &S);
+    if (rc != ORBX_OK) return rc;
+    const int F = left->lastFrames, cap = P.outCap;
+    const size_t T = (size_t)F * cap;
+    ORBX_CUDA(S->misc.reserve((size_t)kMaxLevels * 4 + T * 20 + 128));
+    cudaStream_t s = S->stream;
+    // both extractions may still be running: order the scratch stream behind the two handles
+    ORBX_CUDA(cudaEventRecord(left->ev[6], left->stream));
+    ORBX_CUDA(cudaStreamWaitEvent(s, left->ev[6], 0));
+    ORBX_CUDA(cudaEventRecord(right->ev[6], right->stream));
+    ORBX_CUDA(cudaStreamWaitEvent(s, right->ev[6], 0));
+    float* sf = (float*)S->misc.p;
+    int32_t* bi = (int32_t*)((uint8_t*)S->misc.p + kMaxLevels * 4);
+    int32_t* bd = bi + T;
+    int32_t* sad = bd + T;
+    float* ur = (float*)(sad + T);
+    float* dp = ur + T;
+    ORBX_CUDA(cudaMemcpyAsync(sf, left->sf.data(), (size_t)P.nlevels * 4, cudaMemcpyHostToDevice, s));
+    const StereoBatch SB{left->buf.outN, right->buf.outN, cap, F, (size_t)P.frameBytes, (size_t)right->plan.frameBytes};
+    const float maxD = bf / b;  // Frame.cc:841
+    launchStereoBanded(left->buf.outKps, left->buf.outDesc, 0, right->buf.outKps, right->buf.outDesc, 0, sf, P.H, maxD, bi, bd, s, &SB);
+    launchStereoRefine(P, left->sf.data(), left->isf.data(), left->buf.pyr, right->buf.pyr, left->buf.outKps, right->buf.outKps, 0, bi,
+                       bd, bf, maxD, ur, dp, sad, s, &SB);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(u_right, ur, T * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(depth, dp, T * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 // ---- Frame::ComputeBoW (row N4) ------------------------------------------------------------------------------------
 struct orbx_vocabulary {
     int device = 0;

@@ -114,8 +114,17 @@ void launchReduceKeys(const uint64_t* k1, const uint64_t* k2, int nsets, int nq,
                       cudaStream_t s);
 void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap, uint64_t* keys1, uint64_t* keys2,
                             int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, cudaStream_t s);
+// Batched ComputeStereoMatches: pair f of F reads keypoints / descriptors [f][cap], counts nl[f] / nr[f] and pyramid blocks
+// pyr + f * pyrStride; every per-keypoint output is [f][cap].  nl == nullptr = one pair (the scalar arguments apply).
+struct StereoBatch {
+    const int* nl;
+    const int* nr;
+    int cap, frames;
+    size_t pyrStrideL, pyrStrideR;
+};
 void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
-                        const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s);
+                        const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s,
+                        const StereoBatch* batch = nullptr);
 void launchAccept(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* l1,
                   const int32_t* l2, int n, uint8_t* accept, cudaStream_t s);
 int gridSortCapacity();
@@ -125,7 +134,7 @@ void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX
                       int32_t* lvl1, int32_t* lvl2, cudaStream_t s);
 void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, const uint8_t* pyrL, const uint8_t* pyrR,
                         const void* kl, const void* kr, int nl, const int* bestIdx, const int* bestDist, float mbf, float maxD,
-                        float* uRight, float* depth, int* sad, cudaStream_t s);
+                        float* uRight, float* depth, int* sad, cudaStream_t s, const StereoBatch* batch = nullptr);
 void launchStage(const uint8_t* dSrc, int sw, int sh, int sstride, int ch, int rgb, uint8_t* dDst, int dw, int dh,
                  const int16_t* tabX, const int16_t* tabY, cudaStream_t s);
 // flat DBoW2 vocabulary on the device (k_bow.cu): children of node c are CSR entries [childBegin[c], childBegin[c+1]) in the

@@ -85,6 +85,7 @@ SYMBOLS = {
                                         C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p, _i32p, C.c_int]),
     "orbx_compute_stereo_matches": (C.c_int, [_vp, _vp, C.c_int, _vp, _u8p, C.c_int, _vp, _u8p, C.c_int, C.c_float, C.c_float,
                                               _f32p, _f32p]),
+    "orbx_compute_stereo_matches_batch": (C.c_int, [_vp, _vp, C.c_float, C.c_float, _f32p, _f32p]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_voc_create": (C.c_int, [C.c_int, _i32p, _u8p, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(_vp)]),
     "orbx_voc_destroy": (None, [_vp]),
@@ -432,6 +433,15 @@ def compute_stereo_matches(left, right, kps_l, desc_l, kps_r, desc_r, bf, b, fra
                                              kps_r.ctypes.data_as(_vp), _ptr(desc_r), len(kps_r), float(bf), float(b),
                                              _ptr(ur, _f32p), _ptr(dp, _f32p)))
     return ur[:n], dp[:n]
+
+
+def compute_stereo_matches_batch(left, right, bf, b, out=None):
+    """Frame::ComputeStereoMatches for every pair of the two extractors' last batches, all inputs read on the device ->
+    (mvuRight, mvDepth), each (F, cap) float32 (entries past a frame's keypoint count are unspecified)."""
+    F, cap = left._frames, left.results_device()[4]
+    ur, dp = out if out is not None else (np.zeros((F, cap), np.float32), np.zeros((F, cap), np.float32))
+    _check(lib().orbx_compute_stereo_matches_batch(left._h, right._h, float(bf), float(b), _ptr(ur, _f32p), _ptr(dp, _f32p)))
+    return ur, dp
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):

@@ -85,6 +85,38 @@ def test_compute_stereo_matches_bit_exact(orbx, oracle, w, h, nf):
     assert (ur0 == -1).all() and (dp0 == -1).all()
 
 
+def test_compute_stereo_matches_batch_equals_per_pair_and_oracle(orbx, oracle):
+    """Config 3: KITTI-shape pairs in one call, everything read on the device == the per-pair call == the oracle."""
+    w, h, nf, F = 1241, 376, 2000, 12
+    exl, exr = orbx.ORBextractor(nf, 1.2, 8, 20, 7), orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+    exl.set_subbatches(2)
+    left, right = synth.frames(0, F, w, h), synth.frames(0, F, w, h, right=True)
+    exl.extract_batch(left, (0, 0), download=False)
+    exr.extract_batch(right, (0, 0), download=False)
+    bf, b = 386.1448, 0.53716
+    ur, dp = orbx.compute_stereo_matches_batch(exl, exr, bf, b)
+    assert ur.shape == (F, exl.capacity)
+    t = None
+    for f in range(F):
+        _, kl, dl = exl.download(f)
+        _, kr, dr = exr.download(f)
+        u1, d1 = orbx.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, b, frame=f)
+        n = len(kl)
+        assert np.array_equal(ur[f, :n].view(np.uint32), u1.view(np.uint32)), f
+        assert np.array_equal(dp[f, :n].view(np.uint32), d1.view(np.uint32)), f
+        if f in (0, F - 1):
+            ol, orr = oracle.PortExtractor(nfeatures=nf), oracle.PortExtractor(nfeatures=nf)
+            ol.extract(left[f], (0, 0)); orr.extract(right[f], (0, 0))
+            t = ol.tables()
+            wu, wd = oracle.compute_stereo_matches(kl, dl, kr, dr, t["scale"], t["inv_scale"], [ol.pyramid(l) for l in range(8)],
+                                                   [orr.pyramid(l) for l in range(8)], bf, b)
+            assert np.array_equal(ur[f, :n].view(np.uint32), wu.view(np.uint32))
+            assert np.array_equal(dp[f, :n].view(np.uint32), wd.view(np.uint32))
+            # the synthetic right image is the left one shifted by 16 px: matched disparities sit there
+            m = ur[f, :n] >= 0
+            assert m.sum() > 300 and abs(np.median(kl["x"][m] - ur[f, :n][m]) - 16.0) < 1.0
+
+
 def test_extract_color_staging_matches_cv2_goldens_and_oracle(orbx, oracle):
     """orbx_extract_color: resize + cvtColor fused ahead of operator() (System.cc:420-425, Tracking.cc:1569-1582)."""
     from conftest import load_golden
