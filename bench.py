@@ -31,6 +31,7 @@ W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 LAP = (0, 1000)  # Frame.cc:311 passes {0,1000} for monocular frames
 E2E_DEPTH = 3   # measured sweep (handles x depth -> frames/s): 2x1 90.2k, 4x1 98.6k, 2x2 110.7k, 4x2 100.2k, 2x3 112.7k, 1x3 112.1k, 3x3 104.4k
 E2E_HANDLES = 2
+RESIDENT_HANDLES = 2  # measured (handles x sub-batches -> frames/s): 1x1 127.9k, 1x2 129.2k, 2x1 131.8k, 2x2 134.6k, 3x1 134.3k, 3x2 132.3k
 SUBBATCHES = 2  # default of --subbatches; measured sweep (profiles/r01_v6_subbatch_sweep_*): 1 -> 108.7k, 2 -> 113.3k, 3 -> 113.2k, 4 -> 113.0k, 6 -> 106.4k
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
 
@@ -254,20 +255,32 @@ def run_ours(args, rank, world, local_rank):
         orbx._check(orbx.lib().orbx_synth_frames_device(imgs[b].data_ptr(), (rank * nb + b) * F, F, W, H, 42, 0, local_rank))
     midx = [torch.empty((max(F - 1, 1), cap), dtype=torch.int32, device=dev) for _ in range(4)]
     stream = torch.cuda.ExternalStream(ex.stream_ptr(), device=dev)
+    # --resident-handles N: steps alternate over N extractor handles (own streams and scratch), so the tail of one step
+    # (describe, matching: latency-bound, partly idle SMs) overlaps the head of the next; the timed region is bracketed by
+    # events on handle 0's stream after every handle's stream has been joined into it
+    exs = [ex]
+    midxs = [midx]
+    for _ in range(1, max(args.resident_handles, 1)):
+        e = orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local_rank)
+        e.set_subbatches(args.subbatches)
+        exs.append(e)
+        midxs.append([torch.empty((max(F - 1, 1), cap), dtype=torch.int32, device=dev) for _ in range(4)])
 
     def step(i):
-        ex.extract_batch_device(imgs[i % nb].data_ptr(), F, W, H, LAP)
+        e, m4 = exs[i % len(exs)], midxs[i % len(exs)]
+        e.extract_batch_device(imgs[i % nb].data_ptr(), F, W, H, LAP)
         if not args.skip_match:
-            ex.match_consecutive_device(*[m.data_ptr() for m in midx])
+            e.match_consecutive_device(*[m.data_ptr() for m in m4])
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(args.warmup):
+    for i in range(max(args.warmup, len(exs))):
         step(i)
-    ex.sync()
+    for e in exs:
+        e.sync()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -279,9 +292,15 @@ def run_ours(args, rank, world, local_rank):
         e0.record()
     for i in range(args.steps):
         step(i)
+    for e in exs[1:]:  # join the other handles' streams into handle 0's before the closing event
+        ev = torch.cuda.Event()
+        with torch.cuda.stream(torch.cuda.ExternalStream(e.stream_ptr(), device=dev)):
+            ev.record()
+        stream.wait_event(ev)
     with torch.cuda.stream(stream):
         e1.record()
-    ex.sync()
+    for e in exs:
+        e.sync()
     barrier()
     ms = e0.elapsed_time(e1)
     launches = orbx.launch_count() - launches0
@@ -487,6 +506,8 @@ def main():
     ap.add_argument("--db-rows", type=int, default=10_000_000)
     ap.add_argument("--subbatches", type=int, default=SUBBATCHES,
                     help="parts of a batch run concurrently on internal stream pairs (orbx_set_subbatches)")
+    ap.add_argument("--resident-handles", type=int, default=RESIDENT_HANDLES,
+                    help="extractor handles the resident (value) leg alternates its steps over")
     ap.add_argument("--e2e-handles", type=int, default=E2E_HANDLES, help="extractor handles the e2e leg pipelines a step over")
     ap.add_argument("--e2e-depth", type=int, default=E2E_DEPTH, help="generations of handles/host buffers in flight in the e2e leg")
     ap.add_argument("--only-e2e", action="store_true", help="development: resident leg + e2e leg only, print the e2e object")
@@ -545,7 +566,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": ctx["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": f"euroc752x480_nf1000_batch{F}_extract" + ("" if args.skip_match else "+consecutive_top2"),
-                   "frames_per_gpu_per_step": F, "subbatches": args.subbatches, "nfeatures": NFEAT, "levels": NLEVELS, "fast": [INI_TH, MIN_TH],
+                   "frames_per_gpu_per_step": F, "subbatches": args.subbatches, "resident_handles": args.resident_handles, "nfeatures": NFEAT, "levels": NLEVELS, "fast": [INI_TH, MIN_TH],
                    "l2": "inputs rotate over 2 device batches (2x92 MB) and ~0.7 GB of intermediates are rewritten per step (> 126 MB L2)",
                    "keypoints_per_frame": ctx["nkp"], "fast_candidates_frame0": ctx["ncand"]},
         "clocks": ctx["clocks"], "gpu_launches": int(ctx["launches"]),

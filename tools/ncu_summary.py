@@ -10,7 +10,9 @@ cols = [("gpu__time_duration.sum", "us"), ("dram__bytes_read.sum", "rdMB"), ("dr
         ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu%"), ("smsp__inst_executed.sum", "winst"),
         ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "bankconf"), ("launch__registers_per_thread", "regs"),
         ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram%"), ("lts__t_sector_hit_rate.pct", "l2hit%")]
-print("kernel".ljust(28), " ".join(n.rjust(9) for _, n in cols), " grid")
+units = rows[1]
+names = [(units[idx[c]] if c == "gpu__time_duration.sum" and c in idx else n) for c, n in cols]  # the duration column's own unit
+print("kernel".ljust(28), " ".join(n.rjust(9) for n in names), " grid")
 for r in rows[2:]:
     name = r[idx["Kernel Name"]].split("(")[0].split("::")[-1][:28]
     vals = []
