@@ -18,15 +18,28 @@
 //               column sum is four dp2a (16-bit x 8-bit, 2-way) on consecutive pairs; even and odd output rows differ
 //               only in the coefficient bytes.  The rounding constant rides in the first accumulator.
 // H <= 65280 fits 16 bits and V <= 65280 * 256 + 32768 fits 32 bits, exactly OpenCV's fixed-point path.
+//
+// v3 (from the per-line ncu profile of v2: the level walk, the tile division and the staging loop were 35 % of the
+// kernel's instructions, the arithmetic a minority):
+//   * the (level, tile row, tile column) of a CTA comes from a table built with the plan (one load instead of a walk over
+//     the levels and an integer division);
+//   * the (32+6) x 144-byte input tile is staged by TMA: ONE cp.async.bulk.tensor.3d per CTA against the level's tensor map
+//     (box 144 x 38 x 1; the tile's first byte is padded column x0 + 16, always 16-byte aligned), completion on an
+//     mbarrier; rows / columns past the plane are zero-filled by the copy engine and only feed outputs that are not stored;
+//   * the final ">> 16" and the byte packing are one PRMT pair (the result is byte 2 of the accumulator).
+#include <cstring>
+
 #include "orbx_internal.cuh"
+#include "tma.cuh"
 
 namespace orbx {
 namespace {
 
 constexpr int kTileW = 128, kTileH = 32, kInRows = kTileH + 6, kInPitch = 144, kPairs = kInRows / 2;
 
-__global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
-                                                  uint8_t* __restrict__ blur) {
+// v2: staging with ordinary loads, level walk per CTA (kept for A/B runs: ORBX_FAST_TMA=0)
+__global__ void __launch_bounds__(256) blurKernelLd(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
+                                                    uint8_t* __restrict__ blur) {
     __shared__ __align__(16) uint8_t sIn[kInRows * kInPitch];
     __shared__ __align__(16) uint32_t sHp[kPairs * kTileW];  // (H[2m][x] | H[2m+1][x] << 16)
 
@@ -106,11 +119,116 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     }
 }
 
+
+__global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FramePlan P, const __grid_constant__ LevelMaps M,
+                                                  const uint32_t* __restrict__ tileTab, uint8_t* __restrict__ blur, int frame0) {
+    __shared__ __align__(128) uint8_t sIn[kInRows * kInPitch];
+    __shared__ __align__(16) uint32_t sHp[kPairs * kTileW];  // (H[2m][x] | H[2m+1][x] << 16)
+    __shared__ __align__(8) uint64_t bar;
+
+    const int tid = threadIdx.x;
+    const uint32_t te = __ldg(tileTab + blockIdx.x);  // level << 24 | tile row << 12 | tile column
+    const int l = (int)(te >> 24);
+    const int x0 = (int)(te & 0xfffu) * kTileW, y0 = (int)((te >> 12) & 0xfffu) * kTileH;
+    const LevelPlan& L = P.lv[l];
+    if (tid == 0) {
+        mbarInit(&bar, 1);
+        mbarInitFence();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        // padded coordinates (x0 + 16, y0 + 16): staged byte 0 of a row = level column x0 - 3
+        mbarExpectTx(&bar, kInRows * kInPitch);
+        tmaLoadTile(sIn, &M.m[l], x0 + 16, y0 + 16, frame0 + (int)blockIdx.y, &bar);
+    }
+    mbarWait(&bar, 0);
+
+    // horizontal pass: item = (row pair m, 4 columns g)
+    constexpr uint32_t K1 = 0x38302212u, K2 = 0x00122230u;  // (18,34,48,56), (48,34,18,0)
+    const int g = tid & 31;
+    for (int m = tid >> 5; m < kPairs; m += 8) {
+        uint32_t h[2][4];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(sIn + (2 * m + rr) * kInPitch) + g;
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t a = j ? __funnelshift_r(w0, w1, 8 * j) : w0;
+                const uint32_t b = j ? __funnelshift_r(w1, w2, 8 * j) : w1;
+                h[rr][j] = __dp4a(a, K1, __dp4a(b, K2, 0u));
+            }
+        }
+        uint4 pk;  // low half = row 2m, high half = row 2m + 1 (H < 2^16)
+        pk.x = __byte_perm(h[0][0], h[1][0], 0x5410);
+        pk.y = __byte_perm(h[0][1], h[1][1], 0x5410);
+        pk.z = __byte_perm(h[0][2], h[1][2], 0x5410);
+        pk.w = __byte_perm(h[0][3], h[1][3], 0x5410);
+        *reinterpret_cast<uint4*>(sHp + m * kTileW + g * 4) = pk;
+    }
+    __syncthreads();
+
+    // vertical pass: thread = 4 columns x 4 rows; output row 4q+i taps staged rows 4q+i .. 4q+i+6 = pairs 2q .. 2q+4
+    const int tx = tid & 31, q = tid >> 5;
+    const int x = x0 + tx * 4, yq = y0 + q * 4;
+    if (x >= L.bpitch || yq >= L.h) return;
+    uint4 pr[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * q + k) * kTileW + tx * 4);
+    uint8_t* out = blur + (size_t)blockIdx.y * P.blurBytes + L.blurOff + (size_t)yq * L.bpitch + x;
+    const int rows = min(4, L.h - yq);
+    // coefficient byte pairs (low byte multiplies the even row of a pair)
+    constexpr uint32_t Ea = 0x2212u, Eb = 0x3830u, Ec = 0x2230u, Ed = 0x0012u;   // even start: 18,34 | 48,56 | 48,34 | 18,0
+    constexpr uint32_t Oa = 0x1200u, Ob = 0x3022u, Oc = 0x3038u, Od = 0x1222u;   // odd start:  0,18 | 34,48 | 56,48 | 34,18
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int b = i >> 1;  // first pair
+        const uint32_t ca = (i & 1) ? Oa : Ea, cb = (i & 1) ? Ob : Eb, cc = (i & 1) ? Oc : Ec, cd = (i & 1) ? Od : Ed;
+        uint32_t v[4];
+        const uint32_t* p0 = &pr[b].x; const uint32_t* p1 = &pr[b + 1].x; const uint32_t* p2 = &pr[b + 2].x; const uint32_t* p3 = &pr[b + 3].x;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t acc = __dp2a_lo(p0[k], ca, 32768u);
+            acc = __dp2a_lo(p1[k], cb, acc);
+            acc = __dp2a_lo(p2[k], cc, acc);
+            v[k] = __dp2a_lo(p3[k], cd, acc);   // (V + 32768); the pixel is bits 16..23 = byte 2 (V + 32768 < 2^24)
+        }
+        const uint32_t word = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+        if (i < rows) *reinterpret_cast<uint32_t*>(out + i * L.bpitch) = word;
+    }
+}
+
 }  // namespace
+
+size_t levelMapsBytes() { return sizeof(LevelMaps); }
+
+// (level << 24 | tile row << 12 | tile column) of every 128 x 32 blur tile, in the order of the plan's blurTile0
+void buildBlurTileTable(const FramePlan& P, std::vector<uint32_t>& tab) {
+    tab.clear();
+    for (int l = 0; l < P.nlevels; ++l) {
+        const LevelPlan& L = P.lv[l];
+        const int ty = (L.h + kTileH - 1) / kTileH;
+        for (int y = 0; y < ty; ++y)
+            for (int x = 0; x < L.blurTilesX; ++x) tab.push_back(((uint32_t)l << 24) | ((uint32_t)y << 12) | (uint32_t)x);
+    }
+}
+
+int buildBlurMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out) {
+    LevelMaps* M = reinterpret_cast<LevelMaps*>(out);
+    std::memset(M, 0, sizeof(LevelMaps));
+    for (int l = 0; l < P.nlevels; ++l) {
+        const int rc = encodeLevelMap(&M->m[l], P, l, pyrBase, capFrames, kInPitch, kInRows);
+        if (rc != 0) return rc;
+    }
+    return 0;
+}
 
 void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     static_assert(kTileW == 128 && kTileH == 32, "the plan's blurTile0 / blurTilesX assume 128 x 32 tiles");
-    blurKernel<<<dim3(P.blurTiles, F), 256, 0, s>>>(P, B.pyr, B.blur);
+    if (B.blurMaps)
+        blurKernel<<<dim3(P.blurTiles, F), 256, 0, s>>>(P, *reinterpret_cast<const LevelMaps*>(B.blurMaps), B.blurTab, B.blur, B.frame0);
+    else
+        blurKernelLd<<<dim3(P.blurTiles, F), 256, 0, s>>>(P, B.pyr, B.blur);
     countLaunch();
 }
 

@@ -37,9 +37,8 @@
 #include <cstring>
 #include <vector>
 
-#include <cuda.h>
-
 #include "orbx_internal.cuh"
+#include "tma.cuh"
 
 namespace orbx {
 namespace {
@@ -50,36 +49,7 @@ constexpr int kPixCap = 256;      // pixel list capacity per warp (one segment o
 __device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
 __device__ __forceinline__ uint32_t min3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
 
-__device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbarInit(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbarExpectTx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smemAddr(bar)), "r"(parity) : "memory");
-}
-// one box of a 3-D u8 tensor (x = byte column, y = row, z = frame) -> dense rows in shared memory
-__device__ __forceinline__ void tmaLoadTile(void* dst, const CUtensorMap* map, int x, int y, int z, uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
-            smemAddr(dst)),
-        "l"(map), "r"(x), "r"(y), "r"(z), "r"(smemAddr(bar))
-        : "memory");
-}
-
-struct FastMaps {
-    CUtensorMap m[kMaxLevels];
-};
+using FastMaps = LevelMaps;
 
 // arc strength of two pixels at once: q[k] = ring pixel k of pixel A in the low half, of pixel B in the high half
 __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32_t cen) {
@@ -133,7 +103,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
     if (TMA) {
         if (lane == 0) {
             mbarInit(bar, 1);
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            mbarInitFence();
         }
         __syncwarp();
     }
@@ -454,6 +424,19 @@ size_t fastMapsBytes() { return sizeof(FastMaps); }
 // plane (extent = pitch), y = plane row, z = frame (stride frameBytes); box = 64 x (hCell+6) x 1.  Sub-batches address
 // their frames through the z coordinate (Buffers::frame0), so the maps only change when the buffer is reallocated.
 int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out) {
+    FastMaps* M = reinterpret_cast<FastMaps*>(out);
+    std::memset(M, 0, sizeof(FastMaps));
+    for (int l = 0; l < P.nlevels; ++l) {
+        const LevelPlan& L = P.lv[l];
+        if (L.nCols <= 0 || L.nRows <= 0 || wideLevel(L)) continue;
+        const int rc = encodeLevelMap(&M->m[l], P, l, pyrBase, capFrames, 64, L.hCell + 6);
+        if (rc != 0) return rc;
+    }
+    return 0;
+}
+
+// shared by every tile-staging kernel (tma.cuh)
+int encodeLevelMap(CUtensorMap* out, const FramePlan& P, int l, const uint8_t* pyrBase, int capFrames, int boxW, int boxH) {
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -466,21 +449,15 @@ int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, voi
             return -1;
         encode = reinterpret_cast<EncodeFn>(fn);
     }
-    FastMaps* M = reinterpret_cast<FastMaps*>(out);
-    std::memset(M, 0, sizeof(FastMaps));
-    for (int l = 0; l < P.nlevels; ++l) {
-        const LevelPlan& L = P.lv[l];
-        if (L.nCols <= 0 || L.nRows <= 0 || wideLevel(L)) continue;
-        const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.h + 2 * kEdge), (cuuint64_t)std::max(capFrames, 1)};
-        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.frameBytes};
-        const cuuint32_t box[3] = {64u, (cuuint32_t)(L.hCell + 6), 1u};
-        const cuuint32_t estr[3] = {1u, 1u, 1u};
-        const CUresult r = encode(&M->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(pyrBase) + L.planeOff, dims,
-                                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) return -(int)r - 100;
-    }
-    return 0;
+    const LevelPlan& L = P.lv[l];
+    const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.h + 2 * kEdge), (cuuint64_t)std::max(capFrames, 1)};
+    const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.frameBytes};
+    const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(pyrBase) + L.planeOff, dims, strides, box,
+                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : -(int)r - 100;
 }
 
 static bool wideLevel(const LevelPlan& L) { return L.wCell + 6 > 48 || L.hCell + 6 > 50; }

@@ -84,6 +84,8 @@ struct orbx_extractor {
     DevMem mFastTab;
     // TMA tensor maps of the FAST tile staging (one per level, over the whole mPyr allocation); rebuilt with the buffers
     alignas(64) unsigned char fastMaps[kMaxLevels * 128];
+    alignas(64) unsigned char blurMaps[kMaxLevels * 128];
+    DevMem mBlurTab;
     bool useTma = true;
     DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
     int stagedW = 0, stagedH = 0;
@@ -199,6 +201,11 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         ORBX_CUDA(h->mFastTab.reserve(std::max<size_t>(cells.size() * 4, 16)));
         if (!cells.empty())
             ORBX_CUDA(cudaMemcpyAsync(h->mFastTab.p, cells.data(), cells.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        std::vector<uint32_t> btiles;
+        buildBlurTileTable(h->plan, btiles);
+        if ((int)btiles.size() != h->plan.blurTiles) return fail(ORBX_ERR_CUDA, "blur tile table does not match the plan");
+        ORBX_CUDA(h->mBlurTab.reserve(std::max<size_t>(btiles.size() * 4, 16)));
+        ORBX_CUDA(cudaMemcpyAsync(h->mBlurTab.p, btiles.data(), btiles.size() * 4, cudaMemcpyHostToDevice, h->stream));
         ORBX_CUDA(cudaStreamSynchronize(h->stream));
         h->havePlan = true;
         h->capFrames = 0;
@@ -226,6 +233,9 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
             if (fastMapsBytes() > sizeof(h->fastMaps)) return fail(ORBX_ERR_CUDA, "tensor map table larger than expected");
             const int rc = buildFastMaps(P, (const uint8_t*)h->mPyr.p, F, h->fastMaps);
             if (rc != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string(rc) + ")");
+            if (levelMapsBytes() > sizeof(h->blurMaps)) return fail(ORBX_ERR_CUDA, "tensor map table larger than expected");
+            const int rb = buildBlurMaps(P, (const uint8_t*)h->mPyr.p, F, h->blurMaps);
+            if (rb != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for the blur tiles (" + std::to_string(rb) + ")");
         }
     }
     Buffers& B = h->buf;
@@ -235,6 +245,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
     B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
     B.fastMaps = h->useTma ? h->fastMaps : nullptr; B.frame0 = 0;
+    B.blurMaps = h->useTma ? h->blurMaps : nullptr; B.blurTab = (uint32_t*)h->mBlurTab.p;
     return ORBX_OK;
 }
 
@@ -391,7 +402,7 @@ void orbx_destroy(orbx_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
-                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab};
+                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab};
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 9; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
