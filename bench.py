@@ -379,7 +379,7 @@ def run_e2e(ctx, args, world):
         step()
     drain()
     ctx["barrier"]()
-    steps = max(3, min(args.steps, 10))
+    steps = max(3, args.steps)
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
