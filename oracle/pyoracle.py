@@ -494,3 +494,75 @@ class PortVocabulary:
         if rc != 0:
             raise ValueError("malformed vocabulary tree")
         return _bow_pack(o)
+
+
+# ---- the reference's own Frame.cc / ORBmatcher.cc function bodies (oracle/_ref/librefslices.so) ------------------------
+
+def refslices_path():
+    return os.path.join(HERE, "_ref", "librefslices.so")
+
+
+def have_refslices():
+    return os.path.exists(refslices_path())
+
+
+_refslices = None
+
+
+def _slices():
+    global _refslices
+    if _refslices is None:
+        lib = C.CDLL(refslices_path())
+        lib.refslice_descriptor_distance.argtypes = [_u8p, _u8p]
+        lib.refslice_compute_stereo_matches.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_void_p, _u8p, C.c_int, _f32p, _f32p, C.c_int,
+                                                        C.c_void_p, C.c_void_p, _i32p, _i32p, C.c_float, C.c_float, _f32p, _f32p]
+        lib.refslice_grid_top2.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, _u8p,
+                                           C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p]
+        _refslices = lib
+    return _refslices
+
+
+def ref_thresholds():
+    """(TH_LOW, TH_HIGH) as the reference's ORBmatcher.cc:35-37 defines them."""
+    return _slices().refslice_th_low(), _slices().refslice_th_high()
+
+
+def ref_descriptor_distance(a, b):
+    """ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074), the reference's own body."""
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return _slices().refslice_descriptor_distance(_ptr(a), _ptr(b))
+
+
+def ref_compute_stereo_matches(kl, dl, kr, dr, scale_factors, inv_scale_factors, pyr_l, pyr_r, bf, b):
+    """Frame::ComputeStereoMatches (Frame.cc:811-981), the reference's own body; arguments as compute_stereo_matches."""
+    kl = np.ascontiguousarray(kl); kr = np.ascontiguousarray(kr)
+    dl = np.ascontiguousarray(dl, dtype=np.uint8); dr = np.ascontiguousarray(dr, dtype=np.uint8)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32); isf = np.ascontiguousarray(inv_scale_factors, dtype=np.float32)
+    nl = len(sf)
+    pl = [np.ascontiguousarray(p, dtype=np.uint8) for p in pyr_l]
+    pr = [np.ascontiguousarray(p, dtype=np.uint8) for p in pyr_r]
+    ptr_l = (C.c_void_p * nl)(*[p.ctypes.data for p in pl])
+    ptr_r = (C.c_void_p * nl)(*[p.ctypes.data for p in pr])
+    w = np.array([p.shape[1] - 38 for p in pl], dtype=np.int32); h = np.array([p.shape[0] - 38 for p in pl], dtype=np.int32)
+    n = len(kl)
+    ur = np.zeros(max(n, 1), dtype=np.float32); dp = np.zeros(max(n, 1), dtype=np.float32)
+    _slices().refslice_compute_stereo_matches(kl.ctypes.data_as(C.c_void_p), _ptr(dl), n, kr.ctypes.data_as(C.c_void_p), _ptr(dr), len(kr),
+                                              _ptr(sf, _f32p), _ptr(isf, _f32p), nl, ptr_l, ptr_r, _ptr(w, _i32p), _ptr(h, _i32p),
+                                              float(bf), float(b), _ptr(ur, _f32p), _ptr(dp, _f32p))
+    return ur[:n], dp[:n]
+
+
+def ref_grid_top2(kps_t, desc_t, bounds, queries, desc_q):
+    """AssignFeaturesToGrid + GetFeaturesInArea + PosInGrid (Frame.cc:385-416, 657-735, the reference's own bodies) and the
+    strict-< best/second loop over what they return -> idx1, d1, idx2, d2, candidates per query.  queries: the 24-byte
+    orbx_grid_query records (ur is ignored: monocular frame)."""
+    kps_t = np.ascontiguousarray(kps_t); queries = np.ascontiguousarray(queries)
+    desc_t = np.ascontiguousarray(desc_t, dtype=np.uint8); desc_q = np.ascontiguousarray(desc_q, dtype=np.uint8)
+    nq = len(queries)
+    q20 = np.zeros((nq, 20), np.uint8)
+    if nq:
+        q20[:] = queries.view(np.uint8).reshape(nq, 24)[:, :20]
+    out = [np.zeros(max(nq, 1), dtype=np.int32) for _ in range(5)]
+    _slices().refslice_grid_top2(kps_t.ctypes.data_as(C.c_void_p), _ptr(desc_t), len(kps_t), *[float(b) for b in bounds],
+                                 q20.ctypes.data, _ptr(desc_q), nq, *[_ptr(o, _i32p) for o in out])
+    return [o[:nq] for o in out]

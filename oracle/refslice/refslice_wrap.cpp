@@ -1,0 +1,118 @@
+// refslice_wrap.cpp — TEST INFRASTRUCTURE (oracle side), not product code.
+//
+// The reference's OWN function bodies, cut out of /root/reference/ORB_SLAM3/src/{Frame,ORBmatcher}.cc by oracle/Makefile
+// (line ranges below, each checked against its expected first line), compiled unchanged inside the class shells of
+// shim.h, behind an extern "C" façade:
+//   ORBmatcher.cc:35-37      TH_HIGH / TH_LOW / HISTO_LENGTH
+//   ORBmatcher.cc:2058-2074  ORBmatcher::DescriptorDistance
+//   Frame.cc:385-416         Frame::AssignFeaturesToGrid
+//   Frame.cc:657-723         Frame::GetFeaturesInArea
+//   Frame.cc:725-735         Frame::PosInGrid
+//   Frame.cc:811-981         Frame::ComputeStereoMatches
+// They pin oracle/match_oracle.cpp (tests/test_oracle_refslices.py).  Built only where /root/reference exists.
+#include <cstdint>
+#include <cstring>
+
+#include "shim.h"
+
+namespace ORB_SLAM3 {
+float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+#include "ORBmatcher_consts.inc"
+#include "ORBmatcher_DescriptorDistance.inc"
+#include "Frame_AssignFeaturesToGrid.inc"
+#include "Frame_GetFeaturesInArea.inc"
+#include "Frame_PosInGrid.inc"
+#include "Frame_ComputeStereoMatches.inc"
+}  // namespace ORB_SLAM3
+
+using ORB_SLAM3::Frame;
+using ORB_SLAM3::ORBmatcher;
+
+namespace {
+static_assert(sizeof(cv::KeyPoint) == 28, "KeyPoint layout");
+std::vector<cv::KeyPoint> keypoints(const void* p, int n) {
+    std::vector<cv::KeyPoint> v(n);
+    if (n) std::memcpy(v.data(), p, (size_t)n * sizeof(cv::KeyPoint));
+    return v;
+}
+cv::Mat descriptors(const uint8_t* p, int n) {
+    cv::Mat m(n > 0 ? n : 1, 32, CV_8U);
+    if (n) std::memcpy(m.data, p, (size_t)n * 32);
+    return m;
+}
+}  // namespace
+
+extern "C" {
+
+int refslice_th_low() { return ORBmatcher::TH_LOW; }
+int refslice_th_high() { return ORBmatcher::TH_HIGH; }
+
+int refslice_descriptor_distance(const uint8_t* a, const uint8_t* b) {
+    alignas(4) uint8_t aa[32], bb[32];
+    std::memcpy(aa, a, 32);
+    std::memcpy(bb, b, 32);
+    return ORBmatcher::DescriptorDistance(cv::Mat(1, 32, CV_8U, aa), cv::Mat(1, 32, CV_8U, bb));
+}
+
+// Frame::ComputeStereoMatches on keypoints / descriptors / padded pyramid planes handed in by the caller.
+// planes_l / planes_r: nlevels pointers to (h_l + 38) x (w_l + 38) padded planes (mvImagePyramid[l] is the ROI at (19, 19),
+// ORBextractor.cc:1176-1178).  u_right / depth: nl floats.
+void refslice_compute_stereo_matches(const void* kps_l, const uint8_t* desc_l, int nl, const void* kps_r, const uint8_t* desc_r,
+                                     int nr, const float* scale, const float* inv_scale, int nlevels, const uint8_t* const* planes_l,
+                                     const uint8_t* const* planes_r, const int* w, const int* h, float bf, float b, float* u_right,
+                                     float* depth) {
+    ORB_SLAM3::ORBextractor L, R;
+    for (int l = 0; l < nlevels; ++l) {
+        const int pw = w[l] + 38, ph = h[l] + 38;
+        cv::Mat pl(ph, pw, CV_8U, const_cast<uint8_t*>(planes_l[l]), (size_t)pw), pr(ph, pw, CV_8U, const_cast<uint8_t*>(planes_r[l]), (size_t)pw);
+        L.mvImagePyramid.push_back(pl(cv::Rect(19, 19, w[l], h[l])));
+        R.mvImagePyramid.push_back(pr(cv::Rect(19, 19, w[l], h[l])));
+    }
+    Frame F;
+    F.mpORBextractorLeft = &L; F.mpORBextractorRight = &R;
+    F.N = nl;
+    F.mvKeys = keypoints(kps_l, nl); F.mvKeysRight = keypoints(kps_r, nr);
+    F.mDescriptors = descriptors(desc_l, nl); F.mDescriptorsRight = descriptors(desc_r, nr);
+    F.mvScaleFactors.assign(scale, scale + nlevels); F.mvInvScaleFactors.assign(inv_scale, inv_scale + nlevels);
+    F.mbf = bf; F.mb = b;
+    F.ComputeStereoMatches();
+    std::memcpy(u_right, F.mvuRight.data(), (size_t)nl * 4);
+    std::memcpy(depth, F.mvDepth.data(), (size_t)nl * 4);
+}
+
+// Monocular frame (Nleft == -1): AssignFeaturesToGrid over mvKeysUn = kps_t, then for every query GetFeaturesInArea and the
+// strict-< best/second loop of ORBmatcher::SearchByProjection (ORBmatcher.cc:75-117) with the reference's DescriptorDistance.
+// queries: nq x (u, v, r, min_level, max_level) as 3 floats + 2 int32 (20 bytes).  cand_count (may be NULL): candidates per query.
+void refslice_grid_top2(const void* kps_t, const uint8_t* desc_t, int nt, float min_x, float max_x, float min_y, float max_y,
+                        const uint8_t* queries, const uint8_t* desc_q, int nq, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,
+                        int32_t* cand_count) {
+    Frame F;
+    F.N = nt;
+    F.Nleft = -1;
+    F.mvKeysUn = keypoints(kps_t, nt);
+    F.mDescriptors = descriptors(desc_t, nt);
+    Frame::mnMinX = min_x; Frame::mnMaxX = max_x; Frame::mnMinY = min_y; Frame::mnMaxY = max_y;
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);   // Frame.cc:251
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);  // Frame.cc:252
+    F.AssignFeaturesToGrid();
+    cv::Mat Q = descriptors(desc_q, nq);
+    for (int q = 0; q < nq; ++q) {
+        float u, v, r;
+        int32_t lo, hi;
+        std::memcpy(&u, queries + (size_t)q * 20, 4); std::memcpy(&v, queries + (size_t)q * 20 + 4, 4);
+        std::memcpy(&r, queries + (size_t)q * 20 + 8, 4); std::memcpy(&lo, queries + (size_t)q * 20 + 12, 4);
+        std::memcpy(&hi, queries + (size_t)q * 20 + 16, 4);
+        const std::vector<size_t> cand = F.GetFeaturesInArea(u, v, r, lo, hi);
+        int best = 256, best2 = 256, bi = -1, bi2 = -1;
+        const cv::Mat dq = Q.row(q);
+        for (size_t j = 0; j < cand.size(); ++j) {
+            const int dist = ORBmatcher::DescriptorDistance(dq, F.mDescriptors.row((int)cand[j]));
+            if (dist < best) { best2 = best; bi2 = bi; best = dist; bi = (int)cand[j]; }
+            else if (dist < best2) { best2 = dist; bi2 = (int)cand[j]; }
+        }
+        idx1[q] = bi; d1[q] = best; idx2[q] = bi2; d2[q] = best2;
+        if (cand_count) cand_count[q] = (int32_t)cand.size();
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,60 @@
+// refslice/shim.h — TEST INFRASTRUCTURE (oracle side), not product code.
+//
+// Declarations that let SLICES of the reference's own src/Frame.cc and src/ORBmatcher.cc compile on their own: the
+// whole translation units need Eigen, Sophus, DBoW2, g2o, KeyFrame, MapPoint ..., but the functions on
+// this path only touch a handful of members.  oracle/Makefile cuts the function bodies out of the reference files
+// where they lie (sed by line range, checked against the expected first line) into oracle/_ref/slices/*.inc and
+// compiles them, unchanged, inside the class shells below.  Member names and types follow include/Frame.h,
+// include/ORBmatcher.h and include/ORBextractor.h; nothing here restates an algorithm.
+#pragma once
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstddef>
+#include <utility>
+#include <vector>
+
+#include <opencv2/core/core.hpp>
+
+using namespace std;  // the reference's headers do this (ORBmatcher.cc:30, and Frame.cc relies on it through its includes)
+
+#define FRAME_GRID_ROWS 48  // include/Frame.h:44-45
+#define FRAME_GRID_COLS 64
+
+namespace ORB_SLAM3 {
+
+struct ORBextractor {  // include/ORBextractor.h:83
+    std::vector<cv::Mat> mvImagePyramid;
+};
+
+class ORBmatcher {  // include/ORBmatcher.h:38-93
+public:
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
+    static const int TH_LOW;
+    static const int TH_HIGH;
+    static const int HISTO_LENGTH;
+};
+
+class Frame {  // include/Frame.h
+public:
+    void ComputeStereoMatches();
+    void AssignFeaturesToGrid();
+    vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1,
+                                     const int maxLevel = -1, const bool bRight = false) const;
+    bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
+
+    ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
+    float mbf = 0, mb = 0;
+    int N = 0;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
+    std::vector<float> mvuRight, mvDepth;
+    cv::Mat mDescriptors, mDescriptorsRight;
+    std::vector<float> mvScaleFactors, mvInvScaleFactors;
+    static float mfGridElementWidthInv, mfGridElementHeightInv;
+    std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+    static float mnMinX, mnMaxX, mnMinY, mnMaxY;
+    int Nleft = -1, Nright = -1;
+    std::vector<std::size_t> mGridRight[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+};
+
+}  // namespace ORB_SLAM3

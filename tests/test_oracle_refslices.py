@@ -1,0 +1,74 @@
+"""Pins oracle/match_oracle.cpp (the restatements the GPU parity tests compare against) to the reference's OWN function
+bodies: oracle/_ref/librefslices.so holds Frame::ComputeStereoMatches, AssignFeaturesToGrid, GetFeaturesInArea, PosInGrid
+and ORBmatcher::DescriptorDistance cut out of /root/reference/ORB_SLAM3/src/{Frame,ORBmatcher}.cc by oracle/Makefile and
+compiled unchanged (built where /root/reference exists; the prebuilt library travels to the GPU box)."""
+import numpy as np
+import pytest
+
+from orb_slam3_ros2_b200 import synth
+from test_oracle_matcher_rows import make_grid_case
+
+
+@pytest.fixture(scope="module")
+def slices(oracle):
+    if not oracle.have_refslices():
+        pytest.skip("oracle/_ref/librefslices.so not built (needs /root/reference at build time)")
+    return oracle
+
+
+def test_thresholds_and_descriptor_distance(slices):
+    from orb_slam3_ros2_b200 import orbx  # constants only; no compute call
+    assert slices.ref_thresholds() == (orbx.TH_LOW, orbx.TH_HIGH) == (50, 100)
+    rng = np.random.default_rng(1)
+    a = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    b[:20] = a[:20]
+    b[20:40] = ~a[20:40]
+    for i in range(300):
+        assert slices.ref_descriptor_distance(a[i], b[i]) == slices.hamming(a[i], b[i])
+    assert slices.ref_descriptor_distance(a[0], b[0]) == 0 and slices.ref_descriptor_distance(a[20], b[20]) == 256
+
+
+@pytest.mark.parametrize("w,h,nf,k", [(1241, 376, 2000, 0), (640, 360, 1000, 5), (752, 480, 1000, 2)])
+def test_compute_stereo_matches_restatement_equals_reference_body(slices, w, h, nf, k):
+    ol, orr = slices.PortExtractor(nfeatures=nf), slices.PortExtractor(nfeatures=nf)
+    _, kl, dl = ol.extract(synth.frame(k, w, h), (0, 0))
+    _, kr, dr = orr.extract(synth.frame(k, w, h, right=True), (0, 0))
+    t = ol.tables()
+    pl, pr = [ol.pyramid(l) for l in range(8)], [orr.pyramid(l) for l in range(8)]
+    bf, b = 386.1448, 0.53716  # config/Stereo/KITTI00-02.yaml
+    got = slices.compute_stereo_matches(kl, dl, kr, dr, t["scale"], t["inv_scale"], pl, pr, bf, b)
+    want = slices.ref_compute_stereo_matches(kl, dl, kr, dr, t["scale"], t["inv_scale"], pl, pr, bf, b)
+    assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32))  # mvuRight, bit for bit
+    assert np.array_equal(got[1].view(np.uint32), want[1].view(np.uint32))  # mvDepth
+    assert (want[0] >= 0).sum() > 200
+    # a different baseline changes maxD and the depth scale
+    got2 = slices.compute_stereo_matches(kl, dl, kr, dr, t["scale"], t["inv_scale"], pl, pr, 40.0, 0.8)
+    want2 = slices.ref_compute_stereo_matches(kl, dl, kr, dr, t["scale"], t["inv_scale"], pl, pr, 40.0, 0.8)
+    assert np.array_equal(got2[0].view(np.uint32), want2[0].view(np.uint32))
+    assert np.array_equal(got2[1].view(np.uint32), want2[1].view(np.uint32))
+
+
+@pytest.mark.parametrize("seed,nt,nq", [(0, 600, 200), (1, 3000, 500), (2, 50, 64), (3, 5000, 300)])
+def test_grid_search_restatement_equals_reference_bodies(slices, seed, nt, nq):
+    kps, desc, bounds, qs, dq, skip, ur = make_grid_case(seed, nt, nq)
+    got = slices.search_grid_top2(kps, desc, bounds, qs, dq)
+    want = slices.ref_grid_top2(kps, desc, bounds, qs, dq)
+    for g, w_ in zip(got[:4], want[:4]):
+        assert np.array_equal(g, w_)
+    assert want[4].max() > 5  # the windows really hold candidates
+
+
+def test_grid_search_on_extracted_frames_equals_reference_bodies(slices):
+    from test_oracle_matcher_rows import GQ
+    e = slices.PortExtractor(nfeatures=1000)
+    _, k0, d0 = e.extract(synth.frame(0, 752, 480), (0, 1000))
+    _, k1, d1 = e.extract(synth.frame(1, 752, 480), (0, 1000))
+    qs = np.zeros(len(k0), dtype=GQ)
+    qs["u"], qs["v"], qs["r"] = k0["x"], k0["y"], 100.0   # SearchForInitialization's window (ORBmatcher.cc:665)
+    qs["min_level"] = qs["max_level"] = k0["octave"]
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    got = slices.search_grid_top2(k1, d1, bounds, qs, d0)
+    want = slices.ref_grid_top2(k1, d1, bounds, qs, d0)
+    for g, w_ in zip(got[:4], want[:4]):
+        assert np.array_equal(g, w_)
