@@ -239,4 +239,98 @@ void orbo_compute_stereo_matches(const void* kpsL_, const uint8_t* descL, int N,
     }
 }
 
+
+// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (ORBmatcher.cc:223-425) for a monocular keyframe / frame
+// (F.Nleft == -1, mpCamera2 == NULL): features are only compared inside the same vocabulary node (the two FeatureVectors,
+// walked in ascending node id, :243-246, :388-400); keyframe features are visited in their node's order, frame features that
+// already received a MapPoint are skipped (:279), strict-< best / second (:287-296), accept best1 <= TH_LOW and
+// (float)best1 < mfNNratio * (float)best2 (:323-327), then the rotation histogram with factor 1/HISTO_LENGTH (:234, :345-352)
+// and ComputeThreeMaxima (:2012-2053) remove the matches outside the three dominant bins (:403-420).
+// valid_kf: 0 = no MapPoint, 1 = good MapPoint, 2 = MapPoint isBad().  match_f[j] = keyframe feature index or -1.
+// Pinned by oracle/_ref/librefslices.so (the reference's own body), tests/test_oracle_refslices.py.
+int orbo_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
+                       const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
+                       const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
+                       int f_nodes, float mfNNratio, int mbCheckOrientation, int32_t* match_f) {
+    const int TH_LOW = 50, HISTO_LENGTH = 30;
+    (void)n_kf;
+    for (int j = 0; j < n_f; ++j) match_f[j] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[30];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int a = 0, b = 0;
+    while (a < kf_nodes && b < f_nodes) {
+        if (kf_node_ids[a] == f_node_ids[b]) {
+            for (int iKF = kf_node_begin[a]; iKF < kf_node_begin[a + 1]; iKF++) {
+                const int realIdxKF = kf_feat_idx[iKF];
+                if (valid_kf[realIdxKF] != 1) continue;  // !pMP, or pMP->isBad()
+                const uint8_t* dKF = desc_kf + (size_t)realIdxKF * 32;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                for (int iF = f_node_begin[b]; iF < f_node_begin[b + 1]; iF++) {
+                    const int realIdxF = f_feat_idx[iF];
+                    if (match_f[realIdxF] >= 0) continue;
+                    const int dist = orbo_hamming(dKF, desc_f + (size_t)realIdxF * 32);
+                    if (dist < bestDist1) {
+                        bestDist2 = bestDist1;
+                        bestDist1 = dist;
+                        bestIdxF = realIdxF;
+                    } else if (dist < bestDist2) {
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        match_f[bestIdxF] = realIdxKF;
+                        if (mbCheckOrientation) {
+                            float rot = angle_kf[realIdxKF] - angle_f[bestIdxF];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            a++;
+            b++;
+        } else if (kf_node_ids[a] < f_node_ids[b]) {
+            while (a < kf_nodes && kf_node_ids[a] < f_node_ids[b]) a++;  // lower_bound
+        } else {
+            while (b < f_nodes && f_node_ids[b] < kf_node_ids[a]) b++;
+        }
+    }
+    if (mbCheckOrientation) {
+        // ComputeThreeMaxima (ORBmatcher.cc:2012-2053)
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) {
+                max3 = max2; max2 = max1; max1 = s;
+                ind3 = ind2; ind2 = ind1; ind1 = i;
+            } else if (s > max2) {
+                max3 = max2; max2 = s;
+                ind3 = ind2; ind2 = i;
+            } else if (s > max3) {
+                max3 = s;
+                ind3 = i;
+            }
+        }
+        if (max2 < 0.1f * (float)max1) {
+            ind2 = -1;
+            ind3 = -1;
+        } else if (max3 < 0.1f * (float)max1) {
+            ind3 = -1;
+        }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                match_f[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 }  // extern "C"

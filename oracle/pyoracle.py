@@ -566,3 +566,31 @@ def ref_grid_top2(kps_t, desc_t, bounds, queries, desc_q):
     _slices().refslice_grid_top2(kps_t.ctypes.data_as(C.c_void_p), _ptr(desc_t), len(kps_t), *[float(b) for b in bounds],
                                  q20.ctypes.data, _ptr(desc_q), nq, *[_ptr(o, _i32p) for o in out])
     return [o[:nq] for o in out]
+
+
+def _search_by_bow(fn, desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio, check_orientation):
+    desc_kf = np.ascontiguousarray(desc_kf, np.uint8).reshape(-1, 32); desc_f = np.ascontiguousarray(desc_f, np.uint8).reshape(-1, 32)
+    valid_kf = np.ascontiguousarray(valid_kf, np.uint8)
+    angle_kf = np.ascontiguousarray(angle_kf, np.float32); angle_f = np.ascontiguousarray(angle_f, np.float32)
+    arrs = []
+    for fv in (fv_kf, fv_f):
+        arrs.append([np.ascontiguousarray(fv[k], np.int32) for k in ("node_ids", "node_begin", "feat_idx")])
+    out = np.full(max(len(desc_f), 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _f32p, _i32p, _i32p, _i32p, C.c_int,
+                   C.c_float, C.c_int, _i32p]
+    n = fn(_ptr(desc_kf), len(desc_kf), _ptr(valid_kf), _ptr(angle_kf, _f32p), *[_ptr(a, _i32p) for a in arrs[0]], len(arrs[0][0]),
+           _ptr(desc_f), len(desc_f), _ptr(angle_f, _f32p), *[_ptr(a, _i32p) for a in arrs[1]], len(arrs[1][0]),
+           float(nnratio), int(bool(check_orientation)), _ptr(out, _i32p))
+    return n, out[:len(desc_f)]
+
+
+def search_by_bow(desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio=0.7, check_orientation=True):
+    """ORBmatcher::SearchByBoW(KF, F) restatement (oracle/match_oracle.cpp) -> (nmatches, match_f).  fv_*: dicts with the
+    FeatureVector CSR arrays of a BoW transform (node_ids, node_begin, feat_idx)."""
+    return _search_by_bow(port_lib().orbo_search_by_bow, desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio, check_orientation)
+
+
+def ref_search_by_bow(desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio=0.7, check_orientation=True):
+    """The same through the reference's own function body (ORBmatcher.cc:223-425, oracle/_ref/librefslices.so)."""
+    return _search_by_bow(_slices().refslice_search_by_bow, desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio, check_orientation)

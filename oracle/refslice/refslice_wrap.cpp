@@ -5,6 +5,8 @@
 // shim.h, behind an extern "C" façade:
 //   ORBmatcher.cc:35-37      TH_HIGH / TH_LOW / HISTO_LENGTH
 //   ORBmatcher.cc:2058-2074  ORBmatcher::DescriptorDistance
+//   ORBmatcher.cc:223-425    ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)
+//   ORBmatcher.cc:2012-2053  ORBmatcher::ComputeThreeMaxima
 //   Frame.cc:385-416         Frame::AssignFeaturesToGrid
 //   Frame.cc:657-723         Frame::GetFeaturesInArea
 //   Frame.cc:725-735         Frame::PosInGrid
@@ -23,6 +25,8 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 #include "Frame_GetFeaturesInArea.inc"
 #include "Frame_PosInGrid.inc"
 #include "Frame_ComputeStereoMatches.inc"
+#include "ORBmatcher_SearchByBoW.inc"
+#include "ORBmatcher_ComputeThreeMaxima.inc"
 }  // namespace ORB_SLAM3
 
 using ORB_SLAM3::Frame;
@@ -113,6 +117,41 @@ void refslice_grid_top2(const void* kps_t, const uint8_t* desc_t, int nt, float 
         idx1[q] = bi; d1[q] = best; idx2[q] = bi2; d2[q] = best2;
         if (cand_count) cand_count[q] = (int32_t)cand.size();
     }
+}
+
+// ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches) for a monocular keyframe / frame (Nleft == -1, mpCamera2 == NULL).
+// valid_kf[i] != 0: keyframe feature i has a (good) MapPoint; 2 = its MapPoint isBad().  The two FeatureVectors arrive as
+// the CSR arrays of the BoW transform.  match_f[j] = keyframe feature whose MapPoint was given to frame feature j, or -1.
+int refslice_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
+                           const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
+                           const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
+                           int f_nodes, float nnratio, int check_orientation, int32_t* match_f) {
+    ORB_SLAM3::KeyFrame KF;
+    Frame F;
+    std::vector<ORB_SLAM3::MapPoint> points(n_kf);
+    KF.mvpMapPoints.assign(n_kf, nullptr);
+    KF.mvKeysUn.resize(n_kf);
+    for (int i = 0; i < n_kf; ++i) {
+        points[i].index = i;
+        points[i].mbBad = valid_kf[i] == 2;
+        if (valid_kf[i]) KF.mvpMapPoints[i] = &points[i];
+        KF.mvKeysUn[i].angle = angle_kf[i];
+    }
+    KF.mDescriptors = descriptors(desc_kf, n_kf);
+    for (int j = 0; j < kf_nodes; ++j)
+        for (int p = kf_node_begin[j]; p < kf_node_begin[j + 1]; ++p) KF.mFeatVec.addFeature((DBoW2::NodeId)kf_node_ids[j], (unsigned)kf_feat_idx[p]);
+    F.N = n_f;
+    F.Nleft = -1;
+    F.mvKeys.resize(n_f);
+    for (int i = 0; i < n_f; ++i) F.mvKeys[i].angle = angle_f[i];
+    F.mDescriptors = descriptors(desc_f, n_f);
+    for (int j = 0; j < f_nodes; ++j)
+        for (int p = f_node_begin[j]; p < f_node_begin[j + 1]; ++p) F.mFeatVec.addFeature((DBoW2::NodeId)f_node_ids[j], (unsigned)f_feat_idx[p]);
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    std::vector<ORB_SLAM3::MapPoint*> out;
+    const int n = matcher.SearchByBoW(&KF, F, out);
+    for (int j = 0; j < n_f; ++j) match_f[j] = out[j] ? out[j]->index : -1;
+    return n;
 }
 
 }  // extern "C"

@@ -16,6 +16,8 @@
 
 #include <opencv2/core/core.hpp>
 
+#include "DBoW2/FeatureVector.h"  // the reference's own (Thirdparty/DBoW2), on the boost::serialization stub of minicv
+
 using namespace std;  // the reference's headers do this (ORBmatcher.cc:30, and Frame.cc relies on it through its includes)
 
 #define FRAME_GRID_ROWS 48  // include/Frame.h:44-45
@@ -27,12 +29,38 @@ struct ORBextractor {  // include/ORBextractor.h:83
     std::vector<cv::Mat> mvImagePyramid;
 };
 
-class ORBmatcher {  // include/ORBmatcher.h:38-93
+class GeometricCamera;
+class Frame;
+
+class MapPoint {  // include/MapPoint.h: only isBad() is used on this path
 public:
+    bool isBad() { return mbBad; }
+    bool mbBad = false;
+    int index = -1;  // (shim) the keyframe feature this map point was created for
+};
+
+class KeyFrame {  // include/KeyFrame.h
+public:
+    std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+    DBoW2::FeatureVector mFeatVec;
+    cv::Mat mDescriptors;
+    GeometricCamera* mpCamera2 = nullptr;
+    std::vector<cv::KeyPoint> mvKeysUn, mvKeys, mvKeysRight;
+    int NLeft = -1;
+    std::vector<MapPoint*> mvpMapPoints;
+};
+
+class ORBmatcher {  // include/ORBmatcher.h:38-103
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
+    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
     static const int TH_LOW;
     static const int TH_HIGH;
     static const int HISTO_LENGTH;
+    void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
+    float mfNNratio;
+    bool mbCheckOrientation;
 };
 
 class Frame {  // include/Frame.h
@@ -55,6 +83,8 @@ public:
     static float mnMinX, mnMaxX, mnMinY, mnMaxY;
     int Nleft = -1, Nright = -1;
     std::vector<std::size_t> mGridRight[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+    DBoW2::FeatureVector mFeatVec;
+    GeometricCamera* mpCamera2 = nullptr;
 };
 
 }  // namespace ORB_SLAM3

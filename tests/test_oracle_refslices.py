@@ -72,3 +72,32 @@ def test_grid_search_on_extracted_frames_equals_reference_bodies(slices):
     want = slices.ref_grid_top2(k1, d1, bounds, qs, d0)
     for g, w_ in zip(got[:4], want[:4]):
         assert np.array_equal(g, w_)
+
+
+def bow_pair_case(oracle, seed=0, n=1000, levelsup=2):
+    """A keyframe / frame pair for SearchByBoW: two overlapping descriptor sets through the synthetic vocabulary."""
+    k, L, _, parent, node_desc, weight, _ = synth.bow_case("k10L4_levelsup2")
+    rng = np.random.default_rng(seed)
+    d_kf = synth.descriptors_near_words(parent, node_desc, n, seed=20 + seed)
+    d_f = d_kf[rng.permutation(n)[: n - 100]].copy()
+    flips = rng.integers(0, 256, (len(d_f), 6))
+    for i in range(len(d_f)):
+        for bpos in flips[i]:
+            d_f[i, bpos >> 3] ^= np.uint8(1 << (bpos & 7))
+    d_f[:30] = d_f[30:60]                      # duplicates: distance ties inside a node, already-matched skips
+    a_kf = rng.uniform(0, 360, n).astype(np.float32)
+    a_f = ((a_kf[rng.integers(0, n, len(d_f))] + rng.choice([0.0, 0.0, 0.0, 45.0, 200.0], len(d_f))) % 360).astype(np.float32)
+    valid = rng.choice([0, 1, 1, 1, 2], n).astype(np.uint8)
+    fv_kf = oracle.bow_transform(parent, node_desc, weight, L, d_kf, levelsup)
+    fv_f = oracle.bow_transform(parent, node_desc, weight, L, d_f, levelsup)
+    return d_kf, valid, a_kf, fv_kf, d_f, a_f, fv_f
+
+
+@pytest.mark.parametrize("seed,levelsup,nnratio,ori", [(0, 2, 0.7, True), (1, 2, 0.9, True), (2, 3, 0.7, False), (3, 1, 0.6, True),
+                                                      (4, 4, 0.75, True)])
+def test_search_by_bow_restatement_equals_reference_body(slices, seed, levelsup, nnratio, ori):
+    case = bow_pair_case(slices, seed, 1000, levelsup)
+    n_ref, m_ref = slices.ref_search_by_bow(*case, nnratio=nnratio, check_orientation=ori)
+    n_got, m_got = slices.search_by_bow(*case, nnratio=nnratio, check_orientation=ori)
+    assert n_got == n_ref and np.array_equal(m_got, m_ref)
+    assert n_ref == int((m_ref >= 0).sum()) and n_ref > 50
