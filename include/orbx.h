@@ -265,6 +265,21 @@ int orbx_bow_transform_extracted(orbx_voc v, orbx_handle h, int levelsup, int32_
                                  int32_t* n_words, int32_t* node_ids, int32_t* node_begin, int32_t* feat_idx,
                                  int32_t* n_nodes);
 
+/* ---- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)  (src/ORBmatcher.cc:223-425), monocular case ------
+ * The consumer of the FeatureVectors: keyframe features are matched to frame features of the SAME vocabulary node only.
+ * Inputs are the two descriptor sets, the two FeatureVectors in the CSR form orbx_bow_transform returns them in, the
+ * keypoint angles (kp.angle of pKF->mvKeysUn / F.mvKeys) and valid_kf[i]: 1 = keyframe feature i has a good MapPoint,
+ * 0 = none, 2 = MapPoint::isBad().  Reproduced: node-by-node walk in ascending node id, keyframe features in node order,
+ * frame features that already received a MapPoint are skipped (:279), strict-< best / second, accept
+ * best1 <= TH_LOW && (float)best1 < nnratio * (float)best2 (:323-327), rotation histogram + ComputeThreeMaxima
+ * (:345-352, :403-420, :2012-2053) when check_orientation != 0.
+ * match_f[j] = index of the keyframe feature whose MapPoint goes to frame feature j (vpMapPointMatches[j] =
+ * vpMapPointsKF[match_f[j]]), or -1; *n_matches = the function's return value.  n_f < 65536. */
+int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
+                       const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
+                       const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
+                       int f_nodes, float nnratio, int check_orientation, int32_t* match_f, int32_t* n_matches, int device);
+
 /* Measured sustained 32-bit POPC rate of the device in giga-POPC/s (8 independent XOR+POPC chains per thread):
  * the denominator of the matcher's roofline, pairs/s = POPC/s / 8. */
 int orbx_bench_popc(int device, double* gpopc_per_s);

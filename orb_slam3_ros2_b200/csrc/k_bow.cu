@@ -195,7 +195,133 @@ __global__ void __launch_bounds__(512) bowCollectKernel(const BowVocDev V, const
     }
 }
 
+
+// ---- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)  (ORB_SLAM3/src/ORBmatcher.cc:223-425), monocular ----------
+// Features are only compared inside the same vocabulary node.  A frame feature belongs to exactly one node, so the
+// reference's sequential bookkeeping (a frame feature that already received a MapPoint is skipped, :279) never crosses
+// nodes: ONE WARP PER KEYFRAME NODE finds its partner in the frame's FeatureVector (binary search in the ascending node ids),
+// then walks the node's keyframe features in order; the lanes take the node's frame features 32 at a time, keys
+// distance << 16 | position reproduce the strict-< best / second updates (:287-296), lane 0 applies the accept rule
+// (:323-327) and records the match and its rotation bin (:345-352).
+struct BowSearchArgs {
+    const uint4* descKF; const uint8_t* validKF; const float* angleKF;
+    const int* kfNodeIds; const int* kfNodeBegin; const int* kfFeatIdx; int kfNodes;
+    const uint4* descF; const float* angleF;
+    const int* fNodeIds; const int* fNodeBegin; const int* fFeatIdx; int fNodes;
+    float nnratio; int checkOrientation;
+    int* matchF; int* binF;
+};
+
+__global__ void __launch_bounds__(256) bowSearchKernel(const BowSearchArgs A) {
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (a >= A.kfNodes) return;
+    const int node = A.kfNodeIds[a];
+    int lo = 0, hi = A.fNodes;  // lower_bound of the keyframe's node id in the frame's ascending node ids
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (A.fNodeIds[mid] < node) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= A.fNodes || A.fNodeIds[lo] != node) return;
+    const int fbeg = A.fNodeBegin[lo], fend = A.fNodeBegin[lo + 1];
+    volatile int* matchF = A.matchF;
+    constexpr unsigned kNone = (256u << 16) | 0xffffu;  // bestDist = 256, no index
+    for (int iKF = A.kfNodeBegin[a]; iKF < A.kfNodeBegin[a + 1]; ++iKF) {
+        const int realKF = A.kfFeatIdx[iKF];
+        if (A.validKF[realKF] != 1) continue;  // no MapPoint, or a bad one (:255-259)
+        const uint4 q0 = A.descKF[2 * realKF], q1 = A.descKF[2 * realKF + 1];
+        unsigned k1 = kNone, k2 = kNone;
+        for (int iF = fbeg + lane; iF < fend; iF += 32) {
+            const int realF = A.fFeatIdx[iF];
+            if (matchF[realF] >= 0) continue;  // vpMapPointMatches[realIdxF] already set (:279)
+            const uint4 b0 = A.descF[2 * realF], b1 = A.descF[2 * realF + 1];
+            const int d = __popc(q0.x ^ b0.x) + __popc(q0.y ^ b0.y) + __popc(q0.z ^ b0.z) + __popc(q0.w ^ b0.w) +
+                          __popc(q1.x ^ b1.x) + __popc(q1.y ^ b1.y) + __popc(q1.z ^ b1.z) + __popc(q1.w ^ b1.w);
+            const unsigned key = ((unsigned)d << 16) | (unsigned)(iF - fbeg);
+            k2 = min(k2, max(k1, key));
+            k1 = min(k1, key);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+            k2 = min(max(k1, o1), min(k2, o2));
+            k1 = min(k1, o1);
+        }
+        const int best1 = (int)(k1 >> 16), best2 = (int)(k2 >> 16);
+        if (best1 <= 50 && (float)best1 < __fmul_rn(A.nnratio, (float)best2)) {  // TH_LOW, mfNNratio (:323-325)
+            if (lane == 0) {
+                const int bestF = A.fFeatIdx[fbeg + (int)(k1 & 0xffffu)];
+                matchF[bestF] = realKF;
+                if (A.checkOrientation) {
+                    float rot = __fsub_rn(A.angleKF[realKF], A.angleF[bestF]);
+                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                    int bin = (int)roundf(__fmul_rn(rot, 1.0f / 30));  // factor = 1.0f / HISTO_LENGTH (:234)
+                    if (bin == 30) bin = 0;
+                    A.binF[bestF] = bin;
+                }
+            }
+        }
+        __syncwarp();  // the match is visible to the warp's next keyframe feature
+    }
+}
+
+// Rotation consistency (:403-420) and the final count: one CTA.  ComputeThreeMaxima (:2012-2053) only needs the bin sizes.
+__global__ void __launch_bounds__(256) bowOrientationKernel(int* __restrict__ matchF, const int* __restrict__ binF, int nF,
+                                                            int checkOrientation, int* __restrict__ nMatches) {
+    __shared__ int hist[30];
+    __shared__ int keep[3];
+    __shared__ int count;
+    if (threadIdx.x < 30) hist[threadIdx.x] = 0;
+    if (threadIdx.x == 0) count = 0;
+    __syncthreads();
+    if (checkOrientation) {
+        for (int j = threadIdx.x; j < nF; j += blockDim.x)
+            if (matchF[j] >= 0) atomicAdd(&hist[binF[j]], 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+            for (int i = 0; i < 30; i++) {
+                const int s = hist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+                else if (s > max3) { max3 = s; ind3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+            keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+        }
+        __syncthreads();
+    }
+    int local = 0;
+    for (int j = threadIdx.x; j < nF; j += blockDim.x) {
+        if (matchF[j] < 0) continue;
+        if (checkOrientation) {
+            const int b = binF[j];
+            if (b != keep[0] && b != keep[1] && b != keep[2]) { matchF[j] = -1; continue; }
+        }
+        ++local;
+    }
+    if (local) atomicAdd(&count, local);
+    __syncthreads();
+    if (threadIdx.x == 0) *nMatches = count;
+}
+
 }  // namespace
+
+void launchBowSearch(const uint8_t* descKF, const uint8_t* validKF, const float* angleKF, const int* kfNodeIds, const int* kfNodeBegin,
+                     const int* kfFeatIdx, int kfNodes, const uint8_t* descF, int nF, const float* angleF, const int* fNodeIds,
+                     const int* fNodeBegin, const int* fFeatIdx, int fNodes, float nnratio, int checkOrientation, int* matchF, int* binF,
+                     int* nMatches, cudaStream_t s) {
+    cudaMemsetAsync(matchF, 0xff, (size_t)std::max(nF, 1) * 4, s);
+    if (kfNodes > 0 && fNodes > 0 && nF > 0) {
+        const BowSearchArgs A{reinterpret_cast<const uint4*>(descKF), validKF, angleKF, kfNodeIds, kfNodeBegin, kfFeatIdx, kfNodes,
+                              reinterpret_cast<const uint4*>(descF), angleF, fNodeIds, fNodeBegin, fFeatIdx, fNodes, nnratio,
+                              checkOrientation, matchF, binF};
+        bowSearchKernel<<<(kfNodes * 32 + 255) / 256, 256, 0, s>>>(A);
+        countLaunch();
+    }
+    bowOrientationKernel<<<1, 256, 0, s>>>(matchF, binF, nF, checkOrientation, nMatches);
+    countLaunch();
+}
 
 int bowSortCapacity() { return 16384; }
 

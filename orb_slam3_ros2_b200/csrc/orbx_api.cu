@@ -1346,6 +1346,60 @@ int orbx_bow_transform_extracted(orbx_voc v, orbx_handle h, int levelsup, int32_
                   node_begin, feat_idx, n_nodes);
 }
 
+int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
+                       const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
+                       const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
+                       int f_nodes, float nnratio, int check_orientation, int32_t* match_f, int32_t* n_matches, int device) {
+    if (n_kf < 0 || n_f < 0 || kf_nodes < 0 || f_nodes < 0 || !match_f || !n_matches) return fail(ORBX_ERR_ARG, "bad argument");
+    if (n_f >= 65536) return fail(ORBX_ERR_ARG, "more than 65535 frame features");
+    if ((n_kf > 0 && (!desc_kf || !valid_kf || !angle_kf)) || (n_f > 0 && (!desc_f || !angle_f)) ||
+        (kf_nodes > 0 && (!kf_node_ids || !kf_node_begin || !kf_feat_idx)) || (f_nodes > 0 && (!f_node_ids || !f_node_begin || !f_feat_idx)))
+        return fail(ORBX_ERR_ARG, "null input");
+    const int kfEntries = kf_nodes ? kf_node_begin[kf_nodes] : 0, fEntries = f_nodes ? f_node_begin[f_nodes] : 0;
+    if (kfEntries < 0 || kfEntries > n_kf || fEntries < 0 || fEntries > n_f) return fail(ORBX_ERR_ARG, "FeatureVector does not fit the descriptor sets");
+    for (int p = 0; p < kfEntries; ++p)
+        if (kf_feat_idx[p] < 0 || kf_feat_idx[p] >= n_kf) return fail(ORBX_ERR_ARG, "keyframe feature index out of range");
+    for (int p = 0; p < fEntries; ++p)
+        if (f_feat_idx[p] < 0 || f_feat_idx[p] >= n_f) return fail(ORBX_ERR_ARG, "frame feature index out of range");
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    // one upload buffer: [descKF | descF | angleKF | angleF | kf ids, begin, idx | f ids, begin, idx | validKF], then [matchF | binF | n]
+    const size_t K = (size_t)std::max(n_kf, 1), Fn = (size_t)std::max(n_f, 1), KN = (size_t)kf_nodes, FN = (size_t)f_nodes;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { const size_t at = o; o += (bytes + 15) & ~(size_t)15; return at; };
+    const size_t oDK = take(K * 32), oDF = take(Fn * 32), oAK = take(K * 4), oAF = take(Fn * 4), oKI = take(KN * 4 + 4), oKB = take(KN * 4 + 4),
+                 oKX = take(K * 4), oFI = take(FN * 4 + 4), oFB = take(FN * 4 + 4), oFX = take(Fn * 4), oV = take(K);
+    ORBX_CUDA(S->db.reserve(o + 64));
+    ORBX_CUDA(S->misc.reserve(Fn * 8 + 64));
+    uint8_t* D = (uint8_t*)S->db.p;
+    int* matchF = (int*)S->misc.p;
+    int* binF = matchF + Fn;
+    int* nM = binF + Fn;
+    cudaStream_t s = S->stream;
+    auto up = [&](size_t at, const void* src, size_t bytes) {
+        return bytes ? cudaMemcpyAsync(D + at, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
+    };
+    ORBX_CUDA(up(oDK, desc_kf, (size_t)n_kf * 32)); ORBX_CUDA(up(oDF, desc_f, (size_t)n_f * 32));
+    ORBX_CUDA(up(oAK, angle_kf, (size_t)n_kf * 4)); ORBX_CUDA(up(oAF, angle_f, (size_t)n_f * 4));
+    ORBX_CUDA(up(oKI, kf_node_ids, KN * 4)); ORBX_CUDA(up(oKB, kf_node_begin, kf_nodes ? (KN + 1) * 4 : 0)); ORBX_CUDA(up(oKX, kf_feat_idx, (size_t)kfEntries * 4));
+    ORBX_CUDA(up(oFI, f_node_ids, FN * 4)); ORBX_CUDA(up(oFB, f_node_begin, f_nodes ? (FN + 1) * 4 : 0)); ORBX_CUDA(up(oFX, f_feat_idx, (size_t)fEntries * 4));
+    ORBX_CUDA(up(oV, valid_kf, (size_t)n_kf));
+    launchBowSearch(D + oDK, D + oV, (const float*)(D + oAK), (const int*)(D + oKI), (const int*)(D + oKB), (const int*)(D + oKX), kf_nodes,
+                    D + oDF, n_f, (const float*)(D + oAF), (const int*)(D + oFI), (const int*)(D + oFB), (const int*)(D + oFX), f_nodes, nnratio,
+                    check_orientation != 0, matchF, binF, nM, s);
+    ORBX_CUDA(cudaGetLastError());
+    if (n_f) ORBX_CUDA(cudaMemcpyAsync(match_f, matchF, (size_t)n_f * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(n_matches, nM, 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_bench_popc(int device, double* gpopc_per_s) {
     if (!gpopc_per_s) return fail(ORBX_ERR_ARG, "null argument");
     int ndev = 0;

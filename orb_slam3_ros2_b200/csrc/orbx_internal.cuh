@@ -156,6 +156,10 @@ int bowSortCapacity();
 void launchBowTransform(const BowVocDev& V, const uint8_t* dDesc, const int* dN, int cap, int F, int levelsup, int* leaf,
                         int* nid, int32_t* wordIds, double* wordVals, int32_t* nWords, int32_t* nodeIds, int32_t* nodeBegin,
                         int32_t* featIdx, int32_t* nNodes, cudaStream_t s);
+void launchBowSearch(const uint8_t* descKF, const uint8_t* validKF, const float* angleKF, const int* kfNodeIds, const int* kfNodeBegin,
+                     const int* kfFeatIdx, int kfNodes, const uint8_t* descF, int nF, const float* angleF, const int* fNodeIds,
+                     const int* fNodeBegin, const int* fFeatIdx, int fNodes, float nnratio, int checkOrientation, int* matchF, int* binF,
+                     int* nMatches, cudaStream_t s);
 void uploadDescribeTables();
 double benchPopcRate(cudaStream_t s);
 

@@ -86,6 +86,8 @@ SYMBOLS = {
     "orbx_compute_stereo_matches": (C.c_int, [_vp, _vp, C.c_int, _vp, _u8p, C.c_int, _vp, _u8p, C.c_int, C.c_float, C.c_float,
                                               _f32p, _f32p]),
     "orbx_compute_stereo_matches_batch": (C.c_int, [_vp, _vp, C.c_float, C.c_float, _f32p, _f32p]),
+    "orbx_search_by_bow": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _f32p, _i32p, _i32p, _i32p,
+                                     C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_voc_create": (C.c_int, [C.c_int, _i32p, _u8p, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(_vp)]),
     "orbx_voc_destroy": (None, [_vp]),
@@ -518,6 +520,24 @@ class ORBVocabulary:
 
     def outputs_for(self, extractor):
         return self._outputs(extractor._frames, extractor.results_device()[4])
+
+
+def search_by_bow(desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio=0.7, check_orientation=True, device=-1):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (ORBmatcher.cc:223-425, monocular) -> (nmatches, match_f): match_f[j] =
+    keyframe feature whose MapPoint goes to frame feature j, or -1.  fv_kf / fv_f: FeatureVector dicts of ORBVocabulary.transform."""
+    desc_kf = np.ascontiguousarray(desc_kf, np.uint8).reshape(-1, 32)
+    desc_f = np.ascontiguousarray(desc_f, np.uint8).reshape(-1, 32)
+    valid_kf = np.ascontiguousarray(valid_kf, np.uint8)
+    angle_kf = np.ascontiguousarray(angle_kf, np.float32)
+    angle_f = np.ascontiguousarray(angle_f, np.float32)
+    a = [np.ascontiguousarray(fv_kf[k], np.int32) for k in ("node_ids", "node_begin", "feat_idx")]
+    b = [np.ascontiguousarray(fv_f[k], np.int32) for k in ("node_ids", "node_begin", "feat_idx")]
+    out = np.full(max(len(desc_f), 1), -1, np.int32)
+    n = np.zeros(1, np.int32)
+    _check(lib().orbx_search_by_bow(_ptr(desc_kf), len(desc_kf), _ptr(valid_kf), _ptr(angle_kf, _f32p), *[_ptr(x, _i32p) for x in a],
+                                    len(a[0]), _ptr(desc_f), len(desc_f), _ptr(angle_f, _f32p), *[_ptr(x, _i32p) for x in b], len(b[0]),
+                                    float(nnratio), int(bool(check_orientation)), _ptr(out, _i32p), _ptr(n, _i32p), device))
+    return int(n[0]), out[:len(desc_f)]
 
 
 class ShardedMatcher:

@@ -77,3 +77,34 @@ def test_transform_on_device_resident_descriptors_of_an_extraction(orbx, oracle)
 def test_bad_arguments(orbx):
     with pytest.raises(orbx.OrbxError):
         orbx.ORBVocabulary(np.array([-1, 0, 3, 1], np.int32), np.zeros((4, 32), np.uint8), np.ones(4), 2)
+
+
+@pytest.mark.parametrize("seed,levelsup,nnratio,ori", [(0, 2, 0.7, True), (1, 2, 0.9, True), (2, 3, 0.7, False), (3, 1, 0.6, True),
+                                                      (4, 4, 0.75, True)])
+def test_search_by_bow_matches_oracle(orbx, oracle, seed, levelsup, nnratio, ori):
+    """ORBmatcher::SearchByBoW(KF, F): the oracle is pinned to the reference's own body in tests/test_oracle_refslices.py."""
+    from test_oracle_refslices import bow_pair_case
+    case = bow_pair_case(oracle, seed, 1000, levelsup)
+    n_want, m_want = oracle.search_by_bow(*case, nnratio=nnratio, check_orientation=ori)
+    n_got, m_got = orbx.search_by_bow(*case, nnratio=nnratio, check_orientation=ori)
+    assert n_got == n_want and np.array_equal(m_got, m_want)
+    if oracle.have_refslices():
+        n_ref, m_ref = oracle.ref_search_by_bow(*case, nnratio=nnratio, check_orientation=ori)
+        assert n_got == n_ref and np.array_equal(m_got, m_ref)
+
+
+def test_search_by_bow_chain_on_extracted_frames(orbx, oracle):
+    """extract -> ComputeBoW (device-resident descriptors) -> SearchByBoW between consecutive frames, all on the device path."""
+    k, L, levelsup, parent, node_desc, weight, _ = synth.bow_case("k10L4_levelsup2")
+    voc = orbx.ORBVocabulary(parent, node_desc, weight, L)
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    ex.extract_batch(synth.frames(0, 2, 752, 480), (0, 1000), download=False)
+    fv = voc.transform_extracted(ex, levelsup)
+    (_, k0, d0), (_, k1, d1) = ex.download(0), ex.download(1)
+    valid = np.ones(len(k0), np.uint8)
+    got = orbx.search_by_bow(d0, valid, k0["angle"], fv[0], d1, k1["angle"], fv[1], 0.7, True)
+    want = oracle.search_by_bow(d0, valid, k0["angle"], fv[0], d1, k1["angle"], fv[1], 0.7, True)
+    assert got[0] == want[0] and np.array_equal(got[1], want[1])
+    # empty keyframe side / nothing valid
+    n0, m0 = orbx.search_by_bow(d0, np.zeros(len(k0), np.uint8), k0["angle"], fv[0], d1, k1["angle"], fv[1])
+    assert n0 == 0 and (m0 == -1).all()
