@@ -350,6 +350,8 @@ def run_e2e(ctx, args, world):
     for g in range(depth):
         hs = [ctx["ex"] if (g == 0 and i == 0) else orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=ctx["dev"].index)
               for i in range(len(parts))]
+        for hnd in hs:
+            hnd.set_subbatches(args.subbatches)
         bs = []
         for lo, cnt in parts:
             bs.append(dict(kps=torch.empty((cnt, cap, 7), dtype=torch.float32).pin_memory(),

@@ -13,7 +13,10 @@
 // the horizontal pass turns each of them into one row of 16-bit (a0*p0 + a1*p1) >> 4 values for the tile's 128
 // columns (a thread keeps the coefficients of its 4 columns in registers), and the vertical pass blends two such
 // rows per output row.  ~18 instructions per output pixel instead of ~80 for the direct per-pixel form.
+#include <cstring>
+
 #include "orbx_internal.cuh"
+#include "tma.cuh"
 
 namespace orbx {
 namespace {
@@ -99,14 +102,26 @@ __global__ void __launch_bounds__(256) pyrLevel0AlignedKernel(const uint8_t* __r
 // SPT = bytes per staged source row (compile-time so that the row loops unroll into immediate offsets).
 constexpr int kRowTiles = 4;
 
-template <int SPT, bool WINDOWED>
+// TMA = true: the source rows of a tile are staged by ONE cp.async.bulk.tensor.3d (box SPT x maxRows x 1 of the source
+// level's tensor map, first byte at the 16-byte aligned plane column A0; what the box holds beyond the nS rows / nC16 chunks
+// the tile needs is never read, rows and columns past the plane arrive as zeros).
+template <int SPT, bool WINDOWED, bool TMA>
 __global__ void __launch_bounds__(256)
     pyrResizeKernel(uint8_t* __restrict__ pyr, unsigned frameBytes, unsigned srcOff, int sw, int sh, int spitch,
                     unsigned dstOff, int dw, int dh, int dpitch, const short4* __restrict__ tabX,
-                    const short4* __restrict__ tabY, int maxRows) {
-    extern __shared__ __align__(16) uint8_t smem[];
+                    const short4* __restrict__ tabY, int maxRows, const __grid_constant__ CUtensorMap srcMap, int frame0) {
+    extern __shared__ __align__(128) uint8_t smem[];
     __shared__ int4 sRow[kTH];  // per tile row: first / second source row (relative to S0), b0 << 16, b1 << 16
     __shared__ int sS0, sNS;
+    __shared__ __align__(8) uint64_t bar;
+    uint32_t barPhase = 0;
+    if (TMA) {
+        if (threadIdx.x == 0) {
+            mbarInit(&bar, 1);
+            mbarInitFence();
+        }
+        // made visible to the other threads by the first __syncthreads of the tile loop
+    }
     uint8_t* sSrc = smem;                                                       // [maxRows][SPT] staged source rows
     uint32_t* sH = reinterpret_cast<uint32_t*>(smem + (size_t)maxRows * SPT);   // [maxRows][kTW] horizontal pass
 
@@ -171,14 +186,22 @@ __global__ void __launch_bounds__(256)
         __syncthreads();
         const int S0 = sS0, nS = sNS;
 
-        // ---- stage the source rows: 16 threads per row, 16 rows per sweep -----------------------------------------
-        {
+        // ---- stage the source rows --------------------------------------------------------------------------------
+        if (TMA) {
+            if (tid == 0) {
+                mbarExpectTx(&bar, (uint32_t)(SPT * maxRows));
+                tmaLoadTile(sSrc, &srcMap, A0, kEdge + S0, frame0 + (int)blockIdx.z, &bar);
+            }
+            mbarWait(&bar, barPhase);
+            barPhase ^= 1u;
+        } else {
+            // 16 threads per row, 16 rows per sweep
             const uint8_t* src = frame + srcOff + (size_t)(kEdge + S0) * spitch + A0;
             for (int c = tid & 15; c < nC16; c += 16)
                 for (int r = tid >> 4; r < nS; r += 16)
                     *reinterpret_cast<uint4*>(sSrc + r * SPT + c * 16) = __ldcg(reinterpret_cast<const uint4*>(src + (size_t)r * spitch) + c);
+            __syncthreads();
         }
-        __syncthreads();
 
         // ---- horizontal pass: H[s][x] = (p0*a0 + p1*a1) >> 4  (<= 32640) ------------------------------------------
         if (WINDOWED) {
@@ -228,18 +251,38 @@ __global__ void __launch_bounds__(256)
 
 }  // namespace
 
-template <int SPT, bool WINDOWED>
+static int pyrMaxRows(const LevelPlan& S, const LevelPlan& D) {
+    return (int)((double)kTH * S.h / D.h) + 4;  // source rows a 32-row tile can need
+}
+
+// m[l] (l >= 1) = map of the SOURCE level l-1 with the box the resize of level l stages: 192 bytes x maxRows rows
+int buildPyrMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out) {
+    LevelMaps* M = reinterpret_cast<LevelMaps*>(out);
+    std::memset(M, 0, sizeof(LevelMaps));
+    for (int l = 1; l < P.nlevels; ++l) {
+        const int rows = pyrMaxRows(P.lv[l - 1], P.lv[l]);
+        if (rows > 256) continue;  // falls back to ordinary loads (launchPyramid checks the same bound)
+        const int rc = encodeLevelMap(&M->m[l], P, l - 1, pyrBase, capFrames, 192, rows);
+        if (rc != 0) return rc;
+    }
+    return 0;
+}
+
+template <int SPT, bool WINDOWED, bool TMA = false>
 static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cudaStream_t s) {
     const LevelPlan& S = P.lv[l - 1];
     const LevelPlan& D = P.lv[l];
     const int pw = D.w + 2 * kEdge, ph = D.h + 2 * kEdge;
-    const int maxRows = (int)((double)kTH * S.h / D.h) + 4;  // source rows a 32-row tile can need
+    const int maxRows = pyrMaxRows(S, D);
     const size_t smem = (size_t)maxRows * (SPT + kTW * 4);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(pyrResizeKernel<SPT, WINDOWED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    auto kern = pyrResizeKernel<SPT, WINDOWED, TMA>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((pw + kTW - 1) / kTW, ((ph + kTH - 1) / kTH + kRowTiles - 1) / kRowTiles, F);
-    pyrResizeKernel<SPT, WINDOWED><<<grid, 256, smem, s>>>(B.pyr, P.frameBytes, S.planeOff, S.w, S.h, S.pitch, D.planeOff, D.w, D.h,
-                                                 D.pitch, reinterpret_cast<const short4*>(B.tab) + D.tabX,
-                                                 reinterpret_cast<const short4*>(B.tab) + D.tabY, maxRows);
+    static const CUtensorMap kNoMap{};
+    const CUtensorMap& map = TMA ? reinterpret_cast<const LevelMaps*>(B.pyrMaps)->m[l] : kNoMap;
+    kern<<<grid, 256, smem, s>>>(B.pyr, P.frameBytes, S.planeOff, S.w, S.h, S.pitch, D.planeOff, D.w, D.h, D.pitch,
+                                 reinterpret_cast<const short4*>(B.tab) + D.tabX, reinterpret_cast<const short4*>(B.tab) + D.tabY, maxRows,
+                                 map, B.frame0);
     countLaunch();
 }
 
@@ -267,7 +310,8 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
         const double need = 128.0 * P.lv[l - 1].w / P.lv[l].w + 2 + 15 + 16;
         // windowed horizontal pass: 4 neighbouring columns span <= 8 source bytes iff floor(3 * step) + 2 <= 7
         const bool windowed = (double)P.lv[l - 1].w / P.lv[l].w < 1.95;
-        if (need <= 192 && windowed) launchResizeT<192, true>(P, B, l, F, s);
+        if (need <= 192 && windowed && B.pyrMaps && pyrMaxRows(P.lv[l - 1], P.lv[l]) <= 256) launchResizeT<192, true, true>(P, B, l, F, s);
+        else if (need <= 192 && windowed) launchResizeT<192, true>(P, B, l, F, s);
         else if (need <= 192) launchResizeT<192, false>(P, B, l, F, s);
         else if (need <= 512) launchResizeT<512, false>(P, B, l, F, s);  // scale factors up to ~3.7
         else launchResizeT<2048, false>(P, B, l, F, s);

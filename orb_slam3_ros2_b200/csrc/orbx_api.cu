@@ -85,6 +85,7 @@ struct orbx_extractor {
     // TMA tensor maps of the FAST tile staging (one per level, over the whole mPyr allocation); rebuilt with the buffers
     alignas(64) unsigned char fastMaps[kMaxLevels * 128];
     alignas(64) unsigned char blurMaps[kMaxLevels * 128];
+    alignas(64) unsigned char pyrMaps[kMaxLevels * 128];
     DevMem mBlurTab;
     bool useTma = true;
     DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
@@ -236,6 +237,8 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
             if (levelMapsBytes() > sizeof(h->blurMaps)) return fail(ORBX_ERR_CUDA, "tensor map table larger than expected");
             const int rb = buildBlurMaps(P, (const uint8_t*)h->mPyr.p, F, h->blurMaps);
             if (rb != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for the blur tiles (" + std::to_string(rb) + ")");
+            const int rp = buildPyrMaps(P, (const uint8_t*)h->mPyr.p, F, h->pyrMaps);
+            if (rp != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for the resize rows (" + std::to_string(rp) + ")");
         }
     }
     Buffers& B = h->buf;
@@ -245,7 +248,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
     B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
     B.fastMaps = h->useTma ? h->fastMaps : nullptr; B.frame0 = 0;
-    B.blurMaps = h->useTma ? h->blurMaps : nullptr; B.blurTab = (uint32_t*)h->mBlurTab.p;
+    B.blurMaps = h->useTma ? h->blurMaps : nullptr; B.pyrMaps = h->useTma ? h->pyrMaps : nullptr; B.blurTab = (uint32_t*)h->mBlurTab.p;
     return ORBX_OK;
 }
 

@@ -87,6 +87,7 @@ struct Buffers {
     const void* fastMaps;  // host copy of the per-level TMA tensor maps over the whole pyramid allocation (buildFastMaps);
                            // nullptr = stage FAST tiles with ordinary loads (ORBX_FAST_TMA=0)
     const void* blurMaps;  // the same for the blur's 144 x 38 input tiles (buildBlurMaps); nullptr = ordinary loads
+    const void* pyrMaps;   // source-level maps of the resize kernels' staged rows (buildPyrMaps); nullptr = ordinary loads
     uint32_t* blurTab;   // blur tile table of the plan (buildBlurTileTable)
     int frame0;          // first frame of these buffers inside the allocation (z coordinate base of the tensor maps)
 };
@@ -99,6 +100,7 @@ void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
 size_t fastMapsBytes();
 size_t levelMapsBytes();
 void buildBlurTileTable(const FramePlan& P, std::vector<uint32_t>& tab);
+int buildPyrMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 int buildBlurMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
