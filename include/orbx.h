@@ -233,6 +233,21 @@ int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, 
  * [nframes][cap] floats with cap = cap_per_frame of orbx_batch_results; entries past a frame's keypoint count are unspecified. */
 int orbx_compute_stereo_matches_batch(orbx_handle left, orbx_handle right, float bf, float b, float* u_right, float* depth);
 
+/* ---- Frame::UndistortKeyPoints / Frame::ComputeImageBounds (row N1, Frame.cc:747-809), pinhole camera -----------------
+ * Replaces cv::undistortPoints(mat, mat, Pinhole::toK(), mDistCoef, cv::Mat(), mK) (Frame.cc:766, :795): K and P are the two
+ * 3 x 3 float matrices row-major, dist = mDistCoef (4, 5, 8 or 12 floats: k1 k2 p1 p2 [k3 [k4 k5 k6 [s1..s4]]]).  Arithmetic
+ * in doubles, 5 fixed iterations, results rounded to float: equal to OpenCV's scalar path bit for bit.  With dist[0] == 0 the
+ * keypoints are copied unchanged (:749-753) and the bounds are (0, cols, 0, rows) (:804-809).
+ * orbx_undistort_keypoints: host arrays (kps_un may alias kps).  orbx_image_bounds: bounds = (mnMinX, mnMaxX, mnMinY,
+ * mnMaxY), what orbx_search_grid_top2 takes.  orbx_undistort_batch: mvKeysUn of EVERY frame of the handle's last batch, read
+ * and written on the device ([frame][cap_per_frame] as orbx_batch_results; entries past a frame's count are unspecified);
+ * kps_un (host, may be NULL) receives a copy, *d_kps_un (may be NULL) the device array, valid until the next call. */
+int orbx_undistort_keypoints(const orbx_keypoint* kps, int n, const float* K, const float* dist, int ndist, const float* P,
+                             orbx_keypoint* kps_un, int device);
+int orbx_image_bounds(int cols, int rows, const float* K, const float* dist, int ndist, const float* P, float bounds[4], int device);
+int orbx_undistort_batch(orbx_handle h, const float* K, const float* dist, int ndist, const float* P, orbx_keypoint* kps_un,
+                         const orbx_keypoint** d_kps_un);
+
 /* ---- Frame::ComputeBoW (row N4): DBoW2 vocabulary-tree transform --------------------------------------------------
  * Replaces mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) (ORB_SLAM3/src/Frame.cc:738-745), i.e.
  * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)

@@ -333,4 +333,49 @@ int orbo_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf
     return nmatches;
 }
 
+// ---- Frame::UndistortKeyPoints (src/Frame.cc:747-780) and Frame::ComputeImageBounds (:782-809), pinhole camera ------------
+// cv::undistortPoints is OpenCV's (un-vendored): minicv's restatement, pinned to cv2 4.13.0 by tests/golden/prim_undistort.npz.
+// K = Pinhole::toK(), P = mK: 3 x 3 float row-major; dist = mDistCoef (ndist floats).  PINNED to the reference's own bodies
+// (oracle/_ref/librefslices.so) by tests/test_oracle_refslices.py.
+void minicv_undistort_points(const float* pts, int n, const float* K, const float* dist, int ndist, const float* P, float* out);
+
+void orbo_undistort_keypoints(const void* kps_in, int n, const float* K, const float* dist, int ndist, const float* P, void* kps_out) {
+    const Kp* in = (const Kp*)kps_in;
+    Kp* out = (Kp*)kps_out;
+    if (dist[0] == 0.0) {  // :749-753 mvKeysUn = mvKeys
+        if (n) std::memcpy(out, in, (size_t)n * sizeof(Kp));
+        return;
+    }
+    std::vector<float> mat((size_t)n * 2), un((size_t)n * 2);
+    for (int i = 0; i < n; i++) {  // :758-762
+        mat[2 * i] = in[i].x;
+        mat[2 * i + 1] = in[i].y;
+    }
+    minicv_undistort_points(mat.data(), n, K, dist, ndist, P, un.data());  // :765-767
+    for (int i = 0; i < n; i++) {  // :771-778 every other field is carried over
+        Kp kp = in[i];
+        kp.x = un[2 * i];
+        kp.y = un[2 * i + 1];
+        out[i] = kp;
+    }
+}
+
+// bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY)
+void orbo_image_bounds(int cols, int rows, const float* K, const float* dist, int ndist, const float* P, float* bounds) {
+    if (dist[0] != 0.0) {
+        float mat[8] = {0.0f, 0.0f, (float)cols, 0.0f, 0.0f, (float)rows, (float)cols, (float)rows}, un[8];  // :786-790
+        minicv_undistort_points(mat, 4, K, dist, ndist, P, un);  // :793-796
+        bounds[0] = std::min(un[0], un[4]);  // :799 min(mat(0,0), mat(2,0))
+        bounds[1] = std::max(un[2], un[6]);  // :800 max(mat(1,0), mat(3,0))
+        bounds[2] = std::min(un[1], un[3]);  // :801 min(mat(0,1), mat(1,1))
+        bounds[3] = std::max(un[5], un[7]);  // :802 max(mat(2,1), mat(3,1))
+    } else {  // :804-809
+        bounds[0] = 0.0f;
+        bounds[1] = (float)cols;
+        bounds[2] = 0.0f;
+        bounds[3] = (float)rows;
+    }
+}
+
+
 }  // extern "C"

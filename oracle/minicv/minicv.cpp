@@ -235,6 +235,67 @@ float fastAtan2(float y, float x) {
 }
 
 // ---------------------------------------------------------------------------------
+// undistortPoints (calib3d, cvUndistortPointsInternal): called by Frame::UndistortKeyPoints / ComputeImageBounds
+// (ORB_SLAM3/src/Frame.cc:766, :795) with R empty and P = mK.  Camera matrix, distortion coefficients and P are
+// converted to double; the coefficient vector is (k1, k2, p1, p2[, k3[, k4, k5, k6[, s1..s4[, tauX, tauY]]]]) padded
+// with zeros (tilt = identity for the 4/5-coefficient vectors of the path).  Default criteria = 5 iterations, no
+// epsilon test.  Scalar double arithmetic, no FMA (baseline SSE2 build of the cv2 wheel; pinned by
+// tests/golden/prim_undistort.npz).
+// ---------------------------------------------------------------------------------
+static double matElem(const Mat& m, int i) { return m.depth() == CV_64F ? m.at<double>(i) : (double)m.at<float>(i); }
+void undistortPoints(InputArray _src, OutputArray _dst, InputArray _K, InputArray _D, InputArray _R, InputArray _P) {
+    const Mat src = _src.getMat(), K = _K.getMat(), D = _D.getMat(), P = _P.getMat();
+    assert(_R.empty());
+    (void)_R;
+    assert(src.depth() == CV_32F && src.channels() == 2 && src.cols == 1);
+    const int n = src.rows;
+    double k[14] = {0};
+    const int nk = D.empty() ? 0 : D.rows * D.cols;
+    for (int i = 0; i < nk && i < 14; ++i) k[i] = matElem(D, i);
+    const double fx = matElem(K.row(0), 0), fy = matElem(K.row(1), 1), cx = matElem(K.row(0), 2), cy = matElem(K.row(1), 2);
+    const double ifx = 1. / fx, ify = 1. / fy;
+    double RR[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    if (!P.empty())  // RR = PP * RR with RR = I: exact
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) RR[r][c] = matElem(P.row(r), c);
+    std::vector<float> out((size_t)n * 2);
+    for (int i = 0; i < n; ++i) {
+        const float* s = src.ptr<float>(i);
+        double x = s[0], y = s[1];
+        const double u = x, v = y;
+        x = (x - cx) * ifx;
+        y = (y - cy) * ify;
+        if (nk) {
+            const double x0 = x, y0 = y;
+            for (int j = 0; j < 5; ++j) {
+                const double r2 = x * x + y * y;
+                const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+                if (icdist < 0) {  // the point is outside the valid area of the model: left as the normalised input
+                    x = (u - cx) * ifx;
+                    y = (v - cy) * ify;
+                    break;
+                }
+                const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+                const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+                x = (x0 - deltaX) * icdist;
+                y = (y0 - deltaY) * icdist;
+            }
+        }
+        const double xx = RR[0][0] * x + RR[0][1] * y + RR[0][2];
+        const double yy = RR[1][0] * x + RR[1][1] * y + RR[1][2];
+        const double ww = 1. / (RR[2][0] * x + RR[2][1] * y + RR[2][2]);
+        out[2 * i] = (float)(xx * ww);
+        out[2 * i + 1] = (float)(yy * ww);
+    }
+    if (_dst.getMat().data != src.data || _dst.getMat().rows != n) {
+        _dst.create(n, 2, CV_32F);
+        _dst.getMatRef() = _dst.getMat().reshape(2);
+    }
+    Mat& dst = _dst.getMatRef();
+    for (int i = 0; i < n; ++i) std::memcpy(dst.ptr<float>(i), &out[2 * i], 8);
+}
+
+// ---------------------------------------------------------------------------------
 // KeyPointsFilter::retainBest — only reachable from the reference's dead
 // ComputeKeyPointsOld (ORBextractor.cc:1049,1067; its call is commented out at :1101).
 // ---------------------------------------------------------------------------------

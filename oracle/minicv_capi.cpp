@@ -40,4 +40,13 @@ void minicv_fast_atan2(const float* y, const float* x, float* out, int n) {
     for (int i = 0; i < n; ++i) out[i] = cv::fastAtan2(y[i], x[i]);
 }
 
+// pts / out: n x 2 floats; K, P: 3 x 3 floats row-major; dist: ndist floats
+void minicv_undistort_points(const float* pts, int n, const float* K, const float* dist, int ndist, const float* P, float* out) {
+    cv::Mat src = cv::Mat(n, 2, CV_32F, const_cast<float*>(pts)).clone().reshape(2);
+    cv::Mat Km(3, 3, CV_32F, const_cast<float*>(K)), Pm(3, 3, CV_32F, const_cast<float*>(P));
+    cv::Mat Dm = ndist ? cv::Mat(ndist, 1, CV_32F, const_cast<float*>(dist)) : cv::Mat();
+    cv::undistortPoints(src, src, Km, Dm, cv::Mat(), Pm);
+    for (int i = 0; i < n; ++i) std::memcpy(out + 2 * i, src.ptr<float>(i), 8);
+}
+
 }  // extern "C"

@@ -168,6 +168,9 @@ def port_lib():
         lib.minicv_fast.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i32p, C.c_int]
         lib.minicv_gauss7.argtypes = [_u8p, C.c_int, C.c_int, _u8p]
         lib.minicv_fast_atan2.argtypes = [_f32p, _f32p, _f32p, C.c_int]
+        lib.minicv_undistort_points.argtypes = [_f32p, C.c_int, _f32p, _f32p, C.c_int, _f32p, _f32p]
+        lib.orbo_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, C.c_int, _f32p, C.c_void_p]
+        lib.orbo_image_bounds.argtypes = [C.c_int, C.c_int, _f32p, _f32p, C.c_int, _f32p, _f32p]
         _port = lib
     return _port
 
@@ -321,6 +324,59 @@ def compute_stereo_matches(kl, dl, kr, dr, scale_factors, inv_scale_factors, pyr
                                            _ptr(st_r, _i32p), _ptr(cols, _i32p), n_rows, float(bf), float(b), _ptr(ur, _f32p),
                                            _ptr(dp, _f32p))
     return ur[:n], dp[:n]
+
+
+def _cam(K, dist, P):
+    K = np.ascontiguousarray(K, dtype=np.float32).reshape(3, 3)
+    P = K if P is None else np.ascontiguousarray(P, dtype=np.float32).reshape(3, 3)
+    return K, np.ascontiguousarray(dist, dtype=np.float32).ravel(), P
+
+
+def undistort_points(pts, K, dist, P=None):
+    """minicv's cv::undistortPoints(pts, K, dist, R = I, P) -> n x 2 float32."""
+    K, dist, P = _cam(K, dist, P)
+    pts = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 2)
+    out = np.zeros_like(pts)
+    port_lib().minicv_undistort_points(_ptr(pts, _f32p), len(pts), _ptr(K, _f32p), _ptr(dist, _f32p), len(dist), _ptr(P, _f32p),
+                                       _ptr(out, _f32p))
+    return out
+
+
+def _undistort_keypoints(fn, kps, K, dist, P):
+    K, dist, P = _cam(K, dist, P)
+    kps = np.ascontiguousarray(kps)
+    assert kps.dtype.itemsize == 28
+    out = np.zeros(max(len(kps), 1), dtype=kps.dtype)
+    fn(kps.ctypes.data_as(C.c_void_p), len(kps), _ptr(K, _f32p), _ptr(dist, _f32p), len(dist), _ptr(P, _f32p),
+       out.ctypes.data_as(C.c_void_p))
+    return out[:len(kps)]
+
+
+def _image_bounds(fn, w, h, K, dist, P):
+    K, dist, P = _cam(K, dist, P)
+    out = np.zeros(4, np.float32)
+    fn(int(w), int(h), _ptr(K, _f32p), _ptr(dist, _f32p), len(dist), _ptr(P, _f32p), _ptr(out, _f32p))
+    return out
+
+
+def undistort_keypoints(kps, K, dist, P=None):
+    """Frame::UndistortKeyPoints (Frame.cc:747-780): mvKeys -> mvKeysUn."""
+    return _undistort_keypoints(port_lib().orbo_undistort_keypoints, kps, K, dist, P)
+
+
+def image_bounds(w, h, K, dist, P=None):
+    """Frame::ComputeImageBounds (Frame.cc:782-809) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    return _image_bounds(port_lib().orbo_image_bounds, w, h, K, dist, P)
+
+
+def ref_undistort_keypoints(kps, K, dist, P=None):
+    """Frame::UndistortKeyPoints, the reference's own body (librefslices.so)."""
+    return _undistort_keypoints(_slices().refslice_undistort_keypoints, kps, K, dist, P)
+
+
+def ref_image_bounds(w, h, K, dist, P=None):
+    """Frame::ComputeImageBounds, the reference's own body (librefslices.so)."""
+    return _image_bounds(_slices().refslice_image_bounds, w, h, K, dist, P)
 
 
 def stage_gray(img, rgb=True, new_size=None):
@@ -518,6 +574,8 @@ def _slices():
                                                         C.c_void_p, C.c_void_p, _i32p, _i32p, C.c_float, C.c_float, _f32p, _f32p]
         lib.refslice_grid_top2.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, _u8p,
                                            C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p]
+        lib.refslice_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, C.c_int, _f32p, C.c_void_p]
+        lib.refslice_image_bounds.argtypes = [C.c_int, C.c_int, _f32p, _f32p, C.c_int, _f32p, _f32p]
         _refslices = lib
     return _refslices
 

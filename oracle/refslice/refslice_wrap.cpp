@@ -11,6 +11,8 @@
 //   Frame.cc:657-723         Frame::GetFeaturesInArea
 //   Frame.cc:725-735         Frame::PosInGrid
 //   Frame.cc:811-981         Frame::ComputeStereoMatches
+//   Frame.cc:747-780         Frame::UndistortKeyPoints   (cv::undistortPoints = minicv's, pinned to cv2 goldens)
+//   Frame.cc:782-809         Frame::ComputeImageBounds
 // They pin oracle/match_oracle.cpp (tests/test_oracle_refslices.py).  Built only where /root/reference exists.
 #include <cstdint>
 #include <cstring>
@@ -25,6 +27,8 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 #include "Frame_GetFeaturesInArea.inc"
 #include "Frame_PosInGrid.inc"
 #include "Frame_ComputeStereoMatches.inc"
+#include "Frame_UndistortKeyPoints.inc"
+#include "Frame_ComputeImageBounds.inc"
 #include "ORBmatcher_SearchByBoW.inc"
 #include "ORBmatcher_ComputeThreeMaxima.inc"
 }  // namespace ORB_SLAM3
@@ -82,6 +86,37 @@ void refslice_compute_stereo_matches(const void* kps_l, const uint8_t* desc_l, i
     F.ComputeStereoMatches();
     std::memcpy(u_right, F.mvuRight.data(), (size_t)nl * 4);
     std::memcpy(depth, F.mvDepth.data(), (size_t)nl * 4);
+}
+
+namespace {
+void pinholeFrame(Frame& F, ORB_SLAM3::Pinhole& cam, const float* K, const float* dist, int ndist, const float* P) {
+    cam.K = cv::Mat(3, 3, CV_32F, const_cast<float*>(K)).clone();
+    F.mpCamera = &cam;
+    F.mK = cv::Mat(3, 3, CV_32F, const_cast<float*>(P)).clone();
+    F.mDistCoef = cv::Mat(ndist, 1, CV_32F, const_cast<float*>(dist)).clone();  // Tracking.cc builds it as ndist x 1 CV_32F
+}
+}  // namespace
+
+// Frame::UndistortKeyPoints: mvKeys = kps -> mvKeysUn = out (n 28-byte cv::KeyPoint records).  K, P: 3 x 3 row-major.
+void refslice_undistort_keypoints(const void* kps, int n, const float* K, const float* dist, int ndist, const float* P, void* out) {
+    Frame F;
+    ORB_SLAM3::Pinhole cam;
+    pinholeFrame(F, cam, K, dist, ndist, P);
+    F.N = n;
+    F.mvKeys = keypoints(kps, n);
+    F.UndistortKeyPoints();
+    if (n) std::memcpy(out, F.mvKeysUn.data(), (size_t)n * sizeof(cv::KeyPoint));
+}
+
+// Frame::ComputeImageBounds(imLeft) for an image of cols x rows -> bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY)
+void refslice_image_bounds(int cols, int rows, const float* K, const float* dist, int ndist, const float* P, float* bounds) {
+    Frame F;
+    ORB_SLAM3::Pinhole cam;
+    pinholeFrame(F, cam, K, dist, ndist, P);
+    cv::Mat im;
+    im.cols = cols; im.rows = rows;
+    F.ComputeImageBounds(im);
+    bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMaxX; bounds[2] = Frame::mnMinY; bounds[3] = Frame::mnMaxY;
 }
 
 // Monocular frame (Nleft == -1): AssignFeaturesToGrid over mvKeysUn = kps_t, then for every query GetFeaturesInArea and the

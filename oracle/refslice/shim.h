@@ -29,7 +29,12 @@ struct ORBextractor {  // include/ORBextractor.h:83
     std::vector<cv::Mat> mvImagePyramid;
 };
 
-class GeometricCamera;
+class GeometricCamera {};  // include/CameraModels/GeometricCamera.h: only the static_cast target below is used
+class Pinhole : public GeometricCamera {  // include/CameraModels/Pinhole.h:81 toK()
+public:
+    cv::Mat toK() { return K.clone(); }
+    cv::Mat K;  // (shim) 3 x 3 CV_32F, what Pinhole::toK builds from mvParameters (src/CameraModels/Pinhole.cpp:134-138)
+};
 class Frame;
 
 class MapPoint {  // include/MapPoint.h: only isBad() is used on this path
@@ -70,6 +75,10 @@ public:
     vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1,
                                      const int maxLevel = -1, const bool bRight = false) const;
     bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
+    void UndistortKeyPoints();
+    void ComputeImageBounds(const cv::Mat& imLeft);
+    cv::Mat mK, mDistCoef;
+    GeometricCamera* mpCamera = nullptr;
 
     ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
     float mbf = 0, mb = 0;

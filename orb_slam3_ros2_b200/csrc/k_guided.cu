@@ -9,6 +9,9 @@
 //   * stereoRefineKernel +  the second half of Frame::ComputeStereoMatches (Frame.cc:896-980): 11 x 11 L1 correlation
 //     stereoCutKernel       over +-5 px read straight from the two extractors' device-resident pyramids, parabola fit,
 //                           disparity / depth, and the 1.5 * 1.4 * median cut through a histogram select.
+//   * undistortKernel       Frame::UndistortKeyPoints / ComputeImageBounds (Frame.cc:747-809): cv::undistortPoints for a
+//                           pinhole camera, one thread per keypoint, the 5 fixed iterations in round-to-nearest doubles
+//                           without contraction (cv2 4.13.0's scalar path, bit for bit).
 #include "orbx_internal.cuh"
 
 namespace orbx {
@@ -301,6 +304,50 @@ __global__ void __launch_bounds__(1024) stereoCutKernel(const int* __restrict__ 
         if (sad[i] >= 0 && !((float)sad[i] < thDist)) { uRight[i] = -1.0f; depth[i] = -1.0f; }
 }
 
+// cv::undistortPoints(src, dst, K, dist, R = I, P) as Frame::UndistortKeyPoints calls it (Frame.cc:766); every operation is
+// written in the order of OpenCV's cvUndistortPointsInternal with explicit _rn intrinsics so that nvcc contracts nothing.
+__device__ __forceinline__ double dm(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double da(double a, double b) { return __dadd_rn(a, b); }
+__global__ void undistortKernel(const float* kpsIn, float* kpsOut, const int* __restrict__ nPerFrame,
+                                int nSingle, int cap, const UndistortCam C) {
+    const int f = blockIdx.y;
+    const int n = nPerFrame ? nPerFrame[f] : nSingle;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* in = kpsIn + ((size_t)f * cap + i) * 7;
+    float* out = kpsOut + ((size_t)f * cap + i) * 7;
+    const double u = (double)in[0], v = (double)in[1];
+    double x = dm(__dsub_rn(u, C.cx), C.ifx), y = dm(__dsub_rn(v, C.cy), C.ify);
+    const double x0 = x, y0 = y;
+    const double* k = C.k;
+    for (int j = 0; j < 5; ++j) {
+        const double r2 = da(dm(x, x), dm(y, y));
+        const double num = da(1.0, dm(da(dm(da(dm(k[7], r2), k[6]), r2), k[5]), r2));
+        const double den = da(1.0, dm(da(dm(da(dm(k[4], r2), k[1]), r2), k[0]), r2));
+        const double icdist = __ddiv_rn(num, den);
+        if (icdist < 0) {
+            x = x0;  // (u - cx) * ifx again
+            y = y0;
+            break;
+        }
+        // deltaX = 2*k2*x*y + k3*(r2 + 2*x*x) + k8*r2 + k9*r2*r2, left to right
+        const double dX = da(da(da(dm(dm(dm(2.0, k[2]), x), y), dm(k[3], da(r2, dm(dm(2.0, x), x)))), dm(k[8], r2)), dm(dm(k[9], r2), r2));
+        // deltaY = k2*(r2 + 2*y*y) + 2*k3*x*y + k10*r2 + k11*r2*r2
+        const double dY = da(da(da(dm(k[2], da(r2, dm(dm(2.0, y), y))), dm(dm(dm(2.0, k[3]), x), y)), dm(k[10], r2)), dm(dm(k[11], r2), r2));
+        x = dm(__dsub_rn(x0, dX), icdist);
+        y = dm(__dsub_rn(y0, dY), icdist);
+    }
+    const double xx = da(da(dm(C.rr[0], x), dm(C.rr[1], y)), C.rr[2]);
+    const double yy = da(da(dm(C.rr[3], x), dm(C.rr[4], y)), C.rr[5]);
+    const double ww = __ddiv_rn(1.0, da(da(dm(C.rr[6], x), dm(C.rr[7], y)), C.rr[8]));
+    out[0] = (float)dm(xx, ww);
+    out[1] = (float)dm(yy, ww);
+    if (out != in) {
+#pragma unroll
+        for (int w = 2; w < 7; ++w) out[w] = in[w];  // size, angle, response, octave, class_id carried over (:773-777)
+    }
+}
+
 }  // namespace
 
 void launchAccept(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* l1,
@@ -351,6 +398,13 @@ void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, c
     cudaFuncSetAttribute(stereoCutKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     stereoCutKernel<<<frames, 1024, smem, s>>>(sad, nl, uRight, depth, SB);
     countLaunch();
+}
+
+void launchUndistort(const void* kpsIn, void* kpsOut, const int* nPerFrame, int nSingle, int frames, int cap, const UndistortCam& C,
+                     cudaStream_t s) {
+    if (frames <= 0 || cap <= 0 || (!nPerFrame && nSingle <= 0)) return;
+    const int most = nPerFrame ? cap : nSingle;
+    undistortKernel<<<dim3((most + 127) / 128, frames), 128, 0, s>>>((const float*)kpsIn, (float*)kpsOut, nPerFrame, nSingle, cap, C);
 }
 
 }  // namespace orbx

@@ -88,6 +88,7 @@ struct orbx_extractor {
     alignas(64) unsigned char pyrMaps[kMaxLevels * 128];
     DevMem mBlurTab;
     bool useTma = true;
+    DevMem mKpsUn;           // orbx_undistort_batch: mvKeysUn of the last batch, [frame][cap]
     DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
     int stagedW = 0, stagedH = 0;
     std::vector<uint8_t> hStage;  // pinned staging would be the caller's; this is only for get_* taps
@@ -405,7 +406,7 @@ void orbx_destroy(orbx_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
-                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab};
+                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn};
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 9; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -1194,6 +1195,95 @@ int orbx_compute_stereo_matches_batch(orbx_handle left, orbx_handle right, float
     ORBX_CUDA(cudaMemcpyAsync(u_right, ur, T * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(depth, dp, T * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+// ---- Frame::UndistortKeyPoints / ComputeImageBounds (row N1, Frame.cc:747-809) ----------------------------------------
+static int undistortCam(const float* K, const float* dist, int ndist, const float* P, UndistortCam* C) {
+    if (!K || !P || ndist < 0 || ndist > 12 || (ndist > 0 && !dist)) return fail(ORBX_ERR_ARG, "bad camera");
+    if (ndist != 0 && ndist != 4 && ndist != 5 && ndist != 8 && ndist != 12)
+        return fail(ORBX_ERR_ARG, "distortion vector must have 4, 5, 8 or 12 coefficients");  // cv::undistortPoints' own check
+    C->ifx = 1. / (double)K[0];
+    C->ify = 1. / (double)K[4];
+    C->cx = (double)K[2];
+    C->cy = (double)K[5];
+    for (int i = 0; i < 12; ++i) C->k[i] = i < ndist ? (double)dist[i] : 0.0;
+    for (int i = 0; i < 9; ++i) C->rr[i] = (double)P[i];
+    return ORBX_OK;
+}
+
+int orbx_undistort_keypoints(const orbx_keypoint* kps, int n, const float* K, const float* dist, int ndist, const float* P,
+                             orbx_keypoint* kps_un, int device) {
+    if (n < 0 || (n > 0 && (!kps || !kps_un))) return fail(ORBX_ERR_ARG, "bad argument");
+    UndistortCam C;
+    int rc = undistortCam(K, dist, ndist, P, &C);
+    if (rc != ORBX_OK) return rc;
+    rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    if (n == 0) return ORBX_OK;
+    if (ndist == 0 || dist[0] == 0.0) {  // Frame.cc:749-753 mvKeysUn = mvKeys
+        if (kps_un != kps) std::memcpy(kps_un, kps, (size_t)n * sizeof(orbx_keypoint));
+        return ORBX_OK;
+    }
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA(S->misc.reserve((size_t)n * sizeof(orbx_keypoint)));
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaMemcpyAsync(S->misc.p, kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, s));
+    launchUndistort(S->misc.p, S->misc.p, nullptr, n, 1, n, C, s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(kps_un, S->misc.p, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_image_bounds(int cols, int rows, const float* K, const float* dist, int ndist, const float* P, float bounds[4], int device) {
+    if (!bounds || cols <= 0 || rows <= 0) return fail(ORBX_ERR_ARG, "bad argument");
+    UndistortCam C;
+    int rc = undistortCam(K, dist, ndist, P, &C);
+    if (rc != ORBX_OK) return rc;
+    if (ndist == 0 || dist[0] == 0.0) {  // Frame.cc:804-809
+        bounds[0] = 0.0f; bounds[1] = (float)cols; bounds[2] = 0.0f; bounds[3] = (float)rows;
+        return ORBX_OK;
+    }
+    orbx_keypoint c[4] = {};
+    c[1].x = (float)cols; c[2].y = (float)rows; c[3].x = (float)cols; c[3].y = (float)rows;  // :786-790
+    rc = orbx_undistort_keypoints(c, 4, K, dist, ndist, P, c, device);
+    if (rc != ORBX_OK) return rc;
+    bounds[0] = std::min(c[0].x, c[2].x);  // :799-802
+    bounds[1] = std::max(c[1].x, c[3].x);
+    bounds[2] = std::min(c[0].y, c[1].y);
+    bounds[3] = std::max(c[2].y, c[3].y);
+    return ORBX_OK;
+}
+
+int orbx_undistort_batch(orbx_handle h, const float* K, const float* dist, int ndist, const float* P, orbx_keypoint* kps_un,
+                         const orbx_keypoint** d_kps_un) {
+    if (!h) return fail(ORBX_ERR_ARG, "bad argument");
+    if (h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    UndistortCam C;
+    int rc = undistortCam(K, dist, ndist, P, &C);
+    if (rc != ORBX_OK) return rc;
+    DeviceGuard guard(h->device);
+    const int F = h->lastFrames, cap = h->plan.outCap;
+    const size_t bytes = (size_t)F * cap * sizeof(orbx_keypoint);
+    ORBX_CUDA(h->mKpsUn.reserve(bytes));
+    cudaStream_t s = h->stream;  // behind the extraction that produced the keypoints
+    if (ndist == 0 || dist[0] == 0.0)
+        ORBX_CUDA(cudaMemcpyAsync(h->mKpsUn.p, h->buf.outKps, bytes, cudaMemcpyDeviceToDevice, s));
+    else
+        launchUndistort(h->buf.outKps, h->mKpsUn.p, h->buf.outN, 0, F, cap, C, s);
+    ORBX_CUDA(cudaGetLastError());
+    if (d_kps_un) *d_kps_un = (const orbx_keypoint*)h->mKpsUn.p;
+    if (kps_un) {
+        ORBX_CUDA(cudaMemcpyAsync(kps_un, h->mKpsUn.p, bytes, cudaMemcpyDeviceToHost, s));
+        ORBX_CUDA(cudaStreamSynchronize(s));
+        return checkDeviceFlags(h);
+    }
     return ORBX_OK;
 }
 

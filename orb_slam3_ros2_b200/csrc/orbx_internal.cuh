@@ -142,6 +142,14 @@ void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX
 void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, const uint8_t* pyrL, const uint8_t* pyrR,
                         const void* kl, const void* kr, int nl, const int* bestIdx, const int* bestDist, float mbf, float maxD,
                         float* uRight, float* depth, int* sad, cudaStream_t s, const StereoBatch* batch = nullptr);
+// Frame::UndistortKeyPoints: the pinhole model in doubles, as cv::undistortPoints converts it (k = k1 k2 p1 p2 k3 k4 k5 k6 s1..s4)
+struct UndistortCam {
+    double ifx, ify, cx, cy;
+    double k[12];
+    double rr[9];  // P (* R = I), row-major
+};
+void launchUndistort(const void* kpsIn, void* kpsOut, const int* nPerFrame, int nSingle, int frames, int cap, const UndistortCam& C,
+                     cudaStream_t s);
 void launchStage(const uint8_t* dSrc, int sw, int sh, int sstride, int ch, int rgb, uint8_t* dDst, int dw, int dh,
                  const int16_t* tabX, const int16_t* tabY, cudaStream_t s);
 // flat DBoW2 vocabulary on the device (k_bow.cu): children of node c are CSR entries [childBegin[c], childBegin[c+1]) in the

@@ -86,6 +86,9 @@ SYMBOLS = {
     "orbx_compute_stereo_matches": (C.c_int, [_vp, _vp, C.c_int, _vp, _u8p, C.c_int, _vp, _u8p, C.c_int, C.c_float, C.c_float,
                                               _f32p, _f32p]),
     "orbx_compute_stereo_matches_batch": (C.c_int, [_vp, _vp, C.c_float, C.c_float, _f32p, _f32p]),
+    "orbx_undistort_keypoints": (C.c_int, [_vp, C.c_int, _f32p, _f32p, C.c_int, _f32p, _vp, C.c_int]),
+    "orbx_image_bounds": (C.c_int, [C.c_int, C.c_int, _f32p, _f32p, C.c_int, _f32p, _f32p, C.c_int]),
+    "orbx_undistort_batch": (C.c_int, [_vp, _f32p, _f32p, C.c_int, _f32p, _vp, C.POINTER(_vp)]),
     "orbx_search_by_bow": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _f32p, _i32p, _i32p, _i32p,
                                      C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
@@ -444,6 +447,44 @@ def compute_stereo_matches_batch(left, right, bf, b, out=None):
     ur, dp = out if out is not None else (np.zeros((F, cap), np.float32), np.zeros((F, cap), np.float32))
     _check(lib().orbx_compute_stereo_matches_batch(left._h, right._h, float(bf), float(b), _ptr(ur, _f32p), _ptr(dp, _f32p)))
     return ur, dp
+
+
+def _camera(K, dist, P):
+    K = np.ascontiguousarray(K, dtype=np.float32).reshape(3, 3)
+    P = K if P is None else np.ascontiguousarray(P, dtype=np.float32).reshape(3, 3)
+    return K, np.ascontiguousarray(dist, dtype=np.float32).ravel(), P
+
+
+def undistort_keypoints(kps, K, dist, P=None, device=-1):
+    """Frame::UndistortKeyPoints (Frame.cc:747-780) for a pinhole camera: mvKeys -> mvKeysUn.  K = Pinhole::toK(), P = mK
+    (default K), dist = mDistCoef."""
+    K, dist, P = _camera(K, dist, P)
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    out = np.zeros(max(len(kps), 1), dtype=KP_DTYPE)
+    _check(lib().orbx_undistort_keypoints(kps.ctypes.data_as(_vp), len(kps), _ptr(K, _f32p), _ptr(dist, _f32p), len(dist),
+                                          _ptr(P, _f32p), out.ctypes.data_as(_vp), device))
+    return out[:len(kps)]
+
+
+def image_bounds(w, h, K, dist, P=None, device=-1):
+    """Frame::ComputeImageBounds (Frame.cc:782-809) -> (mnMinX, mnMaxX, mnMinY, mnMaxY) float32."""
+    K, dist, P = _camera(K, dist, P)
+    out = np.zeros(4, np.float32)
+    _check(lib().orbx_image_bounds(int(w), int(h), _ptr(K, _f32p), _ptr(dist, _f32p), len(dist), _ptr(P, _f32p), _ptr(out, _f32p),
+                                   device))
+    return out
+
+
+def undistort_batch(extractor, K, dist, P=None, download=True):
+    """mvKeysUn of every frame of the extractor's last batch, computed in place on the device -> (F, cap) KP_DTYPE array
+    (entries past a frame's keypoint count are unspecified) or, with download=False, the device pointer."""
+    K, dist, P = _camera(K, dist, P)
+    F, cap = extractor._frames, extractor.capacity
+    out = np.zeros((F, cap), dtype=KP_DTYPE) if download else None
+    dptr = _vp()
+    _check(lib().orbx_undistort_batch(extractor._h, _ptr(K, _f32p), _ptr(dist, _f32p), len(dist), _ptr(P, _f32p),
+                                      out.ctypes.data_as(_vp) if download else None, C.byref(dptr)))
+    return out if download else dptr.value
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):

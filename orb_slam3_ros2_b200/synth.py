@@ -175,6 +175,39 @@ BOW_CASES = [
     ("k10L3_one", 10, 3, False, 0, None, 1, 1),
 ]
 
+# (name, w, h, fx, fy, cx, cy, distortion (k1, k2, p1, p2[, k3])): the Frame::UndistortKeyPoints / ComputeImageBounds parity
+# cases (pinhole cameras) shared by tools/gen_golden.py (cv2.undistortPoints -> tests/golden/prim_undistort.npz) and the tests.
+# euroc = the reference's config/Monocular-Inertial/EuRoC.yaml:11-19; the others exercise k3, strong barrel / pincushion
+# distortion, the icdist < 0 exit and the zero-k1 early return (Frame.cc:749-753).
+UNDISTORT_CASES = [
+    ("euroc", 752, 480, 458.654, 457.296, 367.215, 248.375, (-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05)),
+    ("k3", 640, 480, 382.613, 382.613, 320.183, 236.455, (-0.05, 0.04, 0.001, -0.002, 0.01)),
+    ("kitti_like", 1241, 376, 718.856, 718.856, 607.1928, 185.2157, (0.1, -0.2, 0.0005, 0.0003)),
+    ("strong_barrel", 752, 480, 300.0, 300.0, 376.0, 240.0, (-0.9, 0.1, 0.0, 0.0)),
+    ("k1_zero", 640, 480, 382.613, 382.613, 320.183, 236.455, (0.0, 0.04, 0.001, -0.002)),
+]
+
+
+def undistort_case(name, n=4000):
+    """-> (w, h, K float32 3x3, dist float32, points float32 n x 2): image corners first (the ComputeImageBounds input,
+    Frame.cc:786-792), then seeded points inside the image, a few on its border and a few far outside."""
+    for nm, w, h, fx, fy, cx, cy, dist in UNDISTORT_CASES:
+        if nm == name:
+            rng = np.random.default_rng(abs(hash_name(nm)) % (1 << 32))
+            K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+            pts = (rng.random((n, 2)) * [w, h]).astype(np.float32)
+            pts[:4] = [[0, 0], [w, 0], [0, h], [w, h]]
+            pts[4:8] = [[cx, cy], [w - 1, h - 1], [-50.5, 3 * h], [2.5 * w, -h]]
+            return w, h, K, np.array(dist, np.float32), pts
+    raise KeyError(name)
+
+
+def hash_name(s):
+    v = 0
+    for ch in s.encode():
+        v = (v * 131 + ch) & 0x7FFFFFFF
+    return v
+
 
 def bow_case(name):
     """-> (k, L, levelsup, parent, node_desc, weight, descriptors) of a BOW_CASES entry."""

@@ -143,3 +143,50 @@ def test_extract_color_staging_matches_cv2_goldens_and_oracle(orbx, oracle):
     assert np.array_equal(ex.staged_gray(), gray)
     wm, wk, wd = oracle.PortExtractor(nfeatures=300).extract(gray, (0, 1000))
     assert mono == wm and np.array_equal(kp, wk) and np.array_equal(desc, wd)
+
+
+@pytest.mark.parametrize("name", [c[0] for c in synth.UNDISTORT_CASES])
+def test_undistort_keypoints_and_image_bounds_bit_exact(orbx, oracle, name):
+    """Frame::UndistortKeyPoints / ComputeImageBounds (Frame.cc:747-809) on the device == oracle == cv2 golden, float bits."""
+    import os
+    from test_oracle_refslices import undistort_keypoint_case
+    w, h, K, dist, kps = undistort_keypoint_case(name)
+    got = orbx.undistort_keypoints(kps, K, dist)
+    want = oracle.undistort_keypoints(kps, K, dist)
+    assert got.tobytes() == want.tobytes()
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "prim_undistort.npz"))
+    if dist[0] != 0:
+        assert np.array_equal(np.stack([got["x"], got["y"]], 1).view(np.uint32), g[f"{name}__out"].view(np.uint32))
+    else:
+        assert got.tobytes() == kps.tobytes()
+    assert orbx.image_bounds(w, h, K, dist).tobytes() == oracle.image_bounds(w, h, K, dist).tobytes()
+    assert len(orbx.undistort_keypoints(kps[:0], K, dist)) == 0
+    # a different projection matrix P than K (cv::undistortPoints' last argument)
+    P = K.copy(); P[0, 0] *= 0.9; P[1, 1] *= 1.1; P[0, 2] += 3.5
+    assert orbx.undistort_keypoints(kps[:500], K, dist, P).tobytes() == oracle.undistort_keypoints(kps[:500], K, dist, P).tobytes()
+
+
+def test_undistort_batch_on_device_resident_keypoints(orbx, oracle):
+    """orbx_undistort_batch: mvKeysUn of a whole extracted batch without leaving the device == per-frame oracle, then the
+    guided search runs on the undistorted keypoints inside the undistorted image bounds (Frame.cc:323-367 order)."""
+    _, w, h, fx, fy, cx, cy, dist = synth.UNDISTORT_CASES[0]
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+    dist = np.array(dist, np.float32)
+    frames = np.stack([synth.frame(k, w, h) for k in range(6)])
+    e = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    mono, n, kps, desc = e.extract_batch(frames, (0, 1000))
+    un = orbx.undistort_batch(e, K, dist)
+    for f in range(len(frames)):
+        assert un[f, :n[f]].tobytes() == oracle.undistort_keypoints(kps[f, :n[f]], K, dist).tobytes(), f
+    assert orbx.undistort_batch(e, K, dist, download=False) != 0
+    zero = np.zeros(4, np.float32)
+    assert orbx.undistort_batch(e, K, zero)[0, :n[0]].tobytes() == kps[0, :n[0]].tobytes()  # Frame.cc:749-753
+    bounds = orbx.image_bounds(w, h, K, dist)
+    qs = np.zeros(int(n[0]), dtype=orbx.GRID_QUERY_DTYPE)
+    qs["u"], qs["v"], qs["r"] = un[0, :n[0]]["x"], un[0, :n[0]]["y"], 100.0
+    qs["min_level"] = qs["max_level"] = kps[0, :n[0]]["octave"]
+    got = orbx.search_grid_top2(un[1, :n[1]], desc[1, :n[1]], bounds, qs, desc[0, :n[0]])
+    want = oracle.search_grid_top2(un[1, :n[1]], desc[1, :n[1]], bounds, qs, desc[0, :n[0]])
+    for g_, w_ in zip(got, want):
+        assert np.array_equal(g_, w_)
+    e.close()

@@ -63,6 +63,17 @@ def test_fast_atan2_bit_exact(oracle):
     assert np.array_equal(got.view(np.uint32), g["angle"].view(np.uint32))
 
 
+def test_undistort_points_bit_exact(oracle):
+    """minicv's cv::undistortPoints (the primitive inside Frame::UndistortKeyPoints, Frame.cc:766) == cv2 4.13.0, float bits."""
+    from orb_slam3_ros2_b200 import synth
+    g = load_golden("prim_undistort.npz")
+    for name, *_ in synth.UNDISTORT_CASES:
+        _, _, K, dist, pts = synth.undistort_case(name)
+        assert np.array_equal(pts, g[f"{name}__pts"]), name
+        got = oracle.undistort_points(pts, K, dist)
+        assert np.array_equal(got.view(np.uint32), g[f"{name}__out"].view(np.uint32)), name
+
+
 def test_knn_top2_order_matches_bfmatcher(oracle):
     g = load_golden("match.npz")
     i1, d1, i2, d2 = oracle.match_top2(g["q"], g["t"])

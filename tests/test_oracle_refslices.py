@@ -1,6 +1,6 @@
 """Pins oracle/match_oracle.cpp (the restatements the GPU parity tests compare against) to the reference's OWN function
-bodies: oracle/_ref/librefslices.so holds Frame::ComputeStereoMatches, AssignFeaturesToGrid, GetFeaturesInArea, PosInGrid
-and ORBmatcher::DescriptorDistance cut out of /root/reference/ORB_SLAM3/src/{Frame,ORBmatcher}.cc by oracle/Makefile and
+bodies: oracle/_ref/librefslices.so holds Frame::ComputeStereoMatches, AssignFeaturesToGrid, GetFeaturesInArea, PosInGrid,
+UndistortKeyPoints, ComputeImageBounds and ORBmatcher::DescriptorDistance cut out of /root/reference/ORB_SLAM3/src/{Frame,ORBmatcher}.cc by oracle/Makefile and
 compiled unchanged (built where /root/reference exists; the prebuilt library travels to the GPU box)."""
 import numpy as np
 import pytest
@@ -101,3 +101,37 @@ def test_search_by_bow_restatement_equals_reference_body(slices, seed, levelsup,
     n_got, m_got = slices.search_by_bow(*case, nnratio=nnratio, check_orientation=ori)
     assert n_got == n_ref and np.array_equal(m_got, m_ref)
     assert n_ref == int((m_ref >= 0).sum()) and n_ref > 50
+
+
+def undistort_keypoint_case(name):
+    """Keypoints with every field set (only pt may change) at the points of the undistortion case `name`."""
+    from orb_slam3_ros2_b200.orbx import KP_DTYPE
+    w, h, K, dist, pts = synth.undistort_case(name)
+    rng = np.random.default_rng(11)
+    kps = np.zeros(len(pts), dtype=KP_DTYPE)
+    kps["x"], kps["y"] = pts[:, 0], pts[:, 1]
+    kps["size"] = 31.0 * 1.2 ** rng.integers(0, 8, len(pts))
+    kps["angle"] = rng.random(len(pts)) * 360
+    kps["response"] = rng.integers(7, 120, len(pts))
+    kps["octave"] = rng.integers(0, 8, len(pts))
+    kps["class_id"] = -1
+    return w, h, K, dist, kps
+
+
+@pytest.mark.parametrize("name", [c[0] for c in synth.UNDISTORT_CASES])
+def test_undistort_keypoints_and_image_bounds_equal_reference_bodies(slices, name):
+    """Frame::UndistortKeyPoints / ComputeImageBounds: restatement == the reference's own bodies (Frame.cc:747-809), and the
+    undistorted coordinates == the cv2 golden (the un-vendored primitive inside)."""
+    import os
+    w, h, K, dist, kps = undistort_keypoint_case(name)
+    got = slices.undistort_keypoints(kps, K, dist)
+    want = slices.ref_undistort_keypoints(kps, K, dist)
+    assert got.tobytes() == want.tobytes()
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "prim_undistort.npz"))
+    if dist[0] != 0:
+        assert np.array_equal(np.stack([got["x"], got["y"]], 1).view(np.uint32), g[f"{name}__out"].view(np.uint32))
+    else:
+        assert got.tobytes() == kps.tobytes()  # Frame.cc:749-753
+    b_got, b_want = slices.image_bounds(w, h, K, dist), slices.ref_image_bounds(w, h, K, dist)
+    assert b_got.tobytes() == b_want.tobytes()
+    assert slices.undistort_keypoints(kps[:0], K, dist).size == 0

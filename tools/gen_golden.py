@@ -3,6 +3,7 @@
 
   prim_*.npz   outputs of cv2 (OpenCV 4.13.0, the declared oracle version) for the five
                un-vendored primitives on small inputs -> pins oracle/minicv
+  prim_undistort.npz  cv2.undistortPoints on the pinhole cases of synth.UNDISTORT_CASES -> pins minicv's undistortPoints
   match.npz    cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) on descriptor sets with planted ties
                -> pins the matcher oracle's (distance, index) order (reference: ORB_SLAM3/src/Frame.cc:1144)
   bow.npz      BowVector / FeatureVector from the reference's own DBoW2 (oracle/_ref/libbowref.so) on synthetic
@@ -189,6 +190,19 @@ def gen_e2e():
         print(name, "n =", len(rec["strict_kp"]), "mono =", rec["strict_mono"], "native_same =", rec.get("native_same", False))
 
 
+def gen_undistort():
+    """cv2.undistortPoints(pts, K, D, None, K) as Frame::UndistortKeyPoints / ComputeImageBounds call it (Frame.cc:766, :795)."""
+    import cv2
+    rec = {"cv2_version": cv2.__version__}
+    for name, *_ in synth.UNDISTORT_CASES:
+        w, h, K, dist, pts = synth.undistort_case(name)
+        out = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, dist.reshape(-1, 1), None, K).reshape(-1, 2)
+        rec[f"{name}__pts"] = pts
+        rec[f"{name}__out"] = out.astype(np.float32)
+        print(name, "max shift", float(np.abs(out - pts).max()))
+    np.savez_compressed(os.path.join(OUT, "prim_undistort.npz"), **rec)
+
+
 def gen_bow():
     """Frame::ComputeBoW: outputs of the reference's own DBoW2 (oracle/_ref/libbowref.so) on synthetic vocabularies."""
     import tempfile
@@ -222,7 +236,7 @@ def gen_bow():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    what = sys.argv[1:] or ["prim", "stage", "e2e", "bow"]
+    what = sys.argv[1:] or ["prim", "stage", "e2e", "bow", "undistort"]
     if "prim" in what:
         gen_primitives()
     if "stage" in what:
@@ -231,3 +245,5 @@ if __name__ == "__main__":
         gen_e2e()
     if "bow" in what:
         gen_bow()
+    if "undistort" in what:
+        gen_undistort()
