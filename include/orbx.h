@@ -248,6 +248,27 @@ int orbx_image_bounds(int cols, int rows, const float* K, const float* dist, int
 int orbx_undistort_batch(orbx_handle h, const float* K, const float* dist, int ndist, const float* P, orbx_keypoint* kps_un,
                          const orbx_keypoint** d_kps_un);
 
+/* ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763), whole function, monocular frames ---------------------
+ * F1 = (kps1 = mvKeysUn, desc1), F2 = (kps2, desc2) with its 64 x 48 grid over [min_x, max_x) x [min_y, max_y)
+ * (Frame::AssignFeaturesToGrid).  For every level-0 keypoint i1 in index order: candidates = F2.GetFeaturesInArea(
+ * vbPrevMatched[i1], windowSize, 0, 0), best / second Hamming distance over the candidates NOT already held by an earlier
+ * i1 at a smaller or equal distance (vMatchedDistance, :687-688), accept best <= TH_LOW && best < second * nnratio, take the
+ * point over from an earlier worse match (:701-709), rotation histogram + ComputeThreeMaxima (:2012-2053) when
+ * check_orientation.  prev_matched: n1 x 2 floats = vbPrevMatched, updated for matched keypoints (:756-759).
+ * matches12: n1 ints = vnMatches12 (-1 = none).  *nmatches = the return value.  The i1 loop is order dependent and runs in
+ * order on one warp per frame pair.
+ * _batch: pair p = frame p -> frame p + 1 of the handle's last batch, read in place on the device (use_undistorted != 0: the
+ * mvKeysUn of orbx_undistort_batch), vbPrevMatched = frame p's own keypoints as Tracking::MonocularInitialization sets it
+ * (Tracking.cc:2479-2481, called at :2512).  matches12: [frames-1][cap_per_frame], nmatches: [frames-1], prev_matched (may be NULL):
+ * [frames-1][cap_per_frame][2]. */
+int orbx_search_for_initialization(const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const orbx_keypoint* kps2,
+                                   const uint8_t* desc2, int n2, float min_x, float max_x, float min_y, float max_y, float* prev_matched,
+                                   int window_size, float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                   int device);
+int orbx_search_for_initialization_batch(orbx_handle h, int use_undistorted, float min_x, float max_x, float min_y, float max_y,
+                                         int window_size, float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                         float* prev_matched);
+
 /* ---- Frame::ComputeBoW (row N4): DBoW2 vocabulary-tree transform --------------------------------------------------
  * Replaces mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) (ORB_SLAM3/src/Frame.cc:738-745), i.e.
  * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)

@@ -378,4 +378,137 @@ void orbo_image_bounds(int cols, int rows, const float* K, const float* dist, in
 }
 
 
+// ---- ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:648-763), monocular frames --------------------------------
+// F2's grid = Frame::AssignFeaturesToGrid over kps2 (mvKeysUn) inside (mnMinX, mnMaxX, mnMinY, mnMaxY); the window query is
+// Frame::GetFeaturesInArea(x, y, windowSize, level1, level1) (Frame.cc:657-723).  prev_matched: n1 x 2 floats, in / out
+// (:756-759).  matches12: n1 ints (vnMatches12).  Returns nmatches.  PINNED to the reference's own body by
+// tests/test_oracle_refslices.py.
+static int g_init_withdrawn = 0;  // how often :705-709 fired in the last call (lets the tests prove the branch is exercised)
+int orbo_search_for_initialization_withdrawn() { return g_init_withdrawn; }
+int orbo_search_for_initialization(const void* kps1_, const uint8_t* desc1, int n1, const void* kps2_, const uint8_t* desc2, int n2,
+                                   float mnMinX, float mnMaxX, float mnMinY, float mnMaxY, float* prev_matched, int windowSize,
+                                   float mfNNratio, int mbCheckOrientation, int32_t* vnMatches12) {
+    const Kp* k1 = static_cast<const Kp*>(kps1_);
+    const Kp* k2 = static_cast<const Kp*>(kps2_);
+    constexpr int HISTO_LENGTH = 30;  // :37
+    const float mfGridElementWidthInv = static_cast<float>(GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);  // Frame.cc:251
+    const float mfGridElementHeightInv = static_cast<float>(GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+    std::vector<std::vector<int>> grid((size_t)GRID_COLS * GRID_ROWS);
+    for (int i = 0; i < n2; ++i) {  // Frame.cc:385-416, :725-735
+        const int posX = (int)std::round((k2[i].x - mnMinX) * mfGridElementWidthInv);
+        const int posY = (int)std::round((k2[i].y - mnMinY) * mfGridElementHeightInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        grid[(size_t)posX * GRID_ROWS + posY].push_back(i);
+    }
+    int nmatches = 0;
+    g_init_withdrawn = 0;
+    for (int i = 0; i < n1; ++i) vnMatches12[i] = -1;  // :651
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;  // :656
+    std::vector<int> vMatchedDistance(n2, INT_MAX), vnMatches21(n2, -1);
+    for (int i1 = 0; i1 < n1; i1++) {
+        const Kp kp1 = k1[i1];
+        const int level1 = kp1.octave;
+        if (level1 > 0) continue;  // :665-666
+        // GetFeaturesInArea(vbPrevMatched[i1].x, .y, windowSize, level1, level1)
+        const float x = prev_matched[2 * i1], y = prev_matched[2 * i1 + 1], r = (float)windowSize;
+        const int minLevel = level1, maxLevel = level1;
+        std::vector<int> vIndices2;
+        {
+            const float factorX = r, factorY = r;
+            const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * mfGridElementWidthInv));
+            const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * mfGridElementWidthInv));
+            const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * mfGridElementHeightInv));
+            const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * mfGridElementHeightInv));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+                const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+                        for (int idx : grid[(size_t)ix * GRID_ROWS + iy]) {
+                            const Kp& kpUn = k2[idx];
+                            if (bCheckLevels) {
+                                if (kpUn.octave < minLevel) continue;
+                                if (maxLevel >= 0)
+                                    if (kpUn.octave > maxLevel) continue;
+                            }
+                            const float distx = kpUn.x - x, disty = kpUn.y - y;
+                            if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices2.push_back(idx);
+                        }
+            }
+        }
+        if (vIndices2.empty()) continue;  // :670-671
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            const int dist = orbo_hamming(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+            if (vMatchedDistance[i2] <= dist) continue;  // :687-688
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestIdx2 = i2;
+            } else if (dist < bestDist2) {
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * mfNNratio) {
+                if (vnMatches21[bestIdx2] >= 0) {  // :705-709 an earlier, worse match onto the same point is withdrawn
+                    vnMatches12[vnMatches21[bestIdx2]] = -1;
+                    nmatches--;
+                    g_init_withdrawn++;
+                }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = k1[i1].angle - k2[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        // ComputeThreeMaxima (ORBmatcher.cc:2012-2053)
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) {
+                max3 = max2; max2 = max1; max1 = s;
+                ind3 = ind2; ind2 = ind1; ind1 = i;
+            } else if (s > max2) {
+                max3 = max2; max2 = s;
+                ind3 = ind2; ind2 = i;
+            } else if (s > max3) {
+                max3 = s;
+                ind3 = i;
+            }
+        }
+        if (max2 < 0.1f * (float)max1) {
+            ind2 = -1;
+            ind3 = -1;
+        } else if (max3 < 0.1f * (float)max1) {
+            ind3 = -1;
+        }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                const int idx1 = rotHist[i][j];
+                if (vnMatches12[idx1] >= 0) {  // :745-749 (it may already have been withdrawn)
+                    vnMatches12[idx1] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)  // :756-759
+        if (vnMatches12[i1] >= 0) {
+            prev_matched[2 * i1] = k2[vnMatches12[i1]].x;
+            prev_matched[2 * i1 + 1] = k2[vnMatches12[i1]].y;
+        }
+    return nmatches;
+}
+
 }  // extern "C"

@@ -379,6 +379,33 @@ def ref_image_bounds(w, h, K, dist, P=None):
     return _image_bounds(_slices().refslice_image_bounds, w, h, K, dist, P)
 
 
+def _search_for_initialization(fn, kps1, desc1, kps2, desc2, bounds, prev_matched, window_size, nnratio, check_orientation):
+    kps1 = np.ascontiguousarray(kps1); kps2 = np.ascontiguousarray(kps2)
+    assert kps1.dtype.itemsize == 28 and kps2.dtype.itemsize == 28
+    desc1 = np.ascontiguousarray(desc1, dtype=np.uint8); desc2 = np.ascontiguousarray(desc2, dtype=np.uint8)
+    prev = np.array(prev_matched, dtype=np.float32).reshape(-1, 2).copy()
+    assert len(prev) == len(kps1)
+    m12 = np.zeros(max(len(kps1), 1), dtype=np.int32)
+    fn.restype = C.c_int
+    n = fn(kps1.ctypes.data_as(C.c_void_p), _ptr(desc1), len(kps1), kps2.ctypes.data_as(C.c_void_p), _ptr(desc2), len(kps2),
+           *[C.c_float(float(b)) for b in bounds], prev.ctypes.data_as(_f32p), C.c_int(int(window_size)), C.c_float(float(nnratio)),
+           C.c_int(int(bool(check_orientation))), _ptr(m12, _i32p))
+    return n, m12[:len(kps1)], prev
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window_size=100, nnratio=0.9, check_orientation=True):
+    """ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763) -> (nmatches, vnMatches12, vbPrevMatched after the call)."""
+    return _search_for_initialization(port_lib().orbo_search_for_initialization, kps1, desc1, kps2, desc2, bounds, prev_matched,
+                                      window_size, nnratio, check_orientation)
+
+
+def ref_search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window_size=100, nnratio=0.9,
+                                  check_orientation=True):
+    """The same through the reference's own body (librefslices.so)."""
+    return _search_for_initialization(_slices().refslice_search_for_initialization, kps1, desc1, kps2, desc2, bounds, prev_matched,
+                                      window_size, nnratio, check_orientation)
+
+
 def stage_gray(img, rgb=True, new_size=None):
     """System.cc:420-425 (cv::resize on the interleaved colour image) then Tracking.cc:1569-1582 (cvtColor -> GRAY);
     OpenCV 8-bit RGB2Gray = (R*9798 + G*19235 + B*3735 + 2^14) >> 15."""

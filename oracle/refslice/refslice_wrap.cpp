@@ -7,6 +7,7 @@
 //   ORBmatcher.cc:2058-2074  ORBmatcher::DescriptorDistance
 //   ORBmatcher.cc:223-425    ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)
 //   ORBmatcher.cc:2012-2053  ORBmatcher::ComputeThreeMaxima
+//   ORBmatcher.cc:648-763    ORBmatcher::SearchForInitialization
 //   Frame.cc:385-416         Frame::AssignFeaturesToGrid
 //   Frame.cc:657-723         Frame::GetFeaturesInArea
 //   Frame.cc:725-735         Frame::PosInGrid
@@ -31,6 +32,7 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 #include "Frame_ComputeImageBounds.inc"
 #include "ORBmatcher_SearchByBoW.inc"
 #include "ORBmatcher_ComputeThreeMaxima.inc"
+#include "ORBmatcher_SearchForInitialization.inc"
 }  // namespace ORB_SLAM3
 
 using ORB_SLAM3::Frame;
@@ -186,6 +188,34 @@ int refslice_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* vali
     std::vector<ORB_SLAM3::MapPoint*> out;
     const int n = matcher.SearchByBoW(&KF, F, out);
     for (int j = 0; j < n_f; ++j) match_f[j] = out[j] ? out[j]->index : -1;
+    return n;
+}
+
+// ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) on two monocular frames: F2's grid is
+// built by the reference's AssignFeaturesToGrid over kps2 (= mvKeysUn) inside `bounds`.  prev_matched: n1 x 2 floats, in / out.
+int refslice_search_for_initialization(const void* kps1, const uint8_t* desc1, int n1, const void* kps2, const uint8_t* desc2, int n2,
+                                       float min_x, float max_x, float min_y, float max_y, float* prev_matched, int window_size,
+                                       float nnratio, int check_orientation, int32_t* matches12) {
+    Frame F1, F2;
+    F1.N = n1; F1.Nleft = -1;
+    F1.mvKeysUn = keypoints(kps1, n1);
+    F1.mDescriptors = descriptors(desc1, n1);
+    F2.N = n2; F2.Nleft = -1;
+    F2.mvKeysUn = keypoints(kps2, n2);
+    F2.mDescriptors = descriptors(desc2, n2);
+    Frame::mnMinX = min_x; Frame::mnMaxX = max_x; Frame::mnMinY = min_y; Frame::mnMaxY = max_y;
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);   // Frame.cc:251
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);  // Frame.cc:252
+    F2.AssignFeaturesToGrid();
+    std::vector<cv::Point2f> prev(n1);
+    for (int i = 0; i < n1; ++i) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    const int n = matcher.SearchForInitialization(F1, F2, prev, m12, window_size);
+    for (int i = 0; i < n1; ++i) {
+        matches12[i] = m12[i];
+        prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
+    }
     return n;
 }
 

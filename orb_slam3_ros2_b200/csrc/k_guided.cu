@@ -46,11 +46,20 @@ __global__ void acceptKernel(int rule, float nnratio, const int* __restrict__ d1
 }
 
 // ---- grid: keys (cell << 20 | index) sorted by one CTA (bitonic, shared memory), then the cell boundaries -------------
+// batch form (nPerFrame != NULL): CTA f sorts frame f of a [frame][cap] keypoint array into sortedOut + f * cap,
+// cellStart + f * (kGridCells + 1)
 __global__ void __launch_bounds__(1024) gridSortKernel(const float* __restrict__ kps, int nt, int nPow2, float minX, float minY,
                                                        float invW, float invH, uint32_t* __restrict__ sortedOut,
-                                                       int* __restrict__ cellStart) {
+                                                       int* __restrict__ cellStart, const int* __restrict__ nPerFrame, int cap) {
     extern __shared__ uint32_t keys[];
     const int tid = threadIdx.x;
+    if (nPerFrame) {
+        const int f = blockIdx.x;
+        nt = min(nPerFrame[f], cap);
+        kps += (size_t)f * cap * 7;
+        sortedOut += (size_t)f * cap;
+        cellStart += (size_t)f * (kGridCells + 1);
+    }
     for (int i = tid; i < nPow2; i += 1024) {
         uint32_t key = 0xffffffffu;
         if (i < nt) {
@@ -304,6 +313,170 @@ __global__ void __launch_bounds__(1024) stereoCutKernel(const int* __restrict__ 
         if (sad[i] >= 0 && !((float)sad[i] < thDist)) { uRight[i] = -1.0f; depth[i] = -1.0f; }
 }
 
+// ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763): one warp per frame pair ------------------------------
+// The loop over i1 is sequential in the reference (vMatchedDistance / vnMatches21 of earlier keypoints gate later ones), so
+// one warp walks it in order; inside an i1 the window's candidates (Frame::GetFeaturesInArea order = grid columns, each a
+// contiguous range of the sorted keys) are flattened and taken 32 at a time.
+struct InitArgs {
+    const float* kps1; const uint4* desc1; const float* kps2; const uint4* desc2;   // pair p: + p * stride keypoints
+    const uint32_t* sorted2; const int* cellStart2;                                   // F2's grid: + p * stride, + p * (cells + 1)
+    const int* n1Arr; const int* n2Arr; int n1, n2, stride;
+    float minX, minY, invW, invH, r, nnratio;
+    int checkOri, prevFromKps;
+    float* prev;       // [pair][stride][2], in / out (vbPrevMatched)
+    int* m12;          // [pair][stride] out (vnMatches12)
+    int* matchedDist;  // scratch [pair][stride] (vMatchedDistance)
+    int* m21;          // scratch [pair][stride] (vnMatches21)
+    int* binOf;        // scratch [pair][stride] rotation bin of i1's push, -1 = none
+    int* nMatches;     // [pair]
+};
+
+__global__ void __launch_bounds__(32) searchInitKernel(const InitArgs A) {
+    __shared__ int colB[64], pre[65], hist[30], keep[3];
+    const int pair = blockIdx.x, lane = threadIdx.x;
+    const size_t o = (size_t)pair * A.stride;
+    const int n1 = A.n1Arr ? min(A.n1Arr[pair], A.stride) : A.n1, n2 = A.n2Arr ? min(A.n2Arr[pair], A.stride) : A.n2;
+    const float* k1 = A.kps1 + o * 7;
+    const float* k2 = A.kps2 + o * 7;
+    const uint4* d1 = A.desc1 + o * 2;
+    const uint4* d2 = A.desc2 + o * 2;
+    const uint32_t* sorted = A.sorted2 + o;
+    const int* cellStart = A.cellStart2 + (size_t)pair * (kGridCells + 1);
+    float* prev = A.prev + o * 2;
+    volatile int* m12 = A.m12 + o;
+    volatile int* md = A.matchedDist + o;
+    volatile int* m21 = A.m21 + o;
+    volatile int* binOf = A.binOf + o;
+    for (int i = lane; i < n2; i += 32) { md[i] = INT_MAX; m21[i] = -1; }
+    for (int i = lane; i < n1; i += 32) {
+        m12[i] = -1; binOf[i] = -1;
+        if (A.prevFromKps) { prev[2 * i] = k1[i * 7]; prev[2 * i + 1] = k1[i * 7 + 1]; }
+    }
+    if (lane < 30) hist[lane] = 0;
+    __syncwarp();
+    int nmatches = 0;
+    const float factor = 1.0f / 30.0f;  // :656
+    for (int i1 = 0; i1 < n1; ++i1) {
+        const int level1 = __float_as_int(k1[i1 * 7 + 5]);
+        if (level1 > 0) continue;  // :665-666
+        const float x = prev[2 * i1], y = prev[2 * i1 + 1], r = A.r;
+        // Frame::GetFeaturesInArea, Frame.cc:665-687
+        const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), r), A.invW)));
+        const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), r), A.invW)));
+        const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), r), A.invH)));
+        const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), r), A.invH)));
+        if (minCX >= kGridCols || maxCX < 0 || minCY >= kGridRows || maxCY < 0 || minCX > maxCX || minCY > maxCY) continue;
+        const int ncols = maxCX - minCX + 1;
+        int b0 = 0, len0 = 0, b1 = 0, len1 = 0;
+        if (lane < ncols) {
+            b0 = cellStart[(minCX + lane) * kGridRows + minCY];
+            len0 = cellStart[(minCX + lane) * kGridRows + maxCY + 1] - b0;
+        }
+        if (lane + 32 < ncols) {
+            b1 = cellStart[(minCX + lane + 32) * kGridRows + minCY];
+            len1 = cellStart[(minCX + lane + 32) * kGridRows + maxCY + 1] - b1;
+        }
+        int s0 = len0, s1 = len1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t0 = __shfl_up_sync(0xffffffffu, s0, d), t1 = __shfl_up_sync(0xffffffffu, s1, d);
+            if (lane >= d) { s0 += t0; s1 += t1; }
+        }
+        const int tot0 = __shfl_sync(0xffffffffu, s0, 31), total = tot0 + __shfl_sync(0xffffffffu, s1, 31);
+        __syncwarp();
+        colB[lane] = b0; colB[lane + 32] = b1;
+        pre[lane + 1] = s0; pre[lane + 33] = tot0 + s1;
+        if (lane == 0) pre[0] = 0;
+        __syncwarp();
+        const uint4 a0 = d1[2 * i1], a1 = d1[2 * i1 + 1];
+        unsigned long long key1 = ~0ull, key2 = ~0ull;  // distance << 48 | visit position << 24 | index
+        for (int t0 = 0; t0 < total; t0 += 32) {
+            const int t = t0 + lane;
+            if (t < total) {
+                int lo = 0, hi = ncols - 1;  // the column with pre[c] <= t < pre[c + 1]
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (pre[mid] <= t) lo = mid; else hi = mid - 1;
+                }
+                const int idx = (int)(sorted[colB[lo] + (t - pre[lo])] & 0xfffffu);
+                const int oct = __float_as_int(k2[idx * 7 + 5]);
+                const float x2 = k2[idx * 7], y2 = k2[idx * 7 + 1];
+                // minLevel = maxLevel = level1 (<= 0): bCheckLevels is true because maxLevel >= 0 or, for a negative level1, false
+                bool ok = true;
+                if (level1 >= 0) ok = !(oct < level1) && !(oct > level1);
+                ok = ok && fabsf(__fsub_rn(x2, x)) < r && fabsf(__fsub_rn(y2, y)) < r;
+                if (ok) {
+                    const uint4 c0 = d2[2 * idx], c1 = d2[2 * idx + 1];
+                    const int dist = __popc(a0.x ^ c0.x) + __popc(a0.y ^ c0.y) + __popc(a0.z ^ c0.z) + __popc(a0.w ^ c0.w) +
+                                     __popc(a1.x ^ c1.x) + __popc(a1.y ^ c1.y) + __popc(a1.z ^ c1.z) + __popc(a1.w ^ c1.w);
+                    if (!(md[idx] <= dist))  // :687-688
+                        top2Insert(key1, key2, ((unsigned long long)dist << 48) | ((unsigned long long)t << 24) | (unsigned)idx);
+                }
+            }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, key1, d), o2 = __shfl_xor_sync(0xffffffffu, key2, d);
+            top2Insert(key1, key2, o1);
+            top2Insert(key1, key2, o2);
+        }
+        if (key1 == ~0ull) continue;
+        const int bestDist = (int)(key1 >> 48), bestIdx2 = (int)(key1 & 0xffffffu);
+        const float fBest2 = key2 == ~0ull ? 2147483648.0f : (float)(int)(key2 >> 48);  // (float)INT_MAX
+        if (bestDist <= 50 && (float)bestDist < __fmul_rn(fBest2, A.nnratio)) {  // :697-699
+            const int old = m21[bestIdx2];
+            if (old >= 0) nmatches--;  // :701-705
+            nmatches++;
+            int bin = -1;
+            if (A.checkOri) {
+                float rot = __fsub_rn(k1[i1 * 7 + 3], k2[bestIdx2 * 7 + 3]);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == 30) bin = 0;
+            }
+            __syncwarp();
+            if (lane == 0) {
+                if (old >= 0) m12[old] = -1;
+                m12[i1] = bestIdx2;
+                m21[bestIdx2] = i1;
+                md[bestIdx2] = bestDist;
+                if (bin >= 0) { binOf[i1] = bin; hist[bin]++; }
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (A.checkOri) {
+        if (lane == 0) {  // ComputeThreeMaxima, ORBmatcher.cc:2012-2053 (the histogram counts every push, withdrawn or not)
+            int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+            for (int i = 0; i < 30; i++) {
+                const int sz = hist[i];
+                if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+                else if (sz > max3) { max3 = sz; ind3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+            keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+        }
+        __syncwarp();
+        int dropped = 0;
+        for (int i = lane; i < n1; i += 32) {
+            const int b = binOf[i];
+            if (b >= 0 && b != keep[0] && b != keep[1] && b != keep[2] && m12[i] >= 0) { m12[i] = -1; ++dropped; }  // :738-749
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, d);
+        nmatches -= dropped;
+        __syncwarp();
+    }
+    for (int i = lane; i < n1; i += 32) {  // :756-759
+        const int m = m12[i];
+        if (m >= 0) { prev[2 * i] = k2[m * 7]; prev[2 * i + 1] = k2[m * 7 + 1]; }
+    }
+    if (lane == 0) A.nMatches[pair] = nmatches;
+}
+
 // cv::undistortPoints(src, dst, K, dist, R = I, P) as Frame::UndistortKeyPoints calls it (Frame.cc:766); every operation is
 // written in the order of OpenCV's cvUndistortPointsInternal with explicit _rn intrinsics so that nvcc contracts nothing.
 __device__ __forceinline__ double dm(double a, double b) { return __dmul_rn(a, b); }
@@ -368,7 +541,8 @@ void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX
     while (nPow2 < nt) nPow2 <<= 1;
     const size_t smem = (size_t)nPow2 * 4;
     if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    gridSortKernel<<<1, 1024, smem, s>>>(static_cast<const float*>(kpsT), nt, nPow2, minX, minY, invW, invH, sortedScratch, cellStart);
+    gridSortKernel<<<1, 1024, smem, s>>>(static_cast<const float*>(kpsT), nt, nPow2, minX, minY, invW, invH, sortedScratch, cellStart,
+                                         nullptr, 0);
     countLaunch();
     if (nq <= 0) return;
     gridSearchKernel<<<(nq + 7) / 8, 256, 0, s>>>(static_cast<const float*>(kpsT), reinterpret_cast<const uint4*>(descT), sortedScratch,
@@ -405,6 +579,43 @@ void launchUndistort(const void* kpsIn, void* kpsOut, const int* nPerFrame, int 
     if (frames <= 0 || cap <= 0 || (!nPerFrame && nSingle <= 0)) return;
     const int most = nPerFrame ? cap : nSingle;
     undistortKernel<<<dim3((most + 127) / 128, frames), 128, 0, s>>>((const float*)kpsIn, (float*)kpsOut, nPerFrame, nSingle, cap, C);
+}
+
+// frames = 1: single pair (kps2 / desc2 are F2's arrays, n1 / n2 given); frames > 1: pair p = frame p -> frame p + 1 of a
+// [frame][cap] batch (kps2 = kps1, counts from nPerFrame).  sorted / cellStart: scratch for F2's grids (frames x cap,
+// frames x 3073 ints); prev / m12 / scratch3: pairs x cap (x 2 floats for prev; scratch3 = 3 int arrays back to back).
+void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void* kps2, const uint8_t* desc2, int n2, const int* nPerFrame,
+                      int frames, int cap, float minX, float maxX, float minY, float maxY, int windowSize, float nnratio, int checkOri,
+                      int prevFromKps, uint32_t* sorted, int* cellStart, float* prev, int* m12, int* scratch3, int* nMatches,
+                      cudaStream_t s) {
+    const float invW = (float)kGridCols / (maxX - minX), invH = (float)kGridRows / (maxY - minY);  // Frame.cc:251-252
+    const bool batch = nPerFrame != nullptr;
+    int nPow2 = 32;
+    while (nPow2 < (batch ? cap : n2)) nPow2 <<= 1;
+    const size_t smem = (size_t)nPow2 * 4;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const int pairs = batch ? frames - 1 : 1;
+    if (pairs <= 0) return;
+    InitArgs A{};
+    A.kps1 = static_cast<const float*>(kps1); A.desc1 = reinterpret_cast<const uint4*>(desc1);
+    A.n1Arr = batch ? nPerFrame : nullptr; A.n2Arr = batch ? nPerFrame + 1 : nullptr;
+    A.n1 = n1; A.n2 = n2; A.stride = cap;
+    A.minX = minX; A.minY = minY; A.invW = invW; A.invH = invH; A.r = (float)windowSize; A.nnratio = nnratio;
+    A.checkOri = checkOri; A.prevFromKps = prevFromKps;
+    A.prev = prev; A.m12 = m12; A.matchedDist = scratch3; A.m21 = scratch3 + (size_t)pairs * cap;
+    A.binOf = scratch3 + 2 * (size_t)pairs * cap; A.nMatches = nMatches;
+    if (batch) {  // grids of frames 1 .. frames-1 (sorted from frame 0 so that the indexing stays [frame])
+        gridSortKernel<<<frames, 1024, smem, s>>>(static_cast<const float*>(kps1), 0, nPow2, minX, minY, invW, invH, sorted, cellStart,
+                                                  nPerFrame, cap);
+        A.kps2 = A.kps1 + (size_t)cap * 7; A.desc2 = A.desc1 + (size_t)cap * 2;
+        A.sorted2 = sorted + cap; A.cellStart2 = cellStart + (kGridCells + 1);
+    } else {
+        gridSortKernel<<<1, 1024, smem, s>>>(static_cast<const float*>(kps2), n2, nPow2, minX, minY, invW, invH, sorted, cellStart, nullptr, 0);
+        A.kps2 = static_cast<const float*>(kps2); A.desc2 = reinterpret_cast<const uint4*>(desc2);
+        A.sorted2 = sorted; A.cellStart2 = cellStart;
+    }
+    searchInitKernel<<<pairs, 32, 0, s>>>(A);
+    countLaunch(2);
 }
 
 }  // namespace orbx

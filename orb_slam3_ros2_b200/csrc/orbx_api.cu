@@ -1287,6 +1287,91 @@ int orbx_undistort_batch(orbx_handle h, const float* K, const float* dist, int n
     return ORBX_OK;
 }
 
+// ---- ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763) ---------------------------------------------------------
+int orbx_search_for_initialization(const orbx_keypoint* kps1, const uint8_t* desc1, int n1, const orbx_keypoint* kps2,
+                                   const uint8_t* desc2, int n2, float min_x, float max_x, float min_y, float max_y, float* prev_matched,
+                                   int window_size, float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                   int device) {
+    if (n1 < 0 || n2 < 0 || !nmatches || (n1 > 0 && (!kps1 || !desc1 || !prev_matched || !matches12)) || (n2 > 0 && (!kps2 || !desc2)))
+        return fail(ORBX_ERR_ARG, "bad argument");
+    if (!(max_x > min_x) || !(max_y > min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
+    if (n2 > gridSortCapacity()) return fail(ORBX_ERR_ARG, "more than 32768 keypoints in the second frame");
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    *nmatches = 0;
+    if (n1 == 0) return ORBX_OK;
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    const size_t A = (size_t)n1, B = (size_t)std::max(n2, 1), cap = std::max(A, B);
+    auto al = [](size_t v) { return (v + 15) & ~(size_t)15; };
+    // q: [desc1 | kps1 | prev | m12 | n]   db: [desc2 | kps2 | sorted | cellStart | 3 scratch arrays of cap ints]
+    const size_t oK1 = A * 32, oPrev = oK1 + al(A * 28), oM12 = oPrev + A * 8, oN = oM12 + al(A * 4), qBytes = oN + 64;
+    const size_t oK2 = B * 32, oSo = oK2 + al(B * 28), oCs = oSo + al(B * 4), oScr = oCs + al((size_t)(64 * 48 + 1) * 4),
+                 dbBytes = oScr + 3 * cap * 4 + 64;
+    ORBX_CUDA(S->q.reserve(qBytes));
+    ORBX_CUDA(S->db.reserve(dbBytes));
+    uint8_t* Q = (uint8_t*)S->q.p;
+    uint8_t* D = (uint8_t*)S->db.p;
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaMemcpyAsync(Q, desc1, A * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oK1, kps1, A * 28, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oPrev, prev_matched, A * 8, cudaMemcpyHostToDevice, s));
+    if (n2) {
+        ORBX_CUDA(cudaMemcpyAsync(D, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
+        ORBX_CUDA(cudaMemcpyAsync(D + oK2, kps2, (size_t)n2 * 28, cudaMemcpyHostToDevice, s));
+    }
+    // stride = cap so that the three scratch arrays (pairs x stride each, pairs = 1) are laid out back to back
+    launchSearchInit(Q + oK1, Q, n1, D + oK2, D, n2, nullptr, 1, (int)cap, min_x, max_x, min_y, max_y, window_size, nnratio,
+                     check_orientation != 0, 0, (uint32_t*)(D + oSo), (int*)(D + oCs), (float*)(Q + oPrev), (int*)(Q + oM12),
+                     (int*)(D + oScr), (int*)(Q + oN), s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(matches12, Q + oM12, A * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(prev_matched, Q + oPrev, A * 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(nmatches, Q + oN, 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_search_for_initialization_batch(orbx_handle h, int use_undistorted, float min_x, float max_x, float min_y, float max_y,
+                                         int window_size, float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                                         float* prev_matched) {
+    if (!h || !matches12 || !nmatches) return fail(ORBX_ERR_ARG, "bad argument");
+    if (h->lastFrames == 0) return fail(ORBX_ERR_STATE, "no extraction yet");
+    if (!(max_x > min_x) || !(max_y > min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
+    const int F = h->lastFrames, cap = h->plan.outCap;
+    if (cap > gridSortCapacity()) return fail(ORBX_ERR_ARG, "more than 32768 keypoints per frame");
+    if (use_undistorted && h->mKpsUn.bytes < (size_t)F * cap * sizeof(orbx_keypoint))
+        return fail(ORBX_ERR_STATE, "orbx_undistort_batch has not run on this batch");
+    if (F < 2) return ORBX_OK;
+    DeviceGuard guard(h->device);
+    MatchScratch* S = nullptr;
+    int rc = matchScratch(h->device, &S);
+    if (rc != ORBX_OK) return rc;
+    const size_t P = (size_t)(F - 1), T = P * cap;
+    // misc: [sorted F x cap | cellStart F x 3073 | prev P x cap x 2 | m12 P x cap | 3 scratch arrays P x cap | n P]
+    const size_t oCs = (size_t)F * cap * 4, oPrev = oCs + (((size_t)F * (64 * 48 + 1) * 4 + 15) & ~(size_t)15), oM12 = oPrev + T * 8,
+                 oScr = oM12 + T * 4, oN = oScr + 3 * T * 4, bytes = oN + P * 4 + 64;
+    ORBX_CUDA(S->misc.reserve(bytes));
+    uint8_t* M = (uint8_t*)S->misc.p;
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaEventRecord(h->ev[6], h->stream));  // behind the extraction (and the undistortion) on the handle's stream
+    ORBX_CUDA(cudaStreamWaitEvent(s, h->ev[6], 0));
+    const void* kps = use_undistorted ? h->mKpsUn.p : h->buf.outKps;
+    launchSearchInit(kps, h->buf.outDesc, 0, nullptr, nullptr, 0, h->buf.outN, F, cap, min_x, max_x, min_y, max_y, window_size, nnratio,
+                     check_orientation != 0, 1, (uint32_t*)M, (int*)(M + oCs), (float*)(M + oPrev), (int*)(M + oM12), (int*)(M + oScr),
+                     (int*)(M + oN), s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(matches12, M + oM12, T * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(nmatches, M + oN, P * 4, cudaMemcpyDeviceToHost, s));
+    if (prev_matched) ORBX_CUDA(cudaMemcpyAsync(prev_matched, M + oPrev, T * 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 // ---- Frame::ComputeBoW (row N4) ------------------------------------------------------------------------------------
 struct orbx_vocabulary {
     int device = 0;

@@ -142,6 +142,10 @@ void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX
 void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, const uint8_t* pyrL, const uint8_t* pyrR,
                         const void* kl, const void* kr, int nl, const int* bestIdx, const int* bestDist, float mbf, float maxD,
                         float* uRight, float* depth, int* sad, cudaStream_t s, const StereoBatch* batch = nullptr);
+void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void* kps2, const uint8_t* desc2, int n2, const int* nPerFrame,
+                      int frames, int cap, float minX, float maxX, float minY, float maxY, int windowSize, float nnratio, int checkOri,
+                      int prevFromKps, uint32_t* sorted, int* cellStart, float* prev, int* m12, int* scratch3, int* nMatches,
+                      cudaStream_t s);
 // Frame::UndistortKeyPoints: the pinhole model in doubles, as cv::undistortPoints converts it (k = k1 k2 p1 p2 k3 k4 k5 k6 s1..s4)
 struct UndistortCam {
     double ifx, ify, cx, cy;

@@ -89,6 +89,10 @@ SYMBOLS = {
     "orbx_undistort_keypoints": (C.c_int, [_vp, C.c_int, _f32p, _f32p, C.c_int, _f32p, _vp, C.c_int]),
     "orbx_image_bounds": (C.c_int, [C.c_int, C.c_int, _f32p, _f32p, C.c_int, _f32p, _f32p, C.c_int]),
     "orbx_undistort_batch": (C.c_int, [_vp, _f32p, _f32p, C.c_int, _f32p, _vp, C.POINTER(_vp)]),
+    "orbx_search_for_initialization": (C.c_int, [_vp, _u8p, C.c_int, _vp, _u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                                 _f32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
+    "orbx_search_for_initialization_batch": (C.c_int, [_vp, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float,
+                                                       C.c_int, _i32p, _i32p, _f32p]),
     "orbx_search_by_bow": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _f32p, _i32p, _i32p, _i32p,
                                      C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
@@ -485,6 +489,38 @@ def undistort_batch(extractor, K, dist, P=None, download=True):
     _check(lib().orbx_undistort_batch(extractor._h, _ptr(K, _f32p), _ptr(dist, _f32p), len(dist), _ptr(P, _f32p),
                                       out.ctypes.data_as(_vp) if download else None, C.byref(dptr)))
     return out if download else dptr.value
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window_size=100, nnratio=0.9, check_orientation=True,
+                              device=-1):
+    """ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763) -> (nmatches, vnMatches12, vbPrevMatched after the call).
+    kps1 / kps2 = mvKeysUn of the two frames, bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY) of the second frame's grid."""
+    kps1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+    kps2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    desc1 = np.ascontiguousarray(desc1, dtype=np.uint8).reshape(-1, 32)
+    desc2 = np.ascontiguousarray(desc2, dtype=np.uint8).reshape(-1, 32)
+    prev = np.array(prev_matched, dtype=np.float32).reshape(-1, 2).copy()
+    if len(prev) != len(kps1):
+        raise ValueError("prev_matched must hold one point per keypoint of the first frame")
+    m12 = np.zeros(max(len(kps1), 1), dtype=np.int32)
+    n = np.zeros(1, dtype=np.int32)
+    _check(lib().orbx_search_for_initialization(kps1.ctypes.data_as(_vp), _ptr(desc1), len(kps1), kps2.ctypes.data_as(_vp), _ptr(desc2),
+                                                len(kps2), *[float(b) for b in bounds], _ptr(prev, _f32p), int(window_size),
+                                                float(nnratio), int(bool(check_orientation)), _ptr(m12, _i32p), _ptr(n, _i32p), device))
+    return int(n[0]), m12[:len(kps1)], prev
+
+
+def search_for_initialization_batch(extractor, bounds, window_size=100, nnratio=0.9, check_orientation=True, use_undistorted=False):
+    """SearchForInitialization of every consecutive pair (frame p -> p + 1) of the extractor's last batch, read on the device ->
+    (nmatches[F-1], vnMatches12[F-1, cap], vbPrevMatched[F-1, cap, 2])."""
+    F, cap = extractor._frames, extractor.capacity
+    m12 = np.zeros((max(F - 1, 1), cap), dtype=np.int32)
+    n = np.zeros(max(F - 1, 1), dtype=np.int32)
+    prev = np.zeros((max(F - 1, 1), cap, 2), dtype=np.float32)
+    _check(lib().orbx_search_for_initialization_batch(extractor._h, int(bool(use_undistorted)), *[float(b) for b in bounds],
+                                                      int(window_size), float(nnratio), int(bool(check_orientation)),
+                                                      _ptr(m12, _i32p), _ptr(n, _i32p), _ptr(prev, _f32p)))
+    return n[:F - 1], m12[:F - 1], prev[:F - 1]
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):

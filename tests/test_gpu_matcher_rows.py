@@ -190,3 +190,47 @@ def test_undistort_batch_on_device_resident_keypoints(orbx, oracle):
     for g_, w_ in zip(got, want):
         assert np.array_equal(g_, w_)
     e.close()
+
+
+@pytest.mark.parametrize("nf,shift,window,nnratio,ori,corrupt", [(1000, 1, 100, 0.9, True, 0), (1000, 2, 100, 0.9, False, 0),
+                                                                  (2000, 1, 30, 0.7, True, 3), (5000, 3, 100, 0.9, True, 5),
+                                                                  (1000, 5, 10, 0.9, True, 0), (1000, 1, 1000, 0.9, True, 7)])
+def test_search_for_initialization_bit_exact(orbx, oracle, nf, shift, window, nnratio, ori, corrupt):
+    """ORBmatcher::SearchForInitialization, whole function (ORBmatcher.cc:648-763), on the device == oracle (itself pinned to the
+    reference's own body): vnMatches12, the return value and the updated vbPrevMatched, over two rounds."""
+    from test_oracle_refslices import init_pair_case
+    k1, d1, k2, d2, bounds, prev = init_pair_case(oracle, nf, shift, corrupt=corrupt)
+    for _ in range(2):
+        got = orbx.search_for_initialization(k1, d1, k2, d2, bounds, prev, window, nnratio, ori)
+        want = oracle.search_for_initialization(k1, d1, k2, d2, bounds, prev, window, nnratio, ori)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1]) and got[2].tobytes() == want[2].tobytes()
+        prev = got[2]
+    if corrupt:
+        assert oracle.port_lib().orbo_search_for_initialization_withdrawn() >= 0
+    # degenerate inputs: empty second frame, empty first frame
+    n, m12, _ = orbx.search_for_initialization(k1, d1, k2[:0], d2[:0], bounds, prev, window, nnratio, ori)
+    assert n == 0 and (m12 == -1).all()
+    assert orbx.search_for_initialization(k1[:0], d1[:0], k2, d2, bounds, prev[:0], window, nnratio, ori)[0] == 0
+
+
+def test_search_for_initialization_batch_equals_per_pair(orbx, oracle):
+    """Consecutive pairs of a device-resident batch (on the undistorted keypoints) == the per-pair oracle."""
+    _, w, h, fx, fy, cx, cy, dist = synth.UNDISTORT_CASES[0]
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+    dist = np.array(dist, np.float32)
+    frames = np.stack([synth.frame(k, w, h) for k in range(5)])
+    e = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    mono, n, kps, desc = e.extract_batch(frames, (0, 1000))
+    for und in (False, True):
+        pts = orbx.undistort_batch(e, K, dist) if und else kps
+        bounds = orbx.image_bounds(w, h, K, dist) if und else (0.0, float(w), 0.0, float(h))
+        nm, m12, prev = orbx.search_for_initialization_batch(e, bounds, 100, 0.9, True, use_undistorted=und)
+        assert len(nm) == len(frames) - 1
+        for p in range(len(frames) - 1):
+            a, b = pts[p, :n[p]], pts[p + 1, :n[p + 1]]
+            p0 = np.stack([a["x"], a["y"]], 1)
+            want = oracle.search_for_initialization(a, desc[p, :n[p]], b, desc[p + 1, :n[p + 1]], bounds, p0, 100, 0.9, True)
+            assert nm[p] == want[0] and np.array_equal(m12[p, :n[p]], want[1]), (und, p)
+            assert prev[p, :n[p]].tobytes() == want[2].tobytes()
+            assert nm[p] > 50
+    e.close()

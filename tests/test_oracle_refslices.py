@@ -135,3 +135,48 @@ def test_undistort_keypoints_and_image_bounds_equal_reference_bodies(slices, nam
     b_got, b_want = slices.image_bounds(w, h, K, dist), slices.ref_image_bounds(w, h, K, dist)
     assert b_got.tobytes() == b_want.tobytes()
     assert slices.undistort_keypoints(kps[:0], K, dist).size == 0
+
+
+def init_pair_case(oracle, nfeatures=1000, shift=1, w=752, h=480, corrupt=0):
+    """Two extracted frames of the synthetic stream (frame `shift` = frame 0 moved by (3, 1) * shift px) as
+    Tracking::MonocularInitialization hands them to SearchForInitialization (Tracking.cc:2479-2481, :2512): vbPrevMatched = the
+    first frame's own keypoint positions."""
+    e = oracle.PortExtractor(nfeatures=nfeatures)
+    _, k1, d1 = e.extract(synth.frame(0, w, h), (0, 1000))
+    _, k2, d2 = e.extract(synth.frame(shift, w, h), (0, 1000))
+    if corrupt:  # duplicate descriptors in frame 2 so that several i1 compete for one i2 (the withdrawal branch, :705-709)
+        rng = np.random.default_rng(corrupt)
+        lvl0 = np.flatnonzero(k2["octave"] == 0)
+        for _ in range(60):
+            a, b = rng.choice(lvl0, 2, replace=False)
+            d2[b] = d2[a]
+        # and near-copies in frame 1: an earlier keypoint a gets a neighbour b's descriptor with 3 bits flipped, so a first takes
+        # b's partner and b, arriving later with the smaller distance, takes it back (:705-709)
+        lvl0 = np.flatnonzero(k1["octave"] == 0)
+        for b in lvl0[10::7]:
+            near = lvl0[(lvl0 < b) & (np.abs(k1["x"][lvl0] - k1["x"][b]) < 8) & (np.abs(k1["y"][lvl0] - k1["y"][b]) < 8)]
+            if len(near):
+                a = near[0]
+                d1[a] = d1[b]
+                d1[a, rng.integers(0, 32, 3)] ^= np.uint8(1) << rng.integers(0, 8, 3).astype(np.uint8)
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    return k1, d1, k2, d2, (0.0, float(w), 0.0, float(h)), prev
+
+
+@pytest.mark.parametrize("nf,shift,window,nnratio,ori,corrupt", [(1000, 1, 100, 0.9, True, 0), (1000, 2, 100, 0.9, False, 0),
+                                                                  (2000, 1, 30, 0.7, True, 3), (5000, 3, 100, 0.9, True, 5),
+                                                                  (1000, 5, 10, 0.9, True, 0)])
+def test_search_for_initialization_restatement_equals_reference_body(slices, nf, shift, window, nnratio, ori, corrupt):
+    k1, d1, k2, d2, bounds, prev = init_pair_case(slices, nf, shift, corrupt=corrupt)
+    got = slices.search_for_initialization(k1, d1, k2, d2, bounds, prev, window, nnratio, ori)
+    want = slices.ref_search_for_initialization(k1, d1, k2, d2, bounds, prev, window, nnratio, ori)
+    assert got[0] == want[0] and np.array_equal(got[1], want[1]) and got[2].tobytes() == want[2].tobytes()
+    assert got[0] == int((got[1] >= 0).sum())
+    if corrupt:
+        assert slices.port_lib().orbo_search_for_initialization_withdrawn() > 0  # the withdrawal branch ran
+    if window >= 30:
+        assert got[0] > 50
+    # second round, as the initializer retries with the updated vbPrevMatched
+    got2 = slices.search_for_initialization(k1, d1, k2, d2, bounds, got[2], window, nnratio, ori)
+    want2 = slices.ref_search_for_initialization(k1, d1, k2, d2, bounds, want[2], window, nnratio, ori)
+    assert got2[0] == want2[0] and np.array_equal(got2[1], want2[1]) and got2[2].tobytes() == want2[2].tobytes()
