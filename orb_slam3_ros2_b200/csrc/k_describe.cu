@@ -11,6 +11,8 @@
 // fmaf(x, b, y*a) in NATIVE mode (what gcc -O3 -march=native emits for the reference).  cvRound = rint.
 #include <algorithm>
 
+#include <cstdlib>
+
 #include "orbx_internal.cuh"
 
 namespace orbx {
@@ -341,6 +343,9 @@ void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int l
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, describeKernel, 256, 0);
     const long long want = ((long long)F * P.outCap + 7) / 8;
+    // ORBX_DESC_PERSM (measurements only): cap on the persistent CTAs per SM
+    static const int capPerSm = [] { const char* e = std::getenv("ORBX_DESC_PERSM"); return e ? std::atoi(e) : 0; }();
+    if (capPerSm > 0) perSm = std::min(perSm, capPerSm);
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
     describeKernel<<<grid, 256, 0, s>>>(P, B.pyr, B.blur, B.sorted, B.outN, reinterpret_cast<float*>(B.outKps), B.outDesc, F);
     countLaunch();

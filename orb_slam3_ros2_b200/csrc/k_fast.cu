@@ -34,6 +34,7 @@
 // (its rows are 8 bank phases apart and the warp's work area still fits 4 CTAs per SM).  Reads past the plane are
 // zero-filled by the copy engine.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -405,6 +406,9 @@ void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, kWarpsPerCta * 32, smem);
     const long long total = (long long)cells * F;
     const long long want = (total + kWarpsPerCta - 1) / kWarpsPerCta;
+    // ORBX_FAST_PERSM (measurements only): fewer persistent CTAs per SM leave shared memory for another stream's kernels
+    static const int capPerSm = [] { const char* e = std::getenv("ORBX_FAST_PERSM"); return e ? std::atoi(e) : 0; }();
+    if (capPerSm > 0) perSm = std::min(perSm, capPerSm);
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
     cudaMemsetAsync(counter, 0, sizeof(int), s);
     static const FastMaps kNoMaps{};

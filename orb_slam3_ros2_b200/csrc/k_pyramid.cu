@@ -111,19 +111,24 @@ __global__ void __launch_bounds__(256)
                     unsigned dstOff, int dw, int dh, int dpitch, const short4* __restrict__ tabX,
                     const short4* __restrict__ tabY, int maxRows, const __grid_constant__ CUtensorMap srcMap, int frame0) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ int4 sRow[kTH];  // per tile row: first / second source row (relative to S0), b0 << 16, b1 << 16
-    __shared__ int sS0, sNS;
-    __shared__ __align__(8) uint64_t bar;
-    uint32_t barPhase = 0;
+    // per tile row: first / second source row (relative to S0), b0 << 16, b1 << 16.  TMA: two generations (tile parity), the
+    // next tile's rows and its source box are set up while the current tile is computed
+    __shared__ int4 sRow[2][kTH];
+    __shared__ int sS0[2], sNS[2];
+    __shared__ __align__(8) uint64_t bar[2];
+    uint32_t barPhase[2] = {0, 0};
     if (TMA) {
         if (threadIdx.x == 0) {
-            mbarInit(&bar, 1);
+            mbarInit(&bar[0], 1);
+            mbarInit(&bar[1], 1);
             mbarInitFence();
         }
         // made visible to the other threads by the first __syncthreads of the tile loop
     }
-    uint8_t* sSrc = smem;                                                       // [maxRows][SPT] staged source rows
-    uint32_t* sH = reinterpret_cast<uint32_t*>(smem + (size_t)maxRows * SPT);   // [maxRows][kTW] horizontal pass
+    // [maxRows][SPT] staged source rows (TMA: two buffers, 128-B aligned), then [maxRows][kTW] horizontal pass
+    const int srcBytes = TMA ? ((maxRows * SPT + 127) & ~127) : maxRows * SPT;
+    uint8_t* sSrcBuf[2] = {smem, smem + (TMA ? srcBytes : 0)};
+    uint32_t* sH = reinterpret_cast<uint32_t*>(smem + (size_t)srcBytes * (TMA ? 2 : 1));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int X0 = blockIdx.x * kTW;
@@ -165,43 +170,60 @@ __global__ void __launch_bounds__(256)
         cf[j] = (uint32_t)a0[j] | ((uint32_t)a1[j] << 16);
     }
 
+    // rows of tile `rt` -> source rows (warp 0); lane 0 then hands the tile's source box to the copy engine (TMA)
+    auto setupTile = [&](int rt, int gen) {
+        const int Y0 = (blockIdx.y * kRowTiles + rt) * kTH;
+        const int Y = min(Y0 + lane, ph - 1);
+        const short4 ty = __ldg(tabY + reflect101(Y - kEdge, dh));  // (sy, b0, b1, -)
+        const int sy0 = min(max((int)ty.x, 0), sh - 1), sy1 = min(max((int)ty.x + 1, 0), sh - 1);
+        int lo = sy0, hi = sy1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        }
+        sRow[gen][lane] = make_int4((sy0 - lo) * kTW, (sy1 - lo) * kTW, (int)ty.y << 16, (int)ty.z << 16);
+        if (lane == 0) {
+            sS0[gen] = lo; sNS[gen] = hi - lo + 1;
+            if (TMA) {
+                mbarExpectTx(&bar[gen], (uint32_t)(SPT * maxRows));
+                tmaLoadTile(sSrcBuf[gen], &srcMap, A0, kEdge + lo, frame0 + (int)blockIdx.z, &bar[gen]);
+            }
+        }
+    };
+    if (TMA) {
+        __syncthreads();  // the mbarriers are initialised
+        if (warp == 0) setupTile(0, 0);
+    }
+
     for (int rt = 0; rt < kRowTiles; ++rt) {
         const int Y0 = (blockIdx.y * kRowTiles + rt) * kTH;
         if (Y0 >= ph) break;
-        __syncthreads();  // the previous tile's readers are done with sRow / sSrc / sH
-        // ---- rows of the tile -> source rows ----------------------------------------------------------------------
-        if (warp == 0) {
-            const int Y = min(Y0 + lane, ph - 1);
-            const short4 ty = __ldg(tabY + reflect101(Y - kEdge, dh));  // (sy, b0, b1, -)
-            const int sy0 = min(max((int)ty.x, 0), sh - 1), sy1 = min(max((int)ty.x + 1, 0), sh - 1);
-            int lo = sy0, hi = sy1;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-                hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-            }
-            sRow[lane] = make_int4((sy0 - lo) * kTW, (sy1 - lo) * kTW, (int)ty.y << 16, (int)ty.z << 16);
-            if (lane == 0) { sS0 = lo; sNS = hi - lo + 1; }
-        }
-        __syncthreads();
-        const int S0 = sS0, nS = sNS;
-
-        // ---- stage the source rows --------------------------------------------------------------------------------
+        const int gen = TMA ? (rt & 1) : 0;
+        __syncthreads();  // the previous tile's readers are done with sRow / sSrc / sH (TMA: of the OTHER generation too)
         if (TMA) {
-            if (tid == 0) {
-                mbarExpectTx(&bar, (uint32_t)(SPT * maxRows));
-                tmaLoadTile(sSrc, &srcMap, A0, kEdge + S0, frame0 + (int)blockIdx.z, &bar);
-            }
-            mbarWait(&bar, barPhase);
-            barPhase ^= 1u;
+            // next tile: rows + source box into the other generation while this tile is computed
+            if (warp == 0 && rt + 1 < kRowTiles && Y0 + kTH < ph) setupTile(rt + 1, gen ^ 1);
+            mbarWait(&bar[gen], barPhase[gen]);
+            barPhase[gen] ^= 1u;
         } else {
-            // 16 threads per row, 16 rows per sweep
-            const uint8_t* src = frame + srcOff + (size_t)(kEdge + S0) * spitch + A0;
-            for (int c = tid & 15; c < nC16; c += 16)
-                for (int r = tid >> 4; r < nS; r += 16)
-                    *reinterpret_cast<uint4*>(sSrc + r * SPT + c * 16) = __ldcg(reinterpret_cast<const uint4*>(src + (size_t)r * spitch) + c);
+            if (warp == 0) setupTile(rt, 0);
             __syncthreads();
         }
+        const int S0 = sS0[gen], nS = sNS[gen];
+        const uint8_t* sSrc = sSrcBuf[gen];
+
+        // ---- stage the source rows (ordinary loads) -----------------------------------------------------------------
+        if (!TMA) {
+            // 16 threads per row, 16 rows per sweep
+            const uint8_t* src = frame + srcOff + (size_t)(kEdge + S0) * spitch + A0;
+            uint8_t* dstS = sSrcBuf[0];
+            for (int c = tid & 15; c < nC16; c += 16)
+                for (int r = tid >> 4; r < nS; r += 16)
+                    *reinterpret_cast<uint4*>(dstS + r * SPT + c * 16) = __ldcg(reinterpret_cast<const uint4*>(src + (size_t)r * spitch) + c);
+            __syncthreads();
+        }
+        (void)S0;
 
         // ---- horizontal pass: H[s][x] = (p0*a0 + p1*a1) >> 4  (<= 32640) ------------------------------------------
         if (WINDOWED) {
@@ -235,7 +257,7 @@ __global__ void __launch_bounds__(256)
             for (int k = 0; k < kTH / 8; ++k) {
                 const int ry = warp * (kTH / 8) + k, Y = Y0 + ry;
                 if (Y >= ph) break;
-                const int4 ri = sRow[ry];
+                const int4 ri = sRow[gen][ry];
                 const uint4 u = *reinterpret_cast<const uint4*>(sH + ri.x + 4 * lane);
                 const uint4 v = *reinterpret_cast<const uint4*>(sH + ri.y + 4 * lane);
                 const uint32_t B0 = (uint32_t)ri.z, B1 = (uint32_t)ri.w;  // b << 16: umulhi(b << 16, h) == (b * h) >> 16
@@ -274,7 +296,7 @@ static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cu
     const LevelPlan& D = P.lv[l];
     const int pw = D.w + 2 * kEdge, ph = D.h + 2 * kEdge;
     const int maxRows = pyrMaxRows(S, D);
-    const size_t smem = (size_t)maxRows * (SPT + kTW * 4);
+    const size_t smem = TMA ? 2 * (size_t)((maxRows * SPT + 127) & ~127) + (size_t)maxRows * kTW * 4 : (size_t)maxRows * (SPT + kTW * 4);
     auto kern = pyrResizeKernel<SPT, WINDOWED, TMA>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((pw + kTW - 1) / kTW, ((ph + kTH - 1) / kTH + kRowTiles - 1) / kRowTiles, F);
