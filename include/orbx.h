@@ -315,6 +315,16 @@ int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf
                        const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
                        const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
                        int f_nodes, float nnratio, int check_orientation, int32_t* match_f, int32_t* n_matches, int device);
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12) (ORBmatcher.cc:765-905, monocular
+ * keyframes; loop closing and map merging): the same node-by-node walk, but a candidate of keyframe 2 needs a good MapPoint
+ * and must not be matched yet (vbMatched2, :826-830), the accept rule is bestDist1 < TH_LOW (strict, :848) and the result is
+ * indexed by keyframe 1: match12[i] = feature of keyframe 2 whose MapPoint goes to feature i, or -1.  valid1 / valid2 as
+ * valid_kf above. */
+int orbx_search_by_bow_kf(const uint8_t* desc1, int n1, const uint8_t* valid1, const float* angle1, const int32_t* node_ids1,
+                          const int32_t* node_begin1, const int32_t* feat_idx1, int nodes1, const uint8_t* desc2, int n2,
+                          const uint8_t* valid2, const float* angle2, const int32_t* node_ids2, const int32_t* node_begin2,
+                          const int32_t* feat_idx2, int nodes2, float nnratio, int check_orientation, int32_t* match12,
+                          int32_t* n_matches, int device);
 
 /* Measured sustained 32-bit POPC rate of the device in giga-POPC/s (8 independent XOR+POPC chains per thread):
  * the denominator of the matcher's roofline, pairs/s = POPC/s / 8. */

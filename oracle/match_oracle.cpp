@@ -511,4 +511,96 @@ int orbo_search_for_initialization(const void* kps1_, const uint8_t* desc1, int 
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) (src/ORBmatcher.cc:765-905), monocular keyframes ----
+// The keyframe-to-keyframe twin of orbo_search_by_bow (loop closing / merging): candidates of keyframe 2 need a good MapPoint
+// and must not be matched yet (vbMatched2, :826-830), the accept rule is STRICT in TH_LOW (bestDist1 < TH_LOW, :848), the
+// result is indexed by keyframe 1's features.  valid: 0 = no MapPoint, 1 = good, 2 = isBad().  match12[i] = feature of
+// keyframe 2 or -1.  PINNED to the reference's own body by tests/test_oracle_refslices.py.
+int orbo_search_by_bow_kf(const uint8_t* desc1, int n1, const uint8_t* valid1, const float* angle1, const int32_t* node_ids1,
+                          const int32_t* node_begin1, const int32_t* feat_idx1, int nodes1, const uint8_t* desc2, int n2,
+                          const uint8_t* valid2, const float* angle2, const int32_t* node_ids2, const int32_t* node_begin2,
+                          const int32_t* feat_idx2, int nodes2, float mfNNratio, int mbCheckOrientation, int32_t* match12) {
+    const int HISTO_LENGTH = 30;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;  // :777
+    std::vector<char> vbMatched2((size_t)std::max(n2, 1), 0);
+    std::vector<int> rotHist[30];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    int a = 0, b = 0;
+    while (a < nodes1 && b < nodes2) {
+        if (node_ids1[a] == node_ids2[b]) {
+            for (int i1 = node_begin1[a]; i1 < node_begin1[a + 1]; i1++) {
+                const int idx1 = feat_idx1[i1];
+                if (valid1[idx1] != 1) continue;  // :803-807 !pMP1 or isBad()
+                const uint8_t* d1 = desc1 + (size_t)idx1 * 32;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int i2 = node_begin2[b]; i2 < node_begin2[b + 1]; i2++) {
+                    const int idx2 = feat_idx2[i2];
+                    if (vbMatched2[idx2] || valid2[idx2] == 0) continue;  // :826-827
+                    if (valid2[idx2] == 2) continue;                      // :829-830 isBad()
+                    const int dist = orbo_hamming(d1, desc2 + (size_t)idx2 * 32);
+                    if (dist < bestDist1) {
+                        bestDist2 = bestDist1;
+                        bestDist1 = dist;
+                        bestIdx2 = idx2;
+                    } else if (dist < bestDist2) {
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist1 < TH_LOW) {  // :848 strict
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        match12[idx1] = bestIdx2;
+                        vbMatched2[bestIdx2] = 1;
+                        if (mbCheckOrientation) {
+                            float rot = angle1[idx1] - angle2[bestIdx2];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            a++;
+            b++;
+        } else if (node_ids1[a] < node_ids2[b]) {
+            while (a < nodes1 && node_ids1[a] < node_ids2[b]) a++;  // lower_bound
+        } else {
+            while (b < nodes2 && node_ids2[b] < node_ids1[a]) b++;
+        }
+    }
+    if (mbCheckOrientation) {
+        // ComputeThreeMaxima (ORBmatcher.cc:2012-2053)
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) {
+                max3 = max2; max2 = max1; max1 = s;
+                ind3 = ind2; ind2 = ind1; ind1 = i;
+            } else if (s > max2) {
+                max3 = max2; max2 = s;
+                ind3 = ind2; ind2 = i;
+            } else if (s > max3) {
+                max3 = s;
+                ind3 = i;
+            }
+        }
+        if (max2 < 0.1f * (float)max1) {
+            ind2 = -1;
+            ind3 = -1;
+        } else if (max3 < 0.1f * (float)max1) {
+            ind3 = -1;
+        }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                match12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 }  // extern "C"

@@ -670,6 +670,35 @@ def _search_by_bow(fn, desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f
     return n, out[:len(desc_f)]
 
 
+def _search_by_bow_kf(fn, desc1, valid1, angle1, fv1, desc2, valid2, angle2, fv2, nnratio, check_orientation):
+    desc1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); desc2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    valid1 = np.ascontiguousarray(valid1, np.uint8); valid2 = np.ascontiguousarray(valid2, np.uint8)
+    angle1 = np.ascontiguousarray(angle1, np.float32); angle2 = np.ascontiguousarray(angle2, np.float32)
+    arrs = []
+    for fv in (fv1, fv2):
+        arrs.append([np.ascontiguousarray(fv[k], np.int32) for k in ("node_ids", "node_begin", "feat_idx")])
+    out = np.full(max(len(desc1), 1), -1, np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int,
+                   C.c_float, C.c_int, _i32p]
+    n = fn(_ptr(desc1), len(desc1), _ptr(valid1), _ptr(angle1, _f32p), *[_ptr(a, _i32p) for a in arrs[0]], len(arrs[0][0]),
+           _ptr(desc2), len(desc2), _ptr(valid2), _ptr(angle2, _f32p), *[_ptr(a, _i32p) for a in arrs[1]], len(arrs[1][0]),
+           float(nnratio), int(bool(check_orientation)), _ptr(out, _i32p))
+    return n, out[:len(desc1)]
+
+
+def search_by_bow_kf(desc1, valid1, angle1, fv1, desc2, valid2, angle2, fv2, nnratio=0.75, check_orientation=True):
+    """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...) restatement (ORBmatcher.cc:765-905) -> (nmatches, match12)."""
+    return _search_by_bow_kf(port_lib().orbo_search_by_bow_kf, desc1, valid1, angle1, fv1, desc2, valid2, angle2, fv2, nnratio,
+                             check_orientation)
+
+
+def ref_search_by_bow_kf(desc1, valid1, angle1, fv1, desc2, valid2, angle2, fv2, nnratio=0.75, check_orientation=True):
+    """The same through the reference's own body (librefslices.so)."""
+    return _search_by_bow_kf(_slices().refslice_search_by_bow_kf, desc1, valid1, angle1, fv1, desc2, valid2, angle2, fv2, nnratio,
+                             check_orientation)
+
+
 def search_by_bow(desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnratio=0.7, check_orientation=True):
     """ORBmatcher::SearchByBoW(KF, F) restatement (oracle/match_oracle.cpp) -> (nmatches, match_f).  fv_*: dicts with the
     FeatureVector CSR arrays of a BoW transform (node_ids, node_begin, feat_idx)."""

@@ -8,6 +8,7 @@
 //   ORBmatcher.cc:223-425    ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)
 //   ORBmatcher.cc:2012-2053  ORBmatcher::ComputeThreeMaxima
 //   ORBmatcher.cc:648-763    ORBmatcher::SearchForInitialization
+//   ORBmatcher.cc:765-905    ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)
 //   Frame.cc:385-416         Frame::AssignFeaturesToGrid
 //   Frame.cc:657-723         Frame::GetFeaturesInArea
 //   Frame.cc:725-735         Frame::PosInGrid
@@ -33,6 +34,7 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 #include "ORBmatcher_SearchByBoW.inc"
 #include "ORBmatcher_ComputeThreeMaxima.inc"
 #include "ORBmatcher_SearchForInitialization.inc"
+#include "ORBmatcher_SearchByBoW_KFKF.inc"
 }  // namespace ORB_SLAM3
 
 using ORB_SLAM3::Frame;
@@ -216,6 +218,37 @@ int refslice_search_for_initialization(const void* kps1, const uint8_t* desc1, i
         matches12[i] = m12[i];
         prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
     }
+    return n;
+}
+
+// ORBmatcher::SearchByBoW(pKF1, pKF2, vpMatches12) for two monocular keyframes (NLeft == -1).  valid1 / valid2: 0 = no MapPoint,
+// 1 = good MapPoint, 2 = isBad().  match12[i] = feature of keyframe 2 whose MapPoint was given to feature i of keyframe 1, or -1.
+int refslice_search_by_bow_kf(const uint8_t* desc1, int n1, const uint8_t* valid1, const float* angle1, const int32_t* node_ids1,
+                              const int32_t* node_begin1, const int32_t* feat_idx1, int nodes1, const uint8_t* desc2, int n2,
+                              const uint8_t* valid2, const float* angle2, const int32_t* node_ids2, const int32_t* node_begin2,
+                              const int32_t* feat_idx2, int nodes2, float nnratio, int check_orientation, int32_t* match12) {
+    ORB_SLAM3::KeyFrame KF1, KF2;
+    std::vector<ORB_SLAM3::MapPoint> p1(n1), p2(n2);
+    auto fill = [](ORB_SLAM3::KeyFrame& KF, std::vector<ORB_SLAM3::MapPoint>& pts, const uint8_t* desc, int n, const uint8_t* valid,
+                   const float* angle, const int32_t* ids, const int32_t* begin, const int32_t* feat, int nodes) {
+        KF.mvpMapPoints.assign(n, nullptr);
+        KF.mvKeysUn.resize(n);
+        for (int i = 0; i < n; ++i) {
+            pts[i].index = i;
+            pts[i].mbBad = valid[i] == 2;
+            if (valid[i]) KF.mvpMapPoints[i] = &pts[i];
+            KF.mvKeysUn[i].angle = angle[i];
+        }
+        KF.mDescriptors = descriptors(desc, n);
+        for (int j = 0; j < nodes; ++j)
+            for (int p = begin[j]; p < begin[j + 1]; ++p) KF.mFeatVec.addFeature((DBoW2::NodeId)ids[j], (unsigned)feat[p]);
+    };
+    fill(KF1, p1, desc1, n1, valid1, angle1, node_ids1, node_begin1, feat_idx1, nodes1);
+    fill(KF2, p2, desc2, n2, valid2, angle2, node_ids2, node_begin2, feat_idx2, nodes2);
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    std::vector<ORB_SLAM3::MapPoint*> out;
+    const int n = matcher.SearchByBoW(&KF1, &KF2, out);
+    for (int i = 0; i < n1; ++i) match12[i] = out[i] ? out[i]->index : -1;
     return n;
 }
 

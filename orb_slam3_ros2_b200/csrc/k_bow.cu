@@ -210,6 +210,9 @@ struct BowSearchArgs {
     const int* fNodeIds; const int* fNodeBegin; const int* fFeatIdx; int fNodes;
     float nnratio; int checkOrientation;
     int* matchF; int* binF;
+    // keyframe <-> keyframe form (ORBmatcher.cc:765-905): candidates of the second side need a good MapPoint (validF == 1, :826-830)
+    // and the accept rule is strict in TH_LOW (:848); validF == NULL, strictLow == 0 is the keyframe -> frame form
+    const uint8_t* validF; int strictLow;
 };
 
 __global__ void __launch_bounds__(256) bowSearchKernel(const BowSearchArgs A) {
@@ -232,7 +235,8 @@ __global__ void __launch_bounds__(256) bowSearchKernel(const BowSearchArgs A) {
         unsigned k1 = kNone, k2 = kNone;
         for (int iF = fbeg + lane; iF < fend; iF += 32) {
             const int realF = A.fFeatIdx[iF];
-            if (matchF[realF] >= 0) continue;  // vpMapPointMatches[realIdxF] already set (:279)
+            if (matchF[realF] >= 0) continue;  // vpMapPointMatches[realIdxF] already set (:279) / vbMatched2 (:826)
+            if (A.validF && A.validF[realF] != 1) continue;
             const uint4 b0 = A.descF[2 * realF], b1 = A.descF[2 * realF + 1];
             const int d = __popc(q0.x ^ b0.x) + __popc(q0.y ^ b0.y) + __popc(q0.z ^ b0.z) + __popc(q0.w ^ b0.w) +
                           __popc(q1.x ^ b1.x) + __popc(q1.y ^ b1.y) + __popc(q1.z ^ b1.z) + __popc(q1.w ^ b1.w);
@@ -247,7 +251,7 @@ __global__ void __launch_bounds__(256) bowSearchKernel(const BowSearchArgs A) {
             k1 = min(k1, o1);
         }
         const int best1 = (int)(k1 >> 16), best2 = (int)(k2 >> 16);
-        if (best1 <= 50 && (float)best1 < __fmul_rn(A.nnratio, (float)best2)) {  // TH_LOW, mfNNratio (:323-325)
+        if ((A.strictLow ? best1 < 50 : best1 <= 50) && (float)best1 < __fmul_rn(A.nnratio, (float)best2)) {  // TH_LOW, mfNNratio (:323-325, :848-850)
             if (lane == 0) {
                 const int bestF = A.fFeatIdx[fbeg + (int)(k1 & 0xffffu)];
                 matchF[bestF] = realKF;
@@ -310,12 +314,12 @@ __global__ void __launch_bounds__(256) bowOrientationKernel(int* __restrict__ ma
 void launchBowSearch(const uint8_t* descKF, const uint8_t* validKF, const float* angleKF, const int* kfNodeIds, const int* kfNodeBegin,
                      const int* kfFeatIdx, int kfNodes, const uint8_t* descF, int nF, const float* angleF, const int* fNodeIds,
                      const int* fNodeBegin, const int* fFeatIdx, int fNodes, float nnratio, int checkOrientation, int* matchF, int* binF,
-                     int* nMatches, cudaStream_t s) {
+                     int* nMatches, cudaStream_t s, const uint8_t* validF, int strictLow) {
     cudaMemsetAsync(matchF, 0xff, (size_t)std::max(nF, 1) * 4, s);
     if (kfNodes > 0 && fNodes > 0 && nF > 0) {
         const BowSearchArgs A{reinterpret_cast<const uint4*>(descKF), validKF, angleKF, kfNodeIds, kfNodeBegin, kfFeatIdx, kfNodes,
                               reinterpret_cast<const uint4*>(descF), angleF, fNodeIds, fNodeBegin, fFeatIdx, fNodes, nnratio,
-                              checkOrientation, matchF, binF};
+                              checkOrientation, matchF, binF, validF, strictLow};
         bowSearchKernel<<<(kfNodes * 32 + 255) / 256, 256, 0, s>>>(A);
         countLaunch();
     }

@@ -1524,10 +1524,12 @@ int orbx_bow_transform_extracted(orbx_voc v, orbx_handle h, int levelsup, int32_
                   node_begin, feat_idx, n_nodes);
 }
 
-int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
-                       const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
-                       const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
-                       int f_nodes, float nnratio, int check_orientation, int32_t* match_f, int32_t* n_matches, int device) {
+// shared by the keyframe -> frame form (valid_f == NULL) and the keyframe <-> keyframe form (valid_f given, strict TH_LOW)
+static int searchByBowImpl(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
+                           const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
+                           const uint8_t* valid_f, const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin,
+                           const int32_t* f_feat_idx, int f_nodes, float nnratio, int check_orientation, int strict_low, int32_t* match_f,
+                           int32_t* n_matches, int device) {
     if (n_kf < 0 || n_f < 0 || kf_nodes < 0 || f_nodes < 0 || !match_f || !n_matches) return fail(ORBX_ERR_ARG, "bad argument");
     if (n_f >= 65536) return fail(ORBX_ERR_ARG, "more than 65535 frame features");
     if ((n_kf > 0 && (!desc_kf || !valid_kf || !angle_kf)) || (n_f > 0 && (!desc_f || !angle_f)) ||
@@ -1552,7 +1554,7 @@ int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf
     size_t o = 0;
     auto take = [&](size_t bytes) { const size_t at = o; o += (bytes + 15) & ~(size_t)15; return at; };
     const size_t oDK = take(K * 32), oDF = take(Fn * 32), oAK = take(K * 4), oAF = take(Fn * 4), oKI = take(KN * 4 + 4), oKB = take(KN * 4 + 4),
-                 oKX = take(K * 4), oFI = take(FN * 4 + 4), oFB = take(FN * 4 + 4), oFX = take(Fn * 4), oV = take(K);
+                 oKX = take(K * 4), oFI = take(FN * 4 + 4), oFB = take(FN * 4 + 4), oFX = take(Fn * 4), oV = take(K), oVF = take(Fn);
     ORBX_CUDA(S->db.reserve(o + 64));
     ORBX_CUDA(S->misc.reserve(Fn * 8 + 64));
     uint8_t* D = (uint8_t*)S->db.p;
@@ -1568,13 +1570,40 @@ int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf
     ORBX_CUDA(up(oKI, kf_node_ids, KN * 4)); ORBX_CUDA(up(oKB, kf_node_begin, kf_nodes ? (KN + 1) * 4 : 0)); ORBX_CUDA(up(oKX, kf_feat_idx, (size_t)kfEntries * 4));
     ORBX_CUDA(up(oFI, f_node_ids, FN * 4)); ORBX_CUDA(up(oFB, f_node_begin, f_nodes ? (FN + 1) * 4 : 0)); ORBX_CUDA(up(oFX, f_feat_idx, (size_t)fEntries * 4));
     ORBX_CUDA(up(oV, valid_kf, (size_t)n_kf));
+    if (valid_f) ORBX_CUDA(up(oVF, valid_f, (size_t)n_f));
     launchBowSearch(D + oDK, D + oV, (const float*)(D + oAK), (const int*)(D + oKI), (const int*)(D + oKB), (const int*)(D + oKX), kf_nodes,
                     D + oDF, n_f, (const float*)(D + oAF), (const int*)(D + oFI), (const int*)(D + oFB), (const int*)(D + oFX), f_nodes, nnratio,
-                    check_orientation != 0, matchF, binF, nM, s);
+                    check_orientation != 0, matchF, binF, nM, s, valid_f ? D + oVF : nullptr, strict_low);
     ORBX_CUDA(cudaGetLastError());
     if (n_f) ORBX_CUDA(cudaMemcpyAsync(match_f, matchF, (size_t)n_f * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(n_matches, nM, 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_search_by_bow(const uint8_t* desc_kf, int n_kf, const uint8_t* valid_kf, const float* angle_kf, const int32_t* kf_node_ids,
+                       const int32_t* kf_node_begin, const int32_t* kf_feat_idx, int kf_nodes, const uint8_t* desc_f, int n_f,
+                       const float* angle_f, const int32_t* f_node_ids, const int32_t* f_node_begin, const int32_t* f_feat_idx,
+                       int f_nodes, float nnratio, int check_orientation, int32_t* match_f, int32_t* n_matches, int device) {
+    return searchByBowImpl(desc_kf, n_kf, valid_kf, angle_kf, kf_node_ids, kf_node_begin, kf_feat_idx, kf_nodes, desc_f, n_f, nullptr,
+                           angle_f, f_node_ids, f_node_begin, f_feat_idx, f_nodes, nnratio, check_orientation, 0, match_f, n_matches, device);
+}
+
+int orbx_search_by_bow_kf(const uint8_t* desc1, int n1, const uint8_t* valid1, const float* angle1, const int32_t* node_ids1,
+                          const int32_t* node_begin1, const int32_t* feat_idx1, int nodes1, const uint8_t* desc2, int n2,
+                          const uint8_t* valid2, const float* angle2, const int32_t* node_ids2, const int32_t* node_begin2,
+                          const int32_t* feat_idx2, int nodes2, float nnratio, int check_orientation, int32_t* match12,
+                          int32_t* n_matches, int device) {
+    if (n1 < 0 || n2 < 0 || !match12 || !n_matches || (n2 > 0 && !valid2)) return fail(ORBX_ERR_ARG, "bad argument");
+    // the device keeps the match per feature of keyframe 2 (= vbMatched2 and the partner in one array); a point of keyframe 2 is
+    // given away at most once (:826, :853), so the map inverts into vpMatches12
+    std::vector<int32_t> m21((size_t)std::max(n2, 1), -1);
+    const int rc = searchByBowImpl(desc1, n1, valid1, angle1, node_ids1, node_begin1, feat_idx1, nodes1, desc2, n2, valid2, angle2,
+                                   node_ids2, node_begin2, feat_idx2, nodes2, nnratio, check_orientation, 1, m21.data(), n_matches, device);
+    if (rc != ORBX_OK) return rc;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    for (int j = 0; j < n2; ++j)
+        if (m21[j] >= 0 && m21[j] < n1) match12[m21[j]] = j;
     return ORBX_OK;
 }
 

@@ -173,7 +173,7 @@ void launchBowTransform(const BowVocDev& V, const uint8_t* dDesc, const int* dN,
 void launchBowSearch(const uint8_t* descKF, const uint8_t* validKF, const float* angleKF, const int* kfNodeIds, const int* kfNodeBegin,
                      const int* kfFeatIdx, int kfNodes, const uint8_t* descF, int nF, const float* angleF, const int* fNodeIds,
                      const int* fNodeBegin, const int* fFeatIdx, int fNodes, float nnratio, int checkOrientation, int* matchF, int* binF,
-                     int* nMatches, cudaStream_t s);
+                     int* nMatches, cudaStream_t s, const uint8_t* validF = nullptr, int strictLow = 0);
 void uploadDescribeTables();
 double benchPopcRate(cudaStream_t s);
 

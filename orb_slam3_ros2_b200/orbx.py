@@ -95,6 +95,8 @@ SYMBOLS = {
                                                        C.c_int, _i32p, _i32p, _f32p]),
     "orbx_search_by_bow": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _f32p, _i32p, _i32p, _i32p,
                                      C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
+    "orbx_search_by_bow_kf": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p,
+                                        _i32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_voc_create": (C.c_int, [C.c_int, _i32p, _u8p, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(_vp)]),
     "orbx_voc_destroy": (None, [_vp]),
@@ -615,6 +617,25 @@ def search_by_bow(desc_kf, valid_kf, angle_kf, fv_kf, desc_f, angle_f, fv_f, nnr
                                     len(a[0]), _ptr(desc_f), len(desc_f), _ptr(angle_f, _f32p), *[_ptr(x, _i32p) for x in b], len(b[0]),
                                     float(nnratio), int(bool(check_orientation)), _ptr(out, _i32p), _ptr(n, _i32p), device))
     return int(n[0]), out[:len(desc_f)]
+
+
+def search_by_bow_kf(desc1, valid1, angle1, fv1, desc2, valid2, angle2, fv2, nnratio=0.75, check_orientation=True, device=-1):
+    """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...) (ORBmatcher.cc:765-905, monocular) -> (nmatches, match12): match12[i] =
+    feature of keyframe 2 whose MapPoint goes to feature i of keyframe 1, or -1."""
+    desc1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+    desc2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    valid1 = np.ascontiguousarray(valid1, np.uint8)
+    valid2 = np.ascontiguousarray(valid2, np.uint8)
+    angle1 = np.ascontiguousarray(angle1, np.float32)
+    angle2 = np.ascontiguousarray(angle2, np.float32)
+    a = [np.ascontiguousarray(fv1[k], np.int32) for k in ("node_ids", "node_begin", "feat_idx")]
+    b = [np.ascontiguousarray(fv2[k], np.int32) for k in ("node_ids", "node_begin", "feat_idx")]
+    out = np.full(max(len(desc1), 1), -1, np.int32)
+    n = np.zeros(1, np.int32)
+    _check(lib().orbx_search_by_bow_kf(_ptr(desc1), len(desc1), _ptr(valid1), _ptr(angle1, _f32p), *[_ptr(x, _i32p) for x in a], len(a[0]),
+                                       _ptr(desc2), len(desc2), _ptr(valid2), _ptr(angle2, _f32p), *[_ptr(x, _i32p) for x in b], len(b[0]),
+                                       float(nnratio), int(bool(check_orientation)), _ptr(out, _i32p), _ptr(n, _i32p), device))
+    return int(n[0]), out[:len(desc1)]
 
 
 class ShardedMatcher:

@@ -108,3 +108,28 @@ def test_search_by_bow_chain_on_extracted_frames(orbx, oracle):
     # empty keyframe side / nothing valid
     n0, m0 = orbx.search_by_bow(d0, np.zeros(len(k0), np.uint8), k0["angle"], fv[0], d1, k1["angle"], fv[1])
     assert n0 == 0 and (m0 == -1).all()
+
+
+@pytest.mark.parametrize("seed,levelsup,nnratio,ori", [(0, 2, 0.75, True), (1, 2, 0.9, True), (2, 3, 0.75, False), (3, 1, 0.6, True),
+                                                      (4, 4, 0.75, True)])
+def test_search_by_bow_keyframes_matches_oracle(orbx, oracle, seed, levelsup, nnratio, ori):
+    """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...) (ORBmatcher.cc:765-905) on the device == oracle == the reference's body."""
+    from test_oracle_refslices import bow_kf_pair_case
+    case = bow_kf_pair_case(oracle, seed, 1000, levelsup)
+    n_want, m_want = oracle.search_by_bow_kf(*case, nnratio=nnratio, check_orientation=ori)
+    n_got, m_got = orbx.search_by_bow_kf(*case, nnratio=nnratio, check_orientation=ori)
+    assert n_got == n_want and np.array_equal(m_got, m_want)
+    if oracle.have_refslices():
+        n_ref, m_ref = oracle.ref_search_by_bow_kf(*case, nnratio=nnratio, check_orientation=ori)
+        assert n_got == n_ref and np.array_equal(m_got, m_ref)
+    # nothing valid on the second side
+    d1, v1, a1, fv1, d2, v2, a2, fv2 = case
+    n0, m0 = orbx.search_by_bow_kf(d1, v1, a1, fv1, d2, np.zeros_like(v2), a2, fv2, nnratio, ori)
+    assert n0 == 0 and (m0 == -1).all()
+    # distance exactly TH_LOW is rejected here (strict, :848) but accepted by the keyframe -> frame form (:323)
+    q = np.zeros((1, 32), np.uint8)
+    t = np.zeros((1, 32), np.uint8); t[0, :6] = 0xff; t[0, 6] = 0x03  # 50 bits
+    fv = {"node_ids": np.array([7], np.int32), "node_begin": np.array([0, 1], np.int32), "feat_idx": np.array([0], np.int32)}
+    one, ang = np.ones(1, np.uint8), np.zeros(1, np.float32)
+    assert orbx.search_by_bow_kf(q, one, ang, fv, t, one, ang, fv, 0.75, False)[0] == 0
+    assert orbx.search_by_bow(q, one, ang, fv, t, ang, fv, 0.75, False)[0] == 1

@@ -180,3 +180,24 @@ def test_search_for_initialization_restatement_equals_reference_body(slices, nf,
     got2 = slices.search_for_initialization(k1, d1, k2, d2, bounds, got[2], window, nnratio, ori)
     want2 = slices.ref_search_for_initialization(k1, d1, k2, d2, bounds, want[2], window, nnratio, ori)
     assert got2[0] == want2[0] and np.array_equal(got2[1], want2[1]) and got2[2].tobytes() == want2[2].tobytes()
+
+
+def bow_kf_pair_case(oracle, seed=0, n=1000, levelsup=2):
+    """Two keyframes for SearchByBoW(KF1, KF2): the pair of bow_pair_case plus MapPoint flags for the second keyframe."""
+    d1, valid1, a1, fv1, d2, a2, fv2 = bow_pair_case(oracle, seed, n, levelsup)
+    valid2 = np.random.default_rng(100 + seed).choice([0, 1, 1, 1, 1, 2], len(d2)).astype(np.uint8)
+    return d1, valid1, a1, fv1, d2, valid2, a2, fv2
+
+
+@pytest.mark.parametrize("seed,levelsup,nnratio,ori", [(0, 2, 0.75, True), (1, 2, 0.9, True), (2, 3, 0.75, False), (3, 1, 0.6, True),
+                                                      (4, 4, 0.75, True)])
+def test_search_by_bow_keyframes_restatement_equals_reference_body(slices, seed, levelsup, nnratio, ori):
+    """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...) (ORBmatcher.cc:765-905): restatement == the reference's own body."""
+    case = bow_kf_pair_case(slices, seed, 1000, levelsup)
+    n_ref, m_ref = slices.ref_search_by_bow_kf(*case, nnratio=nnratio, check_orientation=ori)
+    n_got, m_got = slices.search_by_bow_kf(*case, nnratio=nnratio, check_orientation=ori)
+    assert n_got == n_ref and np.array_equal(m_got, m_ref)
+    assert n_ref == int((m_ref >= 0).sum()) and n_ref > 30
+    sel = m_ref[m_ref >= 0]
+    assert len(np.unique(sel)) == len(sel)                      # vbMatched2: a point of keyframe 2 is given away once
+    assert (case[1][m_ref >= 0] == 1).all() and (case[5][sel] == 1).all()  # only good MapPoints on both sides
