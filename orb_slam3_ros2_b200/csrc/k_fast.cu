@@ -44,7 +44,10 @@
 namespace orbx {
 namespace {
 
-constexpr int kWarpsPerCta = 8;
+#ifndef ORBX_FAST_WARPS
+#define ORBX_FAST_WARPS 8
+#endif
+constexpr int kWarpsPerCta = ORBX_FAST_WARPS;
 constexpr int kPixCap = 256;      // pixel list capacity per warp (one segment of flagged pixels)
 
 __device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
@@ -87,7 +90,7 @@ __device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32
 // TMA = true (needs SHIFTED): the tile is staged by the copy engine from the per-level tensor maps in M; the arc map
 // then has its own pitch APITCH = 48 and is indexed with cell x (tile x - shift).
 template <int PITCH, bool SHIFTED, bool TMA>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 32 / kWarpsPerCta)
     fastCellsKernel(const __grid_constant__ FramePlan P, const __grid_constant__ FastMaps M, const uint8_t* __restrict__ pyr,
                     uint32_t* __restrict__ cand, int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes,
                     const uint32_t* __restrict__ cellTab, int cellsInLaunch, int totalWork, int* __restrict__ workCounter,

@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(256) pyrLevel0AlignedKernel(const uint8_t* __r
 // level l >= 1 from level l-1, tiled and separable.  A CTA owns a 128-column strip of the padded plane and walks
 // kRowTiles 32-row tiles of it; the column coefficients live in registers for the whole walk.
 // SPT = bytes per staged source row (compile-time so that the row loops unroll into immediate offsets).
-constexpr int kRowTiles = 4;
+#ifndef ORBX_PYR_ROWTILES
+#define ORBX_PYR_ROWTILES 4
+#endif
+constexpr int kRowTiles = ORBX_PYR_ROWTILES;
 
 // TMA = true: the source rows of a tile are staged by ONE cp.async.bulk.tensor.3d (box SPT x maxRows x 1 of the source
 // level's tensor map, first byte at the 16-byte aligned plane column A0; what the box holds beyond the nS rows / nC16 chunks

@@ -19,7 +19,10 @@
 namespace orbx {
 namespace {
 
-constexpr int kQT = 256;  // threads per CTA
+#ifndef ORBX_QT_THREADS
+#define ORBX_QT_THREADS 128
+#endif
+constexpr int kQT = ORBX_QT_THREADS;  // threads per CTA
 
 struct Box {
     short ulx, urx, uly, bry;
