@@ -29,8 +29,9 @@ if ROOT not in sys.path:
 
 W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
 LAP = (0, 1000)  # Frame.cc:311 passes {0,1000} for monocular frames
+E2E_SUBBATCHES = 1  # measured (profiles/r01_v15_e2e_sweep.txt): sub-batches 2 -> 110 k, 1 -> 126-131 k frames/s through host buffers
 E2E_DEPTH = 3   # measured sweep (handles x depth -> frames/s): 2x1 90.2k, 4x1 98.6k, 2x2 110.7k, 4x2 100.2k, 2x3 112.7k, 1x3 112.1k, 3x3 104.4k
-E2E_HANDLES = 2
+E2E_HANDLES = 1  # v15 sweep with sub-batches off (handles x depth): 1x2 105k, 1x3 131k, 1x4 125k, 2x2 125k, 2x3 127k, 3x3 114k
 RESIDENT_HANDLES = 2  # measured (handles x sub-batches -> frames/s): 1x1 127.9k, 1x2 129.2k, 2x1 131.8k, 2x2 134.6k, 3x1 134.3k, 3x2 132.3k
 SUBBATCHES = 2  # default of --subbatches; measured sweep (profiles/r01_v6_subbatch_sweep_*): 1 -> 108.7k, 2 -> 113.3k, 3 -> 113.2k, 4 -> 113.0k, 6 -> 106.4k
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
@@ -351,7 +352,7 @@ def run_e2e(ctx, args, world):
         hs = [ctx["ex"] if (g == 0 and i == 0) else orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=ctx["dev"].index)
               for i in range(len(parts))]
         for hnd in hs:
-            hnd.set_subbatches(args.subbatches)
+            hnd.set_subbatches(args.e2e_subbatches)
         bs = []
         for lo, cnt in parts:
             bs.append(dict(kps=torch.empty((cnt, cap, 7), dtype=torch.float32).pin_memory(),
@@ -401,7 +402,7 @@ def run_e2e(ctx, args, world):
         if ex is not ctx["ex"]:
             ex.close()
     return {"value": world * F * steps / dt, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "steps": steps, "handles": len(parts), "depth": depth,
+            "steps": steps, "handles": len(parts), "depth": depth, "subbatches": args.e2e_subbatches,
             "api": f"orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check; a step is split over {len(parts)} handles, {depth} generation(s) of handles and pinned host buffers in flight"}
 
 
@@ -511,6 +512,7 @@ def main():
     ap.add_argument("--resident-handles", type=int, default=RESIDENT_HANDLES,
                     help="extractor handles the resident (value) leg alternates its steps over")
     ap.add_argument("--e2e-handles", type=int, default=E2E_HANDLES, help="extractor handles the e2e leg pipelines a step over")
+    ap.add_argument("--e2e-subbatches", type=int, default=E2E_SUBBATCHES, help="sub-batch setting of the e2e leg's handles")
     ap.add_argument("--e2e-depth", type=int, default=E2E_DEPTH, help="generations of handles/host buffers in flight in the e2e leg")
     ap.add_argument("--only-e2e", action="store_true", help="development: resident leg + e2e leg only, print the e2e object")
     ap.add_argument("--skip-match", action="store_true")
