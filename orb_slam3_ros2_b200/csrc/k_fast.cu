@@ -469,6 +469,13 @@ int encodeLevelMap(CUtensorMap* out, const FramePlan& P, int l, const uint8_t* p
 
 static bool wideLevel(const LevelPlan& L) { return L.wCell + 6 > 48 || L.hCell + 6 > 50; }
 
+bool fastHasBothClasses(const FramePlan& P) {
+    bool any[2] = {false, false};
+    for (int l = 0; l < P.nlevels; ++l)
+        if (P.lv[l].nCols > 0 && P.lv[l].nRows > 0) any[wideLevel(P.lv[l]) ? 1 : 0] = true;
+    return any[0] && any[1];
+}
+
 // (level << 24 | cell row << 12 | cell column) of every FAST cell, the narrow class first, then the wide one; inside a
 // class level-major and row-major, i.e. the reference's visiting order (ORBextractor.cc:805-808)
 void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab) {
@@ -482,7 +489,9 @@ void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab) {
         }
 }
 
-void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
+// which: -1 = both classes back to back on s; 0 = only the narrow class; 1 = only the wide class (the two touch disjoint cells,
+// candidate slots and work counters, so they may run on different streams at the same time)
+void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int which) {
     // Two launches at most: levels whose cells fit a 48-byte unshifted tile row (cell width wCell+6 <= 48) and 50 rows —
     // every level of a large image — and the few small levels with wider or taller cells, staged chunk for chunk with
     // the global misalignment kept (wCell, hCell <= 70 always, since nCols = floor(width / 35); 15 + 76 + 4 <= 96).
@@ -498,6 +507,10 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
+        if (which >= 0 && which != wide) {
+            first += cells;
+            continue;
+        }
         if (!wide) {
             if (B.fastMaps) launchClass<64, true, true>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
             else launchClass<48, false, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);

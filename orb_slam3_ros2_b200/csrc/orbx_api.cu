@@ -66,12 +66,12 @@ struct orbx_extractor {
     std::vector<int> nPerLevel;
     cudaStream_t stream = nullptr;
     cudaStream_t aux = nullptr;  // blur runs here, beside FAST + quadtree on `stream` (both only need the pyramid)
-    cudaEvent_t ev[9] = {};      // 0..5 stage boundaries on `stream`; 6 pyramid done -> aux, 7/8 blur begin/end on aux
+    cudaEvent_t ev[10] = {};     // 0..5 stage boundaries on `stream`; 6 pyramid done -> aux, 7/8 blur begin/end on aux, 9 wide FAST done on aux
     // sub-batch mode (orbx_set_subbatches): part p of a batch runs the whole pipeline on subS[p] (+ subX[p] for the blur)
     int nSub = 1;
     bool lastSplit = false;
     cudaStream_t subS[8] = {}, subX[8] = {};
-    cudaEvent_t subFork = nullptr, subBlur0[8] = {}, subBlur1[8] = {}, subDone[8] = {};
+    cudaEvent_t subFork = nullptr, subBlur0[8] = {}, subBlur1[8] = {}, subDone[8] = {}, subPyr[8] = {}, subWide[8] = {};
     // plan + buffers of the current (W, H, capacity F)
     FramePlan plan{};
     bool havePlan = false;
@@ -266,6 +266,12 @@ static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int p
     return O;
 }
 
+// ORBX_FAST_FORK=0 keeps the two FAST cell classes back to back on one stream (A/B measurements)
+static bool forkWideFast() {
+    static const bool on = [] { const char* e = std::getenv("ORBX_FAST_FORK"); return !e || std::atoi(e) != 0; }();
+    return on;
+}
+
 // Sub-batch mode: the batch is cut into nSub contiguous parts, each running the whole pipeline on its own stream pair.
 // Frames are independent, so the parts only share the SMs: one part's latency-bound stages (quadtree, describe) run
 // beside another part's issue-bound ones (FAST, blur, resize) instead of each stage owning the whole GPU in turn.
@@ -273,6 +279,7 @@ static int runPipelineSplit(orbx_extractor* h, const uint8_t* dImgs, int stride,
     const FramePlan& P = h->plan;
     cudaStream_t s = h->stream;
     const int n = h->nSub;
+    const bool forkWide = forkWideFast() && fastHasBothClasses(P);
     cudaEventRecord(h->ev[0], s);
     cudaEventRecord(h->subFork, s);
     for (int p = 0; p < n; ++p) {
@@ -283,7 +290,16 @@ static int runPipelineSplit(orbx_extractor* h, const uint8_t* dImgs, int stride,
         cudaStream_t a = h->subS[p], x = h->subX[p];
         cudaStreamWaitEvent(a, h->subFork, 0);
         launchPyramid(P, B, img, stride, frameStride, f1 - f0, a);
-        launchFast(P, B, f1 - f0, a);
+        if (forkWide) {  // the few wide cells (small levels) run on the blur's stream beside the narrow class
+            cudaEventRecord(h->subPyr[p], a);
+            cudaStreamWaitEvent(x, h->subPyr[p], 0);
+            launchFast(P, B, f1 - f0, x, 1);
+            cudaEventRecord(h->subWide[p], x);
+            launchFast(P, B, f1 - f0, a, 0);
+            cudaStreamWaitEvent(a, h->subWide[p], 0);
+        } else {
+            launchFast(P, B, f1 - f0, a);
+        }
         cudaEventRecord(h->subBlur0[p], a);
         cudaStreamWaitEvent(x, h->subBlur0[p], 0);
         launchBlur(P, B, f1 - f0, x);
@@ -312,7 +328,17 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
     cudaEventRecord(h->ev[0], s);
     launchPyramid(P, B, dImgs, stride, frameStride, F, s);
     cudaEventRecord(h->ev[1], s);
-    launchFast(P, B, F, s);
+    if (forkWideFast() && fastHasBothClasses(P)) {
+        // the wide class (few, expensive cells of the small levels: low occupancy, latency-bound) starts first on the auxiliary
+        // stream and the narrow class fills the rest of every SM beside it
+        cudaStreamWaitEvent(x, h->ev[1], 0);
+        launchFast(P, B, F, x, 1);
+        cudaEventRecord(h->ev[9], x);
+        launchFast(P, B, F, s, 0);
+        cudaStreamWaitEvent(s, h->ev[9], 0);
+    } else {
+        launchFast(P, B, F, s);
+    }
     cudaEventRecord(h->ev[2], s);
     // fork: the quadtree is latency-bound (one CTA per (frame, level), serial rounds with barriers, ~30 % issue rate), the
     // blur is issue-bound and independent of it: run them side by side so the blur fills the quadtree's bubbles
@@ -390,7 +416,7 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     }
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
-    for (int i = 0; i < 9 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    for (int i = 0; i < 10 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e != cudaSuccess) {
         delete h;
         return fail(ORBX_ERR_CUDA, std::string("stream/event creation: ") + cudaGetErrorString(e));
@@ -408,7 +434,7 @@ void orbx_destroy(orbx_handle h) {
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
                      &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn};
     for (DevMem* m : all) m->release();
-    for (int i = 0; i < 9; ++i)
+    for (int i = 0; i < 10; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int p = 0; p < 8; ++p) {
         if (h->subS[p]) cudaStreamDestroy(h->subS[p]);
@@ -416,6 +442,8 @@ void orbx_destroy(orbx_handle h) {
         if (h->subBlur0[p]) cudaEventDestroy(h->subBlur0[p]);
         if (h->subBlur1[p]) cudaEventDestroy(h->subBlur1[p]);
         if (h->subDone[p]) cudaEventDestroy(h->subDone[p]);
+        if (h->subPyr[p]) cudaEventDestroy(h->subPyr[p]);
+        if (h->subWide[p]) cudaEventDestroy(h->subWide[p]);
     }
     if (h->subFork) cudaEventDestroy(h->subFork);
     if (h->aux) cudaStreamDestroy(h->aux);
@@ -626,6 +654,8 @@ int orbx_set_subbatches(orbx_handle h, int n) {
         ORBX_CUDA(cudaEventCreateWithFlags(&h->subBlur0[p], cudaEventDisableTiming));
         ORBX_CUDA(cudaEventCreateWithFlags(&h->subBlur1[p], cudaEventDisableTiming));
         ORBX_CUDA(cudaEventCreateWithFlags(&h->subDone[p], cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->subPyr[p], cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->subWide[p], cudaEventDisableTiming));
     }
     h->nSub = n;
     return ORBX_OK;

@@ -95,7 +95,8 @@ struct Buffers {
 // kernel launchers (each in its own .cu); all asynchronous on `s`
 void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
                    cudaStream_t s);
-void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int which = -1);
+bool fastHasBothClasses(const FramePlan& P);
 void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
 size_t fastMapsBytes();
 size_t levelMapsBytes();
