@@ -398,7 +398,7 @@ FastGeom geomFor(const FramePlan& P, unsigned mask, int pitch, int apitch) {
 
 template <int PITCH, bool SHIFTED, bool TMA>
 void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int cells, const uint32_t* cellTab, int* counter,
-                 cudaStream_t s) {
+                 cudaStream_t s, int perSmCap = 0) {
     const FastGeom g = geomFor(P, mask, PITCH, TMA ? 48 : PITCH);
     const size_t smem = (size_t)g.warpBytes * kWarpsPerCta + 8 * kWarpsPerCta;  // + one mbarrier per warp
     auto kern = fastCellsKernel<PITCH, SHIFTED, TMA>;
@@ -412,6 +412,7 @@ void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int
     // ORBX_FAST_PERSM (measurements only): fewer persistent CTAs per SM leave shared memory for another stream's kernels
     static const int capPerSm = [] { const char* e = std::getenv("ORBX_FAST_PERSM"); return e ? std::atoi(e) : 0; }();
     if (capPerSm > 0) perSm = std::min(perSm, capPerSm);
+    if (perSmCap > 0) perSm = std::min(perSm, perSmCap);
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
     cudaMemsetAsync(counter, 0, sizeof(int), s);
     static const FastMaps kNoMaps{};
@@ -489,8 +490,10 @@ void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab) {
         }
 }
 
-// which: -1 = both classes back to back on s; 0 = only the narrow class; 1 = only the wide class (the two touch disjoint cells,
-// candidate slots and work counters, so they may run on different streams at the same time)
+// which: -1 = both classes back to back on s; 0 = only the narrow class; 1 = only the wide class; 2 = only level 0 of the narrow
+// class, on at most 2 persistent CTAs per SM (it runs beside the resize of levels 1..7, whose CTAs need the rest of the shared
+// memory); 3 = the narrow class without level 0.  The parts touch disjoint cells, candidate slots and work counters, so they
+// may run on different streams at the same time.
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int which) {
     // Two launches at most: levels whose cells fit a 48-byte unshifted tile row (cell width wCell+6 <= 48) and 50 rows —
     // every level of a large image — and the few small levels with wider or taller cells, staged chunk for chunk with
@@ -507,18 +510,38 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int
             cells += L.nCols * L.nRows;
         }
         if (!cells) continue;
-        if (which >= 0 && which != wide) {
+        const bool wanted = which < 0 || (wide ? which == 1 : (which == 0 || which == 2 || which == 3));
+        if (!wanted) {
             first += cells;
             continue;
         }
         if (!wide) {
-            if (B.fastMaps) launchClass<64, true, true>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
-            else launchClass<48, false, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr, s);
+            // the narrow table is level-major: level 0's cells are its first entries
+            int skip = 0, take = cells, cap = 0;
+            unsigned m = mask;
+            int* ctr = B.workCtr;
+            if (which == 2 || which == 3) {
+                const int c0 = (mask & 1u) ? P.lv[0].nCols * P.lv[0].nRows : 0;
+                if (which == 2) { take = c0; m = mask & 1u; cap = 2; ctr = B.workCtr2; }
+                else { skip = c0; take = cells - c0; m = mask & ~1u; }
+            }
+            if (take > 0) {
+                if (B.fastMaps) launchClass<64, true, true>(P, B, F, m, take, B.fastTab + first + skip, ctr, s, cap);
+                else launchClass<48, false, false>(P, B, F, m, take, B.fastTab + first + skip, ctr, s, cap);
+            }
         } else {
             launchClass<96, true, false>(P, B, F, mask, cells, B.fastTab + first, B.workCtr + 1, s);
         }
         first += cells;
     }
+}
+
+// level 0 is in the narrow class and so is at least one more level: the early level-0 launch (which = 2 / 3) applies
+bool fastLevel0Early(const FramePlan& P) {
+    if (P.nlevels < 2 || P.lv[0].nCols <= 0 || P.lv[0].nRows <= 0 || wideLevel(P.lv[0])) return false;
+    for (int l = 1; l < P.nlevels; ++l)
+        if (P.lv[l].nCols > 0 && P.lv[l].nRows > 0 && !wideLevel(P.lv[l])) return true;
+    return false;
 }
 
 }  // namespace orbx

@@ -312,8 +312,8 @@ static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cu
 }
 
 void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
-                   cudaStream_t s) {
-    {
+                   cudaStream_t s, int levels) {
+    if (levels != 1) {
         const LevelPlan& L = P.lv[0];
         const int pw = L.w + 2 * kEdge, ph = L.h + 2 * kEdge;
         const bool aligned = ((reinterpret_cast<uintptr_t>(dImgs) | (uintptr_t)stride | (uintptr_t)frameStride) & 15) == 0;
@@ -330,6 +330,7 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
         }
         countLaunch();
     }
+    if (levels == 0) return;
     for (int l = 1; l < P.nlevels; ++l) {
         // bytes of a source row a 128-column strip can need: 128 * scale + 2, + 15 for the 16-B alignment, rounded to chunks
         const double need = 128.0 * P.lv[l - 1].w / P.lv[l].w + 2 + 15 + 16;

@@ -14,15 +14,15 @@
 //     of the next round (how many non-empty children, where `size >= N` is first reached) needs only scans;
 //   * the only inherently sequential step is std::sort on (count, UL.x) in the second phase: ties are frequent
 //     and libstdc++'s introsort is not stable, so its exact move sequence is replayed by one lane (App. D).
+#include <cstdlib>
+
 #include "orbx_internal.cuh"
 
 namespace orbx {
 namespace {
 
-#ifndef ORBX_QT_THREADS
-#define ORBX_QT_THREADS 128
-#endif
-constexpr int kQT = ORBX_QT_THREADS;  // threads per CTA
+// threads per CTA = template parameter kQT of the kernel: 128 for the usual 1000-2000 feature settings (the co-running blur loses
+// less), 256 for large per-level targets (launchQuadtree)
 
 struct Box {
     short ulx, urx, uly, bry;
@@ -50,6 +50,7 @@ __device__ __forceinline__ Box childBox(const Box& b, int q) {
 }
 
 // In-place exclusive scan of a[0..n) by the whole CTA; returns the total to every thread.
+template <int kQT>
 __device__ int blockScanExclusive(int* a, int n, int* sPartial) {
     const int tid = threadIdx.x;
     const int per = (n + kQT - 1) / kQT;
@@ -207,6 +208,7 @@ struct QtShared {
     int* cellOff;
 };
 
+template <int kQT>
 __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ FramePlan P, const uint32_t* __restrict__ cand,
                                                       const int* __restrict__ cellCnt, uint32_t* __restrict__ gath,
                                                       uint16_t* __restrict__ nidAll, LevelKp* __restrict__ lkp,
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
     const int* cc = cellCnt + (size_t)f * P.nCellsTotal + L.cellBase;
     for (int c = tid; c < nCells; c += kQT) S.cellOff[c] = cc[c];
     __syncthreads();
-    const int n = nCells > 0 ? blockScanExclusive(S.cellOff, nCells, sPartial) : 0;
+    const int n = nCells > 0 ? blockScanExclusive<kQT>(S.cellOff, nCells, sPartial) : 0;
     const int width = L.w - 2 * kMinBorder, height = L.h - 2 * kMinBorder;
     const int nIni = (height > 0 && width > 0) ? (int)roundf((float)width / (float)height) : 0;  // :559
     if (n == 0 || nIni <= 0) {
@@ -283,7 +285,7 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
     __syncthreads();
     for (int r = tid; r < nIni; r += kQT) S.scan[r] = S.cntB[r] > 0;
     __syncthreads();
-    int size = blockScanExclusive(S.scan, nIni, sPartial);
+    int size = blockScanExclusive<kQT>(S.scan, nIni, sPartial);
     for (int r = tid; r < nIni; r += kQT)
         if (S.cntB[r] > 0) {
             const int np = S.scan[r];
@@ -310,14 +312,14 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
         if (phase == 1) {  // breadth pass: every node with more than one point is split (:618-681)
             for (int p = tid; p < size; p += kQT) S.scan[p] = S.cntA[p] > 1;
             __syncthreads();
-            K = blockScanExclusive(S.scan, size, sPartial);
+            K = blockScanExclusive<kQT>(S.scan, size, sPartial);
             for (int p = tid; p < size; p += kQT)
                 if (S.cntA[p] > 1) { S.visit[S.scan[p]] = p; S.rk[p] = S.scan[p]; }
             __syncthreads();
         } else {  // (:692-753) expandable nodes of the previous round, sorted, split from the back until size >= N
             for (int j = tid; j < cLast; j += kQT) S.scan[j] = S.cntA[cLast - 1 - j] > 1;
             __syncthreads();
-            const int m = blockScanExclusive(S.scan, cLast, sPartial);
+            const int m = blockScanExclusive<kQT>(S.scan, cLast, sPartial);
             for (int j = tid; j < cLast; j += kQT) {
                 const int p = cLast - 1 - j;
                 if (S.cntA[p] > 1)
@@ -338,7 +340,7 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
                 // inclusive sizes need the scan; do it on a copy kept in visit[]
                 for (int r = tid; r < m; r += kQT) S.visit[r] = S.cb[r];
                 __syncthreads();
-                blockScanExclusive(S.visit, m, sPartial);
+                blockScanExclusive<kQT>(S.visit, m, sPartial);
                 for (int r = tid; r < m; r += kQT) {
                     const int sz = size + S.visit[r] + S.cb[r] - (r + 1);
                     if (sz >= N) atomicMin(&sRed, r + 1);
@@ -357,7 +359,7 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
                 S.scan[p] = 1;
             }
             __syncthreads();
-            blockScanExclusive(S.scan, size, sPartial);
+            blockScanExclusive<kQT>(S.scan, size, sPartial);
         }
         if (K == 0) break;  // nothing expandable: size == prevSize (:685, :750)
         for (int r = tid; r < K; r += kQT) {
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
             S.cb[r] = (S.ccA[4 * p] > 0) + (S.ccA[4 * p + 1] > 0) + (S.ccA[4 * p + 2] > 0) + (S.ccA[4 * p + 3] > 0);
         }
         __syncthreads();
-        const int C = blockScanExclusive(S.cb, K, sPartial);
+        const int C = blockScanExclusive<kQT>(S.cb, K, sPartial);
         const int newSize = C + size - K;
         if (newSize > NC) {  // cannot happen (size <= N+3); guard the shared arrays anyway
             if (tid == 0) atomicOr(errFlag, 2);
@@ -471,12 +473,22 @@ int qtMaxCells(const FramePlan& P) {
 
 size_t quadtreeSmemBytes(const FramePlan& P) { return qtSmem(qtNodeCap(P), qtMaxCells(P)); }
 
+template <int QT>
+static void launchQuadtreeT(const FramePlan& P, const Buffers& B, int F, int NC, int maxCells, size_t smem, cudaStream_t s) {
+    if (smem > 48 * 1024) cudaFuncSetAttribute(quadtreeKernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    quadtreeKernel<QT><<<dim3(P.nlevels, F), QT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag, NC, maxCells);
+}
+
 void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     const int NC = qtNodeCap(P), maxCells = qtMaxCells(P);
     const size_t smem = qtSmem(NC, maxCells);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(quadtreeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    quadtreeKernel<<<dim3(P.nlevels, F), kQT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag,
-                                                         NC, maxCells);
+    // CTA size by the largest per-level target: 128 threads up to 300 nodes per level (1000 features: 141.2 -> 144.7 k frames/s
+    // against 256), 256 above (2000 features, stereo pairs: 54.5 k pairs/s with 128, 55.7 k with 256; 4000 features at 1080p:
+    // 28.2 k frames/s with 128, 31.0 k with 256); ORBX_QT_THREADS overrides (A/B measurements)
+    static const int forced = [] { const char* e = std::getenv("ORBX_QT_THREADS"); return e ? std::atoi(e) : 0; }();
+    const int qt = forced ? forced : (NC <= 300 ? 128 : 256);
+    if (qt <= 128) launchQuadtreeT<128>(P, B, F, NC, maxCells, smem, s);
+    else launchQuadtreeT<256>(P, B, F, NC, maxCells, smem, s);
     countLaunch();
 }
 }  // namespace orbx

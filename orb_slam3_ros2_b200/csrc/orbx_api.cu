@@ -66,7 +66,7 @@ struct orbx_extractor {
     std::vector<int> nPerLevel;
     cudaStream_t stream = nullptr;
     cudaStream_t aux = nullptr;  // blur runs here, beside FAST + quadtree on `stream` (both only need the pyramid)
-    cudaEvent_t ev[10] = {};     // 0..5 stage boundaries on `stream`; 6 pyramid done -> aux, 7/8 blur begin/end on aux, 9 wide FAST done on aux
+    cudaEvent_t ev[12] = {};     // 0..5 stage boundaries on `stream`; 6 pyramid done -> aux, 7/8 blur begin/end on aux, 9 wide FAST done on aux, 10 level 0 of the pyramid done, 11 (unused)
     // sub-batch mode (orbx_set_subbatches): part p of a batch runs the whole pipeline on subS[p] (+ subX[p] for the blur)
     int nSub = 1;
     bool lastSplit = false;
@@ -247,7 +247,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.cand = (uint32_t*)h->mCand.p; B.cellCnt = (int*)h->mCellCnt.p; B.gath = (uint32_t*)h->mGath.p;
     B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.sorted = (LevelKp*)h->mSlot.p;
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
-    B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4;
+    B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4; B.workCtr2 = B.errFlag + 32;
     B.fastMaps = h->useTma ? h->fastMaps : nullptr; B.frame0 = 0;
     B.blurMaps = h->useTma ? h->blurMaps : nullptr; B.pyrMaps = h->useTma ? h->pyrMaps : nullptr; B.blurTab = (uint32_t*)h->mBlurTab.p;
     return ORBX_OK;
@@ -262,6 +262,7 @@ static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int p
     O.sorted += f * P.outCap; O.outKps = (uint8_t*)O.outKps + f * P.outCap * 28; O.outDesc += f * P.outCap * 32;
     O.outN += f; O.outMono += f;
     O.workCtr = B.errFlag + 4 + 2 * part;
+    O.workCtr2 = B.errFlag + 32 + part;
     O.frame0 = B.frame0 + f0;
     return O;
 }
@@ -269,6 +270,13 @@ static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int p
 // ORBX_FAST_FORK=0 keeps the two FAST cell classes back to back on one stream (A/B measurements)
 static bool forkWideFast() {
     static const bool on = [] { const char* e = std::getenv("ORBX_FAST_FORK"); return !e || std::atoi(e) != 0; }();
+    return on;
+}
+
+// ORBX_FAST_EARLY=1 starts level 0's FAST beside the resize chain (A/B measurements; measured no gain: pyramid + FAST
+// 0.396 + 0.506 ms apart, 0.543 + 0.371 ms overlapped, profiles/r01_v15_e2e_sweep.txt) - off by default
+static bool earlyLevel0Fast() {
+    static const bool on = [] { const char* e = std::getenv("ORBX_FAST_EARLY"); return e && std::atoi(e) != 0; }();
     return on;
 }
 
@@ -326,18 +334,38 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
     cudaStream_t s = h->stream;
     cudaStream_t x = h->aux;
     cudaEventRecord(h->ev[0], s);
-    launchPyramid(P, B, dImgs, stride, frameStride, F, s);
-    cudaEventRecord(h->ev[1], s);
-    if (forkWideFast() && fastHasBothClasses(P)) {
-        // the wide class (few, expensive cells of the small levels: low occupancy, latency-bound) starts first on the auxiliary
-        // stream and the narrow class fills the rest of every SM beside it
-        cudaStreamWaitEvent(x, h->ev[1], 0);
-        launchFast(P, B, F, x, 1);
+    const bool forkWide = forkWideFast() && fastHasBothClasses(P);
+    if (earlyLevel0Fast() && fastLevel0Early(P)) {
+        // level 0 holds a third of the cells and needs no resize: its FAST starts on the auxiliary stream as soon as the level-0
+        // plane is written and runs (on 2 CTAs per SM) beside the resize chain of levels 1..7, whose kernels are barrier- and
+        // latency-bound (60 % issue) and leave it the issue slots
+        launchPyramid(P, B, dImgs, stride, frameStride, F, s, 0);
+        cudaEventRecord(h->ev[10], s);
+        cudaStreamWaitEvent(x, h->ev[10], 0);
+        launchFast(P, B, F, x, 2);
+        launchPyramid(P, B, dImgs, stride, frameStride, F, s, 1);
+        cudaEventRecord(h->ev[1], s);
+        if (fastHasBothClasses(P)) {
+            cudaStreamWaitEvent(x, h->ev[1], 0);
+            launchFast(P, B, F, x, 1);
+        }
         cudaEventRecord(h->ev[9], x);
-        launchFast(P, B, F, s, 0);
+        launchFast(P, B, F, s, 3);
         cudaStreamWaitEvent(s, h->ev[9], 0);
     } else {
-        launchFast(P, B, F, s);
+        launchPyramid(P, B, dImgs, stride, frameStride, F, s);
+        cudaEventRecord(h->ev[1], s);
+        if (forkWide) {
+            // the wide class (few, expensive cells of the small levels: low occupancy, latency-bound) starts first on the
+            // auxiliary stream and the narrow class fills the rest of every SM beside it
+            cudaStreamWaitEvent(x, h->ev[1], 0);
+            launchFast(P, B, F, x, 1);
+            cudaEventRecord(h->ev[9], x);
+            launchFast(P, B, F, s, 0);
+            cudaStreamWaitEvent(s, h->ev[9], 0);
+        } else {
+            launchFast(P, B, F, s);
+        }
     }
     cudaEventRecord(h->ev[2], s);
     // fork: the quadtree is latency-bound (one CTA per (frame, level), serial rounds with barriers, ~30 % issue rate), the
@@ -416,7 +444,7 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     }
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
-    for (int i = 0; i < 10 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    for (int i = 0; i < 12 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e != cudaSuccess) {
         delete h;
         return fail(ORBX_ERR_CUDA, std::string("stream/event creation: ") + cudaGetErrorString(e));
@@ -434,7 +462,7 @@ void orbx_destroy(orbx_handle h) {
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
                      &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn};
     for (DevMem* m : all) m->release();
-    for (int i = 0; i < 10; ++i)
+    for (int i = 0; i < 12; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int p = 0; p < 8; ++p) {
         if (h->subS[p]) cudaStreamDestroy(h->subS[p]);

@@ -83,6 +83,7 @@ struct Buffers {
     int16_t* tab;        // resize coefficient tables
     int* errFlag;        // device-side invariant violations (capacity overflow)
     uint32_t* fastTab;   // FAST cell table of the plan (buildFastCellTable)
+    int* workCtr2;       // work counter of the early level-0 FAST launch
     int* workCtr;        // two work counters of the persistent FAST launches (distinct per concurrently running sub-batch)
     const void* fastMaps;  // host copy of the per-level TMA tensor maps over the whole pyramid allocation (buildFastMaps);
                            // nullptr = stage FAST tiles with ordinary loads (ORBX_FAST_TMA=0)
@@ -93,8 +94,10 @@ struct Buffers {
 };
 
 // kernel launchers (each in its own .cu); all asynchronous on `s`
+// levels: -1 = whole pyramid; 0 = only level 0 (copy + border); 1 = only levels >= 1 (level 0 must be complete on the stream)
 void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
-                   cudaStream_t s);
+                   cudaStream_t s, int levels = -1);
+bool fastLevel0Early(const FramePlan& P);
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int which = -1);
 bool fastHasBothClasses(const FramePlan& P);
 void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
