@@ -89,6 +89,7 @@ struct orbx_extractor {
     DevMem mBlurTab;
     bool useTma = true;
     DevMem mKpsUn;           // orbx_undistort_batch: mvKeysUn of the last batch, [frame][cap]
+    bool kpsUnValid = false;  // mKpsUn belongs to the CURRENT batch (cleared by every extraction)
     DevMem mRaw, mStageTab;  // orbx_extract_color: raw colour frame and the staging resize tables
     int stagedW = 0, stagedH = 0;
     std::vector<uint8_t> hStage;  // pinned staging would be the caller's; this is only for get_* taps
@@ -327,6 +328,7 @@ static int runPipelineSplit(orbx_extractor* h, const uint8_t* dImgs, int stride,
 
 // the whole operator() pipeline for F device-resident frames, asynchronous on the handle's stream
 static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size_t frameStride, int F, int lap0, int lap1) {
+    h->kpsUnValid = false;
     if (h->nSub > 1 && F >= 8 * h->nSub) return runPipelineSplit(h, dImgs, stride, frameStride, F, lap0, lap1);
     h->lastSplit = false;
     const FramePlan& P = h->plan;
@@ -1336,6 +1338,7 @@ int orbx_undistort_batch(orbx_handle h, const float* K, const float* dist, int n
     else
         launchUndistort(h->buf.outKps, h->mKpsUn.p, h->buf.outN, 0, F, cap, C, s);
     ORBX_CUDA(cudaGetLastError());
+    h->kpsUnValid = true;
     if (d_kps_un) *d_kps_un = (const orbx_keypoint*)h->mKpsUn.p;
     if (kps_un) {
         ORBX_CUDA(cudaMemcpyAsync(kps_un, h->mKpsUn.p, bytes, cudaMemcpyDeviceToHost, s));
@@ -1402,7 +1405,7 @@ int orbx_search_for_initialization_batch(orbx_handle h, int use_undistorted, flo
     if (!(max_x > min_x) || !(max_y > min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
     const int F = h->lastFrames, cap = h->plan.outCap;
     if (cap > gridSortCapacity()) return fail(ORBX_ERR_ARG, "more than 32768 keypoints per frame");
-    if (use_undistorted && h->mKpsUn.bytes < (size_t)F * cap * sizeof(orbx_keypoint))
+    if (use_undistorted && (!h->kpsUnValid || h->mKpsUn.bytes < (size_t)F * cap * sizeof(orbx_keypoint)))
         return fail(ORBX_ERR_STATE, "orbx_undistort_batch has not run on this batch");
     if (F < 2) return ORBX_OK;
     DeviceGuard guard(h->device);

@@ -233,4 +233,8 @@ def test_search_for_initialization_batch_equals_per_pair(orbx, oracle):
             assert nm[p] == want[0] and np.array_equal(m12[p, :n[p]], want[1]), (und, p)
             assert prev[p, :n[p]].tobytes() == want[2].tobytes()
             assert nm[p] > 50
+    # a new extraction invalidates the undistorted keypoints of the previous batch
+    e.extract_batch(frames[:2], (0, 1000))
+    with pytest.raises(orbx.OrbxError):
+        orbx.search_for_initialization_batch(e, bounds, 100, 0.9, True, use_undistorted=True)
     e.close()
