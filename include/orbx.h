@@ -255,8 +255,8 @@ int orbx_undistort_batch(orbx_handle h, const float* K, const float* dist, int n
  * i1 at a smaller or equal distance (vMatchedDistance, :687-688), accept best <= TH_LOW && best < second * nnratio, take the
  * point over from an earlier worse match (:701-709), rotation histogram + ComputeThreeMaxima (:2012-2053) when
  * check_orientation.  prev_matched: n1 x 2 floats = vbPrevMatched, updated for matched keypoints (:756-759).
- * matches12: n1 ints = vnMatches12 (-1 = none).  *nmatches = the return value.  The i1 loop is order dependent and runs in
- * order on one warp per frame pair.
+ * matches12: n1 ints = vnMatches12 (-1 = none).  *nmatches = the return value.  The window queries and distances (order
+ * independent) run one warp per keypoint; the i1 loop itself is order dependent and runs in order on one warp per frame pair.
  * _batch: pair p = frame p -> frame p + 1 of the handle's last batch, read in place on the device (use_undistorted != 0: the
  * mvKeysUn of orbx_undistort_batch), vbPrevMatched = frame p's own keypoints as Tracking::MonocularInitialization sets it
  * (Tracking.cc:2479-2481, called at :2512).  matches12: [frames-1][cap_per_frame], nmatches: [frames-1], prev_matched (may be NULL):

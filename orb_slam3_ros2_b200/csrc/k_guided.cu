@@ -329,7 +329,96 @@ struct InitArgs {
     int* m21;          // scratch [pair][stride] (vnMatches21)
     int* binOf;        // scratch [pair][stride] rotation bin of i1's push, -1 = none
     int* nMatches;     // [pair]
+    // candidate lists of phase A (initCandKernel): per (pair, i1) the window's candidates in visiting order as dist << 20 | index,
+    // kInitListCap entries at most; candCount > kInitListCap = the list overflowed and the walk is redone here
+    uint32_t* candList; int* candCount;
 };
+constexpr int kInitListCap = kSearchInitListCap;
+
+// Phase A, one warp per (pair, i1): the order-independent part of SearchForInitialization — the window query of
+// Frame::GetFeaturesInArea(vbPrevMatched[i1], windowSize, level1, level1) (Frame.cc:657-723) and the Hamming distance of every
+// candidate — written as a list in the reference's visiting order.  The order-dependent part (vMatchedDistance gate, best /
+// second, accept, take-over) is phase B, which then only streams these lists.
+__global__ void __launch_bounds__(256) initCandKernel(const InitArgs A, int pairs) {
+    __shared__ int sColB[8][64], sPre[8][65];
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, wip = threadIdx.x >> 5;
+    const int pair = wid / A.stride, i1 = wid - pair * A.stride;
+    if (pair >= pairs) return;
+    const size_t o = (size_t)pair * A.stride;
+    const int n1 = A.n1Arr ? min(A.n1Arr[pair], A.stride) : A.n1;
+    if (i1 >= n1) return;
+    const float* k1 = A.kps1 + o * 7;
+    const float* k2 = A.kps2 + o * 7;
+    const int level1 = __float_as_int(k1[i1 * 7 + 5]);
+    if (level1 > 0) return;
+    int* colB = sColB[wip];
+    int* pre = sPre[wip];
+    const uint4* d1 = A.desc1 + o * 2;
+    const uint4* d2 = A.desc2 + o * 2;
+    const uint32_t* sorted = A.sorted2 + o;
+    const int* cellStart = A.cellStart2 + (size_t)pair * (kGridCells + 1);
+    const float x = A.prevFromKps ? k1[i1 * 7] : A.prev[(o + i1) * 2], y = A.prevFromKps ? k1[i1 * 7 + 1] : A.prev[(o + i1) * 2 + 1];
+    const float r = A.r;
+    uint32_t* list = A.candList + (o + i1) * kInitListCap;
+    int count = 0;
+    const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), r), A.invW)));
+    const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), r), A.invW)));
+    const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), r), A.invH)));
+    const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), r), A.invH)));
+    if (!(minCX >= kGridCols || maxCX < 0 || minCY >= kGridRows || maxCY < 0 || minCX > maxCX || minCY > maxCY)) {
+        const int ncols = maxCX - minCX + 1;
+        int b0 = 0, len0 = 0, b1 = 0, len1 = 0;
+        if (lane < ncols) {
+            b0 = cellStart[(minCX + lane) * kGridRows + minCY];
+            len0 = cellStart[(minCX + lane) * kGridRows + maxCY + 1] - b0;
+        }
+        if (lane + 32 < ncols) {
+            b1 = cellStart[(minCX + lane + 32) * kGridRows + minCY];
+            len1 = cellStart[(minCX + lane + 32) * kGridRows + maxCY + 1] - b1;
+        }
+        int s0 = len0, s1 = len1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t0 = __shfl_up_sync(0xffffffffu, s0, d), t1 = __shfl_up_sync(0xffffffffu, s1, d);
+            if (lane >= d) { s0 += t0; s1 += t1; }
+        }
+        const int tot0 = __shfl_sync(0xffffffffu, s0, 31), total = tot0 + __shfl_sync(0xffffffffu, s1, 31);
+        colB[lane] = b0; colB[lane + 32] = b1;
+        pre[lane + 1] = s0; pre[lane + 33] = tot0 + s1;
+        if (lane == 0) pre[0] = 0;
+        __syncwarp();
+        const uint4 a0 = d1[2 * i1], a1 = d1[2 * i1 + 1];
+        for (int t0 = 0; t0 < total; t0 += 32) {
+            const int t = t0 + lane;
+            bool ok = false;
+            uint32_t entry = 0;
+            if (t < total) {
+                int lo = 0, hi = ncols - 1;
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (pre[mid] <= t) lo = mid; else hi = mid - 1;
+                }
+                const int idx = (int)(sorted[colB[lo] + (t - pre[lo])] & 0xfffffu);
+                const int oct = __float_as_int(k2[idx * 7 + 5]);
+                const float x2 = k2[idx * 7], y2 = k2[idx * 7 + 1];
+                ok = true;
+                if (level1 >= 0) ok = !(oct < level1) && !(oct > level1);
+                ok = ok && fabsf(__fsub_rn(x2, x)) < r && fabsf(__fsub_rn(y2, y)) < r;
+                if (ok) {
+                    const uint4 c0 = d2[2 * idx], c1 = d2[2 * idx + 1];
+                    const int dist = __popc(a0.x ^ c0.x) + __popc(a0.y ^ c0.y) + __popc(a0.z ^ c0.z) + __popc(a0.w ^ c0.w) +
+                                     __popc(a1.x ^ c1.x) + __popc(a1.y ^ c1.y) + __popc(a1.z ^ c1.z) + __popc(a1.w ^ c1.w);
+                    entry = ((uint32_t)dist << 20) | (uint32_t)idx;
+                }
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            const int pos = count + __popc(bal & ((1u << lane) - 1u));
+            if (ok && pos < kInitListCap) list[pos] = entry;
+            count += __popc(bal);
+        }
+    }
+    if (lane == 0) A.candCount[o + i1] = count;
+}
 
 __global__ void __launch_bounds__(32) searchInitKernel(const InitArgs A) {
     __shared__ int colB[64], pre[65], hist[30], keep[3];
@@ -356,61 +445,80 @@ __global__ void __launch_bounds__(32) searchInitKernel(const InitArgs A) {
     __syncwarp();
     int nmatches = 0;
     const float factor = 1.0f / 30.0f;  // :656
+    int lvlBlock = 0, cntBlock = -1;
     for (int i1 = 0; i1 < n1; ++i1) {
-        const int level1 = __float_as_int(k1[i1 * 7 + 5]);
+        // octave and list length of 32 consecutive keypoints are fetched by the lanes at once (two dependent loads per i1 less)
+        if ((i1 & 31) == 0) {
+            const int j = i1 + lane;
+            lvlBlock = j < n1 ? __float_as_int(k1[j * 7 + 5]) : 1;
+            cntBlock = (A.candCount && j < n1 && lvlBlock <= 0) ? A.candCount[o + j] : -1;
+        }
+        const int level1 = __shfl_sync(0xffffffffu, lvlBlock, i1 & 31);
+        const int listed = __shfl_sync(0xffffffffu, cntBlock, i1 & 31);
         if (level1 > 0) continue;  // :665-666
-        const float x = prev[2 * i1], y = prev[2 * i1 + 1], r = A.r;
-        // Frame::GetFeaturesInArea, Frame.cc:665-687
-        const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), r), A.invW)));
-        const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), r), A.invW)));
-        const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), r), A.invH)));
-        const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), r), A.invH)));
-        if (minCX >= kGridCols || maxCX < 0 || minCY >= kGridRows || maxCY < 0 || minCX > maxCX || minCY > maxCY) continue;
-        const int ncols = maxCX - minCX + 1;
-        int b0 = 0, len0 = 0, b1 = 0, len1 = 0;
-        if (lane < ncols) {
-            b0 = cellStart[(minCX + lane) * kGridRows + minCY];
-            len0 = cellStart[(minCX + lane) * kGridRows + maxCY + 1] - b0;
-        }
-        if (lane + 32 < ncols) {
-            b1 = cellStart[(minCX + lane + 32) * kGridRows + minCY];
-            len1 = cellStart[(minCX + lane + 32) * kGridRows + maxCY + 1] - b1;
-        }
-        int s0 = len0, s1 = len1;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t0 = __shfl_up_sync(0xffffffffu, s0, d), t1 = __shfl_up_sync(0xffffffffu, s1, d);
-            if (lane >= d) { s0 += t0; s1 += t1; }
-        }
-        const int tot0 = __shfl_sync(0xffffffffu, s0, 31), total = tot0 + __shfl_sync(0xffffffffu, s1, 31);
-        __syncwarp();
-        colB[lane] = b0; colB[lane + 32] = b1;
-        pre[lane + 1] = s0; pre[lane + 33] = tot0 + s1;
-        if (lane == 0) pre[0] = 0;
-        __syncwarp();
-        const uint4 a0 = d1[2 * i1], a1 = d1[2 * i1 + 1];
         unsigned long long key1 = ~0ull, key2 = ~0ull;  // distance << 48 | visit position << 24 | index
-        for (int t0 = 0; t0 < total; t0 += 32) {
-            const int t = t0 + lane;
-            if (t < total) {
-                int lo = 0, hi = ncols - 1;  // the column with pre[c] <= t < pre[c + 1]
-                while (lo < hi) {
-                    const int mid = (lo + hi + 1) >> 1;
-                    if (pre[mid] <= t) lo = mid; else hi = mid - 1;
-                }
-                const int idx = (int)(sorted[colB[lo] + (t - pre[lo])] & 0xfffffu);
-                const int oct = __float_as_int(k2[idx * 7 + 5]);
-                const float x2 = k2[idx * 7], y2 = k2[idx * 7 + 1];
-                // minLevel = maxLevel = level1 (<= 0): bCheckLevels is true because maxLevel >= 0 or, for a negative level1, false
-                bool ok = true;
-                if (level1 >= 0) ok = !(oct < level1) && !(oct > level1);
-                ok = ok && fabsf(__fsub_rn(x2, x)) < r && fabsf(__fsub_rn(y2, y)) < r;
-                if (ok) {
-                    const uint4 c0 = d2[2 * idx], c1 = d2[2 * idx + 1];
-                    const int dist = __popc(a0.x ^ c0.x) + __popc(a0.y ^ c0.y) + __popc(a0.z ^ c0.z) + __popc(a0.w ^ c0.w) +
-                                     __popc(a1.x ^ c1.x) + __popc(a1.y ^ c1.y) + __popc(a1.z ^ c1.z) + __popc(a1.w ^ c1.w);
-                    if (!(md[idx] <= dist))  // :687-688
-                        top2Insert(key1, key2, ((unsigned long long)dist << 48) | ((unsigned long long)t << 24) | (unsigned)idx);
+        if (listed >= 0 && listed <= kInitListCap) {
+            // phase A's list (already in visiting order, distances attached): only the order-dependent gate is left
+            const uint32_t* list = A.candList + (o + i1) * kInitListCap;
+            for (int t = lane; t < listed; t += 32) {
+                const uint32_t e = list[t];
+                const int idx = (int)(e & 0xfffffu), dist = (int)(e >> 20);
+                if (!(md[idx] <= dist))  // :687-688
+                    top2Insert(key1, key2, ((unsigned long long)dist << 48) | ((unsigned long long)t << 24) | (unsigned)idx);
+            }
+        } else {
+            const float x = prev[2 * i1], y = prev[2 * i1 + 1], r = A.r;
+            // Frame::GetFeaturesInArea, Frame.cc:665-687
+            const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), r), A.invW)));
+            const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), r), A.invW)));
+            const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), r), A.invH)));
+            const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), r), A.invH)));
+            const bool inGrid = !(minCX >= kGridCols || maxCX < 0 || minCY >= kGridRows || maxCY < 0 || minCX > maxCX || minCY > maxCY);
+            const int ncols = inGrid ? maxCX - minCX + 1 : 0;
+            int b0 = 0, len0 = 0, b1 = 0, len1 = 0;
+            if (lane < ncols) {
+                b0 = cellStart[(minCX + lane) * kGridRows + minCY];
+                len0 = cellStart[(minCX + lane) * kGridRows + maxCY + 1] - b0;
+            }
+            if (lane + 32 < ncols) {
+                b1 = cellStart[(minCX + lane + 32) * kGridRows + minCY];
+                len1 = cellStart[(minCX + lane + 32) * kGridRows + maxCY + 1] - b1;
+            }
+            int s0 = len0, s1 = len1;
+    #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t0 = __shfl_up_sync(0xffffffffu, s0, d), t1 = __shfl_up_sync(0xffffffffu, s1, d);
+                if (lane >= d) { s0 += t0; s1 += t1; }
+            }
+            const int tot0 = __shfl_sync(0xffffffffu, s0, 31), total = tot0 + __shfl_sync(0xffffffffu, s1, 31);
+            __syncwarp();
+            colB[lane] = b0; colB[lane + 32] = b1;
+            pre[lane + 1] = s0; pre[lane + 33] = tot0 + s1;
+            if (lane == 0) pre[0] = 0;
+            __syncwarp();
+            const uint4 a0 = d1[2 * i1], a1 = d1[2 * i1 + 1];
+            for (int t0 = 0; t0 < total; t0 += 32) {
+                const int t = t0 + lane;
+                if (t < total) {
+                    int lo = 0, hi = ncols - 1;  // the column with pre[c] <= t < pre[c + 1]
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) >> 1;
+                        if (pre[mid] <= t) lo = mid; else hi = mid - 1;
+                    }
+                    const int idx = (int)(sorted[colB[lo] + (t - pre[lo])] & 0xfffffu);
+                    const int oct = __float_as_int(k2[idx * 7 + 5]);
+                    const float x2 = k2[idx * 7], y2 = k2[idx * 7 + 1];
+                    // minLevel = maxLevel = level1 (<= 0): bCheckLevels is true because maxLevel >= 0 or, for a negative level1, false
+                    bool ok = true;
+                    if (level1 >= 0) ok = !(oct < level1) && !(oct > level1);
+                    ok = ok && fabsf(__fsub_rn(x2, x)) < r && fabsf(__fsub_rn(y2, y)) < r;
+                    if (ok) {
+                        const uint4 c0 = d2[2 * idx], c1 = d2[2 * idx + 1];
+                        const int dist = __popc(a0.x ^ c0.x) + __popc(a0.y ^ c0.y) + __popc(a0.z ^ c0.z) + __popc(a0.w ^ c0.w) +
+                                         __popc(a1.x ^ c1.x) + __popc(a1.y ^ c1.y) + __popc(a1.z ^ c1.z) + __popc(a1.w ^ c1.w);
+                        if (!(md[idx] <= dist))  // :687-688
+                            top2Insert(key1, key2, ((unsigned long long)dist << 48) | ((unsigned long long)t << 24) | (unsigned)idx);
+                    }
                 }
             }
         }
@@ -584,10 +692,11 @@ void launchUndistort(const void* kpsIn, void* kpsOut, const int* nPerFrame, int 
 // frames = 1: single pair (kps2 / desc2 are F2's arrays, n1 / n2 given); frames > 1: pair p = frame p -> frame p + 1 of a
 // [frame][cap] batch (kps2 = kps1, counts from nPerFrame).  sorted / cellStart: scratch for F2's grids (frames x cap,
 // frames x 3073 ints); prev / m12 / scratch3: pairs x cap (x 2 floats for prev; scratch3 = 3 int arrays back to back).
+// candList / candCount (may be NULL: phase B then walks every window itself): pairs x cap x kInitListCap words, pairs x cap ints.
 void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void* kps2, const uint8_t* desc2, int n2, const int* nPerFrame,
                       int frames, int cap, float minX, float maxX, float minY, float maxY, int windowSize, float nnratio, int checkOri,
                       int prevFromKps, uint32_t* sorted, int* cellStart, float* prev, int* m12, int* scratch3, int* nMatches,
-                      cudaStream_t s) {
+                      cudaStream_t s, uint32_t* candList, int* candCount) {
     const float invW = (float)kGridCols / (maxX - minX), invH = (float)kGridRows / (maxY - minY);  // Frame.cc:251-252
     const bool batch = nPerFrame != nullptr;
     int nPow2 = 32;
@@ -613,6 +722,12 @@ void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void
         gridSortKernel<<<1, 1024, smem, s>>>(static_cast<const float*>(kps2), n2, nPow2, minX, minY, invW, invH, sorted, cellStart, nullptr, 0);
         A.kps2 = static_cast<const float*>(kps2); A.desc2 = reinterpret_cast<const uint4*>(desc2);
         A.sorted2 = sorted; A.cellStart2 = cellStart;
+    }
+    A.candList = candList; A.candCount = candCount;
+    if (candList && candCount) {  // phase A: one warp per (pair, i1); slots of higher-level or absent keypoints are never read
+        const long long warps = (long long)pairs * cap;
+        initCandKernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, s>>>(A, pairs);
+        countLaunch();
     }
     searchInitKernel<<<pairs, 32, 0, s>>>(A);
     countLaunch(2);

@@ -1385,10 +1385,19 @@ int orbx_search_for_initialization(const orbx_keypoint* kps1, const uint8_t* des
         ORBX_CUDA(cudaMemcpyAsync(D, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
         ORBX_CUDA(cudaMemcpyAsync(D + oK2, kps2, (size_t)n2 * 28, cudaMemcpyHostToDevice, s));
     }
+    // candidate lists of phase A (ORBX_INIT_LISTS=0: phase B walks every window itself, A/B measurements)
+    static const bool useLists = [] { const char* e = std::getenv("ORBX_INIT_LISTS"); return !e || std::atoi(e) != 0; }();
+    uint32_t* candList = nullptr;
+    int* candCount = nullptr;
+    if (useLists) {
+        ORBX_CUDA(S->k1.reserve(cap * (size_t)(kSearchInitListCap + 1) * 4 + 64));
+        candList = (uint32_t*)S->k1.p;
+        candCount = (int*)(candList + cap * (size_t)kSearchInitListCap);
+    }
     // stride = cap so that the three scratch arrays (pairs x stride each, pairs = 1) are laid out back to back
     launchSearchInit(Q + oK1, Q, n1, D + oK2, D, n2, nullptr, 1, (int)cap, min_x, max_x, min_y, max_y, window_size, nnratio,
                      check_orientation != 0, 0, (uint32_t*)(D + oSo), (int*)(D + oCs), (float*)(Q + oPrev), (int*)(Q + oM12),
-                     (int*)(D + oScr), (int*)(Q + oN), s);
+                     (int*)(D + oScr), (int*)(Q + oN), s, candList, candCount);
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(matches12, Q + oM12, A * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(prev_matched, Q + oPrev, A * 8, cudaMemcpyDeviceToHost, s));
@@ -1422,9 +1431,17 @@ int orbx_search_for_initialization_batch(orbx_handle h, int use_undistorted, flo
     ORBX_CUDA(cudaEventRecord(h->ev[6], h->stream));  // behind the extraction (and the undistortion) on the handle's stream
     ORBX_CUDA(cudaStreamWaitEvent(s, h->ev[6], 0));
     const void* kps = use_undistorted ? h->mKpsUn.p : h->buf.outKps;
+    static const bool useLists = [] { const char* e = std::getenv("ORBX_INIT_LISTS"); return !e || std::atoi(e) != 0; }();
+    uint32_t* candList = nullptr;
+    int* candCount = nullptr;
+    if (useLists) {
+        ORBX_CUDA(S->k1.reserve(T * (size_t)(kSearchInitListCap + 1) * 4 + 64));
+        candList = (uint32_t*)S->k1.p;
+        candCount = (int*)(candList + T * (size_t)kSearchInitListCap);
+    }
     launchSearchInit(kps, h->buf.outDesc, 0, nullptr, nullptr, 0, h->buf.outN, F, cap, min_x, max_x, min_y, max_y, window_size, nnratio,
                      check_orientation != 0, 1, (uint32_t*)M, (int*)(M + oCs), (float*)(M + oPrev), (int*)(M + oM12), (int*)(M + oScr),
-                     (int*)(M + oN), s);
+                     (int*)(M + oN), s, candList, candCount);
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(matches12, M + oM12, T * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(nmatches, M + oN, P * 4, cudaMemcpyDeviceToHost, s));

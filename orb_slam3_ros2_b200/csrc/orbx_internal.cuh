@@ -149,7 +149,8 @@ void launchStereoRefine(const FramePlan& P, const float* sf, const float* isf, c
 void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void* kps2, const uint8_t* desc2, int n2, const int* nPerFrame,
                       int frames, int cap, float minX, float maxX, float minY, float maxY, int windowSize, float nnratio, int checkOri,
                       int prevFromKps, uint32_t* sorted, int* cellStart, float* prev, int* m12, int* scratch3, int* nMatches,
-                      cudaStream_t s);
+                      cudaStream_t s, uint32_t* candList = nullptr, int* candCount = nullptr);
+constexpr int kSearchInitListCap = 64;  // = kInitListCap of k_guided.cu
 // Frame::UndistortKeyPoints: the pinhole model in doubles, as cv::undistortPoints converts it (k = k1 k2 p1 p2 k3 k4 k5 k6 s1..s4)
 struct UndistortCam {
     double ifx, ify, cx, cy;
