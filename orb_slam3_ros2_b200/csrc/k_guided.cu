@@ -687,6 +687,7 @@ void launchUndistort(const void* kpsIn, void* kpsOut, const int* nPerFrame, int 
     if (frames <= 0 || cap <= 0 || (!nPerFrame && nSingle <= 0)) return;
     const int most = nPerFrame ? cap : nSingle;
     undistortKernel<<<dim3((most + 127) / 128, frames), 128, 0, s>>>((const float*)kpsIn, (float*)kpsOut, nPerFrame, nSingle, cap, C);
+    countLaunch();
 }
 
 // frames = 1: single pair (kps2 / desc2 are F2's arrays, n1 / n2 given); frames > 1: pair p = frame p -> frame p + 1 of a

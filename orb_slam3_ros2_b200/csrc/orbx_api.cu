@@ -1263,6 +1263,7 @@ static int undistortCam(const float* K, const float* dist, int ndist, const floa
     if (!K || !P || ndist < 0 || ndist > 12 || (ndist > 0 && !dist)) return fail(ORBX_ERR_ARG, "bad camera");
     if (ndist != 0 && ndist != 4 && ndist != 5 && ndist != 8 && ndist != 12)
         return fail(ORBX_ERR_ARG, "distortion vector must have 4, 5, 8 or 12 coefficients");  // cv::undistortPoints' own check
+    if (K[0] == 0.0f || K[4] == 0.0f) return fail(ORBX_ERR_ARG, "camera matrix with a zero focal length");
     C->ifx = 1. / (double)K[0];
     C->ify = 1. / (double)K[4];
     C->cx = (double)K[2];

@@ -161,6 +161,10 @@ def test_undistort_keypoints_and_image_bounds_bit_exact(orbx, oracle, name):
         assert got.tobytes() == kps.tobytes()
     assert orbx.image_bounds(w, h, K, dist).tobytes() == oracle.image_bounds(w, h, K, dist).tobytes()
     assert len(orbx.undistort_keypoints(kps[:0], K, dist)) == 0
+    with pytest.raises(orbx.OrbxError):  # zero focal length, 3 coefficients: rejected, as cv::undistortPoints asserts
+        orbx.undistort_keypoints(kps[:4], np.zeros((3, 3), np.float32), dist)
+    with pytest.raises(orbx.OrbxError):
+        orbx.undistort_keypoints(kps[:4], K, np.array([0.1, 0.2, 0.3], np.float32))
     # a different projection matrix P than K (cv::undistortPoints' last argument)
     P = K.copy(); P[0, 0] *= 0.9; P[1, 1] *= 1.1; P[0, 2] += 3.5
     assert orbx.undistort_keypoints(kps[:500], K, dist, P).tobytes() == oracle.undistort_keypoints(kps[:500], K, dist, P).tobytes()
