@@ -69,6 +69,12 @@ void orbx_destroy(orbx_handle h);
 int orbx_get_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
                     int* features_per_level);
 
+/* Upper bound of the keypoints operator() returns for a w x hgt frame = the room kps / desc / cap_per_frame must offer:
+ * the sum over the levels of max(N_l + 4, 4 * nIni_l + 1).  DistributeOctTree (ORBextractor.cc:555-779) stops splitting at
+ * the first node count >= N_l (each split adds at most 3), but its first breadth pass splits every one of the
+ * nIni_l = round(width / height) root nodes whatever N_l is (:610-681), so small nfeatures return more than N_l + 3. */
+int orbx_capacity(orbx_handle h, int w, int hgt, int* cap);
+
 /* ---- single frame: ORBextractor::operator() (ORBextractor.cc:1086-1168) ---------------------------
  * img: host, 8-bit single channel, `stride` bytes per row.  lap0/lap1 = vLappingArea[0..1].
  * kps/desc: host outputs with room for `cap` keypoints (desc is cap x 32 bytes).  *n_out = number of

@@ -40,6 +40,7 @@
 
 #include "orbx_internal.cuh"
 #include "tma.cuh"
+#include "fast_common.cuh"
 
 namespace orbx {
 namespace {
@@ -50,36 +51,7 @@ namespace {
 constexpr int kWarpsPerCta = ORBX_FAST_WARPS;
 constexpr int kPixCap = 256;      // pixel list capacity per warp (one segment of flagged pixels)
 
-__device__ __forceinline__ uint32_t max3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2(a, b, c); }
-__device__ __forceinline__ uint32_t min3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_s16x2(a, b, c); }
-
 using FastMaps = LevelMaps;
-
-// arc strength of two pixels at once: q[k] = ring pixel k of pixel A in the low half, of pixel B in the high half
-__device__ __forceinline__ uint32_t arcStrength2(const uint32_t (&q)[16], uint32_t cen) {
-    uint32_t mx3[16], mn3[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        mx3[k] = max3(q[k], q[(k + 1) & 15], q[(k + 2) & 15]);
-        mn3[k] = min3(q[k], q[(k + 1) & 15], q[(k + 2) & 15]);
-    }
-    uint32_t mx9[16], mn9[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        mx9[k] = max3(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
-        mn9[k] = min3(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
-    }
-    // A = min_k max9_k (strongest "centre brighter": I - A), B = max_k min9_k ("centre darker": B - I)
-    uint32_t A = min3(mx9[0], mx9[1], mx9[2]), B = max3(mn9[0], mn9[1], mn9[2]);
-#pragma unroll
-    for (int k = 3; k < 15; k += 2) {
-        A = min3(A, mx9[k], mx9[k + 1]);
-        B = max3(B, mn9[k], mn9[k + 1]);
-    }
-    A = __vmins2(A, mx9[15]);
-    B = __vmaxs2(B, mn9[15]);
-    return __vimax3_s16x2_relu(__vsub2(cen, A), __vsub2(B, cen), 0u);
-}
 
 // PITCH = bytes per tile row in shared memory (multiple of 16).
 // SHIFTED = true : tile x = cell x + (global column & 15): rows are copied chunk for chunk (cells up to 76 px wide).
@@ -94,13 +66,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 32 / kWarpsPerCta)
     fastCellsKernel(const __grid_constant__ FramePlan P, const __grid_constant__ FastMaps M, const uint8_t* __restrict__ pyr,
                     uint32_t* __restrict__ cand, int* __restrict__ cellCnt, int rowsMax, int itemsMax, int warpBytes,
                     const uint32_t* __restrict__ cellTab, int cellsInLaunch, int totalWork, int* __restrict__ workCounter,
-                    int frame0) {
+                    int frame0, const unsigned long long* __restrict__ fbList, const int* __restrict__ fbCount) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int P16 = PITCH / 16;
     constexpr int APITCH = TMA ? 48 : PITCH, A16 = APITCH / 16;
     static_assert(!TMA || SHIFTED, "the TMA box starts on a 16-byte boundary: the tile keeps the shift");
     const int lane = threadIdx.x & 31, wip = threadIdx.x >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
+    // LIST MODE (fbList != nullptr): the work items are the (frame, cell) entries the strip kernel (k_fast_strip.cu) left
+    // behind - cells with no corner at iniThFAST (entry bit 31 set: start at the minThFAST pass, ORBextractor.cc:843-846)
+    // and the cells of strips whose lists overflowed (both passes); their number is only known on the device
+    if (fbList) {
+        totalWork = min(__ldg(fbCount), totalWork);
+        if (totalWork <= 0) return;
+    }
     // per-warp mbarrier of the TMA staging, behind the warps' work areas
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (size_t)kWarpsPerCta * warpBytes) + wip;
     uint32_t barPhase = 0;
@@ -120,9 +99,18 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 32 / kWarpsPerCta)
     if (lane == 0) work = atomicAdd(workCounter, 1);
     work = __shfl_sync(0xffffffffu, work, 0);
     if (work >= totalWork) break;
-    const int f = work / cellsInLaunch;
-    // (level, cell row, cell column) of the launch's k-th cell: a table built with the plan (level-major, row-major)
-    const uint32_t ce = __ldg(cellTab + (work - f * cellsInLaunch));
+    int f, pass0 = 0;
+    uint32_t ce;
+    if (fbList) {
+        const unsigned long long e = fbList[work];
+        f = (int)(e >> 32);
+        ce = (uint32_t)e & 0x7fffffffu;
+        pass0 = (int)((uint32_t)e >> 31);
+    } else {
+        f = work / cellsInLaunch;
+        // (level, cell row, cell column) of the launch's k-th cell: a table built with the plan (level-major, row-major)
+        ce = __ldg(cellTab + (work - f * cellsInLaunch));
+    }
     const int l = (int)(ce >> 24), ci = (int)((ce >> 12) & 0xfffu), cj = (int)(ce & 0xfffu);
     const LevelPlan& L = P.lv[l];
     const int c = ci * L.nCols + cj;
@@ -210,7 +198,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 32 / kWarpsPerCta)
     const int tIni = max(P.iniTh, 1), tMin = max(P.minTh, 1);
 
     int kept = 0;
-    for (int pass = 0; pass < 2; ++pass) {
+    for (int pass = pass0; pass < 2; ++pass) {
         const int t = pass == 0 ? tIni : tMin;
         if (pass == 1 && (kept > 0 || tMin >= tIni)) break;  // :843-846: redo at minThFAST only if nothing was found
         // per byte: ((d & 0x7f) + K) | d has bit 7 set iff d > tq, tq = min(t, 126) (a NECESSARY condition for t > 126)
@@ -418,13 +406,34 @@ void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int
     static const FastMaps kNoMaps{};
     const FastMaps& maps = TMA ? *reinterpret_cast<const FastMaps*>(B.fastMaps) : kNoMaps;
     kern<<<grid, kWarpsPerCta * 32, smem, s>>>(P, maps, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, cellTab, cells,
-                                                (int)total, counter, B.frame0);
+                                                (int)total, counter, B.frame0, nullptr, nullptr);
+    countLaunch();
+}
+
+// list mode: a fixed grid of persistent CTAs walks the device-side list (count read on the device; nothing to do = the
+// CTAs leave at once)
+template <int PITCH, bool SHIFTED, bool TMA>
+void launchClassList(const FramePlan& P, const Buffers& B, unsigned mask, const unsigned long long* list, const int* count, int cap,
+                     int* counter, cudaStream_t s) {
+    const FastGeom g = geomFor(P, mask, PITCH, TMA ? 48 : PITCH);
+    const size_t smem = (size_t)g.warpBytes * kWarpsPerCta + 8 * kWarpsPerCta;
+    auto kern = fastCellsKernel<PITCH, SHIFTED, TMA>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = (int)std::min<long long>(((long long)cap + kWarpsPerCta - 1) / kWarpsPerCta, 2LL * sms);
+    static const FastMaps kNoMaps{};
+    const FastMaps& maps = TMA ? *reinterpret_cast<const FastMaps*>(B.fastMaps) : kNoMaps;
+    kern<<<grid, kWarpsPerCta * 32, smem, s>>>(P, maps, B.pyr, B.cand, B.cellCnt, g.rowsMax, g.itemsMax, g.warpBytes, nullptr, 1, cap, counter,
+                                                B.frame0, list, count);
     countLaunch();
 }
 
 }  // namespace
 
 static bool wideLevel(const LevelPlan& L);
+bool fastWideLevel(const LevelPlan& L) { return wideLevel(L); }
 
 size_t fastMapsBytes() { return sizeof(FastMaps); }
 
@@ -534,6 +543,24 @@ void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int
         }
         first += cells;
     }
+}
+
+// The strip kernel's leftovers: list 0 = narrow-class cells, list 1 = wide-class cells (fbList[cls * cap ..], fbCount[cls]).
+// The work counters B.workCtr[0..1] must be zero (the caller clears them together with the list counts).
+void launchFastFallback(const FramePlan& P, const Buffers& B, int F, const unsigned long long* fbList, const int* fbCount, int cap,
+                        cudaStream_t s) {
+    (void)F;
+    unsigned maskN = 0, maskW = 0;
+    for (int l = 0; l < P.nlevels; ++l) {
+        const LevelPlan& L = P.lv[l];
+        if (L.nCols <= 0 || L.nRows <= 0) continue;
+        (wideLevel(L) ? maskW : maskN) |= 1u << l;
+    }
+    if (maskN) {
+        if (B.fastMaps) launchClassList<64, true, true>(P, B, maskN, fbList, fbCount, cap, B.workCtr, s);
+        else launchClassList<48, false, false>(P, B, maskN, fbList, fbCount, cap, B.workCtr, s);
+    }
+    if (maskW) launchClassList<96, true, false>(P, B, maskW, fbList + cap, fbCount + 1, cap, B.workCtr + 1, s);
 }
 
 // level 0 is in the narrow class and so is at least one more level: the early level-0 launch (which = 2 / 3) applies

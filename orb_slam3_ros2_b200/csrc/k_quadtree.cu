@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
         __syncthreads();
         const int C = blockScanExclusive<kQT>(S.cb, K, sPartial);
         const int newSize = C + size - K;
-        if (newSize > NC) {  // cannot happen (size <= N+3); guard the shared arrays anyway
+        if (newSize > NC) {  // cannot happen (size <= max(N + 3, 4 * nIni)); guard the shared arrays anyway
             if (tid == 0) atomicOr(errFlag, 2);
             break;
         }
@@ -460,7 +460,8 @@ int qtNodeCap(const FramePlan& P) {
         const int width = P.lv[l].w - 2 * kMinBorder, height = P.lv[l].h - 2 * kMinBorder;
         const int nIni = (height > 0 && width > 0) ? (int)roundf((float)width / (float)height) : 0;
         nc = P.lv[l].nFeat + 8 > nc ? P.lv[l].nFeat + 8 : nc;
-        nc = nIni + 8 > nc ? nIni + 8 : nc;
+        // the first breadth pass splits EVERY multi-point root whatever N is (:610-681): up to 4 * nIni nodes
+        nc = 4 * nIni + 8 > nc ? 4 * nIni + 8 : nc;
     }
     return nc;
 }

@@ -87,6 +87,9 @@ struct orbx_extractor {
     alignas(64) unsigned char blurMaps[kMaxLevels * 128];
     alignas(64) unsigned char pyrMaps[kMaxLevels * 128];
     DevMem mBlurTab;
+    alignas(64) unsigned char stripMaps[kMaxLevels * 128];
+    DevMem mStripTab, mFb;
+    bool useStrips = true;  // FAST over strips of the cell grid (k_fast_strip.cu); ORBX_FAST_STRIP=0 = per-cell kernels only
     bool useTma = true;
     DevMem mKpsUn;           // orbx_undistort_batch: mvKeysUn of the last batch, [frame][cap]
     bool kpsUnValid = false;  // mKpsUn belongs to the CURRENT batch (cleared by every extraction)
@@ -139,6 +142,14 @@ static void resizeTable(int srcN, int dstN, bool xAxis, std::vector<int16_t>& ou
     }
 }
 
+// per-level keypoint capacity: DistributeOctTree returns at most max(N + 3, 4 * nIni) nodes — phase 2 stops at the first split
+// that reaches N (+3 at most), but the first breadth pass splits every root whatever N is (ORBextractor.cc:610-681)
+static int levelKpCap(int nFeat, int lw, int lh) {
+    const float width = (float)(lw - 2 * kMinBorder), height = (float)(lh - 2 * kMinBorder);
+    const int nIni = (width > 0 && height > 0) ? (int)std::round(width / height) : 0;  // :559
+    return std::max(nFeat + 4, 4 * nIni + 1);
+}
+
 static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab) {
     FramePlan& P = h->plan;
     std::memset(&P, 0, sizeof(P));
@@ -171,7 +182,7 @@ static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab)
         L.gathOff = gathOff; gathOff += (unsigned)L.maxCand;
         if (L.maxCand >= (1 << 24)) return fail(ORBX_ERR_ARG, "level too large (candidate index exceeds 24 bits)");
         L.nFeat = h->nPerLevel[l];
-        L.lkpBase = lkpBase; L.lkpCap = L.nFeat + 4; lkpBase += L.lkpCap;
+        L.lkpBase = lkpBase; L.lkpCap = levelKpCap(L.nFeat, L.w, L.h); lkpBase += L.lkpCap;
         L.scale = h->sf[l];
         L.patchSize = (float)(int)(kPatch * h->sf[l]);  // :879
         if (l > 0) {
@@ -187,6 +198,7 @@ static int buildPlan(orbx_extractor* h, int W, int H, std::vector<int16_t>& tab)
     P.blurTiles = blurTiles;
     P.lkpTotal = lkpBase;
     P.outCap = lkpBase;
+    planFastStrips(P);
     if (quadtreeSmemBytes(P) > 220 * 1024) return fail(ORBX_ERR_ARG, "nfeatures too large for the quadtree kernel's shared memory");
     return ORBX_OK;
 }
@@ -209,6 +221,12 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         if ((int)btiles.size() != h->plan.blurTiles) return fail(ORBX_ERR_CUDA, "blur tile table does not match the plan");
         ORBX_CUDA(h->mBlurTab.reserve(std::max<size_t>(btiles.size() * 4, 16)));
         ORBX_CUDA(cudaMemcpyAsync(h->mBlurTab.p, btiles.data(), btiles.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        std::vector<uint32_t> strips;
+        buildFastStripTable(h->plan, strips);
+        if (strips.size() != (size_t)h->plan.stripTiles * 16) return fail(ORBX_ERR_CUDA, "FAST strip table does not match the plan");
+        ORBX_CUDA(h->mStripTab.reserve(std::max<size_t>(strips.size() * 4, 16)));
+        if (!strips.empty())
+            ORBX_CUDA(cudaMemcpyAsync(h->mStripTab.p, strips.data(), strips.size() * 4, cudaMemcpyHostToDevice, h->stream));
         ORBX_CUDA(cudaStreamSynchronize(h->stream));
         h->havePlan = true;
         h->capFrames = 0;
@@ -229,7 +247,8 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         ORBX_CUDA(h->mOutD.reserve(f * P.outCap * 32));
         ORBX_CUDA(h->mOutN.reserve(f * 4));
         ORBX_CUDA(h->mOutM.reserve(f * 4));
-        ORBX_CUDA(h->mErr.reserve(256));  // [0] error flags, [4 + 2p ..] work counters of persistent kernels, sub-batch p
+        ORBX_CUDA(h->mFb.reserve(std::max<size_t>(2 * f * P.nCellsTotal * 8, 16)));
+        ORBX_CUDA(h->mErr.reserve(256));  // [0] error flags, [4 + 2p ..] work counters of persistent kernels, sub-batch p; [32 + p] early level-0 FAST; [40 + 2p ..] fallback list counts
         ORBX_CUDA(cudaMemsetAsync(h->mErr.p, 0, 256, h->stream));
         h->capFrames = F;
         if (h->useTma) {
@@ -241,6 +260,10 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
             if (rb != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for the blur tiles (" + std::to_string(rb) + ")");
             const int rp = buildPyrMaps(P, (const uint8_t*)h->mPyr.p, F, h->pyrMaps);
             if (rp != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for the resize rows (" + std::to_string(rp) + ")");
+            if (h->useStrips) {
+                const int rs = buildStripMaps(P, (const uint8_t*)h->mPyr.p, F, h->stripMaps);
+                if (rs != 0) return fail(ORBX_ERR_CUDA, "cuTensorMapEncodeTiled failed for the FAST strips (" + std::to_string(rs) + ")");
+            }
         }
     }
     Buffers& B = h->buf;
@@ -251,11 +274,13 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4; B.workCtr2 = B.errFlag + 32;
     B.fastMaps = h->useTma ? h->fastMaps : nullptr; B.frame0 = 0;
     B.blurMaps = h->useTma ? h->blurMaps : nullptr; B.pyrMaps = h->useTma ? h->pyrMaps : nullptr; B.blurTab = (uint32_t*)h->mBlurTab.p;
+    B.stripMaps = (h->useTma && h->useStrips) ? h->stripMaps : nullptr; B.stripTab = (uint32_t*)h->mStripTab.p;
+    B.fbList = (unsigned long long*)h->mFb.p; B.fbCount = B.errFlag + 40; B.fbCap = h->capFrames * P.nCellsTotal;
     return ORBX_OK;
 }
 
 // Buffers of frames [f0, ...) of the batch, with the work counters of sub-batch `part`
-static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int part) {
+static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int part, int nFrames) {
     Buffers O = B;
     const size_t f = (size_t)f0;
     O.pyr += f * P.frameBytes; O.blur += f * P.blurBytes; O.cand += f * P.candWords; O.cellCnt += f * P.nCellsTotal;
@@ -264,6 +289,7 @@ static Buffers offsetBuffers(const Buffers& B, const FramePlan& P, int f0, int p
     O.outN += f; O.outMono += f;
     O.workCtr = B.errFlag + 4 + 2 * part;
     O.workCtr2 = B.errFlag + 32 + part;
+    O.fbList = B.fbList + 2 * f * P.nCellsTotal; O.fbCount = B.errFlag + 40 + 2 * part; O.fbCap = nFrames * P.nCellsTotal;
     O.frame0 = B.frame0 + f0;
     return O;
 }
@@ -294,12 +320,14 @@ static int runPipelineSplit(orbx_extractor* h, const uint8_t* dImgs, int stride,
     for (int p = 0; p < n; ++p) {
         const int f0 = (int)((long long)F * p / n), f1 = (int)((long long)F * (p + 1) / n);
         if (f1 <= f0) continue;
-        const Buffers B = offsetBuffers(h->buf, P, f0, p);
+        const Buffers B = offsetBuffers(h->buf, P, f0, p, f1 - f0);
         const uint8_t* img = dImgs + (size_t)f0 * frameStride;
         cudaStream_t a = h->subS[p], x = h->subX[p];
         cudaStreamWaitEvent(a, h->subFork, 0);
         launchPyramid(P, B, img, stride, frameStride, f1 - f0, a);
-        if (forkWide) {  // the few wide cells (small levels) run on the blur's stream beside the narrow class
+        if (B.stripMaps) {
+            launchFastStrips(P, B, f1 - f0, a);
+        } else if (forkWide) {  // the few wide cells (small levels) run on the blur's stream beside the narrow class
             cudaEventRecord(h->subPyr[p], a);
             cudaStreamWaitEvent(x, h->subPyr[p], 0);
             launchFast(P, B, f1 - f0, x, 1);
@@ -337,7 +365,11 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
     cudaStream_t x = h->aux;
     cudaEventRecord(h->ev[0], s);
     const bool forkWide = forkWideFast() && fastHasBothClasses(P);
-    if (earlyLevel0Fast() && fastLevel0Early(P)) {
+    if (B.stripMaps) {
+        launchPyramid(P, B, dImgs, stride, frameStride, F, s);
+        cudaEventRecord(h->ev[1], s);
+        launchFastStrips(P, B, F, s);
+    } else if (earlyLevel0Fast() && fastLevel0Early(P)) {
         // level 0 holds a third of the cells and needs no resize: its FAST starts on the auxiliary stream as soon as the level-0
         // plane is written and runs (on 2 CTAs per SM) beside the resize chain of levels 1..7, whose kernels are barrier- and
         // latency-bound (60 % issue) and leave it the issue slots
@@ -443,6 +475,8 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     {
         const char* t = std::getenv("ORBX_FAST_TMA");  // 0 = stage FAST tiles with ordinary loads (A/B measurements only)
         h->useTma = !(t && t[0] == '0');
+        const char* st = std::getenv("ORBX_FAST_STRIP");  // 0 = the per-cell FAST kernels only (A/B measurements)
+        h->useStrips = !(st && st[0] == '0');
     }
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
@@ -456,13 +490,23 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     return ORBX_OK;
 }
 
+int orbx_capacity(orbx_handle h, int w, int hgt, int* cap) {
+    if (!h || !cap) return fail(ORBX_ERR_ARG, "null argument");
+    if (w < 1 || hgt < 1) return fail(ORBX_ERR_ARG, "bad frame size");
+    int sum = 0;
+    for (int l = 0; l < h->prm.nlevels; ++l)
+        sum += levelKpCap(h->nPerLevel[l], cvRoundF((float)w * h->isf[l]), cvRoundF((float)hgt * h->isf[l]));
+    *cap = sum;
+    return ORBX_OK;
+}
+
 void orbx_destroy(orbx_handle h) {
     if (!h) return;
     DeviceGuard guard(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
-                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn};
+                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn, &h->mStripTab, &h->mFb};
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 12; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);

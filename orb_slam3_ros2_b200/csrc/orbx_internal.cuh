@@ -38,9 +38,10 @@ struct LevelPlan {
     unsigned gathOff;    // word offset of the level's gathered candidate list in a frame's gather block
     int nFeat;           // mnFeaturesPerLevel[l]
     int lkpBase;         // first slot of this level in the frame's level-keypoint array
-    int lkpCap;          // nFeat + 4 (F5: the quadtree returns N..N+3)
+    int lkpCap;          // max(nFeat + 4, 4 * nIni + 1) (F5: the quadtree returns N..N+3, or the 4 * nIni children of the roots)
     int tabX, tabY;      // offsets into the resize coefficient table (int16 triplets ofs,a0,a1)
     int blurTile0, blurTilesX;  // first 128x32 blur tile of the level in the launch's tile list, tiles per row
+    int stripCells, stripSegs, stripPitch;  // FAST strips (k_fast_strip.cu): cells per strip, strips per cell row, tile pitch (bytes)
     float scale;         // mvScaleFactor[l]
     float patchSize;     // (float)(int)(31*scale) (ORBextractor.cc:879)
 };
@@ -55,6 +56,7 @@ struct FramePlan {
     int iniTh, minTh;
     int fpMode;
     int blurTiles;      // total 128x32 tiles over all levels
+    int stripTiles;     // FAST strips per frame over all levels
     LevelPlan lv[kMaxLevels];
 };
 
@@ -90,6 +92,11 @@ struct Buffers {
     const void* blurMaps;  // the same for the blur's 144 x 38 input tiles (buildBlurMaps); nullptr = ordinary loads
     const void* pyrMaps;   // source-level maps of the resize kernels' staged rows (buildPyrMaps); nullptr = ordinary loads
     uint32_t* blurTab;   // blur tile table of the plan (buildBlurTileTable)
+    const void* stripMaps;  // per-level tensor maps of the FAST strips (buildStripMaps); nullptr = per-cell FAST kernels only
+    uint32_t* stripTab;     // strip table of the plan (buildFastStripTable)
+    unsigned long long* fbList;  // [2][fbCap] cells the strip kernel hands to the per-cell kernel (narrow / wide class)
+    int* fbCount;           // [2]
+    int fbCap;              // frames x cells per frame
     int frame0;          // first frame of these buffers inside the allocation (z coordinate base of the tensor maps)
 };
 
@@ -99,6 +106,14 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
                    cudaStream_t s, int levels = -1);
 bool fastLevel0Early(const FramePlan& P);
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int which = -1);
+// strip-wise FAST (k_fast_strip.cu): the whole stage = strips at iniThFAST + the per-cell kernel on what they leave behind
+void planFastStrips(FramePlan& P);
+void buildFastStripTable(const FramePlan& P, std::vector<uint32_t>& tab);
+int buildStripMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
+void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void launchFastFallback(const FramePlan& P, const Buffers& B, int F, const unsigned long long* fbList, const int* fbCount, int cap,
+                        cudaStream_t s);
+bool fastWideLevel(const LevelPlan& L);
 bool fastHasBothClasses(const FramePlan& P);
 void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
 size_t fastMapsBytes();

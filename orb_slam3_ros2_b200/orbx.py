@@ -97,6 +97,7 @@ SYMBOLS = {
                                      C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_search_by_bow_kf": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p,
                                         _i32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
+    "orbx_capacity": (C.c_int, [_vp, C.c_int, C.c_int, _i32p]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_voc_create": (C.c_int, [C.c_int, _i32p, _u8p, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(_vp)]),
     "orbx_voc_destroy": (None, [_vp]),
@@ -179,13 +180,20 @@ class ORBextractor:
 
     @property
     def capacity(self):
-        """Upper bound of keypoints per frame (sum over levels of N_l + 4)."""
-        return int(self._nfeat.sum()) + 4 * self.nlevels
+        """Upper bound of keypoints per frame for the size of the last frames seen (orbx_capacity: sum over the levels of
+        max(N_l + 4, 4 * nIni_l + 1)); before any frame, the size-independent part sum(N_l + 4)."""
+        return self._cap if getattr(self, "_cap", 0) else int(self._nfeat.sum()) + 4 * self.nlevels
+
+    def capacity_for(self, w, h):
+        c = C.c_int32(0)
+        _check(lib().orbx_capacity(self._h, int(w), int(h), C.byref(c)))
+        self._cap = int(c.value)
+        return self._cap
 
     # --- operator() (ORBextractor.cc:1086-1168)
     def __call__(self, image, mask=None, vLappingArea=(0, 1000), pyramid=True):
         """-> (monoIndex, keypoints[KP_DTYPE], descriptors[n,32]).  `mask` is ignored, as in the reference."""
-        cap = self.capacity
+        cap = self.capacity if image is None or image.size == 0 else self.capacity_for(image.shape[1], image.shape[0])
         kps = np.zeros(cap, dtype=KP_DTYPE)
         desc = np.zeros((cap, 32), dtype=np.uint8)
         n, mono = C.c_int32(0), C.c_int32(0)
@@ -215,7 +223,7 @@ class ORBextractor:
         ch = 1 if image.ndim == 2 else image.shape[2]
         h, w = image.shape[:2]
         nw, nh = new_size if new_size else (0, 0)
-        cap = self.capacity
+        cap = self.capacity_for(nw or w, nh or h)
         kps = np.zeros(cap, dtype=KP_DTYPE)
         desc = np.zeros((cap, 32), dtype=np.uint8)
         n, mono = C.c_int32(0), C.c_int32(0)
@@ -259,7 +267,7 @@ class ORBextractor:
         """images: (F, H, W) uint8 host array.  -> (mono[F], n[F], kps[F,cap], desc[F,cap,32])"""
         images = np.ascontiguousarray(images, dtype=np.uint8)
         F, h, w = images.shape
-        cap = self.capacity
+        cap = self.capacity_for(w, h)
         n = np.zeros(F, dtype=np.int32)
         mono = np.zeros(F, dtype=np.int32)
         kps = np.zeros((F, cap), dtype=KP_DTYPE) if download else None
@@ -294,6 +302,7 @@ class ORBextractor:
         _check(lib().orbx_extract_batch_device(self._h, dev_ptr, F, w, h, stride or w, frame_stride or w * h,
                                                vLappingArea[0], vLappingArea[1]))
         self._frames = F
+        self.capacity_for(w, h)
 
     def sync(self):
         _check(lib().orbx_sync(self._h))

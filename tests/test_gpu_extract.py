@@ -185,3 +185,11 @@ def test_subbatch_streams_give_identical_results(orbx, nsub):
             for f in range(F - 1):
                 assert np.array_equal(a[f, :n[f]], b[f, :n[f]])
     assert ex.timing()[0] > 0
+
+
+@pytest.mark.parametrize("w,h,nf", [(752, 480, 40), (752, 480, 100), (1241, 376, 100), (1241, 376, 150)])
+def test_small_nfeatures_match_reference(orbx, oracle, w, h, nf):
+    """A level returns up to 4 * nIni keypoints when its target N is smaller than that (the first breadth pass of
+    DistributeOctTree splits every root, ORBextractor.cc:610-681): capacity max(N + 4, 4 * nIni + 1) per level."""
+    n = _vs(orbx, oracle, synth.frame(7, w, h), nf, (0, 1000))
+    assert n >= nf

@@ -97,3 +97,14 @@ def test_port_equals_reference_binary_on_fresh_inputs(oracle):
     for k, (w, h, nf) in enumerate([(752, 480, 1000), (640, 480, 300), (500, 500, 1500), (900, 300, 800)]):
         total += _compare_with_ref(oracle, synth.frame(20 + k, w, h), nf, (0, 1000), "native" if k % 2 else "strict")
     assert total > 5000
+
+
+@pytest.mark.parametrize("w,h,nf", [(752, 480, 40), (752, 480, 100), (1241, 376, 100), (1241, 376, 150)])
+def test_port_equals_reference_for_small_nfeatures(oracle, w, h, nf):
+    """DistributeOctTree's first breadth pass splits every root whatever N is (ORBextractor.cc:610-681), so a level can
+    return up to 4 * nIni keypoints when N is smaller than that: more than N + 3 and, summed, more than nfeatures + 3 * nlevels."""
+    if not oracle.have_ref("strict"):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    n = _compare_with_ref(oracle, synth.frame(7, w, h), nf, (0, 1000))
+    if (w, h, nf) == (1241, 376, 100):
+        assert n > nf + 3 * 8  # the case the N + 3 bound misses (16 keypoints on levels whose target is 13 and less)
