@@ -36,17 +36,34 @@
 namespace orbx {
 namespace {
 
-constexpr int kListCap = 4096;    // flagged pixels per strip (u16 entries: tile row << 8 | tile x)
-constexpr int kCornerCap = 1536;  // corners per strip
+// flagged pixels per strip (u16 entries: tile row << 8 | tile x) and corners per strip (3/8 of that): ORBX_STRIP_LIST
+static int stripListCap() {
+    static const int v = [] {
+        const char* e = std::getenv("ORBX_STRIP_LIST");
+        const int n = e ? std::atoi(e) : 0;
+        return n >= 256 && n <= 16384 ? (n & ~63) : 4096;
+    }();
+    return v;
+}
+// widest strip in tested columns (one TMA box: 15 + width + 6 <= 256): ORBX_STRIP_MAXW
+static int stripMaxWidth() {
+    static const int v = [] {
+        const char* e = std::getenv("ORBX_STRIP_MAXW");
+        const int n = e ? std::atoi(e) : 0;
+        return n >= 16 && n <= 235 ? n : 235;
+    }();
+    return v;
+}
 constexpr int kKeptCap = 128;     // survivors per strip ranked by counting; more = bitmap walk
 constexpr int kBmWords = 8;       // bitmap words per row (tile pitch <= 256)
 constexpr int kMaxStripCells = 32;
 
 // one strip, everything derived on the host (16 ints = four 128-bit loads per thread instead of ~80 integer instructions)
 struct StripDesc {
-    int level;      // level | class << 8 (class 1 = the per-cell kernel's wide class)
+    int level;      // level | class << 8 (class 1 = the per-cell kernel's wide class) | (hCell + 6) << 16
     int pitch;      // tile pitch TP (bytes, multiple of 16, <= 256)
-    int wCell, hCell;
+    int wCell;
+    unsigned divW;  // 65536 / wCell + 1: (x * divW) >> 16 == x / wCell for x < 256
     int nCells;     // cells of the strip
     int testedW;    // tested columns of the strip (<= 0: nothing to test)
     int nRy;        // tested rows (<= 0: nothing to test)
@@ -63,7 +80,8 @@ static_assert(sizeof(StripDesc) == 64, "four 128-bit loads");
 struct StripLayout {
     int tileBytes, arcBytes, bmBytes, total;
 };
-__host__ __device__ inline StripLayout stripLayout(int rowsMax, int pitchMax) {
+__host__ __device__ inline StripLayout stripLayout(int rowsMax, int pitchMax, int kListCap) {
+    const int kCornerCap = kListCap * 3 / 8;
     StripLayout s;
     s.tileBytes = (rowsMax * pitchMax + 127) & ~127;
     s.arcBytes = ((rowsMax - 4) * pitchMax + 15) & ~15;
@@ -76,7 +94,8 @@ template <int NT>
 __global__ void __launch_bounds__(NT)
     fastStripKernel(const __grid_constant__ LevelMaps M, const StripDesc* __restrict__ stripTab, uint32_t* __restrict__ cand,
                     int* __restrict__ cellCnt, unsigned long long* __restrict__ fbList, int* __restrict__ fbCount, int fbCap,
-                    int candWords, int nCellsTotal, int tIni, int tMin, int rowsMax, int pitchMax, int frame0) {
+                    int candWords, int nCellsTotal, int tIni, int tMin, int rowsMax, int pitchMax, int frame0, int kListCap) {
+    const int kCornerCap = kListCap * 3 / 8;
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.y;
@@ -97,7 +116,7 @@ __global__ void __launch_bounds__(NT)
         return;
     }
 
-    const StripLayout lay = stripLayout(rowsMax, pitchMax);
+    const StripLayout lay = stripLayout(rowsMax, pitchMax, kListCap);
     uint8_t* tile = smem;                                   // [hCell + 6][TP]; tile x = sub-image x + shift
     uint8_t* arcStore = tile + lay.tileBytes;               // [nRy + 2][TP]: arc strength of tile rows 2 .. nRy + 3 (first / last stay 0)
     uint32_t* bitmap = reinterpret_cast<uint32_t*>(arcStore + lay.arcBytes);  // [nRy][kBmWords]: survivors, bit = tile x
@@ -109,13 +128,11 @@ __global__ void __launch_bounds__(NT)
     uint64_t* bar = reinterpret_cast<uint64_t*>(ctr + 8);
 
     // ---- stage the strip: one TMA box, first byte on a 16-byte boundary of the plane row (the tile keeps the shift) ----
+    // thread 0 alone owns the mbarrier (init, expect, wait); the block barrier behind its wait publishes the tile
     if (tid == 0) {
         mbarInit(bar, 1);
         mbarInitFence();
-    }
-    __syncthreads();
-    if (tid == 0) {
-        mbarExpectTx(bar, (uint32_t)(TP * (D.hCell + 6)));
+        mbarExpectTx(bar, (uint32_t)(TP * (D.level >> 16)));
         tmaLoadTile(tile, &M.m[D.level & 0xff], D.gx, D.gy, frame0 + f, bar);
     }
     {
@@ -127,13 +144,13 @@ __global__ void __launch_bounds__(NT)
         for (int i = tid; i < nB; i += NT) b4[i] = make_uint4(0, 0, 0, 0);
         if (tid < kMaxStripCells + 8) cellKept[tid] = 0;  // + the counters behind it
     }
-    mbarWait(bar, 0);
+    if (tid == 0) mbarWait(bar, 0);
     __syncthreads();
 
     const int xs = shift + 3, xe = xs + testedW;  // tested tile columns; tested tile rows are [3, 3 + nRy)
     const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(tile);
     const uint4* tile128 = reinterpret_cast<const uint4*>(tile);
-    const unsigned divW = 65536u / (unsigned)wCell + 1u;  // (x * divW) >> 16 == x / wCell for x < 256, wCell <= 76
+    const unsigned divW = D.divW;
 
     // ---- quick reject of the tile columns [rxa, rxb) at threshold t, 16 pixels per lane (any 9-arc holds
     // ring[0] or ring[8] and ring[4] or ring[12]); the flagged pixels are appended to `list` ----------------------------------
@@ -317,7 +334,7 @@ __global__ void __launch_bounds__(NT)
         }
     };
 
-    const int cls = (D.level >> 8) & 1;
+    const int cls = (D.level >> 8) & 1;  // bits 16.. hold the tile rows
     auto handOver = [&](int clA, int clB, uint32_t flag) {  // cells [clA, clB) go to the per-cell kernel (it writes their counts)
         const int cl = clA + tid;
         if (cl < clB) {
@@ -396,7 +413,7 @@ void planFastStrips(FramePlan& P) {
         LevelPlan& L = P.lv[l];
         L.stripCells = L.stripSegs = L.stripPitch = 0;
         if (L.nCols <= 0 || L.nRows <= 0) continue;
-        const int maxCells = std::min(kMaxStripCells, std::max(1, (256 - 15 - 6) / L.wCell));
+        const int maxCells = std::min(kMaxStripCells, std::max(1, stripMaxWidth() / L.wCell));
         L.stripSegs = (L.nCols + maxCells - 1) / maxCells;
         L.stripCells = (L.nCols + L.stripSegs - 1) / L.stripSegs;
         L.stripSegs = (L.nCols + L.stripCells - 1) / L.stripCells;
@@ -417,9 +434,10 @@ void buildFastStripTable(const FramePlan& P, std::vector<uint32_t>& tab) {
             for (int sg = 0; sg < L.stripSegs; ++sg) {
                 StripDesc D;
                 const int cj0 = sg * L.stripCells;
-                D.level = l | (fastWideLevel(L) ? 0x100 : 0);
+                D.level = l | (fastWideLevel(L) ? 0x100 : 0) | ((L.hCell + 6) << 16);
                 D.pitch = L.stripPitch;
-                D.wCell = L.wCell; D.hCell = L.hCell;
+                D.wCell = L.wCell;
+                D.divW = 65536u / (unsigned)L.wCell + 1u;
                 D.nCells = std::min(L.stripCells, L.nCols - cj0);
                 // tested pixels relative to the level's tested origin (19, 19): columns [cj0 * wCell, .. + testedW), rows
                 // [ci * hCell, .. + nRy); the last cell column / row is clipped by the reference's maxBorder (:809-812, :817-819)
@@ -456,13 +474,13 @@ int buildStripMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, vo
 
 template <int NT>
 static void launchStripT(const FramePlan& P, const Buffers& B, int F, int rowsMax, int pitchMax, cudaStream_t s) {
-    const StripLayout lay = stripLayout(rowsMax, pitchMax);
+    const StripLayout lay = stripLayout(rowsMax, pitchMax, stripListCap());
     auto kern = fastStripKernel<NT>;
     if (lay.total > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, lay.total);
     kern<<<dim3(P.stripTiles, F), NT, lay.total, s>>>(*reinterpret_cast<const LevelMaps*>(B.stripMaps),
                                                      reinterpret_cast<const StripDesc*>(B.stripTab), B.cand, B.cellCnt, B.fbList, B.fbCount,
                                                      B.fbCap, (int)P.candWords, P.nCellsTotal, std::max(P.iniTh, 1), std::max(P.minTh, 1),
-                                                     rowsMax, pitchMax, B.frame0);
+                                                     rowsMax, pitchMax, B.frame0, stripListCap());
     countLaunch();
 }
 

@@ -112,7 +112,8 @@ template <int SPT, bool WINDOWED, bool TMA>
 __global__ void __launch_bounds__(256)
     pyrResizeKernel(uint8_t* __restrict__ pyr, unsigned frameBytes, unsigned srcOff, int sw, int sh, int spitch,
                     unsigned dstOff, int dw, int dh, int dpitch, const short4* __restrict__ tabX,
-                    const short4* __restrict__ tabY, int maxRows, const __grid_constant__ CUtensorMap srcMap, int frame0) {
+                    const short4* __restrict__ tabY, int maxRows, const __grid_constant__ CUtensorMap srcMap, int frame0,
+                    const uint4* __restrict__ gtab, const int* __restrict__ stripA0) {
     extern __shared__ __align__(128) uint8_t smem[];
     // per tile row: first / second source row (relative to S0), b0 << 16, b1 << 16.  TMA: two generations (tile parity), the
     // next tile's rows and its source box are set up while the current tile is computed
@@ -136,41 +137,54 @@ __global__ void __launch_bounds__(256)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int X0 = blockIdx.x * kTW;
     const int pw = dw + 2 * kEdge, ph = dh + 2 * kEdge;
+    (void)tid;
     uint8_t* frame = pyr + (size_t)blockIdx.z * frameBytes;
 
     // ---- the 4 columns of this lane (the same in every warp) -> source columns and coefficients -----------------
-    int o0[4], o1[4], a0[4], a1[4];
-    int cLo = 1 << 30, cHi = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int X = min(X0 + 4 * lane + j, pw - 1);
-        const short4 tx = __ldg(tabX + reflect101(X - kEdge, dw));  // (sx, a0, a1, -)
-        o0[j] = tx.x; o1[j] = min(tx.x + 1, sw - 1);
-        a0[j] = tx.y; a1[j] = tx.z;
-        cLo = min(cLo, o0[j]); cHi = max(cHi, o1[j]);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        cLo = min(cLo, __shfl_xor_sync(0xffffffffu, cLo, o));
-        cHi = max(cHi, __shfl_xor_sync(0xffffffffu, cHi, o));
-    }
-    const int A0 = (kEdge + cLo) & ~15;                      // plane column of the first staged byte (16-B aligned)
-    const int nC16 = ((kEdge + cHi) - A0) / 16 + 1;          // 16-B chunks per staged row (<= 16)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { o0[j] += kEdge - A0; o1[j] += kEdge - A0; }
+    int o0[4] = {0, 0, 0, 0}, o1[4] = {0, 0, 0, 0}, a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
+    int A0 = 0, nC16 = 0, wOfs = 0, wSh = 0;
+    uint32_t sel[4] = {0, 0, 0, 0}, cf[4] = {0, 0, 0, 0};
     const int X = X0 + 4 * lane;
-    // The 4 columns of a lane read source bytes within a window of <= 8 bytes whenever the scale step is <= 2 (always at
-    // ORB-SLAM3's 1.2): then a source row costs the lane three aligned 32-bit loads and two funnel shifts, and each
-    // (p0, p1) pair is one PRMT away from the two-way dot product with (a0, a1).  Wider windows keep the byte loads.
-    int wLo = min(min(o0[0], o0[1]), min(o0[2], o0[3]));
-    const int wHi = max(max(o1[0], o1[1]), max(o1[2], o1[3]));
-    (void)wHi;  // WINDOWED is chosen on the host: source step < 2 => wHi - wLo <= 7
-    const int wOfs = wLo & ~3, wSh = (wLo & 3) * 8;
-    uint32_t sel[4], cf[4];
+    if (WINDOWED && gtab) {
+        // host-built (buildPyrGroupTable): per group of 4 padded columns the aligned source window, the byte selectors of the
+        // four (p0, p1) pairs and the packed coefficients; per strip the first staged byte.  Two 128-bit loads per lane instead
+        // of four table look-ups with the border reflection and two warp reductions.
+        const uint4 e0 = __ldg(gtab + 2 * (blockIdx.x * 32 + lane)), e1 = __ldg(gtab + 2 * (blockIdx.x * 32 + lane) + 1);
+        A0 = __ldg(stripA0 + blockIdx.x);
+        nC16 = SPT / 16;  // ordinary-load staging (ORBX_FAST_TMA=0) copies whole staged rows; the allocation has slack behind the last plane
+        wOfs = (int)(e0.x & 0xffffu) - A0;
+        wSh = (int)(e0.x >> 16);
+        sel[0] = e0.y & 0xffu; sel[1] = (e0.y >> 8) & 0xffu; sel[2] = (e0.y >> 16) & 0xffu; sel[3] = e0.y >> 24;
+        cf[0] = e0.z; cf[1] = e0.w; cf[2] = e1.x; cf[3] = e1.y;
+    } else {
+        int cLo = 1 << 30, cHi = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        sel[j] = (uint32_t)((o0[j] - wLo) & 7) | ((uint32_t)((o1[j] - wLo) & 7) << 4);
-        cf[j] = (uint32_t)a0[j] | ((uint32_t)a1[j] << 16);
+        for (int j = 0; j < 4; ++j) {
+            const int Xc = min(X0 + 4 * lane + j, pw - 1);
+            const short4 tx = __ldg(tabX + reflect101(Xc - kEdge, dw));  // (sx, a0, a1, -)
+            o0[j] = tx.x; o1[j] = min(tx.x + 1, sw - 1);
+            a0[j] = tx.y; a1[j] = tx.z;
+            cLo = min(cLo, o0[j]); cHi = max(cHi, o1[j]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cLo = min(cLo, __shfl_xor_sync(0xffffffffu, cLo, o));
+            cHi = max(cHi, __shfl_xor_sync(0xffffffffu, cHi, o));
+        }
+        A0 = (kEdge + cLo) & ~15;                      // plane column of the first staged byte (16-B aligned)
+        nC16 = ((kEdge + cHi) - A0) / 16 + 1;          // 16-B chunks per staged row (<= 16)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { o0[j] += kEdge - A0; o1[j] += kEdge - A0; }
+        // The 4 columns of a lane read source bytes within a window of <= 8 bytes whenever the scale step is <= 2 (always at
+        // ORB-SLAM3's 1.2): then a source row costs the lane three aligned 32-bit loads and two funnel shifts, and each
+        // (p0, p1) pair is one PRMT away from the two-way dot product with (a0, a1).  Wider windows keep the byte loads.
+        const int wLo = min(min(o0[0], o0[1]), min(o0[2], o0[3]));
+        wOfs = wLo & ~3; wSh = (wLo & 3) * 8;   // WINDOWED is chosen on the host: source step < 2 => window <= 8 bytes
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            sel[j] = (uint32_t)((o0[j] - wLo) & 7) | ((uint32_t)((o1[j] - wLo) & 7) << 4);
+            cf[j] = (uint32_t)a0[j] | ((uint32_t)a1[j] << 16);
+        }
     }
 
     // rows of tile `rt` -> source rows (warp 0); lane 0 then hands the tile's source box to the copy engine (TMA)
@@ -230,8 +244,9 @@ __global__ void __launch_bounds__(256)
 
         // ---- horizontal pass: H[s][x] = (p0*a0 + p1*a1) >> 4  (<= 32640) ------------------------------------------
         if (WINDOWED) {
-            for (int s = warp; s < nS; s += 8) {
-                const uint32_t* row = reinterpret_cast<const uint32_t*>(sSrc + s * SPT + wOfs);
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(sSrc + warp * SPT + wOfs);
+            uint4* hp = reinterpret_cast<uint4*>(sH + warp * kTW + 4 * lane);
+            for (int s = warp; s < nS; s += 8, row += 8 * SPT / 4, hp += 8 * kTW / 4) {
                 const uint32_t w0 = row[0], w1 = row[1], w2 = row[2];
                 const uint32_t lo = __funnelshift_r(w0, w1, wSh), hi = __funnelshift_r(w1, w2, wSh);
                 uint4 hv;
@@ -239,7 +254,7 @@ __global__ void __launch_bounds__(256)
                 hv.y = __dp2a_lo(cf[1], __byte_perm(lo, hi, sel[1]), 0u) >> 4;
                 hv.z = __dp2a_lo(cf[2], __byte_perm(lo, hi, sel[2]), 0u) >> 4;
                 hv.w = __dp2a_lo(cf[3], __byte_perm(lo, hi, sel[3]), 0u) >> 4;
-                *reinterpret_cast<uint4*>(sH + s * kTW + 4 * lane) = hv;
+                *hp = hv;
             }
         } else {
             for (int s = warp; s < nS; s += 8) {
@@ -256,11 +271,13 @@ __global__ void __launch_bounds__(256)
 
         // ---- vertical pass + store: ((b0*h0) >> 16) + ((b1*h1) >> 16) + 2 >> 2, at most 255 (b0 + b1 = 2048) ------------
         if (X < pw) {
+            const int ry0 = warp * (kTH / 8);
+            const int rowsHere = min(kTH / 8, ph - (Y0 + ry0));  // <= 0 below the plane
+            uint8_t* outp = frame + dstOff + (size_t)(Y0 + ry0) * dpitch + X;
 #pragma unroll
-            for (int k = 0; k < kTH / 8; ++k) {
-                const int ry = warp * (kTH / 8) + k, Y = Y0 + ry;
-                if (Y >= ph) break;
-                const int4 ri = sRow[gen][ry];
+            for (int k = 0; k < kTH / 8; ++k, outp += dpitch) {
+                if (k >= rowsHere) break;
+                const int4 ri = sRow[gen][ry0 + k];
                 const uint4 u = *reinterpret_cast<const uint4*>(sH + ri.x + 4 * lane);
                 const uint4 v = *reinterpret_cast<const uint4*>(sH + ri.y + 4 * lane);
                 const uint32_t B0 = (uint32_t)ri.z, B1 = (uint32_t)ri.w;  // b << 16: umulhi(b << 16, h) == (b * h) >> 16
@@ -268,7 +285,7 @@ __global__ void __launch_bounds__(256)
                 const uint32_t v1 = (__umulhi(B0, u.y) + __umulhi(B1, v.y) + 2u) >> 2;
                 const uint32_t v2 = (__umulhi(B0, u.z) + __umulhi(B1, v.z) + 2u) >> 2;
                 const uint32_t v3 = (__umulhi(B0, u.w) + __umulhi(B1, v.w) + 2u) >> 2;
-                *reinterpret_cast<uint32_t*>(frame + dstOff + (size_t)Y * dpitch + X) = v0 + (v1 << 8) + (v2 << 16) + (v3 << 24);
+                *reinterpret_cast<uint32_t*>(outp) = __byte_perm(__byte_perm(v0, v1, 0x0040), __byte_perm(v2, v3, 0x0040), 0x5410);
             }
         }
     }
@@ -293,6 +310,54 @@ int buildPyrMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void
     return 0;
 }
 
+// Per level l >= 1 (windowed levels only): for every group of 4 padded columns 8 words
+//   {source window byte (plane column & ~3) | funnel shift << 16, 4 byte selectors, cf0, cf1, cf2, cf3, 0, 0}
+// and, behind the groups of the level, one word per 128-column strip: the plane column of the strip's first staged byte.
+// offsets[l] = first word of level l's groups, stripOfs[l] = first word of its strip entries (0 = level not windowed).
+void buildPyrGroupTable(const FramePlan& P, const std::vector<int16_t>& tab, std::vector<uint32_t>& out, int* offsets, int* stripOfs) {
+    out.assign(8, 0u);  // word 0 stays unused so that offset 0 means "no table"
+    for (int l = 0; l < kMaxLevels; ++l) offsets[l] = stripOfs[l] = 0;
+    for (int l = 1; l < P.nlevels; ++l) {
+        const LevelPlan& S = P.lv[l - 1];
+        const LevelPlan& D = P.lv[l];
+        if (!((double)S.w / D.w < 1.95)) continue;
+        const int pw = D.w + 2 * kEdge;
+        const int strips = (pw + kTW - 1) / kTW, groups = strips * 32;
+        const int16_t* tx = tab.data() + (size_t)D.tabX * 4;
+        auto refl = [](int i, int n) {
+            if (n == 1) return 0;
+            while (i < 0 || i >= n) i = i < 0 ? -i : 2 * n - 2 - i;
+            return i;
+        };
+        offsets[l] = (int)out.size();
+        std::vector<int> cLo(strips, 1 << 30);
+        for (int g = 0; g < groups; ++g) {
+            int o0[4], o1[4], a0[4], a1[4];
+            for (int j = 0; j < 4; ++j) {
+                const int Xc = std::min(4 * g + j, pw - 1);
+                const int16_t* e = tx + 4 * refl(Xc - kEdge, D.w);
+                o0[j] = e[0]; o1[j] = std::min(e[0] + 1, S.w - 1);
+                a0[j] = e[1]; a1[j] = e[2];
+                cLo[g / 32] = std::min(cLo[g / 32], o0[j]);
+            }
+            const int wLo = kEdge + std::min(std::min(o0[0], o0[1]), std::min(o0[2], o0[3]));
+            uint32_t selp = 0, cf[4];
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t sel = (uint32_t)((kEdge + o0[j] - wLo) & 7) | ((uint32_t)((kEdge + o1[j] - wLo) & 7) << 4);
+                selp |= sel << (8 * j);
+                cf[j] = (uint32_t)(uint16_t)a0[j] | ((uint32_t)(uint16_t)a1[j] << 16);
+            }
+            out.push_back((uint32_t)(wLo & ~3) | ((uint32_t)((wLo & 3) * 8) << 16));
+            out.push_back(selp);
+            out.push_back(cf[0]); out.push_back(cf[1]); out.push_back(cf[2]); out.push_back(cf[3]);
+            out.push_back(0u); out.push_back(0u);
+        }
+        stripOfs[l] = (int)out.size();
+        for (int t = 0; t < strips; ++t) out.push_back((uint32_t)((kEdge + cLo[t]) & ~15));
+        while (out.size() % 8) out.push_back(0u);
+    }
+}
+
 template <int SPT, bool WINDOWED, bool TMA = false>
 static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cudaStream_t s) {
     const LevelPlan& S = P.lv[l - 1];
@@ -307,7 +372,9 @@ static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cu
     const CUtensorMap& map = TMA ? reinterpret_cast<const LevelMaps*>(B.pyrMaps)->m[l] : kNoMap;
     kern<<<grid, 256, smem, s>>>(B.pyr, P.frameBytes, S.planeOff, S.w, S.h, S.pitch, D.planeOff, D.w, D.h, D.pitch,
                                  reinterpret_cast<const short4*>(B.tab) + D.tabX, reinterpret_cast<const short4*>(B.tab) + D.tabY, maxRows,
-                                 map, B.frame0);
+                                 map, B.frame0,
+                                 (WINDOWED && B.pyrGroupTab && D.gtabOff) ? reinterpret_cast<const uint4*>(B.pyrGroupTab + D.gtabOff) : nullptr,
+                                 (WINDOWED && B.pyrGroupTab && D.gtabOff) ? reinterpret_cast<const int*>(B.pyrGroupTab + D.gtabStrip) : nullptr);
     countLaunch();
 }
 

@@ -88,7 +88,7 @@ struct orbx_extractor {
     alignas(64) unsigned char pyrMaps[kMaxLevels * 128];
     DevMem mBlurTab;
     alignas(64) unsigned char stripMaps[kMaxLevels * 128];
-    DevMem mStripTab, mFb;
+    DevMem mStripTab, mFb, mGroupTab;
     bool useStrips = true;  // FAST over strips of the cell grid (k_fast_strip.cu); ORBX_FAST_STRIP=0 = per-cell kernels only
     bool useTma = true;
     DevMem mKpsUn;           // orbx_undistort_batch: mvKeysUn of the last batch, [frame][cap]
@@ -211,6 +211,14 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
         if (rc != ORBX_OK) return rc;
         ORBX_CUDA(h->mTab.reserve(std::max<size_t>(tab.size() * sizeof(int16_t), 16)));
         ORBX_CUDA(cudaMemcpyAsync(h->mTab.p, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
+        std::vector<uint32_t> gtab;
+        {
+            int go[kMaxLevels], gs[kMaxLevels];
+            buildPyrGroupTable(h->plan, tab, gtab, go, gs);
+            for (int l = 0; l < kMaxLevels; ++l) { h->plan.lv[l].gtabOff = go[l]; h->plan.lv[l].gtabStrip = gs[l]; }
+        }
+        ORBX_CUDA(h->mGroupTab.reserve(std::max<size_t>(gtab.size() * 4, 16)));
+        ORBX_CUDA(cudaMemcpyAsync(h->mGroupTab.p, gtab.data(), gtab.size() * 4, cudaMemcpyHostToDevice, h->stream));
         std::vector<uint32_t> cells;
         buildFastCellTable(h->plan, cells);
         ORBX_CUDA(h->mFastTab.reserve(std::max<size_t>(cells.size() * 4, 16)));
@@ -271,6 +279,7 @@ static int ensureCapacity(orbx_extractor* h, int W, int H, int F) {
     B.cand = (uint32_t*)h->mCand.p; B.cellCnt = (int*)h->mCellCnt.p; B.gath = (uint32_t*)h->mGath.p;
     B.nid = (uint16_t*)h->mNid.p; B.lkp = (LevelKp*)h->mLkp.p; B.lkpCnt = (int*)h->mLkpCnt.p; B.sorted = (LevelKp*)h->mSlot.p;
     B.outKps = h->mOutK.p; B.outDesc = (uint8_t*)h->mOutD.p; B.outN = (int*)h->mOutN.p; B.outMono = (int*)h->mOutM.p;
+    B.pyrGroupTab = (const uint32_t*)h->mGroupTab.p;
     B.tab = (int16_t*)h->mTab.p; B.fastTab = (uint32_t*)h->mFastTab.p; B.errFlag = (int*)h->mErr.p; B.workCtr = B.errFlag + 4; B.workCtr2 = B.errFlag + 32;
     B.fastMaps = h->useTma ? h->fastMaps : nullptr; B.frame0 = 0;
     B.blurMaps = h->useTma ? h->blurMaps : nullptr; B.pyrMaps = h->useTma ? h->pyrMaps : nullptr; B.blurTab = (uint32_t*)h->mBlurTab.p;
@@ -506,7 +515,7 @@ void orbx_destroy(orbx_handle h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     DevMem* all[] = {&h->mImg, &h->mPyr, &h->mBlur, &h->mCand, &h->mCellCnt, &h->mGath, &h->mNid, &h->mLkp, &h->mLkpCnt,
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
-                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn, &h->mStripTab, &h->mFb};
+                     &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn, &h->mStripTab, &h->mFb, &h->mGroupTab};
     for (DevMem* m : all) m->release();
     for (int i = 0; i < 12; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);

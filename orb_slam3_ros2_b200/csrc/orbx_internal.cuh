@@ -40,6 +40,7 @@ struct LevelPlan {
     int lkpBase;         // first slot of this level in the frame's level-keypoint array
     int lkpCap;          // max(nFeat + 4, 4 * nIni + 1) (F5: the quadtree returns N..N+3, or the 4 * nIni children of the roots)
     int tabX, tabY;      // offsets into the resize coefficient table (int16 triplets ofs,a0,a1)
+    int gtabOff, gtabStrip;  // word offsets of the level's column-group entries / strip entries in the resize group table (0 = none)
     int blurTile0, blurTilesX;  // first 128x32 blur tile of the level in the launch's tile list, tiles per row
     int stripCells, stripSegs, stripPitch;  // FAST strips (k_fast_strip.cu): cells per strip, strips per cell row, tile pitch (bytes)
     float scale;         // mvScaleFactor[l]
@@ -83,6 +84,7 @@ struct Buffers {
     int* outN;           // F
     int* outMono;        // F
     int16_t* tab;        // resize coefficient tables
+    const uint32_t* pyrGroupTab;  // per level: packed windows / selectors / coefficients per 4 padded columns (buildPyrGroupTable)
     int* errFlag;        // device-side invariant violations (capacity overflow)
     uint32_t* fastTab;   // FAST cell table of the plan (buildFastCellTable)
     int* workCtr2;       // work counter of the early level-0 FAST launch
@@ -119,6 +121,7 @@ void buildFastCellTable(const FramePlan& P, std::vector<uint32_t>& tab);
 size_t fastMapsBytes();
 size_t levelMapsBytes();
 void buildBlurTileTable(const FramePlan& P, std::vector<uint32_t>& tab);
+void buildPyrGroupTable(const FramePlan& P, const std::vector<int16_t>& tab, std::vector<uint32_t>& out, int* offsets, int* stripOfs);
 int buildPyrMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 int buildBlurMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
