@@ -187,12 +187,14 @@ typedef enum orbx_accept_rule {
     ORBX_ACCEPT_PROJ_MAP = 0,   /* SearchByProjection(F, map points), ORBmatcher.cc:123-128: d1 <= TH_HIGH and
                                    (level1 != level2 or (float)d1 <= nnratio * d2); levels NULL = always equal */
     ORBX_ACCEPT_BOW_KF_F = 1,   /* SearchByBoW(KF, F), :327-329: d1 <= TH_LOW and (float)d1 < nnratio * (float)d2 */
-    ORBX_ACCEPT_INIT = 2,       /* SearchForInitialization, :697-699: d1 <= TH_LOW and d1 < (float)d2 * nnratio */
+    ORBX_ACCEPT_INIT = 2,       /* SearchForInitialization, :702-705: d1 <= TH_LOW and d1 < (float)d2 * nnratio */
     ORBX_ACCEPT_BOW_KF_KF = 3,  /* SearchByBoW(KF, KF), :848-850: d1 < TH_LOW (strict) and (float)d1 < nnratio * (float)d2 */
-    ORBX_ACCEPT_BEST_HIGH = 4,  /* SearchByProjection(frame, frame), :1767: d1 <= TH_HIGH, best only */
+    ORBX_ACCEPT_BEST_HIGH = 4,  /* SearchByProjection(frame, frame) :1770, SearchBySim3 :1569, :1649: d1 <= TH_HIGH, best only */
     ORBX_ACCEPT_BEST_LOW = 5,   /* Fuse / SearchBySim3 style, :1312, :1437: d1 <= TH_LOW, best only */
-    ORBX_ACCEPT_KNN_RATIO = 6   /* fisheye stereo on knnMatch results, Frame.cc:1149: two results and
+    ORBX_ACCEPT_KNN_RATIO = 6,  /* fisheye stereo on knnMatch results, Frame.cc:1151: two results and
                                    (double)d1 < (double)d2 * 0.7 (the literal is a double; nnratio is ignored) */
+    ORBX_ACCEPT_LOW_RATIO = 7   /* SearchByProjection(KF, Sim3, points, ..., th, ratioHamming), :523, :636:
+                                   (float)d1 <= TH_LOW * ratioHamming, best only; nnratio carries ratioHamming */
 } orbx_accept_rule;
 /* d1, d2: n distances; idx2: second indices (only ORBX_ACCEPT_KNN_RATIO reads it: < 0 = fewer than two results; may be
  * NULL = always two); level1/level2: octaves of the best / second candidate (PROJ_MAP only, may be NULL).

@@ -48,19 +48,20 @@ void orbo_accept_top2(int rule, float nnratio, const int32_t* d1, const int32_t*
             case 1:  // :327-329
                 if (bestDist <= TH_LOW) ok = static_cast<float>(bestDist) < nnratio * static_cast<float>(bestDist2);
                 break;
-            case 2:  // :697-699
+            case 2:  // :702-705
                 if (bestDist <= TH_LOW) ok = bestDist < (float)bestDist2 * nnratio;
                 break;
             case 3:  // :848-850
                 if (bestDist < TH_LOW) ok = static_cast<float>(bestDist) < nnratio * static_cast<float>(bestDist2);
                 break;
-            case 4: ok = bestDist <= TH_HIGH; break;  // :1767
+            case 4: ok = bestDist <= TH_HIGH; break;  // :1770, :1569, :1649
             case 5: ok = bestDist <= TH_LOW; break;   // :1312, :1437
-            case 6: {                                 // src/Frame.cc:1149 (DMatch::distance is float, 0.7 a double)
+            case 6: {                                 // src/Frame.cc:1151 (DMatch::distance is float, 0.7 a double)
                 const float f1 = (float)bestDist, f2 = (float)bestDist2;
                 ok = (!idx2 || idx2[i] >= 0) && f1 < f2 * 0.7;
                 break;
             }
+            case 7: ok = bestDist <= TH_LOW * nnratio; break;  // :523, :636 (nnratio carries ratioHamming)
         }
         accept[i] = ok ? 1 : 0;
     }

@@ -603,8 +603,19 @@ def _slices():
                                            C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p]
         lib.refslice_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, C.c_int, _f32p, C.c_void_p]
         lib.refslice_image_bounds.argtypes = [C.c_int, C.c_int, _f32p, _f32p, C.c_int, _f32p, _f32p]
+        lib.refslice_accept.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        lib.refslice_accept_grid.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, _u8p]
         _refslices = lib
     return _refslices
+
+
+def ref_accept_grid(site, ratio, level1=0, level2=0, results=2):
+    """The reference's own accept condition at ORBmatcher.cc:<site> (Frame.cc:1151 for site 1151), compiled from the sliced source
+    lines (librefslices.so), over every (d1, d2) in [0, 256]^2 -> bool array [257, 257]."""
+    out = np.zeros((257, 257), dtype=np.uint8)
+    _slices().refslice_accept_grid(int(site), float(ratio), int(level1), int(level2), int(results), _ptr(out))
+    assert out.max() <= 1, "unknown site"
+    return out.astype(bool)
 
 
 def ref_thresholds():

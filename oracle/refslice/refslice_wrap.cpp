@@ -15,6 +15,9 @@
 //   Frame.cc:811-981         Frame::ComputeStereoMatches
 //   Frame.cc:747-780         Frame::UndistortKeyPoints   (cv::undistortPoints = minicv's, pinned to cv2 goldens)
 //   Frame.cc:782-809         Frame::ComputeImageBounds
+//   ORBmatcher.cc:123-128, 327-330, 523-524, 636-637, 702-705, 848-851, 1312-1313, 1437-1438, 1569-1570, 1649-1650,
+//   1770-1771 and Frame.cc:1151   the ACCEPT CONDITIONS on (best, second) of every matcher: the `if`
+//                            lines as written, up to the opening brace of the accepted branch (AcceptShell below)
 // They pin oracle/match_oracle.cpp (tests/test_oracle_refslices.py).  Built only where /root/reference exists.
 #include <cstdint>
 #include <cstring>
@@ -40,6 +43,88 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 using ORB_SLAM3::Frame;
 using ORB_SLAM3::ORBmatcher;
 
+namespace cv {
+struct DMatch {  // the one member Frame.cc:1151 reads
+    float distance;
+};
+}  // namespace cv
+
+namespace {
+// The accept conditions of the reference's matchers, each compiled from its own source lines.  A slice ends at the opening
+// brace of the accepted branch, so the shell only adds `return true;` and the closing braces; the member / local names are
+// the ones the reference uses at that site.
+struct AcceptShell {
+    static constexpr int TH_HIGH = 100, TH_LOW = 50;  // checked against the sliced ORBmatcher.cc:35-37 in refslice_accept
+    float mfNNratio;
+    bool projMap(int bestDist, int bestDist2, int bestLevel, int bestLevel2) const {  // ORBmatcher.cc:123-128
+        for (int once = 0; once < 1; ++once) {
+#include "accept_proj_map_123.inc"
+                return true; } }
+        }
+        return false;
+    }
+    bool bowKfF(int bestDist1, int bestDist2) const {  // :327-330
+#include "accept_bow_kf_f_327.inc"
+            return true; } }
+        return false;
+    }
+    bool lowRatio523(int bestDist, float ratioHamming) const {  // :523-524
+#include "accept_low_ratio_523.inc"
+            return true; }
+        return false;
+    }
+    bool lowRatio636(int bestDist, float ratioHamming) const {  // :636-637
+#include "accept_low_ratio_636.inc"
+            return true; }
+        return false;
+    }
+    bool init(int bestDist, int bestDist2) const {  // :702-705
+#include "accept_init_702.inc"
+            return true; } }
+        return false;
+    }
+    bool bowKfKf(int bestDist1, int bestDist2) const {  // :848-851
+#include "accept_bow_kf_kf_848.inc"
+            return true; } }
+        return false;
+    }
+    bool bestLow1312(int bestDist) const {
+#include "accept_best_low_1312.inc"
+            return true; }
+        return false;
+    }
+    bool bestLow1437(int bestDist) const {
+#include "accept_best_low_1437.inc"
+            return true; }
+        return false;
+    }
+    bool bestHigh1569(int bestDist) const {
+#include "accept_best_high_1569.inc"
+            return true; }
+        return false;
+    }
+    bool bestHigh1649(int bestDist) const {
+#include "accept_best_high_1649.inc"
+            return true; }
+        return false;
+    }
+    bool bestHigh1770(int bestDist) const {
+#include "accept_best_high_1770.inc"
+            return true; }
+        return false;
+    }
+    bool knnRatio(int d1, int d2, int results) const {  // Frame.cc:1151, `it` walks the knnMatch result
+        std::vector<std::vector<cv::DMatch>> matches(1);
+        if (results >= 1) matches[0].push_back(cv::DMatch{(float)d1});
+        if (results >= 2) matches[0].push_back(cv::DMatch{(float)d2});
+        std::vector<std::vector<cv::DMatch>>::iterator it = matches.begin();
+#include "accept_knn_ratio_1151.inc"
+            return true; }
+        return false;
+    }
+};
+}  // namespace
+
 namespace {
 static_assert(sizeof(cv::KeyPoint) == 28, "KeyPoint layout");
 std::vector<cv::KeyPoint> keypoints(const void* p, int n) {
@@ -55,6 +140,35 @@ cv::Mat descriptors(const uint8_t* p, int n) {
 }  // namespace
 
 extern "C" {
+
+// site = the reference line of the condition; ratio = mfNNratio (or ratioHamming at 523 / 636); results = entries of the
+// knnMatch row (1151 only).  -1 = unknown site.
+int refslice_accept(int site, float ratio, int d1, int d2, int level1, int level2, int results) {
+    static_assert(AcceptShell::TH_HIGH == 100 && AcceptShell::TH_LOW == 50, "");
+    if (ORBmatcher::TH_HIGH != AcceptShell::TH_HIGH || ORBmatcher::TH_LOW != AcceptShell::TH_LOW) return -2;
+    AcceptShell a{ratio};
+    switch (site) {
+        case 123: return a.projMap(d1, d2, level1, level2);
+        case 327: return a.bowKfF(d1, d2);
+        case 523: return a.lowRatio523(d1, ratio);
+        case 636: return a.lowRatio636(d1, ratio);
+        case 702: return a.init(d1, d2);
+        case 848: return a.bowKfKf(d1, d2);
+        case 1312: return a.bestLow1312(d1);
+        case 1437: return a.bestLow1437(d1);
+        case 1569: return a.bestHigh1569(d1);
+        case 1649: return a.bestHigh1649(d1);
+        case 1770: return a.bestHigh1770(d1);
+        case 1151: return a.knnRatio(d1, d2, results);
+    }
+    return -1;
+}
+
+// the same over every (d1, d2) in [0, 256]^2: out[d1 * 257 + d2]
+void refslice_accept_grid(int site, float ratio, int level1, int level2, int results, uint8_t* out) {
+    for (int d1 = 0; d1 <= 256; ++d1)
+        for (int d2 = 0; d2 <= 256; ++d2) out[d1 * 257 + d2] = (uint8_t)refslice_accept(site, ratio, d1, d2, level1, level2, results);
+}
 
 int refslice_th_low() { return ORBmatcher::TH_LOW; }
 int refslice_th_high() { return ORBmatcher::TH_HIGH; }

@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) blurKernelLd(const __grid_constant__ Fram
 }
 
 
-__global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FramePlan P, const __grid_constant__ LevelMaps M,
+__global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ FramePlan P, const __grid_constant__ LevelMaps M,
                                                   const uint32_t* __restrict__ tileTab, uint8_t* __restrict__ blur, int frame0) {
     __shared__ __align__(128) uint8_t sIn[kInRows * kInPitch];
     __shared__ __align__(16) uint32_t sHp[kPairs * kTileW];  // (H[2m][x] | H[2m+1][x] << 16)
@@ -131,22 +131,28 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     const int l = (int)(te >> 24);
     const int x0 = (int)(te & 0xfffu) * kTileW, y0 = (int)((te >> 12) & 0xfffu) * kTileH;
     const LevelPlan& L = P.lv[l];
+    // thread 0 alone owns the mbarrier (init, expect, wait); the block barrier behind its wait publishes the tile
     if (tid == 0) {
         mbarInit(&bar, 1);
         mbarInitFence();
-    }
-    __syncthreads();
-    if (tid == 0) {
         // padded coordinates (x0 + 16, y0 + 16): staged byte 0 of a row = level column x0 - 3
         mbarExpectTx(&bar, kInRows * kInPitch);
         tmaLoadTile(sIn, &M.m[l], x0 + 16, y0 + 16, frame0 + (int)blockIdx.y, &bar);
+        mbarWait(&bar, 0);
     }
-    mbarWait(&bar, 0);
+    // the part of the tile inside the level: nG groups of 4 columns, `rows` output rows -> nP pairs of staged rows.  Items are
+    // numbered over the VALID part only, so a tile at the right / bottom edge costs its share of instructions (15 % of the
+    // 128 x 32 tiles' pixels lie outside the levels at 752 x 480).
+    const int nG = min(kTileW / 4, (L.w - x0 + 3) >> 2);  // columns [w, bpitch) of the blurred plane are never read
+    const int rows = min(kTileH, L.h - y0);
+    const int nP = (rows + 7) >> 1;  // staged rows 0 .. rows + 5
+    const unsigned divG = 65536u / (unsigned)nG + 1u;  // (i * divG) >> 16 == i / nG for i < 2048
+    __syncthreads();
 
     // horizontal pass: item = (row pair m, 4 columns g)
     constexpr uint32_t K1 = 0x38302212u, K2 = 0x00122230u;  // (18,34,48,56), (48,34,18,0)
-    const int g = tid & 31;
-    for (int m = tid >> 5; m < kPairs; m += 8) {
+    for (int i = tid; i < nP * nG; i += 256) {
+        const int m = (int)(((unsigned)i * divG) >> 16), g = i - m * nG;
         uint32_t h[2][4];
 #pragma unroll
         for (int rr = 0; rr < 2; ++rr) {
@@ -168,33 +174,35 @@ __global__ void __launch_bounds__(256) blurKernel(const __grid_constant__ FrameP
     }
     __syncthreads();
 
-    // vertical pass: thread = 4 columns x 4 rows; output row 4q+i taps staged rows 4q+i .. 4q+i+6 = pairs 2q .. 2q+4
-    const int tx = tid & 31, q = tid >> 5;
-    const int x = x0 + tx * 4, yq = y0 + q * 4;
-    if (x >= L.bpitch || yq >= L.h) return;
-    uint4 pr[5];
-#pragma unroll
-    for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * q + k) * kTileW + tx * 4);
-    uint8_t* out = blur + (size_t)blockIdx.y * P.blurBytes + L.blurOff + (size_t)yq * L.bpitch + x;
-    const int rows = min(4, L.h - yq);
+    // vertical pass: item = (4 output rows q, 4 columns tx); output row 4q+i taps staged rows 4q+i .. 4q+i+6 = pairs 2q .. 2q+4
     // coefficient byte pairs (low byte multiplies the even row of a pair)
     constexpr uint32_t Ea = 0x2212u, Eb = 0x3830u, Ec = 0x2230u, Ed = 0x0012u;   // even start: 18,34 | 48,56 | 48,34 | 18,0
     constexpr uint32_t Oa = 0x1200u, Ob = 0x3022u, Oc = 0x3038u, Od = 0x1222u;   // odd start:  0,18 | 34,48 | 56,48 | 34,18
+    const int nQ = (rows + 3) >> 2;
+    for (int it = tid; it < nQ * nG; it += 256) {
+        const int q = (int)(((unsigned)it * divG) >> 16), tx = it - q * nG;
+        const int x = x0 + tx * 4, yq = y0 + q * 4;
+        uint4 pr[5];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int b = i >> 1;  // first pair
-        const uint32_t ca = (i & 1) ? Oa : Ea, cb = (i & 1) ? Ob : Eb, cc = (i & 1) ? Oc : Ec, cd = (i & 1) ? Od : Ed;
-        uint32_t v[4];
-        const uint32_t* p0 = &pr[b].x; const uint32_t* p1 = &pr[b + 1].x; const uint32_t* p2 = &pr[b + 2].x; const uint32_t* p3 = &pr[b + 3].x;
+        for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * q + k) * kTileW + tx * 4);
+        uint8_t* out = blur + (size_t)blockIdx.y * P.blurBytes + L.blurOff + (size_t)yq * L.bpitch + x;
+        const int rq = min(4, L.h - yq);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            uint32_t acc = __dp2a_lo(p0[k], ca, 32768u);
-            acc = __dp2a_lo(p1[k], cb, acc);
-            acc = __dp2a_lo(p2[k], cc, acc);
-            v[k] = __dp2a_lo(p3[k], cd, acc);   // (V + 32768); the pixel is bits 16..23 = byte 2 (V + 32768 < 2^24)
+        for (int i = 0; i < 4; ++i, out += L.bpitch) {
+            const int b = i >> 1;  // first pair
+            const uint32_t ca = (i & 1) ? Oa : Ea, cb = (i & 1) ? Ob : Eb, cc = (i & 1) ? Oc : Ec, cd = (i & 1) ? Od : Ed;
+            uint32_t v[4];
+            const uint32_t* p0 = &pr[b].x; const uint32_t* p1 = &pr[b + 1].x; const uint32_t* p2 = &pr[b + 2].x; const uint32_t* p3 = &pr[b + 3].x;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                uint32_t acc = __dp2a_lo(p0[k], ca, 32768u);
+                acc = __dp2a_lo(p1[k], cb, acc);
+                acc = __dp2a_lo(p2[k], cc, acc);
+                v[k] = __dp2a_lo(p3[k], cd, acc);   // (V + 32768); the pixel is bits 16..23 = byte 2 (V + 32768 < 2^24)
+            }
+            const uint32_t word = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+            if (i < rq) *reinterpret_cast<uint32_t*>(out) = word;
         }
-        const uint32_t word = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
-        if (i < rows) *reinterpret_cast<uint32_t*>(out + i * L.bpitch) = word;
     }
 }
 

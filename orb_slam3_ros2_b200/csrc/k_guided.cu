@@ -41,6 +41,7 @@ __global__ void acceptKernel(int rule, float nnratio, const int* __restrict__ d1
         case 4: ok = b1 <= 100; break;
         case 5: ok = b1 <= 50; break;
         case 6: ok = (!idx2 || idx2[i] >= 0) && (double)f1 < __dmul_rn((double)f2, 0.7); break;
+        case 7: ok = f1 <= __fmul_rn(50.f, nnratio); break;  // int * float -> float, then (float)bestDist <= that (:523, :636)
     }
     accept[i] = ok ? 1 : 0;
 }

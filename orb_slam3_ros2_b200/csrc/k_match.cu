@@ -13,6 +13,8 @@
 // Chunks of the database (< 2^23 rows) go to different CTAs; their per-chunk top-2 are written as 64-bit keys
 // (distance << 40 | global row) and reduced by mergeKernel — the same kernel that merges the per-rank candidates
 // after the NCCL all-gather of the sharded path.
+#include <cstdlib>
+
 #include "orbx_internal.cuh"
 
 
@@ -141,6 +143,66 @@ __global__ void mergeKernel(const unsigned long long* __restrict__ k1, const uns
     d2[i] = b2 == kNoKey64 ? 256 : (int)(b2 >> 40);
 }
 
+// Consecutive frames of a batch in ONE kernel (v2): frame z against frame z + 1, every thread keeps R queries, a CTA walks
+// ALL rows of frame z + 1 (no database chunks, so no 64-bit partial keys and no merge pass) and writes the int32 results
+// itself; 128-thread CTAs, 8 q-tiles x 255 pairs all resident at once.  Slots [n, cap) get the "no match" values (-1, 256).
+template <int R, int NT>
+__global__ void __launch_bounds__(NT) matchConsecutiveKernel(const uint8_t* __restrict__ desc, const int* __restrict__ counts, int cap,
+                                                             int* __restrict__ idx1, int* __restrict__ d1, int* __restrict__ idx2,
+                                                             int* __restrict__ d2) {
+    __shared__ __align__(16) uint4 sDb[kStage * 2];
+    const int tid = threadIdx.x;
+    const int z = blockIdx.y;
+    const uint8_t* q = desc + (size_t)z * cap * 32;
+    const uint8_t* db = q + (size_t)cap * 32;
+    const int nq = min(counts[z], cap), nd = min(counts[z + 1], cap);
+    const int q0 = blockIdx.x * NT * R;
+
+    uint32_t qw[R][8];
+    uint32_t k1[R], k2[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int qi = q0 + r * NT + tid;
+        const uint4* p = reinterpret_cast<const uint4*>(q + (size_t)(qi < nq ? qi : 0) * 32);
+        const uint4 a = qi < nq ? __ldg(p) : make_uint4(0, 0, 0, 0), b = qi < nq ? __ldg(p + 1) : make_uint4(0, 0, 0, 0);
+        qw[r][0] = a.x; qw[r][1] = a.y; qw[r][2] = a.z; qw[r][3] = a.w;
+        qw[r][4] = b.x; qw[r][5] = b.y; qw[r][6] = b.z; qw[r][7] = b.w;
+        k1[r] = k2[r] = kNoKey32;
+    }
+    if (q0 < nq) {
+        for (int s0 = 0; s0 < nd; s0 += kStage) {
+            const int rows = min(nd - s0, kStage);
+            __syncthreads();
+            const uint4* src = reinterpret_cast<const uint4*>(db + (size_t)s0 * 32);
+            for (int i = tid; i < rows * 2; i += NT) sDb[i] = __ldg(src + i);
+            __syncthreads();
+#pragma unroll 2
+            for (int j = 0; j < rows; ++j) {
+                const uint4 a = sDb[2 * j], b = sDb[2 * j + 1];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int d = hamming256(qw[r], a, b);
+                    const uint32_t key = ((uint32_t)d << 23) | (uint32_t)(s0 + j);
+                    k2[r] = min(k2[r], max(k1[r], key));
+                    k1[r] = min(k1[r], key);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int qi = q0 + r * NT + tid;
+        if (qi < cap) {
+            const size_t o = (size_t)z * cap + qi;
+            const bool v1 = qi < nq && k1[r] != kNoKey32, v2 = qi < nq && k2[r] != kNoKey32;
+            idx1[o] = v1 ? (int)(k1[r] & 0x7fffffu) : -1;
+            d1[o] = v1 ? (int)(k1[r] >> 23) : 256;
+            idx2[o] = v2 ? (int)(k2[r] & 0x7fffffu) : -1;
+            d2[o] = v2 ? (int)(k2[r] >> 23) : 256;
+        }
+    }
+}
+
 // consecutive mode epilogue: keys [pair][cap] -> int32 outputs [pair][cap]
 __global__ void unpackPairsKernel(const unsigned long long* __restrict__ k1, const unsigned long long* __restrict__ k2,
                                   const int* __restrict__ counts, int cap, int* __restrict__ idx1, int* __restrict__ d1,
@@ -263,6 +325,20 @@ void launchReduceKeys(const uint64_t* k1, const uint64_t* k2, int nsets, int nq,
 void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap, uint64_t* keys1, uint64_t* keys2,
                             int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2, cudaStream_t s) {
     if (F < 2) return;
+    // ORBX_MATCH_R: queries per thread of the one-kernel form (1, 2, 4; default 1); 0 = the two-kernel form (matchKernel<1> + unpack).
+    // Measured (frames/s of the whole step): R = 1 158.2 k, R = 2 145.1 k, R = 4 146.2 k, two-kernel form 156.9 k - the loop is bound by
+    // the POPC (XU 84 %) and ALU (80 %) pipes, not by issue slots, so sharing the row loads between queries buys nothing and costs occupancy
+    static const int rSel = [] { const char* e = std::getenv("ORBX_MATCH_R"); return e ? std::atoi(e) : 1; }();
+    if (rSel == 1 || rSel == 2 || rSel == 4) {
+        constexpr int NT = 128;
+        const int tiles = (cap + NT * rSel - 1) / (NT * rSel);
+        const dim3 grid(tiles, F - 1);
+        if (rSel == 1) matchConsecutiveKernel<1, NT><<<grid, NT, 0, s>>>(dDesc, dN, cap, idx1, d1, idx2, d2);
+        else if (rSel == 2) matchConsecutiveKernel<2, NT><<<grid, NT, 0, s>>>(dDesc, dN, cap, idx1, d1, idx2, d2);
+        else matchConsecutiveKernel<4, NT><<<grid, NT, 0, s>>>(dDesc, dN, cap, idx1, d1, idx2, d2);
+        countLaunch();
+        return;
+    }
     const int tiles = (cap + kMT - 1) / kMT;
     matchKernel<1><<<dim3(1, tiles, F - 1), kMT, 0, s>>>(dDesc, 0, nullptr, 0, 0, (long long)cap,
                                                          reinterpret_cast<unsigned long long*>(keys1),

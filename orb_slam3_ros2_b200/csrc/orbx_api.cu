@@ -1132,7 +1132,7 @@ static int needDevice() {
 
 int orbx_accept_top2_device(int rule, float nnratio, const int32_t* d_d1, const int32_t* d_d2, const int64_t* d_idx2,
                             const int32_t* d_level1, const int32_t* d_level2, int n, uint8_t* d_accept, void* stream) {
-    if (rule < 0 || rule > ORBX_ACCEPT_KNN_RATIO || n < 0 || (n > 0 && (!d_d1 || !d_d2 || !d_accept))) return fail(ORBX_ERR_ARG, "bad argument");
+    if (rule < 0 || rule > ORBX_ACCEPT_LOW_RATIO || n < 0 || (n > 0 && (!d_d1 || !d_d2 || !d_accept))) return fail(ORBX_ERR_ARG, "bad argument");
     launchAccept(rule, nnratio, d_d1, d_d2, d_idx2, d_level1, d_level2, n, d_accept, (cudaStream_t)stream);
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -1140,7 +1140,7 @@ int orbx_accept_top2_device(int rule, float nnratio, const int32_t* d_d1, const 
 
 int orbx_accept_top2(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* level1,
                      const int32_t* level2, int n, uint8_t* accept, int device) {
-    if (rule < 0 || rule > ORBX_ACCEPT_KNN_RATIO || n < 0 || (n > 0 && (!d1 || !d2 || !accept))) return fail(ORBX_ERR_ARG, "bad argument");
+    if (rule < 0 || rule > ORBX_ACCEPT_LOW_RATIO || n < 0 || (n > 0 && (!d1 || !d2 || !accept))) return fail(ORBX_ERR_ARG, "bad argument");
     if (n == 0) return ORBX_OK;
     int rc = needDevice();
     if (rc != ORBX_OK) return rc;

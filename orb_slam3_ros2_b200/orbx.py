@@ -395,7 +395,7 @@ def bench_popc(device=-1):
 
 
 # orbx_accept_rule (include/orbx.h)
-ACCEPT_PROJ_MAP, ACCEPT_BOW_KF_F, ACCEPT_INIT, ACCEPT_BOW_KF_KF, ACCEPT_BEST_HIGH, ACCEPT_BEST_LOW, ACCEPT_KNN_RATIO = range(7)
+ACCEPT_PROJ_MAP, ACCEPT_BOW_KF_F, ACCEPT_INIT, ACCEPT_BOW_KF_KF, ACCEPT_BEST_HIGH, ACCEPT_BEST_LOW, ACCEPT_KNN_RATIO, ACCEPT_LOW_RATIO = range(8)
 
 GRID_QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
                              ("ur", "<f4")])

@@ -22,8 +22,8 @@ def test_accept_rules_match_oracle_exhaustively(orbx, oracle):
     rng = np.random.default_rng(0)
     l1, l2 = rng.integers(0, 3, d1.size), rng.integers(0, 3, d1.size)
     idx2 = np.where(d2 == 256, -1, 5).astype(np.int64)
-    for rule in range(7):
-        for nn in (0.6, 0.7, 0.9, 0.75):
+    for rule in range(8):  # 7 = TH_LOW * ratioHamming (ORBmatcher.cc:523, :636): the ratio argument carries ratioHamming
+        for nn in (0.6, 0.7, 0.9, 0.75, 1.0, 1.5):
             got = orbx.accept_top2(rule, d1, d2, nn, idx2=idx2, level1=l1, level2=l2)
             want = oracle.accept_top2(rule, d1, d2, nn, idx2=idx2, level1=l1, level2=l2)
             assert np.array_equal(got, want), (rule, nn)

@@ -201,3 +201,25 @@ def test_search_by_bow_keyframes_restatement_equals_reference_body(slices, seed,
     sel = m_ref[m_ref >= 0]
     assert len(np.unique(sel)) == len(sel)                      # vbMatched2: a point of keyframe 2 is given away once
     assert (case[1][m_ref >= 0] == 1).all() and (case[5][sel] == 1).all()  # only good MapPoints on both sides
+
+
+# row a11: orbx_accept_rule -> the reference sites whose `if` it restates (ORBmatcher.cc line; 1151 = Frame.cc:1151)
+ACCEPT_SITES = {0: [123], 1: [327], 2: [702], 3: [848], 4: [1569, 1649, 1770], 5: [1312, 1437], 6: [1151], 7: [523, 636]}
+
+
+@pytest.mark.parametrize("rule", sorted(ACCEPT_SITES))
+def test_accept_rules_equal_the_reference_conditions(slices, rule):
+    """The restated accept rules (oracle/match_oracle.cpp, the checker of the GPU acceptKernel) against the reference's own `if`
+    lines, compiled from the sliced sources, over EVERY (d1, d2) in [0, 256]^2 and the ratios the reference uses (constructor
+    calls: 0.6, 0.7, 0.75, 0.8, 0.9; ratioHamming 1.0 and the loop-closing values)."""
+    d1, d2 = [a.ravel().astype(np.int32) for a in np.meshgrid(np.arange(257), np.arange(257), indexing="ij")]
+    ratios = [0.6, 0.7, 0.75, 0.8, 0.9, 1.0] if rule != 7 else [1.0, 0.9, 1.5, 0.85, 2.0]
+    for site in ACCEPT_SITES[rule]:
+        for ratio in ratios:
+            for lv in ([(0, 0), (2, 3), (3, 3)] if rule == 0 else [(0, 0)]):
+                for results in ([2, 1, 0] if rule == 6 else [2]):
+                    want = slices.ref_accept_grid(site, ratio, lv[0], lv[1], results).ravel()
+                    idx2 = np.full(d1.shape, 5 if results >= 2 else -1, np.int64)
+                    got = slices.accept_top2(rule, d1, d2, ratio, idx2=idx2, level1=np.full(d1.shape, lv[0], np.int32),
+                                             level2=np.full(d1.shape, lv[1], np.int32))
+                    assert np.array_equal(np.asarray(got, bool), want), (rule, site, ratio, lv, results)
