@@ -27,6 +27,7 @@
 //     (box 144 x 38 x 1; the tile's first byte is padded column x0 + 16, always 16-byte aligned), completion on an
 //     mbarrier; rows / columns past the plane are zero-filled by the copy engine and only feed outputs that are not stored;
 //   * the final ">> 16" and the byte packing are one PRMT pair (the result is byte 2 of the accumulator).
+#include <cstdlib>
 #include <cstring>
 
 #include "orbx_internal.cuh"
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(256) blurKernelLd(const __grid_constant__ Fram
 }
 
 
+template <bool ONEWAIT, bool REMAP>
 __global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ FramePlan P, const __grid_constant__ LevelMaps M,
                                                   const uint32_t* __restrict__ tileTab, uint8_t* __restrict__ blur, int frame0) {
     __shared__ __align__(128) uint8_t sIn[kInRows * kInPitch];
@@ -138,21 +140,25 @@ __global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ Fra
         // padded coordinates (x0 + 16, y0 + 16): staged byte 0 of a row = level column x0 - 3
         mbarExpectTx(&bar, kInRows * kInPitch);
         tmaLoadTile(sIn, &M.m[l], x0 + 16, y0 + 16, frame0 + (int)blockIdx.y, &bar);
+        if (ONEWAIT) mbarWait(&bar, 0);
+    }
+    if (!ONEWAIT) {
+        __syncthreads();
         mbarWait(&bar, 0);
     }
     // the part of the tile inside the level: nG groups of 4 columns, `rows` output rows -> nP pairs of staged rows.  Items are
     // numbered over the VALID part only, so a tile at the right / bottom edge costs its share of instructions (15 % of the
     // 128 x 32 tiles' pixels lie outside the levels at 752 x 480).
-    const int nG = min(kTileW / 4, (L.w - x0 + 3) >> 2);  // columns [w, bpitch) of the blurred plane are never read
-    const int rows = min(kTileH, L.h - y0);
+    const int nG = REMAP ? min(kTileW / 4, (L.w - x0 + 3) >> 2) : kTileW / 4;  // columns [w, bpitch) of the blurred plane are never read
+    const int rows = REMAP ? min(kTileH, L.h - y0) : kTileH;
     const int nP = (rows + 7) >> 1;  // staged rows 0 .. rows + 5
     const unsigned divG = 65536u / (unsigned)nG + 1u;  // (i * divG) >> 16 == i / nG for i < 2048
-    __syncthreads();
+    if (ONEWAIT) __syncthreads();
 
     // horizontal pass: item = (row pair m, 4 columns g)
     constexpr uint32_t K1 = 0x38302212u, K2 = 0x00122230u;  // (18,34,48,56), (48,34,18,0)
     for (int i = tid; i < nP * nG; i += 256) {
-        const int m = (int)(((unsigned)i * divG) >> 16), g = i - m * nG;
+        const int m = REMAP ? (int)(((unsigned)i * divG) >> 16) : (i >> 5), g = i - m * nG;
         uint32_t h[2][4];
 #pragma unroll
         for (int rr = 0; rr < 2; ++rr) {
@@ -180,8 +186,9 @@ __global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ Fra
     constexpr uint32_t Oa = 0x1200u, Ob = 0x3022u, Oc = 0x3038u, Od = 0x1222u;   // odd start:  0,18 | 34,48 | 56,48 | 34,18
     const int nQ = (rows + 3) >> 2;
     for (int it = tid; it < nQ * nG; it += 256) {
-        const int q = (int)(((unsigned)it * divG) >> 16), tx = it - q * nG;
+        const int q = REMAP ? (int)(((unsigned)it * divG) >> 16) : (it >> 5), tx = it - q * nG;
         const int x = x0 + tx * 4, yq = y0 + q * 4;
+        if (!REMAP && (x >= L.bpitch || yq >= L.h)) continue;
         uint4 pr[5];
 #pragma unroll
         for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * q + k) * kTileW + tx * 4);
@@ -233,8 +240,19 @@ int buildBlurMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, voi
 
 void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     static_assert(kTileW == 128 && kTileH == 32, "the plan's blurTile0 / blurTilesX assume 128 x 32 tiles");
-    if (B.blurMaps)
-        blurKernel<<<dim3(P.blurTiles, F), 256, 0, s>>>(P, *reinterpret_cast<const LevelMaps*>(B.blurMaps), B.blurTab, B.blur, B.frame0);
+    // ORBX_BLUR_MODE (A/B measurements): bit 0 = one mbarrier waiter, bit 1 = items numbered over the valid part of edge tiles.
+    // Measured beside the quadtree (blur stage ms / frames per s): mode 0 0.303 / 157.2 k, 1 0.305 / 156.9 k, 2 0.322 / 155.1 k,
+    // 3 0.332 / 154.4 k: the kernel waits for its TMA tile (43 % of the stall samples), not for issue slots, so the 15 % fewer
+    // instructions of the edge tiles buy nothing and the extra index arithmetic costs; default = one waiter, no remapping.
+    static const int mode = [] { const char* e = std::getenv("ORBX_BLUR_MODE"); return e ? std::atoi(e) : 1; }();
+    const LevelMaps& M = *reinterpret_cast<const LevelMaps*>(B.blurMaps);
+    const dim3 grid(P.blurTiles, F);
+    if (B.blurMaps) {
+        if (mode == 3) blurKernel<true, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
+        else if (mode == 2) blurKernel<false, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
+        else if (mode == 1) blurKernel<true, false><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
+        else blurKernel<false, false><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
+    }
     else
         blurKernelLd<<<dim3(P.blurTiles, F), 256, 0, s>>>(P, B.pyr, B.blur);
     countLaunch();
