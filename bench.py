@@ -35,6 +35,9 @@ E2E_HANDLES = 1  # v15 sweep with sub-batches off (handles x depth): 1x2 105k, 1
 RESIDENT_HANDLES = 2  # measured (handles x sub-batches -> frames/s): 1x1 127.9k, 1x2 129.2k, 2x1 131.8k, 2x2 134.6k, 3x1 134.3k, 3x2 132.3k
 SUBBATCHES = 1  # v15 sweep with the forked FAST classes (sub-batches x resident handles -> frames/s): 1x1 140.6k, 1x2 150.4k, 1x3 147.2k, 2x1 140.5k, 2x2 144.3k, 2x3 145.3k
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
+# what the CPU arm's OpenCV calls run on (so that nobody reads the GPU / CPU ratio as a ratio against a SIMD OpenCV build)
+OPENCV_NOTE = ("the reference's cv:: calls (resize, copyMakeBorder, FAST, GaussianBlur) run on the scalar minicv shim (OpenCV C++ is not "
+               "installed): about 2x slower per frame than cv2 4.13.0's SIMD primitives (BASELINE.md section 2)")
 
 
 def level_sizes(w, h):
@@ -110,7 +113,7 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for l in self.lines:
             f = [x.strip() for x in l.split(",")]
@@ -120,11 +123,16 @@ class ClockSampler:
                 sm.append(float(f[0])); mx.append(float(f[1]))
             except ValueError:
                 continue
+            try:
+                pw.append(float(f[2]))
+            except ValueError:
+                pass
             for n, v in zip(names, f[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "power_w_median": float(np.median(pw)) if pw else None,
+                "power_w_max": max(pw) if pw else None}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -183,7 +191,7 @@ def run_reference(args, rank, world):
         return
     from orb_slam3_ros2_b200 import synth
     cores = os.cpu_count() or 1
-    per_step = max(2 * cores, 16)
+    per_step = args.frames  # the CUDA arm's step: the same 256 frames of the same stream, the same matching
     frames = synth.frames(0, per_step, W, H)
     kind = None
     for _ in range(args.warmup):
@@ -200,9 +208,12 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "euroc752x480_nf1000_extract+consecutive_top2 (CPU reference, bounded sample)", "frames_per_step": per_step,
-                   "nfeatures": NFEAT, "levels": NLEVELS, "fast": [INI_TH, MIN_TH]},
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
+        "config": {"workload": f"euroc752x480_nf1000_batch{per_step}_extract+consecutive_top2", "frames_per_gpu_per_step": per_step,
+                   "nfeatures": NFEAT, "levels": NLEVELS, "fast": [INI_TH, MIN_TH],
+                   "arm": "the reference's own ORBextractor.cc compiled unchanged (oracle/_ref) on the box's host cores, one extractor "
+                          "instance per thread; DescriptorDistance top-2 loop for the matching"},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample,
+                         "opencv_layer": OPENCV_NOTE},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "keypoints_per_frame": nkp / (per_step * args.steps),
     }
@@ -326,7 +337,176 @@ def run_ours(args, rank, world, local_rank):
     fps = world * F * args.steps / (ms * 1e-3)
     return dict(torch=torch, dist=dist, orbx=orbx, synth=synth, ex=ex, dev=dev, F=F, cap=cap, ms=ms, fps=fps,
                 launches=launches, clocks=clocks, stage_ms=stage_ms, total_ms=total_ms, nkp=nkp, ncand=ncand,
-                imgs=imgs, midx=midx, step=step, barrier=barrier)
+                imgs=imgs, midx=midx, step=step, barrier=barrier, exs=exs, stream=stream, local_rank=local_rank)
+
+
+def run_sustained(ctx, args, world):
+    """The headline step back to back for >= --sustained-s seconds on the same handles: frames/s, SM clock, power and throttle
+    reasons over that window (the K-step timed region of `value` lasts tens of milliseconds: too short for the clock / power
+    sampler to say anything about steady state)."""
+    torch, dist = ctx["torch"], ctx["dist"]
+    exs, stream, step, F = ctx["exs"], ctx["stream"], ctx["step"], ctx["F"]
+    n = max(int(np.ceil(args.sustained_s * 1e3 / max(ctx["ms"] / args.steps, 1e-3))), args.steps)
+    ctx["barrier"]()
+    sampler = ClockSampler(ctx["local_rank"])
+    sampler.start()
+    time.sleep(0.2)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record()
+    for i in range(n):
+        step(i)
+    for e in exs[1:]:
+        ev = torch.cuda.Event()
+        with torch.cuda.stream(torch.cuda.ExternalStream(e.stream_ptr(), device=ctx["dev"])):
+            ev.record()
+        stream.wait_event(ev)
+    with torch.cuda.stream(stream):
+        e1.record()
+    for e in exs:
+        e.sync()
+    ctx["barrier"]()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=ctx["dev"])
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    fps = world * F * n / (ms * 1e-3)
+    return {"value": fps, "unit": "frames/s", "steps": n, "seconds": ms * 1e-3, "clocks": clocks,
+            "vs_value": fps / ctx["fps"],
+            "note": "same step, same handles, back to back; `value` (the K-step burst) is the headline when the two agree within 3 %, "
+                    "otherwise this one is"}
+
+
+def issue_roofline(fps_per_gpu, sm_mhz):
+    """Instruction-issue roofline next to the HBM one: the extraction + matching kernels are bound by warp-instruction issue /
+    the integer pipes, not by bytes.  warp_inst_per_frame comes from the committed ncu --set full capture of this workload
+    (profiles/traffic_r02.json, smsp__inst_executed.sum per stage per 256-frame batch); peak = SMs x 4 schedulers x SM clock."""
+    tp = os.path.join(ROOT, "profiles", "traffic_r02.json")
+    if not os.path.exists(tp):
+        return None
+    tj = json.load(open(tp))
+    if "winst" not in tj:
+        return None
+    winst = sum(tj["winst"].values()) / tj["frames"]
+    peak = 148 * 4 * (sm_mhz or 1965.0) * 1e6
+    return {"warp_inst_per_frame": winst, "per_stage": {k: v / tj["frames"] for k, v in tj["winst"].items()},
+            "achieved": fps_per_gpu * winst, "peak": peak, "unit": "warp-instructions/s", "frac": fps_per_gpu * winst / peak,
+            "source": tj["source"]}
+
+
+def _timed_ms(torch, stream, fn, warm=3, reps=8):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record()
+    for i in range(reps):
+        fn(i)
+    with torch.cuda.stream(stream):
+        e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def run_configs(ctx, args, rank, world):
+    """BASELINE.json configs 2-4 on this rank's GPU (config 1's shape is the headline, config 5 the `match` object): inputs
+    generated on the device and resident in HBM, CUDA events on the handle's stream, 3 warm-up + 8 timed batches rotating over
+    2 input batches.  frac = frames/s x B_alg / measured HBM peak."""
+    torch, orbx, dev = ctx["torch"], ctx["orbx"], ctx["dev"]
+    peak, _ = measured_peaks()
+    out = {}
+
+    def frames_on_device(k0, F, w, h, right=0):
+        t = torch.empty((F, h, w), dtype=torch.uint8, device=dev)
+        orbx._check(orbx.lib().orbx_synth_frames_device(t.data_ptr(), k0, F, w, h, 42, right, dev.index))
+        return t
+
+    for name, w, h, nf, F, match, balg in (("cfg2", 640, 480, 1000, 256, True, 1525572), ("cfg4", 1920, 1080, 4000, 128, False, 9269885)):
+        ex = orbx.ORBextractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, device=dev.index)
+        imgs = [frames_on_device((rank * 2 + b) * F, F, w, h) for b in range(2)]
+        ex.extract_batch_device(imgs[0].data_ptr(), F, w, h, LAP)
+        cap = ex.capacity
+        midx = [torch.empty((F - 1, cap), dtype=torch.int32, device=dev) for _ in range(4)]
+        stream = torch.cuda.ExternalStream(ex.stream_ptr(), device=dev)
+
+        def step(i):
+            ex.extract_batch_device(imgs[i % 2].data_ptr(), F, w, h, LAP)
+            if match:
+                ex.match_consecutive_device(*[m.data_ptr() for m in midx])
+        ms = _timed_ms(torch, stream, step)
+        n = ex.counts()[0]
+        fps = F / (ms * 1e-3)
+        out[name] = {"workload": f"{w}x{h}, {nf} features, batch {F}" + (", + frame-to-frame top-2" if match else " (one GPU's share of the 10k-frame job)"),
+                     "frames_per_s": fps, "ms_per_batch": ms, "keypoints_per_frame": float(n.mean()),
+                     "algorithmic_bytes_per_frame": balg, "frac": fps * balg / 1e9 / peak}
+        ex.close()
+        del imgs, midx
+    # config 3: KITTI stereo pairs, left + right extraction on two handles, then the whole ComputeStereoMatches of every pair
+    w, h, nf, F = 1241, 376, 2000, 64
+    exl = orbx.ORBextractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, device=dev.index)
+    exr = orbx.ORBextractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, device=dev.index)
+    left = [frames_on_device((rank * 2 + b) * F, F, w, h, 0) for b in range(2)]
+    right = [frames_on_device((rank * 2 + b) * F, F, w, h, 1) for b in range(2)]
+    sl = torch.cuda.ExternalStream(exl.stream_ptr(), device=dev)
+
+    def pair_step(i):
+        exl.extract_batch_device(left[i % 2].data_ptr(), F, w, h, (0, 0))
+        exr.extract_batch_device(right[i % 2].data_ptr(), F, w, h, (0, 0))
+        exr.sync()  # the pair is complete when both handles are (host-side join; the left handle's events time it)
+    ms = _timed_ms(torch, sl, pair_step)
+    fx, bf = 718.856, 386.1448  # config/Stereo/KITTI00-02.yaml
+    res = (np.zeros((F, exl.capacity), np.float32), np.zeros((F, exl.capacity), np.float32))
+
+    def full(i):
+        exl.extract_batch_device(left[i % 2].data_ptr(), F, w, h, (0, 0))
+        exr.extract_batch_device(right[i % 2].data_ptr(), F, w, h, (0, 0))
+        orbx.compute_stereo_matches_batch(exl, exr, bf, bf / fx, out=res)
+    for i in range(2):
+        full(i)
+    t0 = time.perf_counter()
+    for i in range(6):
+        full(i)
+    full_ms = (time.perf_counter() - t0) / 6 * 1e3
+    n = exl.counts()[0]
+    pps = F / (ms * 1e-3)
+    out["cfg3"] = {"workload": f"{w}x{h} stereo pairs, {nf} features, batch {F} pairs (left + right extraction on two handles)",
+                   "pairs_per_s": pps, "ms_per_batch": ms, "algorithmic_bytes_per_pair": 2 * 2325715, "frac": pps * 2 * 2325715 / 1e9 / peak,
+                   "with_compute_stereo_matches": {"pairs_per_s": F / (full_ms * 1e-3), "ms_per_batch": full_ms,
+                                                   "matched_per_pair": float(np.mean([(res[1][f, :n[f]] > 0).sum() for f in range(F)])),
+                                                   "timing": "host wall clock: both extractions + orbx_compute_stereo_matches_batch, uRight / depth downloaded"}}
+    exl.close()
+    exr.close()
+    return out
+
+
+def run_single_frame(ctx, args):
+    """Drop-in latency: ORB_SLAM3::ORBextractor::operator() of the compat class (orb_slam3_ros2_b200/compat, what Frame::ExtractORB
+    calls, Frame.cc:418-425) on one host thread, one 752x480 frame at a time, with and without the mvImagePyramid download, and the
+    reference class on the same frames (tests/cpp/compat_driver --time)."""
+    import tempfile
+    drv = os.path.join(ROOT, "tests", "cpp", "build", "compat_driver")
+    if not os.path.exists(drv):
+        return {"unavailable": "tests/cpp/build/compat_driver not built (__graft_entry__.build())"}
+    ref = os.path.join(ROOT, "oracle", "_ref", "liborbref_strict.so")
+    nfr = 8
+    frames = ctx["imgs"][0][:nfr].cpu().numpy()
+    with tempfile.TemporaryDirectory() as td:
+        raw = os.path.join(td, "frames.raw")
+        np.ascontiguousarray(frames).tofile(raw)
+        cmd = [drv, "--time", raw, str(W), str(H), str(nfr), str(NFEAT), str(LAP[0]), str(LAP[1]), "300"]
+        if os.path.exists(ref):
+            cmd.append(ref)
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", str(ctx["dev"].index)))
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    if r.returncode != 0:
+        return {"unavailable": (r.stderr or r.stdout)[-300:]}
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    out["api"] = "compat::ORBextractor::operator() -> orbx_extract_frame (one pinned staging buffer, one cudaStreamSynchronize)"
+    out["reference_class"] = "oracle/_ref/liborbref_strict.so (the reference's ORBextractor.cc unchanged on the scalar OpenCV shim), one host thread"
+    return out
 
 
 def run_e2e(ctx, args, world):
@@ -401,7 +581,39 @@ def run_e2e(ctx, args, world):
     for ex in handles:
         if ex is not ctx["ex"]:
             ex.close()
-    return {"value": world * F * steps / dt, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+    # the host <-> device bound of this leg: the same bytes per step, H2D and D2H on two streams at once, nothing else running
+    probe = None
+    try:
+        d_in = torch.empty(h2d, dtype=torch.uint8, device=ctx["dev"])
+        d_out = torch.empty(d2h, dtype=torch.uint8, device=ctx["dev"])
+        h_out = torch.empty(d2h, dtype=torch.uint8).pin_memory()
+        s1, s2 = torch.cuda.Stream(device=ctx["dev"]), torch.cuda.Stream(device=ctx["dev"])
+        flat = h_img.view(-1)[:h2d]
+
+        def both():
+            with torch.cuda.stream(s1):
+                d_in.copy_(flat, non_blocking=True)
+            with torch.cuda.stream(s2):
+                h_out.copy_(d_out, non_blocking=True)
+        both()
+        torch.cuda.synchronize()
+        ctx["barrier"]()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            both()
+        torch.cuda.synchronize()
+        pt = (time.perf_counter() - t0) / 5
+        if world > 1:
+            t = torch.tensor([pt], dtype=torch.float64, device=ctx["dev"])
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            pt = float(t.item())
+        probe = {"seconds_per_step_copies_only": pt, "h2d_GBps_per_gpu": h2d / pt / 1e9, "d2h_GBps_per_gpu": d2h / pt / 1e9,
+                 "aggregate_GBps": world * (h2d + d2h) / pt / 1e9,
+                 "what": "this step's H2D and D2H bytes copied on two streams at once by every rank, max over ranks, no kernels"}
+    except Exception as e:  # the probe is evidence, not part of the measurement
+        probe = {"unavailable": str(e)[:200]}
+    host_bound = world * F / probe["seconds_per_step_copies_only"] if probe and "seconds_per_step_copies_only" in probe else None
+    return {"value": world * F * steps / dt, "host_bound_frames_per_s": host_bound, "pcie_probe": probe, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "steps": steps, "handles": len(parts), "depth": depth, "subbatches": args.e2e_subbatches,
             "api": f"orbx_extract_batch_async + orbx_match_batch_consecutive(mode 2) + orbx_check; a step is split over {len(parts)} handles, {depth} generation(s) of handles and pinned host buffers in flight"}
 
@@ -504,6 +716,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--sustained-s", type=float, default=2.0, help="seconds of back-to-back steps of the sustained leg (0 = skip)")
+    ap.add_argument("--skip-configs", action="store_true", help="skip the configs 2-4 legs")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=256, help="frames per batch (per GPU)")
     ap.add_argument("--db-rows", type=int, default=10_000_000)
@@ -551,7 +765,9 @@ def main():
     achieved = alg / (stage_ms[dom] * 1e-3) / 1e9
     # DRAM traffic of the stage from the committed ncu --set full capture of this same workload (per launch, like `achieved`)
     traffic, traffic_src = None, None
-    tp = os.path.join(ROOT, "profiles", "traffic_r01.json")
+    tp = os.path.join(ROOT, "profiles", "traffic_r02.json")
+    if not os.path.exists(tp):
+        tp = os.path.join(ROOT, "profiles", "traffic_r01.json")
     if os.path.exists(tp) and (W, H) == (752, 480):
         tj = json.load(open(tp))
         if STAGES[dom] in tj:
@@ -576,7 +792,10 @@ def main():
         "clocks": ctx["clocks"], "gpu_launches": int(ctx["launches"]),
         "stage_ms_last_batch": dict(zip(STAGES, [round(x, 4) for x in stage_ms])), "extract_ms_last_batch": ctx["total_ms"],
         "roofline": roofline, "pipeline_roofline": pipeline,
+        "issue_roofline": issue_roofline(ctx["fps"] / world, ctx["clocks"].get("sm_mhz")),
     }
+    if args.sustained_s > 0:
+        out["sustained"] = run_sustained(ctx, args, world)
     if args.only_e2e:
         e = run_e2e(ctx, args, world)
         if rank == 0:
@@ -586,13 +805,17 @@ def main():
         out["e2e"] = run_e2e(ctx, args, world)
         out["match"] = run_match_cfg5(ctx, args, rank, world, local_rank)
         out["bow"] = run_bow(ctx, args, rank, world)
+        if not args.skip_configs:
+            out["configs"] = run_configs(ctx, args, rank, world)
+        if rank == 0 and world == 1:
+            out["single_frame"] = run_single_frame(ctx, args)
         if rank == 0 and world == 1:
             from orb_slam3_ros2_b200 import synth
             cores = os.cpu_count() or 1
             nfr = max(8 * cores, 64)
             frames = synth.frames(0, nfr, W, H)
             fps, kind, _ = cpu_extract_frames_per_s(frames, cores, reps=2)
-            out["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
+            out["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "opencv_layer": OPENCV_NOTE,
                                    "sample": f"{nfr} frames of the same 752x480 stream, best of 2, extraction + frame-to-frame "
                                              f"top-2 matching, one extractor instance per thread",
                                    "match_gpairs_per_s": cpu_match_gpairs_per_s(cores)}

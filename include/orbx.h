@@ -83,6 +83,29 @@ int orbx_capacity(orbx_handle h, int w, int hgt, int* cap);
 int orbx_extract(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int lap0, int lap1,
                  orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index);
 
+/* The drop-in path of one frame with ONE host synchronisation (what compat/ORBextractor.cc calls): the frame is copied into
+ * a page-locked staging buffer owned by the handle, and the keypoints (28-byte cv::KeyPoint records), the descriptors, the
+ * counts and - if want_pyramid - the frame's whole padded pyramid block come back into the same staging buffer behind one
+ * cudaStreamSynchronize.  The returned pointers stay valid until the next call on this handle.  out->pyramid + level[l].offset
+ * is the padded plane of level l: (h + 38) rows of `pitch` bytes, (w + 38) of them meaningful; mvImagePyramid[l] is the ROI at
+ * (19, 19) (ORBextractor.cc:1176-1178).  An empty image is not an error: mono_index = -1, n = 0 (:1090-1091). */
+typedef struct orbx_frame_level {
+    int w, h;            /* level size (ORBextractor.cc:1175) */
+    int pitch;           /* bytes per row of the padded plane */
+    unsigned offset;     /* byte offset of the padded plane inside `pyramid` */
+} orbx_frame_level;
+typedef struct orbx_frame_result {
+    const orbx_keypoint* kps;  /* n records, operator()'s output order */
+    const uint8_t* desc;       /* n x 32 bytes */
+    int n;
+    int mono_index;
+    const uint8_t* pyramid;    /* NULL unless want_pyramid */
+    int nlevels;
+    orbx_frame_level level[16];
+} orbx_frame_result;
+int orbx_extract_frame(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int lap0, int lap1, int want_pyramid,
+                       orbx_frame_result* out);
+
 /* Input staging fused ahead of the pyramid: System::TrackMonocular's cv::resize(im, resized, newImSize) (System.cc:420-425)
  * followed by Tracking::GrabImageMonocular's cvtColor(... -> GRAY) (Tracking.cc:1569-1582), in the reference's order
  * (resize on the interleaved colour image, then grey), then operator().  img: host, `channels` (1, 3 or 4) interleaved

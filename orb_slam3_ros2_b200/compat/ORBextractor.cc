@@ -4,6 +4,8 @@
 
 #include <cassert>
 #include <climits>
+#include <cstddef>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 
@@ -12,6 +14,13 @@
 namespace ORB_SLAM3 {
 
 static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint must be the 28-byte record orbx writes");
+// field by field: pt (x, y), size, angle, response, octave, class_id (opencv2/core/types.hpp; ORBextractor.cc:880-890 writes them)
+static_assert(offsetof(cv::KeyPoint, pt) == offsetof(orbx_keypoint, x) && offsetof(cv::KeyPoint, size) == offsetof(orbx_keypoint, size) &&
+                  offsetof(cv::KeyPoint, angle) == offsetof(orbx_keypoint, angle) &&
+                  offsetof(cv::KeyPoint, response) == offsetof(orbx_keypoint, response) &&
+                  offsetof(cv::KeyPoint, octave) == offsetof(orbx_keypoint, octave) &&
+                  offsetof(cv::KeyPoint, class_id) == offsetof(orbx_keypoint, class_id),
+              "cv::KeyPoint field layout differs from orbx_keypoint");
 
 namespace {
 [[noreturn]] void raise(const char* what) {
@@ -53,32 +62,33 @@ int ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, st
     cv::Mat image = _image.getMat();
     assert(image.type() == CV_8UC1);  // :1094
 
-    int n = 0, monoIndex = 0;
-    // pass 1: run the pipeline, learn the keypoint count (outputs stay on the device)
-    if (orbx_extract(mHandle, image.data, image.cols, image.rows, (int)image.step, vLappingArea[0], vLappingArea[1],
-                     nullptr, nullptr, INT_MAX, &n, &monoIndex) != ORBX_OK)
-        raise("orbx_extract");
+    // one call, one host synchronisation: the results and (if wanted) the padded pyramid arrive in the handle's page-locked
+    // staging buffer and are copied into the caller's containers here
+    orbx_frame_result r;
+    if (orbx_extract_frame(mHandle, image.data, image.cols, image.rows, (int)image.step, vLappingArea[0], vLappingArea[1],
+                           downloadPyramid ? 1 : 0, &r) != ORBX_OK)
+        raise("orbx_extract_frame");
+    const int n = r.n, monoIndex = r.mono_index;
 
-    // pass 2: size the caller's containers as the reference does (:1108-1118) and copy straight into them
+    // size the caller's containers as the reference does (:1108-1118)
     _keypoints = std::vector<cv::KeyPoint>(n);
     if (n == 0) {
         _descriptors.release();
     } else {
+        std::memcpy(static_cast<void*>(_keypoints.data()), r.kps, (size_t)n * sizeof(cv::KeyPoint));
         _descriptors.create(n, 32, CV_8U);
         cv::Mat descriptors = _descriptors.getMat();
         assert(descriptors.isContinuous());
-        if (orbx_batch_download(mHandle, 0, reinterpret_cast<orbx_keypoint*>(_keypoints.data()), descriptors.data, n, &n,
-                                &monoIndex) != ORBX_OK)
-            raise("orbx_batch_download");
+        std::memcpy(descriptors.data, r.desc, (size_t)n * 32);
     }
 
     if (downloadPyramid) {
         for (int level = 0; level < nlevels; ++level) {
-            int w = 0, h = 0;
-            if (orbx_get_pyramid(mHandle, 0, level, nullptr, &w, &h) != ORBX_OK) raise("orbx_get_pyramid");
-            cv::Mat temp(h + 38, w + 38, CV_8UC1);  // fresh buffer per call, like `Mat temp` at :1177
-            if (orbx_get_pyramid(mHandle, 0, level, temp.data, nullptr, nullptr) != ORBX_OK) raise("orbx_get_pyramid");
-            mvImagePyramid[level] = temp(cv::Rect(19, 19, w, h));
+            const orbx_frame_level& L = r.level[level];
+            cv::Mat temp(L.h + 38, L.w + 38, CV_8UC1);  // fresh buffer per call, like `Mat temp` at :1177
+            const uint8_t* src = r.pyramid + L.offset;
+            for (int y = 0; y < L.h + 38; ++y) std::memcpy(temp.ptr(y), src + (size_t)y * L.pitch, (size_t)L.w + 38);
+            mvImagePyramid[level] = temp(cv::Rect(19, 19, L.w, L.h));
         }
     }
     return monoIndex;

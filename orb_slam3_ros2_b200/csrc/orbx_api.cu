@@ -89,6 +89,9 @@ struct orbx_extractor {
     DevMem mBlurTab;
     alignas(64) unsigned char stripMaps[kMaxLevels * 128];
     DevMem mStripTab, mFb, mGroupTab;
+    // orbx_extract_frame: page-locked staging (input frame | counts + flags | keypoints | descriptors | padded pyramid block)
+    void* hostStage = nullptr;
+    size_t hostStageBytes = 0;
     bool useStrips = true;  // FAST over strips of the cell grid (k_fast_strip.cu); ORBX_FAST_STRIP=0 = per-cell kernels only
     bool useTma = true;
     DevMem mKpsUn;           // orbx_undistort_batch: mvKeysUn of the last batch, [frame][cap]
@@ -517,6 +520,7 @@ void orbx_destroy(orbx_handle h) {
                      &h->mSlot, &h->mOutK, &h->mOutD, &h->mOutN, &h->mOutM, &h->mTab, &h->mErr, &h->mKeys1, &h->mKeys2,
                      &h->mMatch, &h->mRaw, &h->mStageTab, &h->mFastTab, &h->mBlurTab, &h->mKpsUn, &h->mStripTab, &h->mFb, &h->mGroupTab};
     for (DevMem* m : all) m->release();
+    if (h->hostStage) cudaFreeHost(h->hostStage);
     for (int i = 0; i < 12; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int p = 0; p < 8; ++p) {
@@ -660,6 +664,65 @@ int orbx_extract(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, 
     if (kps && n) ORBX_CUDA(cudaMemcpyAsync(kps, h->buf.outKps, (size_t)n * 28, cudaMemcpyDeviceToHost, h->stream));
     if (desc && n) ORBX_CUDA(cudaMemcpyAsync(desc, h->buf.outDesc, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream));
     ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_extract_frame(orbx_handle h, const uint8_t* img, int w, int hgt, int stride, int lap0, int lap1, int want_pyramid,
+                       orbx_frame_result* out) {
+    if (!h || !out) return fail(ORBX_ERR_ARG, "null argument");
+    std::memset(out, 0, sizeof(*out));
+    if (!img || w <= 0 || hgt <= 0) {  // ORBextractor.cc:1090-1091
+        out->mono_index = -1;
+        return ORBX_OK;
+    }
+    if (stride < w) return fail(ORBX_ERR_ARG, "stride < width");
+    DeviceGuard guard(h->device);
+    int rc = ensureCapacity(h, w, hgt, 1);
+    if (rc != ORBX_OK) return rc;
+    const FramePlan& P = h->plan;
+    const size_t imgBytes = (size_t)w * hgt;
+    const size_t oImg = 0, oCnt = alignUp((unsigned)imgBytes, 256), oKps = oCnt + 256, oDesc = oKps + alignUp((unsigned)P.outCap * 28, 256);
+    const size_t oPyr = oDesc + alignUp((unsigned)P.outCap * 32, 256), need = oPyr + P.frameBytes;
+    if (need > h->hostStageBytes) {
+        if (h->hostStage) cudaFreeHost(h->hostStage);
+        h->hostStage = nullptr;
+        h->hostStageBytes = 0;
+        ORBX_CUDA(cudaHostAlloc(&h->hostStage, need, cudaHostAllocDefault));
+        h->hostStageBytes = need;
+    }
+    uint8_t* hs = static_cast<uint8_t*>(h->hostStage);
+    if (stride == w) std::memcpy(hs + oImg, img, imgBytes);
+    else
+        for (int y = 0; y < hgt; ++y) std::memcpy(hs + oImg + (size_t)y * w, img + (size_t)y * stride, (size_t)w);
+    ORBX_CUDA(h->mImg.reserve(imgBytes + 64));
+    h->buf.img = (uint8_t*)h->mImg.p;
+    ORBX_CUDA(cudaMemcpyAsync(h->mImg.p, hs + oImg, imgBytes, cudaMemcpyHostToDevice, h->stream));
+    rc = runPipeline(h, (const uint8_t*)h->mImg.p, w, imgBytes, 1, lap0, lap1);
+    if (rc != ORBX_OK) return rc;
+    int* cnt = reinterpret_cast<int*>(hs + oCnt);  // [0] n, [1] monoIndex, [2] device-side flags
+    ORBX_CUDA(cudaMemcpyAsync(cnt, h->buf.outN, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaMemcpyAsync(cnt + 1, h->buf.outMono, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaMemcpyAsync(cnt + 2, h->mErr.p, 4, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaMemcpyAsync(hs + oKps, h->buf.outKps, (size_t)P.outCap * 28, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaMemcpyAsync(hs + oDesc, h->buf.outDesc, (size_t)P.outCap * 32, cudaMemcpyDeviceToHost, h->stream));
+    if (want_pyramid) ORBX_CUDA(cudaMemcpyAsync(hs + oPyr, h->buf.pyr, P.frameBytes, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    if (cnt[2]) {
+        cudaMemsetAsync(h->mErr.p, 0, 16, h->stream);
+        char msg[96];
+        snprintf(msg, sizeof msg, "device-side capacity invariant violated (flags 0x%x)", cnt[2]);
+        return fail(ORBX_ERR_CAPACITY, msg);
+    }
+    out->kps = reinterpret_cast<const orbx_keypoint*>(hs + oKps);
+    out->desc = hs + oDesc;
+    out->n = cnt[0];
+    out->mono_index = cnt[1];
+    out->pyramid = want_pyramid ? hs + oPyr : nullptr;
+    out->nlevels = P.nlevels;
+    for (int l = 0; l < P.nlevels; ++l) {
+        out->level[l].w = P.lv[l].w; out->level[l].h = P.lv[l].h;
+        out->level[l].pitch = P.lv[l].pitch; out->level[l].offset = P.lv[l].planeOff;
+    }
     return ORBX_OK;
 }
 

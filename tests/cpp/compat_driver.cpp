@@ -5,11 +5,17 @@
 //
 //   compat_driver <frames.raw> <w> <h> <nframes> <nfeatures> <lap0> <lap1> <liborbref.so>
 // exit 0 = every frame bit-identical (monoIndex, keypoints, descriptors, all padded pyramid planes, tables).
+//   compat_driver --time <frames.raw> <w> <h> <nframes> <nfeatures> <lap0> <lap1> <reps> [<liborbref.so>]
+// the DROP-IN LATENCY: median / p90 wall milliseconds of ORB_SLAM3::ORBextractor::operator() on one host thread, frame by
+// frame (what Frame::ExtractORB costs the tracking thread, Frame.cc:418-425), with and without the mvImagePyramid download,
+// and of the reference class on the same frames; one JSON line.
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <vector>
 
 #include "ORBextractor.h"
@@ -30,7 +36,82 @@ typedef float (*ref_sf_t)(void*);
         }                                 \
     } while (0)
 
+static double nowMs() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+static void stats(std::vector<double> v, double* med, double* p90) {
+    std::sort(v.begin(), v.end());
+    *med = v.empty() ? 0 : v[v.size() / 2];
+    *p90 = v.empty() ? 0 : v[std::min(v.size() - 1, (size_t)(v.size() * 9 / 10))];
+}
+
+static int timeMode(int argc, char** argv) {
+    if (argc < 10) {
+        fprintf(stderr, "usage: compat_driver --time frames.raw w h nframes nfeatures lap0 lap1 reps [liborbref.so]\n");
+        return 2;
+    }
+    const int w = atoi(argv[3]), h = atoi(argv[4]), nframes = atoi(argv[5]), nfeat = atoi(argv[6]), reps = atoi(argv[9]);
+    std::vector<int> lap = {atoi(argv[7]), atoi(argv[8])};
+    std::vector<uint8_t> frames((size_t)w * h * nframes);
+    FILE* fp = fopen(argv[2], "rb");
+    CHECK(fp, "cannot open %s", argv[2]);
+    CHECK(fread(frames.data(), 1, frames.size(), fp) == frames.size(), "short read");
+    fclose(fp);
+    ORB_SLAM3::ORBextractor ex(nfeat, 1.2f, 8, 20, 7);
+    double res[2][2] = {{0, 0}, {0, 0}};
+    size_t kp = 0;
+    for (int withPyr = 1; withPyr >= 0; --withPyr) {
+        ex.downloadPyramid = withPyr != 0;
+        std::vector<double> t;
+        for (int r = -3; r < reps; ++r) {  // three warm-up calls (plan, buffers, staging)
+            const int f = ((r % nframes) + nframes) % nframes;
+            cv::Mat im(h, w, CV_8UC1, frames.data() + (size_t)f * w * h, (size_t)w);
+            std::vector<cv::KeyPoint> keys;
+            cv::Mat desc;
+            const double t0 = nowMs();
+            ex(im, cv::Mat(), keys, desc, lap);
+            if (r >= 0) t.push_back(nowMs() - t0);
+            kp = keys.size();
+        }
+        stats(t, &res[withPyr][0], &res[withPyr][1]);
+    }
+    double refMed = 0, refP90 = 0;
+    int refReps = 0;
+    if (argc > 10) {
+        void* lib = dlopen(argv[10], RTLD_NOW | RTLD_LOCAL);
+        if (lib) {
+            ref_create_t rcreate = (ref_create_t)dlsym(lib, "orbref_create");
+            ref_destroy_t rdestroy = (ref_destroy_t)dlsym(lib, "orbref_destroy");
+            ref_extract_t rextract = (ref_extract_t)dlsym(lib, "orbref_extract");
+            if (rcreate && rdestroy && rextract) {
+                void* ref = rcreate(nfeat, 1.2f, 8, 20, 7);
+                const int cap = nfeat + 64;
+                std::vector<cv::KeyPoint> rk(cap);
+                std::vector<uint8_t> rd((size_t)cap * 32);
+                std::vector<double> t;
+                refReps = std::min(reps, 24);
+                for (int r = -1; r < refReps; ++r) {
+                    const int f = ((r % nframes) + nframes) % nframes;
+                    int rn = 0;
+                    const double t0 = nowMs();
+                    rextract(ref, frames.data() + (size_t)f * w * h, w, h, w, lap[0], lap[1], rk.data(), rd.data(), cap, &rn);
+                    if (r >= 0) t.push_back(nowMs() - t0);
+                }
+                stats(t, &refMed, &refP90);
+                rdestroy(ref);
+            }
+        }
+    }
+    printf("{\"frame\": \"%dx%d\", \"nfeatures\": %d, \"reps\": %d, \"keypoints\": %zu, \"with_pyramid_ms\": {\"median\": %.4f, \"p90\": %.4f}, "
+           "\"without_pyramid_ms\": {\"median\": %.4f, \"p90\": %.4f}, \"reference_class_ms\": {\"median\": %.3f, \"p90\": %.3f, \"reps\": %d}}\n",
+           w, h, nfeat, reps, kp, res[1][0], res[1][1], res[0][0], res[0][1], refMed, refP90, refReps);
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && strcmp(argv[1], "--time") == 0) return timeMode(argc, argv);
     if (argc < 9) {
         fprintf(stderr, "usage: compat_driver frames.raw w h nframes nfeatures lap0 lap1 liborbref.so\n");
         return 2;

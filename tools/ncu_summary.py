@@ -14,7 +14,7 @@ units = rows[1]
 names = [(units[idx[c]] if c == "gpu__time_duration.sum" and c in idx else n) for c, n in cols]  # the duration column's own unit
 print("kernel".ljust(28), " ".join(n.rjust(9) for n in names), " grid")
 for r in rows[2:]:
-    name = r[idx["Kernel Name"]].split("(")[0].split("::")[-1][:28]
+    name = r[idx["Kernel Name"]].split("(")[0].split("::")[-1].replace(" ", "")[:28]
     vals = []
     for c, _ in cols:
         v = r[idx[c]] if c in idx else ""
