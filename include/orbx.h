@@ -62,6 +62,10 @@ unsigned long long orbx_launch_count(void);
 /* ---- extractor life cycle: ORBextractor::ORBextractor (ORBextractor.cc:409-469) -------------------- */
 int orbx_create(const orbx_params* params, orbx_handle* out);
 void orbx_destroy(orbx_handle h);
+/* Debugging aid (the reference has no sanitizer set-up; compute-sanitizer is closed on the GPU pool this was
+ * built on): with ORBX_GUARD=1 in the environment every device buffer of a handle carries a 256-byte guard band; this call
+ * synchronises the device and returns ORBX_ERR_CAPACITY naming the buffer if a kernel wrote behind one, ORBX_OK otherwise. */
+int orbx_debug_check_guards(orbx_handle h);
 
 /* Per-level tables the reference exposes through GetScaleFactors(), GetInverseScaleFactors(),
  * GetScaleSigmaSquares(), GetInverseScaleSigmaSquares() (ORBextractor.h:61-83) and mnFeaturesPerLevel

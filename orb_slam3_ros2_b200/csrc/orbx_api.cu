@@ -35,6 +35,14 @@ static int fail(int code, const std::string& msg) {
 static inline int cvRoundF(float v) { return (int)lrintf(v); }  // cvRound: round half to even
 static inline unsigned alignUp(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
 
+// ORBX_GUARD=1 (debugging; compute-sanitizer is closed on this pool): every device buffer gets a 256-byte guard band behind it,
+// filled with 0xA5; orbx_debug_check_guards verifies the bands after a run (an out-of-bounds WRITE of a kernel lands there)
+static bool guardOn() {
+    static const bool on = [] { const char* e = std::getenv("ORBX_GUARD"); return e && e[0] == '1'; }();
+    return on;
+}
+constexpr size_t kGuardBytes = 256;
+
 struct DevMem {
     void* p = nullptr;
     size_t bytes = 0;
@@ -43,9 +51,19 @@ struct DevMem {
         if (p) cudaFree(p);
         p = nullptr;
         bytes = 0;
-        cudaError_t e = cudaMalloc(&p, need);
+        cudaError_t e = cudaMalloc(&p, need + (guardOn() ? kGuardBytes : 0));
         if (e == cudaSuccess) bytes = need;
+        if (e == cudaSuccess && guardOn()) e = cudaMemset(static_cast<uint8_t*>(p) + need, 0xA5, kGuardBytes);
         return e;
+    }
+    // 0 = intact (or guards off / nothing allocated), 1 = overwritten, -1 = CUDA error
+    int guardIntact() const {
+        if (!guardOn() || !p) return 0;
+        uint8_t host[kGuardBytes];
+        if (cudaMemcpy(host, static_cast<const uint8_t*>(p) + bytes, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+        for (size_t i = 0; i < kGuardBytes; ++i)
+            if (host[i] != 0xA5) return 1;
+        return 0;
     }
     void release() {
         if (p) cudaFree(p);
@@ -509,6 +527,25 @@ int orbx_capacity(orbx_handle h, int w, int hgt, int* cap) {
     for (int l = 0; l < h->prm.nlevels; ++l)
         sum += levelKpCap(h->nPerLevel[l], cvRoundF((float)w * h->isf[l]), cvRoundF((float)hgt * h->isf[l]));
     *cap = sum;
+    return ORBX_OK;
+}
+
+int orbx_debug_check_guards(orbx_handle h) {
+    if (!h) return fail(ORBX_ERR_ARG, "null handle");
+    if (!guardOn()) return fail(ORBX_ERR_STATE, "guard bands are off (set ORBX_GUARD=1 before the first call)");
+    DeviceGuard guard(h->device);
+    ORBX_CUDA(cudaDeviceSynchronize());
+    struct { const char* name; const DevMem* m; } all[] = {
+        {"img", &h->mImg}, {"pyr", &h->mPyr}, {"blur", &h->mBlur}, {"cand", &h->mCand}, {"cellCnt", &h->mCellCnt}, {"gath", &h->mGath},
+        {"nid", &h->mNid}, {"lkp", &h->mLkp}, {"lkpCnt", &h->mLkpCnt}, {"slot", &h->mSlot}, {"outK", &h->mOutK}, {"outD", &h->mOutD},
+        {"outN", &h->mOutN}, {"outM", &h->mOutM}, {"tab", &h->mTab}, {"err", &h->mErr}, {"keys1", &h->mKeys1}, {"keys2", &h->mKeys2},
+        {"match", &h->mMatch}, {"fastTab", &h->mFastTab}, {"blurTab", &h->mBlurTab}, {"stripTab", &h->mStripTab}, {"fb", &h->mFb},
+        {"groupTab", &h->mGroupTab}, {"kpsUn", &h->mKpsUn}, {"raw", &h->mRaw}, {"stageTab", &h->mStageTab}};
+    for (const auto& e : all) {
+        const int r = e.m->guardIntact();
+        if (r < 0) return fail(ORBX_ERR_CUDA, std::string("reading the guard band of ") + e.name);
+        if (r > 0) return fail(ORBX_ERR_CAPACITY, std::string("guard band behind device buffer '") + e.name + "' was overwritten");
+    }
     return ORBX_OK;
 }
 

@@ -98,6 +98,8 @@ SYMBOLS = {
     "orbx_search_by_bow_kf": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p,
                                         _i32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_capacity": (C.c_int, [_vp, C.c_int, C.c_int, _i32p]),
+    "orbx_debug_check_guards": (C.c_int, [_vp]),
+    "orbx_extract_frame": (C.c_int, [_vp, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "orbx_voc_create": (C.c_int, [C.c_int, _i32p, _u8p, C.POINTER(C.c_double), C.c_int, C.c_int, C.POINTER(_vp)]),
     "orbx_voc_destroy": (None, [_vp]),
@@ -211,6 +213,10 @@ class ORBextractor:
         if pyramid:
             self.mvImagePyramid = [self.pyramid_level(0, l)[19:-19, 19:-19] for l in range(self.nlevels)]
         return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def check_guards(self):
+        """ORBX_GUARD=1 only: raises if a kernel wrote behind one of this handle's device buffers."""
+        _check(lib().orbx_debug_check_guards(self._h))
 
     def set_subbatches(self, n):
         _check(lib().orbx_set_subbatches(self._h, int(n)))
