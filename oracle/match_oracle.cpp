@@ -512,6 +512,157 @@ int orbo_search_for_initialization(const void* kps1_, const uint8_t* desc1, int 
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono) (src/ORBmatcher.cc:1676-1887) ----
+// TrackWithMotionModel's matcher (Tracking.cc:2876, :2906, :2914), frames with Nleft == -1 (monocular, rectified stereo, RGB-D).
+// Restated statement by statement; the Sophus / Eigen operations are written out in the order the vendored headers write them
+// (Thirdparty/Sophus/sophus/so3.hpp:358-368, se3.hpp:321-325 and inverse(); Eigen's cross product), every operation rounded once
+// (this file is compiled with -ffp-contract=off): the declared STRICT arithmetic, the same as oracle/refslice/shim.h.
+// Arguments as refslice_search_by_projection_ff (oracle/refslice/refslice_wrap.cpp).  PINNED to the reference's own body by
+// tests/test_oracle_refslices.py.
+namespace {
+struct V3 { float x, y, z; };
+inline V3 crossq(float ax, float ay, float az, V3 b) { return {ay * b.z - az * b.y, az * b.x - ax * b.z, ax * b.y - ay * b.x}; }
+inline V3 rotq(const float* q, V3 p) {  // so3.hpp:366-368
+    V3 uv = crossq(q[0], q[1], q[2], p);
+    uv.x += uv.x; uv.y += uv.y; uv.z += uv.z;
+    const V3 c = crossq(q[0], q[1], q[2], uv);
+    return {(p.x + q[3] * uv.x) + c.x, (p.y + q[3] * uv.y) + c.y, (p.z + q[3] * uv.z) + c.z};
+}
+inline V3 se3mul(const float* T, V3 p) {  // se3.hpp:324
+    const V3 r = rotq(T, p);
+    return {r.x + T[4], r.y + T[5], r.z + T[6]};
+}
+}  // namespace
+
+int orbo_search_by_projection_ff(const void* kps_last_, const uint8_t* last_flags, const float* world, const uint8_t* mp_desc, int n_last,
+                                 const void* kps_cur_, const uint8_t* desc_cur, const float* cur_u_right, const uint8_t* cur_taken, int n_cur,
+                                 const float* pose_cw, const float* pose_lw, const float* cam, float mnMinX, float mnMaxX, float mnMinY,
+                                 float mnMaxY, const float* mvScaleFactors, int nlevels, float mbf, float mb, float th, int bMono,
+                                 float mfNNratio, int mbCheckOrientation, int32_t* match_cur) {
+    (void)mfNNratio; (void)nlevels;
+    const Kp* kl = static_cast<const Kp*>(kps_last_);
+    const Kp* kc = static_cast<const Kp*>(kps_cur_);
+    constexpr int HISTO_LENGTH = 30;
+    const float mfGridElementWidthInv = static_cast<float>(GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);  // Frame.cc:251
+    const float mfGridElementHeightInv = static_cast<float>(GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+    std::vector<std::vector<int>> grid((size_t)GRID_COLS * GRID_ROWS);
+    for (int i = 0; i < n_cur; ++i) {  // Frame.cc:385-416, :725-735
+        const int posX = (int)std::round((kc[i].x - mnMinX) * mfGridElementWidthInv);
+        const int posY = (int)std::round((kc[i].y - mnMinY) * mfGridElementHeightInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        grid[(size_t)posX * GRID_ROWS + posY].push_back(i);
+    }
+    // CurrentFrame.mvpMapPoints: -1 = NULL, -2 = a map point of the caller with Observations() > 0, i >= 0 = LastFrame's map point i
+    for (int i = 0; i < n_cur; ++i) match_cur[i] = (cur_taken && cur_taken[i]) ? -2 : -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    // :1686-1693
+    float invq[7] = {-pose_cw[0], -pose_cw[1], -pose_cw[2], pose_cw[3], 0, 0, 0};
+    const V3 twc = rotq(invq, {pose_cw[4] * -1.f, pose_cw[5] * -1.f, pose_cw[6] * -1.f});  // Tcw.inverse().translation()
+    const V3 tlc = se3mul(pose_lw, twc);
+    const bool bForward = tlc.z > mb && !bMono;
+    const bool bBackward = -tlc.z > mb && !bMono;
+    for (int i = 0; i < n_last; i++) {
+        if (!(last_flags[i] & 1)) continue;  // pMP && !mvbOutlier[i]
+        const V3 x3Dc = se3mul(pose_cw, {world[3 * i], world[3 * i + 1], world[3 * i + 2]});
+        const float invzc = 1.0 / x3Dc.z;  // double division, rounded to float (:1709)
+        if (invzc < 0) continue;
+        const float u = cam[0] * x3Dc.x / x3Dc.z + cam[2], v = cam[1] * x3Dc.y / x3Dc.z + cam[3];  // Pinhole.cpp:45-46
+        if (u < mnMinX || u > mnMaxX) continue;
+        if (v < mnMinY || v > mnMaxY) continue;
+        const int nLastOctave = kl[i].octave;
+        const float radius = th * mvScaleFactors[nLastOctave];
+        int minLevel, maxLevel;
+        if (bForward) { minLevel = nLastOctave; maxLevel = -1; }
+        else if (bBackward) { minLevel = 0; maxLevel = nLastOctave; }
+        else { minLevel = nLastOctave - 1; maxLevel = nLastOctave + 1; }
+        std::vector<int> vIndices2;
+        {
+            const float x = u, y = v, factorX = radius, factorY = radius;
+            const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * mfGridElementWidthInv));
+            const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * mfGridElementWidthInv));
+            const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * mfGridElementHeightInv));
+            const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * mfGridElementHeightInv));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+                const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+                        for (int idx : grid[(size_t)ix * GRID_ROWS + iy]) {
+                            const Kp& kpUn = kc[idx];
+                            if (bCheckLevels) {
+                                if (kpUn.octave < minLevel) continue;
+                                if (maxLevel >= 0)
+                                    if (kpUn.octave > maxLevel) continue;
+                            }
+                            const float distx = kpUn.x - x, disty = kpUn.y - y;
+                            if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices2.push_back(idx);
+                        }
+            }
+        }
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            // :1745-1747 a feature that already holds a map point with observations is skipped
+            if (match_cur[i2] == -2 || (match_cur[i2] >= 0 && (last_flags[match_cur[i2]] & 2))) continue;
+            if (cur_u_right && cur_u_right[i2] > 0) {  // :1749-1755 (Nleft == -1)
+                const float ur = u - mbf * invzc;
+                const float er = std::fabs(ur - cur_u_right[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = orbo_hamming(mp_desc + (size_t)i * 32, desc_cur + (size_t)i2 * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx2 = i2;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            match_cur[bestIdx2] = i;
+            nmatches++;
+            if (mbCheckOrientation) {
+                float rot = kl[i].angle - kc[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        // ComputeThreeMaxima (ORBmatcher.cc:2012-2053)
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) {
+                max3 = max2; max2 = max1; max1 = s;
+                ind3 = ind2; ind2 = ind1; ind1 = i;
+            } else if (s > max2) {
+                max3 = max2; max2 = s;
+                ind3 = ind2; ind2 = i;
+            } else if (s > max3) {
+                max3 = s;
+                ind3 = i;
+            }
+        }
+        if (max2 < 0.1f * (float)max1) {
+            ind2 = -1;
+            ind3 = -1;
+        } else if (max3 < 0.1f * (float)max1) {
+            ind3 = -1;
+        }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {  // :1877-1881: unconditional, entry by entry
+                match_cur[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    for (int i = 0; i < n_cur; ++i)
+        if (match_cur[i] == -2) match_cur[i] = -1;  // the caller's own map points are not reported
+    return nmatches;
+}
+
 // ---- ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) (src/ORBmatcher.cc:765-905), monocular keyframes ----
 // The keyframe-to-keyframe twin of orbo_search_by_bow (loop closing / merging): candidates of keyframe 2 need a good MapPoint
 // and must not be matched yet (vbMatched2, :826-830), the accept rule is STRICT in TH_LOW (bestDist1 < TH_LOW, :848), the

@@ -406,6 +406,41 @@ def ref_search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched
                                       window_size, nnratio, check_orientation)
 
 
+def _search_by_projection_ff(fn, kps_last, last_flags, world, mp_desc, kps_cur, desc_cur, pose_cw, pose_lw, cam, bounds, scale_factors,
+                             th, mono, mbf=0.0, mb=0.0, cur_u_right=None, cur_taken=None, nnratio=0.9, check_orientation=True):
+    kps_last = np.ascontiguousarray(kps_last); kps_cur = np.ascontiguousarray(kps_cur)
+    assert kps_last.dtype.itemsize == 28 and kps_cur.dtype.itemsize == 28
+    n_last, n_cur = len(kps_last), len(kps_cur)
+    last_flags = np.ascontiguousarray(last_flags, dtype=np.uint8)
+    world = np.ascontiguousarray(world, dtype=np.float32).reshape(-1, 3)
+    mp_desc = np.ascontiguousarray(mp_desc, dtype=np.uint8); desc_cur = np.ascontiguousarray(desc_cur, dtype=np.uint8)
+    pose_cw = np.ascontiguousarray(pose_cw, dtype=np.float32); pose_lw = np.ascontiguousarray(pose_lw, dtype=np.float32)
+    cam = np.ascontiguousarray(cam, dtype=np.float32); sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    ur = None if cur_u_right is None else np.ascontiguousarray(cur_u_right, dtype=np.float32)
+    tk = None if cur_taken is None else np.ascontiguousarray(cur_taken, dtype=np.uint8)
+    out = np.full(max(n_cur, 1), -1, dtype=np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_void_p, _u8p, _f32p, _u8p, C.c_int, C.c_void_p, _u8p, _f32p, _u8p, C.c_int, _f32p, _f32p, _f32p, C.c_float,
+                   C.c_float, C.c_float, C.c_float, _f32p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, _i32p]
+    n = fn(kps_last.ctypes.data_as(C.c_void_p), _ptr(last_flags), _ptr(world, _f32p), _ptr(mp_desc), n_last,
+           kps_cur.ctypes.data_as(C.c_void_p), _ptr(desc_cur), None if ur is None else _ptr(ur, _f32p), None if tk is None else _ptr(tk),
+           n_cur, _ptr(pose_cw, _f32p), _ptr(pose_lw, _f32p), _ptr(cam, _f32p), *[float(b) for b in bounds], _ptr(sf, _f32p), len(sf),
+           float(mbf), float(mb), float(th), 1 if mono else 0, float(nnratio), 1 if check_orientation else 0, _ptr(out, _i32p))
+    return int(n), out[:n_cur]
+
+
+def search_by_projection_ff(*a, **k):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1676-1887), Nleft == -1 frames ->
+    (nmatches, match_cur[n_cur]: index of the last-frame feature whose map point the current feature holds, or -1).
+    poses = (qx, qy, qz, qw, tx, ty, tz); cam = (fx, fy, cx, cy); last_flags bit 0 = map point and not outlier, bit 1 = Observations() > 0."""
+    return _search_by_projection_ff(port_lib().orbo_search_by_projection_ff, *a, **k)
+
+
+def ref_search_by_projection_ff(*a, **k):
+    """The same through the reference's own body (librefslices.so)."""
+    return _search_by_projection_ff(_slices().refslice_search_by_projection_ff, *a, **k)
+
+
 def stage_gray(img, rgb=True, new_size=None):
     """System.cc:420-425 (cv::resize on the interleaved colour image) then Tracking.cc:1569-1582 (cvtColor -> GRAY);
     OpenCV 8-bit RGB2Gray = (R*9798 + G*19235 + B*3735 + 2^14) >> 15."""

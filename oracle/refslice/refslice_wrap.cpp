@@ -9,6 +9,8 @@
 //   ORBmatcher.cc:2012-2053  ORBmatcher::ComputeThreeMaxima
 //   ORBmatcher.cc:648-763    ORBmatcher::SearchForInitialization
 //   ORBmatcher.cc:765-905    ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)
+//   ORBmatcher.cc:1676-1887  ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono)  (TrackWithMotionModel's matcher)
+//   Pinhole.cpp:43-49        Pinhole::project(const Eigen::Vector3f&)
 //   Frame.cc:385-416         Frame::AssignFeaturesToGrid
 //   Frame.cc:657-723         Frame::GetFeaturesInArea
 //   Frame.cc:725-735         Frame::PosInGrid
@@ -38,6 +40,8 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 #include "ORBmatcher_ComputeThreeMaxima.inc"
 #include "ORBmatcher_SearchForInitialization.inc"
 #include "ORBmatcher_SearchByBoW_KFKF.inc"
+#include "Pinhole_project.inc"
+#include "ORBmatcher_SearchByProjection_FF.inc"
 }  // namespace ORB_SLAM3
 
 using ORB_SLAM3::Frame;
@@ -363,6 +367,65 @@ int refslice_search_by_bow_kf(const uint8_t* desc1, int n1, const uint8_t* valid
     std::vector<ORB_SLAM3::MapPoint*> out;
     const int n = matcher.SearchByBoW(&KF1, &KF2, out);
     for (int i = 0; i < n1; ++i) match12[i] = out[i] ? out[i]->index : -1;
+    return n;
+}
+
+// ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) for Nleft == -1 frames (monocular / rectified stereo / RGB-D).
+// last_flags[i]: bit 0 = LastFrame.mvpMapPoints[i] != NULL and !mvbOutlier[i], bit 1 = that map point's Observations() > 0;
+// world: n_last x 3; mp_desc: the map points' descriptors; pose = (qx, qy, qz, qw, tx, ty, tz); cur_taken[i2] != 0: the current
+// frame's feature already holds a map point with Observations() > 0; cur_u_right may be NULL (all -1).  match_cur[i2] = index of the
+// last-frame feature whose map point CurrentFrame.mvpMapPoints[i2] ends up holding, or -1.  Returns nmatches.
+int refslice_search_by_projection_ff(const void* kps_last, const uint8_t* last_flags, const float* world, const uint8_t* mp_desc, int n_last,
+                                     const void* kps_cur, const uint8_t* desc_cur, const float* cur_u_right, const uint8_t* cur_taken,
+                                     int n_cur, const float* pose_cw, const float* pose_lw, const float* cam, float min_x, float max_x,
+                                     float min_y, float max_y, const float* scale_factors, int nlevels, float mbf, float mb, float th,
+                                     int b_mono, float nnratio, int check_orientation, int32_t* match_cur) {
+    Frame Cur, Last;
+    auto pose = [](const float* p) {
+        Sophus::SE3f T;
+        T.qx = p[0]; T.qy = p[1]; T.qz = p[2]; T.qw = p[3]; T.t[0] = p[4]; T.t[1] = p[5]; T.t[2] = p[6];
+        return T;
+    };
+    ORB_SLAM3::Pinhole camera;
+    camera.mvParameters = {cam[0], cam[1], cam[2], cam[3]};
+    Cur.N = n_cur; Cur.Nleft = -1;
+    Cur.mvKeysUn = keypoints(kps_cur, n_cur);
+    Cur.mvKeys = Cur.mvKeysUn;
+    Cur.mDescriptors = descriptors(desc_cur, n_cur);
+    Cur.mvuRight.assign(n_cur, -1.f);
+    if (cur_u_right) Cur.mvuRight.assign(cur_u_right, cur_u_right + n_cur);
+    Cur.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    Cur.mbf = mbf; Cur.mb = mb;
+    Cur.mTcw = pose(pose_cw);
+    Cur.mpCamera = &camera;
+    Frame::mnMinX = min_x; Frame::mnMaxX = max_x; Frame::mnMinY = min_y; Frame::mnMaxY = max_y;
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);   // Frame.cc:251
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);  // Frame.cc:252
+    Cur.AssignFeaturesToGrid();
+    std::vector<ORB_SLAM3::MapPoint> takenPts(n_cur);
+    Cur.mvpMapPoints.assign(n_cur, nullptr);
+    for (int i = 0; i < n_cur; ++i)
+        if (cur_taken && cur_taken[i]) {
+            takenPts[i].nObs = 1; takenPts[i].index = -2;
+            Cur.mvpMapPoints[i] = &takenPts[i];
+        }
+    Last.N = n_last; Last.Nleft = -1;
+    Last.mvKeysUn = keypoints(kps_last, n_last);
+    Last.mvKeys = Last.mvKeysUn;
+    Last.mTcw = pose(pose_lw);
+    std::vector<ORB_SLAM3::MapPoint> pts(n_last);
+    Last.mvpMapPoints.assign(n_last, nullptr);
+    Last.mvbOutlier.assign(n_last, false);
+    for (int i = 0; i < n_last; ++i) {
+        pts[i].index = i;
+        pts[i].nObs = (last_flags[i] & 2) ? 3 : 0;
+        pts[i].mWorldPos = Eigen::Vector3f(world[3 * i], world[3 * i + 1], world[3 * i + 2]);
+        pts[i].mDescriptor = descriptors(mp_desc + (size_t)i * 32, 1);
+        if (last_flags[i] & 1) Last.mvpMapPoints[i] = &pts[i];
+    }
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    const int n = matcher.SearchByProjection(Cur, Last, th, b_mono != 0);
+    for (int i = 0; i < n_cur; ++i) match_cur[i] = (Cur.mvpMapPoints[i] && Cur.mvpMapPoints[i]->index >= 0) ? Cur.mvpMapPoints[i]->index : -1;
     return n;
 }
 

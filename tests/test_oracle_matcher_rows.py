@@ -143,3 +143,49 @@ def test_compute_stereo_matches_known_disparity(oracle):
     # no right keypoints -> nothing matched, no crash
     ur0, dp0 = oracle.compute_stereo_matches(kl, dl, kr[:0], dr[:0], sf, isf, pl, pr, bf, b)
     assert (ur0 == -1).all() and (dp0 == -1).all()
+
+
+def make_projection_case(oracle, k=0, w=752, h=480, nf=1000, seed=0, mono=True, dz=0.0, rot=0.0, taken_frac=0.05, stereo=False):
+    """Two consecutive synthetic frames (frame k+1 is frame k shifted by (-3, -1) px), the last frame's keypoints back-projected with
+    pseudo-random depths into map points, a current pose that moves them by about the image shift (+ an optional z motion / roll)."""
+    from orb_slam3_ros2_b200 import synth
+    rng = np.random.default_rng(seed)
+    ex = oracle.PortExtractor(nfeatures=nf)
+    _, kl, dl = ex.extract(synth.frame(k, w, h), (0, 1000))
+    _, kc, dc = ex.extract(synth.frame(k + 1, w, h), (0, 1000))
+    sf = ex.tables()["scale"]
+    fx, fy, cx, cy = 458.654, 457.296, 367.215, 248.375  # config/Monocular/EuRoC.yaml
+    n = len(kl)
+    z = rng.uniform(4.0, 9.0, n).astype(np.float32)
+    world = np.stack([(kl["x"] - cx) / fx * z, (kl["y"] - cy) / fy * z, z], axis=1).astype(np.float32)  # LastFrame pose = identity
+    flags = (rng.random(n) < 0.85).astype(np.uint8) | ((rng.random(n) < 0.7).astype(np.uint8) << 1)
+    mp_desc = dl.copy()
+    flip = rng.random(n) < 0.3  # some map point descriptors differ from the last observation by a few bits
+    for i in np.flatnonzero(flip):
+        for b in rng.integers(0, 256, 6):
+            mp_desc[i, b // 8] ^= np.uint8(1 << (b % 8))
+    half = np.float32(rot / 2)
+    pose_cw = np.array([0, 0, np.sin(half), np.cos(half), -3.0 * 6.0 / fx, -1.0 * 6.0 / fy, dz], dtype=np.float32)
+    pose_lw = np.array([0, 0, 0, 1, 0, 0, 0], dtype=np.float32)
+    taken = (rng.random(len(kc)) < taken_frac).astype(np.uint8)
+    ur = None
+    if stereo:
+        ur = np.where(rng.random(len(kc)) < 0.6, kc["x"] - rng.uniform(2, 40, len(kc)), -1).astype(np.float32)
+    return dict(kps_last=kl, last_flags=flags, world=world, mp_desc=mp_desc, kps_cur=kc, desc_cur=dc, pose_cw=pose_cw, pose_lw=pose_lw,
+                cam=(fx, fy, cx, cy), bounds=(0.0, float(w), 0.0, float(h)), scale_factors=sf, th=15 if mono else 7, mono=mono,
+                mbf=40.0 if stereo else 0.0, mb=0.08 if stereo else 0.0, cur_u_right=ur, cur_taken=taken)
+
+
+def test_search_by_projection_frame_frame_known_properties(oracle):
+    c = make_projection_case(oracle, k=2, seed=1)
+    n, m = oracle.search_by_projection_ff(**c)
+    assert n > 300  # most projected map points find their feature again
+    hit = np.flatnonzero(m >= 0)
+    assert len(hit) <= n  # later points may overwrite earlier ones (nmatches counts both)
+    kl, kc = c["kps_last"], c["kps_cur"]
+    dx = kc["x"][hit] - kl["x"][m[hit]]
+    assert np.median(np.abs(dx + 3.0 * c["scale_factors"][kl["octave"][m[hit]]] ** 0)) < 15  # matches sit near the shifted position
+    assert not np.any(c["cur_taken"][hit])          # features that already held a map point are never given another
+    assert np.all(c["last_flags"][m[hit]] & 1)      # only valid map points are projected
+    n0, m0 = oracle.search_by_projection_ff(**dict(c, check_orientation=False))
+    assert n0 >= n                                   # the rotation histogram only removes matches

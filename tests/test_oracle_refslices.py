@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from orb_slam3_ros2_b200 import synth
-from test_oracle_matcher_rows import make_grid_case
+from test_oracle_matcher_rows import make_grid_case, make_projection_case
 
 
 @pytest.fixture(scope="module")
@@ -223,3 +223,19 @@ def test_accept_rules_equal_the_reference_conditions(slices, rule):
                     got = slices.accept_top2(rule, d1, d2, ratio, idx2=idx2, level1=np.full(d1.shape, lv[0], np.int32),
                                              level2=np.full(d1.shape, lv[1], np.int32))
                     assert np.array_equal(np.asarray(got, bool), want), (rule, site, ratio, lv, results)
+
+
+@pytest.mark.parametrize("kw", [dict(k=0, seed=0), dict(k=3, seed=1, nf=2000, w=1241, h=376), dict(k=1, seed=2, mono=False, stereo=True, dz=0.3),
+                                dict(k=2, seed=3, mono=False, stereo=True, dz=-0.3), dict(k=4, seed=4, rot=0.35), dict(k=5, seed=5, taken_frac=0.5),
+                                dict(k=6, seed=6, w=640, h=360, nf=1250, mono=False, stereo=True)])
+def test_search_by_projection_frame_frame_restatement_equals_reference_body(slices, kw):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1676-1887, TrackWithMotionModel's matcher):
+    the restatement against the reference's own body on shim Frame / MapPoint / Sophus classes - nmatches and, per current feature,
+    the map point it ends up holding; monocular and stereo (uRight gate, forward / backward level windows), with and without the
+    rotation histogram, with a roll that empties some histogram bins."""
+    c = make_projection_case(slices, **kw)
+    for ori in (True, False):
+        want = slices.ref_search_by_projection_ff(**dict(c, check_orientation=ori))
+        got = slices.search_by_projection_ff(**dict(c, check_orientation=ori))
+        assert got[0] == want[0] and np.array_equal(got[1], want[1]), (kw, ori, got[0], want[0])
+        assert want[0] > 50
