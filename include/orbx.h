@@ -231,6 +231,36 @@ int orbx_accept_top2(int rule, float nnratio, const int32_t* d1, const int32_t* 
 int orbx_accept_top2_device(int rule, float nnratio, const int32_t* d_d1, const int32_t* d_d2, const int64_t* d_idx2,
                             const int32_t* d_level1, const int32_t* d_level2, int n, uint8_t* d_accept, void* stream);
 
+/* ---- ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono), whole function ------------------
+ * (ORBmatcher.cc:1676-1887; Tracking::TrackWithMotionModel, Tracking.cc:2876, :2906, :2914), frames with Nleft == -1 (monocular,
+ * rectified stereo, RGB-D).  `pairs` independent (last, current) frame pairs in one call; arrays are [pair][cap_last] /
+ * [pair][cap_cur], host pointers.
+ *   kps_last   LastFrame.mvKeysUn (octave and angle are read)          last_flags  bit 0: mvpMapPoints[i] != NULL and !mvbOutlier[i],
+ *   world      MapPoint::GetWorldPos(), 3 floats per feature                        bit 1: that map point's Observations() > 0
+ *   mp_desc    MapPoint::GetDescriptor(), 32 bytes per feature         n_last / n_cur  features per pair
+ *   kps_cur    CurrentFrame.mvKeysUn, desc_cur = mDescriptors          cur_u_right mvuRight or NULL (monocular)
+ *   cur_taken  != 0: CurrentFrame.mvpMapPoints[i2] already holds a map point with observations (NULL = none; TrackWithMotionModel
+ *              clears the vector first, Tracking.cc:2866)
+ *   poses      14 floats per pair: Tcw then Tlw, each (qx, qy, qz, qw, tx, ty, tz) - Sophus::SE3f's own storage
+ * Results: match_cur[pair][i2] = index of the LAST-frame feature whose map point CurrentFrame.mvpMapPoints[i2] holds after the
+ * call (-1 = none); nmatches[pair] = the function's return value (it counts overwritten matches too, as the reference does).
+ * Float arithmetic: the operations of Sophus' SE3f * point (so3.hpp:358-368, se3.hpp:321-325) and Pinhole::project
+ * (CameraModels/Pinhole.cpp:43-49), each rounded once, in source order (the reference built with -ffp-contract=off). */
+typedef struct orbx_proj_params {
+    float fx, fy, cx, cy;                  /* CurrentFrame.mpCamera (pinhole) */
+    float min_x, max_x, min_y, max_y;      /* Frame::mnMinX .. mnMaxY */
+    float scale_factors[16];               /* CurrentFrame.mvScaleFactors */
+    int nlevels;
+    float mbf, mb;                         /* CurrentFrame.mbf, mb */
+    float th;
+    int mono;                              /* bMono */
+    int check_orientation;                 /* ORBmatcher::mbCheckOrientation */
+} orbx_proj_params;
+int orbx_search_by_projection(const orbx_keypoint* kps_last, const uint8_t* last_flags, const float* world, const uint8_t* mp_desc,
+                              const int32_t* n_last, const orbx_keypoint* kps_cur, const uint8_t* desc_cur, const float* cur_u_right,
+                              const uint8_t* cur_taken, const int32_t* n_cur, const float* poses, int pairs, int cap_last, int cap_cur,
+                              const orbx_proj_params* params, int32_t* match_cur, int32_t* nmatches, int device);
+
 /* ---- guided search: Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea + the best/second loop ---------------
  * The inner loop of ORBmatcher::SearchByProjection (frame to frame, ORBmatcher.cc:1676-1887), SearchForInitialization
  * (:648-763) and SearchByProjection(F, map points) (:45-138): for every query (u, v, radius, [min_level, max_level],

@@ -641,6 +641,19 @@ void launchAccept(int rule, float nnratio, const int32_t* d1, const int32_t* d2,
 
 int gridSortCapacity() { return 32768; }  // keys of one CTA's shared memory (128 KB)
 
+void launchGridSortBatch(const void* kps, const int* nPerFrame, int frames, int cap, float minX, float maxX, float minY, float maxY,
+                         uint32_t* sorted, int* cellStart, cudaStream_t s) {
+    if (frames <= 0) return;
+    const float invW = (float)kGridCols / (maxX - minX), invH = (float)kGridRows / (maxY - minY);  // Frame.cc:251-252
+    int nPow2 = 32;
+    while (nPow2 < cap) nPow2 <<= 1;
+    const size_t smem = (size_t)nPow2 * 4;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    gridSortKernel<<<frames, 1024, smem, s>>>(static_cast<const float*>(kps), 0, nPow2, minX, minY, invW, invH, sorted, cellStart,
+                                              nPerFrame, cap);
+    countLaunch();
+}
+
 void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX, float maxX, float minY, float maxY,
                       const uint8_t* skipT, const float* uRightT, const void* queries, const uint8_t* descQ, int nq,
                       uint32_t* sortedScratch, int* cellStart, int32_t* idx1, int32_t* d1, int32_t* idx2, int32_t* d2,

@@ -1560,6 +1560,81 @@ int orbx_search_for_initialization(const orbx_keypoint* kps1, const uint8_t* des
     return ORBX_OK;
 }
 
+int orbx_search_by_projection(const orbx_keypoint* kps_last, const uint8_t* last_flags, const float* world, const uint8_t* mp_desc,
+                              const int32_t* n_last, const orbx_keypoint* kps_cur, const uint8_t* desc_cur, const float* cur_u_right,
+                              const uint8_t* cur_taken, const int32_t* n_cur, const float* poses, int pairs, int cap_last, int cap_cur,
+                              const orbx_proj_params* params, int32_t* match_cur, int32_t* nmatches, int device) {
+    if (pairs < 0 || cap_last < 0 || cap_cur < 0 || !params || !n_last || !n_cur || !poses || !nmatches ||
+        (cap_last > 0 && (!kps_last || !last_flags || !world || !mp_desc)) || (cap_cur > 0 && (!kps_cur || !desc_cur || !match_cur)))
+        return fail(ORBX_ERR_ARG, "bad argument");
+    if (!(params->max_x > params->min_x) || !(params->max_y > params->min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
+    if (params->nlevels < 1 || params->nlevels > kMaxLevels) return fail(ORBX_ERR_ARG, "nlevels must be in [1,16]");
+    if (cap_cur > gridSortCapacity()) return fail(ORBX_ERR_ARG, "more than 32768 keypoints in the current frame");
+    for (int p = 0; p < pairs; ++p) {
+        if (n_last[p] < 0 || n_last[p] > cap_last || n_cur[p] < 0 || n_cur[p] > cap_cur) return fail(ORBX_ERR_ARG, "count exceeds capacity");
+        nmatches[p] = 0;
+        // octaves index mvScaleFactors (:1723): reject what the reference would read out of bounds
+        for (int i = 0; i < n_last[p]; ++i) {
+            const int oct = kps_last[(size_t)p * cap_last + i].octave;
+            if (oct < 0 || oct >= params->nlevels) return fail(ORBX_ERR_ARG, "last-frame keypoint octave outside [0, nlevels)");
+        }
+    }
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    if (pairs == 0 || cap_last == 0 || cap_cur == 0) {
+        for (size_t i = 0; i < (size_t)pairs * cap_cur; ++i) match_cur[i] = -1;
+        return ORBX_OK;
+    }
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t P = (size_t)pairs, L = P * cap_last, Cn = P * cap_cur;
+    // q (last side): [mpDesc | kps | world | flags | nLast | nCur | poses | nMatches]
+    const size_t oKl = al(L * 32), oW = oKl + al(L * 28), oF = oW + al(L * 12), oNl = oF + al(L), oNc = oNl + al(P * 4), oPo = oNc + al(P * 4),
+                 oNm = oPo + al(P * 56), qBytes = oNm + al(P * 4);
+    // db (current side): [desc | kps | uRight | taken | sorted | cellStart | match]
+    const size_t oKc = al(Cn * 32), oUr = oKc + al(Cn * 28), oTk = oUr + al(Cn * 4), oSo = oTk + al(Cn), oCs = oSo + al(Cn * 4),
+                 oMa = oCs + al(P * (size_t)(64 * 48 + 1) * 4), dbBytes = oMa + al(Cn * 4);
+    ORBX_CUDA(S->q.reserve(qBytes));
+    ORBX_CUDA(S->db.reserve(dbBytes));
+    ORBX_CUDA(S->k1.reserve(L * projScratchWordsPerLast() * 4 + 256));
+    uint8_t* Q = (uint8_t*)S->q.p;
+    uint8_t* D = (uint8_t*)S->db.p;
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaMemcpyAsync(Q, mp_desc, L * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oKl, kps_last, L * 28, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oW, world, L * 12, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oF, last_flags, L, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oNl, n_last, P * 4, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oNc, n_cur, P * 4, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oPo, poses, P * 56, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(D, desc_cur, Cn * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(D + oKc, kps_cur, Cn * 28, cudaMemcpyHostToDevice, s));
+    if (cur_u_right) ORBX_CUDA(cudaMemcpyAsync(D + oUr, cur_u_right, Cn * 4, cudaMemcpyHostToDevice, s));
+    if (cur_taken) ORBX_CUDA(cudaMemcpyAsync(D + oTk, cur_taken, Cn, cudaMemcpyHostToDevice, s));
+    launchGridSortBatch(D + oKc, (const int*)(Q + oNc), pairs, cap_cur, params->min_x, params->max_x, params->min_y, params->max_y,
+                        (uint32_t*)(D + oSo), (int*)(D + oCs), s);
+    ProjCam C{};
+    C.fx = params->fx; C.fy = params->fy; C.cx = params->cx; C.cy = params->cy;
+    C.minX = params->min_x; C.maxX = params->max_x; C.minY = params->min_y; C.maxY = params->max_y;
+    C.mbf = params->mbf; C.mb = params->mb; C.th = params->th; C.mono = params->mono != 0; C.checkOri = params->check_orientation != 0;
+    C.nlevels = params->nlevels;
+    for (int l = 0; l < params->nlevels; ++l) C.sf[l] = params->scale_factors[l];
+    launchSearchByProjection(Q + oKl, Q + oF, (const float*)(Q + oW), Q, (const int*)(Q + oNl), D + oKc, D,
+                             cur_u_right ? (const float*)(D + oUr) : nullptr, cur_taken ? D + oTk : nullptr, (const int*)(Q + oNc),
+                             (const float*)(Q + oPo), pairs, cap_last, cap_cur, C, (uint32_t*)(D + oSo), (int*)(D + oCs), (uint32_t*)S->k1.p,
+                             (int*)(D + oMa), (int*)(Q + oNm), s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(match_cur, D + oMa, Cn * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(nmatches, Q + oNm, P * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_search_for_initialization_batch(orbx_handle h, int use_undistorted, float min_x, float max_x, float min_y, float max_y,
                                          int window_size, float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches,
                                          float* prev_matched) {

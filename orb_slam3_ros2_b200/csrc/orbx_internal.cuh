@@ -169,6 +169,21 @@ void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void
                       int prevFromKps, uint32_t* sorted, int* cellStart, float* prev, int* m12, int* scratch3, int* nMatches,
                       cudaStream_t s, uint32_t* candList = nullptr, int* candCount = nullptr);
 constexpr int kSearchInitListCap = 64;  // = kInitListCap of k_guided.cu
+// grids of `frames` keypoint sets [frame][cap] (Frame::AssignFeaturesToGrid as one sort per frame): sorted frames x cap words,
+// cellStart frames x 3073 ints
+void launchGridSortBatch(const void* kps, const int* nPerFrame, int frames, int cap, float minX, float maxX, float minY, float maxY,
+                         uint32_t* sorted, int* cellStart, cudaStream_t s);
+// ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (k_project.cu)
+struct ProjCam {
+    float fx, fy, cx, cy, minX, maxX, minY, maxY, mbf, mb, th;
+    int mono, checkOri, nlevels;
+    float sf[kMaxLevels];
+};
+size_t projScratchWordsPerLast();
+void launchSearchByProjection(const void* kpsLast, const uint8_t* lastFlags, const float* world, const uint8_t* mpDesc, const int* nLast,
+                              const void* kpsCur, const uint8_t* descCur, const float* uRightCur, const uint8_t* takenCur, const int* nCur,
+                              const float* poses, int pairs, int capLast, int capCur, const ProjCam& C, uint32_t* sorted, int* cellStart,
+                              uint32_t* scratch, int* matchCur, int* nMatches, cudaStream_t s);
 // Frame::UndistortKeyPoints: the pinhole model in doubles, as cv::undistortPoints converts it (k = k1 k2 p1 p2 k3 k4 k5 k6 s1..s4)
 struct UndistortCam {
     double ifx, ify, cx, cy;

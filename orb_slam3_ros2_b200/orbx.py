@@ -98,6 +98,8 @@ SYMBOLS = {
     "orbx_search_by_bow_kf": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p,
                                         _i32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_capacity": (C.c_int, [_vp, C.c_int, C.c_int, _i32p]),
+    "orbx_search_by_projection": (C.c_int, [_vp, _u8p, _vp, _u8p, _i32p, _vp, _u8p, _vp, _vp, _i32p, _vp, C.c_int, C.c_int, C.c_int, _vp,
+                                            _i32p, _i32p, C.c_int]),
     "orbx_debug_check_guards": (C.c_int, [_vp]),
     "orbx_extract_frame": (C.c_int, [_vp, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
     "orbx_bench_popc": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
@@ -538,6 +540,50 @@ def search_for_initialization_batch(extractor, bounds, window_size=100, nnratio=
                                                       int(window_size), float(nnratio), int(bool(check_orientation)),
                                                       _ptr(m12, _i32p), _ptr(n, _i32p), _ptr(prev, _f32p)))
     return n[:F - 1], m12[:F - 1], prev[:F - 1]
+
+
+class ProjParams(C.Structure):
+    """orbx_proj_params (include/orbx.h)."""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float),
+                ("min_y", C.c_float), ("max_y", C.c_float), ("scale_factors", C.c_float * 16), ("nlevels", C.c_int), ("mbf", C.c_float),
+                ("mb", C.c_float), ("th", C.c_float), ("mono", C.c_int), ("check_orientation", C.c_int)]
+
+
+def search_by_projection(cases, cam, bounds, scale_factors, th, mono, mbf=0.0, mb=0.0, check_orientation=True, device=-1):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1676-1887) on the device for a list of
+    independent frame pairs.  Each case is a dict with kps_last, last_flags, world, mp_desc, kps_cur, desc_cur, pose_cw, pose_lw and
+    optionally cur_u_right, cur_taken (None on every case or on none).  -> [(nmatches, match_cur[n_cur])] per case."""
+    P = len(cases)
+    cap_l = max([len(c["kps_last"]) for c in cases] + [1])
+    cap_c = max([len(c["kps_cur"]) for c in cases] + [1])
+    kl = np.zeros((P, cap_l), dtype=KP_DTYPE); fl = np.zeros((P, cap_l), np.uint8); wd = np.zeros((P, cap_l, 3), np.float32)
+    md = np.zeros((P, cap_l, 32), np.uint8); kc = np.zeros((P, cap_c), dtype=KP_DTYPE); dc = np.zeros((P, cap_c, 32), np.uint8)
+    has_ur = cases[0].get("cur_u_right") is not None
+    has_tk = cases[0].get("cur_taken") is not None
+    ur = np.full((P, cap_c), -1, np.float32); tk = np.zeros((P, cap_c), np.uint8)
+    nl = np.zeros(P, np.int32); nc = np.zeros(P, np.int32); poses = np.zeros((P, 14), np.float32)
+    for p, c in enumerate(cases):
+        a, b = len(c["kps_last"]), len(c["kps_cur"])
+        nl[p], nc[p] = a, b
+        kl[p, :a] = c["kps_last"]; fl[p, :a] = c["last_flags"]; wd[p, :a] = np.asarray(c["world"], np.float32).reshape(-1, 3)
+        md[p, :a] = c["mp_desc"]; kc[p, :b] = c["kps_cur"]; dc[p, :b] = c["desc_cur"]
+        if has_ur: ur[p, :b] = c["cur_u_right"]
+        if has_tk: tk[p, :b] = c["cur_taken"]
+        poses[p, :7] = c["pose_cw"]; poses[p, 7:] = c["pose_lw"]
+    prm = ProjParams()
+    prm.fx, prm.fy, prm.cx, prm.cy = [float(v) for v in cam]
+    prm.min_x, prm.max_x, prm.min_y, prm.max_y = [float(v) for v in bounds]
+    sf = np.asarray(scale_factors, np.float32)
+    for l in range(len(sf)):
+        prm.scale_factors[l] = float(sf[l])
+    prm.nlevels = len(sf); prm.mbf = float(mbf); prm.mb = float(mb); prm.th = float(th)
+    prm.mono = 1 if mono else 0; prm.check_orientation = 1 if check_orientation else 0
+    match = np.full((P, cap_c), -1, np.int32); nm = np.zeros(P, np.int32)
+    _check(lib().orbx_search_by_projection(kl.ctypes.data_as(_vp), _ptr(fl), wd.ctypes.data_as(_vp), _ptr(md), _ptr(nl, _i32p),
+                                           kc.ctypes.data_as(_vp), _ptr(dc), ur.ctypes.data_as(_vp) if has_ur else None,
+                                           tk.ctypes.data_as(_vp) if has_tk else None, _ptr(nc, _i32p), poses.ctypes.data_as(_vp), P, cap_l,
+                                           cap_c, C.byref(prm), _ptr(match, _i32p), _ptr(nm, _i32p), device))
+    return [(int(nm[p]), match[p, :nc[p]].copy()) for p in range(P)]
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):

@@ -242,3 +242,36 @@ def test_search_for_initialization_batch_equals_per_pair(orbx, oracle):
     with pytest.raises(orbx.OrbxError):
         orbx.search_for_initialization_batch(e, bounds, 100, 0.9, True, use_undistorted=True)
     e.close()
+
+
+@pytest.mark.parametrize("kw", [dict(k=0, seed=0), dict(k=3, seed=1, nf=2000, w=1241, h=376), dict(k=1, seed=2, mono=False, stereo=True, dz=0.3),
+                                dict(k=2, seed=3, mono=False, stereo=True, dz=-0.3), dict(k=4, seed=4, rot=0.35), dict(k=5, seed=5, taken_frac=0.5),
+                                dict(k=6, seed=6, w=640, h=360, nf=1250, mono=False, stereo=True)])
+def test_search_by_projection_frame_frame_matches_oracle(orbx, oracle, kw):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), whole function on the device (k_project.cu), against the
+    restatement that tests/test_oracle_refslices.py pins to the reference's own body: nmatches and every current feature's map point."""
+    from test_oracle_matcher_rows import make_projection_case
+    c = make_projection_case(oracle, **kw)
+    for ori in (True, False):
+        want = oracle.search_by_projection_ff(**dict(c, check_orientation=ori))
+        got = orbx.search_by_projection([c], c["cam"], c["bounds"], c["scale_factors"], c["th"], c["mono"], c["mbf"], c["mb"], ori)[0]
+        assert got[0] == want[0], (kw, ori, got[0], want[0])
+        assert np.array_equal(got[1], want[1]), (kw, ori, np.flatnonzero(got[1] != want[1])[:10])
+
+
+def test_search_by_projection_batch_and_crowded_windows(orbx, oracle):
+    """Several pairs in one call (one warp per pair in the order-dependent walk) and windows with more candidates than the per-feature
+    list holds (th = 60: the walk re-enumerates the window in place)."""
+    from test_oracle_matcher_rows import make_projection_case
+    cases = [make_projection_case(oracle, k=k, seed=10 + k, nf=nf) for k, nf in ((0, 1000), (1, 500), (2, 1500), (3, 1000))]
+    c0 = cases[0]
+    for th in (15, 60):
+        got = orbx.search_by_projection(cases, c0["cam"], c0["bounds"], c0["scale_factors"], th, True)
+        for c, g in zip(cases, got):
+            want = oracle.search_by_projection_ff(**dict(c, th=th))
+            assert g[0] == want[0] and np.array_equal(g[1], want[1]), th
+    # argument errors: an octave outside the scale table, counts above the capacity
+    bad = dict(c0, kps_last=c0["kps_last"].copy())
+    bad["kps_last"]["octave"][0] = 9
+    with pytest.raises(orbx.OrbxError):
+        orbx.search_by_projection([bad], c0["cam"], c0["bounds"], c0["scale_factors"], 15, True)
