@@ -636,9 +636,9 @@ def run_match_cfg5(ctx, args, rank, world, local_rank):
         dist.broadcast_object_list(uid, src=0)
         matcher = orbx.ShardedMatcher(rank, world, uid[0], local_rank)
 
-    def run():
+    def run(sync=True):
         if matcher:
-            matcher.match(q.data_ptr(), nq, db.data_ptr(), hi - lo, lo, *[o.data_ptr() for o in out])
+            (matcher.match if sync else matcher.match_async)(q.data_ptr(), nq, db.data_ptr(), hi - lo, lo, *[o.data_ptr() for o in out])
         else:
             orbx._check(orbx.lib().orbx_match_top2_device(q.data_ptr(), nq, db.data_ptr(), nd, 0,
                                                           *[o.data_ptr() for o in out], None))
@@ -646,6 +646,32 @@ def run_match_cfg5(ctx, args, rank, world, local_rank):
 
     run()
     assert np.array_equal(out[0].cpu().numpy(), rows) and bool((out[1] == 20).all()), "cfg5 known answers violated"
+    exchange_check = None
+    if matcher:
+        # the exchange itself (the driver's 1-GPU test box cannot run the 2-rank pytest): a 200 k-row prefix of the database sharded over
+        # the ranks, with an exact duplicate of a query planted on both sides of every shard boundary, against the same prefix matched on
+        # this rank alone - all four outputs (idx1, d1, idx2, d2) must be equal
+        nd_s, nq_s = 200_000, 256
+        db_s = synth.descriptor_db(nd_s).copy()
+        q_s = q_np[:nq_s]
+        for r in range(world - 1):
+            b = orbx.shard_range(nd_s, r, world)[1]
+            db_s[b - 1] = q_s[r]
+            db_s[b] = q_s[r]
+        lo_s, hi_s = orbx.shard_range(nd_s, rank, world)
+        d_db_s = torch.from_numpy(db_s).to(dev)
+        d_q_s = torch.from_numpy(np.ascontiguousarray(q_s)).to(dev)
+        ref = [torch.empty(nq_s, dtype=o.dtype, device=dev) for o in out]
+        got = [torch.empty(nq_s, dtype=o.dtype, device=dev) for o in out]
+        orbx._check(orbx.lib().orbx_match_top2_device(d_q_s.data_ptr(), nq_s, d_db_s.data_ptr(), nd_s, 0, *[o.data_ptr() for o in ref], None))
+        torch.cuda.synchronize()
+        matcher.match(d_q_s.data_ptr(), nq_s, d_db_s[lo_s:hi_s].data_ptr(), hi_s - lo_s, lo_s, *[o.data_ptr() for o in got])
+        same = all(bool(torch.equal(a, b)) for a, b in zip(ref, got))
+        for r in range(world - 1):
+            b = orbx.shard_range(nd_s, r, world)[1]
+            same = same and int(got[0][r]) == b - 1 and int(got[2][r]) == b and int(got[1][r]) == 0 and int(got[3][r]) == 0
+        assert same, "sharded top-2 differs from the single-GPU top-2 on the 200k-row prefix (idx1 / d1 / idx2 / d2)"
+        exchange_check = f"idx1, d1, idx2, d2 of {nq_s} queries x {nd_s} rows over {world} shards == single-GPU result; duplicates planted across every shard boundary resolve to (lower row, higher row, 0, 0)"
     ctx["barrier"]()
     reps = 5
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -653,7 +679,9 @@ def run_match_cfg5(ctx, args, rank, world, local_rank):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(reps):
-        run()
+        run(sync=False)  # sharded: enqueue-only calls back to back on the communicator's stream, one wait at the end
+    if matcher:
+        matcher.sync()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / reps
     if world > 1:
@@ -667,6 +695,7 @@ def run_match_cfg5(ctx, args, rank, world, local_rank):
         matcher.close()
     return {"workload": f"cfg5: {nq} queries x {nd} rows, {world} shard(s)" + (", ncclAllGather of per-shard top-2" if world > 1 else ""),
             "gpairs_per_s": gpairs, "ms": dt * 1e3, "launches_per_call": (orbx.launch_count() - launches0 - 4) / reps,
+            "exchange_check": exchange_check,
             "roofline": {"bound": "popc", "achieved": gpairs, "peak": peak, "unit": "Gpairs/s", "frac": gpairs / peak,
                          "peak_source": f"measured POPC rate {gpopc:.0f} Gpopc/s per GPU / 8 POPC per pair"}}
 

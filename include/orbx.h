@@ -407,6 +407,11 @@ int orbx_comm_init(int rank, int nranks, const uint8_t id[128], int device, orbx
 void orbx_comm_destroy(orbx_comm c);
 int orbx_match_top2_sharded(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local,
                             int64_t db_index_base, int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2);
+/* The same, only ENQUEUED on the communicator's stream (no host synchronisation): consecutive calls on one communicator run back to
+ * back on the device; orbx_comm_sync waits for all of them.  nq must not grow between un-synchronised calls. */
+int orbx_match_top2_sharded_async(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local,
+                                  int64_t db_index_base, int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2);
+int orbx_comm_sync(orbx_comm c);
 /* The merge alone, on already gathered candidates laid out [rank][query] (used by the CPU-side tests of
  * the exchange step and by the single-process emulation of G shards on one GPU). */
 int orbx_merge_top2_device(const uint64_t* d_keys1, const uint64_t* d_keys2, int nranks, int nq, int64_t* d_idx1,

@@ -1975,12 +1975,39 @@ void orbx_comm_destroy(orbx_comm c) {
     delete c;
 }
 
-// local top-2 on this rank's shard -> pack (k1[nq] | k2[nq]) -> ncclAllGather over NVLink -> merge on every rank.
+// local top-2 on this rank's shard -> pack (k1[nq] | k2[nq]) -> ncclAllGather over NVLink -> merge on every rank, all enqueued on
+// the communicator's stream: no host synchronisation (orbx_comm_sync waits).  Calls on one communicator are ordered by that stream,
+// so the scratch buffers can be reused; nq must not grow between un-synchronised calls (a reallocation would free memory in use).
+static int shardedEnqueue(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local, int64_t db_index_base,
+                          int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2);
+
+int orbx_match_top2_sharded_async(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local,
+                                  int64_t db_index_base, int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2) {
+    if (!c || nq < 1 || !d_q || nd_local < 0) return fail(ORBX_ERR_ARG, "bad argument");
+    DeviceGuard guard(c->device);
+    return shardedEnqueue(c, d_q, nq, d_db_local, nd_local, db_index_base, d_idx1, d_d1, d_idx2, d_d2);
+}
+
+int orbx_comm_sync(orbx_comm c) {
+    if (!c) return fail(ORBX_ERR_ARG, "null communicator");
+    DeviceGuard guard(c->device);
+    ORBX_CUDA(cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
+}
+
 // Synchronous with respect to the host on return.
 int orbx_match_top2_sharded(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local,
                             int64_t db_index_base, int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2) {
     if (!c || nq < 1 || !d_q || nd_local < 0) return fail(ORBX_ERR_ARG, "bad argument");
     DeviceGuard guard(c->device);
+    const int rc = shardedEnqueue(c, d_q, nq, d_db_local, nd_local, db_index_base, d_idx1, d_d1, d_idx2, d_d2);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA(cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
+}
+
+static int shardedEnqueue(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t* d_db_local, int64_t nd_local, int64_t db_index_base,
+                          int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2) {
     cudaStream_t s = c->stream;
     int nsets = 1;
     int rc = localTop2Keys(d_q, nq, d_db_local, nd_local, db_index_base, c->k1, c->k2, &nsets, s);
@@ -1996,7 +2023,6 @@ int orbx_match_top2_sharded(orbx_comm c, const uint8_t* d_q, int nq, const uint8
     orbx::launchUnpackTop2Strided((const uint64_t*)c->gathered.p, (const uint64_t*)c->gathered.p + nq, c->nranks, nq,
                                   (size_t)nq * 2, d_idx1, d_d1, d_idx2, d_d2, s);
     ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaStreamSynchronize(s));
     return ORBX_OK;
 }
 

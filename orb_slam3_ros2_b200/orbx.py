@@ -112,6 +112,8 @@ SYMBOLS = {
     "orbx_comm_init": (C.c_int, [C.c_int, C.c_int, _u8p, C.c_int, C.POINTER(_vp)]),
     "orbx_comm_destroy": (None, [_vp]),
     "orbx_match_top2_sharded": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp]),
+    "orbx_match_top2_sharded_async": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp]),
+    "orbx_comm_sync": (C.c_int, [_vp]),
     "orbx_merge_top2_device": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
 }
 
@@ -718,6 +720,13 @@ class ShardedMatcher:
     def match(self, d_q, nq, d_db_local, nd_local, index_base, d_idx1, d_d1, d_idx2, d_d2):
         _check(lib().orbx_match_top2_sharded(self._c, d_q, nq, d_db_local, nd_local, index_base, d_idx1, d_d1, d_idx2,
                                              d_d2))
+
+    def match_async(self, d_q, nq, d_db_local, nd_local, index_base, d_idx1, d_d1, d_idx2, d_d2):
+        """Enqueue only (orbx_match_top2_sharded_async); sync() waits for every call queued so far."""
+        _check(lib().orbx_match_top2_sharded_async(self._c, d_q, nq, d_db_local, nd_local, index_base, d_idx1, d_d1, d_idx2, d_d2))
+
+    def sync(self):
+        _check(lib().orbx_comm_sync(self._c))
 
     def close(self):
         if getattr(self, "_c", None) is not None and self._c.value:
