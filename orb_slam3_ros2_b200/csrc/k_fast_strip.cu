@@ -473,33 +473,39 @@ int buildStripMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, vo
 }
 
 template <int NT>
-static void launchStripT(const FramePlan& P, const Buffers& B, int F, int rowsMax, int pitchMax, cudaStream_t s) {
+static void launchStripT(const FramePlan& P, const Buffers& B, int F, int rowsMax, int pitchMax, cudaStream_t s, int tile0, int nTiles) {
     const StripLayout lay = stripLayout(rowsMax, pitchMax, stripListCap());
     auto kern = fastStripKernel<NT>;
     if (lay.total > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, lay.total);
-    kern<<<dim3(P.stripTiles, F), NT, lay.total, s>>>(*reinterpret_cast<const LevelMaps*>(B.stripMaps),
-                                                     reinterpret_cast<const StripDesc*>(B.stripTab), B.cand, B.cellCnt, B.fbList, B.fbCount,
+    kern<<<dim3(nTiles, F), NT, lay.total, s>>>(*reinterpret_cast<const LevelMaps*>(B.stripMaps),
+                                                     reinterpret_cast<const StripDesc*>(B.stripTab) + tile0, B.cand, B.cellCnt, B.fbList, B.fbCount,
                                                      B.fbCap, (int)P.candWords, P.nCellsTotal, std::max(P.iniTh, 1), std::max(P.minTh, 1),
                                                      rowsMax, pitchMax, B.frame0, stripListCap());
     countLaunch();
 }
 
-void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
+void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int part, int splitLevel) {
     int rowsMax = 7, pitchMax = 16;
+    // the strip table lists the levels from the smallest down to level 0: the strips of the levels > splitLevel come first
+    int upper = 0;
+    for (int l = P.nlevels - 1; l > splitLevel; --l) upper += P.lv[l].stripSegs * P.lv[l].nRows;
     for (int l = 0; l < P.nlevels; ++l) {
         const LevelPlan& L = P.lv[l];
         if (L.stripSegs <= 0) continue;
         rowsMax = std::max(rowsMax, L.hCell + 6);
         pitchMax = std::max(pitchMax, L.stripPitch);
     }
-    // the list counts [2] and the per-cell kernel's two work counters
-    cudaMemsetAsync(B.fbCount, 0, 2 * sizeof(int), s);
-    cudaMemsetAsync(B.workCtr, 0, 2 * sizeof(int), s);
-    if (P.stripTiles > 0) {
-        if (stripThreads() == 256) launchStripT<256>(P, B, F, rowsMax, pitchMax, s);
-        else launchStripT<128>(P, B, F, rowsMax, pitchMax, s);
+    if (part == 0 || part == 4) {  // the list counts [2] and the per-cell kernel's two work counters
+        cudaMemsetAsync(B.fbCount, 0, 2 * sizeof(int), s);
+        cudaMemsetAsync(B.workCtr, 0, 2 * sizeof(int), s);
     }
-    launchFastFallback(P, B, F, B.fbList, B.fbCount, B.fbCap, s);
+    const int tile0 = part == 1 ? upper : 0;
+    const int nTiles = part == 0 ? P.stripTiles : (part == 1 ? P.stripTiles - upper : (part == 2 ? upper : 0));  // parts 3, 4: none
+    if (nTiles > 0) {
+        if (stripThreads() == 256) launchStripT<256>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else launchStripT<128>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+    }
+    if (part == 0 || part == 3) launchFastFallback(P, B, F, B.fbList, B.fbCount, B.fbCap, s);
 }
 
 }  // namespace orbx

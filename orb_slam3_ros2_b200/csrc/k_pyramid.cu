@@ -13,6 +13,7 @@
 // the horizontal pass turns each of them into one row of 16-bit (a0*p0 + a1*p1) >> 4 values for the tile's 128
 // columns (a thread keeps the coefficients of its 4 columns in registers), and the vertical pass blends two such
 // rows per output row.  ~18 instructions per output pixel instead of ~80 for the direct per-pixel form.
+#include <algorithm>
 #include <cstring>
 
 #include "orbx_internal.cuh"
@@ -379,8 +380,8 @@ static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cu
 }
 
 void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
-                   cudaStream_t s, int levels) {
-    if (levels != 1) {
+                   cudaStream_t s, int levels, int firstLevel, int lastLevel) {
+    if (levels != 1 && firstLevel <= 0) {
         const LevelPlan& L = P.lv[0];
         const int pw = L.w + 2 * kEdge, ph = L.h + 2 * kEdge;
         const bool aligned = ((reinterpret_cast<uintptr_t>(dImgs) | (uintptr_t)stride | (uintptr_t)frameStride) & 15) == 0;
@@ -398,7 +399,7 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
         countLaunch();
     }
     if (levels == 0) return;
-    for (int l = 1; l < P.nlevels; ++l) {
+    for (int l = std::max(1, firstLevel); l < P.nlevels && l <= lastLevel; ++l) {
         // bytes of a source row a 128-column strip can need: 128 * scale + 2, + 15 for the 16-B alignment, rounded to chunks
         const double need = 128.0 * P.lv[l - 1].w / P.lv[l].w + 2 + 15 + 16;
         // windowed horizontal pass: 4 neighbouring columns span <= 8 source bytes iff floor(3 * step) + 2 <= 7

@@ -104,15 +104,19 @@ struct Buffers {
 
 // kernel launchers (each in its own .cu); all asynchronous on `s`
 // levels: -1 = whole pyramid; 0 = only level 0 (copy + border); 1 = only levels >= 1 (level 0 must be complete on the stream)
+// firstLevel / lastLevel: only the levels in [firstLevel, lastLevel] (the chain below firstLevel must be complete on the stream)
 void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, int stride, size_t frameStride, int F,
-                   cudaStream_t s, int levels = -1);
+                   cudaStream_t s, int levels = -1, int firstLevel = 0, int lastLevel = kMaxLevels);
 bool fastLevel0Early(const FramePlan& P);
 void launchFast(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int which = -1);
 // strip-wise FAST (k_fast_strip.cu): the whole stage = strips at iniThFAST + the per-cell kernel on what they leave behind
 void planFastStrips(FramePlan& P);
 void buildFastStripTable(const FramePlan& P, std::vector<uint32_t>& tab);
 int buildStripMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
-void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+// part: 0 = everything on s (clear the lists, strips of all levels, fallback); the split form runs the strips of the levels
+// <= splitLevel beside the rest of the resize chain: 1 = clear the lists + strips of the levels <= splitLevel, 2 = strips of the
+// levels > splitLevel, 3 = the fallback kernels (after 1 and 2 have completed)
+void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int part = 0, int splitLevel = 3);
 void launchFastFallback(const FramePlan& P, const Buffers& B, int F, const unsigned long long* fbList, const int* fbCount, int cap,
                         cudaStream_t s);
 bool fastWideLevel(const LevelPlan& L);
