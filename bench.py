@@ -482,6 +482,55 @@ def run_configs(ctx, args, rank, world):
     return out
 
 
+def run_search_by_projection(ctx, args):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1676-1887), the matcher TrackWithMotionModel runs
+    on every frame: 64 consecutive frame pairs of the resident batch in ONE call through the C ABI with host arrays (uploads and the
+    download of the matches inside the timed call); map points = the last frame's keypoints back-projected with pseudo-random depths,
+    current pose = the stream's image shift.  CPU leg: the oracle restatement (pinned to the reference's own body) on the same pairs."""
+    orbx, ex = ctx["orbx"], ctx["ex"]
+    from oracle import pyoracle
+    ex.extract_batch_device(ctx["imgs"][0].data_ptr(), ctx["F"], W, H, LAP)
+    ex.sync()
+    P = min(64, ctx["F"] - 1)
+    fr = [ex.download(f) for f in range(P + 1)]
+    sf = ex.GetScaleFactors()
+    fx, fy, cx, cy = 458.654, 457.296, 367.215, 248.375  # config/Monocular/EuRoC.yaml
+    rng = np.random.default_rng(0)
+    cases = []
+    for p in range(P):
+        kl, dl = fr[p][1], fr[p][2]
+        kc, dc = fr[p + 1][1], fr[p + 1][2]
+        n = len(kl)
+        z = rng.uniform(4.0, 9.0, n).astype(np.float32)
+        world = np.stack([(kl["x"] - cx) / fx * z, (kl["y"] - cy) / fy * z, z], axis=1).astype(np.float32)
+        flags = (rng.random(n) < 0.85).astype(np.uint8) | ((rng.random(n) < 0.7).astype(np.uint8) << 1)
+        cases.append(dict(kps_last=kl, last_flags=flags, world=world, mp_desc=dl, kps_cur=kc, desc_cur=dc,
+                          pose_cw=np.array([0, 0, 0, 1, -3.0 * 6.0 / fx, -1.0 * 6.0 / fy, 0], np.float32),
+                          pose_lw=np.array([0, 0, 0, 1, 0, 0, 0], np.float32)))
+    bounds = (0.0, float(W), 0.0, float(H))
+    call = lambda: orbx.search_by_projection(cases, (fx, fy, cx, cy), bounds, sf, 15, True)
+    got = call()
+    l0 = orbx.launch_count()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        call()
+    dt = (time.perf_counter() - t0) / reps
+    launches = (orbx.launch_count() - l0) / reps
+    t0 = time.perf_counter()
+    ncpu = min(16, P)
+    want = [pyoracle.search_by_projection_ff(**dict(cases[p], cam=(fx, fy, cx, cy), bounds=bounds, scale_factors=sf, th=15, mono=True))
+            for p in range(ncpu)]
+    cdt = (time.perf_counter() - t0) / ncpu
+    same = all(got[p][0] == want[p][0] and np.array_equal(got[p][1], want[p][1]) for p in range(ncpu))
+    return {"workload": f"{P} consecutive 752x480 frame pairs, ~{int(np.mean([len(c['kps_last']) for c in cases]))} features each, th 15, monocular",
+            "pairs_per_s": P / dt, "ms_per_call": dt * 1e3, "us_per_pair": dt / P * 1e6, "launches_per_call": launches,
+            "matches_per_pair": float(np.mean([g[0] for g in got])),
+            "timing": "host wall clock around orbx_search_by_projection incl. the Python packing of the host arrays, uploads and the download",
+            "cpu_baseline": {"us_per_pair": cdt * 1e6, "cores": 1, "kind": "port", "sample": f"{ncpu} of the pairs, oracle/match_oracle.cpp",
+                             "equal_to_gpu": bool(same)}}
+
+
 def run_single_frame(ctx, args):
     """Drop-in latency: ORB_SLAM3::ORBextractor::operator() of the compat class (orb_slam3_ros2_b200/compat, what Frame::ExtractORB
     calls, Frame.cc:418-425) on one host thread, one 752x480 frame at a time, with and without the mvImagePyramid download, and the
@@ -838,6 +887,7 @@ def main():
             out["configs"] = run_configs(ctx, args, rank, world)
         if rank == 0 and world == 1:
             out["single_frame"] = run_single_frame(ctx, args)
+            out["search_by_projection"] = run_search_by_projection(ctx, args)
         if rank == 0 and world == 1:
             from orb_slam3_ros2_b200 import synth
             cores = os.cpu_count() or 1

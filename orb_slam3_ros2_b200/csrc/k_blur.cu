@@ -27,6 +27,7 @@
 //     (box 144 x 38 x 1; the tile's first byte is padded column x0 + 16, always 16-byte aligned), completion on an
 //     mbarrier; rows / columns past the plane are zero-filled by the copy engine and only feed outputs that are not stored;
 //   * the final ">> 16" and the byte packing are one PRMT pair (the result is byte 2 of the accumulator).
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -213,6 +214,99 @@ __global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ Fra
     }
 }
 
+// v5: persistent CTAs, the NEXT tile's TMA box is in flight while the current tile is computed (two input buffers, two
+// mbarriers).  The one-tile-per-CTA kernel spends 43 % of its stall samples waiting for its only box.
+__global__ void __launch_bounds__(256, 8) blurPersistKernel(const __grid_constant__ FramePlan P, const __grid_constant__ LevelMaps M,
+                                                            const uint32_t* __restrict__ tileTab, uint8_t* __restrict__ blur, int frame0,
+                                                            int tilesPerFrame, int total) {
+    __shared__ __align__(128) uint8_t sIn[2][(kInRows * kInPitch + 127) & ~127];  // TMA destinations are 128-byte aligned
+    __shared__ __align__(16) uint32_t sHp[kPairs * kTileW];  // (H[2m][x] | H[2m+1][x] << 16)
+    __shared__ __align__(8) uint64_t bar[2];
+    const int tid = threadIdx.x;
+    const int stride = gridDim.x;
+    auto issue = [&](int t, int b) {  // thread 0 only
+        const int f = t / tilesPerFrame;
+        const uint32_t te = __ldg(tileTab + (t - f * tilesPerFrame));
+        const int l = (int)(te >> 24);
+        const int x0 = (int)(te & 0xfffu) * kTileW, y0 = (int)((te >> 12) & 0xfffu) * kTileH;
+        mbarExpectTx(&bar[b], kInRows * kInPitch);
+        tmaLoadTile(sIn[b], &M.m[l], x0 + 16, y0 + 16, frame0 + f, &bar[b]);
+    };
+    int t = blockIdx.x;
+    if (t >= total) return;
+    if (tid == 0) {
+        mbarInit(&bar[0], 1);
+        mbarInit(&bar[1], 1);
+        mbarInitFence();
+        issue(t, 0);
+    }
+    constexpr uint32_t K1 = 0x38302212u, K2 = 0x00122230u;  // (18,34,48,56), (48,34,18,0)
+    constexpr uint32_t Ea = 0x2212u, Eb = 0x3830u, Ec = 0x2230u, Ed = 0x0012u;   // even start: 18,34 | 48,56 | 48,34 | 18,0
+    constexpr uint32_t Oa = 0x1200u, Ob = 0x3022u, Oc = 0x3038u, Od = 0x1222u;   // odd start:  0,18 | 34,48 | 56,48 | 34,18
+    const int g = tid & 31, w = tid >> 5;
+    for (int i = 0; t < total; ++i, t += stride) {
+        const int b = i & 1;
+        if (tid == 0) {
+            // buffer b ^ 1 was last read by the horizontal pass of the previous iteration, which ended before that iteration's
+            // second block barrier: it is free, so the next tile's box can fly while this tile is computed
+            if (t + stride < total) issue(t + stride, b ^ 1);
+            mbarWait(&bar[b], (uint32_t)((i >> 1) & 1));
+        }
+        const int f = t / tilesPerFrame;
+        const uint32_t te = __ldg(tileTab + (t - f * tilesPerFrame));
+        const int l = (int)(te >> 24);
+        const int x0 = (int)(te & 0xfffu) * kTileW, y0 = (int)((te >> 12) & 0xfffu) * kTileH;
+        const LevelPlan& L = P.lv[l];
+        __syncthreads();  // the tile has landed (thread 0 saw the barrier complete); the previous vertical pass is done with sHp
+        const uint8_t* in = sIn[b];
+        for (int m = w; m < kPairs; m += 8) {
+            uint32_t h[2][4];
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(in + (2 * m + rr) * kInPitch) + g;
+                const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t a = j ? __funnelshift_r(w0, w1, 8 * j) : w0;
+                    const uint32_t bb = j ? __funnelshift_r(w1, w2, 8 * j) : w1;
+                    h[rr][j] = __dp4a(a, K1, __dp4a(bb, K2, 0u));
+                }
+            }
+            uint4 pk;
+            pk.x = __byte_perm(h[0][0], h[1][0], 0x5410);
+            pk.y = __byte_perm(h[0][1], h[1][1], 0x5410);
+            pk.z = __byte_perm(h[0][2], h[1][2], 0x5410);
+            pk.w = __byte_perm(h[0][3], h[1][3], 0x5410);
+            *reinterpret_cast<uint4*>(sHp + m * kTileW + g * 4) = pk;
+        }
+        __syncthreads();
+        const int x = x0 + g * 4, yq = y0 + w * 4;
+        if (x < L.bpitch && yq < L.h) {
+            uint4 pr[5];
+#pragma unroll
+            for (int k = 0; k < 5; ++k) pr[k] = *reinterpret_cast<const uint4*>(sHp + (2 * w + k) * kTileW + g * 4);
+            uint8_t* out = blur + (size_t)f * P.blurBytes + L.blurOff + (size_t)yq * L.bpitch + x;
+            const int rq = min(4, L.h - yq);
+#pragma unroll
+            for (int r = 0; r < 4; ++r, out += L.bpitch) {
+                const int b2 = r >> 1;  // first pair
+                const uint32_t ca = (r & 1) ? Oa : Ea, cb = (r & 1) ? Ob : Eb, cc = (r & 1) ? Oc : Ec, cd = (r & 1) ? Od : Ed;
+                uint32_t v[4];
+                const uint32_t* p0 = &pr[b2].x; const uint32_t* p1 = &pr[b2 + 1].x; const uint32_t* p2 = &pr[b2 + 2].x; const uint32_t* p3 = &pr[b2 + 3].x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    uint32_t acc = __dp2a_lo(p0[k], ca, 32768u);
+                    acc = __dp2a_lo(p1[k], cb, acc);
+                    acc = __dp2a_lo(p2[k], cc, acc);
+                    v[k] = __dp2a_lo(p3[k], cd, acc);
+                }
+                const uint32_t word = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+                if (r < rq) *reinterpret_cast<uint32_t*>(out) = word;
+            }
+        }
+    }
+}
+
 }  // namespace
 
 size_t levelMapsBytes() { return sizeof(LevelMaps); }
@@ -242,12 +336,21 @@ void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
     static_assert(kTileW == 128 && kTileH == 32, "the plan's blurTile0 / blurTilesX assume 128 x 32 tiles");
     // ORBX_BLUR_MODE (A/B measurements): bit 0 = one mbarrier waiter, bit 1 = items numbered over the valid part of edge tiles.
     // Measured beside the quadtree (blur stage ms / frames per s): mode 0 0.303 / 157.2 k, 1 0.305 / 156.9 k, 2 0.322 / 155.1 k,
-    // 3 0.332 / 154.4 k: the kernel waits for its TMA tile (43 % of the stall samples), not for issue slots, so the 15 % fewer
-    // instructions of the edge tiles buy nothing and the extra index arithmetic costs; default = one waiter, no remapping.
+    // 3 0.332 / 154.4 k: the 15 % fewer instructions of the edge tiles buy nothing and the extra index arithmetic costs.  Mode 4 =
+    // persistent CTAs with the next tile's TMA box in flight while the current tile is computed (blurPersistKernel): 0.379 ms /
+    // 153.7 k - eight one-tile CTAs per SM already overlap each other's loads, and the persistent grid leaves the co-running quadtree
+    // fewer slots.  Default = one waiter, no remapping, one tile per CTA.
     static const int mode = [] { const char* e = std::getenv("ORBX_BLUR_MODE"); return e ? std::atoi(e) : 1; }();
     const LevelMaps& M = *reinterpret_cast<const LevelMaps*>(B.blurMaps);
     const dim3 grid(P.blurTiles, F);
-    if (B.blurMaps) {
+    if (B.blurMaps && mode == 4) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const long long total = (long long)P.blurTiles * F;
+        const int gridP = (int)std::min<long long>(total, (long long)sms * 8);
+        blurPersistKernel<<<gridP, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0, P.blurTiles, (int)total);
+    } else if (B.blurMaps) {
         if (mode == 3) blurKernel<true, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
         else if (mode == 2) blurKernel<false, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
         else if (mode == 1) blurKernel<true, false><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);

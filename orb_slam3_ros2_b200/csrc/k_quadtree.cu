@@ -212,13 +212,15 @@ template <int kQT>
 __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ FramePlan P, const uint32_t* __restrict__ cand,
                                                       const int* __restrict__ cellCnt, uint32_t* __restrict__ gath,
                                                       uint16_t* __restrict__ nidAll, LevelKp* __restrict__ lkp,
-                                                      int* __restrict__ lkpCnt, int* __restrict__ errFlag, int NC,
+                                                      int* __restrict__ lkpCnt, int* __restrict__ errFlag, int levelMajor, int NC,
                                                       int maxCells) {
     extern __shared__ __align__(16) uint8_t smemRaw[];
     __shared__ int sPartial[kQT / 32];
     __shared__ int sRed;
 
-    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    // levelMajor: the grid is (frames, levels) - every frame's level 0 first, then level 1, ...: the big levels start first and the
+    // small ones fill the SMs as those drain (with (levels, frames) every wave of resident CTAs ends with its own level-0 CTAs)
+    const int l = levelMajor ? blockIdx.y : blockIdx.x, f = levelMajor ? blockIdx.x : blockIdx.y, tid = threadIdx.x;
     const LevelPlan& L = P.lv[l];
     const int N = L.nFeat;
 
@@ -477,7 +479,10 @@ size_t quadtreeSmemBytes(const FramePlan& P) { return qtSmem(qtNodeCap(P), qtMax
 template <int QT>
 static void launchQuadtreeT(const FramePlan& P, const Buffers& B, int F, int NC, int maxCells, size_t smem, cudaStream_t s) {
     if (smem > 48 * 1024) cudaFuncSetAttribute(quadtreeKernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    quadtreeKernel<QT><<<dim3(P.nlevels, F), QT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag, NC, maxCells);
+    // ORBX_QT_ORDER=0: the round-1 grid (levels, frames) for A/B runs
+    static const int levelMajor = [] { const char* e = std::getenv("ORBX_QT_ORDER"); return e ? std::atoi(e) : 1; }();
+    const dim3 grid = levelMajor ? dim3(F, P.nlevels) : dim3(P.nlevels, F);
+    quadtreeKernel<QT><<<grid, QT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag, levelMajor, NC, maxCells);
 }
 
 void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
