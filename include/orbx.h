@@ -261,6 +261,18 @@ int orbx_search_by_projection(const orbx_keypoint* kps_last, const uint8_t* last
                               const uint8_t* cur_taken, const int32_t* n_cur, const float* poses, int pairs, int cap_last, int cap_cur,
                               const orbx_proj_params* params, int32_t* match_cur, int32_t* nmatches, int device);
 
+/* ---- ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, th, bFarPoints, thFarPoints), whole function ----
+ * (ORBmatcher.cc:43-210 + RadiusByViewingCos :215-221; Tracking::SearchLocalPoints, Tracking.cc:3410, :3433), frames with Nleft == -1.
+ * The map points arrive projected, as Frame::isInFrustum leaves them: track = 5 floats per point (mTrackProjX, mTrackProjY,
+ * mTrackProjXR, mTrackViewCos, mTrackDepth), level = mnTrackScaleLevel, flags bit 0 = mbTrackInView, bit 1 = Observations() > 0,
+ * bit 2 = isBad(), mp_desc = GetDescriptor().  The frame side, `pairs`, the [pair][cap] layout, cur_taken and the results are those
+ * of orbx_search_by_projection; of `params` the image bounds, scale factors and th are read; nnratio = ORBmatcher::mfNNratio (0.8 in
+ * SearchLocalPoints).  match_cur[pair][i] = index of the map point F.mvpMapPoints[i] holds after the call, -1 = none. */
+int orbx_search_by_projection_map(const float* track, const int32_t* level, const uint8_t* flags, const uint8_t* mp_desc, const int32_t* n_mp,
+                                  const orbx_keypoint* kps_cur, const uint8_t* desc_cur, const float* cur_u_right, const uint8_t* cur_taken,
+                                  const int32_t* n_cur, int pairs, int cap_mp, int cap_cur, const orbx_proj_params* params, float nnratio,
+                                  int far_points, float th_far_points, int32_t* match_cur, int32_t* nmatches, int device);
+
 /* ---- guided search: Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea + the best/second loop ---------------
  * The inner loop of ORBmatcher::SearchByProjection (frame to frame, ORBmatcher.cc:1676-1887), SearchForInitialization
  * (:648-763) and SearchByProjection(F, map points) (:45-138): for every query (u, v, radius, [min_level, max_level],

@@ -663,6 +663,93 @@ int orbo_search_by_projection_ff(const void* kps_last_, const uint8_t* last_flag
     return nmatches;
 }
 
+// ---- ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, th, bFarPoints, thFarPoints) -------------------
+// (src/ORBmatcher.cc:43-210 + RadiusByViewingCos :215-221), Tracking::SearchLocalPoints' matcher (Tracking.cc:3410, :3433), frames with
+// Nleft == -1.  Arguments as refslice_search_by_projection_map.  PINNED to the reference's own body by tests/test_oracle_refslices.py.
+int orbo_search_by_projection_map(const float* track, const int32_t* level, const uint8_t* flags, const uint8_t* mp_desc, int n_mp,
+                                  const void* kps_cur_, const uint8_t* desc_cur, const float* cur_u_right, const uint8_t* cur_taken, int n_cur,
+                                  float mnMinX, float mnMaxX, float mnMinY, float mnMaxY, const float* mvScaleFactors, int nlevels, float th,
+                                  int bFarPoints, float thFarPoints, float mfNNratio, int32_t* match_cur) {
+    (void)nlevels;
+    const Kp* kc = static_cast<const Kp*>(kps_cur_);
+    const float mfGridElementWidthInv = static_cast<float>(GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);  // Frame.cc:251
+    const float mfGridElementHeightInv = static_cast<float>(GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+    std::vector<std::vector<int>> grid((size_t)GRID_COLS * GRID_ROWS);
+    for (int i = 0; i < n_cur; ++i) {  // Frame.cc:385-416, :725-735
+        const int posX = (int)std::round((kc[i].x - mnMinX) * mfGridElementWidthInv);
+        const int posY = (int)std::round((kc[i].y - mnMinY) * mfGridElementHeightInv);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        grid[(size_t)posX * GRID_ROWS + posY].push_back(i);
+    }
+    // F.mvpMapPoints: -1 = NULL, -2 = a map point of the caller with Observations() > 0, i >= 0 = vpMapPoints[i]
+    for (int i = 0; i < n_cur; ++i) match_cur[i] = (cur_taken && cur_taken[i]) ? -2 : -1;
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;  // :47
+    for (int iMP = 0; iMP < n_mp; iMP++) {
+        if (!(flags[iMP] & 1)) continue;                                  // :52-53 (mbTrackInViewR is false for Nleft == -1 frames)
+        if (bFarPoints && track[5 * iMP + 4] > thFarPoints) continue;     // :55-56
+        if (flags[iMP] & 4) continue;                                     // :58-59 isBad()
+        const int nPredictedLevel = level[iMP];
+        float r = track[5 * iMP + 3] > 0.998 ? 2.5f : 4.0f;               // RadiusByViewingCos: a float compared with a double literal
+        if (bFactor) r *= th;
+        const float x = track[5 * iMP], y = track[5 * iMP + 1];
+        const float factorX = r * mvScaleFactors[nPredictedLevel], factorY = factorX;
+        const int minLevel = nPredictedLevel - 1, maxLevel = nPredictedLevel;
+        std::vector<int> vIndices;
+        {
+            const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - factorX) * mfGridElementWidthInv));
+            const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)std::ceil((x - mnMinX + factorX) * mfGridElementWidthInv));
+            const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - factorY) * mfGridElementHeightInv));
+            const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)std::ceil((y - mnMinY + factorY) * mfGridElementHeightInv));
+            if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+                const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+                for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                    for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+                        for (int idx : grid[(size_t)ix * GRID_ROWS + iy]) {
+                            const Kp& kpUn = kc[idx];
+                            if (bCheckLevels) {
+                                if (kpUn.octave < minLevel) continue;
+                                if (maxLevel >= 0)
+                                    if (kpUn.octave > maxLevel) continue;
+                            }
+                            const float distx = kpUn.x - x, disty = kpUn.y - y;
+                            if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices.push_back(idx);
+                        }
+            }
+        }
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (match_cur[idx] == -2 || (match_cur[idx] >= 0 && (flags[match_cur[idx]] & 2))) continue;  // :84-86
+            if (cur_u_right && cur_u_right[idx] > 0) {                                                     // :88-93
+                const float er = std::fabs(track[5 * iMP + 2] - cur_u_right[idx]);
+                if (er > r * mvScaleFactors[nPredictedLevel]) continue;
+            }
+            const int dist = orbo_hamming(mp_desc + (size_t)iMP * 32, desc_cur + (size_t)idx * 32);
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestLevel2 = bestLevel;
+                bestLevel = kc[idx].octave;
+                bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = kc[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {  // :123-128
+            if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+            if (bestLevel != bestLevel2 || bestDist <= mfNNratio * bestDist2) {
+                match_cur[bestIdx] = iMP;
+                nmatches++;
+            }
+        }
+    }
+    for (int i = 0; i < n_cur; ++i)
+        if (match_cur[i] == -2) match_cur[i] = -1;
+    return nmatches;
+}
+
 // ---- ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) (src/ORBmatcher.cc:765-905), monocular keyframes ----
 // The keyframe-to-keyframe twin of orbo_search_by_bow (loop closing / merging): candidates of keyframe 2 need a good MapPoint
 // and must not be matched yet (vbMatched2, :826-830), the accept rule is STRICT in TH_LOW (bestDist1 < TH_LOW, :848), the

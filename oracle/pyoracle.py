@@ -441,6 +441,39 @@ def ref_search_by_projection_ff(*a, **k):
     return _search_by_projection_ff(_slices().refslice_search_by_projection_ff, *a, **k)
 
 
+def _search_by_projection_map(fn, track, level, flags, mp_desc, kps_cur, desc_cur, bounds, scale_factors, th=3.0, far_points=False,
+                              th_far_points=50.0, nnratio=0.8, cur_u_right=None, cur_taken=None):
+    track = np.ascontiguousarray(track, dtype=np.float32).reshape(-1, 5)
+    level = np.ascontiguousarray(level, dtype=np.int32); flags = np.ascontiguousarray(flags, dtype=np.uint8)
+    mp_desc = np.ascontiguousarray(mp_desc, dtype=np.uint8); desc_cur = np.ascontiguousarray(desc_cur, dtype=np.uint8)
+    kps_cur = np.ascontiguousarray(kps_cur)
+    assert kps_cur.dtype.itemsize == 28
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    ur = None if cur_u_right is None else np.ascontiguousarray(cur_u_right, dtype=np.float32)
+    tk = None if cur_taken is None else np.ascontiguousarray(cur_taken, dtype=np.uint8)
+    n_mp, n_cur = len(track), len(kps_cur)
+    out = np.full(max(n_cur, 1), -1, dtype=np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = [_f32p, _i32p, _u8p, _u8p, C.c_int, C.c_void_p, _u8p, _f32p, _u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                   _f32p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, _i32p]
+    n = fn(_ptr(track, _f32p), _ptr(level, _i32p), _ptr(flags), _ptr(mp_desc), n_mp, kps_cur.ctypes.data_as(C.c_void_p), _ptr(desc_cur),
+           None if ur is None else _ptr(ur, _f32p), None if tk is None else _ptr(tk), n_cur, *[float(b) for b in bounds], _ptr(sf, _f32p),
+           len(sf), float(th), 1 if far_points else 0, float(th_far_points), float(nnratio), _ptr(out, _i32p))
+    return int(n), out[:n_cur]
+
+
+def search_by_projection_map(*a, **k):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) (ORBmatcher.cc:43-210), Nleft == -1 frames ->
+    (nmatches, match_cur[n_cur]: index of the map point the feature holds, or -1).  track: n x 5 (mTrackProjX, mTrackProjY, mTrackProjXR,
+    mTrackViewCos, mTrackDepth); flags bit 0 = mbTrackInView, bit 1 = Observations() > 0, bit 2 = isBad()."""
+    return _search_by_projection_map(port_lib().orbo_search_by_projection_map, *a, **k)
+
+
+def ref_search_by_projection_map(*a, **k):
+    """The same through the reference's own body (librefslices.so)."""
+    return _search_by_projection_map(_slices().refslice_search_by_projection_map, *a, **k)
+
+
 def stage_gray(img, rgb=True, new_size=None):
     """System.cc:420-425 (cv::resize on the interleaved colour image) then Tracking.cc:1569-1582 (cvtColor -> GRAY);
     OpenCV 8-bit RGB2Gray = (R*9798 + G*19235 + B*3735 + 2^14) >> 15."""

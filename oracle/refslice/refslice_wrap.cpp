@@ -11,6 +11,8 @@
 //   ORBmatcher.cc:765-905    ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)
 //   ORBmatcher.cc:1676-1887  ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono)  (TrackWithMotionModel's matcher)
 //   Pinhole.cpp:43-49        Pinhole::project(const Eigen::Vector3f&)
+//   ORBmatcher.cc:43-221     ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints) +
+//                            RadiusByViewingCos  (Tracking::SearchLocalPoints' matcher)
 //   Frame.cc:385-416         Frame::AssignFeaturesToGrid
 //   Frame.cc:657-723         Frame::GetFeaturesInArea
 //   Frame.cc:725-735         Frame::PosInGrid
@@ -42,6 +44,7 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 #include "ORBmatcher_SearchByBoW_KFKF.inc"
 #include "Pinhole_project.inc"
 #include "ORBmatcher_SearchByProjection_FF.inc"
+#include "ORBmatcher_SearchByProjection_FM.inc"
 }  // namespace ORB_SLAM3
 
 using ORB_SLAM3::Frame;
@@ -426,6 +429,52 @@ int refslice_search_by_projection_ff(const void* kps_last, const uint8_t* last_f
     ORBmatcher matcher(nnratio, check_orientation != 0);
     const int n = matcher.SearchByProjection(Cur, Last, th, b_mono != 0);
     for (int i = 0; i < n_cur; ++i) match_cur[i] = (Cur.mvpMapPoints[i] && Cur.mvpMapPoints[i]->index >= 0) ? Cur.mvpMapPoints[i]->index : -1;
+    return n;
+}
+
+// ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) for an Nleft == -1 frame (Tracking::SearchLocalPoints).
+// Per map point: track = (mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos, mTrackDepth), level = mnTrackScaleLevel,
+// flags bit 0 = mbTrackInView, bit 1 = Observations() > 0, bit 2 = isBad().  cur_taken / cur_u_right as in
+// refslice_search_by_projection_ff.  match_cur[i] = index of the map point F.mvpMapPoints[i] ends up holding, or -1.
+int refslice_search_by_projection_map(const float* track, const int32_t* level, const uint8_t* flags, const uint8_t* mp_desc, int n_mp,
+                                      const void* kps_cur, const uint8_t* desc_cur, const float* cur_u_right, const uint8_t* cur_taken,
+                                      int n_cur, float min_x, float max_x, float min_y, float max_y, const float* scale_factors, int nlevels,
+                                      float th, int far_points, float th_far_points, float nnratio, int32_t* match_cur) {
+    Frame F;
+    F.N = n_cur; F.Nleft = -1;
+    F.mvKeysUn = keypoints(kps_cur, n_cur);
+    F.mvKeys = F.mvKeysUn;
+    F.mDescriptors = descriptors(desc_cur, n_cur);
+    F.mvuRight.assign(n_cur, -1.f);
+    if (cur_u_right) F.mvuRight.assign(cur_u_right, cur_u_right + n_cur);
+    F.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    Frame::mnMinX = min_x; Frame::mnMaxX = max_x; Frame::mnMinY = min_y; Frame::mnMaxY = max_y;
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(Frame::mnMaxX - Frame::mnMinX);   // Frame.cc:251
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(Frame::mnMaxY - Frame::mnMinY);  // Frame.cc:252
+    F.AssignFeaturesToGrid();
+    std::vector<ORB_SLAM3::MapPoint> takenPts(n_cur), pts(n_mp);
+    F.mvpMapPoints.assign(n_cur, nullptr);
+    for (int i = 0; i < n_cur; ++i)
+        if (cur_taken && cur_taken[i]) {
+            takenPts[i].nObs = 1; takenPts[i].index = -2;
+            F.mvpMapPoints[i] = &takenPts[i];
+        }
+    std::vector<ORB_SLAM3::MapPoint*> vp(n_mp);
+    for (int i = 0; i < n_mp; ++i) {
+        ORB_SLAM3::MapPoint& p = pts[i];
+        p.index = i;
+        p.mTrackProjX = track[5 * i]; p.mTrackProjY = track[5 * i + 1]; p.mTrackProjXR = track[5 * i + 2];
+        p.mTrackViewCos = track[5 * i + 3]; p.mTrackDepth = track[5 * i + 4];
+        p.mnTrackScaleLevel = level[i];
+        p.mbTrackInView = (flags[i] & 1) != 0; p.mbTrackInViewR = false;
+        p.nObs = (flags[i] & 2) ? 3 : 0;
+        p.mbBad = (flags[i] & 4) != 0;
+        p.mDescriptor = descriptors(mp_desc + (size_t)i * 32, 1);
+        vp[i] = &p;
+    }
+    ORBmatcher matcher(nnratio, true);
+    const int n = matcher.SearchByProjection(F, vp, th, far_points != 0, th_far_points);
+    for (int i = 0; i < n_cur; ++i) match_cur[i] = (F.mvpMapPoints[i] && F.mvpMapPoints[i]->index >= 0) ? F.mvpMapPoints[i]->index : -1;
     return n;
 }
 

@@ -103,6 +103,10 @@ public:
     int Observations() { return nObs; }
     bool mbBad = false;
     int index = -1;  // (shim) the keyframe feature this map point was created for
+    // tracking variables set by Frame::isInFrustum (include/MapPoint.h:141-152), read by SearchByProjection(Frame&, vector<MapPoint*>&)
+    float mTrackProjX = 0, mTrackProjY = 0, mTrackDepth = 0, mTrackProjXR = 0, mTrackProjYR = 0, mTrackViewCos = 0, mTrackViewCosR = 0;
+    bool mbTrackInView = false, mbTrackInViewR = false;
+    int mnTrackScaleLevel = 0, mnTrackScaleLevelR = -1;
     Eigen::Vector3f mWorldPos;
     cv::Mat mDescriptor;
     int nObs = 0;
@@ -128,6 +132,9 @@ public:
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
                                 int windowSize = 10);
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
+    int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3, const bool bFarPoints = false,
+                           const float thFarPoints = 50.0f);
+    float RadiusByViewingCos(const float& viewCos);
     static const int TH_LOW;
     static const int TH_HIGH;
     static const int HISTO_LENGTH;
@@ -168,6 +175,7 @@ public:
     Sophus::SE3f mTcw, mTrl;
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<bool> mvbOutlier;
+    std::vector<int> mvLeftToRightMatch, mvRightToLeftMatch;
 };
 
 }  // namespace ORB_SLAM3

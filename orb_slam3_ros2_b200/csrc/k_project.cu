@@ -52,6 +52,10 @@ struct ProjArgs {
     float sf[kMaxLevels];
 };
 
+struct GridGeom {
+    float minX, minY, invW, invH;
+};
+
 struct V3 {
     float x, y, z;
 };
@@ -78,7 +82,7 @@ __device__ __forceinline__ V3 se3mul(const float* T, V3 p) {  // se3.hpp:324
 // reference's visiting order (grid column by grid column, rows inside, insertion order inside a cell), 32 candidates per trip:
 // emit(ok, idx, dist, position) is called by the whole warp.  colB / pre: 64 + 65 ints of shared memory of this warp.
 template <class Emit>
-__device__ __forceinline__ int projEnumerate(const ProjArgs& A, const float* kc, const uint4* dc, const float* urc, const uint32_t* sorted,
+__device__ __forceinline__ int projEnumerate(const GridGeom A, const float* kc, const uint4* dc, const float* urc, const uint32_t* sorted,
                                              const int* cellStart, float u, float v, float radius, int minLevel, int maxLevel, float ur,
                                              const uint4 a0, const uint4 a1, int lane, int* colB, int* pre, Emit emit) {
     const int minCX = max(0, (int)floorf(fm(fs(fs(u, A.minX), radius), A.invW)));
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(256) projCandKernel(const ProjArgs A, int pair
     const uint4 a0 = A.mpDesc[(oL + i) * 2], a1 = A.mpDesc[(oL + i) * 2 + 1];
     uint32_t* list = A.candList + (oL + i) * kProjListCap;
     int count = 0;
-    projEnumerate(A, A.kpsCur + oC * 7, A.descCur + oC * 2, A.uRightCur ? A.uRightCur + oC : nullptr, A.sorted + oC,
+    projEnumerate(GridGeom{A.minX, A.minY, A.invW, A.invH}, A.kpsCur + oC * 7, A.descCur + oC * 2, A.uRightCur ? A.uRightCur + oC : nullptr, A.sorted + oC,
                   A.cellStart + (size_t)pair * (kGridCells + 1), u, v, radius, minLevel, maxLevel, ur, a0, a1, lane, sColB[wip], sPre[wip],
                   [&](bool ok, int idx, int dist, int) {
                       const unsigned bal = __ballot_sync(0xffffffffu, ok);
@@ -235,7 +239,7 @@ __global__ void __launch_bounds__(32) projWalkKernel(const ProjArgs A) {
         } else {  // the list overflowed: walk the window again, here
             const float* pj = A.proj + (oL + i) * 4;
             const uint4 a0 = A.mpDesc[(oL + i) * 2], a1 = A.mpDesc[(oL + i) * 2 + 1];
-            projEnumerate(A, kc, A.descCur + oC * 2, A.uRightCur ? A.uRightCur + oC : nullptr, A.sorted + oC,
+            projEnumerate(GridGeom{A.minX, A.minY, A.invW, A.invH}, kc, A.descCur + oC * 2, A.uRightCur ? A.uRightCur + oC : nullptr, A.sorted + oC,
                           A.cellStart + (size_t)pair * (kGridCells + 1), pj[0], pj[1], pj[2], A.levels[(oL + i) * 2], A.levels[(oL + i) * 2 + 1],
                           pj[3], a0, a1, lane, colB, pre, [&](bool ok, int idx, int dist, int t) {
                               if (ok && !((taken[idx >> 5] >> (idx & 31)) & 1u))
@@ -293,6 +297,147 @@ __global__ void __launch_bounds__(32) projWalkKernel(const ProjArgs A) {
     if (lane == 0) A.nMatches[pair] = nmatches;
 }
 
+// ---- ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, th, bFarPoints, thFarPoints) -------------------
+// (ORBmatcher.cc:43-210 + RadiusByViewingCos :215-221; Tracking::SearchLocalPoints, Tracking.cc:3410, :3433), Nleft == -1 frames.
+// The map points arrive already projected (Frame::isInFrustum set mTrackProjX / Y / XR, mnTrackScaleLevel, mTrackViewCos), so phase A
+// is the window query alone; phase B keeps best AND second (strict <, first in visiting order) with their octaves and applies the
+// accept rule of :123-128 before F.mvpMapPoints[bestIdx] = pMP.
+struct MapArgs {
+    const float* track;        // [pair][capMp] x 5: mTrackProjX, mTrackProjY, mTrackProjXR, mTrackViewCos, mTrackDepth
+    const int* level;          // mnTrackScaleLevel
+    const uint8_t* flags;      // bit 0 = mbTrackInView, bit 1 = Observations() > 0, bit 2 = isBad()
+    const uint4* mpDesc;
+    const int* nMp;            // [pair]
+    const float* kpsCur;
+    const uint4* descCur;
+    const float* uRightCur;
+    const uint8_t* takenCur;
+    const int* nCur;
+    const uint32_t* sorted;
+    const int* cellStart;
+    uint32_t* candList;        // [pair][capMp][kProjListCap]
+    int* candCount;
+    float* radius;             // [pair][capMp]: r * mvScaleFactors[level]
+    int* matchCur;
+    int* nMatches;
+    int capMp, capCur;
+    float minX, minY, invW, invH, th, thFar, nnratio;
+    int farPoints;
+    float sf[kMaxLevels];
+};
+
+__global__ void __launch_bounds__(256) mapCandKernel(const MapArgs A, int pairs) {
+    __shared__ int sColB[8][64], sPre[8][65];
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, wip = threadIdx.x >> 5;
+    const int pair = wid / A.capMp, i = wid - pair * A.capMp;
+    if (pair >= pairs) return;
+    const int nMp = min(A.nMp[pair], A.capMp);
+    if (i >= nMp) return;
+    const size_t oM = (size_t)pair * A.capMp, oC = (size_t)pair * A.capCur;
+    int* cnt = A.candCount + oM + i;
+    const float* tr = A.track + (oM + i) * 5;
+    const uint8_t fl = A.flags[oM + i];
+    // :52-59: not in view, too far, bad
+    if (!(fl & 1) || (A.farPoints && tr[4] > A.thFar) || (fl & 4)) {
+        if (lane == 0) *cnt = -1;
+        return;
+    }
+    const int lvl = min(max(A.level[oM + i], 0), kMaxLevels - 1);
+    float r = (double)tr[3] > 0.998 ? 2.5f : 4.0f;  // RadiusByViewingCos: the float against a double literal
+    if (A.th != 1.0f) r = fm(r, A.th);             // bFactor (:47, :68-69)
+    const float radius = fm(r, A.sf[lvl]);
+    const uint4 a0 = A.mpDesc[(oM + i) * 2], a1 = A.mpDesc[(oM + i) * 2 + 1];
+    uint32_t* list = A.candList + (oM + i) * kProjListCap;
+    int count = 0;
+    projEnumerate(GridGeom{A.minX, A.minY, A.invW, A.invH}, A.kpsCur + oC * 7, A.descCur + oC * 2, A.uRightCur ? A.uRightCur + oC : nullptr,
+                  A.sorted + oC, A.cellStart + (size_t)pair * (kGridCells + 1), tr[0], tr[1], radius, lvl - 1, lvl, tr[2], a0, a1, lane,
+                  sColB[wip], sPre[wip], [&](bool ok, int idx, int dist, int) {
+                      const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                      const int pos = count + __popc(bal & ((1u << lane) - 1u));
+                      if (ok && pos < kProjListCap) list[pos] = ((uint32_t)dist << 20) | (uint32_t)idx;
+                      count += __popc(bal);
+                  });
+    if (lane == 0) {
+        *cnt = count;
+        A.radius[oM + i] = radius;
+    }
+}
+
+__device__ __forceinline__ void top2Key(unsigned long long& k1, unsigned long long& k2, unsigned long long k) {
+    k2 = min(k2, max(k1, k));
+    k1 = min(k1, k);
+}
+
+__global__ void __launch_bounds__(32) mapWalkKernel(const MapArgs A) {
+    __shared__ uint32_t taken[kMaxCur / 32];
+    __shared__ int colB[64], pre[65];
+    const int pair = blockIdx.x, lane = threadIdx.x;
+    const size_t oM = (size_t)pair * A.capMp, oC = (size_t)pair * A.capCur;
+    const int nMp = min(A.nMp[pair], A.capMp), nCur = min(min(A.nCur[pair], A.capCur), kMaxCur);
+    const float* kc = A.kpsCur + oC * 7;
+    int* match = A.matchCur + oC;
+    for (int w = lane; w < (nCur + 31) / 32; w += 32) {
+        uint32_t bits = 0;
+        if (A.takenCur)
+            for (int b = 0; b < 32 && w * 32 + b < nCur; ++b) bits |= (A.takenCur[oC + w * 32 + b] ? 1u : 0u) << b;
+        taken[w] = bits;
+    }
+    for (int i = lane; i < A.capCur; i += 32) match[i] = -1;
+    __syncwarp();
+    int nmatches = 0;
+    for (int i = 0; i < nMp; ++i) {
+        const int cnt = A.candCount[oM + i];
+        if (cnt <= 0) continue;
+        unsigned long long k1 = ~0ull, k2 = ~0ull;  // distance << 40 | visiting position << 20 | index
+        if (cnt <= kProjListCap) {
+            const uint32_t* list = A.candList + (oM + i) * kProjListCap;
+            for (int p0 = 0; p0 < cnt; p0 += 32) {
+                const int p = p0 + lane;
+                if (p < cnt) {
+                    const uint32_t e = list[p];
+                    const uint32_t idx = e & 0xfffffu;
+                    if (!((taken[idx >> 5] >> (idx & 31)) & 1u))
+                        top2Key(k1, k2, ((unsigned long long)(e >> 20) << 40) | ((unsigned long long)p << 20) | idx);
+                }
+            }
+        } else {
+            const float* tr = A.track + (oM + i) * 5;
+            const int lvl = min(max(A.level[oM + i], 0), kMaxLevels - 1);
+            const uint4 a0 = A.mpDesc[(oM + i) * 2], a1 = A.mpDesc[(oM + i) * 2 + 1];
+            projEnumerate(GridGeom{A.minX, A.minY, A.invW, A.invH}, kc, A.descCur + oC * 2, A.uRightCur ? A.uRightCur + oC : nullptr,
+                          A.sorted + oC, A.cellStart + (size_t)pair * (kGridCells + 1), tr[0], tr[1], A.radius[oM + i], lvl - 1, lvl, tr[2],
+                          a0, a1, lane, colB, pre, [&](bool ok, int idx, int dist, int t) {
+                              if (ok && !((taken[idx >> 5] >> (idx & 31)) & 1u))
+                                  top2Key(k1, k2, ((unsigned long long)dist << 40) | ((unsigned long long)t << 20) | (unsigned)idx);
+                          });
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+            top2Key(k1, k2, o1);
+            top2Key(k1, k2, o2);
+        }
+        if (k1 != ~0ull) {
+            const int bestDist = (int)(k1 >> 40), bestIdx = (int)(k1 & 0xfffffu);
+            const int bestDist2 = k2 != ~0ull ? (int)(k2 >> 40) : 256;
+            const int bestLevel = __float_as_int(kc[bestIdx * 7 + 5]);
+            const int bestLevel2 = k2 != ~0ull ? __float_as_int(kc[(int)(k2 & 0xfffffu) * 7 + 5]) : -1;
+            // :123-128: bestDist <= TH_HIGH and (levels differ or (float)bestDist <= mfNNratio * bestDist2)
+            const float lim = fm(A.nnratio, (float)bestDist2);
+            const bool ok = bestDist <= 100 && (bestLevel != bestLevel2 || (float)bestDist <= lim);
+            if (ok) {
+                ++nmatches;
+                if (lane == 0) {
+                    match[bestIdx] = i;
+                    if (A.flags[oM + i] & 2) taken[bestIdx >> 5] |= 1u << (bestIdx & 31);
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (lane == 0) A.nMatches[pair] = nmatches;
+}
+
 }  // namespace
 
 size_t projScratchWordsPerLast() { return kProjListCap + 1 + 4 + 2 + 1; }  // list, count, proj, levels, pushes (32-bit words per last-frame slot)
@@ -328,6 +473,34 @@ void launchSearchByProjection(const void* kpsLast, const uint8_t* lastFlags, con
     projCandKernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, s>>>(A, pairs);
     countLaunch();
     projWalkKernel<<<pairs, 32, 0, s>>>(A);
+    countLaunch();
+}
+
+size_t mapScratchWordsPerPoint() { return kProjListCap + 1 + 1; }  // list, count, radius
+
+// Tracking::SearchLocalPoints' matcher for `pairs` independent (map point set, frame) problems; device pointers, [pair][cap...].
+void launchSearchByProjectionMap(const float* track, const int* level, const uint8_t* flags, const uint8_t* mpDesc, const int* nMp,
+                                 const void* kpsCur, const uint8_t* descCur, const float* uRightCur, const uint8_t* takenCur, const int* nCur,
+                                 int pairs, int capMp, int capCur, const ProjCam& C, float nnratio, int farPoints, float thFar,
+                                 uint32_t* sorted, int* cellStart, uint32_t* scratch, int* matchCur, int* nMatches, cudaStream_t s) {
+    if (pairs <= 0) return;
+    MapArgs A{};
+    A.track = track; A.level = level; A.flags = flags; A.mpDesc = reinterpret_cast<const uint4*>(mpDesc); A.nMp = nMp;
+    A.kpsCur = static_cast<const float*>(kpsCur); A.descCur = reinterpret_cast<const uint4*>(descCur);
+    A.uRightCur = uRightCur; A.takenCur = takenCur; A.nCur = nCur; A.sorted = sorted; A.cellStart = cellStart;
+    const size_t slots = (size_t)pairs * capMp;
+    A.candList = scratch;
+    A.candCount = reinterpret_cast<int*>(scratch + slots * kProjListCap);
+    A.radius = reinterpret_cast<float*>(scratch + slots * (kProjListCap + 1));
+    A.matchCur = matchCur; A.nMatches = nMatches; A.capMp = capMp; A.capCur = capCur;
+    A.minX = C.minX; A.minY = C.minY;
+    A.invW = (float)kGridCols / (C.maxX - C.minX); A.invH = (float)kGridRows / (C.maxY - C.minY);  // Frame.cc:251-252
+    A.th = C.th; A.thFar = thFar; A.nnratio = nnratio; A.farPoints = farPoints;
+    for (int l = 0; l < kMaxLevels; ++l) A.sf[l] = l < C.nlevels ? C.sf[l] : 1.f;
+    const long long warps = (long long)pairs * capMp;
+    mapCandKernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, s>>>(A, pairs);
+    countLaunch();
+    mapWalkKernel<<<pairs, 32, 0, s>>>(A);
     countLaunch();
 }
 

@@ -1668,6 +1668,77 @@ int orbx_search_by_projection(const orbx_keypoint* kps_last, const uint8_t* last
     return ORBX_OK;
 }
 
+int orbx_search_by_projection_map(const float* track, const int32_t* level, const uint8_t* flags, const uint8_t* mp_desc, const int32_t* n_mp,
+                                  const orbx_keypoint* kps_cur, const uint8_t* desc_cur, const float* cur_u_right, const uint8_t* cur_taken,
+                                  const int32_t* n_cur, int pairs, int cap_mp, int cap_cur, const orbx_proj_params* params, float nnratio,
+                                  int far_points, float th_far_points, int32_t* match_cur, int32_t* nmatches, int device) {
+    if (pairs < 0 || cap_mp < 0 || cap_cur < 0 || !params || !n_mp || !n_cur || !nmatches ||
+        (cap_mp > 0 && (!track || !level || !flags || !mp_desc)) || (cap_cur > 0 && (!kps_cur || !desc_cur || !match_cur)))
+        return fail(ORBX_ERR_ARG, "bad argument");
+    if (!(params->max_x > params->min_x) || !(params->max_y > params->min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
+    if (params->nlevels < 1 || params->nlevels > kMaxLevels) return fail(ORBX_ERR_ARG, "nlevels must be in [1,16]");
+    if (cap_cur > gridSortCapacity()) return fail(ORBX_ERR_ARG, "more than 32768 keypoints in the frame");
+    for (int p = 0; p < pairs; ++p) {
+        if (n_mp[p] < 0 || n_mp[p] > cap_mp || n_cur[p] < 0 || n_cur[p] > cap_cur) return fail(ORBX_ERR_ARG, "count exceeds capacity");
+        nmatches[p] = 0;
+        for (int i = 0; i < n_mp[p]; ++i) {  // mnTrackScaleLevel indexes mvScaleFactors (:71)
+            const int l = level[(size_t)p * cap_mp + i];
+            if ((flags[(size_t)p * cap_mp + i] & 1) && (l < 0 || l >= params->nlevels))
+                return fail(ORBX_ERR_ARG, "predicted level of a map point in view outside [0, nlevels)");
+        }
+    }
+    int rc = needDevice();
+    if (rc != ORBX_OK) return rc;
+    if (pairs == 0 || cap_mp == 0 || cap_cur == 0) {
+        for (size_t i = 0; i < (size_t)pairs * cap_cur; ++i) match_cur[i] = -1;
+        return ORBX_OK;
+    }
+    DeviceGuard guard(device);
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    MatchScratch* S = nullptr;
+    rc = matchScratch(dev, &S);
+    if (rc != ORBX_OK) return rc;
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t P = (size_t)pairs, L = P * cap_mp, Cn = P * cap_cur;
+    // q (map point side): [mpDesc | track | level | flags | nMp | nCur | nMatches]
+    const size_t oTr = al(L * 32), oLv = oTr + al(L * 20), oF = oLv + al(L * 4), oNm = oF + al(L), oNc = oNm + al(P * 4), oNr = oNc + al(P * 4),
+                 qBytes = oNr + al(P * 4);
+    const size_t oKc = al(Cn * 32), oUr = oKc + al(Cn * 28), oTk = oUr + al(Cn * 4), oSo = oTk + al(Cn), oCs = oSo + al(Cn * 4),
+                 oMa = oCs + al(P * (size_t)(64 * 48 + 1) * 4), dbBytes = oMa + al(Cn * 4);
+    ORBX_CUDA(S->q.reserve(qBytes));
+    ORBX_CUDA(S->db.reserve(dbBytes));
+    ORBX_CUDA(S->k1.reserve(L * mapScratchWordsPerPoint() * 4 + 256));
+    uint8_t* Q = (uint8_t*)S->q.p;
+    uint8_t* D = (uint8_t*)S->db.p;
+    cudaStream_t s = S->stream;
+    ORBX_CUDA(cudaMemcpyAsync(Q, mp_desc, L * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oTr, track, L * 20, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oLv, level, L * 4, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oF, flags, L, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oNm, n_mp, P * 4, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(Q + oNc, n_cur, P * 4, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(D, desc_cur, Cn * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(D + oKc, kps_cur, Cn * 28, cudaMemcpyHostToDevice, s));
+    if (cur_u_right) ORBX_CUDA(cudaMemcpyAsync(D + oUr, cur_u_right, Cn * 4, cudaMemcpyHostToDevice, s));
+    if (cur_taken) ORBX_CUDA(cudaMemcpyAsync(D + oTk, cur_taken, Cn, cudaMemcpyHostToDevice, s));
+    launchGridSortBatch(D + oKc, (const int*)(Q + oNc), pairs, cap_cur, params->min_x, params->max_x, params->min_y, params->max_y,
+                        (uint32_t*)(D + oSo), (int*)(D + oCs), s);
+    ProjCam C{};
+    C.minX = params->min_x; C.maxX = params->max_x; C.minY = params->min_y; C.maxY = params->max_y;
+    C.th = params->th; C.nlevels = params->nlevels;
+    for (int l = 0; l < params->nlevels; ++l) C.sf[l] = params->scale_factors[l];
+    launchSearchByProjectionMap((const float*)(Q + oTr), (const int*)(Q + oLv), Q + oF, Q, (const int*)(Q + oNm), D + oKc, D,
+                                cur_u_right ? (const float*)(D + oUr) : nullptr, cur_taken ? D + oTk : nullptr, (const int*)(Q + oNc), pairs,
+                                cap_mp, cap_cur, C, nnratio, far_points != 0, th_far_points, (uint32_t*)(D + oSo), (int*)(D + oCs),
+                                (uint32_t*)S->k1.p, (int*)(D + oMa), (int*)(Q + oNr), s);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(match_cur, D + oMa, Cn * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(nmatches, Q + oNr, P * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_search_for_initialization_batch(orbx_handle h, int use_undistorted, float min_x, float max_x, float min_y, float max_y,
                                          int window_size, float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches,
                                          float* prev_matched) {

@@ -184,6 +184,11 @@ struct ProjCam {
     float sf[kMaxLevels];
 };
 size_t projScratchWordsPerLast();
+size_t mapScratchWordsPerPoint();
+void launchSearchByProjectionMap(const float* track, const int* level, const uint8_t* flags, const uint8_t* mpDesc, const int* nMp,
+                                 const void* kpsCur, const uint8_t* descCur, const float* uRightCur, const uint8_t* takenCur, const int* nCur,
+                                 int pairs, int capMp, int capCur, const ProjCam& C, float nnratio, int farPoints, float thFar,
+                                 uint32_t* sorted, int* cellStart, uint32_t* scratch, int* matchCur, int* nMatches, cudaStream_t s);
 void launchSearchByProjection(const void* kpsLast, const uint8_t* lastFlags, const float* world, const uint8_t* mpDesc, const int* nLast,
                               const void* kpsCur, const uint8_t* descCur, const float* uRightCur, const uint8_t* takenCur, const int* nCur,
                               const float* poses, int pairs, int capLast, int capCur, const ProjCam& C, uint32_t* sorted, int* cellStart,

@@ -98,6 +98,8 @@ SYMBOLS = {
     "orbx_search_by_bow_kf": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p,
                                         _i32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_capacity": (C.c_int, [_vp, C.c_int, C.c_int, _i32p]),
+    "orbx_search_by_projection_map": (C.c_int, [_vp, _i32p, _u8p, _u8p, _i32p, _vp, _u8p, _vp, _vp, _i32p, C.c_int, C.c_int, C.c_int, _vp,
+                                                C.c_float, C.c_int, C.c_float, _i32p, _i32p, C.c_int]),
     "orbx_search_by_projection": (C.c_int, [_vp, _u8p, _vp, _u8p, _i32p, _vp, _u8p, _vp, _vp, _i32p, _vp, C.c_int, C.c_int, C.c_int, _vp,
                                             _i32p, _i32p, C.c_int]),
     "orbx_debug_check_guards": (C.c_int, [_vp]),
@@ -586,6 +588,41 @@ def search_by_projection(cases, cam, bounds, scale_factors, th, mono, mbf=0.0, m
                                            tk.ctypes.data_as(_vp) if has_tk else None, _ptr(nc, _i32p), poses.ctypes.data_as(_vp), P, cap_l,
                                            cap_c, C.byref(prm), _ptr(match, _i32p), _ptr(nm, _i32p), device))
     return [(int(nm[p]), match[p, :nc[p]].copy()) for p in range(P)]
+
+
+def search_by_projection_map(cases, bounds, scale_factors, th=3.0, far_points=False, th_far_points=50.0, nnratio=0.8, device=-1):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) (ORBmatcher.cc:43-210, Tracking::SearchLocalPoints) on the
+    device for a list of independent (map points, frame) problems.  Each case: track (n x 5), level, flags, mp_desc, kps_cur, desc_cur and
+    optionally cur_u_right, cur_taken.  -> [(nmatches, match_cur[n_cur])] per case."""
+    P = len(cases)
+    cap_m = max([len(c["level"]) for c in cases] + [1])
+    cap_c = max([len(c["kps_cur"]) for c in cases] + [1])
+    tr = np.zeros((P, cap_m, 5), np.float32); lv = np.zeros((P, cap_m), np.int32); fl = np.zeros((P, cap_m), np.uint8)
+    md = np.zeros((P, cap_m, 32), np.uint8); kc = np.zeros((P, cap_c), dtype=KP_DTYPE); dc = np.zeros((P, cap_c, 32), np.uint8)
+    has_ur = cases[0].get("cur_u_right") is not None
+    has_tk = cases[0].get("cur_taken") is not None
+    ur = np.full((P, cap_c), -1, np.float32); tk = np.zeros((P, cap_c), np.uint8)
+    nm_ = np.zeros(P, np.int32); nc = np.zeros(P, np.int32)
+    for p, c in enumerate(cases):
+        a, b = len(c["level"]), len(c["kps_cur"])
+        nm_[p], nc[p] = a, b
+        tr[p, :a] = np.asarray(c["track"], np.float32).reshape(-1, 5); lv[p, :a] = c["level"]; fl[p, :a] = c["flags"]; md[p, :a] = c["mp_desc"]
+        kc[p, :b] = c["kps_cur"]; dc[p, :b] = c["desc_cur"]
+        if has_ur: ur[p, :b] = c["cur_u_right"]
+        if has_tk: tk[p, :b] = c["cur_taken"]
+    prm = ProjParams()
+    prm.min_x, prm.max_x, prm.min_y, prm.max_y = [float(v) for v in bounds]
+    sf = np.asarray(scale_factors, np.float32)
+    for l in range(len(sf)):
+        prm.scale_factors[l] = float(sf[l])
+    prm.nlevels = len(sf); prm.th = float(th)
+    match = np.full((P, cap_c), -1, np.int32); nmat = np.zeros(P, np.int32)
+    _check(lib().orbx_search_by_projection_map(tr.ctypes.data_as(_vp), _ptr(lv, _i32p), _ptr(fl), _ptr(md), _ptr(nm_, _i32p),
+                                               kc.ctypes.data_as(_vp), _ptr(dc), ur.ctypes.data_as(_vp) if has_ur else None,
+                                               tk.ctypes.data_as(_vp) if has_tk else None, _ptr(nc, _i32p), P, cap_m, cap_c, C.byref(prm),
+                                               float(nnratio), 1 if far_points else 0, float(th_far_points), _ptr(match, _i32p),
+                                               _ptr(nmat, _i32p), device))
+    return [(int(nmat[p]), match[p, :nc[p]].copy()) for p in range(P)]
 
 
 def accept_bow(d1, d2, nnratio=0.7, th=TH_LOW):

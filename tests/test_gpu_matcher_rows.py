@@ -275,3 +275,26 @@ def test_search_by_projection_batch_and_crowded_windows(orbx, oracle):
     bad["kps_last"]["octave"][0] = 9
     with pytest.raises(orbx.OrbxError):
         orbx.search_by_projection([bad], c0["cam"], c0["bounds"], c0["scale_factors"], 15, True)
+
+
+@pytest.mark.parametrize("kw,th,far", [(dict(k=0, seed=0), 3.0, False), (dict(k=1, seed=1, stereo=True), 3.0, False), (dict(k=2, seed=2, nf=2000, w=1241, h=376, stereo=True), 5.0, True),
+                                      (dict(k=3, seed=3, taken_frac=0.7), 1.0, False), (dict(k=4, seed=4, w=640, h=360, nf=1250), 15.0, True)])
+def test_search_by_projection_map_points_matches_oracle(orbx, oracle, kw, th, far):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) (Tracking::SearchLocalPoints), whole function on the
+    device, against the restatement pinned to the reference's own body; th = 15 makes windows longer than the per-point list."""
+    from test_oracle_matcher_rows import make_local_points_case
+    c = make_local_points_case(oracle, **kw)
+    for nn in (0.8, 0.6):
+        want = oracle.search_by_projection_map(**c, th=th, far_points=far, th_far_points=30.0, nnratio=nn)
+        got = orbx.search_by_projection_map([c], c["bounds"], c["scale_factors"], th, far, 30.0, nn)[0]
+        assert got[0] == want[0], (kw, th, nn, got[0], want[0])
+        assert np.array_equal(got[1], want[1]), (kw, th, nn, np.flatnonzero(got[1] != want[1])[:10])
+
+
+def test_search_by_projection_map_points_batch(orbx, oracle):
+    from test_oracle_matcher_rows import make_local_points_case
+    cases = [make_local_points_case(oracle, k=k, seed=20 + k, nf=nf) for k, nf in ((0, 1000), (1, 600), (2, 1400))]
+    got = orbx.search_by_projection_map(cases, cases[0]["bounds"], cases[0]["scale_factors"], 3.0)
+    for c, g in zip(cases, got):
+        want = oracle.search_by_projection_map(**c, th=3.0)
+        assert g[0] == want[0] and np.array_equal(g[1], want[1])

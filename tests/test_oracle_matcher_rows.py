@@ -189,3 +189,50 @@ def test_search_by_projection_frame_frame_known_properties(oracle):
     assert np.all(c["last_flags"][m[hit]] & 1)      # only valid map points are projected
     n0, m0 = oracle.search_by_projection_ff(**dict(c, check_orientation=False))
     assert n0 >= n                                   # the rotation histogram only removes matches
+
+
+def make_local_points_case(oracle, k=0, w=752, h=480, nf=1000, seed=0, stereo=False, taken_frac=0.3, n_extra=400):
+    """Tracking::SearchLocalPoints' input: map points projected into the frame (here: the frame's own keypoints jittered by a few pixels,
+    plus points that match nothing), predicted levels around the observed octave, viewing cosines on both sides of 0.998, some points
+    out of view / bad / far, part of the features already matched (TrackWithMotionModel ran before)."""
+    from orb_slam3_ros2_b200 import synth
+    rng = np.random.default_rng(seed)
+    ex = oracle.PortExtractor(nfeatures=nf)
+    _, kc, dc = ex.extract(synth.frame(k, w, h), (0, 1000))
+    sf = ex.tables()["scale"]
+    n = len(kc)
+    pick = rng.permutation(n)[: int(0.8 * n)]
+    m = len(pick) + n_extra
+    track = np.zeros((m, 5), np.float32)
+    level = np.zeros(m, np.int32)
+    desc = np.zeros((m, 32), np.uint8)
+    track[:len(pick), 0] = kc["x"][pick] + rng.normal(0, 2.0, len(pick))
+    track[:len(pick), 1] = kc["y"][pick] + rng.normal(0, 2.0, len(pick))
+    level[:len(pick)] = np.clip(kc["octave"][pick] + rng.integers(0, 2, len(pick)), 0, 7)
+    desc[:len(pick)] = dc[pick]
+    for i in range(len(pick)):  # a few bits of noise
+        for b in rng.integers(0, 256, int(rng.integers(0, 25))):
+            desc[i, b // 8] ^= np.uint8(1 << (b % 8))
+    track[len(pick):, 0] = rng.uniform(0, w, n_extra); track[len(pick):, 1] = rng.uniform(0, h, n_extra)
+    level[len(pick):] = rng.integers(0, 8, n_extra)
+    desc[len(pick):] = rng.integers(0, 256, (n_extra, 32), dtype=np.uint8)
+    track[:, 2] = track[:, 0] - rng.uniform(2, 40, m)            # mTrackProjXR
+    track[:, 3] = np.where(rng.random(m) < 0.5, 0.9995, 0.95)    # mTrackViewCos
+    track[:, 4] = rng.uniform(1, 80, m)                          # mTrackDepth
+    flags = (rng.random(m) < 0.9).astype(np.uint8) | ((rng.random(m) < 0.9).astype(np.uint8) << 1) | ((rng.random(m) < 0.03).astype(np.uint8) << 2)
+    order = rng.permutation(m)
+    taken = (rng.random(n) < taken_frac).astype(np.uint8)
+    ur = np.where(rng.random(n) < 0.6, kc["x"] - rng.uniform(2, 40, n), -1).astype(np.float32) if stereo else None
+    return dict(track=track[order], level=level[order], flags=flags[order], mp_desc=desc[order], kps_cur=kc, desc_cur=dc,
+                bounds=(0.0, float(w), 0.0, float(h)), scale_factors=sf, cur_u_right=ur, cur_taken=taken)
+
+
+def test_search_by_projection_map_points_known_properties(oracle):
+    c = make_local_points_case(oracle, k=1, seed=2)
+    n, m = oracle.search_by_projection_map(**c, th=3.0)
+    hit = np.flatnonzero(m >= 0)
+    assert n > 150 and len(hit) <= n
+    assert not np.any(c["cur_taken"][hit])
+    assert np.all(c["flags"][m[hit]] & 1) and not np.any(c["flags"][m[hit]] & 4)
+    nfar, _ = oracle.search_by_projection_map(**c, th=3.0, far_points=True, th_far_points=20.0)
+    assert nfar < n  # far points are skipped

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from orb_slam3_ros2_b200 import synth
-from test_oracle_matcher_rows import make_grid_case, make_projection_case
+from test_oracle_matcher_rows import make_grid_case, make_local_points_case, make_projection_case
 
 
 @pytest.fixture(scope="module")
@@ -238,4 +238,17 @@ def test_search_by_projection_frame_frame_restatement_equals_reference_body(slic
         want = slices.ref_search_by_projection_ff(**dict(c, check_orientation=ori))
         got = slices.search_by_projection_ff(**dict(c, check_orientation=ori))
         assert got[0] == want[0] and np.array_equal(got[1], want[1]), (kw, ori, got[0], want[0])
+        assert want[0] > 50
+
+
+@pytest.mark.parametrize("kw,th,far", [(dict(k=0, seed=0), 3.0, False), (dict(k=1, seed=1, stereo=True), 3.0, False), (dict(k=2, seed=2, nf=2000, w=1241, h=376, stereo=True), 5.0, True),
+                                      (dict(k=3, seed=3, taken_frac=0.7), 1.0, False), (dict(k=4, seed=4, w=640, h=360, nf=1250), 15.0, True)])
+def test_search_by_projection_map_points_restatement_equals_reference_body(slices, kw, th, far):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) (ORBmatcher.cc:43-210, Tracking::SearchLocalPoints):
+    restatement == the reference's own body, for the ratios the reference uses (0.8 in SearchLocalPoints), th = 1 (no factor), 3, 5, 15."""
+    c = make_local_points_case(slices, **kw)
+    for nn in (0.8, 0.6, 0.9):
+        want = slices.ref_search_by_projection_map(**c, th=th, far_points=far, th_far_points=30.0, nnratio=nn)
+        got = slices.search_by_projection_map(**c, th=th, far_points=far, th_far_points=30.0, nnratio=nn)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1]), (kw, th, nn, got[0], want[0])
         assert want[0] > 50
