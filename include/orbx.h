@@ -192,6 +192,12 @@ int orbx_match_top2(const uint8_t* q, int nq, const uint8_t* db, int64_t nd, int
                     int64_t* idx2, int32_t* d2, int device);
 int orbx_match_top2_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t nd, int64_t db_index_base,
                            int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream);
+/* The matching entry points that take no handle (orbx_match_top2, _device, orbx_match_stereo_banded, orbx_accept_top2,
+ * orbx_search_*, orbx_compute_stereo_matches, ...) keep their device scratch and one CUDA stream PER CALLING THREAD.  Consequences:
+ * calls of one thread are serialised through that scratch - orbx_match_top2_device may only be given streams whose work is ordered
+ * with the thread's previous call (the same stream, or after a synchronisation) -, and a thread that is about to exit should call
+ * orbx_thread_cleanup() to release the scratch (it is not released automatically). */
+void orbx_thread_cleanup(void);
 
 /* Frame-to-frame top-2 over the last batch held by `h` (config 2): frame f's descriptors against frame
  * f+1's, f = 0..nframes-2.  Outputs are (nframes-1) x cap entries; to_host = 0: device pointers, results left on the

@@ -311,12 +311,13 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
 }  // namespace
 
 // per device, once per extractor (orbx_create)
-void uploadDescribeTables() {
+cudaError_t uploadDescribeTables() {
     static const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};  // ORBextractor.cc:453-468
     float4 pat[256];
     for (int i = 0; i < 256; ++i)
         pat[i] = make_float4((float)kOrbPattern[i][0], (float)kOrbPattern[i][1], (float)kOrbPattern[i][2], (float)kOrbPattern[i][3]);
-    cudaMemcpyToSymbol(gPatternF, pat, sizeof(pat));
+    cudaError_t e = cudaMemcpyToSymbol(gPatternF, pat, sizeof(pat));
+    if (e != cudaSuccess) return e;
     uint2 coef[248];
     for (int r = 0; r < 31; ++r)
         for (int k = 0; k < 8; ++k) {
@@ -332,7 +333,7 @@ void uploadDescribeTables() {
             }
             coef[r * 8 + k] = make_uint2(cu, cm);
         }
-    cudaMemcpyToSymbol(gIcCoef, coef, sizeof(coef));
+    return cudaMemcpyToSymbol(gIcCoef, coef, sizeof(coef));
 }
 
 void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s) {

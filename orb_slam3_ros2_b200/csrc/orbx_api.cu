@@ -545,10 +545,14 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
     for (int i = 0; i < 12 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e != cudaSuccess) {
-        delete h;
+        orbx_destroy(h);  // releases whatever streams / events were created
         return fail(ORBX_ERR_CUDA, std::string("stream/event creation: ") + cudaGetErrorString(e));
     }
-    uploadDescribeTables();
+    e = uploadDescribeTables();
+    if (e != cudaSuccess) {
+        orbx_destroy(h);
+        return fail(ORBX_ERR_CUDA, std::string("uploading the rBRIEF pattern / disc tables: ") + cudaGetErrorString(e));
+    }
     *out = h;
     return ORBX_OK;
 }
@@ -1015,7 +1019,23 @@ int orbx_synth_frames_device(uint8_t* d_out, int k0, int nframes, int w, int hgt
 // Matching
 // ======================================================================================================
 #include <dlfcn.h>
+// NCCL is loaded with dlopen (the extractor half must work on hosts without it), so the header is optional too: without it the few
+// types and enumerators the sharded entry points use are declared here as NCCL 2.x defines them (nccl.h: ncclUniqueId is 128 opaque
+// bytes, ncclComm_t an opaque pointer, ncclSuccess = 0, ncclUint64 = 5).
+#if defined(__has_include) && !defined(ORBX_NO_NCCL_H)
+#if __has_include(<nccl.h>)
 #include <nccl.h>
+#define ORBX_HAVE_NCCL_H 1
+#endif
+#endif
+#ifndef ORBX_HAVE_NCCL_H
+extern "C" {
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef enum { ncclSuccess = 0 } ncclResult_t;
+typedef enum { ncclInt8 = 0, ncclUint8 = 1, ncclInt32 = 2, ncclUint32 = 3, ncclInt64 = 4, ncclUint64 = 5 } ncclDataType_t;
+}
+#endif
 
 namespace orbx {
 
@@ -1043,6 +1063,20 @@ static int matchScratch(int device, MatchScratch** out) {
     *out = &S;
     return ORBX_OK;
 }
+
+}  // namespace orbx
+extern "C" void orbx_thread_cleanup(void) {
+    MatchScratch& S = tlsMatch;
+    if (S.device < 0) return;
+    DeviceGuard g(S.device);
+    if (S.stream) cudaStreamSynchronize(S.stream);
+    DevMem* all[] = {&S.q, &S.db, &S.k1, &S.k2, &S.i1, &S.i2, &S.d1, &S.d2, &S.misc};
+    for (DevMem* m : all) m->release();
+    if (S.stream) cudaStreamDestroy(S.stream);
+    S.stream = nullptr;
+    S.device = -1;
+}
+namespace orbx {
 
 static int smCount() {
     int dev = 0, sms = 148;
@@ -1217,6 +1251,9 @@ int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, 
                              float max_d, int32_t* best_idx, int32_t* best_dist, int device) {
     if (nl < 0 || nr < 0 || !scale_factors || nlevels < 1 || !best_idx || !best_dist) return fail(ORBX_ERR_ARG, "bad argument");
     if (nl == 0) return ORBX_OK;
+    // the kernel indexes scale_factors with the right keypoints' octaves (Frame.cc:831): reject what would read out of bounds
+    for (int i = 0; i < nr; ++i)
+        if (kps_r[i].octave < 0 || kps_r[i].octave >= nlevels) return fail(ORBX_ERR_ARG, "right keypoint octave outside [0, nlevels)");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();

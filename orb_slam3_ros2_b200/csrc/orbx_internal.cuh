@@ -221,7 +221,7 @@ void launchBowSearch(const uint8_t* descKF, const uint8_t* validKF, const float*
                      const int* kfFeatIdx, int kfNodes, const uint8_t* descF, int nF, const float* angleF, const int* fNodeIds,
                      const int* fNodeBegin, const int* fFeatIdx, int fNodes, float nnratio, int checkOrientation, int* matchF, int* binF,
                      int* nMatches, cudaStream_t s, const uint8_t* validF = nullptr, int strictLow = 0);
-void uploadDescribeTables();
+cudaError_t uploadDescribeTables();
 double benchPopcRate(cudaStream_t s);
 
 void countLaunch(int n = 1);

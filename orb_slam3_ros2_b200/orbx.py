@@ -98,6 +98,7 @@ SYMBOLS = {
     "orbx_search_by_bow_kf": (C.c_int, [_u8p, C.c_int, _u8p, _f32p, _i32p, _i32p, _i32p, C.c_int, _u8p, C.c_int, _u8p, _f32p, _i32p, _i32p,
                                         _i32p, C.c_int, C.c_float, C.c_int, _i32p, _i32p, C.c_int]),
     "orbx_capacity": (C.c_int, [_vp, C.c_int, C.c_int, _i32p]),
+    "orbx_thread_cleanup": (None, []),
     "orbx_search_by_projection_map": (C.c_int, [_vp, _i32p, _u8p, _u8p, _i32p, _vp, _u8p, _vp, _vp, _i32p, C.c_int, C.c_int, C.c_int, _vp,
                                                 C.c_float, C.c_int, C.c_float, _i32p, _i32p, C.c_int]),
     "orbx_search_by_projection": (C.c_int, [_vp, _u8p, _vp, _u8p, _i32p, _vp, _u8p, _vp, _vp, _i32p, _vp, C.c_int, C.c_int, C.c_int, _vp,
