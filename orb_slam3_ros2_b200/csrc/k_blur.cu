@@ -122,7 +122,17 @@ __global__ void __launch_bounds__(256) blurKernelLd(const __grid_constant__ Fram
 }
 
 
-template <bool ONEWAIT, bool REMAP>
+// horizontal 7-tap sums of 4 neighbouring pixels from three aligned words WITHOUT funnel shifts: pixel x+j taps bytes (j .. j+6) of the
+// 12-byte window, so each pixel is two or three dp4a against coefficient words that carry the shift (10 dp4a per 4 pixels instead of
+// 8 dp4a + 6 SHF: the shifts run on the ALU pipe, the dot products on the FMA pipe)
+__device__ __forceinline__ void hsum4(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t (&h)[4]) {
+    h[0] = __dp4a(w0, 0x38302212u, __dp4a(w1, 0x00122230u, 0u));
+    h[1] = __dp4a(w0, 0x30221200u, __dp4a(w1, 0x12223038u, 0u));
+    h[2] = __dp4a(w0, 0x22120000u, __dp4a(w1, 0x22303830u, __dp4a(w2, 0x00000012u, 0u)));
+    h[3] = __dp4a(w0, 0x12000000u, __dp4a(w1, 0x30383022u, __dp4a(w2, 0x00001222u, 0u)));
+}
+
+template <bool ONEWAIT, bool REMAP, bool NOSHIFT = false>
 __global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ FramePlan P, const __grid_constant__ LevelMaps M,
                                                   const uint32_t* __restrict__ tileTab, uint8_t* __restrict__ blur, int frame0) {
     __shared__ __align__(128) uint8_t sIn[kInRows * kInPitch];
@@ -165,6 +175,10 @@ __global__ void __launch_bounds__(256, 8) blurKernel(const __grid_constant__ Fra
         for (int rr = 0; rr < 2; ++rr) {
             const uint32_t* p = reinterpret_cast<const uint32_t*>(sIn + (2 * m + rr) * kInPitch) + g;
             const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+            if (NOSHIFT) {
+                hsum4(w0, w1, w2, h[rr]);
+                continue;
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const uint32_t a = j ? __funnelshift_r(w0, w1, 8 * j) : w0;
@@ -351,7 +365,8 @@ void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
         const int gridP = (int)std::min<long long>(total, (long long)sms * 8);
         blurPersistKernel<<<gridP, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0, P.blurTiles, (int)total);
     } else if (B.blurMaps) {
-        if (mode == 3) blurKernel<true, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
+        if (mode == 5) blurKernel<true, false, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
+        else if (mode == 3) blurKernel<true, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
         else if (mode == 2) blurKernel<false, true><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
         else if (mode == 1) blurKernel<true, false><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);
         else blurKernel<false, false><<<grid, 256, 0, s>>>(P, M, B.blurTab, B.blur, B.frame0);

@@ -90,11 +90,13 @@ __host__ __device__ inline StripLayout stripLayout(int rowsMax, int pitchMax, in
     return s;
 }
 
-template <int NT>
+// FMAQ: the quick test's per-byte threshold adds and its mask packing as integer multiply-adds (IMAD, FMA pipe) instead of IADD / LEA /
+// SHF (ALU pipe, the busier one: 56 % against 14 %); `one` is a kernel argument (= 1) so that the compiler keeps the multiply.
+template <int NT, bool FMAQ>
 __global__ void __launch_bounds__(NT)
     fastStripKernel(const __grid_constant__ LevelMaps M, const StripDesc* __restrict__ stripTab, uint32_t* __restrict__ cand,
                     int* __restrict__ cellCnt, unsigned long long* __restrict__ fbList, int* __restrict__ fbCount, int fbCap,
-                    int candWords, int nCellsTotal, int tIni, int tMin, int rowsMax, int pitchMax, int frame0, int kListCap) {
+                    int candWords, int nCellsTotal, int tIni, int tMin, int rowsMax, int pitchMax, int frame0, int kListCap, uint32_t one) {
     const int kCornerCap = kListCap * 3 / 8;
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -176,10 +178,18 @@ __global__ void __launch_bounds__(NT)
                 const uint32_t rt = __byte_perm(ce, cw4[k + 2], 0x6543);  // pixels x+3 .. x+6
                 const uint32_t d0 = __vabsdiffu4(uw[k], ce), d8 = __vabsdiffu4(dw4[k], ce);
                 const uint32_t d4 = __vabsdiffu4(rt, ce), d12 = __vabsdiffu4(lf, ce);
+                if (FMAQ) {
+                    const uint32_t v = (((d0 & 0x7f7f7f7fu) * one + K) | d0) | (((d8 & 0x7f7f7f7fu) * one + K) | d8);
+                    const uint32_t h = (((d4 & 0x7f7f7f7fu) * one + K) | d4) | (((d12 & 0x7f7f7f7fu) * one + K) | d12);
+                    const uint32_t F = v & h & 0x80808080u;
+                    // flags at bits 7, 15, 23, 31 -> bits 28 .. 31: F * (2^21 + 2^14 + 2^7 + 1); the cross terms stay below bit 24
+                    m = ((F * 0x00204081u) >> 28) * (one << (4 * k)) + m;
+                } else {
                 const uint32_t v = (((d0 & 0x7f7f7f7fu) + K) | d0) | (((d8 & 0x7f7f7f7fu) + K) | d8);
                 const uint32_t h = (((d4 & 0x7f7f7f7fu) + K) | d4) | (((d12 & 0x7f7f7f7fu) + K) | d12);
                 const uint32_t F = v & h & 0x80808080u;
                 m |= (((F >> 7) * 0x01020408u) >> 24) << (4 * k);  // bit 4k+j = pixel 4k+j of the chunk
+                }
             }
             const int x0 = cx << 4;
             const int lo = min(max(rxa - x0, 0), 16), hi = min(max(rxb - x0, 0), 16);
@@ -472,15 +482,15 @@ int buildStripMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, vo
     return 0;
 }
 
-template <int NT>
+template <int NT, bool FMAQ>
 static void launchStripT(const FramePlan& P, const Buffers& B, int F, int rowsMax, int pitchMax, cudaStream_t s, int tile0, int nTiles) {
     const StripLayout lay = stripLayout(rowsMax, pitchMax, stripListCap());
-    auto kern = fastStripKernel<NT>;
+    auto kern = fastStripKernel<NT, FMAQ>;
     if (lay.total > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, lay.total);
     kern<<<dim3(nTiles, F), NT, lay.total, s>>>(*reinterpret_cast<const LevelMaps*>(B.stripMaps),
                                                      reinterpret_cast<const StripDesc*>(B.stripTab) + tile0, B.cand, B.cellCnt, B.fbList, B.fbCount,
                                                      B.fbCap, (int)P.candWords, P.nCellsTotal, std::max(P.iniTh, 1), std::max(P.minTh, 1),
-                                                     rowsMax, pitchMax, B.frame0, stripListCap());
+                                                     rowsMax, pitchMax, B.frame0, stripListCap(), 1u);
     countLaunch();
 }
 
@@ -502,8 +512,10 @@ void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t 
     const int tile0 = part == 1 ? upper : 0;
     const int nTiles = part == 0 ? P.stripTiles : (part == 1 ? P.stripTiles - upper : (part == 2 ? upper : 0));  // parts 3, 4: none
     if (nTiles > 0) {
-        if (stripThreads() == 256) launchStripT<256>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
-        else launchStripT<128>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        static const bool fmaq = [] { const char* e = std::getenv("ORBX_STRIP_FMAQ"); return e && e[0] == '1'; }();
+        if (stripThreads() == 256) launchStripT<256, false>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else if (fmaq) launchStripT<128, true>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else launchStripT<128, false>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
     }
     if (part == 0 || part == 3) launchFastFallback(P, B, F, B.fbList, B.fbCount, B.fbCap, s);
 }
