@@ -11,7 +11,7 @@
 // (y' / hCell, x' / wCell).  The per-cell kernel (k_fast.cu, one warp per 35-px cell) spends most of its instructions on
 // per-cell fixed costs and on 16-byte chunks that straddle its 42-px tile (measured 1.49 warp-instructions per level
 // pixel, the byte-SIMD quick test itself being 0.25).  Here one CTA owns a strip = several neighbouring cells of one cell
-// row (up to 235 tested columns, one TMA box), so
+// row (up to 150 tested columns = 4 cells at the usual 36-px cells, one TMA box; up to 235 columns fit a box), so
 //   * the quick test walks dense rows of 16-byte chunks (94 % of the lanes' pixels are tested pixels, was 56-75 %);
 //   * the flagged pixels of the whole strip go to ONE list (order-free, shared-memory atomics) and the exact arc strength is
 //     computed with every lane busy (was: per-cell lists of ~130 pixels in 64-pixel trips);
@@ -36,12 +36,18 @@
 namespace orbx {
 namespace {
 
+// Strip geometry and occupancy (measured, FAST stage ms / frames per s of the whole step; extra shared memory per CTA shows the
+// sensitivity: 6 resident CTAs per SM 0.459 ms, 5 0.516, 4 0.518, 3 0.623, 2 0.846):
+//   235 columns, 4096-entry list, 64 registers (6 CTAs / SM)   0.459-0.465 / 158.4 k
+//   150 columns, 2560-entry list, 48 registers (9 CTAs / SM)   0.439 / 160.1 k        <- default
+//   150 columns, 2048-entry list, 48 registers                 0.445 / 161.4 k
+//   115 columns, 2048-entry list, 48 / 40 registers            0.473 / 0.498 (more strips: more fixed cost, small-level strips overflow)
 // flagged pixels per strip (u16 entries: tile row << 8 | tile x) and corners per strip (3/8 of that): ORBX_STRIP_LIST
 static int stripListCap() {
     static const int v = [] {
         const char* e = std::getenv("ORBX_STRIP_LIST");
         const int n = e ? std::atoi(e) : 0;
-        return n >= 256 && n <= 16384 ? (n & ~63) : 4096;
+        return n >= 256 && n <= 16384 ? (n & ~63) : 2560;
     }();
     return v;
 }
@@ -50,7 +56,7 @@ static int stripMaxWidth() {
     static const int v = [] {
         const char* e = std::getenv("ORBX_STRIP_MAXW");
         const int n = e ? std::atoi(e) : 0;
-        return n >= 16 && n <= 235 ? n : 235;
+        return n >= 16 && n <= 235 ? n : 150;
     }();
     return v;
 }
@@ -92,8 +98,8 @@ __host__ __device__ inline StripLayout stripLayout(int rowsMax, int pitchMax, in
 
 // FMAQ: the quick test's per-byte threshold adds and its mask packing as integer multiply-adds (IMAD, FMA pipe) instead of IADD / LEA /
 // SHF (ALU pipe, the busier one: 56 % against 14 %); `one` is a kernel argument (= 1) so that the compiler keeps the multiply.
-template <int NT, bool FMAQ>
-__global__ void __launch_bounds__(NT)
+template <int NT, bool FMAQ, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
     fastStripKernel(const __grid_constant__ LevelMaps M, const StripDesc* __restrict__ stripTab, uint32_t* __restrict__ cand,
                     int* __restrict__ cellCnt, unsigned long long* __restrict__ fbList, int* __restrict__ fbCount, int fbCap,
                     int candWords, int nCellsTotal, int tIni, int tMin, int rowsMax, int pitchMax, int frame0, int kListCap, uint32_t one) {
@@ -482,10 +488,13 @@ int buildStripMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, vo
     return 0;
 }
 
-template <int NT, bool FMAQ>
+template <int NT, bool FMAQ, int MINB>
 static void launchStripT(const FramePlan& P, const Buffers& B, int F, int rowsMax, int pitchMax, cudaStream_t s, int tile0, int nTiles) {
-    const StripLayout lay = stripLayout(rowsMax, pitchMax, stripListCap());
-    auto kern = fastStripKernel<NT, FMAQ>;
+    StripLayout lay = stripLayout(rowsMax, pitchMax, stripListCap());
+    // ORBX_STRIP_PAD_KB (measurements only): extra dynamic shared memory per CTA = fewer resident CTAs per SM (occupancy sensitivity)
+    static const int padKb = [] { const char* e = std::getenv("ORBX_STRIP_PAD_KB"); return e ? std::atoi(e) : 0; }();
+    lay.total += padKb * 1024;
+    auto kern = fastStripKernel<NT, FMAQ, MINB>;
     if (lay.total > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, lay.total);
     kern<<<dim3(nTiles, F), NT, lay.total, s>>>(*reinterpret_cast<const LevelMaps*>(B.stripMaps),
                                                      reinterpret_cast<const StripDesc*>(B.stripTab) + tile0, B.cand, B.cellCnt, B.fbList, B.fbCount,
@@ -513,9 +522,13 @@ void launchFastStrips(const FramePlan& P, const Buffers& B, int F, cudaStream_t 
     const int nTiles = part == 0 ? P.stripTiles : (part == 1 ? P.stripTiles - upper : (part == 2 ? upper : 0));  // parts 3, 4: none
     if (nTiles > 0) {
         static const bool fmaq = [] { const char* e = std::getenv("ORBX_STRIP_FMAQ"); return e && e[0] == '1'; }();
-        if (stripThreads() == 256) launchStripT<256, false>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
-        else if (fmaq) launchStripT<128, true>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
-        else launchStripT<128, false>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        // ORBX_STRIP_MINB: resident CTAs per SM the register allocation aims at (8 = 64 registers, 10 = 48, 12 = 40 with 44 bytes of spills)
+        static const int minb = [] { const char* e = std::getenv("ORBX_STRIP_MINB"); return e ? std::atoi(e) : 10; }();
+        if (stripThreads() == 256) launchStripT<256, false, 4>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else if (fmaq) launchStripT<128, true, 8>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else if (minb >= 12) launchStripT<128, false, 12>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else if (minb >= 10) launchStripT<128, false, 10>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
+        else launchStripT<128, false, 8>(P, B, F, rowsMax, pitchMax, s, tile0, nTiles);
     }
     if (part == 0 || part == 3) launchFastFallback(P, B, F, B.fbList, B.fbCount, B.fbCap, s);
 }

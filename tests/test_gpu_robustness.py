@@ -14,7 +14,8 @@ from conftest import ROOT
 
 pytestmark = pytest.mark.gpu
 
-ENVS = [{}, {"ORBX_STRIP_THREADS": "256"}, {"ORBX_STRIP_LIST": "256"}, {"ORBX_FAST_STRIP": "0"}, {"ORBX_FAST_TMA": "0"},
+ENVS = [{}, {"ORBX_STRIP_THREADS": "256"}, {"ORBX_STRIP_LIST": "256"}, {"ORBX_STRIP_MAXW": "235", "ORBX_STRIP_LIST": "4096", "ORBX_STRIP_MINB": "8"},
+        {"ORBX_STRIP_MINB": "12", "ORBX_STRIP_MAXW": "75"}, {"ORBX_FAST_STRIP": "0"}, {"ORBX_FAST_TMA": "0"},
         {"ORBX_MATCH_R": "0"}, {"ORBX_BLUR_MODE": "3"}]
 
 
