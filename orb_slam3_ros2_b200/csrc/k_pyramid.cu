@@ -14,6 +14,7 @@
 // columns (a thread keeps the coefficients of its 4 columns in registers), and the vertical pass blends two such
 // rows per output row.  ~18 instructions per output pixel instead of ~80 for the direct per-pixel form.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "orbx_internal.cuh"
@@ -365,7 +366,10 @@ static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cu
     const LevelPlan& D = P.lv[l];
     const int pw = D.w + 2 * kEdge, ph = D.h + 2 * kEdge;
     const int maxRows = pyrMaxRows(S, D);
-    const size_t smem = TMA ? 2 * (size_t)((maxRows * SPT + 127) & ~127) + (size_t)maxRows * kTW * 4 : (size_t)maxRows * (SPT + kTW * 4);
+    size_t smem = TMA ? 2 * (size_t)((maxRows * SPT + 127) & ~127) + (size_t)maxRows * kTW * 4 : (size_t)maxRows * (SPT + kTW * 4);
+    // ORBX_PYR_PAD_KB (measurements only): extra dynamic shared memory per CTA = fewer resident CTAs per SM (occupancy sensitivity)
+    static const int padKb = [] { const char* e = std::getenv("ORBX_PYR_PAD_KB"); return e ? std::atoi(e) : 0; }();
+    smem += (size_t)padKb * 1024;
     auto kern = pyrResizeKernel<SPT, WINDOWED, TMA>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((pw + kTW - 1) / kTW, ((ph + kTH - 1) / kTH + kRowTiles - 1) / kRowTiles, F);
