@@ -547,6 +547,43 @@ def search_for_initialization_batch(extractor, bounds, window_size=100, nnratio=
     return n[:F - 1], m12[:F - 1], prev[:F - 1]
 
 
+class FrameLevel(C.Structure):
+    _fields_ = [("w", C.c_int), ("h", C.c_int), ("pitch", C.c_int), ("offset", C.c_uint)]
+
+
+class FrameResult(C.Structure):
+    """orbx_frame_result (include/orbx.h)."""
+    _fields_ = [("kps", _vp), ("desc", _vp), ("n", C.c_int), ("mono_index", C.c_int), ("pyramid", _vp), ("nlevels", C.c_int),
+                ("level", FrameLevel * 16)]
+
+
+def extract_frame(extractor, image, vLappingArea=(0, 1000), pyramid=True):
+    """orbx_extract_frame: operator() with one host synchronisation (the call compat/ORBextractor.cc makes).
+    -> (monoIndex, keypoints, descriptors, [padded planes] or None); the arrays are copies of the handle's staging buffer."""
+    r = FrameResult()
+    if image is None or image.size == 0:
+        _check(lib().orbx_extract_frame(extractor._h, None, 0, 0, 0, vLappingArea[0], vLappingArea[1], 1 if pyramid else 0, C.byref(r)))
+        return r.mono_index, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8), None
+    assert image.dtype == np.uint8 and image.ndim == 2
+    if image.strides[1] != 1:
+        image = np.ascontiguousarray(image)
+    h, w = image.shape
+    _check(lib().orbx_extract_frame(extractor._h, C.cast(image.ctypes.data, _u8p), w, h, image.strides[0], vLappingArea[0], vLappingArea[1],
+                                    1 if pyramid else 0, C.byref(r)))
+    extractor._frames = 1
+    n = r.n
+    kps = np.frombuffer((C.c_char * (n * 28)).from_address(r.kps), dtype=KP_DTYPE).copy() if n else np.zeros(0, KP_DTYPE)
+    desc = np.frombuffer((C.c_char * (n * 32)).from_address(r.desc), dtype=np.uint8).reshape(n, 32).copy() if n else np.zeros((0, 32), np.uint8)
+    planes = None
+    if pyramid and r.pyramid:
+        planes = []
+        for l in range(r.nlevels):
+            L = r.level[l]
+            raw = np.frombuffer((C.c_char * (L.pitch * (L.h + 38))).from_address(r.pyramid + L.offset), dtype=np.uint8)
+            planes.append(raw.reshape(L.h + 38, L.pitch)[:, :L.w + 38].copy())
+    return r.mono_index, kps, desc, planes
+
+
 class ProjParams(C.Structure):
     """orbx_proj_params (include/orbx.h)."""
     _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float),

@@ -193,3 +193,25 @@ def test_small_nfeatures_match_reference(orbx, oracle, w, h, nf):
     DistributeOctTree splits every root, ORBextractor.cc:610-681): capacity max(N + 4, 4 * nIni + 1) per level."""
     n = _vs(orbx, oracle, synth.frame(7, w, h), nf, (0, 1000))
     assert n >= nf
+
+
+def test_extract_frame_one_sync_path_equals_extract(orbx):
+    """orbx_extract_frame (the call the C++ drop-in class makes: results and the padded pyramid through one pinned staging buffer, one
+    host synchronisation) returns exactly what orbx_extract + orbx_get_pyramid return; an empty image gives -1."""
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    for k, (w, h), lap in ((0, (752, 480), (0, 1000)), (3, (640, 360), (0, 0)), (5, (700, 500), (300, 600))):
+        im = synth.frame(k, w, h)
+        view = np.zeros((h, w + 24), np.uint8)  # a strided view: stride != width
+        view[:, :w] = im
+        mono, kp, desc = ex(im, None, lap)
+        planes = [ex.pyramid_level(0, l) for l in range(8)]
+        for src in (im, view[:, :w]):
+            m2, k2, d2, p2 = orbx.extract_frame(ex, src, lap, pyramid=True)
+            assert m2 == mono
+            _same(k2, kp, "keypoints")
+            _same(d2, desc, "descriptors")
+            assert all(np.array_equal(a, b) for a, b in zip(p2, planes))
+        m3, k3, d3, p3 = orbx.extract_frame(ex, im, lap, pyramid=False)
+        assert m3 == mono and p3 is None and np.array_equal(k3, kp) and np.array_equal(d3, desc)
+    assert orbx.extract_frame(ex, None)[0] == -1
+    ex.close()
