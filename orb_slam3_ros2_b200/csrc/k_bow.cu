@@ -338,7 +338,7 @@ void launchBowTransform(const BowVocDev& V, const uint8_t* dDesc, const int* dN,
     int n2 = 32;
     while (n2 < cap) n2 <<= 1;
     const size_t smem = (size_t)n2 * sizeof(uint64_t);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(bowCollectKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(bowCollectKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     bowCollectKernel<<<F, 512, smem, s>>>(V, dN, cap, n2, leaf, nid, wordIds, wordVals, nWords, nodeIds, nodeBegin, featIdx, nNodes);
     countLaunch(2);
 }

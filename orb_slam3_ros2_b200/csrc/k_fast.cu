@@ -390,7 +390,7 @@ void launchClass(const FramePlan& P, const Buffers& B, int F, unsigned mask, int
     const FastGeom g = geomFor(P, mask, PITCH, TMA ? 48 : PITCH);
     const size_t smem = (size_t)g.warpBytes * kWarpsPerCta + 8 * kWarpsPerCta;  // + one mbarrier per warp
     auto kern = fastCellsKernel<PITCH, SHIFTED, TMA>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int dev = 0, sms = 148, perSm = 1;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -418,7 +418,7 @@ void launchClassList(const FramePlan& P, const Buffers& B, unsigned mask, const 
     const FastGeom g = geomFor(P, mask, PITCH, TMA ? 48 : PITCH);
     const size_t smem = (size_t)g.warpBytes * kWarpsPerCta + 8 * kWarpsPerCta;
     auto kern = fastCellsKernel<PITCH, SHIFTED, TMA>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -495,7 +495,7 @@ static void launchStripT(const FramePlan& P, const Buffers& B, int F, int rowsMa
     static const int padKb = [] { const char* e = std::getenv("ORBX_STRIP_PAD_KB"); return e ? std::atoi(e) : 0; }();
     lay.total += padKb * 1024;
     auto kern = fastStripKernel<NT, FMAQ, MINB>;
-    if (lay.total > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, lay.total);
+    if (lay.total > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, lay.total);
     kern<<<dim3(nTiles, F), NT, lay.total, s>>>(*reinterpret_cast<const LevelMaps*>(B.stripMaps),
                                                      reinterpret_cast<const StripDesc*>(B.stripTab) + tile0, B.cand, B.cellCnt, B.fbList, B.fbCount,
                                                      B.fbCap, (int)P.candWords, P.nCellsTotal, std::max(P.iniTh, 1), std::max(P.minTh, 1),

@@ -648,7 +648,7 @@ void launchGridSortBatch(const void* kps, const int* nPerFrame, int frames, int 
     int nPow2 = 32;
     while (nPow2 < cap) nPow2 <<= 1;
     const size_t smem = (size_t)nPow2 * 4;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     gridSortKernel<<<frames, 1024, smem, s>>>(static_cast<const float*>(kps), 0, nPow2, minX, minY, invW, invH, sorted, cellStart,
                                               nPerFrame, cap);
     countLaunch();
@@ -662,7 +662,7 @@ void launchGridSearch(const void* kpsT, const uint8_t* descT, int nt, float minX
     int nPow2 = 32;
     while (nPow2 < nt) nPow2 <<= 1;
     const size_t smem = (size_t)nPow2 * 4;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     gridSortKernel<<<1, 1024, smem, s>>>(static_cast<const float*>(kpsT), nt, nPow2, minX, minY, invW, invH, sortedScratch, cellStart,
                                          nullptr, 0);
     countLaunch();
@@ -717,7 +717,7 @@ void launchSearchInit(const void* kps1, const uint8_t* desc1, int n1, const void
     int nPow2 = 32;
     while (nPow2 < (batch ? cap : n2)) nPow2 <<= 1;
     const size_t smem = (size_t)nPow2 * 4;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(gridSortKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const int pairs = batch ? frames - 1 : 1;
     if (pairs <= 0) return;
     InitArgs A{};

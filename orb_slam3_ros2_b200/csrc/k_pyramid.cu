@@ -371,7 +371,9 @@ static void launchResizeT(const FramePlan& P, const Buffers& B, int l, int F, cu
     static const int padKb = [] { const char* e = std::getenv("ORBX_PYR_PAD_KB"); return e ? std::atoi(e) : 0; }();
     smem += (size_t)padKb * 1024;
     auto kern = pyrResizeKernel<SPT, WINDOWED, TMA>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // the opt-in is needed as soon as dynamic + STATIC shared memory pass 48 KB (the kernel has ~1.2 KB of static arrays: exactly
+    // 48 KB of dynamic memory - 606 x 177 at scale 1.4 - used to fail the launch with "invalid argument"), hence the margin
+    if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((pw + kTW - 1) / kTW, ((ph + kTH - 1) / kTH + kRowTiles - 1) / kRowTiles, F);
     static const CUtensorMap kNoMap{};
     const CUtensorMap& map = TMA ? reinterpret_cast<const LevelMaps*>(B.pyrMaps)->m[l] : kNoMap;

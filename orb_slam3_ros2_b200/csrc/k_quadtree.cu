@@ -478,7 +478,7 @@ size_t quadtreeSmemBytes(const FramePlan& P) { return qtSmem(qtNodeCap(P), qtMax
 
 template <int QT>
 static void launchQuadtreeT(const FramePlan& P, const Buffers& B, int F, int NC, int maxCells, size_t smem, cudaStream_t s) {
-    if (smem > 48 * 1024) cudaFuncSetAttribute(quadtreeKernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 40 * 1024) cudaFuncSetAttribute(quadtreeKernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     // ORBX_QT_ORDER=0: the round-1 grid (levels, frames) for A/B runs
     static const int levelMajor = [] { const char* e = std::getenv("ORBX_QT_ORDER"); return e ? std::atoi(e) : 1; }();
     const dim3 grid = levelMajor ? dim3(F, P.nlevels) : dim3(P.nlevels, F);

@@ -471,6 +471,7 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
         launchBlur(P, B, F, x);
         cudaEventRecord(h->ev[8], x);
     }
+    ORBX_CUDA(cudaGetLastError());  // a failed launch of the pyramid / FAST / blur stages is reported as such, not carried further
     launchQuadtree(P, B, F, s);
     cudaEventRecord(h->ev[3], s);
     cudaStreamWaitEvent(s, h->ev[8], 0);  // join

@@ -215,3 +215,29 @@ def test_extract_frame_one_sync_path_equals_extract(orbx):
         assert m3 == mono and p3 is None and np.array_equal(k3, kp) and np.array_equal(d3, desc)
     assert orbx.extract_frame(ex, None)[0] == -1
     ex.close()
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_random_geometry_sweep_matches_reference(orbx, oracle, seed):
+    """Random frame sizes (cell widths from 35 to 69 px, clipped last cells, levels smaller than one cell), feature counts, thresholds,
+    scale factors, level counts and contents (texture, texture + noise, low contrast): every strip / cell geometry the FAST kernels can
+    meet, against the reference.  Shapes keep round(width / height) >= 1 on every level (below that the reference indexes an empty vector)."""
+    rng = np.random.default_rng(1000 + seed)
+    h = int(rng.integers(70, 600))
+    w = int(rng.integers(max(h, 90), 1000))
+    levels = int(rng.integers(1, 11))
+    scale = float(rng.choice([1.1, 1.2, 1.25, 1.4, 1.7]))
+    while levels > 1 and h / scale ** (levels - 1) < 48:  # a level of <= 32 rows makes the REFERENCE resize a vector to a negative size
+        levels -= 1
+    nf = int(rng.choice([60, 300, 1000, 2500]))
+    ini = int(rng.integers(5, 60))
+    mn = int(rng.integers(2, ini + 1))
+    im = synth.frame(seed, w, h).astype(np.int32)
+    kind = seed % 3
+    if kind == 1:
+        im = im + rng.integers(-25, 26, im.shape)
+    elif kind == 2:
+        im = (im - 128) // 4 + 128
+    im = np.clip(im, 0, 255).astype(np.uint8)
+    lap = [(0, 1000), (0, 0), (w // 3, 2 * w // 3)][seed % 3]
+    _vs(orbx, oracle, im, nf, lap, mode="native" if seed % 4 == 3 else "strict", ini=ini, mn=mn, scale=scale, levels=levels)

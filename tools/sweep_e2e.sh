@@ -1,8 +1,7 @@
 #!/bin/bash
-# e2e leg sweep (measurements only): sub-batches x handles x generations in flight.  usage (GPU box): bash tools/sweep_e2e.sh
-for sb in ${SB:-1}; do for h in ${HS:-1 2 3}; do for d in ${DS:-2 3 4}; do
-  echo -n "subbatches $sb handles $h depth $d -> "
-  python bench.py --only-e2e --steps 30 --warmup 3 --subbatches $sb --e2e-handles $h --e2e-depth $d 2>/dev/null | python -c "
+# e2e leg (host buffers) over handles x generations in flight; one line per setting
+for hd in "1 2" "1 3" "1 4" "1 5" "2 2" "2 3" "2 4" "3 3"; do set -- $hd
+  python bench.py --only-e2e --steps 20 --warmup 3 --sustained-s 0 --e2e-handles $1 --e2e-depth $2 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); e=d.get('e2e',d); print(round(e['value']))"
-done; done; done
+d=json.loads(sys.stdin.read()); print('handles $1 depth $2: e2e', round(d['e2e']['value']), 'bound', round(d['e2e']['host_bound_frames_per_s'] or 0), 'value', round(d['value']))"
+done
