@@ -217,9 +217,9 @@ def test_extract_frame_one_sync_path_equals_extract(orbx):
     ex.close()
 
 
-@pytest.mark.parametrize("seed", range(16))
+@pytest.mark.parametrize("seed", range(64))
 def test_random_geometry_sweep_matches_reference(orbx, oracle, seed):
-    """Random frame sizes (cell widths from 35 to 69 px, clipped last cells, levels smaller than one cell), feature counts, thresholds,
+    """Random frame sizes (64 configurations; cell widths from 35 to 69 px, clipped last cells, levels smaller than one cell), feature counts, thresholds,
     scale factors, level counts and contents (texture, texture + noise, low contrast): every strip / cell geometry the FAST kernels can
     meet, against the reference.  Shapes keep round(width / height) >= 1 on every level (below that the reference indexes an empty vector)."""
     rng = np.random.default_rng(1000 + seed)
