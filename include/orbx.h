@@ -199,6 +199,19 @@ int orbx_match_top2_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int6
  * orbx_thread_cleanup() to release the scratch (it is not released automatically). */
 void orbx_thread_cleanup(void);
 
+/* orbx_match_top2_device for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same arguments, same
+ * kernels and bit-identical results as orbx_match_top2_device; it calls no cudaMalloc / cudaFree / allocating routine and creates
+ * no stream - the per-chunk partial keys go to a file-scope device array of 2 x ORBX_NOALLOC_MAX_KEYS x 8 B = 16 MiB that every
+ * GPU loading the library holds until exit.  Limit: nq x (database chunks) <= ORBX_NOALLOC_MAX_KEYS, else ORBX_ERR_CAPACITY with a
+ * message naming the sizes (on a 148-SM B200 every nq <= 32768 with nd <= 100 M rows fits: the chunk count is about 592 / ceil(nq /
+ * 1024)).  All calls on one GPU share the array, from every thread and stream: calls that overlap on the GPU race - order them on
+ * one stream or with events.  The array keeps the last call's keys; nothing in it has to start cleared (every slot read is
+ * written first by the same call).  The work is only enqueued on `stream` (a cudaStream_t, may be 0); the current device is used. */
+#define ORBX_NOALLOC_MAX_KEYS (1u << 20)
+int orbx_match_top2_device_noalloc(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t nd, int64_t db_index_base,
+                                   int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream);
+
 /* Frame-to-frame top-2 over the last batch held by `h` (config 2): frame f's descriptors against frame
  * f+1's, f = 0..nframes-2.  Outputs are (nframes-1) x cap entries; to_host = 0: device pointers, results left on the
  * stream; 1: host pointers, synchronous; 2: host pointers, copies only enqueued (see orbx_extract_batch_async). */

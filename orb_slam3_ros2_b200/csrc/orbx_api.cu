@@ -2169,3 +2169,65 @@ static int shardedEnqueue(orbx_comm c, const uint8_t* d_q, int nq, const uint8_t
 }
 
 }  // extern "C"
+
+// ---- orbx_match_top2_device_noalloc: the top-2 matcher for callers that may not allocate ------------------------------------
+// No counterpart in the reference; added (CUDA graph capture, tight serving loops and
+// harnesses that forbid cudaMalloc).  Same kernels as orbx_match_top2_device (matchKernel<4> + mergeKernel); the per-chunk
+// partial keys live in a file-scope device array instead of the per-thread DevMem scratch.  2 x 2^20 keys x 8 B = 16 MiB per
+// GPU that loads the library, held until exit.  Every call shares the array: calls that overlap on the GPU race.
+// matchKernel writes every [chunk][query < nq] slot mergeKernel reads (k_match.cu:106-115), so nothing has to start cleared;
+// the nd = 0 case fills the first nq slots with the "no key" value itself.
+namespace orbx {
+constexpr size_t kNoAllocKeys = ORBX_NOALLOC_MAX_KEYS;
+static __device__ __align__(256) unsigned long long gNoAllocKeys[2 * kNoAllocKeys];
+
+constexpr int kNoAllocMaxDevices = 64;
+static uint64_t* gNoAllocPtr[kNoAllocMaxDevices];  // device address of gNoAllocKeys per device (the symbol itself is a host-side stand-in)
+static std::mutex gNoAllocMutex;
+
+// once per device, with that device current
+static int noAllocScratch(int dev, uint64_t** out) {
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(ORBX_ERR_ARG, "device ordinal beyond the no-alloc table");
+    std::lock_guard<std::mutex> lock(gNoAllocMutex);
+    if (!gNoAllocPtr[dev]) {
+        void* p = nullptr;
+        ORBX_CUDA(cudaGetSymbolAddress(&p, gNoAllocKeys));
+        if (!p) return fail(ORBX_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        gNoAllocPtr[dev] = (uint64_t*)p;
+    }
+    *out = gNoAllocPtr[dev];
+    return ORBX_OK;
+}
+}  // namespace orbx
+
+extern "C" int orbx_match_top2_device_noalloc(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t nd, int64_t db_index_base,
+                                              int64_t* d_idx1, int32_t* d_d1, int64_t* d_idx2, int32_t* d_d2, void* stream) {
+    if (nq < 0 || nd < 0 || (nq > 0 && !d_q) || (nd > 0 && !d_db)) return fail(ORBX_ERR_ARG, "bad argument");
+    if (nq == 0) return ORBX_OK;
+    if (!d_idx1 || !d_d1 || !d_idx2 || !d_d2) return fail(ORBX_ERR_ARG, "bad argument");
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    const int chunks = nd > 0 ? matchNumChunks(nq, nd, smCount()) : 0;
+    const size_t need = (size_t)std::max(chunks, 1) * (size_t)nq;
+    if (need > kNoAllocKeys) {
+        char msg[192];
+        std::snprintf(msg, sizeof msg, "orbx_match_top2_device_noalloc: nq (%d) x database chunks (%d) = %zu partial keys exceeds "
+                      "ORBX_NOALLOC_MAX_KEYS (%zu); use orbx_match_top2_device", nq, chunks, need, kNoAllocKeys);
+        return fail(ORBX_ERR_CAPACITY, msg);
+    }
+    uint64_t* keys = nullptr;
+    const int rc = noAllocScratch(dev, &keys);
+    if (rc != ORBX_OK) return rc;
+    uint64_t *k1 = keys, *k2 = keys + kNoAllocKeys;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (chunks == 0) {
+        ORBX_CUDA(cudaMemsetAsync(k1, 0xff, (size_t)nq * 8, s));
+        ORBX_CUDA(cudaMemsetAsync(k2, 0xff, (size_t)nq * 8, s));
+    } else {
+        launchMatchTop2(d_q, nq, d_db, nd, db_index_base, k1, k2, s);
+        ORBX_CUDA(cudaGetLastError());
+    }
+    launchUnpackTop2(k1, k2, std::max(chunks, 1), nq, d_idx1, d_d1, d_idx2, d_d2, s);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}

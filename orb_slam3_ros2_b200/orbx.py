@@ -76,6 +76,7 @@ SYMBOLS = {
     "orbx_hamming": (C.c_int, [_u8p, _u8p]),
     "orbx_match_top2": (C.c_int, [_u8p, C.c_int, _u8p, C.c_int64, _i64p, _i32p, _i64p, _i32p, C.c_int]),
     "orbx_match_top2_device": (C.c_int, [_vp, C.c_int, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_match_top2_device_noalloc": (C.c_int, [_vp, C.c_int, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     "orbx_match_batch_consecutive": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int]),
     "orbx_match_stereo_banded": (C.c_int, [_vp, _u8p, C.c_int, _vp, _u8p, C.c_int, _f32p, C.c_int, C.c_int, C.c_float,
                                            _i32p, _i32p, C.c_int]),
