@@ -14,6 +14,7 @@
 #include <cstdlib>
 
 #include "orbx_internal.cuh"
+#include "tma.cuh"
 
 namespace orbx {
 namespace {
@@ -308,6 +309,215 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __gr
     }  // persistent loop
 }
 
+
+// ---- describeAsyncKernel (round 2, default): the same arithmetic, software-pipelined with cp.async ---------------------------
+// describeKernel's first stall reason is long_scoreboard: every warp starts a keypoint with 21 global loads and waits for them.
+// Here both patches of the NEXT keypoint are copied global -> shared memory by cp.async while the current one is computed: the
+// orientation patch (31 rows x 3 sixteen-byte chunks of the padded plane) is requested as soon as IC_Angle has read the current
+// one, the blurred 37 x 37 patch as soon as the 512 samples are taken; one buffer of each per warp, two commit groups in flight.
+constexpr int kIcPitch = 48;  // 3 chunks: (px & 15 rounded down to a word) + 36 bytes <= 48
+__device__ __forceinline__ void cpAsync16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cpAsyncWait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// BULK: one cp.async.bulk per patch ROW (lane r copies row r; completion on a per-warp mbarrier) instead of one cp.async per
+// 16-byte chunk: 3 copy instructions per lane and keypoint instead of 8, and one address multiply each.
+__device__ __forceinline__ void bulkRow(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smemAddr(dst)), "l"(src),
+                 "r"(bytes), "r"(smemAddr(bar))
+                 : "memory");
+}
+
+template <bool BULK>
+__global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
+                                                           const uint8_t* __restrict__ blur, const LevelKp* __restrict__ sorted,
+                                                           const int* __restrict__ outN, float* __restrict__ outKps,
+                                                           uint8_t* __restrict__ outDesc, int F) {
+    __shared__ float4 sPat[256];
+    __shared__ uint2 sCoef[248];
+    __shared__ __align__(16) uint8_t sPatch[8][kPatchRows * kPatchPitch];
+    __shared__ __align__(16) uint8_t sIc[8][31 * kIcPitch];
+    __shared__ __align__(8) uint64_t sBar[8][2];
+    sPat[(threadIdx.x & 7) * 32 + (threadIdx.x >> 3)] = gPatternF[threadIdx.x];
+    if (threadIdx.x < 248) sCoef[threadIdx.x] = gIcCoef[threadIdx.x];
+    if (BULK && threadIdx.x < 16) mbarInit(&sBar[threadIdx.x >> 1][threadIdx.x & 1], 1);
+    if (BULK) mbarInitFence();
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    uint8_t* patch = sPatch[threadIdx.x >> 5];
+    uint8_t* ic = sIc[threadIdx.x >> 5];
+    uint64_t* barIc = &sBar[threadIdx.x >> 5][0];
+    uint64_t* barPatch = &sBar[threadIdx.x >> 5][1];
+    uint32_t phIc = 0, phPatch = 0;
+    const int total = F * P.outCap, stride = gridDim.x * 8;
+    const int qs = stride / P.outCap, rs = stride - qs * P.outCap;
+
+    auto issueIc = [&](int f, const LevelKp& kp) {
+        const LevelPlan& L = P.lv[kp.level];
+        const int px = kp.x + kEdge - kHalfPatch;
+        const uint8_t* p0 = pyr + (size_t)f * P.frameBytes + L.planeOff + (size_t)(kp.y + kEdge - kHalfPatch) * L.pitch + (px & ~15);
+        if (BULK) {
+            if (lane == 0) mbarExpectTx(barIc, 31 * kIcPitch);
+            if (lane < 31) bulkRow(ic + lane * kIcPitch, p0 + (size_t)(lane * L.pitch), kIcPitch, barIc);
+            return;
+        }
+#pragma unroll
+        for (int it = 0; it < 3; ++it) {
+            const int item = it * 32 + lane;  // 93 chunks: row = item / 3, chunk = item % 3
+            const int r = (item * 43) >> 7, c = item - 3 * r;
+            if (item < 93) cpAsync16(ic + r * kIcPitch + c * 16, p0 + (size_t)r * L.pitch + c * 16);
+        }
+    };
+    auto issuePatch = [&](int f, const LevelKp& kp) {
+        const LevelPlan& L = P.lv[kp.level];
+        const int bx0 = (kp.x - kPatchR) & ~15;
+        const uint8_t* src = blur + (size_t)f * P.blurBytes + L.blurOff + (size_t)(kp.y - kPatchR) * L.bpitch + bx0;
+        if (BULK) {
+            if (lane == 0) mbarExpectTx(barPatch, kPatchRows * 64);
+            bulkRow(patch + lane * kPatchPitch, src + (size_t)(lane * L.bpitch), 64, barPatch);
+            if (lane < kPatchRows - 32) bulkRow(patch + (32 + lane) * kPatchPitch, src + (size_t)((32 + lane) * L.bpitch), 64, barPatch);
+            return;
+        }
+#pragma unroll
+        for (int it = 0; it < 5; ++it) {
+            const int item = it * 32 + lane;  // row = item >> 2, chunk = item & 3
+            if (item < kPatchRows * 4)
+                cpAsync16(patch + (item >> 2) * kPatchPitch + (item & 3) * 16, src + (size_t)((item >> 2) * L.bpitch) + (item & 3) * 16);
+        }
+    };
+
+    int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+    int f = w / P.outCap, s = w - f * P.outCap;
+    // slot A = w (its patches are in flight / in shared memory), slot B = w + stride (record loaded)
+    LevelKp kpA = {0, 0, 0, 0}, kpB = {0, 0, 0, 0};
+    int nA = 0, nB = 0;
+    int fB = f + qs, sB = s + rs;
+    if (sB >= P.outCap) { sB -= P.outCap; ++fB; }
+    if (w < total) { nA = __ldg(outN + f); kpA = sorted[w]; }
+    if (w + stride < total) { nB = __ldg(outN + fB); kpB = sorted[w + stride]; }
+    if (w < total && s < nA) issueIc(f, kpA);
+    if (!BULK) cpAsyncCommit();
+    if (w < total && s < nA) issuePatch(f, kpA);
+    if (!BULK) cpAsyncCommit();
+
+    for (; w < total; w += stride) {
+        const bool valid = s < nA, validB = w + stride < total && sB < nB;
+        const LevelKp kp = kpA;
+        // record of the slot after the next
+        int fC = fB + qs, sC = sB + rs;
+        if (sC >= P.outCap) { sC -= P.outCap; ++fC; }
+        LevelKp kpC = {0, 0, 0, 0};
+        int nC = 0;
+        if (w + 2 * stride < total) { nC = __ldg(outN + fC); kpC = sorted[w + 2 * stride]; }
+
+        const int l = kp.level;
+        const LevelPlan& L = P.lv[l];
+        float angle = 0.f;
+        if (valid) {
+            // this slot's orientation patch has landed (its blurred patch may still be in flight)
+            if (BULK) { mbarWait(barIc, phIc); phIc ^= 1; }
+            else { cpAsyncWait1(); __syncwarp(); }
+            // ---- IC_Angle (ORBextractor.cc:76-103), see describeKernel ----
+            const int px = kp.x + kEdge - kHalfPatch;
+            const uint32_t* icw = reinterpret_cast<const uint32_t*>(ic) + ((px & 15) >> 2);
+            const int sh = (px & 3) * 8;
+            int m10 = 0, m01 = 0;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int item = it * 32 + lane;  // row = item >> 3, word = item & 7
+                const bool ok = item < 248;
+                const uint32_t* q = icw + (ok ? (item >> 3) * (kIcPitch / 4) + (item & 7) : 0);
+                const uint32_t lo = q[0], hi = q[1];
+                const uint2 cf = sCoef[ok ? item : 0];
+                const uint32_t wv = ok ? __funnelshift_r(lo, hi, sh) : 0u;
+                m10 = dp4a_us(wv, cf.x, m10);
+                m01 += ((item >> 3) - kHalfPatch) * (int)__dp4a(wv, cf.y, 0u);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+                m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+            }
+            angle = fastAtan2Deg((float)m01, (float)m10);
+        }
+        __syncwarp();  // every lane is done with `ic`
+        if (validB) issueIc(fB, kpB);
+        if (!BULK) cpAsyncCommit();
+
+        if (valid) {
+            // ---- rBRIEF: lane i computes byte i (pairs 8i .. 8i+7, LSB first) ----
+            const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+            float a, b;
+            glibcSincosf(__fmul_rn(angle, factorPI), &b, &a);
+            // this slot's blurred patch has landed (the next slot's orientation patch may be in flight)
+            if (BULK) { mbarWait(barPatch, phPatch); phPatch ^= 1; }
+            else { cpAsyncWait1(); __syncwarp(); }
+            const int bx0 = (kp.x - kPatchR) & ~15;
+            const uint8_t* center = patch + kPatchR * kPatchPitch + (kp.x - bx0);
+            constexpr int step = kPatchPitch;
+            const bool strict = P.fpMode == 0;
+            uint32_t t0[8], t1[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float4 pt = sPat[k * 32 + lane];
+                int r0, c0, r1, c1;
+                if (strict) {
+                    r0 = __float2int_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
+                    c0 = __float2int_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
+                    r1 = __float2int_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
+                    c1 = __float2int_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
+                } else {
+                    r0 = __float2int_rn(__fmaf_rn(pt.x, b, __fmul_rn(pt.y, a)));
+                    c0 = __float2int_rn(__fmaf_rn(pt.x, a, -__fmul_rn(pt.y, b)));
+                    r1 = __float2int_rn(__fmaf_rn(pt.z, b, __fmul_rn(pt.w, a)));
+                    c1 = __float2int_rn(__fmaf_rn(pt.z, a, -__fmul_rn(pt.w, b)));
+                }
+                t0[k] = center[r0 * step + c0];
+                t1[k] = center[r1 * step + c1];
+            }
+            uint32_t byte = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) byte |= (uint32_t)(t0[k] < t1[k]) << k;
+            uint32_t word = byte << (8 * (lane & 3));
+            word |= __shfl_xor_sync(0xffffffffu, word, 1);
+            word |= __shfl_xor_sync(0xffffffffu, word, 2);
+            const int half = lane & 16;
+            uint4 q;
+            q.x = __shfl_sync(0xffffffffu, word, half + 0);
+            q.y = __shfl_sync(0xffffffffu, word, half + 4);
+            q.z = __shfl_sync(0xffffffffu, word, half + 8);
+            q.w = __shfl_sync(0xffffffffu, word, half + 12);
+            uint8_t* d = outDesc + ((size_t)f * P.outCap + s) * 32;
+            if ((lane & 15) == 0) *reinterpret_cast<uint4*>(d + (lane >> 4) * 16) = q;
+        }
+        __syncwarp();  // every lane is done with `patch`
+        if (validB) issuePatch(fB, kpB);
+        if (!BULK) cpAsyncCommit();
+
+        // cv::KeyPoint record (:880-890, :1149-1151)
+        if (valid && lane < 7) {
+            float x = (float)kp.x, y = (float)kp.y;
+            if (l != 0) { x = __fmul_rn(x, L.scale); y = __fmul_rn(y, L.scale); }
+            float v;
+            switch (lane) {
+                case 0: v = x; break;
+                case 1: v = y; break;
+                case 2: v = L.patchSize; break;
+                case 3: v = angle; break;
+                case 4: v = (float)kp.resp; break;
+                case 5: v = __int_as_float(l); break;
+                default: v = __int_as_float(-1); break;
+            }
+            outKps[((size_t)f * P.outCap + s) * 7 + lane] = v;
+        }
+        kpA = kpB; nA = nB; f = fB; s = sB;
+        kpB = kpC; nB = nC; fB = fC; sB = sC;
+    }
+    if (!BULK) asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
 }  // namespace
 
 // per device, once per extractor (orbx_create)
@@ -342,13 +552,23 @@ void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int l
     int dev = 0, sms = 148, perSm = 1;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, describeKernel, 256, 0);
+    // ORBX_DESC_MODE=0: the round-1 kernel (plain loads at the start of every keypoint); default: the cp.async pipeline
+    // ORBX_DESC_MODE=0: the round-1 kernel (plain loads at the start of every keypoint, 0.280 ms per 256 frames); default (1):
+    // cp.async per 16-byte chunk (0.276 ms; ncu: long_scoreboard 3.2 -> 0.4 stall cycles per issue, issue slots 67.6 -> 74.7 %, but 8 %
+    // more instructions for the copies' addresses); 2: one bulk copy per patch row - measured 0.476 ms (68 TMA operations of 48-64
+    // bytes per keypoint: the copy engine's per-operation cost dominates), kept for A/B runs only
+    static const int mode = [] { const char* e = std::getenv("ORBX_DESC_MODE"); return e ? std::atoi(e) : 1; }();
+    if (mode == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, describeAsyncKernel<true>, 256, 0);
+    else if (mode == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, describeAsyncKernel<false>, 256, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, describeKernel, 256, 0);
     const long long want = ((long long)F * P.outCap + 7) / 8;
     // ORBX_DESC_PERSM (measurements only): cap on the persistent CTAs per SM
     static const int capPerSm = [] { const char* e = std::getenv("ORBX_DESC_PERSM"); return e ? std::atoi(e) : 0; }();
     if (capPerSm > 0) perSm = std::min(perSm, capPerSm);
     const int grid = (int)std::min<long long>(want, (long long)sms * std::max(perSm, 1));
-    describeKernel<<<grid, 256, 0, s>>>(P, B.pyr, B.blur, B.sorted, B.outN, reinterpret_cast<float*>(B.outKps), B.outDesc, F);
+    if (mode == 2) describeAsyncKernel<true><<<grid, 256, 0, s>>>(P, B.pyr, B.blur, B.sorted, B.outN, reinterpret_cast<float*>(B.outKps), B.outDesc, F);
+    else if (mode == 1) describeAsyncKernel<false><<<grid, 256, 0, s>>>(P, B.pyr, B.blur, B.sorted, B.outN, reinterpret_cast<float*>(B.outKps), B.outDesc, F);
+    else describeKernel<<<grid, 256, 0, s>>>(P, B.pyr, B.blur, B.sorted, B.outN, reinterpret_cast<float*>(B.outKps), B.outDesc, F);
     countLaunch();
 }
 
