@@ -5,7 +5,7 @@ usage: ncu_traffic.py summary.txt > traffic.json"""
 import json, sys
 STAGE = {"pyrLevel0AlignedKernel": "pyramid", "pyrLevel0Kernel": "pyramid", "pyrResizeKernel": "pyramid", "fastCellsKernel": "fast_cells",
          "fastStripKernel": "fast_cells", "blurKernel": "blur", "blurKernelLd": "blur", "quadtreeKernel": "quadtree", "slotKernel": "describe",
-         "describeKernel": "describe", "matchKernel": "match", "matchConsecutiveKernel": "match", "unpackPairsKernel": "match"}
+         "describeKernel": "describe", "describeAsyncKernel": "describe", "matchKernel": "match", "matchConsecutiveKernel": "match", "unpackPairsKernel": "match"}
 lines = open(sys.argv[1]).read().splitlines()
 hdr = lines[0].split()
 rows = [l.split() for l in lines[1:] if l.strip()]
