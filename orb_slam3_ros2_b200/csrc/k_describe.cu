@@ -157,6 +157,11 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
 #ifndef ORBX_DESC_MINB
 #define ORBX_DESC_MINB 4
 #endif
+// the pipelined kernel: 3 CTAs per SM = 80 registers (measured, whole step: 165.4 k frames/s against 162.7 k at 4 CTAs / 64 registers and
+// 164.0 k at 2 CTAs; the kernel alone is 0.255 ms either way at 3 or 4)
+#ifndef ORBX_DESC_ASYNC_MINB
+#define ORBX_DESC_ASYNC_MINB 3
+#endif
 __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
                                                       const uint8_t* __restrict__ blur, const LevelKp* __restrict__ sorted,
                                                       const int* __restrict__ outN, float* __restrict__ outKps,
@@ -331,7 +336,7 @@ __device__ __forceinline__ void bulkRow(void* dst, const void* src, uint32_t byt
 }
 
 template <bool BULK>
-__global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
+__global__ void __launch_bounds__(256, ORBX_DESC_ASYNC_MINB) describeAsyncKernel(const __grid_constant__ FramePlan P, const uint8_t* __restrict__ pyr,
                                                            const uint8_t* __restrict__ blur, const LevelKp* __restrict__ sorted,
                                                            const int* __restrict__ outN, float* __restrict__ outKps,
                                                            uint8_t* __restrict__ outDesc, int F) {
@@ -354,6 +359,14 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
     const int total = F * P.outCap, stride = gridDim.x * 8;
     const int qs = stride / P.outCap, rs = stride - qs * P.outCap;
 
+    // lane-invariant parts of the copies' addresses (shared-memory window addresses; the global side is one multiply per patch)
+    const uint32_t patchDst = smemAddr(patch) + (lane >> 2) * kPatchPitch + (lane & 3) * 16;  // row (lane >> 2) + 8 it, chunk lane & 3
+    const uint32_t* icRd = reinterpret_cast<const uint32_t*>(ic) + (lane >> 3) * (kIcPitch / 4) + (lane & 7);
+    const uint2* coefRd = sCoef + lane;
+    const int rowW = (lane >> 3) - kHalfPatch;
+    auto cp16 = [](uint32_t dst, const uint8_t* src) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+    };
     auto issueIc = [&](int f, const LevelKp& kp) {
         const LevelPlan& L = P.lv[kp.level];
         const int px = kp.x + kEdge - kHalfPatch;
@@ -363,11 +376,13 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
             if (lane < 31) bulkRow(ic + lane * kIcPitch, p0 + (size_t)(lane * L.pitch), kIcPitch, barIc);
             return;
         }
+        // 93 chunks: row = item / 3, chunk = item % 3.  Three lanes share a row, so a request touches 11 lines; one row per lane
+        // (trivial addresses, 31 lines per request) was measured slower: 0.269 against 0.259 ms.
 #pragma unroll
         for (int it = 0; it < 3; ++it) {
-            const int item = it * 32 + lane;  // 93 chunks: row = item / 3, chunk = item % 3
+            const int item = it * 32 + lane;
             const int r = (item * 43) >> 7, c = item - 3 * r;
-            if (item < 93) cpAsync16(ic + r * kIcPitch + c * 16, p0 + (size_t)r * L.pitch + c * 16);
+            if (item < 93) cp16(smemAddr(ic) + r * kIcPitch + c * 16, p0 + (unsigned)(r * L.pitch + c * 16));
         }
     };
     auto issuePatch = [&](int f, const LevelKp& kp) {
@@ -380,12 +395,12 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
             if (lane < kPatchRows - 32) bulkRow(patch + (32 + lane) * kPatchPitch, src + (size_t)((32 + lane) * L.bpitch), 64, barPatch);
             return;
         }
+        // rows (lane >> 2) + 8 it, chunk lane & 3: 4 full sweeps + rows 32..36
+        const uint8_t* q = src + (unsigned)((lane >> 2) * L.bpitch + (lane & 3) * 16);
+        const unsigned step = 8u * (unsigned)L.bpitch;
 #pragma unroll
-        for (int it = 0; it < 5; ++it) {
-            const int item = it * 32 + lane;  // row = item >> 2, chunk = item & 3
-            if (item < kPatchRows * 4)
-                cpAsync16(patch + (item >> 2) * kPatchPitch + (item & 3) * 16, src + (size_t)((item >> 2) * L.bpitch) + (item & 3) * 16);
-        }
+        for (int it = 0; it < 4; ++it, q += step) cp16(patchDst + it * 8 * kPatchPitch, q);
+        if (lane < 4 * (kPatchRows - 32)) cp16(patchDst + 32 * kPatchPitch, q);
     };
 
     int w = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -405,7 +420,8 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
     for (; w < total; w += stride) {
         const bool valid = s < nA, validB = w + stride < total && sB < nB;
         const LevelKp kp = kpA;
-        // record of the slot after the next
+        // record of the slot after the next (fetching it at the END of the iteration instead, to shorten its live range, was
+        // measured slower: 0.278 against 0.255 ms)
         int fC = fB + qs, sC = sB + rs;
         if (sC >= P.outCap) { sC -= P.outCap; ++fC; }
         LevelKp kpC = {0, 0, 0, 0};
@@ -419,22 +435,25 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
             // this slot's orientation patch has landed (its blurred patch may still be in flight)
             if (BULK) { mbarWait(barIc, phIc); phIc ^= 1; }
             else { cpAsyncWait1(); __syncwarp(); }
-            // ---- IC_Angle (ORBextractor.cc:76-103), see describeKernel ----
+            // ---- IC_Angle (ORBextractor.cc:76-103), see describeKernel.  item = 32 it + lane: row 4 it + (lane >> 3), word lane & 7,
+            // so every address is a lane-invariant base plus an immediate; m01 = sum (row - 15) S = rowW sum S + 4 sum it S ----
             const int px = kp.x + kEdge - kHalfPatch;
-            const uint32_t* icw = reinterpret_cast<const uint32_t*>(ic) + ((px & 15) >> 2);
             const int sh = (px & 3) * 8;
             int m10 = 0, m01 = 0;
+            const uint32_t* q = icRd + ((px & 15) >> 2);
+            int sA = 0, sB4 = 0;
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
-                const int item = it * 32 + lane;  // row = item >> 3, word = item & 7
-                const bool ok = item < 248;
-                const uint32_t* q = icw + (ok ? (item >> 3) * (kIcPitch / 4) + (item & 7) : 0);
-                const uint32_t lo = q[0], hi = q[1];
-                const uint2 cf = sCoef[ok ? item : 0];
-                const uint32_t wv = ok ? __funnelshift_r(lo, hi, sh) : 0u;
+                const uint32_t lo = q[it * kIcPitch], hi = q[it * kIcPitch + 1];  // 4 rows = 4 * kIcPitch / 4 words
+                const uint2 cf = coefRd[it * 32];
+                uint32_t wv = __funnelshift_r(lo, hi, sh);
+                if (it == 7 && lane >= 24) wv = 0u;  // items 248..255 do not exist (what was read is other shared memory)
                 m10 = dp4a_us(wv, cf.x, m10);
-                m01 += ((item >> 3) - kHalfPatch) * (int)__dp4a(wv, cf.y, 0u);
+                const int S = (int)__dp4a(wv, cf.y, 0u);
+                sA += S;
+                sB4 += it * S;
             }
+            m01 = rowW * sA + 4 * sB4;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 m10 += __shfl_xor_sync(0xffffffffu, m10, o);
@@ -458,9 +477,11 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
             const uint8_t* center = patch + kPatchR * kPatchPitch + (kp.x - bx0);
             constexpr int step = kPatchPitch;
             const bool strict = P.fpMode == 0;
-            uint32_t t0[8], t1[8];
+            uint32_t byte = 0;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            // the sign of t0 - t1 = (t0 < t1) enters at bit 0: pair 7 first, so pair k ends at bit k.  Each pair is consumed at once: keeping
+            // the 16 samples in registers until the end made ptxas spill (64 registers), 0.294 ms
+            for (int k = 7; k >= 0; --k) {
                 const float4 pt = sPat[k * 32 + lane];
                 int r0, c0, r1, c1;
                 if (strict) {
@@ -474,12 +495,9 @@ __global__ void __launch_bounds__(256, ORBX_DESC_MINB) describeAsyncKernel(const
                     r1 = __float2int_rn(__fmaf_rn(pt.z, b, __fmul_rn(pt.w, a)));
                     c1 = __float2int_rn(__fmaf_rn(pt.z, a, -__fmul_rn(pt.w, b)));
                 }
-                t0[k] = center[r0 * step + c0];
-                t1[k] = center[r1 * step + c1];
+                const uint32_t t0 = center[r0 * step + c0], t1 = center[r1 * step + c1];
+                byte = __funnelshift_l(t0 - t1, byte, 1);
             }
-            uint32_t byte = 0;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) byte |= (uint32_t)(t0[k] < t1[k]) << k;
             uint32_t word = byte << (8 * (lane & 3));
             word |= __shfl_xor_sync(0xffffffffu, word, 1);
             word |= __shfl_xor_sync(0xffffffffu, word, 2);
