@@ -44,6 +44,43 @@ __device__ __forceinline__ int hamming256(const uint32_t (&q)[8], const uint4& a
     return __popc(s1) + __popc(s2) + 2 * (__popc(c0) + __popc(c1) + __popc(c2));
 }
 
+// The packed key of one pair, distance << 23 | row, with everything but the logic and the counts on the FMA pipe.  ncu on the loop
+// that used hamming256() + shift + or: ALU pipe 84 %, XU (POPC) 84 %, FMA 6 % - the ALU pipe carried 21 operations per pair (8 XOR,
+// 6 carry-save LOP3, IADD3, OR, 3 min / max and 2 of the compiler's own loop-bound recomputation).  Here the weight-2 and weight-1
+// sums stay apart and enter the key through two multiply-adds with the multipliers 2^24 and 2^23 held in registers the compiler
+// cannot see through (a shift + or would go back to the ALU pipe): key = t * 2^24 + (u * 2^23 + row).  ALU operations per pair: 17.
+// Measured on B200: cfg5 630 -> 666 Gpairs/s, and 702 once matchKernel may use 126 registers (launch bound 1 CTA: ptxas had settled on 64
+// registers with 72 bytes of spills); whole step 164.6 -> 169.0 k frames/s, most of it from the explicit trip counts.  One more adder on the
+// three weight-2 words (4 POPC + 16 LOP3): 637 Gpairs/s, 166.8 k frames/s - rejected again.
+#ifndef ORBX_MATCH_FMAKEY
+#define ORBX_MATCH_FMAKEY 1
+#endif
+__device__ __forceinline__ uint32_t madLo(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// (read from __constant__ memory: ptxas folds multipliers it can see - an immediate, a `mov` - back into LEA / IADD3 on the ALU pipe)
+__constant__ uint32_t gKeyMul[3] = {1u << 23, 1u << 24, 1u};
+struct KeyMul {
+    uint32_t m23, m24, one;
+    __device__ __forceinline__ KeyMul() : m23(gKeyMul[0]), m24(gKeyMul[1]), one(gKeyMul[2]) {}
+};
+__device__ __forceinline__ uint32_t pairKey(const uint32_t (&q)[8], const uint4& a, const uint4& b, uint32_t row, const KeyMul& M) {
+#if ORBX_MATCH_FMAKEY
+    const uint32_t x0 = q[0] ^ a.x, x1 = q[1] ^ a.y, x2 = q[2] ^ a.z, x3 = q[3] ^ a.w;
+    const uint32_t x4 = q[4] ^ b.x, x5 = q[5] ^ b.y, x6 = q[6] ^ b.z, x7 = q[7] ^ b.w;
+    const uint32_t s0 = x0 ^ x1 ^ x2, c0 = (x0 & x1) | (x2 & (x0 | x1));
+    const uint32_t s1 = x3 ^ x4 ^ x5, c1 = (x3 & x4) | (x5 & (x3 | x4));
+    const uint32_t s2 = x6 ^ x7 ^ s0, c2 = (x6 & x7) | (s0 & (x6 | x7));
+    const uint32_t u = madLo(__popc(s1), M.one, __popc(s2));                               // weight 1
+    const uint32_t t = madLo(__popc(c0), M.one, madLo(__popc(c1), M.one, __popc(c2)));     // weight 2
+    return madLo(t, M.m24, madLo(u, M.m23, row));
+#else
+    return ((uint32_t)hamming256(q, a, b) << 23) | row;
+#endif
+}
+
 struct MatchProblem {
     const uint8_t* q;    // nq x 32
     const uint8_t* db;   // nd x 32
@@ -52,8 +89,11 @@ struct MatchProblem {
 };
 
 // Problem z: either the single (q, db) pair, or — consecutive mode — frame z against frame z+1 of a batch.
+#ifndef ORBX_MATCH_MINB
+#define ORBX_MATCH_MINB 1
+#endif
 template <int R>
-__global__ void __launch_bounds__(kMT) matchKernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ db,
+__global__ void __launch_bounds__(kMT, ORBX_MATCH_MINB) matchKernel(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ db,
                                                    long long nd, long long indexBase, long long chunkRows,
                                                    unsigned long long* __restrict__ part1,
                                                    unsigned long long* __restrict__ part2, const int* __restrict__ counts,
@@ -72,6 +112,8 @@ __global__ void __launch_bounds__(kMT) matchKernel(const uint8_t* __restrict__ q
     const long long c0 = (long long)blockIdx.x * chunkRows;
     const long long c1 = c0 + chunkRows < nd ? c0 + chunkRows : nd;
 
+    const KeyMul M;
+    constexpr int kUnroll = R >= 4 ? 2 : 4;
     uint32_t qw[R][8];
     uint32_t k1[R], k2[R];
 #pragma unroll
@@ -91,17 +133,22 @@ __global__ void __launch_bounds__(kMT) matchKernel(const uint8_t* __restrict__ q
         for (int i = tid; i < rows * 2; i += kMT) sDb[i] = __ldg(src + i);
         __syncthreads();
         const uint32_t idx0 = (uint32_t)(s0 - c0);
-#pragma unroll 2
-        for (int j = 0; j < rows; ++j) {
+        auto onePair = [&](int j) {
             const uint4 a = sDb[2 * j], b = sDb[2 * j + 1];
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                const int d = hamming256(qw[r], a, b);
-const uint32_t key = ((uint32_t)d << 23) | (idx0 + (uint32_t)j);
+                const uint32_t key = pairKey(qw[r], a, b, idx0 + (uint32_t)j, M);
                 k2[r] = min(k2[r], max(k1[r], key));
                 k1[r] = min(k1[r], key);
             }
+        };
+        // the trip counts are explicit: with `j < rows` the compiler recomputed min(c1 - s0, kStage) in every iteration
+        const int rowsU = rows & ~(kUnroll - 1);
+        for (int j = 0; j < rowsU; j += kUnroll) {
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) onePair(j + u);
         }
+        for (int j = rowsU; j < rows; ++j) onePair(j);
     }
     const size_t nqPad = counts ? (size_t)cap : (size_t)nq;
 #pragma unroll
@@ -158,6 +205,8 @@ __global__ void __launch_bounds__(NT) matchConsecutiveKernel(const uint8_t* __re
     const int nq = min(counts[z], cap), nd = min(counts[z + 1], cap);
     const int q0 = blockIdx.x * NT * R;
 
+    const KeyMul M;
+    constexpr int kUnroll = R >= 4 ? 2 : 4;
     uint32_t qw[R][8];
     uint32_t k1[R], k2[R];
 #pragma unroll
@@ -176,17 +225,21 @@ __global__ void __launch_bounds__(NT) matchConsecutiveKernel(const uint8_t* __re
             const uint4* src = reinterpret_cast<const uint4*>(db + (size_t)s0 * 32);
             for (int i = tid; i < rows * 2; i += NT) sDb[i] = __ldg(src + i);
             __syncthreads();
-#pragma unroll 2
-            for (int j = 0; j < rows; ++j) {
+            auto onePair = [&](int j) {
                 const uint4 a = sDb[2 * j], b = sDb[2 * j + 1];
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    const int d = hamming256(qw[r], a, b);
-                    const uint32_t key = ((uint32_t)d << 23) | (uint32_t)(s0 + j);
+                    const uint32_t key = pairKey(qw[r], a, b, (uint32_t)(s0 + j), M);
                     k2[r] = min(k2[r], max(k1[r], key));
                     k1[r] = min(k1[r], key);
                 }
+            };
+            const int rowsU = rows & ~(kUnroll - 1);
+            for (int j = 0; j < rowsU; j += kUnroll) {
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) onePair(j + u);
             }
+            for (int j = rowsU; j < rows; ++j) onePair(j);
         }
     }
 #pragma unroll
@@ -329,6 +382,16 @@ void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap,
     // Measured (frames/s of the whole step): R = 1 158.2 k, R = 2 145.1 k, R = 4 146.2 k, two-kernel form 156.9 k - the loop is bound by
     // the POPC (XU 84 %) and ALU (80 %) pipes, not by issue slots, so sharing the row loads between queries buys nothing and costs occupancy
     static const int rSel = [] { const char* e = std::getenv("ORBX_MATCH_R"); return e ? std::atoi(e) : 1; }();
+    // ORBX_MATCH_NT: threads (= queries) per CTA of the R = 1 form (64, 96; default 128).  Measured, whole step: 166.2 k / 165.7 k / 168.0 k
+    // frames/s - CTAs beyond a frame's count skip the walk, so 128-thread CTAs waste only the 17 idle slots of the eighth one
+    static const int ntSel = [] { const char* e = std::getenv("ORBX_MATCH_NT"); return e ? std::atoi(e) : 128; }();
+    if (rSel == 1 && (ntSel == 64 || ntSel == 96)) {
+        const dim3 grid((cap + ntSel - 1) / ntSel, F - 1);
+        if (ntSel == 64) matchConsecutiveKernel<1, 64><<<grid, 64, 0, s>>>(dDesc, dN, cap, idx1, d1, idx2, d2);
+        else matchConsecutiveKernel<1, 96><<<grid, 96, 0, s>>>(dDesc, dN, cap, idx1, d1, idx2, d2);
+        countLaunch();
+        return;
+    }
     if (rSel == 1 || rSel == 2 || rSel == 4) {
         constexpr int NT = 128;
         const int tiles = (cap + NT * rSel - 1) / (NT * rSel);
