@@ -193,8 +193,11 @@ __global__ void mergeKernel(const unsigned long long* __restrict__ k1, const uns
 // Consecutive frames of a batch in ONE kernel (v2): frame z against frame z + 1, every thread keeps R queries, a CTA walks
 // ALL rows of frame z + 1 (no database chunks, so no 64-bit partial keys and no merge pass) and writes the int32 results
 // itself; 128-thread CTAs, 8 q-tiles x 255 pairs all resident at once.  Slots [n, cap) get the "no match" values (-1, 256).
+#ifndef ORBX_MATCHC_MINB
+#define ORBX_MATCHC_MINB 12
+#endif
 template <int R, int NT>
-__global__ void __launch_bounds__(NT) matchConsecutiveKernel(const uint8_t* __restrict__ desc, const int* __restrict__ counts, int cap,
+__global__ void __launch_bounds__(NT, R == 1 ? ORBX_MATCHC_MINB : 1) matchConsecutiveKernel(const uint8_t* __restrict__ desc, const int* __restrict__ counts, int cap,
                                                              int* __restrict__ idx1, int* __restrict__ d1, int* __restrict__ idx2,
                                                              int* __restrict__ d2) {
     __shared__ __align__(16) uint4 sDb[kStage * 2];

@@ -542,8 +542,13 @@ int orbx_create(const orbx_params* params, orbx_handle* out) {
         const char* st = std::getenv("ORBX_FAST_STRIP");  // 0 = the per-cell FAST kernels only (A/B measurements)
         h->useStrips = !(st && st[0] == '0');
     }
-    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
+    // ORBX_PRIO (A/B measurements): 1 = the main stream (pyramid, FAST, quadtree, describe) above the auxiliary one (blur), so the
+    // quadtree's long serial CTAs are placed first and the blur fills in around them; 2 = the other way round; default 0 = equal
+    static const int prio = [] { const char* v = std::getenv("ORBX_PRIO"); return v ? std::atoi(v) : 0; }();
+    int prLeast = 0, prGreatest = 0;
+    cudaDeviceGetStreamPriorityRange(&prLeast, &prGreatest);
+    cudaError_t e = cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, prio == 1 ? prGreatest : prLeast);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&h->aux, cudaStreamNonBlocking, prio == 2 ? prGreatest : prLeast);
     for (int i = 0; i < 12 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e != cudaSuccess) {
         orbx_destroy(h);  // releases whatever streams / events were created
