@@ -55,6 +55,16 @@ __device__ __forceinline__ int hamming256(const uint32_t (&q)[8], const uint4& a
 #ifndef ORBX_MATCH_FMAKEY
 #define ORBX_MATCH_FMAKEY 1
 #endif
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xe8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 __device__ __forceinline__ uint32_t madLo(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t d;
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
@@ -68,11 +78,13 @@ struct KeyMul {
 };
 __device__ __forceinline__ uint32_t pairKey(const uint32_t (&q)[8], const uint4& a, const uint4& b, uint32_t row, const KeyMul& M) {
 #if ORBX_MATCH_FMAKEY
+    // the adders are written as lop3 instructions: left to itself the compiler re-associates the XOR chains through the raw q / db words
+    // (with 4 queries per thread it issued 20 LOP3 per pair instead of the 14 written here)
     const uint32_t x0 = q[0] ^ a.x, x1 = q[1] ^ a.y, x2 = q[2] ^ a.z, x3 = q[3] ^ a.w;
     const uint32_t x4 = q[4] ^ b.x, x5 = q[5] ^ b.y, x6 = q[6] ^ b.z, x7 = q[7] ^ b.w;
-    const uint32_t s0 = x0 ^ x1 ^ x2, c0 = (x0 & x1) | (x2 & (x0 | x1));
-    const uint32_t s1 = x3 ^ x4 ^ x5, c1 = (x3 & x4) | (x5 & (x3 | x4));
-    const uint32_t s2 = x6 ^ x7 ^ s0, c2 = (x6 & x7) | (s0 & (x6 | x7));
+    const uint32_t s0 = xor3(x0, x1, x2), c0 = maj3(x0, x1, x2);
+    const uint32_t s1 = xor3(x3, x4, x5), c1 = maj3(x3, x4, x5);
+    const uint32_t s2 = xor3(x6, x7, s0), c2 = maj3(x6, x7, s0);
     const uint32_t u = madLo(__popc(s1), M.one, __popc(s2));                               // weight 1
     const uint32_t t = madLo(__popc(c0), M.one, madLo(__popc(c1), M.one, __popc(c2)));     // weight 2
     return madLo(t, M.m24, madLo(u, M.m23, row));
@@ -194,7 +206,7 @@ __global__ void mergeKernel(const unsigned long long* __restrict__ k1, const uns
 // ALL rows of frame z + 1 (no database chunks, so no 64-bit partial keys and no merge pass) and writes the int32 results
 // itself; 128-thread CTAs, 8 q-tiles x 255 pairs all resident at once.  Slots [n, cap) get the "no match" values (-1, 256).
 #ifndef ORBX_MATCHC_MINB
-#define ORBX_MATCHC_MINB 12
+#define ORBX_MATCHC_MINB 8
 #endif
 template <int R, int NT>
 __global__ void __launch_bounds__(NT, R == 1 ? ORBX_MATCHC_MINB : 1) matchConsecutiveKernel(const uint8_t* __restrict__ desc, const int* __restrict__ counts, int cap,
