@@ -32,7 +32,7 @@ LAP = (0, 1000)  # Frame.cc:311 passes {0,1000} for monocular frames
 E2E_SUBBATCHES = 1  # measured (profiles/r01_v15_e2e_sweep.txt): sub-batches 2 -> 110 k, 1 -> 126-131 k frames/s through host buffers
 E2E_DEPTH = 3   # measured sweep (handles x depth -> frames/s): 2x1 90.2k, 4x1 98.6k, 2x2 110.7k, 4x2 100.2k, 2x3 112.7k, 1x3 112.1k, 3x3 104.4k
 E2E_HANDLES = 1  # v15 sweep with sub-batches off (handles x depth): 1x2 105k, 1x3 131k, 1x4 125k, 2x2 125k, 2x3 127k, 3x3 114k
-RESIDENT_HANDLES = 2  # measured (handles x sub-batches -> frames/s): 1x1 127.9k, 1x2 129.2k, 2x1 131.8k, 2x2 134.6k, 3x1 134.3k, 3x2 132.3k
+RESIDENT_HANDLES = 4  # round-2 kernels: 2 handles 168.9k, 3 171.0k, 4 171.6k, 6 171.0k, 8 171.3k frames/s; round-1 kernels measured (handles x sub-batches -> frames/s): 1x1 127.9k, 1x2 129.2k, 2x1 131.8k, 2x2 134.6k, 3x1 134.3k, 3x2 132.3k
 SUBBATCHES = 1  # v15 sweep with the forked FAST classes (sub-batches x resident handles -> frames/s): 1x1 140.6k, 1x2 150.4k, 1x3 147.2k, 2x1 140.5k, 2x2 144.3k, 2x3 145.3k
 METRIC = "ORB extract frames/s @752x480x1000kp (extract + frame-to-frame top-2 match, batched)"
 # what the CPU arm's OpenCV calls run on (so that nobody reads the GPU / CPU ratio as a ratio against a SIMD OpenCV build)
