@@ -59,25 +59,40 @@ __global__ void __launch_bounds__(256) pyrLevel0AlignedKernel(const uint8_t* __r
                                                               uint8_t* __restrict__ pyr, unsigned frameBytes, int w, int h,
                                                               int pitch, int kFirst, int nFast, int nChunks) {
     const int ph = h + 2 * kEdge, pw = w + 2 * kEdge;
-    const int item = blockIdx.x * 256 + threadIdx.x;
     const int fastItems = ph * nFast;
+    const int nbFast = (fastItems + 511) / 512;  // the first nbFast CTAs: two interior chunks per thread (both loads in flight at once)
     uint8_t* dst = pyr + (size_t)blockIdx.z * frameBytes;
     const uint8_t* frame = img + (size_t)blockIdx.z * frameStride;
-    if (item < fastItems) {
-        const int yp = item / nFast, k = kFirst + (item - yp * nFast);
-        int y = yp - kEdge;
-        y = y < 0 ? -y : (y >= h ? 2 * h - 2 - y : y);
-        const uint8_t* src = frame + (size_t)y * stride + (k * 16 - kEdge);
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(src + 3));      // source bytes x0+3 .. x0+18
-        const uint32_t p = __ldg(reinterpret_cast<const uint32_t*>(src - 1));  // source bytes x0-1 .. x0+2
-        uint4 out;
-        out.x = __byte_perm(p, a.x, 0x4321);
-        out.y = __byte_perm(a.x, a.y, 0x4321);
-        out.z = __byte_perm(a.y, a.z, 0x4321);
-        out.w = __byte_perm(a.z, a.w, 0x4321);
-        *reinterpret_cast<uint4*>(dst + (size_t)yp * pitch + k * 16) = out;
+    if ((int)blockIdx.x < nbFast) {
+        uint4 a[2];
+        uint32_t p[2];
+        size_t o[2];
+        bool ok[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int it = blockIdx.x * 512 + u * 256 + threadIdx.x;
+            ok[u] = it < fastItems;
+            const int itc = ok[u] ? it : 0;
+            const int yp = itc / nFast, k = kFirst + (itc - yp * nFast);
+            int y = yp - kEdge;
+            y = y < 0 ? -y : (y >= h ? 2 * h - 2 - y : y);
+            const uint8_t* src = frame + (size_t)y * stride + (k * 16 - kEdge);
+            a[u] = __ldg(reinterpret_cast<const uint4*>(src + 3));        // source bytes x0+3 .. x0+18
+            p[u] = __ldg(reinterpret_cast<const uint32_t*>(src - 1));     // source bytes x0-1 .. x0+2
+            o[u] = (size_t)yp * pitch + k * 16;
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            uint4 out;
+            out.x = __byte_perm(p[u], a[u].x, 0x4321);
+            out.y = __byte_perm(a[u].x, a[u].y, 0x4321);
+            out.z = __byte_perm(a[u].y, a[u].z, 0x4321);
+            out.w = __byte_perm(a[u].z, a[u].w, 0x4321);
+            if (ok[u]) *reinterpret_cast<uint4*>(dst + o[u]) = out;
+        }
         return;
     }
+    const int item = fastItems + ((int)blockIdx.x - nbFast) * 256 + threadIdx.x;
     const int nSlow = nChunks - nFast;
     const int sItem = item - fastItems;
     if (sItem >= ph * nSlow) return;
@@ -394,8 +409,8 @@ void launchPyramid(const FramePlan& P, const Buffers& B, const uint8_t* dImgs, i
         // interior chunks k: source x0 = 16k - 19 >= 1 and x0 + 19 <= w
         const int kFirst = 2, nFast = L.w / 16 - kFirst + 1, nChunks = (pw + 15) / 16;
         if (aligned && nFast > 0 && L.w >= 20 && L.h >= 20) {
-            const long long items = (long long)ph * nChunks;
-            dim3 grid((unsigned)((items + 255) / 256), 1, F);
+            const long long fastItems = (long long)ph * nFast, slowItems = (long long)ph * (nChunks - nFast);
+            dim3 grid((unsigned)((fastItems + 511) / 512 + (slowItems + 255) / 256), 1, F);
             pyrLevel0AlignedKernel<<<grid, 256, 0, s>>>(dImgs, stride, frameStride, B.pyr, P.frameBytes, L.w, L.h, L.pitch,
                                                         kFirst, nFast, nChunks);
         } else {
