@@ -213,14 +213,22 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
                                                       const int* __restrict__ cellCnt, uint32_t* __restrict__ gath,
                                                       uint16_t* __restrict__ nidAll, LevelKp* __restrict__ lkp,
                                                       int* __restrict__ lkpCnt, int* __restrict__ errFlag, int levelMajor, int NC,
-                                                      int maxCells) {
+                                                      int maxCells, int lBase, const int* __restrict__ gate, int gateMode,
+                                                      int gateLevels) {
     extern __shared__ __align__(16) uint8_t smemRaw[];
     __shared__ int sPartial[kQT / 32];
     __shared__ int sRed;
 
     // levelMajor: the grid is (frames, levels) - every frame's level 0 first, then level 1, ...: the big levels start first and the
     // small ones fill the SMs as those drain (with (levels, frames) every wave of resident CTAs ends with its own level-0 CTAs)
-    const int l = levelMajor ? blockIdx.y : blockIdx.x, f = levelMajor ? blockIdx.x : blockIdx.y, tid = threadIdx.x;
+    const int l = (levelMajor ? blockIdx.y : blockIdx.x) + lBase, f = levelMajor ? blockIdx.x : blockIdx.y, tid = threadIdx.x;
+    // early / late pass of the split pipeline (launchQuadtree): gate[0..1] = the strips' overflow counts once the levels below gateLevels
+    // were done.  Early pass (1): runs those levels unless a strip overflowed (their cells then wait for the per-cell kernel); late pass (2):
+    // runs them only in that case
+    if (gateMode) {
+        const bool over = (gate[0] | gate[1]) != 0;
+        if (gateMode == 1 ? over : (l < gateLevels && !over)) return;
+    }
     const LevelPlan& L = P.lv[l];
     const int N = L.nFeat;
 
@@ -477,15 +485,20 @@ int qtMaxCells(const FramePlan& P) {
 size_t quadtreeSmemBytes(const FramePlan& P) { return qtSmem(qtNodeCap(P), qtMaxCells(P)); }
 
 template <int QT>
-static void launchQuadtreeT(const FramePlan& P, const Buffers& B, int F, int NC, int maxCells, size_t smem, cudaStream_t s) {
+static void launchQuadtreeT(const FramePlan& P, const Buffers& B, int F, int NC, int maxCells, size_t smem, cudaStream_t s, int lBase,
+                            int nLv, const int* gate, int gateMode, int gateLevels) {
     if (smem > 40 * 1024) cudaFuncSetAttribute(quadtreeKernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     // ORBX_QT_ORDER=0: the round-1 grid (levels, frames) for A/B runs
     static const int levelMajor = [] { const char* e = std::getenv("ORBX_QT_ORDER"); return e ? std::atoi(e) : 1; }();
-    const dim3 grid = levelMajor ? dim3(F, P.nlevels) : dim3(P.nlevels, F);
-    quadtreeKernel<QT><<<grid, QT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag, levelMajor, NC, maxCells);
+    const dim3 grid = levelMajor ? dim3(F, nLv) : dim3(nLv, F);
+    quadtreeKernel<QT><<<grid, QT, smem, s>>>(P, B.cand, B.cellCnt, B.gath, B.nid, B.lkp, B.lkpCnt, B.errFlag, levelMajor, NC, maxCells,
+                                              lBase, gate, gateMode, gateLevels);
 }
 
-void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s) {
+void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int lBase, int nLv, const int* gate, int gateMode,
+                    int gateLevels) {
+    if (nLv < 0) nLv = P.nlevels - lBase;
+    if (nLv <= 0) return;
     const int NC = qtNodeCap(P), maxCells = qtMaxCells(P);
     const size_t smem = qtSmem(NC, maxCells);
     // CTA size by the largest per-level target: 128 threads up to 300 nodes per level (1000 features: 141.2 -> 144.7 k frames/s
@@ -493,8 +506,8 @@ void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s)
     // 28.2 k frames/s with 128, 31.0 k with 256); ORBX_QT_THREADS overrides (A/B measurements)
     static const int forced = [] { const char* e = std::getenv("ORBX_QT_THREADS"); return e ? std::atoi(e) : 0; }();
     const int qt = forced ? forced : (NC <= 300 ? 128 : 256);
-    if (qt <= 128) launchQuadtreeT<128>(P, B, F, NC, maxCells, smem, s);
-    else launchQuadtreeT<256>(P, B, F, NC, maxCells, smem, s);
+    if (qt <= 128) launchQuadtreeT<128>(P, B, F, NC, maxCells, smem, s, lBase, nLv, gate, gateMode, gateLevels);
+    else launchQuadtreeT<256>(P, B, F, NC, maxCells, smem, s, lBase, nLv, gate, gateMode, gateLevels);
     countLaunch();
 }
 }  // namespace orbx

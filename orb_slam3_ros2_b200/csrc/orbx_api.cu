@@ -399,10 +399,34 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
     // complete, beside FAST (it only needs the pyramid); 2 = additionally the strips of the levels 0..3 start when level 3 is written and
     // run beside the resize of the small levels (launch- and latency-bound kernels of 20-40 us).  Measured (frames/s of the whole step):
     // 0 156.1 k, 1 152.6 k (FAST + blur together 0.64 ms, quadtree alone 0.19), 2 152.8 k: the stages share the same integer pipes, so
-    // running them side by side moves time around without saving any; default 0.
+    // running them side by side moves time around without saving any; 3 = see below; default 0.
     static const int pipeMode = [] { const char* e = std::getenv("ORBX_PIPE"); return e ? std::atoi(e) : 0; }();
-    bool blurLaunched = false;
-    if (B.stripMaps && pipeMode == 2 && P.nlevels > 4) {
+    bool blurLaunched = false, quadSplit = false;
+    constexpr int kEarlyLevels = 2;  // pipeMode 3: the levels whose quadtree starts before FAST has finished the others
+    int* gate = B.errFlag + 56;
+    if (B.stripMaps && pipeMode == 3 && P.nlevels > kEarlyLevels) {
+        // The quadtree is a chain of short rounds per (frame, level): latency-bound, 30 % of the issue slots, and the two big levels set its
+        // length.  Their FAST strips run first; their quadtree then starts on the auxiliary stream beside the strips of the small levels
+        // (gate = snapshot of the strips' overflow counts: if a strip of the big levels overflowed, their cells wait for the per-cell
+        // kernel and the late pass takes those levels as well); the blur follows it on that stream.
+        // Measured (parity-green incl. the overflow cases): 170.4-170.5 k against 171.3-172.1 k frames/s, one handle's batch 1.41 against
+        // 1.36 ms - beside the strips the quadtree costs FAST what it saves itself; not the default.
+        launchFastStrips(P, B, F, s, 4, kEarlyLevels - 1);
+        launchPyramid(P, B, dImgs, stride, frameStride, F, s);
+        cudaEventRecord(h->ev[1], s);
+        launchFastStrips(P, B, F, s, 1, kEarlyLevels - 1);
+        cudaMemcpyAsync(gate, B.fbCount, 2 * sizeof(int), cudaMemcpyDeviceToDevice, s);
+        cudaEventRecord(h->ev[10], s);
+        cudaStreamWaitEvent(x, h->ev[10], 0);
+        launchQuadtree(P, B, F, x, 0, kEarlyLevels, gate, 1, kEarlyLevels);
+        cudaEventRecord(h->ev[7], x);
+        launchBlur(P, B, F, x);
+        cudaEventRecord(h->ev[8], x);
+        blurLaunched = true;
+        quadSplit = true;
+        launchFastStrips(P, B, F, s, 2, kEarlyLevels - 1);
+        launchFastStrips(P, B, F, s, 3, kEarlyLevels - 1);
+    } else if (B.stripMaps && pipeMode == 2 && P.nlevels > 4) {
         launchFastStrips(P, B, F, s, 4, 3);   // list counts cleared before either part can append
         launchPyramid(P, B, dImgs, stride, frameStride, F, s, -1, 0, 3);
         cudaEventRecord(h->ev[10], s);
@@ -472,7 +496,8 @@ static int runPipeline(orbx_extractor* h, const uint8_t* dImgs, int stride, size
         cudaEventRecord(h->ev[8], x);
     }
     ORBX_CUDA(cudaGetLastError());  // a failed launch of the pyramid / FAST / blur stages is reported as such, not carried further
-    launchQuadtree(P, B, F, s);
+    if (quadSplit) launchQuadtree(P, B, F, s, 0, -1, gate, 2, kEarlyLevels);
+    else launchQuadtree(P, B, F, s);
     cudaEventRecord(h->ev[3], s);
     cudaStreamWaitEvent(s, h->ev[8], 0);  // join
     cudaEventRecord(h->ev[4], s);

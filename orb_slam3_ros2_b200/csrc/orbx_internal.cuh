@@ -129,7 +129,8 @@ void buildPyrGroupTable(const FramePlan& P, const std::vector<int16_t>& tab, std
 int buildPyrMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 int buildBlurMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
 int buildFastMaps(const FramePlan& P, const uint8_t* pyrBase, int capFrames, void* out);
-void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
+void launchQuadtree(const FramePlan& P, const Buffers& B, int F, cudaStream_t s, int lBase = 0, int nLv = -1, const int* gate = nullptr,
+                    int gateMode = 0, int gateLevels = 0);
 void launchBlur(const FramePlan& P, const Buffers& B, int F, cudaStream_t s);
 void launchDescribe(const FramePlan& P, const Buffers& B, int F, int lap0, int lap1, cudaStream_t s);
 size_t quadtreeSmemBytes(const FramePlan& P);
