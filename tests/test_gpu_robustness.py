@@ -3,7 +3,7 @@
 sizes, results compared with the oracle, one batch repeated ten times for bit-identical output - runs with 256-byte guard bands behind
 every device buffer of the handles (ORBX_GUARD=1, orbx_debug_check_guards) and under the runtime switches that select the other code
 paths: 256-thread strips, a tiny strip list (every strip overflows into the per-cell kernel), the per-cell FAST alone, ordinary-load
-staging instead of TMA."""
+staging instead of TMA, the other describe kernels, the split quadtree pipeline, the matcher's CTA widths, stream priorities."""
 import os
 import subprocess
 import sys
@@ -16,7 +16,11 @@ pytestmark = pytest.mark.gpu
 
 ENVS = [{}, {"ORBX_STRIP_THREADS": "256"}, {"ORBX_STRIP_LIST": "256"}, {"ORBX_STRIP_MAXW": "235", "ORBX_STRIP_LIST": "4096", "ORBX_STRIP_MINB": "8"},
         {"ORBX_STRIP_MINB": "12", "ORBX_STRIP_MAXW": "75"}, {"ORBX_FAST_STRIP": "0"}, {"ORBX_FAST_TMA": "0"},
-        {"ORBX_MATCH_R": "0"}, {"ORBX_BLUR_MODE": "3"}]
+        {"ORBX_MATCH_R": "0"}, {"ORBX_BLUR_MODE": "3"},
+        # round 2, later: the round-1 describe kernel and the bulk-copy form of the pipelined one, the split quadtree pipeline (on its own and
+        # with every strip overflowing, i.e. the gated late pass), narrow CTAs in the consecutive matcher, the main stream above the auxiliary
+        {"ORBX_DESC_MODE": "0"}, {"ORBX_DESC_MODE": "2"}, {"ORBX_PIPE": "3"}, {"ORBX_PIPE": "3", "ORBX_STRIP_LIST": "256"},
+        {"ORBX_MATCH_NT": "64"}, {"ORBX_PRIO": "1"}]
 
 
 @pytest.mark.parametrize("extra", ENVS, ids=lambda e: "+".join(f"{k}={v}" for k, v in e.items()) or "default")
