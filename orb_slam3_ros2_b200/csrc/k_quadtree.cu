@@ -208,6 +208,11 @@ struct QtShared {
     int* cellOff;
 };
 
+#ifndef ORBX_QT_UNROLL
+#define ORBX_QT_UNROLL 4
+#endif
+constexpr int kCandUnroll = ORBX_QT_UNROLL;
+
 template <int kQT>
 __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ FramePlan P, const uint32_t* __restrict__ cand,
                                                       const int* __restrict__ cellCnt, uint32_t* __restrict__ gath,
@@ -269,9 +274,26 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
     {
         const uint32_t* slots = cand + (size_t)f * P.candWords + L.candOff;
         const int warp = tid >> 5, lane = tid & 31;
-        for (int c = warp; c < nCells; c += kQT / 32) {
-            const int b = S.cellOff[c], e = (c + 1 < nCells) ? S.cellOff[c + 1] : n;
-            for (int k = lane; k < e - b; k += 32) g[b + k] = slots[(size_t)c * L.cellCap + k];
+        // four cells per trip, the loads of all four first (a cell rarely holds more than 32 candidates: the tail loop is for those)
+        constexpr int kW = kQT / 32;
+        for (int c0 = warp; c0 < nCells; c0 += 4 * kW) {
+            int bb[4], cnt[4];
+            uint32_t v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int c = c0 + u * kW;
+                bb[u] = 0; cnt[u] = 0; v[u] = 0u;
+                if (c < nCells) {
+                    bb[u] = S.cellOff[c];
+                    cnt[u] = ((c + 1 < nCells) ? S.cellOff[c + 1] : n) - bb[u];
+                    if (lane < cnt[u]) v[u] = slots[(size_t)c * L.cellCap + lane];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (lane < cnt[u]) g[bb[u] + lane] = v[u];
+                for (int k = lane + 32; k < cnt[u]; k += 32) g[bb[u] + k] = slots[(size_t)(c0 + u * kW) * L.cellCap + k];
+            }
         }
     }
     // ---- roots (:559-602) -----------------------------------------------------------------------------------
@@ -286,11 +308,19 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
         S.cntB[r] = 0;
     }
     __syncthreads();
-    for (int i = tid; i < n; i += kQT) {
-        int r = (int)((float)(g[i] & 0xfff) / hX);  // :585
-        r = min(r, nIni - 1);
-        nid[i] = (uint16_t)r;
-        atomicAdd(&S.cntB[r], 1);
+    for (int i0 = tid; i0 < n; i0 += kCandUnroll * kQT) {
+        uint32_t pts[kCandUnroll];
+#pragma unroll
+        for (int u = 0; u < kCandUnroll; ++u) pts[u] = i0 + u * kQT < n ? g[i0 + u * kQT] : 0u;
+#pragma unroll
+        for (int u = 0; u < kCandUnroll; ++u) {
+            const int i = i0 + u * kQT;
+            if (i >= n) continue;
+            int r = (int)((float)(pts[u] & 0xfff) / hX);  // :585
+            r = min(r, nIni - 1);
+            nid[i] = (uint16_t)r;
+            atomicAdd(&S.cntB[r], 1);
+        }
     }
     __syncthreads();
     for (int r = tid; r < nIni; r += kQT) S.scan[r] = S.cntB[r] > 0;
@@ -305,10 +335,26 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
             S.map[4 * r] = (short)np;
         }
     __syncthreads();
-    for (int i = tid; i < n; i += kQT) {
-        const int np = S.map[4 * nid[i]];
-        nid[i] = (uint16_t)np;
-        if (S.cntA[np] > 1) atomicAdd(&S.ccA[4 * np + quadrantOf(g[i], S.boxA[np])], 1);
+    // (the loops over the candidates take four at a time, loads first: a thread's candidates are independent, but one global round trip
+    // per candidate and round is what the length of a level-0 CTA was made of)
+    for (int i0 = tid; i0 < n; i0 += kCandUnroll * kQT) {
+        int pp[kCandUnroll];
+        uint32_t pts[kCandUnroll];
+#pragma unroll
+        for (int u = 0; u < kCandUnroll; ++u) {
+            const int i = i0 + u * kQT;
+            pp[u] = i < n ? (int)nid[i] : 0;
+            pts[u] = i < n ? g[i] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < kCandUnroll; ++u) {
+            const int i = i0 + u * kQT;
+            if (i < n) {
+                const int np = S.map[4 * pp[u]];
+                nid[i] = (uint16_t)np;
+                if (S.cntA[np] > 1) atomicAdd(&S.ccA[4 * np + quadrantOf(pts[u], S.boxA[np])], 1);
+            }
+        }
     }
     __syncthreads();
 
@@ -410,15 +456,28 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
             }
         }
         __syncthreads();
-        for (int i = tid; i < n; i += kQT) {
-            const int p = nid[i];
-            if (S.rk[p] >= 0) {
-                const uint32_t pt = g[i];
-                const int np = S.map[4 * p + quadrantOf(pt, S.boxA[p])];
-                nid[i] = (uint16_t)np;
-                if (S.cntB[np] > 1) atomicAdd(&S.ccB[4 * np + quadrantOf(pt, S.boxB[np])], 1);
-            } else {
-                nid[i] = (uint16_t)S.map[4 * p];
+        for (int i0 = tid; i0 < n; i0 += kCandUnroll * kQT) {
+            int pp[kCandUnroll];
+            uint32_t pts[kCandUnroll];
+#pragma unroll
+            for (int u = 0; u < kCandUnroll; ++u) {
+                const int i = i0 + u * kQT;
+                pp[u] = i < n ? (int)nid[i] : 0;
+                pts[u] = i < n ? g[i] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < kCandUnroll; ++u) {
+                const int i = i0 + u * kQT;
+                if (i >= n) continue;
+                const int p = pp[u];
+                if (S.rk[p] >= 0) {
+                    const uint32_t pt = pts[u];
+                    const int np = S.map[4 * p + quadrantOf(pt, S.boxA[p])];
+                    nid[i] = (uint16_t)np;
+                    if (S.cntB[np] > 1) atomicAdd(&S.ccB[4 * np + quadrantOf(pt, S.boxB[np])], 1);
+                } else {
+                    nid[i] = (uint16_t)S.map[4 * p];
+                }
             }
         }
         __syncthreads();
@@ -446,7 +505,21 @@ __global__ void __launch_bounds__(kQT) quadtreeKernel(const __grid_constant__ Fr
     unsigned* best = reinterpret_cast<unsigned*>(S.scan);
     for (int p = tid; p < size; p += kQT) best[p] = 0;
     __syncthreads();
-    for (int i = tid; i < n; i += kQT) atomicMax(&best[nid[i]], (g[i] & 0xff000000u) | (0xffffffu - (unsigned)i));
+    for (int i0 = tid; i0 < n; i0 += kCandUnroll * kQT) {
+        int pp[kCandUnroll];
+        uint32_t pts[kCandUnroll];
+#pragma unroll
+        for (int u = 0; u < kCandUnroll; ++u) {
+            const int i = i0 + u * kQT;
+            pp[u] = i < n ? (int)nid[i] : 0;
+            pts[u] = i < n ? g[i] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < kCandUnroll; ++u) {
+            const int i = i0 + u * kQT;
+            if (i < n) atomicMax(&best[pp[u]], (pts[u] & 0xff000000u) | (0xffffffu - (unsigned)i));
+        }
+    }
     __syncthreads();
     for (int p = tid; p < size; p += kQT) {
         const uint32_t pt = g[0xffffffu - (best[p] & 0xffffffu)];
