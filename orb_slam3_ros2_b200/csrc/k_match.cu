@@ -299,31 +299,51 @@ __global__ void stereoBandedKernel(const float* __restrict__ kl, const uint4* __
         nl = min(SB.nl[blockIdx.y], SB.cap); nr = min(SB.nr[blockIdx.y], SB.cap);
         kl += o * 7; kr += o * 7; dl += o * 2; dr += o * 2; bestIdx += o; bestDist += o;
     }
+    // The row band, octave and column of a right keypoint do not depend on the left one: a CTA works them out once per tile of 256 right
+    // keypoints (shared memory, int4 = minr, maxr, octave, uR) and every thread then walks the tile with one broadcast load and five
+    // compares per candidate instead of three global loads, ceilf / floorf and a multiply (right keypoints in ascending index, strict <).
+    __shared__ int4 sR[256];
     const int iL = blockIdx.x * blockDim.x + threadIdx.x;
-    if (iL >= nl) return;
+    const bool live = iL < nl;
     int bd = 100, bi = 0;  // ORBmatcher::TH_HIGH, bestIdxR = 0 (:867-868)
-    const float uL = kl[iL * 7], vL = kl[iL * 7 + 1];
-    const int levelL = __float_as_int(kl[iL * 7 + 5]);
+    float uL = 0.f, vL = 0.f;
+    int levelL = 0;
+    if (live) { uL = kl[iL * 7]; vL = kl[iL * 7 + 1]; levelL = __float_as_int(kl[iL * 7 + 5]); }
     const int row = (int)vL;  // vRowIndices[vL] (:858)
     const float minU = __fsub_rn(uL, maxD), maxU = uL;
-    if (row >= 0 && row < nRows && !(maxU < 0)) {
-        const uint4 a0 = dl[2 * iL], a1 = dl[2 * iL + 1];
-        for (int iR = 0; iR < nr; ++iR) {
+    const bool search = live && row >= 0 && row < nRows && !(maxU < 0);
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+    if (search) { a0 = dl[2 * iL]; a1 = dl[2 * iL + 1]; }
+    for (int t0 = 0; t0 < nr; t0 += 256) {
+        const int nt = min(256, nr - t0);
+        __syncthreads();
+        for (int j = threadIdx.x; j < nt; j += blockDim.x) {
+            const int iR = t0 + j;
             const float uR = kr[iR * 7], vR = kr[iR * 7 + 1];
             const int octR = __float_as_int(kr[iR * 7 + 5]);
             const float r = __fmul_rn(2.0f, sf[octR]);
             const int maxr = (int)ceilf(__fadd_rn(vR, r)), minr = (int)floorf(__fsub_rn(vR, r));  // :833-834
-            if (row < minr || row > maxr) continue;
-            if (octR < levelL - 1 || octR > levelL + 1) continue;
+            sR[j] = make_int4(minr, maxr, octR, __float_as_int(uR));
+        }
+        __syncthreads();
+        if (!search) continue;
+        for (int j = 0; j < nt; ++j) {
+            const int4 e = sR[j];
+            if (row < e.x || row > e.y) continue;
+            if (e.z < levelL - 1 || e.z > levelL + 1) continue;
+            const float uR = __int_as_float(e.w);
             if (!(uR >= minU && uR <= maxU)) continue;
+            const int iR = t0 + j;
             const uint4 b0 = dr[2 * iR], b1 = dr[2 * iR + 1];
             const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
                           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
             if (d < bd) { bd = d; bi = iR; }
         }
     }
-    bestIdx[iL] = bi;
-    bestDist[iL] = bd;
+    if (live) {
+        bestIdx[iL] = bi;
+        bestDist[iL] = bd;
+    }
 }
 
 }  // namespace
