@@ -13,6 +13,7 @@
 // Chunks of the database (< 2^23 rows) go to different CTAs; their per-chunk top-2 are written as 64-bit keys
 // (distance << 40 | global row) and reduced by mergeKernel — the same kernel that merges the per-rank candidates
 // after the NCCL all-gather of the sharded path.
+#include <algorithm>
 #include <cstdlib>
 
 #include "orbx_internal.cuh"
@@ -346,6 +347,98 @@ __global__ void stereoBandedKernel(const float* __restrict__ kl, const uint4* __
     }
 }
 
+
+// ---- the same search over ROW LISTS (Frame.cc:820-838 builds vRowIndices the same way): a right keypoint enters the list of every image
+// row of its band; a left keypoint then only meets the right keypoints of its own row (about 2 % of them on KITTI frames).  The lists
+// are filled with atomics, i.e. in no particular order: the result does not depend on it, because "first strict minimum in ascending
+// index" == the minimum of distance << 20 | index.  Scratch per pair: cnt / start / fill [nRows + 1] ints, the right keypoints' records
+// (minr, maxr, octave, uR) and the lists (cap x bandMax ints).
+struct StereoRows {
+    int* cnt; int* start; int* fill;  // [pairs][nRows + 1]
+    int4* rt;                          // [pairs][cap]
+    int* list;                         // [pairs][cap * bandMax]
+    int nRows, cap, bandMax;
+};
+__global__ void stereoBandKernel(const float* __restrict__ kr, int nr, const float* __restrict__ sf, const StereoBatch SB, StereoRows R, int fillPass) {
+    const int pair = blockIdx.y;
+    if (SB.nr) { nr = min(SB.nr[pair], SB.cap); kr += (size_t)pair * SB.cap * 7; }
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nr) return;
+    int4 e;
+    if (!fillPass) {
+        const float uR = kr[j * 7], vR = kr[j * 7 + 1];
+        const int octR = __float_as_int(kr[j * 7 + 5]);
+        const float r = __fmul_rn(2.0f, sf[octR]);
+        e = make_int4((int)floorf(__fsub_rn(vR, r)), (int)ceilf(__fadd_rn(vR, r)), octR, __float_as_int(uR));  // :833-834
+        R.rt[(size_t)pair * R.cap + j] = e;
+    } else {
+        e = R.rt[(size_t)pair * R.cap + j];
+    }
+    const int r0 = max(e.x, 0), r1 = min(e.y, R.nRows - 1);
+    int* cnt = (fillPass ? R.fill : R.cnt) + (size_t)pair * (R.nRows + 1);
+    const int* start = R.start + (size_t)pair * (R.nRows + 1);
+    int* list = R.list + (size_t)pair * R.cap * R.bandMax;
+    for (int r = r0; r <= r1; ++r) {
+        const int k = atomicAdd(&cnt[r], 1);
+        if (fillPass) list[start[r] + k] = j;
+    }
+}
+__global__ void __launch_bounds__(256) stereoRowScanKernel(StereoRows R) {
+    __shared__ int sPart[256];
+    const int pair = blockIdx.x, tid = threadIdx.x;
+    const int* cnt = R.cnt + (size_t)pair * (R.nRows + 1);
+    int* start = R.start + (size_t)pair * (R.nRows + 1);
+    const int per = (R.nRows + 255) / 256, b = min(tid * per, R.nRows), e = min(b + per, R.nRows);
+    int sum = 0;
+    for (int r = b; r < e; ++r) sum += cnt[r];
+    sPart[tid] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0;
+        for (int t = 0; t < 256; ++t) { const int v = sPart[t]; sPart[t] = acc; acc += v; }
+        start[R.nRows] = acc;
+    }
+    __syncthreads();
+    int acc = sPart[tid];
+    for (int r = b; r < e; ++r) { start[r] = acc; acc += cnt[r]; }
+}
+__global__ void stereoRowMatchKernel(const float* __restrict__ kl, const uint4* __restrict__ dl, int nl, const uint4* __restrict__ dr,
+                                     float maxD, int* __restrict__ bestIdx, int* __restrict__ bestDist, const StereoBatch SB, StereoRows R) {
+    const int pair = blockIdx.y;
+    if (SB.nl) {
+        const size_t o = (size_t)pair * SB.cap;
+        nl = min(SB.nl[pair], SB.cap);
+        kl += o * 7; dl += o * 2; dr += o * 2; bestIdx += o; bestDist += o;
+    }
+    const int iL = blockIdx.x * blockDim.x + threadIdx.x;
+    if (iL >= nl) return;
+    const float uL = kl[iL * 7], vL = kl[iL * 7 + 1];
+    const int levelL = __float_as_int(kl[iL * 7 + 5]);
+    const int row = (int)vL;  // vRowIndices[vL] (:858)
+    const float minU = __fsub_rn(uL, maxD), maxU = uL;
+    uint32_t best = (100u << 20);  // ORBmatcher::TH_HIGH, bestIdxR = 0 (:867-868)
+    if (row >= 0 && row < R.nRows && !(maxU < 0)) {
+        const uint4 a0 = dl[2 * iL], a1 = dl[2 * iL + 1];
+        const int* start = R.start + (size_t)pair * (R.nRows + 1);
+        const int* list = R.list + (size_t)pair * R.cap * R.bandMax;
+        const int4* rt = R.rt + (size_t)pair * R.cap;
+        const int tb = start[row], te = start[row + 1];
+        for (int t = tb; t < te; ++t) {
+            const int iR = list[t];
+            const int4 e = rt[iR];
+            if (e.z < levelL - 1 || e.z > levelL + 1) continue;
+            const float uR = __int_as_float(e.w);
+            if (!(uR >= minU && uR <= maxU)) continue;
+            const uint4 b0 = dr[2 * iR], b1 = dr[2 * iR + 1];
+            const uint32_t d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                               __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+            best = min(best, (d << 20) | (uint32_t)iR);
+        }
+    }
+    bestIdx[iL] = (int)(best & 0xfffffu);
+    bestDist[iL] = (int)(best >> 20);
+}
+
 }  // namespace
 
 // How the database is cut into chunks: enough CTAs to fill the GPU a few times over, chunk < 2^23 rows.
@@ -448,12 +541,44 @@ void launchMatchConsecutive(const uint8_t* dDesc, const int* dN, int F, int cap,
     countLaunch();
 }
 
+size_t stereoRowScratchBytes(int pairs, int cap, int nRows, int bandMax) {
+    return (size_t)pairs * ((size_t)3 * (nRows + 1) * 4 + (size_t)cap * 16 + (size_t)cap * bandMax * 4) + 256;
+}
+
 void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
                         const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s,
-                        const StereoBatch* batch) {
+                        const StereoBatch* batch, void* rowScratch, int bandMax) {
     const StereoBatch SB = batch ? *batch : StereoBatch{};
     if (batch) nl = batch->cap;
     if (nl <= 0) return;
+    const int pairs = batch ? batch->frames : 1, cap = batch ? batch->cap : std::max(nr, 1);
+    // ORBX_STEREO_ROWS=0: the all-pairs kernel (A/B runs); it is also what runs without scratch or with 2^20 keypoints or more
+    static const bool rows = [] { const char* e = std::getenv("ORBX_STEREO_ROWS"); return !(e && e[0] == '0'); }();
+    if (rows && rowScratch && bandMax > 0 && cap < (1 << 20) && nRows > 0) {
+        StereoRows R;
+        uint8_t* p = static_cast<uint8_t*>(rowScratch);
+        const size_t rowInts = (size_t)pairs * (nRows + 1);
+        R.cnt = reinterpret_cast<int*>(p); R.start = R.cnt + rowInts; R.fill = R.start + rowInts;
+        p += ((3 * rowInts * 4 + 15) / 16) * 16;
+        R.rt = reinterpret_cast<int4*>(p); p += (size_t)pairs * cap * 16;
+        R.list = reinterpret_cast<int*>(p);
+        R.nRows = nRows; R.cap = cap; R.bandMax = bandMax;
+        cudaMemsetAsync(R.cnt, 0, 3 * rowInts * 4, s);
+        if (!batch && nr <= 0) {  // no right keypoints: every list is empty
+            stereoRowMatchKernel<<<dim3((nl + 127) / 128, 1), 128, 0, s>>>(static_cast<const float*>(kl), reinterpret_cast<const uint4*>(dl), nl,
+                                                                         reinterpret_cast<const uint4*>(dr), maxD, bi, bd, SB, R);
+            countLaunch();
+            return;
+        }
+        const dim3 gR((cap + 255) / 256, pairs);
+        stereoBandKernel<<<gR, 256, 0, s>>>(static_cast<const float*>(kr), nr, sf, SB, R, 0);
+        stereoRowScanKernel<<<pairs, 256, 0, s>>>(R);
+        stereoBandKernel<<<gR, 256, 0, s>>>(static_cast<const float*>(kr), nr, sf, SB, R, 1);
+        stereoRowMatchKernel<<<dim3((nl + 127) / 128, pairs), 128, 0, s>>>(static_cast<const float*>(kl), reinterpret_cast<const uint4*>(dl), nl,
+                                                                           reinterpret_cast<const uint4*>(dr), maxD, bi, bd, SB, R);
+        countLaunch(4);
+        return;
+    }
     stereoBandedKernel<<<dim3((nl + 127) / 128, batch ? batch->frames : 1), 128, 0, s>>>(
         static_cast<const float*>(kl), reinterpret_cast<const uint4*>(dl), nl, static_cast<const float*>(kr),
         reinterpret_cast<const uint4*>(dr), nr, sf, nRows, maxD, bi, bd, SB);

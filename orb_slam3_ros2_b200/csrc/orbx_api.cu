@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <string>
@@ -1314,7 +1315,11 @@ int orbx_match_stereo_banded(const orbx_keypoint* kps_l, const uint8_t* desc_l, 
         ORBX_CUDA(cudaMemcpyAsync(kr, kps_r, (size_t)nr * 28, cudaMemcpyHostToDevice, s));
     }
     ORBX_CUDA(cudaMemcpyAsync(sf, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, s));
-    launchStereoBanded(kl, dl, nl, kr, dr, nr, sf, n_rows, max_d, bi, bd, s);
+    float sfMax = 1.f;
+    for (int l = 0; l < nlevels; ++l) sfMax = std::max(sfMax, scale_factors[l]);
+    const int bandMax = stereoBandMax(sfMax);
+    ORBX_CUDA(S->k1.reserve(stereoRowScratchBytes(1, std::max(nr, 1), n_rows, bandMax)));
+    launchStereoBanded(kl, dl, nl, kr, dr, nr, sf, n_rows, max_d, bi, bd, s, nullptr, S->k1.p, bandMax);
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(best_idx, bi, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(best_dist, bd, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
@@ -1460,7 +1465,9 @@ int orbx_compute_stereo_matches(orbx_handle left, orbx_handle right, int frame, 
     }
     ORBX_CUDA(cudaMemcpyAsync(sf, left->sf.data(), (size_t)P.nlevels * 4, cudaMemcpyHostToDevice, s));
     const float maxD = bf / b;  // Frame.cc:841
-    launchStereoBanded(kl, dl, nl, kr, dr, nr, sf, P.H, maxD, bi, bd, s);  // nRows = mvImagePyramid[0].rows (:818)
+    const int bandMax = stereoBandMax(*std::max_element(left->sf.begin(), left->sf.end()));
+    ORBX_CUDA(S->k1.reserve(stereoRowScratchBytes(1, std::max(nr, 1), P.H, bandMax)));
+    launchStereoBanded(kl, dl, nl, kr, dr, nr, sf, P.H, maxD, bi, bd, s, nullptr, S->k1.p, bandMax);  // nRows = mvImagePyramid[0].rows (:818)
     launchStereoRefine(P, left->sf.data(), left->isf.data(), left->buf.pyr + (size_t)frame * P.frameBytes,
                        right->buf.pyr + (size_t)frame * right->plan.frameBytes, kl, kr, nl, bi, bd, bf, maxD, ur, dp, sad, s);
     ORBX_CUDA(cudaGetLastError());
@@ -1502,7 +1509,10 @@ int orbx_compute_stereo_matches_batch(orbx_handle left, orbx_handle right, float
     ORBX_CUDA(cudaMemcpyAsync(sf, left->sf.data(), (size_t)P.nlevels * 4, cudaMemcpyHostToDevice, s));
     const StereoBatch SB{left->buf.outN, right->buf.outN, cap, F, (size_t)P.frameBytes, (size_t)right->plan.frameBytes};
     const float maxD = bf / b;  // Frame.cc:841
-    launchStereoBanded(left->buf.outKps, left->buf.outDesc, 0, right->buf.outKps, right->buf.outDesc, 0, sf, P.H, maxD, bi, bd, s, &SB);
+    const int bandMax = stereoBandMax(*std::max_element(left->sf.begin(), left->sf.end()));
+    ORBX_CUDA(S->k1.reserve(stereoRowScratchBytes(F, cap, P.H, bandMax)));
+    launchStereoBanded(left->buf.outKps, left->buf.outDesc, 0, right->buf.outKps, right->buf.outDesc, 0, sf, P.H, maxD, bi, bd, s, &SB,
+                       S->k1.p, bandMax);
     launchStereoRefine(P, left->sf.data(), left->isf.data(), left->buf.pyr, right->buf.pyr, left->buf.outKps, right->buf.outKps, 0, bi,
                        bd, bf, maxD, ur, dp, sad, s, &SB);
     ORBX_CUDA(cudaGetLastError());

@@ -158,7 +158,10 @@ struct StereoBatch {
 };
 void launchStereoBanded(const void* kl, const uint8_t* dl, int nl, const void* kr, const uint8_t* dr, int nr,
                         const float* sf, int nRows, float maxD, int32_t* bi, int32_t* bd, cudaStream_t s,
-                        const StereoBatch* batch = nullptr);
+                        const StereoBatch* batch = nullptr, void* rowScratch = nullptr, int bandMax = 0);
+// scratch of the row-list form of the search (bandMax = stereoBandMax(largest scale factor))
+size_t stereoRowScratchBytes(int pairs, int cap, int nRows, int bandMax);
+inline int stereoBandMax(float sfMax) { return (int)(4.0f * sfMax) + 4; }  // rows of [floor(v - 2 sf), ceil(v + 2 sf)] <= 4 sf + 3
 void launchAccept(int rule, float nnratio, const int32_t* d1, const int32_t* d2, const int64_t* idx2, const int32_t* l1,
                   const int32_t* l2, int n, uint8_t* accept, cudaStream_t s);
 int gridSortCapacity();
