@@ -20,7 +20,7 @@ ENVS = [{}, {"ORBX_STRIP_THREADS": "256"}, {"ORBX_STRIP_LIST": "256"}, {"ORBX_ST
         # round 2, later: the round-1 describe kernel and the bulk-copy form of the pipelined one, the split quadtree pipeline (on its own and
         # with every strip overflowing, i.e. the gated late pass), narrow CTAs in the consecutive matcher, the main stream above the auxiliary
         {"ORBX_DESC_MODE": "0"}, {"ORBX_DESC_MODE": "2"}, {"ORBX_PIPE": "3"}, {"ORBX_PIPE": "3", "ORBX_STRIP_LIST": "256"},
-        {"ORBX_MATCH_NT": "64"}, {"ORBX_PRIO": "1"}]
+        {"ORBX_MATCH_NT": "64"}, {"ORBX_PRIO": "1"}, {"ORBX_STEREO_ROWS": "0"}]
 
 
 @pytest.mark.parametrize("extra", ENVS, ids=lambda e: "+".join(f"{k}={v}" for k, v in e.items()) or "default")
